@@ -1,0 +1,128 @@
+/* ifgen.h - deterministic synthetic IF generator (host + device).
+ *
+ * The reference ships no IF recordings (test/testdata_download_link.txt only
+ * lists URLs), so every parity test and benchmark runs on IF produced here.
+ * One sample is a pure function of (configuration, sample index): the same
+ * code is compiled as plain C for the CPU tools and as a CUDA device function
+ * for the on-GPU generator kernel, so a 30 s / 491 MS stream can be made in
+ * HBM in milliseconds.  CPU and GPU outputs may differ in isolated samples by
+ * one LSB (libm vs CUDA cos/log rounding); parity tests therefore always feed
+ * the SAME byte stream to both the oracle and the CUDA path.
+ *
+ * Signal model per satellite s (t = k / f_sf):
+ *   chips(t) = code_phase + crate*(1 + fd/f_cf)*t + 0.5*crate*fdr/f_cf*t^2
+ *   cyc(t)   = carr_phase + (f_if + fd)*t + 0.5*fdr*t^2
+ *   real : x += A * D[bit] * c[chip] * cos(2*pi*cyc)
+ *   IQ   : x += A * D[bit] * c[chip] * exp(-i*2*pi*cyc)   (the convention the
+ *          reference's complex carrier wipe-off expects, src/sdrcmn.c:653-657)
+ * plus white Gaussian noise of std `sigma` LSB per component, rounded to
+ * nearest and clipped to [-127,127] (signed 8 bit, the format every reference
+ * front end expands to, src/sdr.h:126-127).
+ */
+#ifndef SDRB200_IFGEN_H
+#define SDRB200_IFGEN_H
+
+#include <stdint.h>
+#include <math.h>
+
+#ifdef __CUDACC__
+#define IFGEN_HD __host__ __device__ __forceinline__
+#else
+#define IFGEN_HD static inline
+#endif
+
+#define IFGEN_MAXSAT   16
+#define IFGEN_MAXCLEN  1023
+
+typedef struct {
+    int      prn;              /* code number (index into the code table)   */
+    int      nav_on;           /* 1: 50 bps random data, 0: all +1          */
+    double   cn0_dbhz;         /* carrier-to-noise density                  */
+    double   doppler_hz;       /* carrier Doppler at t=0                    */
+    double   doppler_rate;     /* Hz/s                                      */
+    double   code_phase;       /* chips at sample 0, in [0, clen*bitlen)    */
+    double   carr_phase;       /* cycles at sample 0                        */
+    uint64_t nav_seed;         /* data bit b = hash(nav_seed, b) & 1        */
+} ifgen_sat_t;
+
+typedef struct {
+    double   f_sf, f_if, f_cf; /* sampling, intermediate, RF carrier (Hz)   */
+    double   crate;            /* chip rate (chip/s)                        */
+    double   sigma;            /* noise std per component (LSB)             */
+    int      dtype;            /* 1 real, 2 interleaved I/Q                 */
+    int      clen;             /* chips per code period                     */
+    int      bitlen;           /* code periods per data bit (20 for L1CA)   */
+    int      nsat;
+    uint64_t seed;
+    ifgen_sat_t sat[IFGEN_MAXSAT];
+    double   amp[IFGEN_MAXSAT];/* filled by ifgen_prepare()                 */
+} ifgen_cfg_t;
+
+IFGEN_HD uint64_t ifgen_mix64(uint64_t z)
+{
+    z += 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+
+/* amplitude in LSB for a given C/N0 (see file header) */
+static inline void ifgen_prepare(ifgen_cfg_t *c)
+{
+    int s;
+    for (s = 0; s < c->nsat; s++) {
+        double cn0 = pow(10.0, c->sat[s].cn0_dbhz / 10.0);
+        c->amp[s] = (c->dtype == 2) ? c->sigma * sqrt(2.0 * cn0 / c->f_sf)
+                                    : 2.0 * c->sigma * sqrt(cn0 / c->f_sf);
+    }
+}
+
+IFGEN_HD int ifgen_navbit(uint64_t nav_seed, int64_t bit)
+{
+    return (ifgen_mix64(nav_seed ^ (uint64_t)bit * 0xD6E8FEB86659FD93ULL) & 1) ? 1 : -1;
+}
+
+/* one sample; codes = [nsat][IFGEN_MAXCLEN] of +-1; out[0]=I (or real), out[1]=Q */
+IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
+                           uint64_t k, signed char *out)
+{
+    const double t = (double)k / c->f_sf;
+    double xi = 0.0, xq = 0.0;
+    int s;
+    for (s = 0; s < c->nsat; s++) {
+        const ifgen_sat_t *sv = &c->sat[s];
+        double fd = sv->doppler_hz, fdr = sv->doppler_rate;
+        double chips = sv->code_phase + c->crate * (1.0 + fd / c->f_cf) * t
+                     + 0.5 * c->crate * fdr / c->f_cf * t * t;
+        double per = floor(chips / (double)c->clen);            /* code period # */
+        int    chip = (int)(chips - per * (double)c->clen);
+        double cyc, fr, a;
+        int    d = 1;
+        if (chip >= c->clen) chip = c->clen - 1;
+        if (chip < 0) chip = 0;
+        if (sv->nav_on) d = ifgen_navbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        cyc = sv->carr_phase + (c->f_if + fd) * t + 0.5 * fdr * t * t;
+        fr  = cyc - floor(cyc);
+        a   = c->amp[s] * (double)(d * codes[s * IFGEN_MAXCLEN + chip]);
+        xi += a * cos(6.283185307179586 * fr);
+        if (c->dtype == 2) xq -= a * sin(6.283185307179586 * fr);
+    }
+    {
+        uint64_t h1 = ifgen_mix64(c->seed ^ (2 * k) * 0x9E3779B97F4A7C15ULL);
+        uint64_t h2 = ifgen_mix64(c->seed ^ (2 * k + 1) * 0x9E3779B97F4A7C15ULL);
+        double u1 = ((double)(h1 >> 11) + 1.0) * (1.0 / 9007199254740992.0);
+        double u2 = (double)(h2 >> 11) * (1.0 / 9007199254740992.0);
+        double r  = c->sigma * sqrt(-2.0 * log(u1));
+        double v;
+        xi += r * cos(6.283185307179586 * u2);
+        xq += r * sin(6.283185307179586 * u2);
+        v = rint(xi); if (v > 127.0) v = 127.0; if (v < -127.0) v = -127.0;
+        out[0] = (signed char)v;
+        if (c->dtype == 2) {
+            v = rint(xq); if (v > 127.0) v = 127.0; if (v < -127.0) v = -127.0;
+            out[1] = (signed char)v;
+        }
+    }
+}
+
+#endif /* SDRB200_IFGEN_H */

@@ -1,0 +1,218 @@
+/* sdrb200.h - C ABI of the B200-native GNSS-SDRLIB correlation engine.
+ *
+ * libsdrb200.so exports exactly the symbols declared here: plain pointers and
+ * sizes, no C++ or torch types.  Two layers sit on this header:
+ *
+ *   1. the batched engine (sdrb200_acq_*, sdrb200_trk_*): one launch sequence
+ *      over the whole PRN x Doppler grid / over all channels, IF resident in
+ *      HBM, only peak tuples / log records leave the GPU;
+ *   2. single-call primitives (sdrb200_correlator, sdrb200_pcorrelator, ...)
+ *      with HOST buffers, which libsdrb200_sdrh.so wraps under the reference's
+ *      own sdr.h names (see include/sdrb200_sdrh.h) so that sdrmain.c /
+ *      sdrinit.c / sdrspec.c link unchanged.
+ *
+ * Every entry point cites the reference interface it stands in for
+ * (file:line under the reference's src/).  There is no CPU fallback: when no
+ * CUDA device is usable every compute entry point returns SDRB200_ENODEV.
+ */
+#ifndef SDRB200_H
+#define SDRB200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ status */
+#define SDRB200_OK        0
+#define SDRB200_EINVAL   -1      /* bad argument                              */
+#define SDRB200_ENODEV   -2      /* no usable CUDA device (no CPU fallback)   */
+#define SDRB200_ENOMEM   -3
+#define SDRB200_ECUDA    -4      /* CUDA runtime error (see last_error)       */
+#define SDRB200_ERANGE   -5      /* request outside the data held             */
+
+const char *sdrb200_version(void);
+const char *sdrb200_last_error(void);           /* thread-local message        */
+int  sdrb200_device_count(void);
+int  sdrb200_set_device(int dev);               /* for the calling thread      */
+int  sdrb200_sm_count(void);
+/* number of kernels this library launched in the calling process so far     */
+uint64_t sdrb200_launch_count(void);
+
+/* code types: same numeric values as the reference (src/sdr.h:205-212)      */
+#define SDRB200_CTYPE_L1CA    1
+#define SDRB200_CTYPE_G1      20
+#define SDRB200_CTYPE_L1SBAS  27
+#define SDRB200_DTYPE_REAL    1  /* DTYPEI  (src/sdr.h:126)                   */
+#define SDRB200_DTYPE_IQ      2  /* DTYPEIQ (src/sdr.h:127)                   */
+
+/* ------------------------------------------------------------------- codes
+ * gencode(), src/sdrcode.c:523-539 (L1CA/SBAS 101-154; G1 426-444, which the
+ * reference defines but never dispatches).  code: +-1, returns the length.   */
+int sdrb200_gencode(int prn, int ctype, int8_t *code, double *crate);
+
+/* ------------------------------------------------------- synthetic front end
+ * The reference has no IF data in-tree; see csrc/ifgen.h for the model.
+ * cfg is an ifgen_cfg_t (csrc/ifgen.h); passed as void* to keep this header
+ * free of the generator's types.  k0 = first sample index, n = samples.      */
+int sdrb200_ifgen_host(const void *ifgen_cfg, uint64_t k0, uint64_t n, int8_t *out);
+int sdrb200_ifgen_device(const void *ifgen_cfg, uint64_t k0, uint64_t n, void *d_out,
+                         void *cuda_stream);
+
+/* --------------------------------------------------------- device IF stream
+ * Device-resident counterpart of the reference's ring buffer sdrstat.buff and
+ * rcvgetbuff() (src/sdrrcv.c:406-463, file front end 469-532): samples are
+ * addressed by ABSOLUTE sample index; `capacity` samples are kept (ring).     */
+typedef struct sdrb200_stream sdrb200_stream_t;
+int  sdrb200_stream_create(sdrb200_stream_t **s, int dtype, uint64_t capacity);
+void sdrb200_stream_destroy(sdrb200_stream_t *s);
+/* append n samples of signed 8-bit IF from host memory (H2D copy)            */
+int  sdrb200_stream_push_host(sdrb200_stream_t *s, const int8_t *host, uint64_t n);
+/* append n samples of RTL-SDR offset-binary u8 I/Q, converted on the device
+ * by the rule of rtlsdr_exp(), src/rcv/rtlsdr/rtlsdr.c:136-142               */
+int  sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, uint64_t n);
+/* append n samples produced on the device by the synthetic front end         */
+int  sdrb200_stream_push_ifgen(sdrb200_stream_t *s, const void *ifgen_cfg, uint64_t n);
+uint64_t sdrb200_stream_count(const sdrb200_stream_t *s);  /* samples pushed   */
+/* copy n samples starting at absolute index `buffloc` back to the host
+ * (the rcvgetbuff contract)                                                   */
+int  sdrb200_stream_read(const sdrb200_stream_t *s, uint64_t buffloc, uint64_t n, int8_t *host);
+
+/* -------------------------------------------------------------- acquisition
+ * Batched counterpart of sdracquisition() (src/sdracq.c:14-62), pcorrelator()
+ * (src/sdrcmn.c:738-773), cpxconv() (228-251) and checkacquisition()
+ * (src/sdracq.c:71-95) over all PRNs x Doppler bins in one pass.              */
+typedef struct {
+    double f_sf;             /* sampling frequency (Hz)                        */
+    int    dtype;            /* SDRB200_DTYPE_*                                */
+    int    nsamp;            /* n: samples per code period (sdrch_t.nsamp)     */
+    int    nsampchip;        /* samples per chip (sdrch_t.nsampchip)           */
+    double ctime;            /* code period (s)                                */
+    int    nfreq;            /* Doppler bins                                   */
+    const double *freq;      /* [nfreq] absolute wipe-off frequencies (Hz)     */
+    int    nprn;             /* replicas in the bank                           */
+    int    clen;             /* chips per code                                 */
+    double crate;            /* chip rate                                      */
+    const int8_t *codes;     /* [nprn][clen] +-1                               */
+    int    intg;             /* max non-coherent integrations (acq.intg)       */
+    int    ncoh;             /* code periods per coherent block (1 = reference)*/
+    double threshold;        /* peak-ratio threshold (ACQTH, src/sdr.h:147)    */
+} sdrb200_acq_cfg_t;
+
+typedef struct {
+    int    acquired;         /* flagacq                                        */
+    int    freqi, codei;     /* acq.freqi, acq.acqcodei                        */
+    int    nintg;            /* integrations consumed before the early exit    */
+    double acqfreq;          /* freq[freqi]                                    */
+    double peakr, cn0;       /* acq.peakr, acq.cn0                             */
+    double maxp, maxp2, meanp;
+} sdrb200_acq_result_t;
+
+typedef struct sdrb200_acq sdrb200_acq_t;
+int  sdrb200_acq_create(sdrb200_acq_t **plan, const sdrb200_acq_cfg_t *cfg);
+void sdrb200_acq_destroy(sdrb200_acq_t *plan);
+/* search windows start at absolute sample `buffloc0` of the stream and hop by
+ * ncoh*nsamp per integration, as sdracquisition does; results: [nprn]         */
+int  sdrb200_acq_run(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t buffloc0,
+                     sdrb200_acq_result_t *results);
+/* same, IF taken from host memory: window = (intg+1)*ncoh*nsamp samples; the
+ * H2D copy is part of the call (the end-to-end path)                          */
+int  sdrb200_acq_run_host(sdrb200_acq_t *plan, const int8_t *host_if, uint64_t nsamples,
+                          sdrb200_acq_result_t *results);
+/* launch-only variant for timing: enqueue on the plan's stream, no sync, no
+ * D2H; results are fetched with sdrb200_acq_fetch()                           */
+int  sdrb200_acq_enqueue(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t buffloc0);
+int  sdrb200_acq_fetch(sdrb200_acq_t *plan, sdrb200_acq_result_t *results);
+void *sdrb200_acq_cuda_stream(sdrb200_acq_t *plan);
+/* copy the accumulated power matrix of one PRN to the host: [nfreq][nsamp]
+ * doubles (the `power` argument of sdracquisition)                           */
+int  sdrb200_acq_power(sdrb200_acq_t *plan, int prn_index, double *power);
+
+/* ----------------------------------------------------------------- tracking
+ * Batched counterpart of sdrtracking() (src/sdrtrk.c:15-54), correlator()
+ * (src/sdrcmn.c:687-722), cumsumcorr/pll/dll (src/sdrtrk.c:64-150) and the
+ * bit-sync / nav-bit part of sdrnavigation() (src/sdrnav.c:15-41,198-282),
+ * for all channels, with the loop filters closed on the device.              */
+#define SDRB200_MAXCORRN 16
+#define SDRB200_MAXTAPS  (1 + 2 * SDRB200_MAXCORRN)
+
+typedef struct {             /* sdrtrkprm_t, src/sdr.h:359-368 (coefficients)  */
+    double dllw2, dllaw, pllw2, pllaw, fllw;
+} sdrb200_loop_t;
+
+typedef struct {
+    /* channel constants (sdrch_t, src/sdr.h:482-511) */
+    double f_sf, f_if, f_cf, foffset;
+    int    dtype;
+    int    clen;  double crate, ctime;
+    int    nsamp;
+    int    prn;              /* selects the bit-sync rule (src/sdrnav.c:203)    */
+    int    corrn;            /* trk.corrn                                       */
+    int    corrp[SDRB200_MAXCORRN]; /* trk.corrp[] tap offsets (samples)        */
+    int    ne, nl;           /* trk.ne, trk.nl                                  */
+    int    loopms;           /* trk.loopms                                      */
+    int    navrate;          /* nav.rate (code periods per data bit)            */
+    sdrb200_loop_t prm1, prm2;
+    const int8_t *code;      /* [clen] +-1                                      */
+    /* state handed over by acquisition (src/sdracq.c:51-56)                    */
+    uint64_t buffloc;        /* first sample of the first code period           */
+    double   acqfreq;        /* acq.acqfreq                                     */
+} sdrb200_trk_chan_t;
+
+typedef struct {             /* one record per channel per code period          */
+    uint64_t cnt, buffloc;
+    int32_t  currnsamp;
+    int32_t  flagsync, flagloopfilter, swsync, swloop, synci, biti, bit;
+    double   II[SDRB200_MAXTAPS], QQ[SDRB200_MAXTAPS];
+    double   sumI0, sumQ0;
+    double   codefreq, codeErr, codeNco;
+    double   carrfreq, carrErr, carrNco, freqErr;
+    double   remcode, remcarr;
+} sdrb200_trk_rec_t;
+
+typedef struct sdrb200_trk sdrb200_trk_t;
+int  sdrb200_trk_create(sdrb200_trk_t **eng, int nch, const sdrb200_trk_chan_t *chan);
+void sdrb200_trk_destroy(sdrb200_trk_t *eng);
+/* advance every channel by up to nperiods code periods (fewer if the stream
+ * runs out); rec (host, may be NULL): [nch][nperiods]; nrec[nch] = written.    */
+int  sdrb200_trk_run(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nperiods,
+                     sdrb200_trk_rec_t *rec, int *nrec);
+/* launch-only variant for timing (records stay on the device)                  */
+int  sdrb200_trk_enqueue(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nperiods);
+int  sdrb200_trk_sync(sdrb200_trk_t *eng);
+int  sdrb200_trk_reset(sdrb200_trk_t *eng);     /* back to the hand-over state   */
+void *sdrb200_trk_cuda_stream(sdrb200_trk_t *eng);
+
+/* ------------------------------------------- single-call primitives (host I/O)
+ * Same argument meaning as the reference functions named; buffers are HOST
+ * memory, the work runs on the GPU.  Return SDRB200_* (the sdr.h wrappers in
+ * libsdrb200_sdrh.so print and return void like the reference).                */
+int sdrb200_correlator(const int8_t *data, int dtype, double ti, int n, double freq,
+                       double phi0, double crate, double coff, const int *s, int ns,
+                       double *II, double *QQ, double *remc, double *remp,
+                       const short *code, int coden);       /* sdrcmn.c:687-722 */
+int sdrb200_mixcarr(const int8_t *data, int dtype, double ti, int n, double freq,
+                    double phi0, short *II, short *QQ, double *rem); /* 633-669 */
+int sdrb200_rescode(const short *code, int len, double coff, int smax, double ci,
+                    int n, short *rcode, double *rem);               /* 608-621 */
+int sdrb200_dot2x(const short *a1, const short *a2, const short *const *b, int nb,
+                  int n, double *d1, double *d2);   /* dot_21/22/23, 287-354    */
+int sdrb200_cpxfft(float *cpx, int n, int inverse);                  /* 134-175 */
+int sdrb200_cpxcpx(const short *II, const short *QQ, double scale, int n,
+                   float *cpx);                                      /* 185-195 */
+int sdrb200_cpxconv(float *cpxa, const float *cpxb, int m, int n, int flagsum,
+                    double *conv);                                   /* 228-251 */
+int sdrb200_cpxpspec(float *cpx, int n, int flagsum, double *pspec); /* 261-276 */
+int sdrb200_pcorrelator(const int8_t *data, int dtype, double ti, int n,
+                        const double *freq, int nfreq, double crate, int m,
+                        const float *codex, double *P);              /* 738-773 */
+int sdrb200_checkacquisition(const double *P, int nsamp, int nfreq, int nsampchip,
+                             double ctime, double *cn0, double *peakr, int *codei,
+                             int *freqi);                      /* sdracq.c:71-95 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDRB200_H */

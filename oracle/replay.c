@@ -1,0 +1,349 @@
+/* replay.c - deterministic single-threaded replay of the reference's channel
+ * thread (TEST INFRASTRUCTURE; compiled only where /root/reference exists).
+ *
+ * It is compiled against the reference's own sdr.h and calls the reference's
+ * own functions (initsdrch, sdracquisition, sdrtracking, cumsumcorr, pll, dll,
+ * setobsdata, clearcumsumcorr); the only thing restated here is the loop body
+ * of sdrthread() (src/sdrmain.c:247-315) with the sleeps, plotting and log
+ * file removed, and the file front end's ring-buffer feed
+ * (file_pushtomembuf, src/sdrrcv.c:469-495) with memory as the source.
+ *
+ * The same source is linked twice (oracle/Makefile):
+ *   libreplay_ref.so   hot symbols from the reference objects   -> the oracle
+ *   libreplay_b200.so  hot symbols from libsdrb200_sdrh.so      -> drop-in proof
+ *
+ * Link-level adjustments (no reference source is modified):
+ *   -Wl,--wrap=sleepms      the 2 s ACQSLEEP (src/sdracq.c:58) and 1 ms
+ *                           starvation sleep (src/sdrtrk.c:50) become no-ops
+ *   -Wl,--wrap=pcorrelator  counts integrations used before the early exit
+ */
+#include "sdr.h"
+#include "harness.h"
+
+#ifndef OH_IMPL_NAME
+#define OH_IMPL_NAME "reference"
+#endif
+
+const char *oh_impl(void) { return OH_IMPL_NAME; }
+
+/* ---- link-time wrappers ------------------------------------------------ */
+void __wrap_sleepms(int ms) { (void)ms; }
+
+static int g_pcorr_calls = 0;
+#ifndef OH_NO_PCORR_WRAP
+extern void __real_pcorrelator(const char *data, int dtype, double ti, int n,
+                               double *freq, int nfreq, double crate, int m,
+                               cpx_t *codex, double *P);
+void __wrap_pcorrelator(const char *data, int dtype, double ti, int n,
+                        double *freq, int nfreq, double crate, int m,
+                        cpx_t *codex, double *P)
+{
+    g_pcorr_calls++;
+    __real_pcorrelator(data, dtype, ti, n, freq, nfreq, crate, m, codex, P);
+}
+#else
+extern int sdrb200_sdrh_last_nintg(void);
+#endif
+
+/* ---- ring-buffer feed (memory-backed file front end) ------------------- */
+static const signed char *g_src = NULL;
+static uint64_t g_srclen = 0;       /* samples */
+static uint64_t g_ringblocks = 0;   /* blocks allocated in sdrstat.buff */
+static int g_handles = 0;
+
+static void ring_release(void)
+{
+    free(sdrstat.buff);
+    sdrstat.buff = NULL;
+    g_ringblocks = 0;
+}
+
+static int ring_setup(const oh_cfg_t *cfg, const signed char *src, uint64_t nsamples)
+{
+    uint64_t blocks = (nsamples + FILE_BUFFSIZE - 1) / FILE_BUFFSIZE + 2;
+    if (blocks > MEMBUFFLEN) blocks = MEMBUFFLEN;
+    ring_release();
+    sdrstat.buff = (unsigned char *)malloc((size_t)cfg->dtype * FILE_BUFFSIZE * blocks);
+    if (!sdrstat.buff) return -1;
+    g_ringblocks = blocks;
+    g_src = src; g_srclen = nsamples;
+    sdrstat.fendbuffsize = FILE_BUFFSIZE;
+    sdrstat.buffsize = FILE_BUFFSIZE * MEMBUFFLEN;
+    sdrstat.buffcnt = 0;
+    sdrstat.stopflag = 0;
+    return 0;
+}
+
+/* push blocks until buffcnt == target (what file_pushtomembuf does per call) */
+static void ring_feed(const oh_cfg_t *cfg, uint64_t target)
+{
+    const size_t blk = (size_t)cfg->dtype * FILE_BUFFSIZE;
+    while (sdrstat.buffcnt < target) {
+        uint64_t b = sdrstat.buffcnt;
+        unsigned char *dst = &sdrstat.buff[(b % MEMBUFFLEN) % g_ringblocks * blk];
+        uint64_t s0 = b * FILE_BUFFSIZE;
+        size_t have = 0;
+        if (s0 < g_srclen) {
+            uint64_t ns = g_srclen - s0;
+            if (ns > FILE_BUFFSIZE) ns = FILE_BUFFSIZE;
+            have = (size_t)ns * cfg->dtype;
+            memcpy(dst, g_src + s0 * cfg->dtype, have);
+        }
+        if (have < blk) memset(dst + have, 0, blk - have);
+        sdrstat.buffcnt++;
+    }
+}
+
+static void setup_ini(const oh_cfg_t *cfg)
+{
+    memset(&sdrini, 0, sizeof(sdrini));
+    sdrini.fend = FEND_FILE;
+    sdrini.f_cf[0] = cfg->f_cf; sdrini.f_sf[0] = cfg->f_sf; sdrini.f_if[0] = cfg->f_if;
+    sdrini.dtype[0] = cfg->dtype;
+    sdrini.useif1 = 1;
+    sdrini.trkcorrn = cfg->corrn; sdrini.trkcorrd = cfg->corrd; sdrini.trkcorrp = cfg->corrp;
+    sdrini.trkdllb[0] = cfg->dllb[0]; sdrini.trkdllb[1] = cfg->dllb[1];
+    sdrini.trkpllb[0] = cfg->pllb[0]; sdrini.trkpllb[1] = cfg->pllb[1];
+    sdrini.trkfllb[0] = cfg->fllb[0]; sdrini.trkfllb[1] = cfg->fllb[1];
+    if (!g_handles) { openhandles(); g_handles = 1; }
+}
+
+static int sys_of(int ctype)
+{
+    if (ctype == CTYPE_G1) return SYS_GLO;
+    if (ctype == CTYPE_L1SBAS) return SYS_SBS;
+    return SYS_GPS;
+}
+
+/* initsdrch + optional override of the compile-time acquisition grid,
+ * following the grid formula of src/sdrinit.c:633-635 */
+static int channel_init(const oh_cfg_t *cfg, int chno, int prn, int ctype, sdrch_t *sdr)
+{
+    int i;
+    memset(sdr, 0, sizeof(*sdr));
+    if (initsdrch(chno, sys_of(ctype), prn, ctype, cfg->dtype, FTYPE1,
+                  cfg->f_cf, cfg->f_sf, cfg->f_if, sdr) < 0) return -1;
+    if (cfg->acq_intg > 0) sdr->acq.intg = cfg->acq_intg;
+    if (cfg->acq_step > 0.0 && cfg->acq_hband > 0.0) {
+        sdr->acq.hband = cfg->acq_hband;
+        sdr->acq.step = cfg->acq_step;
+        sdr->acq.nfreq = 2 * (int)(cfg->acq_hband / cfg->acq_step) + 1;
+        free(sdr->acq.freq);
+        sdr->acq.freq = (double *)malloc(sizeof(double) * sdr->acq.nfreq);
+        if (!sdr->acq.freq) return -1;
+        for (i = 0; i < sdr->acq.nfreq; i++)
+            sdr->acq.freq[i] = sdr->f_if + ((i - (sdr->acq.nfreq - 1) / 2) * sdr->acq.step)
+                               + sdr->foffset;
+    }
+    return 0;
+}
+
+static uint64_t do_acquire(sdrch_t *sdr, oh_acq_t *o, double *power_out)
+{
+    size_t np = (size_t)sdr->nsamp * sdr->acq.nfreq;
+    double *power = (double *)calloc(sizeof(double), np);   /* src/sdrmain.c:252 */
+    uint64_t buffloc;
+    g_pcorr_calls = 0;
+    buffloc = sdracquisition(sdr, power);
+    o->prn = sdr->prn; o->ctype = sdr->ctype;
+    o->acquired = sdr->flagacq;
+    o->freqi = sdr->acq.freqi; o->codei = sdr->acq.acqcodei;
+    o->acqfreq = sdr->acq.acqfreq; o->peakr = sdr->acq.peakr; o->cn0 = sdr->acq.cn0;
+    o->maxp = power[(size_t)sdr->acq.freqi * sdr->nsamp + sdr->acq.acqcodei];
+#ifndef OH_NO_PCORR_WRAP
+    o->nintg_used = g_pcorr_calls;
+#else
+    o->nintg_used = sdrb200_sdrh_last_nintg();
+#endif
+    o->buffloc = buffloc;
+    if (power_out) memcpy(power_out, power, sizeof(double) * np);
+    free(power);
+    return buffloc;
+}
+
+int oh_acquire(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamples,
+               uint64_t avail, int nprn, const int *prn, const int *ctype,
+               oh_acq_t *out, double *power_out)
+{
+    int i;
+    if (avail % FILE_BUFFSIZE || avail > nsamples) return -2;
+    setup_ini(cfg);
+    if (ring_setup(cfg, if_data, nsamples) < 0) return -1;
+    ring_feed(cfg, avail / FILE_BUFFSIZE);
+    for (i = 0; i < nprn; i++) {
+        sdrch_t *sdr = &sdrch[0];
+        memset(&out[i], 0, sizeof(out[i]));
+        if (channel_init(cfg, 1, prn[i], ctype[i], sdr) < 0) { ring_release(); return -3; }
+        do_acquire(sdr, &out[i],
+                   power_out ? power_out + (size_t)i * sdr->nsamp * sdr->acq.nfreq : NULL);
+        freesdrch(sdr);
+    }
+    ring_release();
+    return 0;
+}
+
+int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamples,
+                 uint64_t avail, int nprn, const int *prn, const int *ctype,
+                 int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked)
+{
+    int i, k, active;
+    uint64_t *buffloc, *cnt, *loopcnt;
+    if (avail % FILE_BUFFSIZE || avail > nsamples || nprn > MAXSAT) return -2;
+    setup_ini(cfg);
+    if (ring_setup(cfg, if_data, nsamples) < 0) return -1;
+    ring_feed(cfg, avail / FILE_BUFFSIZE);
+    buffloc = (uint64_t *)calloc(sizeof(uint64_t), 3 * (size_t)nprn);
+    cnt = buffloc + nprn; loopcnt = cnt + nprn;
+    memset(rec, 0, sizeof(oh_trkrec_t) * (size_t)nprn * nperiods);
+
+    for (i = 0; i < nprn; i++) {
+        sdrch_t *sdr = &sdrch[i];
+        memset(&acq[i], 0, sizeof(acq[i]));
+        ntracked[i] = 0;
+        if (channel_init(cfg, i + 1, prn[i], ctype[i], sdr) < 0) { ring_release(); free(buffloc); return -3; }
+        buffloc[i] = do_acquire(sdr, &acq[i], NULL);
+    }
+
+    /* lock-step tracking: one code period per channel per sweep */
+    do {
+        active = 0;
+        for (i = 0; i < nprn; i++) {
+            sdrch_t *sdr = &sdrch[i];
+            oh_trkrec_t *r;
+            uint64_t need;
+            if (!sdr->flagacq || ntracked[i] >= nperiods) continue;
+            /* stop when the stream cannot supply another full window */
+            if (buffloc[i] + 2 * (uint64_t)sdr->nsamp + 200 > nsamples) continue;
+            need = (buffloc[i] + 2 * (uint64_t)sdr->nsamp) / FILE_BUFFSIZE + 2;
+            if (need > sdrstat.buffcnt) ring_feed(cfg, need);
+
+            sdrtracking(sdr, buffloc[i], cnt[i]);
+            if (!sdr->flagtrk) continue;                 /* cannot happen after the feed */
+            active = 1;
+
+            cumsumcorr(&sdr->trk, sdr->nav.ocode[sdr->nav.ocodei]);
+            sdr->trk.flagloopfilter = 0;
+            if (!sdr->nav.flagsync) {
+                pll(sdr, &sdr->trk.prm1, sdr->ctime);
+                dll(sdr, &sdr->trk.prm1, sdr->ctime);
+                sdr->trk.flagloopfilter = 1;
+            } else if (sdr->nav.swloop) {
+                pll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
+                dll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
+                sdr->trk.flagloopfilter = 2;
+                if (loopcnt[i] % (SNSMOOTHMS / sdr->trk.loopms) == 0)
+                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 1);
+                else
+                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 0);
+                loopcnt[i]++;
+            }
+
+            r = &rec[(size_t)i * nperiods + ntracked[i]];
+            r->cnt = cnt[i]; r->buffloc = buffloc[i]; r->currnsamp = sdr->currnsamp;
+            r->flagsync = sdr->nav.flagsync; r->flagsyncf = sdr->nav.flagsyncf;
+            r->flagtow = sdr->nav.flagtow; r->flagdec = sdr->nav.flagdec;
+            r->flagloopfilter = sdr->trk.flagloopfilter;
+            r->swsync = sdr->nav.swsync; r->swloop = sdr->nav.swloop;
+            r->synci = sdr->nav.synci; r->biti = sdr->nav.biti; r->bit = sdr->nav.bit;
+            for (k = 0; k < 1 + 2 * sdr->trk.corrn && k < OH_MAXTAPS; k++) {
+                r->II[k] = sdr->trk.II[k]; r->QQ[k] = sdr->trk.QQ[k];
+            }
+            r->sumI0 = sdr->trk.sumI[0]; r->sumQ0 = sdr->trk.sumQ[0];
+            r->codefreq = sdr->trk.codefreq; r->codeErr = sdr->trk.codeErr; r->codeNco = sdr->trk.codeNco;
+            r->carrfreq = sdr->trk.carrfreq; r->carrErr = sdr->trk.carrErr; r->carrNco = sdr->trk.carrNco;
+            r->freqErr = sdr->trk.freqErr;
+            r->remcode = sdr->trk.remcode; r->remcarr = sdr->trk.remcarr;
+            r->L0 = sdr->trk.L[0];
+
+            if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
+            cnt[i]++;
+            buffloc[i] += sdr->currnsamp;
+            sdr->trk.buffloc = buffloc[i];
+            ntracked[i]++;
+        }
+    } while (active);
+
+    for (i = 0; i < nprn; i++) freesdrch(&sdrch[i]);
+    ring_release();
+    free(buffloc);
+    return 0;
+}
+
+/* ---- single-function pass-throughs ------------------------------------- */
+void oh_correlator(const signed char *data, int dtype, double ti, int n,
+                   double freq, double phi0, double crate, double coff,
+                   const int *s, int ns, double *II, double *QQ,
+                   double *remc, double *remp, const short *code, int coden)
+{
+    correlator((const char *)data, dtype, ti, n, freq, phi0, crate, coff,
+               (int *)s, ns, II, QQ, remc, remp, (short *)code, coden);
+}
+
+double oh_mixcarr(const signed char *data, int dtype, double ti, int n,
+                  double freq, double phi0, short *II, short *QQ)
+{
+    return mixcarr((const char *)data, dtype, ti, n, freq, phi0, II, QQ);
+}
+
+double oh_rescode(const short *code, int len, double coff, int smax,
+                  double ci, int n, short *rcode)
+{
+    return rescode(code, len, coff, smax, ci, n, rcode);
+}
+
+void oh_pcorrelator(const signed char *data, int dtype, double ti, int n,
+                    const double *freq, int nfreq, double crate, int m,
+                    const float *codex, double *P)
+{
+    if (!g_handles) { openhandles(); g_handles = 1; }
+    pcorrelator((const char *)data, dtype, ti, n, (double *)freq, nfreq, crate, m,
+                (cpx_t *)codex, P);
+}
+
+void oh_cpxfft(float *cpx, int n, int inverse)
+{
+    if (!g_handles) { openhandles(); g_handles = 1; }
+    if (inverse) cpxifft(NULL, (cpx_t *)cpx, n);
+    else         cpxfft(NULL, (cpx_t *)cpx, n);
+}
+
+void oh_cpxconv(float *cpxa, const float *cpxb, int m, int n, int flagsum, double *conv)
+{
+    if (!g_handles) { openhandles(); g_handles = 1; }
+    cpxconv(NULL, NULL, (cpx_t *)cpxa, (cpx_t *)cpxb, m, n, flagsum, conv);
+}
+
+void oh_cpxpspec(float *cpx, int n, int flagsum, double *pspec)
+{
+    if (!g_handles) { openhandles(); g_handles = 1; }
+    cpxpspec(NULL, (cpx_t *)cpx, n, flagsum, pspec);
+}
+
+int oh_gencode(int prn, int ctype, short *code, double *crate)
+{
+    int len = 0;
+    double cr = 0.0;
+    short *c = gencode(prn, ctype, &len, &cr);
+    if (!c) return -1;
+    memcpy(code, c, sizeof(short) * len);
+    if (crate) *crate = cr;
+    free(c);
+    return len;
+}
+
+int oh_codefft(int prn, int ctype, double f_sf, float *xcode, int *nsamp, int *nfft)
+{
+    sdrch_t tmp;
+    oh_cfg_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.f_sf = f_sf; cfg.f_cf = 1575.42e6; cfg.dtype = 1;
+    cfg.corrn = 1; cfg.corrd = 1; cfg.corrp = 1;
+    setup_ini(&cfg);
+    memset(&tmp, 0, sizeof(tmp));
+    if (initsdrch(1, sys_of(ctype), prn, ctype, 1, FTYPE1, cfg.f_cf, f_sf, 0.0, &tmp) < 0) return -1;
+    if (nsamp) *nsamp = tmp.nsamp;
+    if (nfft) *nfft = tmp.acq.nfft;
+    if (xcode) memcpy(xcode, tmp.xcode, sizeof(float) * 2 * (size_t)tmp.acq.nfft);
+    freesdrch(&tmp);
+    return 0;
+}

@@ -1,0 +1,108 @@
+/* nco_check.c - CPU check of csrc/nco_exact.h against the plain sequential
+ * loops it must reproduce (the loops restate src/sdrcmn.c:608-621, 647-668). */
+#include <stdio.h>
+#include <stdlib.h>
+#include "nco_exact.h"
+
+static uint64_t rs;
+static double urand(void)
+{
+    rs = rs * 6364136223846793005ULL + 1442695040888963407ULL;
+    return (double)(rs >> 11) * (1.0 / 9007199254740992.0);
+}
+
+/* returns mismatches; carrier NCO */
+int check_carrier(double freq, double phi0, double ti, int n)
+{
+    static nco_table_t t;
+    double phi, ps, p, prem;
+    int k, bad = 0, hint = 0;
+    nco_carrier_init(freq, phi0, ti, &phi, &ps);
+    if (nco_walk(phi, ps, n, 0.0, &t)) return -1;
+    p = phi;
+    for (k = 0; k < n; k++, p += ps) {
+        double v = nco_value(&t, k, &hint);
+        if (v != p) bad++;
+    }
+    if (p != t.x_end) bad++;
+    prem = p * NCO_TWO_PI / 32.0;
+    while (prem > NCO_TWO_PI) prem -= NCO_TWO_PI;
+    if (prem != nco_carrier_rem(t.x_end)) bad++;
+    return bad;
+}
+
+int check_code(double coff, int smax, double ci, int len, int n)
+{
+    static nco_table_t t;
+    double c, c0;
+    int k, bad = 0, hint = 0, N = n + 2 * smax;
+    c0 = nco_code_init(coff, smax, ci, len);
+    if (nco_walk(c0, ci, N, (double)len, &t)) return -1;
+    c = coff;
+    c -= smax * ci;
+    c -= floor(c / len) * len;
+    if (c != c0) bad++;
+    for (k = 0; k < N; k++, c += ci) {
+        double v;
+        if (c >= len) c -= len;
+        v = nco_value(&t, k, &hint);
+        if (v != c) bad++;
+    }
+    if (c != t.x_end) bad++;
+    if (c - smax * ci != nco_code_rem(t.x_end, smax, ci)) bad++;
+    return bad;
+}
+
+int max_segments = 0;
+
+/* mode 0: IF-style carrier (fs/4 +- doppler), 1: baseband carrier (+-10 kHz),
+ * 2: code 16.368 MS/s, 3: code 2.048 MS/s, 4: adversarial steps with short mantissas */
+int fuzz(unsigned long long seed, int iters, int mode)
+{
+    int i, bad = 0;
+    rs = seed;
+    for (i = 0; i < iters; i++) {
+        int r;
+        if (mode == 0) {
+            double fs = 16.368e6, f = 4.092e6 + (urand() - 0.5) * 2e4;
+            r = check_carrier(f, urand() * NCO_TWO_PI, 1.0 / fs, 16360 + (int)(urand() * 20));
+        } else if (mode == 1) {
+            double fs = 2.048e6, f = (urand() - 0.5) * 2e4;
+            r = check_carrier(f, urand() * NCO_TWO_PI, 1.0 / fs, 2040 + (int)(urand() * 20));
+        } else if (mode == 2) {
+            double fs = 16.368e6, cr = 1.023e6 + (urand() - 0.5) * 20.0;
+            r = check_code(urand() * 0.07, 18, (1.0 / fs) * cr, 1023, 16360 + (int)(urand() * 20));
+        } else if (mode == 3) {
+            double fs = 2.048e6, cr = 1.023e6 + (urand() - 0.5) * 20.0;
+            r = check_code(urand() * 1023.0, 4, (1.0 / fs) * cr, 1023, 2040 + (int)(urand() * 20));
+        } else {
+            /* steps with few mantissa bits force exact ties in many binades */
+            double step = ldexp(floor(urand() * 4096.0) + 0.5, -(int)(urand() * 12));
+            double x0 = ldexp(floor(urand() * 65536.0), -(int)(urand() * 20));
+            if (urand() < 0.3) step = -step;
+            {
+                static nco_table_t t;
+                double p = x0; int k, n = 3000 + (int)(urand() * 3000), hint = 0;
+                r = 0;
+                if (nco_walk(x0, step, n, 0.0, &t)) r = -1;
+                else {
+                    for (k = 0; k < n; k++, p += step) if (nco_value(&t, k, &hint) != p) r++;
+                    if (p != t.x_end) r++;
+                    if (t.nseg > max_segments) max_segments = t.nseg;
+                }
+            }
+        }
+        if (r) { bad++; if (bad < 5) fprintf(stderr, "mismatch mode %d iter %d r=%d\n", mode, i, r); }
+    }
+    return bad;
+}
+
+#ifdef NCO_MAIN
+int main(int argc, char **argv)
+{
+    int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
+    for (m = 0; m < 5; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
+    printf("max segments (mode 4) %d\n", max_segments);
+    return bad != 0;
+}
+#endif
