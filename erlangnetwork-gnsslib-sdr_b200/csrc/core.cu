@@ -1,0 +1,259 @@
+/* core.cu - device management, error reporting, the device-resident IF stream
+ * and the synthetic front end of libsdrb200.
+ *
+ * The IF stream replaces the reference's host ring buffer sdrstat.buff and
+ * rcvgetbuff() (src/sdrrcv.c:406-463; file front end 469-532): samples keep
+ * their ABSOLUTE index, `capacity` samples are retained, and the first
+ * SDRB200_STREAM_GUARD bytes of the ring are mirrored behind its end so that a
+ * kernel can read any window shorter than the guard with plain linear
+ * (vectorised) loads even when the window wraps.
+ */
+#include <stdio.h>
+#include <stdarg.h>
+#include <stdlib.h>
+#include <string.h>
+#include <atomic>
+#include "sdrb200_internal.h"
+#include "ifgen.h"
+
+static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+extern "C" void sdrb200_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+extern "C" const char *sdrb200_last_error(void) { return g_err; }
+extern "C" const char *sdrb200_version(void) { return "sdrb200 0.1 (sm_100a)"; }
+extern "C" void sdrb200_count_launch(int n) { g_launches.fetch_add((uint64_t)n); }
+extern "C" uint64_t sdrb200_launch_count(void) { return g_launches.load(); }
+
+extern "C" int sdrb200_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+extern "C" int sdrb200_ensure_device(void)
+{
+    if (sdrb200_device_count() < 1) {
+        sdrb200_set_error("no CUDA device: libsdrb200 has no CPU fallback");
+        return SDRB200_ENODEV;
+    }
+    return SDRB200_OK;
+}
+extern "C" int sdrb200_set_device(int dev)
+{
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    SDRB200_CUDA_TRY(cudaSetDevice(dev));
+    return SDRB200_OK;
+}
+extern "C" int sdrb200_sm_count(void)
+{
+    int dev = 0, n = 0;
+    if (sdrb200_ensure_device()) return 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+    return n;
+}
+
+/* ------------------------------------------------------------ IF stream */
+extern "C" int sdrb200_stream_create(sdrb200_stream_t **out, int dtype, uint64_t capacity)
+{
+    if (!out || (dtype != 1 && dtype != 2) || capacity == 0) {
+        sdrb200_set_error("stream_create: bad argument"); return SDRB200_EINVAL;
+    }
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    sdrb200_stream_t *s = (sdrb200_stream_t *)calloc(1, sizeof(*s));
+    if (!s) return SDRB200_ENOMEM;
+    s->dtype = dtype; s->capacity = capacity;
+    cudaStream_t st;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) { free(s); return SDRB200_ECUDA; }
+    s->cuda_stream = st;
+    size_t bytes = (size_t)capacity * dtype + SDRB200_STREAM_GUARD;
+    cudaError_t e = cudaMalloc((void **)&s->d_buf, bytes);
+    if (e != cudaSuccess) {
+        sdrb200_set_error("stream_create: cudaMalloc(%zu) -> %s", bytes, cudaGetErrorString(e));
+        cudaStreamDestroy(st); free(s); return SDRB200_ENOMEM;
+    }
+    cudaMemsetAsync(s->d_buf, 0, bytes, st);
+    cudaStreamSynchronize(st);
+    *out = s;
+    return SDRB200_OK;
+}
+
+extern "C" void sdrb200_stream_destroy(sdrb200_stream_t *s)
+{
+    if (!s) return;
+    cudaFree(s->d_buf);
+    cudaStreamDestroy((cudaStream_t)s->cuda_stream);
+    free(s);
+}
+
+extern "C" uint64_t sdrb200_stream_count(const sdrb200_stream_t *s) { return s ? s->count : 0; }
+
+/* after bytes [off, off+len) of the ring were written, refresh the guard mirror */
+static int mirror_guard(sdrb200_stream_t *s, size_t off, size_t len)
+{
+    size_t ring = (size_t)s->capacity * s->dtype;
+    if (off >= SDRB200_STREAM_GUARD) return SDRB200_OK;
+    size_t m = len; if (off + m > SDRB200_STREAM_GUARD) m = SDRB200_STREAM_GUARD - off;
+    if (off + m > ring) m = ring - off;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(s->d_buf + ring + off, s->d_buf + off, m,
+                                     cudaMemcpyDeviceToDevice, (cudaStream_t)s->cuda_stream));
+    return SDRB200_OK;
+}
+
+/* generic chunked append; src_kind 0: host int8, 1: host rtlsdr u8, 2: ifgen */
+__global__ void k_rtlsdr_expand(const uint8_t *__restrict__ in, int8_t *__restrict__ out, size_t n)
+{
+    /* rtlsdr_exp: (char)(buf-127.5), src/rcv/rtlsdr/rtlsdr.c:136-142.
+     * float subtraction then C truncation toward zero.                          */
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = (int8_t)(int)((float)in[i] - 127.5f);
+}
+
+__global__ void k_ifgen(ifgen_cfg_t cfg, const signed char *__restrict__ codes,
+                        uint64_t k0, uint64_t n, signed char *__restrict__ out)
+{
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        signed char v[2];
+        ifgen_sample(&cfg, codes, k0 + i, v);
+        if (cfg.dtype == 2) { out[2 * i] = v[0]; out[2 * i + 1] = v[1]; }
+        else out[i] = v[0];
+    }
+}
+
+static int ifgen_codes(const ifgen_cfg_t *c, signed char *codes /*[MAXSAT][MAXCLEN]*/)
+{
+    memset(codes, 0, (size_t)IFGEN_MAXSAT * IFGEN_MAXCLEN);
+    if (c->nsat < 0 || c->nsat > IFGEN_MAXSAT || c->clen < 1 || c->clen > IFGEN_MAXCLEN) {
+        sdrb200_set_error("ifgen: bad nsat/clen"); return SDRB200_EINVAL;
+    }
+    for (int s = 0; s < c->nsat; s++) {
+        int8_t tmp[IFGEN_MAXCLEN];
+        int len = (c->clen == 511) ? sdrb200_gencode_g1(tmp) : sdrb200_gencode_l1ca(c->sat[s].prn, tmp);
+        if (len != c->clen) { sdrb200_set_error("ifgen: code length mismatch"); return SDRB200_EINVAL; }
+        memcpy(codes + (size_t)s * IFGEN_MAXCLEN, tmp, (size_t)len);
+    }
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_ifgen_host(const void *vcfg, uint64_t k0, uint64_t n, int8_t *out)
+{
+    if (!vcfg || !out) return SDRB200_EINVAL;
+    ifgen_cfg_t c = *(const ifgen_cfg_t *)vcfg;
+    static thread_local signed char codes[IFGEN_MAXSAT * IFGEN_MAXCLEN];
+    int rc = ifgen_codes(&c, codes);
+    if (rc) return rc;
+    ifgen_prepare(&c);
+    for (uint64_t i = 0; i < n; i++) ifgen_sample(&c, codes, k0 + i, (signed char *)out + i * c.dtype);
+    return SDRB200_OK;
+}
+
+static int ifgen_launch(const ifgen_cfg_t *cfg_in, uint64_t k0, uint64_t n, void *d_out, cudaStream_t st)
+{
+    ifgen_cfg_t c = *cfg_in;
+    signed char codes[IFGEN_MAXSAT * IFGEN_MAXCLEN];
+    int rc = ifgen_codes(&c, codes);
+    if (rc) return rc;
+    ifgen_prepare(&c);
+    signed char *d_codes = NULL;
+    SDRB200_CUDA_TRY(cudaMallocAsync((void **)&d_codes, sizeof(codes), st));
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(d_codes, codes, sizeof(codes), cudaMemcpyHostToDevice, st));
+    /* codes[] is on the stack: make the copy complete before returning */
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(st));
+    int blocks = 148 * 8;
+    k_ifgen<<<blocks, 256, 0, st>>>(c, d_codes, k0, n, (signed char *)d_out);
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    SDRB200_CUDA_TRY(cudaFreeAsync(d_codes, st));
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_ifgen_device(const void *vcfg, uint64_t k0, uint64_t n, void *d_out, void *cuda_stream)
+{
+    if (!vcfg || !d_out) return SDRB200_EINVAL;
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    return ifgen_launch((const ifgen_cfg_t *)vcfg, k0, n, d_out, (cudaStream_t)cuda_stream);
+}
+
+static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifgen_cfg_t *gen, uint64_t n)
+{
+    if (!s || (kind != 2 && !src)) { sdrb200_set_error("stream_push: bad argument"); return SDRB200_EINVAL; }
+    cudaStream_t st = (cudaStream_t)s->cuda_stream;
+    const size_t bps = (size_t)s->dtype;
+    uint64_t done = 0;
+    while (done < n) {
+        uint64_t pos = s->count % s->capacity;
+        uint64_t chunk = n - done;
+        if (chunk > s->capacity - pos) chunk = s->capacity - pos;
+        int8_t *dst = s->d_buf + pos * bps;
+        if (kind == 0) {
+            SDRB200_CUDA_TRY(cudaMemcpyAsync(dst, (const int8_t *)src + done * bps, chunk * bps,
+                                             cudaMemcpyHostToDevice, st));
+        } else if (kind == 1) {
+            uint8_t *tmp = NULL;
+            SDRB200_CUDA_TRY(cudaMallocAsync((void **)&tmp, chunk * bps, st));
+            SDRB200_CUDA_TRY(cudaMemcpyAsync(tmp, (const uint8_t *)src + done * bps, chunk * bps,
+                                             cudaMemcpyHostToDevice, st));
+            k_rtlsdr_expand<<<148 * 4, 256, 0, st>>>(tmp, dst, chunk * bps);
+            sdrb200_count_launch(1);
+            SDRB200_CUDA_TRY(cudaGetLastError());
+            SDRB200_CUDA_TRY(cudaFreeAsync(tmp, st));
+        } else {
+            int rc = ifgen_launch(gen, s->ifgen_next, chunk, dst, st);
+            if (rc) return rc;
+            s->ifgen_next += chunk;
+        }
+        int rc = mirror_guard(s, pos * bps, chunk * bps);
+        if (rc) return rc;
+        s->count += chunk;
+        done += chunk;
+    }
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(st));
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_stream_push_host(sdrb200_stream_t *s, const int8_t *host, uint64_t n)
+{
+    return stream_push(s, 0, host, NULL, n);
+}
+extern "C" int sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, uint64_t n)
+{
+    if (s && s->dtype != 2) { sdrb200_set_error("rtlsdr samples are I/Q (dtype 2)"); return SDRB200_EINVAL; }
+    return stream_push(s, 1, host, NULL, n);
+}
+extern "C" int sdrb200_stream_push_ifgen(sdrb200_stream_t *s, const void *cfg, uint64_t n)
+{
+    if (!cfg) return SDRB200_EINVAL;
+    if (s && ((const ifgen_cfg_t *)cfg)->dtype != s->dtype) { sdrb200_set_error("ifgen dtype != stream dtype"); return SDRB200_EINVAL; }
+    return stream_push(s, 2, NULL, (const ifgen_cfg_t *)cfg, n);
+}
+
+extern "C" int sdrb200_stream_read(const sdrb200_stream_t *s, uint64_t buffloc, uint64_t n, int8_t *host)
+{
+    if (!s || !host) return SDRB200_EINVAL;
+    if (buffloc + n > s->count || s->count - buffloc > s->capacity) {
+        sdrb200_set_error("stream_read: [%llu,+%llu) not held (count %llu, capacity %llu)",
+                          (unsigned long long)buffloc, (unsigned long long)n,
+                          (unsigned long long)s->count, (unsigned long long)s->capacity);
+        return SDRB200_ERANGE;
+    }
+    const size_t bps = (size_t)s->dtype;
+    uint64_t done = 0;
+    while (done < n) {
+        uint64_t pos = (buffloc + done) % s->capacity;
+        uint64_t chunk = n - done;
+        if (chunk > s->capacity - pos) chunk = s->capacity - pos;
+        SDRB200_CUDA_TRY(cudaMemcpy(host + done * bps, s->d_buf + pos * bps, chunk * bps, cudaMemcpyDeviceToHost));
+        done += chunk;
+    }
+    return SDRB200_OK;
+}

@@ -165,6 +165,11 @@ NCO_HD int nco_walk(double x, double step, int32_t count, double wrap, nco_table
         int32_t J;
         if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
         x1 = NCO_ADD(x, step);
+        if (x1 == x) {                      /* step is zero or below half an ulp: */
+            nco_emit(t, k, x, 0.0);         /* the accumulator never moves again  */
+            k = count;
+            break;
+        }
         if (k + 1 >= count || (lim && x1 >= wrap) || !nco_same_binade(x, x1)) {
             nco_emit(t, k, x, 0.0); k += 1; x = x1; continue;
         }

@@ -1,0 +1,537 @@
+/* trk.cu - tracking correlator: single-call primitive and batched engine.
+ *
+ * sdrb200_correlator  <-> correlator()  src/sdrcmn.c:687-722
+ * sdrb200_trk_*       <-> sdrtracking() src/sdrtrk.c:15-54 + cumsumcorr/pll/dll
+ *                         src/sdrtrk.c:64-150 + bit sync src/sdrnav.c:15-41,198-282
+ */
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <mutex>
+#include "sdrb200_internal.h"
+#include "trk_device.cuh"
+
+static std::once_flag g_lut_once;
+static int g_lut_rc = SDRB200_OK;
+
+/* re-derive the carrier table exactly as mixcarr builds it (src/sdrcmn.c:641-646)
+ * and compare with the constants compiled into the kernels */
+static void lut_init(void)
+{
+    static const int8_t kc[32] = SDRB200_COST_INIT, ks[32] = SDRB200_SINT_INIT;
+    const double DPI = 2.0 * 3.1415926535897932;
+    for (int i = 0; i < 32; i++) {
+        short c = (short)floor((cos(DPI / 32 * i) / SDRB200_CSCALE + 0.5));
+        short s = (short)floor((sin(DPI / 32 * i) / SDRB200_CSCALE + 0.5));
+        if (c != kc[i] || s != ks[i]) {
+            sdrb200_set_error("carrier table mismatch at %d: libm gives (%d,%d)", i, c, s);
+            g_lut_rc = SDRB200_EINVAL;
+        }
+    }
+}
+extern "C" int sdrb200_trk_lut_ready(void)
+{
+    std::call_once(g_lut_once, lut_init);
+    return g_lut_rc;
+}
+
+/* ------------------------------------------------------------------------
+ * single-call kernel: one CTA, one code period
+ * out: II[ntap], QQ[ntap], remc, remp  (doubles)
+ * ---------------------------------------------------------------------- */
+template <int DTYPE>
+__global__ void __launch_bounds__(1024, 1)
+k_correlator(const int8_t *__restrict__ data, double ti, int n, double freq, double phi0,
+             double crate, double coff, const int *__restrict__ taps_g, int ns,
+             const int8_t *__restrict__ code_g, int coden, double *__restrict__ out,
+             int *__restrict__ err)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    trk_smem_t *sm = (trk_smem_t *)smem_raw;
+    int *taps = (int *)(smem_raw + sizeof(trk_smem_t));
+    int8_t *rc = (int8_t *)(taps + SDRB200_MAXCORRN);
+
+    if (threadIdx.x == 0) sm->err = 0;
+    for (int i = threadIdx.x; i < coden; i += blockDim.x) sm->codetab[i] = code_g[i];
+    if (threadIdx.x < ns) taps[threadIdx.x] = taps_g[threadIdx.x];
+    __syncthreads();
+    const int smax = taps[ns - 1];                                   /* sdrcmn.c:694 */
+
+    trk_build_tables(sm, DTYPE, ti, n, freq, phi0, crate, coff, smax, coden);
+    __syncthreads();
+    trk_fill_replica(sm, rc, n, smax);
+    __syncthreads();
+    trk_accumulate<DTYPE>(sm, rc, data, n, taps, ns, smax);
+
+    const int ntap = 1 + 2 * ns;
+    if (threadIdx.x < ntap) {
+        out[threadIdx.x]        = (double)(long long)sm->sumI[threadIdx.x] * SDRB200_CSCALE;
+        out[ntap + threadIdx.x] = (double)(long long)sm->sumQ[threadIdx.x] * SDRB200_CSCALE;
+    }
+    if (threadIdx.x == 0) {
+        out[2 * ntap] = sm->remc;
+        out[2 * ntap + 1] = sm->remp;
+        *err = sm->err;
+    }
+}
+
+static size_t corr_smem_bytes(int n, int smax)
+{
+    return sizeof(trk_smem_t) + sizeof(int) * SDRB200_MAXCORRN + (size_t)(n + 2 * smax + 64);
+}
+
+extern "C" int sdrb200_correlator(const int8_t *data, int dtype, double ti, int n, double freq,
+                                  double phi0, double crate, double coff, const int *s, int ns,
+                                  double *II, double *QQ, double *remc, double *remp,
+                                  const short *code, int coden)
+{
+    if (!data || !s || !II || !QQ || !remc || !remp || !code || n < 1 || ns < 1 ||
+        ns > SDRB200_MAXCORRN || coden < 1 || coden > 1024 || (dtype != 1 && dtype != 2)) {
+        sdrb200_set_error("correlator: bad argument"); return SDRB200_EINVAL;
+    }
+    const int smax = s[ns - 1];
+    if (smax < 0) { sdrb200_set_error("correlator: negative tap"); return SDRB200_EINVAL; }
+    const size_t smem = corr_smem_bytes(n, smax);
+    if (smem > 220 * 1024) { sdrb200_set_error("correlator: window of %d samples too long", n); return SDRB200_EINVAL; }
+    const int ntap = 1 + 2 * ns;
+    const size_t nbytes = (size_t)n * dtype;
+    /* device arena: [16 guard][data][32 guard] | code | taps | out | err */
+    const size_t off_data = 256, off_code = off_data + ((nbytes + 64 + 255) & ~(size_t)255);
+    const size_t off_taps = off_code + 1024, off_out = off_taps + 256, off_err = off_out + 1024;
+    const size_t h_out = 2048;
+    sdrb200_ws_t *w = sdrb200_ws(off_err + 256, h_out + 1024 + 256);
+    if (!w) return SDRB200_ENODEV;
+    int rc = sdrb200_trk_lut_ready();
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)w->cuda_stream;
+
+    int8_t *h_code = (int8_t *)(w->h_arena + h_out);
+    for (int i = 0; i < coden; i++) {
+        if (code[i] < -127 || code[i] > 127) { sdrb200_set_error("correlator: code value out of int8 range"); return SDRB200_EINVAL; }
+        h_code[i] = (int8_t)code[i];
+    }
+    int *h_taps = (int *)(w->h_arena + h_out + 1024);
+    memcpy(h_taps, s, sizeof(int) * ns);
+
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(w->d_arena + off_data, data, nbytes, cudaMemcpyHostToDevice, st));
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(w->d_arena + off_code, h_code, coden, cudaMemcpyHostToDevice, st));
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(w->d_arena + off_taps, h_taps, sizeof(int) * ns, cudaMemcpyHostToDevice, st));
+
+    double *d_out = (double *)(w->d_arena + off_out);
+    int *d_err = (int *)(w->d_arena + off_err);
+    if (dtype == 1) {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_correlator<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_correlator<1><<<1, 1024, smem, st>>>((const int8_t *)(w->d_arena + off_data), ti, n, freq, phi0, crate, coff,
+                                              (const int *)(w->d_arena + off_taps), ns,
+                                              (const int8_t *)(w->d_arena + off_code), coden, d_out, d_err);
+    } else {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_correlator<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_correlator<2><<<1, 1024, smem, st>>>((const int8_t *)(w->d_arena + off_data), ti, n, freq, phi0, crate, coff,
+                                              (const int *)(w->d_arena + off_taps), ns,
+                                              (const int8_t *)(w->d_arena + off_code), coden, d_out, d_err);
+    }
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    double *h = (double *)w->h_arena;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(h, d_out, sizeof(double) * (2 * ntap + 2), cudaMemcpyDeviceToHost, st));
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(h + 2 * ntap + 2, d_err, sizeof(int), cudaMemcpyDeviceToHost, st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(st));
+    if (*(int *)(h + 2 * ntap + 2)) { sdrb200_set_error("correlator: NCO segment table overflow"); return SDRB200_ERANGE; }
+    memcpy(II, h, sizeof(double) * ntap);
+    memcpy(QQ, h + ntap, sizeof(double) * ntap);
+    *remc = h[2 * ntap];
+    *remp = h[2 * ntap + 1];
+    return SDRB200_OK;
+}
+
+/* ========================================================================
+ * Batched tracking engine: one CTA per channel, persistent over code periods.
+ * The per-period scalar epilogue restates, on the device:
+ *   sdrtracking bookkeeping      src/sdrtrk.c:31-38 (currnsamp, old* copies)
+ *   sdrnavigation bit sync       src/sdrnav.c:15-41
+ *   checksync / checkbit         src/sdrnav.c:198-233 / 241-282
+ *   cumsumcorr / clearcumsumcorr src/sdrtrk.c:64-86
+ *   pll / dll                    src/sdrtrk.c:94-150
+ *   loop scheduling              src/sdrmain.c:269-312
+ * ====================================================================== */
+#define TRK_NAVSYNCTH 50                       /* NAVSYNCTH, src/sdr.h:157 */
+#define TRK_PI 3.1415926535897932              /* PI, src/sdr.h:103        */
+
+struct trk_chan_dev_t {
+    double f_sf, ti, f_if, f_cf, foffset, crate, ctime, acqfreq;
+    uint64_t buffloc0;
+    int32_t dtype, clen, nsamp, prn, corrn, ne, nl, loopms, navrate, pad;
+    int32_t corrp[SDRB200_MAXCORRN];
+    sdrb200_loop_t prm1, prm2;
+    int8_t code[1024];
+};
+
+struct trk_state_t {
+    uint64_t buffloc, cnt;
+    double codefreq, carrfreq, remcode, remcarr, oldremcode, oldremcarr;
+    double codeNco, codeErr, carrNco, carrErr, freqErr;
+    double II[SDRB200_MAXTAPS], QQ[SDRB200_MAXTAPS], oldI[SDRB200_MAXTAPS], oldQ[SDRB200_MAXTAPS];
+    double sumI[SDRB200_MAXTAPS], sumQ[SDRB200_MAXTAPS], oldsumI[SDRB200_MAXTAPS], oldsumQ[SDRB200_MAXTAPS];
+    /* nav (sdrnav_t subset, src/sdr.h:440-479) */
+    double bitIP;
+    int32_t biti, ocodei, synci, flagsync, swsync, swreset, swloop, navcnt, bit, flagloopfilter;
+    int32_t currnsamp, pad;
+    int32_t bitsync[32];
+};
+
+/* checksync(), src/sdrnav.c:198-233 */
+__device__ static int trk_checksync(double IP, double IPold, trk_state_t *st, int prn, int rate)
+{
+    if (prn > 5) {
+        int corr = 0;
+        for (int i = 0; i < rate - 1; i++) st->bitsync[i] = st->bitsync[i + 1];
+        st->bitsync[rate - 1] = (IP < 0 ? -1 : 1);
+        for (int i = 0; i < rate; i++) corr += st->bitsync[i];      /* overlay code is all ones */
+        if (abs(corr) == rate) { st->synci = st->biti; return 1; }
+    } else {
+        if (IPold * IP < 0) {
+            st->bitsync[st->biti] += 1;
+            int maxv = st->bitsync[0], ind = 0;                     /* maxvi(), sdrcmn.c:417-431 */
+            for (int i = 1; i < rate; i++) if (maxv < st->bitsync[i]) { maxv = st->bitsync[i]; ind = i; }
+            st->synci = ind;
+            if (maxv > TRK_NAVSYNCTH) {
+                st->synci--;
+                if (st->synci < 0) st->synci = rate - 1;
+                return 1;
+            }
+        }
+    }
+    return 0;
+}
+
+/* checkbit(), src/sdrnav.c:241-282 (fbits shift register is kept on the host) */
+__device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int rate)
+{
+    int diffi = st->biti - st->synci;
+    st->swreset = 0; st->swsync = 0;
+    if (diffi == 1 || diffi == -rate + 1) {
+        st->bitIP = IP; st->swreset = 1; st->navcnt = 1;
+    } else {
+        st->bitIP += IP;
+    }
+    st->swloop = (st->navcnt % loopms == 0) ? 1 : 0;
+    if (diffi == 0) {
+        st->bit = (st->bitIP < 0) ? -1 : 1;
+        st->swsync = 1;
+    }
+    st->navcnt++;
+}
+
+/* pll(), src/sdrtrk.c:94-125 */
+__device__ static void trk_pll(trk_state_t *st, const sdrb200_loop_t *prm, double dt, double acqfreq)
+{
+    double IP = st->sumI[0], QP = st->sumQ[0];
+    double oldIP = st->oldsumI[0], oldQP = st->oldsumQ[0];
+    double carrErr, freqErr, f1, f2;
+    if (IP > 0) carrErr = atan2(QP, IP) / TRK_PI;
+    else        carrErr = atan2(-QP, -IP) / TRK_PI;
+    f1 = (IP == 0) ? TRK_PI / 2 : atan(QP / IP);
+    f2 = (oldIP == 0) ? TRK_PI / 2 : atan(oldQP / oldIP);
+    freqErr = f1 - f2;
+    if (freqErr > TRK_PI / 2) freqErr = TRK_PI - freqErr;
+    if (freqErr < -TRK_PI / 2) freqErr = -TRK_PI - freqErr;
+    st->carrNco += prm->pllaw * (carrErr - st->carrErr) + prm->pllw2 * dt * carrErr + prm->fllw * dt * freqErr;
+    st->carrfreq = acqfreq + st->carrNco;
+    st->carrErr = carrErr;
+    st->freqErr = freqErr;
+}
+
+/* dll(), src/sdrtrk.c:133-150 */
+__device__ static void trk_dll(trk_state_t *st, const sdrb200_loop_t *prm, double dt, const trk_chan_dev_t *ch)
+{
+    double IE = st->sumI[ch->ne], IL = st->sumI[ch->nl];
+    double QE = st->sumQ[ch->ne], QL = st->sumQ[ch->nl];
+    double e = sqrt(IE * IE + QE * QE), l = sqrt(IL * IL + QL * QL);
+    double codeErr = (e - l) / (e + l);
+    st->codeNco += prm->dllaw * (codeErr - st->codeErr) + prm->dllw2 * dt * codeErr;
+    st->codefreq = ch->crate - st->codeNco + (st->carrfreq - ch->f_if - ch->foffset) / (ch->f_cf / ch->crate);
+    st->codeErr = codeErr;
+}
+
+/* scalar epilogue of one code period (thread 0): everything sdrtracking and
+ * the sdrthread loop body do around correlator()                              */
+__device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const trk_smem_t *sm,
+                                    sdrb200_trk_rec_t *rec)
+{
+    const int ntap = 1 + 2 * ch->corrn;
+    /* src/sdrtrk.c:35-38: the memcpy length 1+2*corrn*8 bytes covers 2*corrn doubles
+     * (plus one stray byte of the next, which no consumer reads)               */
+    for (int i = 0; i < 2 * ch->corrn; i++) { st->oldI[i] = st->II[i]; st->oldQ[i] = st->QQ[i]; }
+    st->oldremcode = st->remcode;
+    st->oldremcarr = st->remcarr;
+    /* src/sdrtrk.c:40-43: correlator's II (cos sums) lands in trk.QQ, QQ (sin sums) in trk.II */
+    for (int i = 0; i < ntap; i++) {
+        st->QQ[i] = (double)(long long)sm->sumI[i] * SDRB200_CSCALE;
+        st->II[i] = (double)(long long)sm->sumQ[i] * SDRB200_CSCALE;
+    }
+    st->remcode = sm->remc;
+    st->remcarr = sm->remp;
+
+    /* sdrnavigation(), src/sdrnav.c:19-41 */
+    const int rate = ch->navrate;
+    const double cntth = 2000 / (ch->ctime * 1000);
+    st->biti = (int)(st->cnt % (uint64_t)rate);
+    st->ocodei = st->biti - st->synci - 1;
+    if (st->ocodei < 0) st->ocodei += rate;
+    if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
+    if (!st->flagsync && (double)st->cnt > cntth)
+        st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
+    if (st->flagsync) trk_checkbit(st->II[0], ch->loopms, st, rate);
+
+    /* cumsumcorr(), src/sdrtrk.c:64-76 (overlay polarity is +1 for L1CA/SBAS/G1) */
+    for (int i = 0; i < ntap; i++) {
+        st->oldsumI[i] += st->oldI[i]; st->oldsumQ[i] += st->oldQ[i];
+        st->sumI[i] += st->II[i];      st->sumQ[i] += st->QQ[i];
+    }
+    /* src/sdrmain.c:271-280 */
+    st->flagloopfilter = 0;
+    if (!st->flagsync) {
+        trk_pll(st, &ch->prm1, ch->ctime, ch->acqfreq);
+        trk_dll(st, &ch->prm1, ch->ctime, ch);
+        st->flagloopfilter = 1;
+    } else if (st->swloop) {
+        trk_pll(st, &ch->prm2, (double)ch->loopms / 1000, ch->acqfreq);
+        trk_dll(st, &ch->prm2, (double)ch->loopms / 1000, ch);
+        st->flagloopfilter = 2;
+    }
+    if (rec) {
+        rec->cnt = st->cnt; rec->buffloc = st->buffloc; rec->currnsamp = st->currnsamp;
+        rec->flagsync = st->flagsync; rec->flagloopfilter = st->flagloopfilter;
+        rec->swsync = st->swsync; rec->swloop = st->swloop; rec->synci = st->synci;
+        rec->biti = st->biti; rec->bit = st->bit;
+        for (int i = 0; i < ntap; i++) { rec->II[i] = st->II[i]; rec->QQ[i] = st->QQ[i]; }
+        rec->sumI0 = st->sumI[0]; rec->sumQ0 = st->sumQ[0];
+        rec->codefreq = st->codefreq; rec->codeErr = st->codeErr; rec->codeNco = st->codeNco;
+        rec->carrfreq = st->carrfreq; rec->carrErr = st->carrErr; rec->carrNco = st->carrNco;
+        rec->freqErr = st->freqErr; rec->remcode = st->remcode; rec->remcarr = st->remcarr;
+    }
+    /* clearcumsumcorr(), src/sdrtrk.c:77-86, src/sdrmain.c:310-312 */
+    if (st->flagloopfilter)
+        for (int i = 0; i < ntap; i++) { st->oldsumI[i] = 0; st->oldsumQ[i] = 0; st->sumI[i] = 0; st->sumQ[i] = 0; }
+    st->cnt++;
+    st->buffloc += (uint64_t)st->currnsamp;
+}
+
+struct trk_run_smem_t {
+    trk_smem_t t;
+    trk_state_t st;
+    sdrb200_trk_rec_t rec;
+    int32_t taps[SDRB200_MAXCORRN];
+    int32_t go, pad;
+};
+
+template <int DTYPE>
+__global__ void __launch_bounds__(1024, 1)
+k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ states,
+          const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods,
+          sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    trk_run_smem_t *sm = (trk_run_smem_t *)smem_raw;
+    int8_t *rc = (int8_t *)(smem_raw + sizeof(trk_run_smem_t));
+    const trk_chan_dev_t *ch = &chans[blockIdx.x];
+    trk_state_t *st = &sm->st;
+
+    /* load channel state and constants */
+    {
+        const uint32_t *src = (const uint32_t *)&states[blockIdx.x];
+        uint32_t *dst = (uint32_t *)st;
+        for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < ch->clen; i += blockDim.x) sm->t.codetab[i] = ch->code[i];
+        if (threadIdx.x < ch->corrn) sm->taps[threadIdx.x] = ch->corrp[threadIdx.x];
+        if (threadIdx.x == 0) sm->t.err = 0;
+    }
+    __syncthreads();
+    const int ns = ch->corrn;
+    const int smax = sm->taps[ns - 1];
+    int done = 0;
+
+    for (int it = 0; it < nperiods; it++) {
+        if (threadIdx.x == 0) {
+            /* sdrtracking(), src/sdrtrk.c:31-32 */
+            st->currnsamp = nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
+            sm->go = (st->currnsamp > 0 && st->currnsamp <= ch->nsamp + ch->nsamp / 8 &&
+                      st->buffloc + (uint64_t)st->currnsamp <= avail) ? 1 : 0;
+        }
+        __syncthreads();
+        if (!sm->go) break;
+        const int n = st->currnsamp;
+        /* correlator(..., carrfreq, oldremcarr(=remcarr), codefreq, oldremcode(=remcode), ...) */
+        trk_build_tables(&sm->t, DTYPE, ch->ti, n, st->carrfreq, st->remcarr, st->codefreq, st->remcode,
+                         smax, ch->clen);
+        __syncthreads();
+        trk_fill_replica(&sm->t, rc, n, smax);
+        __syncthreads();
+        const int8_t *data = ifbuf + (size_t)(st->buffloc % capacity) * DTYPE;
+        trk_accumulate<DTYPE>(&sm->t, rc, data, n, sm->taps, ns, smax);
+        if (threadIdx.x == 0) trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr);
+        __syncthreads();
+        if (recs) {
+            const uint32_t *src = (const uint32_t *)&sm->rec;
+            uint32_t *dst = (uint32_t *)&recs[(size_t)blockIdx.x * nperiods + it];
+            for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) dst[i] = src[i];
+        }
+        done++;
+    }
+    __syncthreads();
+    {
+        uint32_t *dst = (uint32_t *)&states[blockIdx.x];
+        const uint32_t *src = (const uint32_t *)st;
+        for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += blockDim.x) dst[i] = src[i];
+    }
+    if (threadIdx.x == 0) { nrec[blockIdx.x] = done; if (sm->t.err) *err = 1; }
+}
+
+/* ------------------------------------------------------------- host side */
+struct sdrb200_trk {
+    int nch, dtype, maxn, smax;
+    cudaStream_t st;
+    trk_chan_dev_t *h_chan, *d_chan;
+    trk_state_t *h_state0, *d_state;
+    sdrb200_trk_rec_t *d_rec; size_t rec_cap;       /* records */
+    int *d_nrec, *d_err;
+    int last_nperiods, last_with_rec;
+};
+
+static void trk_init_state(const trk_chan_dev_t *c, trk_state_t *s)
+{
+    memset(s, 0, sizeof(*s));
+    s->buffloc = c->buffloc0;
+    s->carrfreq = c->acqfreq;             /* src/sdracq.c:54-55 */
+    s->codefreq = c->crate;
+}
+
+extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_trk_chan_t *chan)
+{
+    if (!out || nch < 1 || !chan) { sdrb200_set_error("trk_create: bad argument"); return SDRB200_EINVAL; }
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    int rc = sdrb200_trk_lut_ready();
+    if (rc) return rc;
+    sdrb200_trk_t *e = (sdrb200_trk_t *)calloc(1, sizeof(*e));
+    if (!e) return SDRB200_ENOMEM;
+    e->nch = nch; e->dtype = chan[0].dtype;
+    e->h_chan = (trk_chan_dev_t *)calloc(nch, sizeof(trk_chan_dev_t));
+    e->h_state0 = (trk_state_t *)calloc(nch, sizeof(trk_state_t));
+    for (int i = 0; i < nch; i++) {
+        const sdrb200_trk_chan_t *c = &chan[i];
+        trk_chan_dev_t *d = &e->h_chan[i];
+        if (c->dtype != e->dtype || (c->dtype != 1 && c->dtype != 2) || c->corrn < 1 ||
+            c->corrn > SDRB200_MAXCORRN || c->clen < 1 || c->clen > 1024 || !c->code ||
+            c->navrate < 1 || c->navrate > 32 || c->nsamp < 1 || c->loopms < 1 ||
+            c->ne < 0 || c->ne > 2 * c->corrn || c->nl < 0 || c->nl > 2 * c->corrn) {
+            sdrb200_set_error("trk_create: channel %d has unsupported parameters", i);
+            free(e->h_chan); free(e->h_state0); free(e); return SDRB200_EINVAL;
+        }
+        d->f_sf = c->f_sf; d->ti = 1 / c->f_sf;                 /* sdr->ti=1/f_sf, sdrinit.c:598 */
+        d->f_if = c->f_if; d->f_cf = c->f_cf; d->foffset = c->foffset;
+        d->crate = c->crate; d->ctime = c->ctime; d->acqfreq = c->acqfreq; d->buffloc0 = c->buffloc;
+        d->dtype = c->dtype; d->clen = c->clen; d->nsamp = c->nsamp; d->prn = c->prn;
+        d->corrn = c->corrn; d->ne = c->ne; d->nl = c->nl; d->loopms = c->loopms; d->navrate = c->navrate;
+        memcpy(d->corrp, c->corrp, sizeof(d->corrp));
+        d->prm1 = c->prm1; d->prm2 = c->prm2;
+        memcpy(d->code, c->code, c->clen);
+        int maxn = c->nsamp + c->nsamp / 8 + 16;
+        if (maxn > e->maxn) e->maxn = maxn;
+        if (c->corrp[c->corrn - 1] > e->smax) e->smax = c->corrp[c->corrn - 1];
+        trk_init_state(d, &e->h_state0[i]);
+    }
+    if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMalloc((void **)&e->d_chan, sizeof(trk_chan_dev_t) * nch) != cudaSuccess ||
+        cudaMalloc((void **)&e->d_state, sizeof(trk_state_t) * nch) != cudaSuccess ||
+        cudaMalloc((void **)&e->d_nrec, sizeof(int) * (nch + 1)) != cudaSuccess) {
+        sdrb200_set_error("trk_create: device allocation failed");
+        sdrb200_trk_destroy(e); return SDRB200_ENOMEM;
+    }
+    e->d_err = e->d_nrec + nch;
+    cudaMemcpyAsync(e->d_chan, e->h_chan, sizeof(trk_chan_dev_t) * nch, cudaMemcpyHostToDevice, e->st);
+    cudaMemcpyAsync(e->d_state, e->h_state0, sizeof(trk_state_t) * nch, cudaMemcpyHostToDevice, e->st);
+    cudaMemsetAsync(e->d_nrec, 0, sizeof(int) * (nch + 1), e->st);
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    *out = e;
+    return SDRB200_OK;
+}
+
+extern "C" void sdrb200_trk_destroy(sdrb200_trk_t *e)
+{
+    if (!e) return;
+    cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_rec); cudaFree(e->d_nrec);
+    if (e->st) cudaStreamDestroy(e->st);
+    free(e->h_chan); free(e->h_state0); free(e);
+}
+
+extern "C" int sdrb200_trk_reset(sdrb200_trk_t *e)
+{
+    if (!e) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(e->d_state, e->h_state0, sizeof(trk_state_t) * e->nch, cudaMemcpyHostToDevice, e->st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    return SDRB200_OK;
+}
+
+extern "C" void *sdrb200_trk_cuda_stream(sdrb200_trk_t *e) { return e ? (void *)e->st : NULL; }
+
+static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods, int with_rec)
+{
+    if (!e || !s || nperiods < 1) { sdrb200_set_error("trk_run: bad argument"); return SDRB200_EINVAL; }
+    if (s->dtype != e->dtype) { sdrb200_set_error("trk_run: stream dtype mismatch"); return SDRB200_EINVAL; }
+    if (with_rec) {
+        size_t need = (size_t)e->nch * nperiods;
+        if (need > e->rec_cap) {
+            SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+            cudaFree(e->d_rec); e->d_rec = NULL; e->rec_cap = 0;
+            if (cudaMalloc((void **)&e->d_rec, need * sizeof(sdrb200_trk_rec_t)) != cudaSuccess) {
+                cudaGetLastError(); sdrb200_set_error("trk_run: record buffer allocation failed"); return SDRB200_ENOMEM;
+            }
+            e->rec_cap = need;
+        }
+    }
+    size_t smem = sizeof(trk_run_smem_t) + (size_t)(e->maxn + 2 * e->smax + 64);
+    if (smem > 220 * 1024) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
+    sdrb200_trk_rec_t *recs = with_rec ? e->d_rec : NULL;
+    if (e->dtype == 1) {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_trk_run<1><<<e->nch, 1024, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count,
+                                                    nperiods, recs, e->d_nrec, e->d_err);
+    } else {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_trk_run<2><<<e->nch, 1024, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count,
+                                                    nperiods, recs, e->d_nrec, e->d_err);
+    }
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    e->last_nperiods = nperiods; e->last_with_rec = with_rec;
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_trk_enqueue(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods)
+{
+    return trk_launch(e, s, nperiods, 0);
+}
+
+extern "C" int sdrb200_trk_sync(sdrb200_trk_t *e)
+{
+    if (!e) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_trk_run(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
+                               sdrb200_trk_rec_t *rec, int *nrec)
+{
+    int rc = trk_launch(e, s, nperiods, rec != NULL);
+    if (rc) return rc;
+    int h[1 + 4096];
+    if (e->nch > 4096) { sdrb200_set_error("trk_run: too many channels"); return SDRB200_EINVAL; }
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(h, e->d_nrec, sizeof(int) * (e->nch + 1), cudaMemcpyDeviceToHost, e->st));
+    if (rec)
+        SDRB200_CUDA_TRY(cudaMemcpyAsync(rec, e->d_rec, sizeof(sdrb200_trk_rec_t) * (size_t)e->nch * nperiods,
+                                         cudaMemcpyDeviceToHost, e->st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    if (h[e->nch]) { sdrb200_set_error("trk_run: NCO segment table overflow"); return SDRB200_ERANGE; }
+    if (nrec) memcpy(nrec, h, sizeof(int) * e->nch);
+    return SDRB200_OK;
+}

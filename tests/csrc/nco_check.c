@@ -56,7 +56,8 @@ int check_code(double coff, int smax, double ci, int len, int n)
 int max_segments = 0;
 
 /* mode 0: IF-style carrier (fs/4 +- doppler), 1: baseband carrier (+-10 kHz),
- * 2: code 16.368 MS/s, 3: code 2.048 MS/s, 4: adversarial steps with short mantissas */
+ * 2: code 16.368 MS/s, 3: code 2.048 MS/s, 5: zero / sub-ulp steps,
+ * other: adversarial steps with short mantissas */
 int fuzz(unsigned long long seed, int iters, int mode)
 {
     int i, bad = 0;
@@ -75,6 +76,10 @@ int fuzz(unsigned long long seed, int iters, int mode)
         } else if (mode == 3) {
             double fs = 2.048e6, cr = 1.023e6 + (urand() - 0.5) * 20.0;
             r = check_code(urand() * 1023.0, 4, (1.0 / fs) * cr, 1023, 2040 + (int)(urand() * 20));
+        } else if (mode == 5) {
+            /* zero and sub-ulp steps (an acquisition bin at exactly 0 Hz) */
+            double f = (urand() < 0.5) ? 0.0 : (urand() - 0.5) * 1e-6;
+            r = check_carrier(f, (urand() < 0.3) ? 0.0 : urand() * NCO_TWO_PI, 1.0 / 2.048e6, 2048);
         } else {
             /* steps with few mantissa bits force exact ties in many binades */
             double step = ldexp(floor(urand() * 4096.0) + 0.5, -(int)(urand() * 12));
@@ -101,7 +106,7 @@ int fuzz(unsigned long long seed, int iters, int mode)
 int main(int argc, char **argv)
 {
     int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
-    for (m = 0; m < 5; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
+    for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
     printf("max segments (mode 4) %d\n", max_segments);
     return bad != 0;
 }

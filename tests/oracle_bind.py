@@ -1,0 +1,203 @@
+"""ctypes bindings of the parity harness (oracle/harness.h).  TEST INFRASTRUCTURE:
+only tests/, __graft_entry__.smoke() and bench.py's CPU legs may import this."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libreplay_ref.so")
+DROPIN_SO = os.path.join(ROOT, "oracle", "_ref", "libreplay_b200.so")
+PORT_SO = os.path.join(ROOT, "oracle", "liboracle_port.so")
+OH_MAXTAPS = 33
+
+
+class OhCfg(C.Structure):
+    _fields_ = [("f_sf", C.c_double), ("f_if", C.c_double), ("f_cf", C.c_double),
+                ("dtype", C.c_int), ("corrn", C.c_int), ("corrd", C.c_int), ("corrp", C.c_int),
+                ("dllb", C.c_double * 2), ("pllb", C.c_double * 2), ("fllb", C.c_double * 2),
+                ("acq_intg", C.c_int), ("acq_hband", C.c_double), ("acq_step", C.c_double)]
+
+
+class OhAcq(C.Structure):
+    _fields_ = [("prn", C.c_int), ("ctype", C.c_int), ("acquired", C.c_int), ("freqi", C.c_int),
+                ("codei", C.c_int), ("nintg_used", C.c_int), ("acqfreq", C.c_double),
+                ("peakr", C.c_double), ("cn0", C.c_double), ("maxp", C.c_double),
+                ("buffloc", C.c_uint64)]
+
+
+class OhTrkRec(C.Structure):
+    _fields_ = [("cnt", C.c_uint64), ("buffloc", C.c_uint64), ("currnsamp", C.c_int),
+                ("flagsync", C.c_int), ("flagsyncf", C.c_int), ("flagtow", C.c_int),
+                ("flagdec", C.c_int), ("flagloopfilter", C.c_int), ("swsync", C.c_int),
+                ("swloop", C.c_int), ("synci", C.c_int), ("biti", C.c_int), ("bit", C.c_int),
+                ("II", C.c_double * OH_MAXTAPS), ("QQ", C.c_double * OH_MAXTAPS),
+                ("sumI0", C.c_double), ("sumQ0", C.c_double), ("codefreq", C.c_double),
+                ("codeErr", C.c_double), ("codeNco", C.c_double), ("carrfreq", C.c_double),
+                ("carrErr", C.c_double), ("carrNco", C.c_double), ("freqErr", C.c_double),
+                ("remcode", C.c_double), ("remcarr", C.c_double), ("L0", C.c_double)]
+
+
+# the INI defaults of frontend/iffile.ini:29-48 and frontend/rtlsdr_L1.ini:29-48
+def cfg_iffile(**kw) -> OhCfg:
+    c = OhCfg(f_sf=16.368e6, f_if=4.092e6, f_cf=1575.42e6, dtype=1, corrn=6, corrd=3, corrp=6)
+    c.dllb[:] = [5.0, 1.0]; c.pllb[:] = [30.0, 10.0]; c.fllb[:] = [200.0, 50.0]
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+def cfg_rtlsdr(**kw) -> OhCfg:
+    c = OhCfg(f_sf=2.048e6, f_if=0.0, f_cf=1575.42e6, dtype=2, corrn=4, corrd=1, corrp=1)
+    c.dllb[:] = [5.0, 2.0]; c.pllb[:] = [30.0, 20.0]; c.fllb[:] = [200.0, 50.0]
+    for k, v in kw.items():
+        setattr(c, k, v)
+    return c
+
+
+_i8p = C.POINTER(C.c_int8)
+_dp = C.POINTER(C.c_double)
+_fp = C.POINTER(C.c_float)
+_sp = C.POINTER(C.c_short)
+_ip = C.POINTER(C.c_int)
+
+
+class Oracle:
+    def __init__(self, path: str):
+        self.lib = C.CDLL(path)
+        self.lib.oh_impl.restype = C.c_char_p
+        self.lib.oh_mixcarr.restype = C.c_double
+        self.lib.oh_rescode.restype = C.c_double
+        self.name = self.lib.oh_impl().decode()
+
+    def acquire(self, cfg, if_data, avail, prns, ctypes=None, want_power=False):
+        if_data = np.ascontiguousarray(if_data, np.int8)
+        n = len(prns)
+        prn_a = (C.c_int * n)(*prns)
+        ct_a = (C.c_int * n)(*(ctypes or [1] * n))
+        out = (OhAcq * n)()
+        nsamples = len(if_data) // cfg.dtype
+        power = None
+        pp = None
+        if want_power:
+            nsamp = int(cfg.f_sf * 1e-3)
+            nfreq = 71 if cfg.acq_step <= 0 else 2 * int(cfg.acq_hband / cfg.acq_step) + 1
+            power = np.zeros((n, nfreq, nsamp))
+            pp = power.ctypes.data_as(_dp)
+        rc = self.lib.oh_acquire(C.byref(cfg), if_data.ctypes.data_as(_i8p), C.c_uint64(nsamples),
+                                 C.c_uint64(avail), n, prn_a, ct_a, out, pp)
+        assert rc == 0, f"oh_acquire rc={rc}"
+        return list(out), power
+
+    def acq_track(self, cfg, if_data, avail, prns, nperiods, ctypes=None):
+        if_data = np.ascontiguousarray(if_data, np.int8)
+        n = len(prns)
+        prn_a = (C.c_int * n)(*prns)
+        ct_a = (C.c_int * n)(*(ctypes or [1] * n))
+        acq = (OhAcq * n)()
+        rec = np.zeros(n * nperiods, dtype=np.dtype(OhTrkRec))
+        ntr = (C.c_int * n)()
+        nsamples = len(if_data) // cfg.dtype
+        rc = self.lib.oh_acq_track(C.byref(cfg), if_data.ctypes.data_as(_i8p), C.c_uint64(nsamples),
+                                   C.c_uint64(avail), n, prn_a, ct_a, int(nperiods), acq,
+                                   rec.ctypes.data_as(C.POINTER(OhTrkRec)), ntr)
+        assert rc == 0, f"oh_acq_track rc={rc}"
+        return list(acq), rec.reshape(n, nperiods), list(ntr)
+
+    def correlator(self, data, dtype, ti, n, freq, phi0, crate, coff, s, code):
+        data = np.ascontiguousarray(data, np.int8)
+        s = np.ascontiguousarray(s, np.int32)
+        code = np.ascontiguousarray(code, np.int16)
+        nt = 1 + 2 * len(s)
+        II, QQ = np.zeros(nt), np.zeros(nt)
+        remc, remp = C.c_double(), C.c_double()
+        self.lib.oh_correlator(data.ctypes.data_as(_i8p), int(dtype), C.c_double(ti), int(n),
+                               C.c_double(freq), C.c_double(phi0), C.c_double(crate), C.c_double(coff),
+                               s.ctypes.data_as(_ip), len(s), II.ctypes.data_as(_dp), QQ.ctypes.data_as(_dp),
+                               C.byref(remc), C.byref(remp), code.ctypes.data_as(_sp), len(code))
+        return II, QQ, remc.value, remp.value
+
+    def mixcarr(self, data, dtype, ti, n, freq, phi0):
+        data = np.ascontiguousarray(data, np.int8)
+        II, QQ = np.zeros(n + 64, np.int16), np.zeros(n + 64, np.int16)
+        rem = self.lib.oh_mixcarr(data.ctypes.data_as(_i8p), int(dtype), C.c_double(ti), int(n),
+                                  C.c_double(freq), C.c_double(phi0), II.ctypes.data_as(_sp),
+                                  QQ.ctypes.data_as(_sp))
+        return II[:n], QQ[:n], rem
+
+    def rescode(self, code, coff, smax, ci, n):
+        code = np.ascontiguousarray(code, np.int16)
+        out = np.zeros(n + 2 * smax, np.int16)
+        rem = self.lib.oh_rescode(code.ctypes.data_as(_sp), len(code), C.c_double(coff), int(smax),
+                                  C.c_double(ci), int(n), out.ctypes.data_as(_sp))
+        return out, rem
+
+    def gencode(self, prn, ctype=1):
+        buf = np.zeros(10230, np.int16)
+        cr = C.c_double()
+        n = self.lib.oh_gencode(int(prn), int(ctype), buf.ctypes.data_as(_sp), C.byref(cr))
+        if n <= 0:
+            return None, 0.0
+        return buf[:n].copy(), cr.value
+
+    def codefft(self, prn, ctype, f_sf):
+        nsamp, nfft = C.c_int(), C.c_int()
+        self.lib.oh_codefft(int(prn), int(ctype), C.c_double(f_sf), None, C.byref(nsamp), C.byref(nfft))
+        x = np.zeros(nfft.value, np.complex64)
+        self.lib.oh_codefft(int(prn), int(ctype), C.c_double(f_sf), x.ctypes.data_as(_fp),
+                            C.byref(nsamp), C.byref(nfft))
+        return x, nsamp.value, nfft.value
+
+    def cpxfft(self, cpx, inverse=False):
+        a = np.ascontiguousarray(cpx, np.complex64).copy()
+        self.lib.oh_cpxfft(a.ctypes.data_as(_fp), len(a), int(bool(inverse)))
+        return a
+
+    def cpxconv(self, cpxa, cpxb, n, conv=None):
+        a = np.ascontiguousarray(cpxa, np.complex64).copy()
+        b = np.ascontiguousarray(cpxb, np.complex64)
+        flagsum = conv is not None
+        out = np.ascontiguousarray(conv, np.float64).copy() if flagsum else np.zeros(n)
+        self.lib.oh_cpxconv(a.ctypes.data_as(_fp), b.ctypes.data_as(_fp), len(a), int(n), int(flagsum),
+                            out.ctypes.data_as(_dp))
+        return out
+
+    def cpxpspec(self, cpx, pspec=None):
+        a = np.ascontiguousarray(cpx, np.complex64).copy()
+        flagsum = pspec is not None
+        out = np.ascontiguousarray(pspec, np.float64).copy() if flagsum else np.zeros(len(a))
+        self.lib.oh_cpxpspec(a.ctypes.data_as(_fp), len(a), int(flagsum), out.ctypes.data_as(_dp))
+        return out
+
+    def pcorrelator(self, data, dtype, ti, n, freq, crate, m, codex, P=None):
+        data = np.ascontiguousarray(data, np.int8)
+        freq = np.ascontiguousarray(freq, np.float64)
+        codex = np.ascontiguousarray(codex, np.complex64)
+        out = np.zeros(len(freq) * n) if P is None else np.ascontiguousarray(P, np.float64).copy()
+        self.lib.oh_pcorrelator(data.ctypes.data_as(_i8p), int(dtype), C.c_double(ti), int(n),
+                                freq.ctypes.data_as(_dp), len(freq), C.c_double(crate), int(m),
+                                codex.ctypes.data_as(_fp), out.ctypes.data_as(_dp))
+        return out
+
+
+def have_ref() -> bool:
+    return os.path.exists(REF_SO)
+
+
+def have_port() -> bool:
+    return os.path.exists(PORT_SO)
+
+
+def ref() -> Oracle:
+    return Oracle(REF_SO)
+
+
+def port() -> Oracle:
+    return Oracle(PORT_SO)
+
+
+def best() -> Oracle:
+    """the reference build when present (this container), else the CPU port."""
+    return ref() if have_ref() else port()

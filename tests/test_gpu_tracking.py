@@ -1,0 +1,75 @@
+"""GPU parity: batched tracking engine vs the oracle's replay of
+sdrtracking + cumsumcorr + pll + dll + sdrnavigation (src/sdrmain.c:264-315).
+
+Integer decisions (sample counts, buffer positions, loop scheduling, bit-sync
+index, nav bits) must be identical.  I/Q sums are exact integers/32 as long as
+the NCO index sequences agree; the loop filters use CUDA libm (atan2/atan/sqrt)
+instead of glibc, so NCO frequencies may differ in the last bits and a sample
+index can flip: tolerance = 2 flipped samples per tap (2*2*127*32/32 = 508)."""
+import numpy as np
+import pytest
+
+import oracle_bind as ob
+import util
+
+pytestmark = pytest.mark.gpu
+
+IQ_TOL = 508.0
+FREQ_RTOL = 1e-9
+
+
+def _compare(sdr, cfgo, acq, rec_o, ntr_o, rec_g, ntr_g, ntap):
+    for ch, a in enumerate(acq):
+        n = min(ntr_o[ch], ntr_g[ch])
+        assert n > 0
+        o, g = rec_o[ch][:n], rec_g[ch][:n]
+        for f in ("cnt", "buffloc", "currnsamp", "flagsync", "flagloopfilter", "swsync", "swloop",
+                  "synci", "biti"):
+            assert np.array_equal(o[f], g[f]), (a.prn, f, int(np.argmax(o[f] != g[f])))
+        m = o["swsync"] == 1
+        assert np.array_equal(o["bit"][m], g["bit"][m]), (a.prn, "nav bits")
+        dI = np.abs(o["II"][:, :ntap] - g["II"][:, :ntap]).max()
+        dQ = np.abs(o["QQ"][:, :ntap] - g["QQ"][:, :ntap]).max()
+        assert dI <= IQ_TOL and dQ <= IQ_TOL, (a.prn, dI, dQ)
+        for f in ("carrfreq", "codefreq"):
+            assert np.allclose(o[f], g[f], rtol=FREQ_RTOL, atol=0), (a.prn, f)
+        for f in ("remcode", "remcarr"):
+            assert np.abs(o[f] - g[f]).max() < 1e-6, (a.prn, f)
+        exact = np.array_equal(o["II"][:, :ntap], g["II"][:, :ntap]) and np.array_equal(o["QQ"][:, :ntap], g["QQ"][:, :ntap])
+        print(f"prn {a.prn}: {n} periods, I/Q bit-exact={exact}, max|dI|={dI}, "
+              f"max|dcarrfreq|={np.abs(o['carrfreq'] - g['carrfreq']).max():.3e}")
+
+
+def _run(sdr, oracle, cfg, prns, cfgo, nper, fs, dtype):
+    nsamp = int(fs * 1e-3)
+    avail = 65536 * ((3 * nsamp) // 65536 + 1)
+    total = avail + nsamp * (nper + 8)
+    st = sdr.Stream(dtype, total)
+    st.push_ifgen(cfg, total)
+    host = st.read(0, total)
+    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, prns, nper)
+    assert all(a.acquired for a in acq)
+    chans = [sdr.make_trk_chan(cfgo.f_sf, cfgo.f_if, cfgo.f_cf, dtype, a.prn, sdr.gencode(a.prn)[0],
+                               a.buffloc, a.acqfreq, cfgo.corrn, cfgo.corrd, cfgo.corrp,
+                               list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb)) for a in acq]
+    eng = sdr.Tracking(chans)
+    rec_g, ntr_g = eng.run(st, nper)
+    _compare(sdr, cfgo, acq, rec_o, ntr_o, rec_g, ntr_g, 1 + 2 * cfgo.corrn)
+    # a second launch continues where the first stopped; reset restores the hand-over state
+    eng.reset()
+    rec_a, na = eng.run(st, nper // 2)
+    rec_b, nb = eng.run(st, nper - nper // 2)
+    for ch in range(len(chans)):
+        whole = rec_g[ch][:ntr_g[ch]]
+        parts = np.concatenate([rec_a[ch][:na[ch]], rec_b[ch][:nb[ch]]])
+        assert whole.tobytes() == parts[:len(whole)].tobytes()
+
+
+def test_tracking_real_if(sdr, oracle):
+    cfg, prns = util.scene_c1(sdr, nsats=3)
+    _run(sdr, oracle, cfg, prns, ob.cfg_iffile(acq_intg=1), 2600, util.FS1, 1)
+
+
+def test_tracking_iq_rtlsdr_style(sdr, oracle):
+    cfg, prns = util.scene_c5(sdr, nsats=4)
+    _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=2), 2600, util.FS5, 2)
