@@ -1,0 +1,575 @@
+/* acq.cu - batched FFT acquisition over the PRN x Doppler x code-phase grid.
+ *
+ * Stands in for sdracquisition() (src/sdracq.c:14-62), pcorrelator()
+ * (src/sdrcmn.c:738-773), cpxconv() (src/sdrcmn.c:228-251) and
+ * checkacquisition() (src/sdracq.c:71-95).
+ *
+ * Mathematics.  The reference correlates a window of 2n live samples with an
+ * n-sample replica zero-padded to m = 2n and keeps lags 0..n-1 of the m-point
+ * circular correlation (src/sdrinit.c:650-652, src/sdrcmn.c:244-246).  For
+ * those lags no index wraps, so the result is the LINEAR correlation and any
+ * transform length M >= 2n gives the same numbers; here M = 2^k >= 2n.
+ * M is split as M = R * L, L <= 16384 handled by one CTA (fft_device.cuh):
+ *   forward :  X[R j + q] = FFT_L{ W_M^(b q) * sum_a x[L a + b] W_R^(a q) }[j]
+ *   inverse :  y[t] = sum_q W_M^(-t q) * IFFT_L{ Y[R j + q] }[t mod L]
+ * so spectra are stored de-interleaved as [q][j] and never re-ordered.
+ * Scaling follows the reference exactly: input scale (float)(CSCALE/m)
+ * (src/sdrcmn.c:764), power (re^2+im^2)/M^2 (src/sdrcmn.c:245).
+ *
+ * Pipeline per integration step (all on one stream, no host round trip):
+ *   k_fwd   int8 IF -> table carrier wipe-off -> forward FFT, one per Doppler bin
+ *   k_row   spectrum x conj(code spectrum) -> inverse sub-FFTs, per (PRN, bin)
+ *   k_comb  recombine, |.|^2, accumulate P, per-row max / masked mean / 2nd max
+ *   k_final per-PRN argmax over bins, C/N0, peak ratio, early-exit freeze
+ */
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include "sdrb200_internal.h"
+#include "nco_exact.h"
+#include "fft_device.cuh"
+
+/* the carrier table (src/sdrcmn.c:641-646), float copies for the wipe-off */
+__constant__ float c_cosf[32] = {32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6,0,6,12,18,23,27,30,31};
+__constant__ float c_sinf[32] = {0,6,12,18,23,27,30,31,32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6};
+
+struct acq_rowstat_t {
+    float maxp;      /* row maximum                                         */
+    int   codei;     /* its first index                                     */
+    float max2;      /* maxvd() over the row outside the exclusion window   */
+    int   cnt;       /* samples outside the window                          */
+    double sum;      /* their sum                                           */
+};
+
+struct sdrb200_acq {
+    sdrb200_acq_cfg_t cfg;
+    int n_eff, m_ref, M, L, R;
+    int chunk;                       /* PRNs per scratch chunk                */
+    double *h_freq;
+    cudaStream_t st;
+    float2 *d_tw;                    /* [M] forward twiddles                  */
+    uint8_t *d_cidx;                 /* [nfreq][m_ref] carrier table indices  */
+    float2 *d_Xs;                    /* [nfreq][R][L]                         */
+    float2 *d_Cs;                    /* [nprn][R][L]                          */
+    float2 *d_S;                     /* [chunk][nfreq][R][L] scratch          */
+    float  *d_P;                     /* [nprn][nfreq][n_eff]                  */
+    acq_rowstat_t *d_row;            /* [nprn][nfreq]                         */
+    sdrb200_acq_result_t *d_res, *h_res;
+    int *d_frozen;
+    double *d_freq;
+    int8_t *d_hostwin; size_t hostwin_cap;   /* staging for run_host          */
+    int8_t *h_pin; size_t pin_cap;
+};
+
+/* ---------------------------------------------------------------- kernels */
+
+/* forward transform of one (item, q).  SRC 0: IF window with carrier wipe-off
+ * (mixcarr + cpxcpx, src/sdrcmn.c:650-662, 185-195); SRC 1: real int8 replica
+ * (cpxcpx(rcode,NULL,1.0,...), src/sdrinit.c:652).                           */
+template <int L, int SRC>
+__global__ void __launch_bounds__(L / 16)
+k_fwd(const int8_t *__restrict__ src, size_t item_stride, int dtype, int nlive,
+      const uint8_t *__restrict__ cidx, int cidx_stride, float scale,
+      const float2 *__restrict__ tw, int R, float2 *__restrict__ out)
+{
+    extern __shared__ float2 fsm[];
+    constexpr int T = L / 16;
+    const int q = blockIdx.x, item = blockIdx.y, tid = threadIdx.x;
+    const int M = L * R;
+    const int8_t *d = src + (SRC == 1 ? (size_t)item * item_stride : 0);
+    const uint8_t *ci = (SRC == 0) ? cidx + (size_t)item * cidx_stride : nullptr;
+    float2 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) {
+        const int b = tid + e * T;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int a = 0; a < R; a++) {
+            const int t = L * a + b;
+            if (t < nlive) {
+                float2 x;
+                if (SRC == 0) {
+                    const int idx = ci[t];
+                    const float c = c_cosf[idx], s = c_sinf[idx];
+                    if (dtype == 1) {
+                        const float s0 = (float)d[t];
+                        x = make_float2(c * s0 * scale, s * s0 * scale);
+                    } else {
+                        const float s0 = (float)d[2 * t], s1 = (float)d[2 * t + 1];
+                        x = make_float2((c * s0 - s * s1) * scale, (s * s0 + c * s1) * scale);
+                    }
+                } else {
+                    x = make_float2((float)d[t], 0.f);
+                }
+                if (a != 0 && q != 0) x = cmul(x, __ldg(&tw[(size_t)((a * q) % R) * L]));
+                acc = cadd(acc, x);
+            }
+        }
+        if (q != 0) acc = cmul(acc, __ldg(&tw[(size_t)b * q]));
+        v[e] = acc;
+    }
+    cta_fft<L, -1>(v, fsm, tw, R);
+    float2 *o = out + ((size_t)item * R + q) * L;
+#pragma unroll
+    for (int e = 0; e < 16; e++) o[tid + e * T] = v[e];
+    (void)M;
+}
+
+/* per-row statistics over a power row held in global memory; all threads of
+ * the CTA call it.  Implements the three scans of checkacquisition() for this
+ * row: maxvd (first index wins, src/sdrcmn.c:461-476), meanvd (487-497) and
+ * the second maxvd with the exclusion window and its data[0] seed quirk.      */
+__device__ void acq_row_stats(const float *Prow, int n, int nsampchip,
+                              float tmax, int tidx, acq_rowstat_t *out)
+{
+    __shared__ float s_f[32];
+    __shared__ int   s_i[32];
+    __shared__ double s_d[32];
+    __shared__ int   s_codei;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+    /* block argmax: larger value, then smaller index */
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, tmax, o);
+        int   oi = __shfl_xor_sync(0xffffffffu, tidx, o);
+        if (ov > tmax || (ov == tmax && oi < tidx)) { tmax = ov; tidx = oi; }
+    }
+    if (lane == 0) { s_f[warp] = tmax; s_i[warp] = tidx; }
+    __syncthreads();
+    if (warp == 0) {
+        tmax = (lane < nwarp) ? s_f[lane] : -1.f;
+        tidx = (lane < nwarp) ? s_i[lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float ov = __shfl_xor_sync(0xffffffffu, tmax, o);
+            int   oi = __shfl_xor_sync(0xffffffffu, tidx, o);
+            if (ov > tmax || (ov == tmax && oi < tidx)) { tmax = ov; tidx = oi; }
+        }
+        if (lane == 0) { s_f[0] = tmax; s_codei = tidx; }
+    }
+    __syncthreads();
+    const float rowmax = s_f[0];
+    const int codei = s_codei;
+    /* exclusion window, src/sdracq.c:81-82 */
+    int exs = codei - 2 * nsampchip; if (exs < 0) exs += n;
+    int exe = codei + 2 * nsampchip; if (exe >= n) exe -= n;
+    double sum = 0.0; int cnt = 0; float m2 = -1.f;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const bool inc = (exs <= exe) ? (i < exs || i > exe) : (i < exs && i > exe);
+        if (inc) {
+            const float p = Prow[i];
+            sum += (double)p; cnt++;
+            if (i >= 1 && p > m2) m2 = p;
+        }
+    }
+    if (threadIdx.x == 0) { const float p0 = Prow[0]; if (p0 > m2) m2 = p0; }   /* max=data[0] seed */
+    __syncthreads();
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    }
+    if (lane == 0) { s_d[warp] = sum; s_i[warp] = cnt; s_f[warp] = m2; }
+    __syncthreads();
+    if (warp == 0) {
+        sum = (lane < nwarp) ? s_d[lane] : 0.0;
+        cnt = (lane < nwarp) ? s_i[lane] : 0;
+        m2  = (lane < nwarp) ? s_f[lane] : -1.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+            m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+        }
+        if (lane == 0) { out->maxp = rowmax; out->codei = codei; out->max2 = m2; out->cnt = cnt; out->sum = sum; }
+    }
+}
+
+/* inverse sub-transform of one (q, bin, PRN): cpxconv()'s spectrum product and
+ * inverse FFT (src/sdrcmn.c:236-242).  For R == 1 the power, accumulation and
+ * row statistics are fused here and nothing but the P row is written.          */
+template <int L>
+__global__ void __launch_bounds__(L / 16)
+k_row(const float2 *__restrict__ Xs, const float2 *__restrict__ Cs, const float2 *__restrict__ tw,
+      int R, int nfreq, int prn0, float2 *__restrict__ S, float *__restrict__ P, int n_eff,
+      int nsampchip, int first_step, float invM2, acq_rowstat_t *__restrict__ rows,
+      const int *__restrict__ frozen)
+{
+    extern __shared__ float2 fsm[];
+    constexpr int T = L / 16;
+    const int q = blockIdx.x, f = blockIdx.y, pc = blockIdx.z, p = prn0 + pc, tid = threadIdx.x;
+    if (frozen[p]) return;
+    const float2 *x = Xs + ((size_t)f * R + q) * L;
+    const float2 *c = Cs + ((size_t)p * R + q) * L;
+    float2 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = cmulc(__ldg(&x[tid + e * T]), __ldg(&c[tid + e * T]));
+    cta_fft<L, +1>(v, fsm, tw, R);
+    if (R > 1) {
+        float2 *o = S + (((size_t)pc * nfreq + f) * R + q) * L;
+#pragma unroll
+        for (int e = 0; e < 16; e++) o[tid + e * T] = v[e];
+        return;
+    }
+    /* R == 1: y[t] = v, t = tid + e*T */
+    float *Prow = P + ((size_t)p * nfreq + f) * n_eff;
+    float tmax = -1.f; int tidx = 0x7fffffff;
+#pragma unroll
+    for (int e = 0; e < 16; e++) {
+        const int t = tid + e * T;
+        if (t < n_eff) {
+            float pw = (v[e].x * v[e].x + v[e].y * v[e].y) * invM2;
+            if (!first_step) pw += Prow[t];
+            Prow[t] = pw;
+            if (pw > tmax) { tmax = pw; tidx = t; }
+        }
+    }
+    __syncthreads();                      /* Prow visible to the whole CTA */
+    acq_row_stats(Prow, n_eff, nsampchip, tmax, tidx, &rows[(size_t)p * nfreq + f]);
+}
+
+/* recombination of the R sub-transforms of one (bin, PRN) row + power +
+ * accumulation (cpxconv flagsum, src/sdrcmn.c:244-246) + row statistics        */
+__global__ void __launch_bounds__(1024)
+k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L, int nfreq, int prn0,
+       float *__restrict__ P, int n_eff, int nsampchip, int first_step, float invM2,
+       acq_rowstat_t *__restrict__ rows, const int *__restrict__ frozen)
+{
+    const int f = blockIdx.x, pc = blockIdx.y, p = prn0 + pc;
+    if (frozen[p]) return;
+    const int M = R * L;
+    const float2 *s = S + ((size_t)pc * nfreq + f) * (size_t)M;
+    float *Prow = P + ((size_t)p * nfreq + f) * n_eff;
+    float tmax = -1.f; int tidx = 0x7fffffff;
+    for (int t = threadIdx.x; t < n_eff; t += blockDim.x) {
+        const int tl = t & (L - 1);
+        float2 y = __ldg(&s[tl]);
+        for (int q = 1; q < R; q++) {
+            float2 w = __ldg(&tw[(size_t)(((long long)t * q) & (M - 1))]);
+            y = cadd(y, cmulc(__ldg(&s[(size_t)q * L + tl]), w));      /* * conj(W_M^(t q)) */
+        }
+        float pw = (y.x * y.x + y.y * y.y) * invM2;
+        if (!first_step) pw += Prow[t];
+        Prow[t] = pw;
+        if (pw > tmax) { tmax = pw; tidx = t; }
+    }
+    __syncthreads();
+    acq_row_stats(Prow, n_eff, nsampchip, tmax, tidx, &rows[(size_t)p * nfreq + f]);
+}
+
+/* checkacquisition() for one PRN from its row statistics (src/sdracq.c:71-95)
+ * plus the early exit of sdracquisition() (src/sdracq.c:38-42)                 */
+__global__ void k_final(const acq_rowstat_t *__restrict__ rows, int nfreq, const double *__restrict__ freq,
+                        double ctime, double thresh, int step, sdrb200_acq_result_t *__restrict__ res,
+                        int *__restrict__ frozen)
+{
+    const int p = blockIdx.x;
+    if (frozen[p]) return;
+    __shared__ float s_v[32]; __shared__ int s_f[32];
+    float best = -1.f; int bf = 0x7fffffff;
+    for (int f = threadIdx.x; f < nfreq; f += blockDim.x) {
+        float v = rows[(size_t)p * nfreq + f].maxp;
+        if (v > best) { best = v; bf = f; }                       /* lowest bin wins ties */
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        int   of = __shfl_xor_sync(0xffffffffu, bf, o);
+        if (ov > best || (ov == best && of < bf)) { best = ov; bf = of; }
+    }
+    if (lane == 0) { s_v[warp] = best; s_f[warp] = bf; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < nwarp; w++)
+            if (s_v[w] > best || (s_v[w] == best && s_f[w] < bf)) { best = s_v[w]; bf = s_f[w]; }
+        const acq_rowstat_t r = rows[(size_t)p * nfreq + bf];
+        sdrb200_acq_result_t o;
+        o.maxp = (double)r.maxp; o.maxp2 = (double)r.max2;
+        o.meanp = r.sum / (double)r.cnt;
+        o.cn0 = 10 * log10(o.maxp / o.meanp / ctime);
+        o.peakr = o.maxp / o.maxp2;
+        o.codei = r.codei; o.freqi = bf; o.acqfreq = freq[bf];
+        o.acquired = (o.peakr > thresh) ? 1 : 0;
+        o.nintg = step + 1;
+        res[p] = o;
+        if (o.acquired) frozen[p] = 1;
+    }
+}
+
+/* ------------------------------------------------------------- host side */
+template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int nitems, const int8_t *src,
+                                       size_t item_stride, int dtype, int nlive, const uint8_t *cidx,
+                                       int cidx_stride, float scale, const float2 *tw, float2 *out)
+{
+    const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
+    dim3 grid(R, nitems);
+    if (src_kind == 0) {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd<L, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_fwd<L, 0><<<grid, L / 16, smem, st>>>(src, item_stride, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
+    } else {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd<L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_fwd<L, 1><<<grid, L / 16, smem, st>>>(src, item_stride, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
+    }
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
+
+template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int first_step)
+{
+    const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
+    dim3 grid(a->R, a->cfg.nfreq, nprn);
+    const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_row<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, a->d_S, a->d_P,
+                                         a->n_eff, a->cfg.nsampchip, first_step, invM2, a->d_row, a->d_frozen);
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
+
+#define ACQ_DISPATCH_L(Lval, CALL)                                             \
+    switch (Lval) {                                                            \
+    case 256:   { constexpr int LL = 256;   rc = CALL; } break;                \
+    case 512:   { constexpr int LL = 512;   rc = CALL; } break;                \
+    case 1024:  { constexpr int LL = 1024;  rc = CALL; } break;                \
+    case 2048:  { constexpr int LL = 2048;  rc = CALL; } break;                \
+    case 4096:  { constexpr int LL = 4096;  rc = CALL; } break;                \
+    case 8192:  { constexpr int LL = 8192;  rc = CALL; } break;                \
+    case 16384: { constexpr int LL = 16384; rc = CALL; } break;                \
+    default: sdrb200_set_error("unsupported sub-FFT length %d", Lval); rc = SDRB200_EINVAL; }
+
+extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
+{
+    if (!a) return;
+    cudaFree(a->d_tw); cudaFree(a->d_cidx); cudaFree(a->d_Xs); cudaFree(a->d_Cs); cudaFree(a->d_S);
+    cudaFree(a->d_P); cudaFree(a->d_row); cudaFree(a->d_res); cudaFree(a->d_frozen); cudaFree(a->d_freq);
+    cudaFree(a->d_hostwin);
+    if (a->h_res) cudaFreeHost(a->h_res);
+    if (a->h_pin) cudaFreeHost(a->h_pin);
+    if (a->st) cudaStreamDestroy(a->st);
+    free(a->h_freq);
+    free(a);
+}
+
+extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)a->st : NULL; }
+
+static int acq_sub_length(int M)
+{
+    int lsub = 8192;
+    const char *env = getenv("SDRB200_LSUB");
+    if (env) { int v = atoi(env); if (v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) lsub = v; }
+    return M < lsub ? M : lsub;
+}
+
+extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *cfg)
+{
+    if (!out || !cfg || !cfg->freq || !cfg->codes || cfg->nsamp < 64 || cfg->nfreq < 1 || cfg->nprn < 1 ||
+        cfg->clen < 1 || cfg->intg < 1 || (cfg->dtype != 1 && cfg->dtype != 2) || cfg->f_sf <= 0) {
+        sdrb200_set_error("acq_create: bad argument"); return SDRB200_EINVAL;
+    }
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    sdrb200_acq *a = (sdrb200_acq *)calloc(1, sizeof(*a));
+    if (!a) return SDRB200_ENOMEM;
+    a->cfg = *cfg;
+    if (a->cfg.ncoh < 1) a->cfg.ncoh = 1;
+    if (a->cfg.threshold <= 0) a->cfg.threshold = 3.0;           /* ACQTH */
+    a->n_eff = cfg->nsamp * a->cfg.ncoh;
+    a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
+    a->M = 256; while (a->M < a->m_ref) a->M <<= 1;
+    a->L = acq_sub_length(a->M);
+    a->R = a->M / a->L;
+    const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
+    if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }
+    a->h_freq = (double *)malloc(sizeof(double) * nfreq);
+    memcpy(a->h_freq, cfg->freq, sizeof(double) * nfreq);
+    a->cfg.freq = a->h_freq; a->cfg.codes = NULL;
+    /* scratch chunking: keep S within ~64 MB so that it stays L2-resident */
+    {
+        size_t per_prn = (size_t)nfreq * M * sizeof(float2);
+        size_t budget = (size_t)64 << 20;
+        a->chunk = (int)(budget / per_prn); if (a->chunk < 1) a->chunk = 1; if (a->chunk > nprn) a->chunk = nprn;
+    }
+    int rc = SDRB200_OK;
+#define ACQ_ALLOC(ptr, bytes) if (rc == SDRB200_OK && cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) { \
+        cudaGetLastError(); sdrb200_set_error("acq_create: cudaMalloc(%zu) failed", (size_t)(bytes)); rc = SDRB200_ENOMEM; }
+    if (cudaStreamCreateWithFlags(&a->st, cudaStreamNonBlocking) != cudaSuccess) rc = SDRB200_ECUDA;
+    ACQ_ALLOC(a->d_tw, sizeof(float2) * M);
+    ACQ_ALLOC(a->d_cidx, (size_t)nfreq * a->m_ref);
+    ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)nfreq * M);
+    ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
+    if (a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * nfreq * M);
+    ACQ_ALLOC(a->d_P, sizeof(float) * (size_t)nprn * nfreq * n_eff);
+    ACQ_ALLOC(a->d_row, sizeof(acq_rowstat_t) * (size_t)nprn * nfreq);
+    ACQ_ALLOC(a->d_res, sizeof(sdrb200_acq_result_t) * nprn);
+    ACQ_ALLOC(a->d_frozen, sizeof(int) * nprn);
+    ACQ_ALLOC(a->d_freq, sizeof(double) * nfreq);
+    if (rc == SDRB200_OK && cudaMallocHost((void **)&a->h_res, sizeof(sdrb200_acq_result_t) * nprn) != cudaSuccess) rc = SDRB200_ENOMEM;
+    if (rc) { sdrb200_acq_destroy(a); return rc; }
+
+    /* twiddles exp(-2*pi*i*k/M), computed in double */
+    {
+        float2 *h = (float2 *)malloc(sizeof(float2) * M);
+        for (int k = 0; k < M; k++) {
+            double ang = -6.283185307179586476925286766559 * (double)k / (double)M;
+            h[k] = make_float2((float)cos(ang), (float)sin(ang));
+        }
+        cudaMemcpyAsync(a->d_tw, h, sizeof(float2) * M, cudaMemcpyHostToDevice, a->st);
+        cudaStreamSynchronize(a->st);
+        free(h);
+    }
+    /* carrier table indices per Doppler bin: mixcarr(dataR,dtype,ti,m,freq[i],0.0,...)
+     * (src/sdrcmn.c:761) has phi0 = 0 and a fixed grid, so the index sequence is a
+     * constant of the configuration; it is generated with the exact NCO replay. */
+    {
+        uint8_t *h = (uint8_t *)malloc((size_t)nfreq * a->m_ref);
+        nco_table_t *tb = (nco_table_t *)malloc(sizeof(nco_table_t));
+        const double ti = 1 / cfg->f_sf;
+        for (int f = 0; f < nfreq && rc == SDRB200_OK; f++) {
+            double phi, ps;
+            nco_carrier_init(a->h_freq[f], 0.0, ti, &phi, &ps);
+            if (nco_walk(phi, ps, a->m_ref, 0.0, tb)) { sdrb200_set_error("acq_create: NCO table overflow"); rc = SDRB200_ERANGE; break; }
+            int32_t hint = 0;
+            uint8_t *row = h + (size_t)f * a->m_ref;
+            for (int t = 0; t < a->m_ref; t++) row[t] = (uint8_t)(((int)nco_value(tb, t, &hint)) & SDRB200_CMASK);
+        }
+        if (rc == SDRB200_OK) {
+            cudaMemcpyAsync(a->d_cidx, h, (size_t)nfreq * a->m_ref, cudaMemcpyHostToDevice, a->st);
+            cudaMemcpyAsync(a->d_freq, a->h_freq, sizeof(double) * nfreq, cudaMemcpyHostToDevice, a->st);
+            cudaStreamSynchronize(a->st);
+        }
+        free(h); free(tb);
+        if (rc) { sdrb200_acq_destroy(a); return rc; }
+    }
+    /* code-spectrum bank: rescode(code,clen,0,0,ci,nsamp,rcode); cpxcpx; cpxfft
+     * (src/sdrinit.c:650-653), at the padded length, resident in HBM            */
+    {
+        int8_t *h = (int8_t *)malloc((size_t)nprn * n_eff);
+        nco_table_t *tb = (nco_table_t *)malloc(sizeof(nco_table_t));
+        const double ti = 1 / cfg->f_sf, ci = ti * cfg->crate;       /* sdr->ci, sdrinit.c:606 */
+        const double c0 = nco_code_init(0.0, 0, ci, cfg->clen);
+        if (nco_walk(c0, ci, n_eff, (double)cfg->clen, tb)) { sdrb200_set_error("acq_create: code NCO overflow"); rc = SDRB200_ERANGE; }
+        if (rc == SDRB200_OK) {
+            int32_t hint = 0;
+            int *chip = (int *)malloc(sizeof(int) * n_eff);
+            for (int t = 0; t < n_eff; t++) chip[t] = (int)nco_value(tb, t, &hint);
+            for (int p = 0; p < nprn; p++)
+                for (int t = 0; t < n_eff; t++) h[(size_t)p * n_eff + t] = cfg->codes[(size_t)p * cfg->clen + chip[t]];
+            free(chip);
+            int8_t *d_rc = NULL;
+            if (cudaMalloc((void **)&d_rc, (size_t)nprn * n_eff) != cudaSuccess) rc = SDRB200_ENOMEM;
+            else {
+                cudaMemcpyAsync(d_rc, h, (size_t)nprn * n_eff, cudaMemcpyHostToDevice, a->st);
+                ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(1, a->st, a->R, nprn, d_rc, (size_t)n_eff, 1, n_eff, NULL, 0, 1.0f, a->d_tw, a->d_Cs)));
+                cudaStreamSynchronize(a->st);
+                cudaFree(d_rc);
+            }
+        }
+        free(h); free(tb);
+        if (rc) { sdrb200_acq_destroy(a); return rc; }
+    }
+    *out = a;
+    return SDRB200_OK;
+}
+
+/* all integration steps of sdracquisition()'s loop (src/sdracq.c:29-43) for every
+ * PRN, enqueued on the plan's stream                                            */
+static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint64_t buffloc0)
+{
+    const sdrb200_acq_cfg_t *c = &a->cfg;
+    int rc = SDRB200_OK;
+    const float scale = (float)(SDRB200_CSCALE / a->m_ref);            /* sdrcmn.c:764 */
+    SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_frozen, 0, sizeof(int) * c->nprn, a->st));
+    SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_res, 0, sizeof(sdrb200_acq_result_t) * c->nprn, a->st));
+    for (int step = 0; step < c->intg; step++) {
+        const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
+        const int8_t *win = base + pos * c->dtype;
+        ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
+                                             a->m_ref, scale, a->d_tw, a->d_Xs)));
+        if (rc) return rc;
+        for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
+            const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
+            ACQ_DISPATCH_L(a->L, (launch_row<LL>(a->st, a, p0, np, step == 0)));
+            if (rc) return rc;
+            if (a->R > 1) {
+                dim3 grid(c->nfreq, np);
+                const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+                k_comb<<<grid, 1024, 0, a->st>>>(a->d_S, a->d_tw, a->R, a->L, c->nfreq, p0, a->d_P, a->n_eff,
+                                                 c->nsampchip, step == 0, invM2, a->d_row, a->d_frozen);
+                sdrb200_count_launch(1);
+                SDRB200_CUDA_TRY(cudaGetLastError());
+            }
+        }
+        k_final<<<c->nprn, 128, 0, a->st>>>(a->d_row, c->nfreq, a->d_freq, c->ctime, c->threshold, step,
+                                           a->d_res, a->d_frozen);
+        sdrb200_count_launch(1);
+        SDRB200_CUDA_TRY(cudaGetLastError());
+    }
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_acq_enqueue(sdrb200_acq_t *a, const sdrb200_stream_t *s, uint64_t buffloc0)
+{
+    if (!a || !s) { sdrb200_set_error("acq_run: bad argument"); return SDRB200_EINVAL; }
+    if (s->dtype != a->cfg.dtype) { sdrb200_set_error("acq_run: stream dtype mismatch"); return SDRB200_EINVAL; }
+    const uint64_t need = (uint64_t)(a->cfg.intg + 1) * a->n_eff;
+    if (buffloc0 + need > s->count || s->count - buffloc0 > s->capacity) {
+        sdrb200_set_error("acq_run: window [%llu,+%llu) not held by the stream (count %llu)",
+                          (unsigned long long)buffloc0, (unsigned long long)need, (unsigned long long)s->count);
+        return SDRB200_ERANGE;
+    }
+    if ((size_t)a->m_ref * a->cfg.dtype > SDRB200_STREAM_GUARD) { sdrb200_set_error("acq_run: window exceeds the ring guard"); return SDRB200_EINVAL; }
+    return acq_steps(a, s->d_buf, s->capacity, buffloc0);
+}
+
+extern "C" int sdrb200_acq_fetch(sdrb200_acq_t *a, sdrb200_acq_result_t *results)
+{
+    if (!a || !results) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(a->h_res, a->d_res, sizeof(sdrb200_acq_result_t) * a->cfg.nprn,
+                                     cudaMemcpyDeviceToHost, a->st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+    memcpy(results, a->h_res, sizeof(sdrb200_acq_result_t) * a->cfg.nprn);
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_acq_run(sdrb200_acq_t *a, const sdrb200_stream_t *s, uint64_t buffloc0,
+                               sdrb200_acq_result_t *results)
+{
+    int rc = sdrb200_acq_enqueue(a, s, buffloc0);
+    if (rc) return rc;
+    return sdrb200_acq_fetch(a, results);
+}
+
+extern "C" int sdrb200_acq_run_host(sdrb200_acq_t *a, const int8_t *host_if, uint64_t nsamples,
+                                    sdrb200_acq_result_t *results)
+{
+    if (!a || !host_if || !results) { sdrb200_set_error("acq_run_host: bad argument"); return SDRB200_EINVAL; }
+    const uint64_t need = (uint64_t)(a->cfg.intg + 1) * a->n_eff;
+    if (nsamples < need) { sdrb200_set_error("acq_run_host: need %llu samples", (unsigned long long)need); return SDRB200_ERANGE; }
+    const size_t bytes = (size_t)need * a->cfg.dtype;
+    if (bytes + 512 > a->hostwin_cap) {
+        SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+        cudaFree(a->d_hostwin); a->d_hostwin = NULL; a->hostwin_cap = 0;
+        if (cudaMalloc((void **)&a->d_hostwin, bytes + 512) != cudaSuccess) { cudaGetLastError(); return SDRB200_ENOMEM; }
+        a->hostwin_cap = bytes + 512;
+    }
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(a->d_hostwin + 256, host_if, bytes, cudaMemcpyHostToDevice, a->st));
+    int rc = acq_steps(a, a->d_hostwin + 256, ~(uint64_t)0, 0);
+    if (rc) return rc;
+    return sdrb200_acq_fetch(a, results);
+}
+
+extern "C" int sdrb200_acq_power(sdrb200_acq_t *a, int prn_index, double *power)
+{
+    if (!a || !power || prn_index < 0 || prn_index >= a->cfg.nprn) return SDRB200_EINVAL;
+    const size_t n = (size_t)a->cfg.nfreq * a->n_eff;
+    float *h = (float *)malloc(sizeof(float) * n);
+    if (!h) return SDRB200_ENOMEM;
+    cudaError_t e = cudaMemcpyAsync(h, a->d_P + (size_t)prn_index * n, sizeof(float) * n, cudaMemcpyDeviceToHost, a->st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(a->st);
+    if (e != cudaSuccess) { free(h); sdrb200_set_error("acq_power: %s", cudaGetErrorString(e)); return SDRB200_ECUDA; }
+    for (size_t i = 0; i < n; i++) power[i] = (double)h[i];
+    free(h);
+    return SDRB200_OK;
+}
