@@ -41,6 +41,7 @@ struct acq_rowstat_t {
     double sum;      /* their sum                                           */
 };
 
+#define ACQ_MAXEV 256
 struct sdrb200_acq {
     sdrb200_acq_cfg_t cfg;
     int n_eff, m_ref, M, L, R;
@@ -59,7 +60,14 @@ struct sdrb200_acq {
     double *d_freq;
     int8_t *d_hostwin; size_t hostwin_cap;   /* staging for run_host          */
     int8_t *h_pin; size_t pin_cap;
+    /* optional per-kernel timing (bench.py): events around every launch      */
+    int timing, nev;
+    cudaEvent_t ev0[ACQ_MAXEV], ev1[ACQ_MAXEV];
+    int evkind[ACQ_MAXEV];
+    double tot_ms[4]; long long tot_cnt[4];
 };
+#define ACQ_T0(a) do { if ((a)->timing && (a)->nev < ACQ_MAXEV) cudaEventRecord((a)->ev0[(a)->nev], (a)->st); } while (0)
+#define ACQ_T1(a, kind) do { if ((a)->timing && (a)->nev < ACQ_MAXEV) { cudaEventRecord((a)->ev1[(a)->nev], (a)->st); (a)->evkind[(a)->nev++] = (kind); } } while (0)
 
 /* ---------------------------------------------------------------- kernels */
 
@@ -348,6 +356,7 @@ extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
     cudaFree(a->d_hostwin);
     if (a->h_res) cudaFreeHost(a->h_res);
     if (a->h_pin) cudaFreeHost(a->h_pin);
+    if (a->ev0[0]) for (int i = 0; i < ACQ_MAXEV; i++) { cudaEventDestroy(a->ev0[i]); cudaEventDestroy(a->ev1[i]); }
     if (a->st) cudaStreamDestroy(a->st);
     free(a->h_freq);
     free(a);
@@ -473,6 +482,43 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     return SDRB200_OK;
 }
 
+/* fold the events of the previous enqueue into the per-kernel totals */
+static int acq_timing_collect(sdrb200_acq *a)
+{
+    if (a->nev == 0) return SDRB200_OK;
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+    for (int i = 0; i < a->nev; i++) {
+        float ms = 0.f;
+        SDRB200_CUDA_TRY(cudaEventElapsedTime(&ms, a->ev0[i], a->ev1[i]));
+        a->tot_ms[a->evkind[i]] += ms; a->tot_cnt[a->evkind[i]]++;
+    }
+    a->nev = 0;
+    return SDRB200_OK;
+}
+
+/* kernel classes: 0 k_fwd, 1 k_row, 2 k_comb, 3 k_final.  on=1 starts (and
+ * clears) the totals, on=0 stops.                                             */
+extern "C" int sdrb200_acq_set_timing(sdrb200_acq_t *a, int on)
+{
+    if (!a) return SDRB200_EINVAL;
+    if (on && !a->ev0[0])
+        for (int i = 0; i < ACQ_MAXEV; i++) {
+            SDRB200_CUDA_TRY(cudaEventCreate(&a->ev0[i]));
+            SDRB200_CUDA_TRY(cudaEventCreate(&a->ev1[i]));
+        }
+    if (on) { memset(a->tot_ms, 0, sizeof(a->tot_ms)); memset(a->tot_cnt, 0, sizeof(a->tot_cnt)); a->nev = 0; }
+    a->timing = on ? 1 : 0;
+    return SDRB200_OK;
+}
+extern "C" int sdrb200_acq_kernel_ms(sdrb200_acq_t *a, double *ms4, long long *cnt4)
+{
+    if (!a || !ms4 || !cnt4) return SDRB200_EINVAL;
+    int rc = acq_timing_collect(a);
+    if (rc) return rc;
+    for (int i = 0; i < 4; i++) { ms4[i] = a->tot_ms[i]; cnt4[i] = a->tot_cnt[i]; }
+    return SDRB200_OK;
+}
+
 /* all integration steps of sdracquisition()'s loop (src/sdracq.c:29-43) for every
  * PRN, enqueued on the plan's stream                                            */
 static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint64_t buffloc0)
@@ -480,31 +526,40 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
     const sdrb200_acq_cfg_t *c = &a->cfg;
     int rc = SDRB200_OK;
     const float scale = (float)(SDRB200_CSCALE / a->m_ref);            /* sdrcmn.c:764 */
+    if (a->timing) { int rc2 = acq_timing_collect(a); if (rc2) return rc2; }
     SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_frozen, 0, sizeof(int) * c->nprn, a->st));
     SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_res, 0, sizeof(sdrb200_acq_result_t) * c->nprn, a->st));
     for (int step = 0; step < c->intg; step++) {
         const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
         const int8_t *win = base + pos * c->dtype;
+        ACQ_T0(a);
         ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
                                              a->m_ref, scale, a->d_tw, a->d_Xs)));
         if (rc) return rc;
+        ACQ_T1(a, 0);
         for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
             const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
+            ACQ_T0(a);
             ACQ_DISPATCH_L(a->L, (launch_row<LL>(a->st, a, p0, np, step == 0)));
             if (rc) return rc;
+            ACQ_T1(a, 1);
             if (a->R > 1) {
                 dim3 grid(c->nfreq, np);
                 const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+                ACQ_T0(a);
                 k_comb<<<grid, 1024, 0, a->st>>>(a->d_S, a->d_tw, a->R, a->L, c->nfreq, p0, a->d_P, a->n_eff,
                                                  c->nsampchip, step == 0, invM2, a->d_row, a->d_frozen);
                 sdrb200_count_launch(1);
                 SDRB200_CUDA_TRY(cudaGetLastError());
+                ACQ_T1(a, 2);
             }
         }
+        ACQ_T0(a);
         k_final<<<c->nprn, 128, 0, a->st>>>(a->d_row, c->nfreq, a->d_freq, c->ctime, c->threshold, step,
                                            a->d_res, a->d_frozen);
         sdrb200_count_launch(1);
         SDRB200_CUDA_TRY(cudaGetLastError());
+        ACQ_T1(a, 3);
     }
     return SDRB200_OK;
 }

@@ -257,3 +257,50 @@ extern "C" int sdrb200_stream_read(const sdrb200_stream_t *s, uint64_t buffloc, 
     }
     return SDRB200_OK;
 }
+
+/* ------------------------------------------------- measurement helpers
+ * CUDA events live in THIS library's runtime instance (cudart is linked
+ * statically), so bench.py times the library's own streams through these
+ * instead of torch.cuda.Event, which only sees torch's current stream.        */
+extern "C" int sdrb200_evt_create(void **evt)
+{
+    if (!evt) return SDRB200_EINVAL;
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    cudaEvent_t e;
+    SDRB200_CUDA_TRY(cudaEventCreate(&e));
+    *evt = (void *)e;
+    return SDRB200_OK;
+}
+extern "C" void sdrb200_evt_destroy(void *evt) { if (evt) cudaEventDestroy((cudaEvent_t)evt); }
+extern "C" int sdrb200_evt_record(void *evt, void *cuda_stream)
+{
+    if (!evt) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaEventRecord((cudaEvent_t)evt, (cudaStream_t)cuda_stream));
+    return SDRB200_OK;
+}
+extern "C" int sdrb200_evt_elapsed_ms(void *start, void *stop, float *ms)
+{
+    if (!start || !stop || !ms) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaEventSynchronize((cudaEvent_t)stop));
+    SDRB200_CUDA_TRY(cudaEventElapsedTime(ms, (cudaEvent_t)start, (cudaEvent_t)stop));
+    return SDRB200_OK;
+}
+extern "C" int sdrb200_device_sync(void)
+{
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    SDRB200_CUDA_TRY(cudaDeviceSynchronize());
+    return SDRB200_OK;
+}
+
+/* overwrite a buffer larger than the 126 MB L2 so that the next timed
+ * iteration starts from HBM                                                   */
+static void *g_flush_buf = NULL;
+static const size_t k_flush_bytes = (size_t)384 << 20;
+extern "C" int sdrb200_l2_flush(void *cuda_stream)
+{
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    if (!g_flush_buf) SDRB200_CUDA_TRY(cudaMalloc(&g_flush_buf, k_flush_bytes));
+    static int v = 0;
+    SDRB200_CUDA_TRY(cudaMemsetAsync(g_flush_buf, ++v & 0xff, k_flush_bytes, (cudaStream_t)cuda_stream));
+    return SDRB200_OK;
+}

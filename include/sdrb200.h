@@ -41,6 +41,15 @@ int  sdrb200_sm_count(void);
 /* number of kernels this library launched in the calling process so far     */
 uint64_t sdrb200_launch_count(void);
 
+/* measurement helpers (bench.py): CUDA events on this library's own streams,
+ * and an L2 flush (a write larger than the 126 MB L2) between timed iterations */
+int  sdrb200_evt_create(void **evt);
+void sdrb200_evt_destroy(void *evt);
+int  sdrb200_evt_record(void *evt, void *cuda_stream);
+int  sdrb200_evt_elapsed_ms(void *start, void *stop, float *ms);  /* waits for stop */
+int  sdrb200_l2_flush(void *cuda_stream);
+int  sdrb200_device_sync(void);
+
 /* code types: same numeric values as the reference (src/sdr.h:205-212)      */
 #define SDRB200_CTYPE_L1CA    1
 #define SDRB200_CTYPE_G1      20
@@ -126,6 +135,11 @@ int  sdrb200_acq_run_host(sdrb200_acq_t *plan, const int8_t *host_if, uint64_t n
 int  sdrb200_acq_enqueue(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t buffloc0);
 int  sdrb200_acq_fetch(sdrb200_acq_t *plan, sdrb200_acq_result_t *results);
 void *sdrb200_acq_cuda_stream(sdrb200_acq_t *plan);
+/* per-kernel CUDA-event timing of the enqueued launches; kernel classes:
+ * 0 forward (wipe-off + FFT), 1 row (spectrum product + inverse FFT),
+ * 2 combine (power, accumulation, row statistics), 3 decision                 */
+int  sdrb200_acq_set_timing(sdrb200_acq_t *plan, int on);
+int  sdrb200_acq_kernel_ms(sdrb200_acq_t *plan, double *ms4, long long *cnt4);
 /* copy the accumulated power matrix of one PRN to the host: [nfreq][nsamp]
  * doubles (the `power` argument of sdracquisition)                           */
 int  sdrb200_acq_power(sdrb200_acq_t *plan, int prn_index, double *power);
