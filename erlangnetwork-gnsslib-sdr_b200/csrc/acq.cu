@@ -455,14 +455,16 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
      * (src/sdrinit.c:650-653), at the padded length, resident in HBM            */
     {
         int8_t *h = (int8_t *)malloc((size_t)nprn * n_eff);
-        nco_table_t *tb = (nco_table_t *)malloc(sizeof(nco_table_t));
         const double ti = 1 / cfg->f_sf, ci = ti * cfg->crate;       /* sdr->ci, sdrinit.c:606 */
-        const double c0 = nco_code_init(0.0, 0, ci, cfg->clen);
-        if (nco_walk(c0, ci, n_eff, (double)cfg->clen, tb)) { sdrb200_set_error("acq_create: code NCO overflow"); rc = SDRB200_ERANGE; }
         if (rc == SDRB200_OK) {
-            int32_t hint = 0;
+            /* the reference's own sequential loop (one-time, host): coff += ci with
+             * the wrap test, src/sdrcmn.c:614-617; ncoh > 1 simply keeps walking    */
             int *chip = (int *)malloc(sizeof(int) * n_eff);
-            for (int t = 0; t < n_eff; t++) chip[t] = (int)nco_value(tb, t, &hint);
+            double coff = nco_code_init(0.0, 0, ci, cfg->clen);
+            for (int t = 0; t < n_eff; t++, coff += ci) {
+                if (coff >= cfg->clen) coff -= cfg->clen;
+                chip[t] = (int)coff;
+            }
             for (int p = 0; p < nprn; p++)
                 for (int t = 0; t < n_eff; t++) h[(size_t)p * n_eff + t] = cfg->codes[(size_t)p * cfg->clen + chip[t]];
             free(chip);
@@ -475,7 +477,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
                 cudaFree(d_rc);
             }
         }
-        free(h); free(tb);
+        free(h);
         if (rc) { sdrb200_acq_destroy(a); return rc; }
     }
     *out = a;

@@ -1,0 +1,119 @@
+/* port_trk.c - one code period of tracking, loop filters and bit sync,
+ * restated for the CPU (TEST INFRASTRUCTURE; see port.h). */
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include "port.h"
+
+/* checksync, src/sdrnav.c:198-233 (overlay code is all ones for L1CA/SBAS/G1,
+ * src/sdrinit.c:520-558) */
+static int bit_sync_step(double IP, double IPold, p_chan_t *c)
+{
+    int i;
+    if (c->prn > 5) {                                        /* keyed on PRN only, :203 */
+        int corr = 0;
+        memmove(&c->bitsync[0], &c->bitsync[1], sizeof(int) * (size_t)(c->rate - 1));
+        c->bitsync[c->rate - 1] = (IP < 0 ? -1 : 1);
+        for (i = 0; i < c->rate; i++) corr += c->bitsync[i];
+        if (abs(corr) == c->rate) { c->synci = c->biti; return 1; }
+    } else if (IPold * IP < 0) {
+        int best, at = 0;
+        c->bitsync[c->biti] += 1;
+        best = c->bitsync[0];                                /* maxvi, src/sdrcmn.c:417-431 */
+        for (i = 1; i < c->rate; i++) if (best < c->bitsync[i]) { best = c->bitsync[i]; at = i; }
+        c->synci = at;
+        if (best > P_NAVSYNCTH) {
+            c->synci--;
+            if (c->synci < 0) c->synci = c->rate - 1;
+            return 1;
+        }
+    }
+    return 0;
+}
+
+/* checkbit, src/sdrnav.c:241-282 (frame-bit shift register omitted: frame
+ * decoding is outside the hot path) */
+static void bit_decide(double IP, p_chan_t *c)
+{
+    const int diffi = c->biti - c->synci;
+    c->swreset = 0; c->swsync = 0;
+    if (diffi == 1 || diffi == -c->rate + 1) { c->bitIP = IP; c->swreset = 1; c->navcnt = 1; }
+    else c->bitIP += IP;
+    c->swloop = (c->navcnt % c->loopms == 0) ? 1 : 0;
+    if (diffi == 0) { c->bit = (c->bitIP < 0) ? -1 : 1; c->swsync = 1; }
+    c->navcnt++;
+}
+
+/* sdrtracking (src/sdrtrk.c:15-54) followed by the bit-sync part of
+ * sdrnavigation (src/sdrnav.c:19-41) */
+void p_tracking(p_chan_t *c, const signed char *stream, uint64_t buffloc, uint64_t cnt)
+{
+    const int nt = 1 + 2 * c->corrn;
+    double carr[P_MAXTAPS], quad[P_MAXTAPS];
+    c->currnsamp = (int)((c->clen - c->remcode) / (c->codefreq / c->f_sf));       /* :31-32 */
+    /* memcpy of 1+2*corrn*8 bytes (:35-36): 2*corrn doubles plus the first byte of the last */
+    memcpy(c->oldI, c->II, 1 + 2 * (size_t)c->corrn * sizeof(double));
+    memcpy(c->oldQ, c->QQ, 1 + 2 * (size_t)c->corrn * sizeof(double));
+    c->oldremcode = c->remcode;
+    c->oldremcarr = c->remcarr;
+    /* the call passes trk.QQ as the cosine output and trk.II as the sine output (:40-43) */
+    p_correlator(stream + buffloc * c->dtype, c->dtype, c->ti, c->currnsamp, c->carrfreq,
+                 c->oldremcarr, c->codefreq, c->oldremcode, c->corrp, c->corrn, carr, quad,
+                 &c->remcode, &c->remcarr, c->code, c->clen);
+    memcpy(c->QQ, carr, sizeof(double) * nt);
+    memcpy(c->II, quad, sizeof(double) * nt);
+
+    c->biti = (int)(cnt % (uint64_t)c->rate);
+    c->ocodei = c->biti - c->synci - 1;
+    if (c->ocodei < 0) c->ocodei += c->rate;
+    if (c->rate == 1 && cnt > 2000 / (c->ctime * 1000)) { c->synci = 0; c->flagsync = 1; }
+    if (!c->flagsync && cnt > 2000 / (c->ctime * 1000))
+        c->flagsync = bit_sync_step(c->II[0], c->oldI[0], c);
+    if (c->flagsync) bit_decide(c->II[0], c);
+}
+
+/* src/sdrtrk.c:64-76 */
+void p_cumsumcorr(p_chan_t *c, int polarity)
+{
+    int i;
+    for (i = 0; i < 1 + 2 * c->corrn; i++) {
+        c->II[i] *= polarity; c->QQ[i] *= polarity;
+        c->oldsumI[i] += c->oldI[i]; c->oldsumQ[i] += c->oldQ[i];
+        c->sumI[i] += c->II[i];      c->sumQ[i] += c->QQ[i];
+    }
+}
+
+/* src/sdrtrk.c:77-86 */
+void p_clearcumsumcorr(p_chan_t *c)
+{
+    int i;
+    for (i = 0; i < 1 + 2 * c->corrn; i++) c->oldsumI[i] = c->oldsumQ[i] = c->sumI[i] = c->sumQ[i] = 0;
+}
+
+/* src/sdrtrk.c:94-125 */
+void p_pll(p_chan_t *c, const p_loop_t *prm, double dt)
+{
+    const double IP = c->sumI[0], QP = c->sumQ[0], oIP = c->oldsumI[0], oQP = c->oldsumQ[0];
+    double carrErr, freqErr, f1, f2;
+    carrErr = (IP > 0) ? atan2(QP, IP) / P_PI : atan2(-QP, -IP) / P_PI;
+    f1 = (IP == 0) ? P_PI / 2 : atan(QP / IP);
+    f2 = (oIP == 0) ? P_PI / 2 : atan(oQP / oIP);
+    freqErr = f1 - f2;
+    if (freqErr > P_PI / 2) freqErr = P_PI - freqErr;
+    if (freqErr < -P_PI / 2) freqErr = -P_PI - freqErr;
+    c->carrNco += prm->pllaw * (carrErr - c->carrErr) + prm->pllw2 * dt * carrErr + prm->fllw * dt * freqErr;
+    c->carrfreq = c->acqfreq + c->carrNco;
+    c->carrErr = carrErr;
+    c->freqErr = freqErr;
+}
+
+/* src/sdrtrk.c:133-150 */
+void p_dll(p_chan_t *c, const p_loop_t *prm, double dt)
+{
+    const double IE = c->sumI[c->ne], IL = c->sumI[c->nl], QE = c->sumQ[c->ne], QL = c->sumQ[c->nl];
+    const double codeErr = (sqrt(IE * IE + QE * QE) - sqrt(IL * IL + QL * QL)) /
+                           (sqrt(IE * IE + QE * QE) + sqrt(IL * IL + QL * QL));
+    c->codeNco += prm->dllaw * (codeErr - c->codeErr) + prm->dllw2 * dt * codeErr;
+    c->codefreq = c->crate - c->codeNco + (c->carrfreq - c->f_if - c->foffset) / (c->f_cf / c->crate);
+    c->codeErr = codeErr;
+}

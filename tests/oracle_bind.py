@@ -198,6 +198,16 @@ def port() -> Oracle:
     return Oracle(PORT_SO)
 
 
+def have_dropin() -> bool:
+    return os.path.exists(DROPIN_SO)
+
+
+def dropin() -> Oracle:
+    """the reference's cold objects + replay.c with every hot sdr.h symbol bound to
+    libsdrb200_sdrh.so (needs a GPU at call time)"""
+    return Oracle(DROPIN_SO)
+
+
 def best() -> Oracle:
     """the reference build when present (this container), else the CPU port."""
     return ref() if have_ref() else port()

@@ -1,0 +1,123 @@
+"""CPU: pins the oracle.  (1) the CPU restatement oracle/port reproduces, bit for
+bit, the golden vectors that tests/golden/make_golden.py recorded from the
+REFERENCE build (the reference's own C sources + oracle FFT shim); (2) where the
+reference build is present (this container) the two are compared directly on
+fresh inputs.  Both use oracle/offt.c for the FFT, so equality is exact."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_bind as ob
+import util
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+REC_FIELDS = ["cnt", "buffloc", "currnsamp", "flagsync", "flagloopfilter", "swsync", "swloop", "synci",
+              "biti", "bit", "II", "QQ", "sumI0", "sumQ0", "codefreq", "codeErr", "codeNco", "carrfreq",
+              "carrErr", "carrNco", "freqErr", "remcode", "remcarr"]
+
+
+@pytest.fixture(scope="module")
+def port():
+    if not ob.have_port():
+        pytest.skip("oracle/liboracle_port.so not built")
+    return ob.port()
+
+
+def _acq_rows(res):
+    return np.array([[r.acquired, r.freqi, r.codei, r.nintg_used, r.acqfreq, r.peakr, r.cn0, r.maxp, r.buffloc]
+                     for r in res])
+
+
+def test_port_primitives_golden(port):
+    g = np.load(os.path.join(G, "primitives.npz"))
+    for i, prm in enumerate(g["params"]):
+        dtype, n = int(prm[0]), int(prm[1])
+        ti, freq, phi0, crate, coff = prm[2:]
+        d = g["d_real"][:n] if dtype == 1 else g["d_iq"][:2 * n]
+        s = g[f"s{i}"]
+        II, QQ, remc, remp = port.correlator(d, dtype, ti, n, freq, phi0, crate, coff, s, g["code7"])
+        assert np.array_equal(II, g[f"II{i}"]) and np.array_equal(QQ, g[f"QQ{i}"])
+        mI, mQ, mrem = port.mixcarr(d, dtype, ti, n, freq, phi0)
+        assert np.array_equal(mI, g[f"mI{i}"]) and np.array_equal(mQ, g[f"mQ{i}"])
+        rc, rrem = port.rescode(g["code7"], coff, int(s[-1]), ti * crate, n)
+        assert np.array_equal(rc, g[f"rc{i}"])
+        assert np.array_equal(np.array([remc, remp, mrem, rrem]), g[f"rem{i}"])
+
+
+def test_port_codes_golden(port):
+    g = np.load(os.path.join(G, "codes.npz"))
+    bits = np.unpackbits(g["l1ca"], axis=1)[:, :1023]
+    for prn in range(1, 211):
+        code, crate = port.gencode(prn, 1)
+        assert crate == 1.023e6 and np.array_equal(code > 0, bits[prn - 1].astype(bool)), prn
+        assert set(np.unique(code)) == {-1, 1}
+    code, crate = port.gencode(3, 20)                    # G1: 511-chip m-sequence, balance -1
+    assert len(code) == 511 and crate == 0.511e6 and abs(int(code.sum())) == 1
+    ac = np.array([np.dot(code, np.roll(code, k)) for k in range(1, 511)])
+    assert np.all(ac == -1)                              # two-valued autocorrelation of an m-sequence
+
+
+def test_port_fft_primitives_golden(port):
+    g = np.load(os.path.join(G, "fftprims.npz"))
+    for n in (12, 62, 1000):
+        a, b = g[f"a{n}"], g[f"b{n}"]
+        assert np.array_equal(port.cpxfft(a), g[f"fft{n}"])
+        assert np.array_equal(port.cpxfft(a, inverse=True), g[f"ifft{n}"])
+        assert np.array_equal(port.cpxconv(a, b, n // 2), g[f"conv{n}"])
+        assert np.array_equal(port.cpxpspec(a), g[f"pspec{n}"])
+        # against numpy's double-precision FFT: float rounding only
+        assert np.abs(g[f"fft{n}"] - np.fft.fft(a.astype(np.complex128))).max() < 1e-5 * np.sqrt(n) * 4
+    x, nsamp, nfft = port.codefft(3, 1, util.FS5)
+    assert (nsamp, nfft) == (2048, 4096) and np.array_equal(x, g["codefft_prn3_fs2048"])
+
+
+def test_port_acquisition_golden(port):
+    g = np.load(os.path.join(G, "acq_c1.npz"))
+    prns = [int(p) for p in g["prns"]]
+    res, pw = port.acquire(ob.cfg_iffile(acq_intg=2), g["if_data"], 65536, prns, want_power=True)
+    assert np.array_equal(_acq_rows(res), g["result"])
+    rows = np.stack([pw[i, res[i].freqi] for i in range(len(prns))]).astype(np.float32)
+    assert np.array_equal(rows, g["power_row"])
+    assert [r.acquired for r in res] == [1, 1, 1, 1, 0, 0]
+    assert {r.nintg_used for r in res} == {1, 2}         # early exit and full depth both covered
+
+
+def test_port_tracking_golden(port):
+    g = np.load(os.path.join(G, "trk_c5.npz"))
+    prns = [int(p) for p in g["prns"]]
+    nper = int(g["nper"])
+    acq, rec, ntr = port.acq_track(ob.cfg_rtlsdr(acq_intg=2), g["if_data"], 65536, prns, nper)
+    assert np.array_equal(_acq_rows(acq), g["acq"])
+    assert np.array_equal(np.array(ntr), g["ntracked"]) and ntr[0] == nper
+    for f in REC_FIELDS:
+        assert np.array_equal(np.ascontiguousarray(rec[f]), g["rec_" + f]), f
+
+
+def test_port_equals_reference_build(port):
+    """fresh random inputs, reference build vs port, everything bit-exact."""
+    if not ob.have_ref():
+        pytest.skip("reference build absent (GPU box): covered by the golden vectors")
+    ref = ob.ref()
+    rng = np.random.default_rng(77)
+    code = ref.gencode(19, 1)[0]
+    assert np.array_equal(code, port.gencode(19, 1)[0])
+    for dtype, n0, fs, s in ((1, 16368, util.FS1, [3, 6, 9, 12, 15, 18]), (2, 2048, util.FS5, [1, 2, 3, 4])):
+        for _ in range(4):
+            n = n0 + int(rng.integers(-2, 3))
+            d = rng.integers(-128, 128, n * dtype, dtype=np.int8)
+            a = (d, dtype, 1 / fs, n, float(rng.uniform(-5e3, 4.1e6)), float(rng.uniform(0, 6.28)),
+                 1.023e6 + float(rng.uniform(-5, 5)), float(rng.uniform(0, 1023)), s, code)
+            r, p = ref.correlator(*a), port.correlator(*a)
+            assert all(np.array_equal(np.asarray(x), np.asarray(y)) for x, y in zip(r, p))
+    # a short closed-loop run through acquisition, bit sync pre-phase and the loop filters
+    import sdrb200_pkg
+    sdr = sdrb200_pkg.load()
+    cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000099)
+    nper = 60
+    host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
+    a1, r1, n1 = ref.acq_track(ob.cfg_rtlsdr(acq_intg=1), host, 65536, vis, nper)
+    a2, r2, n2 = port.acq_track(ob.cfg_rtlsdr(acq_intg=1), host, 65536, vis, nper)
+    assert np.array_equal(_acq_rows(a1), _acq_rows(a2)) and n1 == n2
+    for f in REC_FIELDS:
+        assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
