@@ -18,9 +18,10 @@
  *   multiples of u below 2^(e+1), hence representable; j*d and the sum are
  *   exact in double arithmetic).
  *
- * nco_walk_* therefore performs real additions only around binade changes /
- * wraps and jumps over the interior of each binade, emitting a short table of
- * linear segments (a few dozen entries for 16368 samples).  Any thread can
+ * nco_walk therefore performs real additions only around binade changes /
+ * wraps and jumps over the interior of each binade with an EXACT run length
+ * (nco_jump), emitting a short table of linear segments (about two per binade
+ * crossed: ~30 entries for 16368 samples).  Any thread can
  * then evaluate x_k for its own k from the table.  Verified against the plain
  * sequential loops over millions of random cases in tests/test_nco_exact.py.
  */
@@ -117,39 +118,55 @@ NCO_HD double nco_binade_lo(double x)
     return nco_from_bits(nco_bits(x) & 0x7FF0000000000000ULL);
 }
 
-/* How many further constant-increment steps may be taken from x1 (increment d,
- * same binade assumed for x1 and x1+d) such that every value stays inside the
- * binade of x1 and strictly below `limit` in the direction of travel
- * (limit_on: 0 none, 1: values must stay < limit, 2: values must stay > limit).
- * Conservative by two steps; the caller finishes with real additions.          */
-NCO_HD int32_t nco_room(double x1, double d, int limit_on, double limit, int32_t maxj)
+/* all values of one run share the binade of its first value and stay on the
+ * permitted side of `limit` (limit_on 0: none, 1: value < limit, 2: value > limit) */
+NCO_HD int nco_in_run(double x1, double y, int limit_on, double limit)
 {
-    double lo = nco_binade_lo(x1);          /* magnitude bounds [lo, 2lo)      */
-    double hi = lo + lo;
-    double m = fabs(x1);
-    double room, j;
+    if (!nco_same_binade(x1, y)) return 0;
+    if (limit_on == 1 && y >= limit) return 0;
+    if (limit_on == 2 && !(y > limit)) return 0;
+    return 1;
+}
+
+/* EXACT run length: the largest J in [0, maxj] such that x1 + j*d stays in the
+ * run for every j <= J (d != 0 keeps the sequence monotone).  An estimate
+ * room * inv_d (inv_d: approximate reciprocal of |d|, computed once per walk) is
+ * corrected with exact double arithmetic: inside one
+ * binade j*d and x1 + j*d are exact, and a sum that leaves the binade compares
+ * on the correct side of its border after rounding.  *y = x1 + J*d.             */
+NCO_HD int32_t nco_jump(double x1, double d, double inv_d, int limit_on, double limit, int32_t maxj, double *y)
+{
+    double lo = nco_binade_lo(x1), hi = lo + lo, m = fabs(x1), room, yy, y2;
     int growing = ((x1 > 0.0) == (d > 0.0));
-    if (d == 0.0) return maxj;
+    int32_t J;
+    double est;
+    if (d == 0.0 || maxj <= 0) { *y = x1; return maxj > 0 ? maxj : 0; }
     room = growing ? (hi - m) : (m - lo);
     if (limit_on == 1 && d > 0.0) { double r2 = limit - x1; if (r2 < room) room = r2; }
     if (limit_on == 2 && d < 0.0) { double r2 = x1 - limit; if (r2 < room) room = r2; }
-    if (!(room > 0.0)) return 0;
-    j = floor(room / fabs(d)) - 2.0;
-    if (j < 0.0) return 0;
-    if (j > (double)maxj) return maxj;
-    return (int32_t)j;
+    est = NCO_MUL(room, inv_d);         /* inv_d ~ 1/|d| (any accuracy: J is corrected below) */
+    if (!(est > 0.0)) J = 0;
+    else if (est >= (double)maxj) J = maxj;
+    else J = (int32_t)est;
+    yy = NCO_ADD(x1, NCO_MUL((double)J, d));
+    while (J > 0 && !nco_in_run(x1, yy, limit_on, limit)) { J--; yy = NCO_ADD(x1, NCO_MUL((double)J, d)); }
+    while (J < maxj) {
+        y2 = NCO_ADD(yy, d);
+        if (!nco_in_run(x1, y2, limit_on, limit)) break;
+        yy = y2; J++;
+    }
+    *y = yy;
+    return J;
 }
 
-NCO_HD void nco_emit(nco_table_t *t, int32_t k0, double x0, double d)
+/* approximate 1/|x| (single-precision accuracy is plenty for nco_jump) */
+NCO_HD double nco_rcp_est(double x)
 {
-    if (t->nseg < NCO_MAXSEG) {
-        t->seg[t->nseg].k0 = k0; t->seg[t->nseg].pad = 0;
-        t->seg[t->nseg].x0 = x0; t->seg[t->nseg].d = d;
-        t->nseg++;
-    } else {
-        t->nseg = NCO_MAXSEG + 1;           /* overflow marker (caller checks) */
-    }
+    return (double)(1.0f / (float)fabs(x));
 }
+
+#define NCO_EMIT(K0, X0, DD) do { if (ns < NCO_MAXSEG) { nco_seg_t *sg_ = &t->seg[ns]; sg_->k0 = (K0); sg_->pad = 0; \
+                                   sg_->x0 = (X0); sg_->d = (DD); } ns++; } while (0)
 
 /* Sequence   for k in 0..count-1: { if (wrap>0 && x>=wrap) x-=wrap; use x; x+=step; }
  * (wrap = 0: no wrap test, the carrier NCO; wrap = code length: the code NCO).
@@ -157,37 +174,39 @@ NCO_HD void nco_emit(nco_table_t *t, int32_t k0, double x0, double d)
  * last addition.  Returns 0, or -1 if the table overflowed.                    */
 NCO_HD int nco_walk(double x, double step, int32_t count, double wrap, nco_table_t *t)
 {
-    int32_t k = 0;
+    int32_t k = 0, ns = 0;
     const int lim = (wrap > 0.0) ? 1 : 0;
-    t->nseg = 0; t->count = count;
+    const double inv = nco_rcp_est(step);
     while (k < count) {
         double x1, x2, d;
         int32_t J;
         if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
         x1 = NCO_ADD(x, step);
         if (x1 == x) {                      /* step is zero or below half an ulp: */
-            nco_emit(t, k, x, 0.0);         /* the accumulator never moves again  */
+            NCO_EMIT(k, x, 0.0);            /* the accumulator never moves again  */
             k = count;
             break;
         }
         if (k + 1 >= count || (lim && x1 >= wrap) || !nco_same_binade(x, x1)) {
-            nco_emit(t, k, x, 0.0); k += 1; x = x1; continue;
+            NCO_EMIT(k, x, 0.0); k += 1; x = x1; continue;
         }
         x2 = NCO_ADD(x1, step);
         if (k + 2 >= count || (lim && x2 >= wrap) || !nco_same_binade(x1, x2)) {
-            nco_emit(t, k, x, NCO_ADD(x1, -x)); k += 2; x = x2; continue;
+            NCO_EMIT(k, x, NCO_ADD(x1, -x)); k += 2; x = x2; continue;
         }
         d = NCO_ADD(x2, -x1);
-        /* steady state from x1: values x1 + j*d, j = 0..J, J >= 1 (x2 is j = 1) */
-        J = nco_room(x1, d, lim, wrap, count - 2 - k);
-        if (J < 1) J = 1;
-        nco_emit(t, k, x, 0.0);
-        nco_emit(t, k + 1, x1, d);
-        x = NCO_ADD(NCO_ADD(x1, NCO_MUL((double)J, d)), step);
+        /* steady state from x1: values x1 + j*d, j = 0..J, J >= 1 (x2 is j = 1),
+         * J exact: the addition after the run leaves the binade (or wraps)      */
+        J = nco_jump(x1, d, inv, lim, wrap, count - 2 - k, &x2);
+        NCO_EMIT(k, x, 0.0);
+        NCO_EMIT(k + 1, x1, d);
+        x = NCO_ADD(x2, step);
         k += 2 + J;
     }
     t->x_end = x;
-    return (t->nseg > NCO_MAXSEG) ? -1 : 0;
+    t->count = count;
+    t->nseg = ns;
+    return (ns > NCO_MAXSEG) ? -1 : 0;
 }
 
 /* value used at index k (0 <= k < count); seg hint speeds up monotone scans */
@@ -200,10 +219,57 @@ NCO_HD double nco_value(const nco_table_t *t, int32_t k, int32_t *hint)
     return NCO_ADD(t->seg[s].x0, NCO_MUL((double)(k - t->seg[s].k0), t->seg[s].d));
 }
 
+
+/* ---- integer form of a segment ------------------------------------------------
+ * All values of a segment lie in ONE binade [2^e, 2^(e+1)) and are multiples of
+ * u = 2^(e-52): value_j = (X0 + j*D) * u with X0 < 2^53 and X0 + j*D < 2^53.
+ * The C cast (int)value, which the reference applies to every NCO value
+ * (src/sdrcmn.c:615,652,659), is therefore sign * ((X0 + j*D) >> (52 - e)):
+ * two integer multiply-adds and a shift per sample instead of FP64 arithmetic. */
+typedef struct {
+    int32_t  k0;
+    int32_t  shift;      /* 52 - e, clamped to 64 (|value| < 1 -> 0)            */
+    uint64_t X0;
+    int64_t  D;          /* signed change of the MAGNITUDE per step             */
+    int32_t  neg;        /* values are negative                                 */
+    int32_t  pad;
+} nco_iseg_t;
+
+NCO_HD void nco_iseg_make(const nco_seg_t *s, nco_iseg_t *o)
+{
+    const uint64_t bx = nco_bits(s->x0), bd = nco_bits(s->d);
+    const int ex = (int)((bx >> 52) & 0x7FF), ed = (int)((bd >> 52) & 0x7FF);
+    o->k0 = s->k0; o->pad = 0;
+    o->neg = (int32_t)(bx >> 63);
+    if (ex == 0) { o->X0 = 0; o->D = 0; o->shift = 64; return; }      /* zero / subnormal: (int) gives 0 */
+    o->X0 = (bx & 0x000FFFFFFFFFFFFFULL) | 0x0010000000000000ULL;
+    {
+        const int sh = 52 - (ex - 1023);
+        o->shift = sh > 64 ? 64 : (sh < 0 ? -1 : sh);                   /* -1: |value| >= 2^53, unsupported */
+    }
+    if (ed == 0 || (bd << 1) == 0) { o->D = 0; return; }
+    {
+        const uint64_t md = (bd & 0x000FFFFFFFFFFFFFULL) | 0x0010000000000000ULL;
+        const int dsh = ex - ed;                                        /* >= 0: |d| < 2^(e+1) */
+        const uint64_t mag = (dsh < 0) ? (md << 1) : (dsh > 63 ? 0 : (md >> dsh));
+        const int grows = ((bx >> 63) == (bd >> 63));
+        o->D = grows ? (int64_t)mag : -(int64_t)mag;
+    }
+}
+
+/* (int)value at index k of the segment (C truncation toward zero) */
+NCO_HD int64_t nco_iseg_trunc(const nco_iseg_t *s, int32_t k)
+{
+    const uint64_t m = s->X0 + (uint64_t)((int64_t)(k - s->k0) * s->D);
+    const int64_t t = (s->shift >= 64) ? 0 : (int64_t)(m >> s->shift);
+    return s->neg ? -t : t;
+}
+
 /* while (x > 2pi) x -= 2pi;   (src/sdrcmn.c:666-668), exactly */
 NCO_HD double nco_reduce_2pi(double x)
 {
     const double P = NCO_TWO_PI;
+    const double inv = 0.15915494309189535;      /* ~1/(2*pi) */
     while (x > P) {
         double x1 = NCO_ADD(x, -P), x2, d;
         int32_t J;
@@ -211,9 +277,8 @@ NCO_HD double nco_reduce_2pi(double x)
         x2 = NCO_ADD(x1, -P);
         if (!(x2 > P) || !nco_same_binade(x1, x2)) { x = x2; continue; }
         d = NCO_ADD(x2, -x1);
-        J = nco_room(x1, d, 2, P, 0x7FFFFFF0);
-        if (J < 1) J = 1;
-        x = NCO_ADD(x1, NCO_MUL((double)J, d));
+        J = nco_jump(x1, d, inv, 2, P, 0x7FFFFFF0, &x);
+        (void)J;
     }
     return x;
 }

@@ -40,33 +40,38 @@ extern "C" int sdrb200_trk_lut_ready(void)
  * out: II[ntap], QQ[ntap], remc, remp  (doubles)
  * ---------------------------------------------------------------------- */
 template <int DTYPE>
-__global__ void __launch_bounds__(1024, 1)
+__global__ void __launch_bounds__(TRK_THREADS, 1)
 k_correlator(const int8_t *__restrict__ data, double ti, int n, double freq, double phi0,
              double crate, double coff, const int *__restrict__ taps_g, int ns,
-             const int8_t *__restrict__ code_g, int coden, double *__restrict__ out,
+             const int8_t *__restrict__ code_g, int coden, int qcap, double *__restrict__ out,
              int *__restrict__ err)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     trk_smem_t *sm = (trk_smem_t *)smem_raw;
     int *taps = (int *)(smem_raw + sizeof(trk_smem_t));
-    int8_t *rc = (int8_t *)(taps + SDRB200_MAXCORRN);
+    const trk_work_t wk = trk_work_layout<DTYPE>((unsigned int *)(taps + SDRB200_MAXCORRN), n, qcap);
+    const bool worker = threadIdx.x >= 64;
 
-    if (threadIdx.x == 0) sm->err = 0;
+    trk_init_smem(sm);
     for (int i = threadIdx.x; i < coden; i += blockDim.x) sm->codetab[i] = code_g[i];
     if (threadIdx.x < ns) taps[threadIdx.x] = taps_g[threadIdx.x];
     __syncthreads();
     const int smax = taps[ns - 1];                                   /* sdrcmn.c:694 */
 
-    trk_build_tables(sm, DTYPE, ti, n, freq, phi0, crate, coff, smax, coden);
+    trk_build_tables(sm, ti, n, freq, phi0, crate, coff, smax, coden);
     __syncthreads();
-    trk_fill_replica(sm, rc, n, smax);
+    trk_convert_tables(sm);
     __syncthreads();
-    trk_accumulate<DTYPE>(sm, rc, data, n, taps, ns, smax);
+    if (worker) trk_mix_prefix<DTYPE>(sm, data, n, wk);
+    else trk_carrier_rem(sm);
+    __syncthreads();
+    if (worker) trk_tap_sums<DTYPE>(sm, wk, data, n, taps, ns, smax);
+    __syncthreads();
 
     const int ntap = 1 + 2 * ns;
     if (threadIdx.x < ntap) {
-        out[threadIdx.x]        = (double)(long long)sm->sumI[threadIdx.x] * SDRB200_CSCALE;
-        out[ntap + threadIdx.x] = (double)(long long)sm->sumQ[threadIdx.x] * SDRB200_CSCALE;
+        out[threadIdx.x]        = (double)(int)sm->sum[threadIdx.x] * SDRB200_CSCALE;
+        out[ntap + threadIdx.x] = (double)(int)sm->sum[SDRB200_MAXTAPS + threadIdx.x] * SDRB200_CSCALE;
     }
     if (threadIdx.x == 0) {
         out[2 * ntap] = sm->remc;
@@ -75,10 +80,16 @@ k_correlator(const int8_t *__restrict__ data, double ti, int n, double freq, dou
     }
 }
 
-static size_t corr_smem_bytes(int n, int smax)
+/* chip transitions inside n + 2*smax samples, with head room */
+static int trk_qcap(int n, int smax, double chips_per_sample)
 {
-    return sizeof(trk_smem_t) + sizeof(int) * SDRB200_MAXCORRN + (size_t)(n + 2 * smax + 64);
+    return (int)((double)(n + 2 * smax) * chips_per_sample * 1.01) + 16;
 }
+static size_t corr_smem_bytes(int n, int dtype, int qcap)
+{
+    return sizeof(trk_smem_t) + sizeof(int) * SDRB200_MAXCORRN + sizeof(unsigned int) * TRK_WORK_WORDS(n, dtype, qcap);
+}
+#define TRK_SMEM_LIMIT (225 * 1024)
 
 extern "C" int sdrb200_correlator(const int8_t *data, int dtype, double ti, int n, double freq,
                                   double phi0, double crate, double coff, const int *s, int ns,
@@ -91,8 +102,10 @@ extern "C" int sdrb200_correlator(const int8_t *data, int dtype, double ti, int 
     }
     const int smax = s[ns - 1];
     if (smax < 0) { sdrb200_set_error("correlator: negative tap"); return SDRB200_EINVAL; }
-    const size_t smem = corr_smem_bytes(n, smax);
-    if (smem > 220 * 1024) { sdrb200_set_error("correlator: window of %d samples too long", n); return SDRB200_EINVAL; }
+    if (!(ti * crate > 0) || ti * crate > 0.5) { sdrb200_set_error("correlator: needs at least two samples per chip"); return SDRB200_EINVAL; }
+    const int qcap = trk_qcap(n, smax, ti * crate);
+    const size_t smem = corr_smem_bytes(n, dtype, qcap);
+    if (smem > TRK_SMEM_LIMIT) { sdrb200_set_error("correlator: window of %d samples too long for one CTA", n); return SDRB200_EINVAL; }
     const int ntap = 1 + 2 * ns;
     const size_t nbytes = (size_t)n * dtype;
     /* device arena: [16 guard][data][32 guard] | code | taps | out | err */
@@ -119,17 +132,14 @@ extern "C" int sdrb200_correlator(const int8_t *data, int dtype, double ti, int 
 
     double *d_out = (double *)(w->d_arena + off_out);
     int *d_err = (int *)(w->d_arena + off_err);
-    if (dtype == 1) {
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_correlator<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_correlator<1><<<1, 1024, smem, st>>>((const int8_t *)(w->d_arena + off_data), ti, n, freq, phi0, crate, coff,
-                                              (const int *)(w->d_arena + off_taps), ns,
-                                              (const int8_t *)(w->d_arena + off_code), coden, d_out, d_err);
-    } else {
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_correlator<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_correlator<2><<<1, 1024, smem, st>>>((const int8_t *)(w->d_arena + off_data), ti, n, freq, phi0, crate, coff,
-                                              (const int *)(w->d_arena + off_taps), ns,
-                                              (const int8_t *)(w->d_arena + off_code), coden, d_out, d_err);
-    }
+#define CORR_LAUNCH(DT)                                                                                   \
+    do {                                                                                                  \
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_correlator<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        k_correlator<DT><<<1, TRK_THREADS, smem, st>>>((const int8_t *)(w->d_arena + off_data), ti, n, freq, phi0, \
+            crate, coff, (const int *)(w->d_arena + off_taps), ns, (const int8_t *)(w->d_arena + off_code), coden, qcap, d_out, d_err); \
+    } while (0)
+    if (dtype == 1) CORR_LAUNCH(1); else CORR_LAUNCH(2);
+#undef CORR_LAUNCH
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     double *h = (double *)w->h_arena;
@@ -222,99 +232,113 @@ __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int 
     st->navcnt++;
 }
 
-/* pll(), src/sdrtrk.c:94-125 */
-__device__ static void trk_pll(trk_state_t *st, const sdrb200_loop_t *prm, double dt, double acqfreq)
+__device__ __forceinline__ long long trk_clock()
 {
-    double IP = st->sumI[0], QP = st->sumQ[0];
-    double oldIP = st->oldsumI[0], oldQP = st->oldsumQ[0];
-    double carrErr, freqErr, f1, f2;
-    if (IP > 0) carrErr = atan2(QP, IP) / TRK_PI;
-    else        carrErr = atan2(-QP, -IP) / TRK_PI;
-    f1 = (IP == 0) ? TRK_PI / 2 : atan(QP / IP);
-    f2 = (oldIP == 0) ? TRK_PI / 2 : atan(oldQP / oldIP);
-    freqErr = f1 - f2;
-    if (freqErr > TRK_PI / 2) freqErr = TRK_PI - freqErr;
-    if (freqErr < -TRK_PI / 2) freqErr = -TRK_PI - freqErr;
-    st->carrNco += prm->pllaw * (carrErr - st->carrErr) + prm->pllw2 * dt * carrErr + prm->fllw * dt * freqErr;
-    st->carrfreq = acqfreq + st->carrNco;
-    st->carrErr = carrErr;
-    st->freqErr = freqErr;
+    long long t;
+    asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory");
+    return t;
 }
 
-/* dll(), src/sdrtrk.c:133-150 */
-__device__ static void trk_dll(trk_state_t *st, const sdrb200_loop_t *prm, double dt, const trk_chan_dev_t *ch)
+/* pll() + dll(), src/sdrtrk.c:94-125 / 133-150, by one warp: the five libm calls
+ * (atan2, 2 x atan, 2 x sqrt) are independent of each other and run on five
+ * lanes at once; lane 0 then finishes the scalar updates in the reference's
+ * order of operations.                                                        */
+__device__ static void trk_loops_warp(trk_state_t *st, const sdrb200_loop_t *prm, double dt,
+                                      const trk_chan_dev_t *ch, int lane)
 {
-    double IE = st->sumI[ch->ne], IL = st->sumI[ch->nl];
-    double QE = st->sumQ[ch->ne], QL = st->sumQ[ch->nl];
-    double e = sqrt(IE * IE + QE * QE), l = sqrt(IL * IL + QL * QL);
-    double codeErr = (e - l) / (e + l);
-    st->codeNco += prm->dllaw * (codeErr - st->codeErr) + prm->dllw2 * dt * codeErr;
-    st->codefreq = ch->crate - st->codeNco + (st->carrfreq - ch->f_if - ch->foffset) / (ch->f_cf / ch->crate);
-    st->codeErr = codeErr;
+    const double IP = st->sumI[0], QP = st->sumQ[0], oldIP = st->oldsumI[0], oldQP = st->oldsumQ[0];
+    const double IE = st->sumI[ch->ne], IL = st->sumI[ch->nl], QE = st->sumQ[ch->ne], QL = st->sumQ[ch->nl];
+    double r = 0.0;
+    if (lane == 0)      r = (IP > 0) ? atan2(QP, IP) : atan2(-QP, -IP);
+    else if (lane == 1) r = (IP == 0) ? TRK_PI / 2 : atan(QP / IP);
+    else if (lane == 2) r = (oldIP == 0) ? TRK_PI / 2 : atan(oldQP / oldIP);
+    else if (lane == 3) r = sqrt(IE * IE + QE * QE);
+    else if (lane == 4) r = sqrt(IL * IL + QL * QL);
+    const double f1 = __shfl_sync(0xffffffffu, r, 1), f2 = __shfl_sync(0xffffffffu, r, 2);
+    const double e = __shfl_sync(0xffffffffu, r, 3), l = __shfl_sync(0xffffffffu, r, 4);
+    if (lane == 0) {
+        const double carrErr = r / TRK_PI;
+        double freqErr = f1 - f2;
+        if (freqErr > TRK_PI / 2) freqErr = TRK_PI - freqErr;
+        if (freqErr < -TRK_PI / 2) freqErr = -TRK_PI - freqErr;
+        st->carrNco += prm->pllaw * (carrErr - st->carrErr) + prm->pllw2 * dt * carrErr + prm->fllw * dt * freqErr;
+        st->carrfreq = ch->acqfreq + st->carrNco;
+        st->carrErr = carrErr;
+        st->freqErr = freqErr;
+        const double codeErr = (e - l) / (e + l);
+        st->codeNco += prm->dllaw * (codeErr - st->codeErr) + prm->dllw2 * dt * codeErr;
+        st->codefreq = ch->crate - st->codeNco + (st->carrfreq - ch->f_if - ch->foffset) / (ch->f_cf / ch->crate);
+        st->codeErr = codeErr;
+    }
 }
 
-/* scalar epilogue of one code period (thread 0): everything sdrtracking and
+/* epilogue of one code period, executed by ONE warp: everything sdrtracking and
  * the sdrthread loop body do around correlator()                              */
 __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const trk_smem_t *sm,
-                                    sdrb200_trk_rec_t *rec)
+                                    sdrb200_trk_rec_t *rec, int lane)
 {
     const int ntap = 1 + 2 * ch->corrn;
     /* src/sdrtrk.c:35-38: the memcpy length 1+2*corrn*8 bytes covers 2*corrn doubles
      * (plus one stray byte of the next, which no consumer reads)               */
-    for (int i = 0; i < 2 * ch->corrn; i++) { st->oldI[i] = st->II[i]; st->oldQ[i] = st->QQ[i]; }
-    st->oldremcode = st->remcode;
-    st->oldremcarr = st->remcarr;
+    for (int i = lane; i < 2 * ch->corrn; i += 32) { st->oldI[i] = st->II[i]; st->oldQ[i] = st->QQ[i]; }
+    __syncwarp();
     /* src/sdrtrk.c:40-43: correlator's II (cos sums) lands in trk.QQ, QQ (sin sums) in trk.II */
-    for (int i = 0; i < ntap; i++) {
-        st->QQ[i] = (double)(long long)sm->sumI[i] * SDRB200_CSCALE;
-        st->II[i] = (double)(long long)sm->sumQ[i] * SDRB200_CSCALE;
+    for (int i = lane; i < ntap; i += 32) {
+        st->QQ[i] = (double)(int)sm->sum[i] * SDRB200_CSCALE;
+        st->II[i] = (double)(int)sm->sum[SDRB200_MAXTAPS + i] * SDRB200_CSCALE;
     }
-    st->remcode = sm->remc;
-    st->remcarr = sm->remp;
-
-    /* sdrnavigation(), src/sdrnav.c:19-41 */
-    const int rate = ch->navrate;
-    const double cntth = 2000 / (ch->ctime * 1000);
-    st->biti = (int)(st->cnt % (uint64_t)rate);
-    st->ocodei = st->biti - st->synci - 1;
-    if (st->ocodei < 0) st->ocodei += rate;
-    if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
-    if (!st->flagsync && (double)st->cnt > cntth)
-        st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
-    if (st->flagsync) trk_checkbit(st->II[0], ch->loopms, st, rate);
-
+    __syncwarp();
+    if (lane == 0) {
+        st->oldremcode = st->remcode;
+        st->oldremcarr = st->remcarr;
+        st->remcode = sm->remc;
+        st->remcarr = sm->remp;
+        /* sdrnavigation(), src/sdrnav.c:19-41 */
+        const int rate = ch->navrate;
+        const double cntth = 2000 / (ch->ctime * 1000);
+        st->biti = (int)(st->cnt % (uint64_t)rate);
+        st->ocodei = st->biti - st->synci - 1;
+        if (st->ocodei < 0) st->ocodei += rate;
+        if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
+        if (!st->flagsync && (double)st->cnt > cntth)
+            st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
+        if (st->flagsync) trk_checkbit(st->II[0], ch->loopms, st, rate);
+    }
+    __syncwarp();
     /* cumsumcorr(), src/sdrtrk.c:64-76 (overlay polarity is +1 for L1CA/SBAS/G1) */
-    for (int i = 0; i < ntap; i++) {
+    for (int i = lane; i < ntap; i += 32) {
         st->oldsumI[i] += st->oldI[i]; st->oldsumQ[i] += st->oldQ[i];
         st->sumI[i] += st->II[i];      st->sumQ[i] += st->QQ[i];
     }
+    __syncwarp();
     /* src/sdrmain.c:271-280 */
-    st->flagloopfilter = 0;
-    if (!st->flagsync) {
-        trk_pll(st, &ch->prm1, ch->ctime, ch->acqfreq);
-        trk_dll(st, &ch->prm1, ch->ctime, ch);
-        st->flagloopfilter = 1;
-    } else if (st->swloop) {
-        trk_pll(st, &ch->prm2, (double)ch->loopms / 1000, ch->acqfreq);
-        trk_dll(st, &ch->prm2, (double)ch->loopms / 1000, ch);
-        st->flagloopfilter = 2;
-    }
+    const int mode = !st->flagsync ? 1 : (st->swloop ? 2 : 0);
+    if (mode == 1) trk_loops_warp(st, &ch->prm1, ch->ctime, ch, lane);
+    else if (mode == 2) trk_loops_warp(st, &ch->prm2, (double)ch->loopms / 1000, ch, lane);
+    __syncwarp();
     if (rec) {
-        rec->cnt = st->cnt; rec->buffloc = st->buffloc; rec->currnsamp = st->currnsamp;
-        rec->flagsync = st->flagsync; rec->flagloopfilter = st->flagloopfilter;
-        rec->swsync = st->swsync; rec->swloop = st->swloop; rec->synci = st->synci;
-        rec->biti = st->biti; rec->bit = st->bit;
-        for (int i = 0; i < ntap; i++) { rec->II[i] = st->II[i]; rec->QQ[i] = st->QQ[i]; }
-        rec->sumI0 = st->sumI[0]; rec->sumQ0 = st->sumQ[0];
-        rec->codefreq = st->codefreq; rec->codeErr = st->codeErr; rec->codeNco = st->codeNco;
-        rec->carrfreq = st->carrfreq; rec->carrErr = st->carrErr; rec->carrNco = st->carrNco;
-        rec->freqErr = st->freqErr; rec->remcode = st->remcode; rec->remcarr = st->remcarr;
+        for (int i = lane; i < ntap; i += 32) { rec->II[i] = st->II[i]; rec->QQ[i] = st->QQ[i]; }
+        if (lane == 0) {
+            rec->cnt = st->cnt; rec->buffloc = st->buffloc; rec->currnsamp = st->currnsamp;
+            rec->flagsync = st->flagsync; rec->flagloopfilter = mode;
+            rec->swsync = st->swsync; rec->swloop = st->swloop; rec->synci = st->synci;
+            rec->biti = st->biti; rec->bit = st->bit;
+            rec->sumI0 = st->sumI[0]; rec->sumQ0 = st->sumQ[0];
+            rec->codefreq = st->codefreq; rec->codeErr = st->codeErr; rec->codeNco = st->codeNco;
+            rec->carrfreq = st->carrfreq; rec->carrErr = st->carrErr; rec->carrNco = st->carrNco;
+            rec->freqErr = st->freqErr; rec->remcode = st->remcode; rec->remcarr = st->remcarr;
+        }
     }
+    __syncwarp();
     /* clearcumsumcorr(), src/sdrtrk.c:77-86, src/sdrmain.c:310-312 */
-    if (st->flagloopfilter)
-        for (int i = 0; i < ntap; i++) { st->oldsumI[i] = 0; st->oldsumQ[i] = 0; st->sumI[i] = 0; st->sumQ[i] = 0; }
-    st->cnt++;
-    st->buffloc += (uint64_t)st->currnsamp;
+    if (mode)
+        for (int i = lane; i < ntap; i += 32) { st->oldsumI[i] = 0; st->oldsumQ[i] = 0; st->sumI[i] = 0; st->sumQ[i] = 0; }
+    if (lane == 0) {
+        st->flagloopfilter = mode;
+        st->cnt++;
+        st->buffloc += (uint64_t)st->currnsamp;
+    }
+    __syncwarp();
 }
 
 struct trk_run_smem_t {
@@ -326,16 +350,18 @@ struct trk_run_smem_t {
 };
 
 template <int DTYPE>
-__global__ void __launch_bounds__(1024, 1)
+__global__ void __launch_bounds__(TRK_THREADS, 1)
 k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ states,
-          const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods,
-          sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err)
+          const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods, int maxn, int qcap,
+          sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err,
+          long long *__restrict__ prof)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     trk_run_smem_t *sm = (trk_run_smem_t *)smem_raw;
-    int8_t *rc = (int8_t *)(smem_raw + sizeof(trk_run_smem_t));
+    const trk_work_t wk = trk_work_layout<DTYPE>((unsigned int *)(smem_raw + sizeof(trk_run_smem_t)), maxn, qcap);
     const trk_chan_dev_t *ch = &chans[blockIdx.x];
     trk_state_t *st = &sm->st;
+    const bool worker = threadIdx.x >= 64;
 
     /* load channel state and constants */
     {
@@ -344,40 +370,64 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += blockDim.x) dst[i] = src[i];
         for (int i = threadIdx.x; i < ch->clen; i += blockDim.x) sm->t.codetab[i] = ch->code[i];
         if (threadIdx.x < ch->corrn) sm->taps[threadIdx.x] = ch->corrp[threadIdx.x];
-        if (threadIdx.x == 0) sm->t.err = 0;
+        trk_init_smem(&sm->t);
     }
     __syncthreads();
     const int ns = ch->corrn;
     const int smax = sm->taps[ns - 1];
     int done = 0;
+    /* optional phase profile (cycles, CTA 0, thread 0): go, tables, convert, mix, taps, epilogue */
+    long long pt[6] = {0, 0, 0, 0, 0, 0}, t0 = 0;
+    const bool prof_on = prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+#define TRK_PT(i) do { if (prof_on) { const long long t1 = trk_clock(); pt[i] += t1 - t0; t0 = t1; } } while (0)
+    if (prof_on) t0 = trk_clock();
 
     for (int it = 0; it < nperiods; it++) {
-        if (threadIdx.x == 0) {
+        if (threadIdx.x == TRK_NCO_A) {
             /* sdrtracking(), src/sdrtrk.c:31-32 */
             st->currnsamp = nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
-            sm->go = (st->currnsamp > 0 && st->currnsamp <= ch->nsamp + ch->nsamp / 8 &&
+            sm->go = (st->currnsamp > 0 && st->currnsamp <= maxn &&
                       st->buffloc + (uint64_t)st->currnsamp <= avail) ? 1 : 0;
         }
         __syncthreads();
         if (!sm->go) break;
+        TRK_PT(0);
         const int n = st->currnsamp;
         /* correlator(..., carrfreq, oldremcarr(=remcarr), codefreq, oldremcode(=remcode), ...) */
-        trk_build_tables(&sm->t, DTYPE, ch->ti, n, st->carrfreq, st->remcarr, st->codefreq, st->remcode,
-                         smax, ch->clen);
+        long long w0 = 0;
+        if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
+        trk_build_tables(&sm->t, ch->ti, n, st->carrfreq, st->remcarr, st->codefreq, st->remcode, smax, ch->clen);
+        if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[8] += trk_clock() - w0;
         __syncthreads();
-        trk_fill_replica(&sm->t, rc, n, smax);
+        TRK_PT(1);
+        trk_convert_tables(&sm->t);
         __syncthreads();
+        TRK_PT(2);
         const int8_t *data = ifbuf + (size_t)(st->buffloc % capacity) * DTYPE;
-        trk_accumulate<DTYPE>(&sm->t, rc, data, n, sm->taps, ns, smax);
-        if (threadIdx.x == 0) trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr);
+        if (worker) {
+            trk_mix_prefix<DTYPE>(&sm->t, data, n, wk);
+        } else {
+            if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
+            trk_carrier_rem(&sm->t);
+            if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[9] += trk_clock() - w0;
+        }
+        __syncthreads();
+        TRK_PT(3);
+        if (worker) trk_tap_sums<DTYPE>(&sm->t, wk, data, n, sm->taps, ns, smax);
+        __syncthreads();
+        TRK_PT(4);
+        if ((threadIdx.x >> 5) == (TRK_NCO_A >> 5))
+            trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31);
         __syncthreads();
         if (recs) {
             const uint32_t *src = (const uint32_t *)&sm->rec;
             uint32_t *dst = (uint32_t *)&recs[(size_t)blockIdx.x * nperiods + it];
             for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) dst[i] = src[i];
         }
+        TRK_PT(5);
         done++;
     }
+    if (prof_on) { for (int i = 0; i < 6; i++) prof[i] = pt[i]; prof[6] = done; }
     __syncthreads();
     {
         uint32_t *dst = (uint32_t *)&states[blockIdx.x];
@@ -389,12 +439,13 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
 
 /* ------------------------------------------------------------- host side */
 struct sdrb200_trk {
-    int nch, dtype, maxn, smax;
+    int nch, dtype, maxn, smax, maxtap, qcap;
     cudaStream_t st;
     trk_chan_dev_t *h_chan, *d_chan;
     trk_state_t *h_state0, *d_state;
     sdrb200_trk_rec_t *d_rec; size_t rec_cap;       /* records */
     int *d_nrec, *d_err;
+    long long *d_prof;               /* phase profile of CTA 0 (NULL: off) */
     int last_nperiods, last_with_rec;
 };
 
@@ -435,10 +486,16 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
         memcpy(d->corrp, c->corrp, sizeof(d->corrp));
         d->prm1 = c->prm1; d->prm2 = c->prm2;
         memcpy(d->code, c->code, c->clen);
-        int maxn = c->nsamp + c->nsamp / 8 + 16;
+        int maxn = c->nsamp + c->nsamp / 64 + 16;
+        if (1 + 2 * c->corrn > e->maxtap) e->maxtap = 1 + 2 * c->corrn;
         if (maxn > e->maxn) e->maxn = maxn;
         if (c->corrp[c->corrn - 1] > e->smax) e->smax = c->corrp[c->corrn - 1];
         trk_init_state(d, &e->h_state0[i]);
+        if (c->crate / c->f_sf > 0.5) {
+            sdrb200_set_error("trk_create: channel %d has fewer than two samples per chip", i);
+            free(e->h_chan); free(e->h_state0); free(e); return SDRB200_EINVAL;
+        }
+        { int q = trk_qcap(maxn, c->corrp[c->corrn - 1], 1.001 * c->crate / c->f_sf); if (q > e->qcap) e->qcap = q; }
     }
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMalloc((void **)&e->d_chan, sizeof(trk_chan_dev_t) * nch) != cudaSuccess ||
@@ -459,9 +516,27 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
 extern "C" void sdrb200_trk_destroy(sdrb200_trk_t *e)
 {
     if (!e) return;
-    cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_rec); cudaFree(e->d_nrec);
+    cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_rec); cudaFree(e->d_nrec); cudaFree(e->d_prof);
     if (e->st) cudaStreamDestroy(e->st);
     free(e->h_chan); free(e->h_state0); free(e);
+}
+
+/* phase profile of channel 0 over the last run (cycles): go, tables, convert,
+ * mix+prefix, tap sums, epilogue, periods; on=1 enables, then read after sync */
+extern "C" int sdrb200_trk_profile(sdrb200_trk_t *e, int on, long long *out7)
+{
+    if (!e) return SDRB200_EINVAL;
+    if (on && !e->d_prof) {
+        SDRB200_CUDA_TRY(cudaMalloc((void **)&e->d_prof, 16 * sizeof(long long)));
+        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
+    }
+    if (out7 && e->d_prof) {
+        SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 10 * sizeof(long long), cudaMemcpyDeviceToHost));
+        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
+    }
+    if (!on && e->d_prof) { cudaFree(e->d_prof); e->d_prof = NULL; }
+    return SDRB200_OK;
 }
 
 extern "C" int sdrb200_trk_reset(sdrb200_trk_t *e)
@@ -489,18 +564,17 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
             e->rec_cap = need;
         }
     }
-    size_t smem = sizeof(trk_run_smem_t) + (size_t)(e->maxn + 2 * e->smax + 64);
-    if (smem > 220 * 1024) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
+    size_t smem = sizeof(trk_run_smem_t) + sizeof(unsigned int) * TRK_WORK_WORDS(e->maxn, e->dtype, e->qcap);
+    if (smem > TRK_SMEM_LIMIT) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
     sdrb200_trk_rec_t *recs = with_rec ? e->d_rec : NULL;
-    if (e->dtype == 1) {
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_trk_run<1><<<e->nch, 1024, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count,
-                                                    nperiods, recs, e->d_nrec, e->d_err);
-    } else {
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_trk_run<2><<<e->nch, 1024, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count,
-                                                    nperiods, recs, e->d_nrec, e->d_err);
-    }
+#define TRK_LAUNCH(DT)                                                                                    \
+    do {                                                                                                  \
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        k_trk_run<DT><<<e->nch, TRK_THREADS, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count, \
+                                                            nperiods, e->maxn, e->qcap, recs, e->d_nrec, e->d_err, e->d_prof); \
+    } while (0)
+    if (e->dtype == 1) TRK_LAUNCH(1); else TRK_LAUNCH(2);
+#undef TRK_LAUNCH
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     e->last_nperiods = nperiods; e->last_with_rec = with_rec;

@@ -1,11 +1,28 @@
-/* trk_device.cuh - one code period of the tracking correlator, executed by a
- * whole CTA.  Device-side counterpart of correlator() (src/sdrcmn.c:687-722):
+/* trk_device.cuh - one code period of the tracking correlator, executed by one
+ * CTA.  Device-side counterpart of correlator() (src/sdrcmn.c:687-722):
  *   mixcarr  (src/sdrcmn.c:633-669)  carrier wipe-off with the 32-entry table
  *   rescode  (src/sdrcmn.c:608-621)  nearest-chip replica, n + 2*smax samples
  *   dot_23 / dot_22 (src/sdrcmn.c:310-354)  1+2*ns tap sums
- * All sums are exact integers (the reference accumulates the same integers in
- * double), the NCO index sequences are reproduced exactly via nco_exact.h, so
- * II/QQ are bit-identical to the reference and remc/remp are identical doubles.
+ *
+ * Formulation (all integer, exact):
+ *   m[k]   = carrier-mixed sample k (I and Q), P[k] = sum_{i<k} m[i]  (prefix sums)
+ *   r[p]   = replica value at window position p, piecewise constant (one run per
+ *            chip, ~16 samples at 16.368 MS/s); B_q = first position of run q
+ *   tap(off) = sum_k m[k] r[k+off]
+ *            = r_last * P[n] + sum_q (r_{q-1} - r_q) * P[clip(B_q - off, 0, n)]
+ * so a tap costs one prefix lookup per chip SIGN CHANGE (~512 per period)
+ * instead of one multiply-add per sample (16368), and all 1+2*ns taps share the
+ * prefix arrays.  Sums are kept modulo 2^32; the true values (|sum| < 2^31) are
+ * recovered exactly.  The reference accumulates the same integers in doubles,
+ * so II/QQ are bit-identical; the NCO index sequences come from nco_exact.h in
+ * integer form (nco_iseg_t), so no FP64 arithmetic is done per sample.
+ *
+ * CTA layout: 1024 threads = two NCO warps (0: carrier NCO lane + epilogue,
+ * 1: code NCO lane) + 960 workers.  Worker u owns TRK_SPAN = 20 bytes
+ * [20u, 20u+20) of the 4-byte-aligned span that covers the window (five
+ * coalesced 32-bit loads).  Workers take a branch-free path when their span lies
+ * inside one NCO segment (almost always), so the per-sample work is independent
+ * integer arithmetic with full instruction-level parallelism.
  */
 #ifndef SDRB200_TRK_DEVICE_CUH
 #define SDRB200_TRK_DEVICE_CUH
@@ -15,160 +32,327 @@
 #include "nco_exact.h"
 #include "sdrb200_internal.h"
 
+#define TRK_WORKERS   960                    /* warps 2..31                        */
+#define TRK_THREADS   1024
+#define TRK_NCO_A     0                      /* carrier NCO lane; warp 0 = epilogue warp */
+#define TRK_NCO_B     32                     /* code NCO lane (warp 1)             */
+#define TRK_SPAN      20                     /* bytes of IF owned by one worker per round */
+#define TRK_ROUND_BYTES (TRK_WORKERS * TRK_SPAN)
+#define TRK_MAXSEG    96                     /* NCO segments held on the device    */
+/* rows of the prefix store: one per 20-byte span of the (4-byte aligned) window */
+#define TRK_ROWS(nbytes) (((nbytes) + 3 + TRK_SPAN - 1) / TRK_SPAN + 1)
+/* dynamic shared memory of one channel, in 32-bit words: prefix rows
+ * (S+1 pairs each), row bases (pairs), run-boundary queue                       */
+#define TRK_WORK_WORDS(n, dtype, qcap) \
+    ((size_t)TRK_ROWS((n) * (dtype)) * ((TRK_SPAN / (dtype)) + 2) * 2 + (size_t)(qcap))
+
 /* carrier table: cost[i]=floor(cos(2*pi*i/32)*32+0.5), sint likewise
  * (src/sdrcmn.c:641-646); trk.cu re-derives the table with libm at start-up
  * and refuses to run if it differs                 */
-static __constant__ int8_t c_cost[32] = {32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6,0,6,12,18,23,27,30,31};
-static __constant__ int8_t c_sint[32] = {0,6,12,18,23,27,30,31,32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6};
-/* the same values for the host-side self check in trk.cu */
 #define SDRB200_COST_INIT {32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6,0,6,12,18,23,27,30,31}
 #define SDRB200_SINT_INIT {0,6,12,18,23,27,30,31,32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6}
+static __constant__ int8_t c_cost[32] = SDRB200_COST_INIT;
+static __constant__ int8_t c_sint[32] = SDRB200_SINT_INIT;
 
 struct trk_smem_t {
-    nco_table_t carr;                       /* carrier NCO segments             */
-    nco_table_t code;                       /* code NCO segments                */
-    unsigned long long sumI[SDRB200_MAXTAPS];
-    unsigned long long sumQ[SDRB200_MAXTAPS];
+    nco_table_t carr;                       /* carrier NCO segments (double form)  */
+    nco_table_t code;                       /* code NCO segments                   */
+    nco_iseg_t  icarr[TRK_MAXSEG];          /* the same, integer form              */
+    nco_iseg_t  icode[TRK_MAXSEG];
+    unsigned int sum[2 * SDRB200_MAXTAPS];  /* tap sums mod 2^32: I[0..], Q[MAXTAPS..] */
+    unsigned int wtot[2][32];               /* per-warp totals of the block scan   */
+    unsigned int carry[2];                  /* prefix carried between rounds       */
+    int          lut[32];                   /* cos | sin << 16                     */
+    int          qcount;                    /* run boundaries queued this period   */
+    int          vlast;                     /* replica value at the last position  */
     double   remc, remp;
     int32_t  err;
-    int8_t   codetab[1024];                 /* +-1 chips                        */
+    int32_t  pad;
+    int8_t   codetab[1024];                 /* +-1 chips                           */
 };
 
-/* binary search: last segment with k0 <= k */
-__device__ __forceinline__ int trk_seg_find(const nco_table_t *t, int k)
+/* the dynamic work area of one channel */
+struct trk_work_t {
+    uint2        *P2;                       /* [rows][S+1] running (I,Q) sums inside a row */
+    uint2        *base;                     /* [rows] sums of all earlier rows             */
+    unsigned int *queue;                    /* [qcap] p | sign<<31 of every replica sign change */
+    int           qcap;
+};
+template <int DTYPE>
+__device__ __forceinline__ trk_work_t trk_work_layout(unsigned int *w, int maxn, int qcap)
 {
-    int lo = 0, hi = t->nseg - 1;
+    trk_work_t k;
+    const int rows = TRK_ROWS(maxn * DTYPE);
+    k.P2 = (uint2 *)w;
+    k.base = k.P2 + (size_t)rows * (TRK_SPAN / DTYPE + 1);
+    k.queue = (unsigned int *)(k.base + rows);
+    k.qcap = qcap;
+    return k;
+}
+
+__device__ __forceinline__ void trk_bar_workers()
+{
+    asm volatile("bar.sync 1, %0;" ::"n"(TRK_WORKERS) : "memory");
+}
+
+/* last segment with k0 <= k */
+__device__ __forceinline__ int trk_iseg_find(const nco_iseg_t *seg, int nseg, int k)
+{
+    int lo = 0, hi = nseg - 1;
     while (lo < hi) {
         int mid = (lo + hi + 1) >> 1;
-        if (t->seg[mid].k0 <= k) lo = mid; else hi = mid - 1;
+        if (seg[mid].k0 <= k) lo = mid; else hi = mid - 1;
     }
     return lo;
 }
 
-/* value at index k given a segment cursor that is advanced monotonically */
-__device__ __forceinline__ double trk_seg_value(const nco_table_t *t, int k, int &s)
+/* cursor over the (int) values of an NCO at consecutive indices */
+struct trk_cursor_t {
+    const nco_iseg_t *seg;
+    int nseg, s, next_k0, shift, negm;
+    unsigned long long m;
+    long long D;
+    __device__ __forceinline__ void load(int k)
+    {
+        const nco_iseg_t *p = &seg[s];
+        shift = p->shift; negm = -p->neg; D = p->D;
+        m = p->X0 + (unsigned long long)((long long)(k - p->k0) * p->D);
+        if (shift >= 64) { shift = 0; m = 0ull; D = 0; }       /* |value| < 1: (int) gives 0 */
+        next_k0 = (s + 1 < nseg) ? seg[s + 1].k0 : 0x7fffffff;
+    }
+    __device__ __forceinline__ void start(const nco_iseg_t *sg, int n, int k)
+    {
+        seg = sg; nseg = n; s = trk_iseg_find(sg, n, k); load(k);
+    }
+    /* low 32 bits of (int) value at the current index k, then step to index k+1 */
+    __device__ __forceinline__ int value_and_advance(int k)
+    {
+        const int t = (int)(unsigned int)(m >> shift);
+        const int v = (t ^ negm) - negm;
+        if (k + 1 >= next_k0) { s++; load(k + 1); } else m += (unsigned long long)D;
+        return v;
+    }
+};
+
+/* ---- phase 0: constants of the CTA (once per launch) ------------------------ */
+__device__ __forceinline__ void trk_init_smem(trk_smem_t *sm)
 {
-    while (s + 1 < t->nseg && t->seg[s + 1].k0 <= k) s++;
-    return __dadd_rn(t->seg[s].x0, __dmul_rn((double)(k - t->seg[s].k0), t->seg[s].d));
+    if (threadIdx.x < 32) sm->lut[threadIdx.x] = ((int)c_cost[threadIdx.x] & 0xffff) | ((int)c_sint[threadIdx.x] << 16);
+    if (threadIdx.x == 0) sm->err = 0;
 }
 
-/* Phase 1 (two threads): build both NCO tables and the remainders.
- * Must be followed by __syncthreads().                                         */
-__device__ __forceinline__ void trk_build_tables(trk_smem_t *sm, int dtype, double ti, int n,
-                                                 double freq, double phi0, double crate,
-                                                 double coff, int smax, int coden)
+/* ---- phase 1: NCO segment tables (two lanes) -------------------------------- *
+ * Must be followed by __syncthreads(); then trk_convert_tables + __syncthreads. *
+ * The carrier remainder (mixcarr's subtract loop, src/sdrcmn.c:665-668) is NOT  *
+ * computed here: trk_carrier_rem() does it on the NCO lane while the workers    *
+ * are busy.                                                                     */
+__device__ __forceinline__ void trk_build_tables(trk_smem_t *sm, double ti, int n, double freq, double phi0,
+                                                 double crate, double coff, int smax, int coden)
 {
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == TRK_NCO_A) {
         double phi, ps;
         nco_carrier_init(freq, phi0, ti, &phi, &ps);
         if (nco_walk(phi, ps, n, 0.0, &sm->carr)) sm->err = 1;
-        sm->remp = nco_carrier_rem(sm->carr.x_end);
     }
-    if (threadIdx.x == 32) {
+    if (threadIdx.x == TRK_NCO_B) {
         double ci = __dmul_rn(ti, crate);                   /* ti*crate, sdrcmn.c:709 */
         double c0 = nco_code_init(coff, smax, ci, coden);
         if (nco_walk(c0, ci, n + 2 * smax, (double)coden, &sm->code)) sm->err = 1;
         sm->remc = nco_code_rem(sm->code.x_end, smax, ci);
     }
-    if (threadIdx.x >= 64 && threadIdx.x < 64 + SDRB200_MAXTAPS) {
-        sm->sumI[threadIdx.x - 64] = 0ULL;
-        sm->sumQ[threadIdx.x - 64] = 0ULL;
-    }
-    (void)dtype;
+    __syncwarp();                       /* the NCO warps reach the CTA barrier converged */
+    if (threadIdx.x < 2 * SDRB200_MAXTAPS) sm->sum[threadIdx.x] = 0u;
+    if (threadIdx.x < 2) sm->carry[threadIdx.x] = 0u;
+    if (threadIdx.x == 2) sm->qcount = 0;
 }
-
-/* Phase 2: resampled replica rc[p], p in [0, n+2*smax) as +-1 bytes.
- * Must be followed by __syncthreads().                                         */
-__device__ __forceinline__ void trk_fill_replica(const trk_smem_t *sm, int8_t *rc, int n, int smax)
+__device__ __forceinline__ void trk_convert_tables(trk_smem_t *sm)
 {
-    const int N = n + 2 * smax;
-    for (int base = threadIdx.x * 16; base < N; base += blockDim.x * 16) {
-        int s = trk_seg_find(&sm->code, base);
-        int end = min(base + 16, N);
-        for (int p = base; p < end; p++) {
-            double v = trk_seg_value(&sm->code, p, s);
-            rc[p] = sm->codetab[__double2int_rz(v)];
-        }
+    const int t = threadIdx.x;
+    if (sm->carr.nseg > TRK_MAXSEG || sm->code.nseg > TRK_MAXSEG) { if (t == 0) sm->err = 1; return; }
+    if (t < sm->carr.nseg) {
+        nco_iseg_make(&sm->carr.seg[t], &sm->icarr[t]);
+        if (sm->icarr[t].shift < 0) sm->err = 1;
+    }
+    const int u = t - 256;
+    if (u >= 0 && u < sm->code.nseg) {
+        nco_iseg_make(&sm->code.seg[u], &sm->icode[u]);
+        if (sm->icode[u].shift < 0) sm->err = 1;
     }
 }
+__device__ __forceinline__ void trk_carrier_rem(trk_smem_t *sm)
+{
+    if (threadIdx.x == TRK_NCO_A) sm->remp = nco_carrier_rem(sm->carr.x_end);
+    __syncwarp();
+}
 
-/* Phase 3: wipe-off + tap sums.  data points at sample 0 of the window in
- * global memory (any alignment; the 16 bytes before and after the window must
- * be readable, which the IF stream's layout guarantees).
- * taps[i] (i < ns) are the correlator offsets in samples (trk.corrp).
- * Output order as the reference: {P, E1, L1, E2, L2, ...} (sdrcmn.c:682-683),
- * E_i uses rc shifted by -taps[i], L_i by +taps[i] (sdrcmn.c:712-715).
- * Ends with the block-level sums complete in sm->sumI/Q after a __syncthreads().*/
+
+/* byte b of w, sign-extended: one PRMT with sign replication */
+__device__ __forceinline__ int trk_sbyte(unsigned int w, int b)
+{
+    const unsigned int n8 = 8u | (unsigned int)b;
+    int d;                                  /* prmt: selector bit 3 = replicate the sign of the byte */
+    asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(w), "r"(0u), "r"((n8 << 12) | (n8 << 8) | (n8 << 4) | (unsigned int)b));
+    return d;
+}
+
+/* ---- phase 2 (workers): wipe-off + prefix sums ------------------------------- *
+ * data: sample 0 of the window in global memory (any alignment; the aligned     *
+ * words touching the window must be readable - the IF stream's guard and the    *
+ * primitive's arena guarantee it).  Row u of wk.P2 receives the running (I,Q)   *
+ * sums of worker u's samples, wk.base[u] the sums of all earlier rows.           */
 template <int DTYPE>
-__device__ __forceinline__ void trk_accumulate(trk_smem_t *sm, const int8_t *rc,
-                                               const int8_t *__restrict__ data, int n,
-                                               const int *taps, int ns, int smax)
+__device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__restrict__ data, int n,
+                                               const trk_work_t &wk)
 {
-    constexpr int SPV = 16 / DTYPE;                     /* samples per 16-byte vector */
+    constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;     /* samples per row, row stride (pairs) */
+    const int u = threadIdx.x - 64, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uintptr_t addr = (uintptr_t)data;
-    const int a = (int)(addr & 15);                     /* bytes of misalignment      */
-    const int4 *vbase = (const int4 *)(addr - a);
-    const int nvec = (n * DTYPE + a + 15) >> 4;
-    const int ntap = 1 + 2 * ns;
-    const int lane = threadIdx.x & 31;
-
-    for (int v0 = 0; v0 < nvec; v0 += blockDim.x) {     /* uniform trip count         */
-        const int v = v0 + threadIdx.x;
-        int I[SPV], Q[SPV];
-        int kfirst = 0;
-        bool active = v < nvec;
-        if (active) {
-            int4 w = __ldg(vbase + v);
-            const int8_t *b = (const int8_t *)&w;
-            /* first sample index covered by this vector (may be < 0 or >= n) */
-            kfirst = (v * 16 - a) / DTYPE;              /* a is even for IQ streams   */
-            if (v * 16 - a < 0) kfirst = -((a - v * 16) / DTYPE);
-            int s = trk_seg_find(&sm->carr, max(kfirst, 0));
+    const int a = (int)(addr & 3);
+    const unsigned int *wbase = (const unsigned int *)(addr - a);
+    const int nbytes = n * DTYPE + a;
+    const int rounds = (nbytes + TRK_ROUND_BYTES - 1) / TRK_ROUND_BYTES;
+    for (int r = 0; r < rounds; r++) {
+        const int row = r * TRK_WORKERS + u;
+        const int byte0 = row * TRK_SPAN;
+        const int kfirst = (byte0 - a) / DTYPE;          /* exact: a is even for I/Q streams */
+        unsigned int runI = 0u, runQ = 0u;
+        if (byte0 < nbytes) {
+            unsigned int w[TRK_SPAN / 4];
 #pragma unroll
-            for (int j = 0; j < SPV; j++) {
-                int k = kfirst + j;
-                I[j] = 0; Q[j] = 0;
-                if (k >= 0 && k < n) {
-                    double phi = trk_seg_value(&sm->carr, k, s);
-                    int idx = __double2int_rz(phi) & SDRB200_CMASK;
-                    int c = c_cost[idx], sn = c_sint[idx];
+            for (int i = 0; i < TRK_SPAN / 4; i++) w[i] = (byte0 + 4 * i < nbytes) ? __ldg(wbase + (byte0 >> 2) + i) : 0u;
+#define TRK_BYTE(j) trk_sbyte(w[(j) >> 2], (j) & 3)
+            trk_cursor_t cur;
+            cur.start(sm->icarr, sm->carr.nseg, max(kfirst, 0));
+            uint2 *rowp = wk.P2 + (size_t)row * RS;
+#pragma unroll
+            for (int j = 0; j < S; j++) {
+                const int kk = kfirst + j;
+                if ((unsigned int)kk < (unsigned int)n) {
+                    const int idx = cur.value_and_advance(kk) & SDRB200_CMASK;
+                    const int cs = sm->lut[idx];
+                    const int c = (int)(short)cs, sn = cs >> 16;
                     if (DTYPE == 1) {
-                        int x = b[j];
-                        I[j] = c * x; Q[j] = sn * x;                   /* sdrcmn.c:660-661 */
+                        const int x = TRK_BYTE(j);
+                        runI += (unsigned int)(c * x); runQ += (unsigned int)(sn * x);      /* sdrcmn.c:660-661 */
                     } else {
-                        int x0 = b[2 * j], x1 = b[2 * j + 1];
-                        I[j] = c * x0 - sn * x1;                       /* sdrcmn.c:654-655 */
-                        Q[j] = sn * x0 + c * x1;
+                        const int x0 = TRK_BYTE(2 * j), x1 = TRK_BYTE(2 * j + 1);
+                        runI += (unsigned int)(c * x0 - sn * x1);                           /* sdrcmn.c:654-655 */
+                        runQ += (unsigned int)(sn * x0 + c * x1);
                     }
                 }
+                rowp[j] = make_uint2(runI, runQ);
             }
+#undef TRK_BYTE
         }
-        for (int t = 0; t < ntap; t++) {
-            int off = 0;
-            if (t > 0) { int i = (t - 1) >> 1; off = ((t - 1) & 1) ? taps[i] : -taps[i]; }
-            int accI = 0, accQ = 0;
-            if (active) {
-                const int8_t *r = rc + smax + off + kfirst;
+        /* block-wide exclusive scan of the row totals over the worker warps 2..31 */
+        unsigned int incI = runI, incQ = runQ;
 #pragma unroll
-                for (int j = 0; j < SPV; j++) {
-                    int k = kfirst + j;
-                    int c = (k >= 0 && k < n) ? (int)r[j] : 0;
-                    accI += c * I[j];
-                    accQ += c * Q[j];
-                }
-            }
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int uI = __shfl_up_sync(0xffffffffu, incI, o), uQ = __shfl_up_sync(0xffffffffu, incQ, o);
+            if (lane >= o) { incI += uI; incQ += uQ; }
+        }
+        if (lane == 31) { sm->wtot[0][warp] = incI; sm->wtot[1][warp] = incQ; }
+        trk_bar_workers();
+        /* lane l holds the total of warp l (l >= 2); inclusive scan over lanes */
+        unsigned int wI = (lane >= 2) ? sm->wtot[0][lane] : 0u, wQ = (lane >= 2) ? sm->wtot[1][lane] : 0u;
 #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                accI += __shfl_xor_sync(0xffffffffu, accI, o);
-                accQ += __shfl_xor_sync(0xffffffffu, accQ, o);
-            }
-            if (lane == 0) {
-                atomicAdd(&sm->sumI[t], (unsigned long long)(long long)accI);
-                atomicAdd(&sm->sumQ[t], (unsigned long long)(long long)accQ);
-            }
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int uI = __shfl_up_sync(0xffffffffu, wI, o), uQ = __shfl_up_sync(0xffffffffu, wQ, o);
+            if (lane >= o) { wI += uI; wQ += uQ; }
+        }
+        const unsigned int allI = __shfl_sync(0xffffffffu, wI, 31), allQ = __shfl_sync(0xffffffffu, wQ, 31);
+        const unsigned int prevI = __shfl_sync(0xffffffffu, wI, warp - 1), prevQ = __shfl_sync(0xffffffffu, wQ, warp - 1);
+        if (byte0 < nbytes + TRK_SPAN)
+            wk.base[row] = make_uint2(sm->carry[0] + prevI + incI - runI, sm->carry[1] + prevQ + incQ - runQ);
+        if (rounds > 1) {
+            trk_bar_workers();                           /* everyone has read wtot / carry */
+            if (u == 0) { sm->carry[0] += allI; sm->carry[1] += allQ; }
+            trk_bar_workers();
         }
     }
-    __syncthreads();
+}
+
+/* sum_{i<k} m[i] for k in [0, n]: I (word 0) or Q (word 1) */
+template <int DTYPE>
+__device__ __forceinline__ unsigned int trk_prefix_at(const trk_work_t &wk, int a, int k, int isQ)
+{
+    constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;
+    if (k <= 0) return 0u;
+    const int byte = (k - 1) * DTYPE + a;
+    const int row = byte / TRK_SPAN;
+    const int j = (byte - row * TRK_SPAN) / DTYPE;
+    const unsigned int *b = (const unsigned int *)wk.base, *p = (const unsigned int *)wk.P2;
+    return b[row * 2 + isQ] + p[((size_t)row * RS + j) * 2 + isQ];
+}
+
+/* ---- phase 3 (workers): replica sign changes -> tap sums --------------------- *
+ * taps[i] (i < ns): correlator offsets in samples (trk.corrp).  Output order as  *
+ * the reference: {P, E1, L1, E2, L2, ...} (sdrcmn.c:682-683); E_i uses the       *
+ * replica shifted by -taps[i], L_i by +taps[i] (sdrcmn.c:712-715).               *
+ *  (a) every worker walks its share of the n + 2*smax replica positions with the *
+ *      integer code NCO and queues the positions where the chip VALUE changes;   *
+ *  (b) the queue is consumed with one LANE PER TAP SUM (I and Q of every tap):   *
+ *      a lane looks its prefix value up and accumulates privately, so there is   *
+ *      no cross-lane reduction and no divergence.                                *
+ * Preceded by a CTA barrier (prefix rows complete), followed by one before       *
+ * sm->sum is read.                                                               */
+template <int DTYPE>
+__device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &wk, const int8_t *data, int n,
+                                             const int *taps, int ns, int smax)
+{
+    const int t = threadIdx.x - 64, lane = threadIdx.x & 31, wwarp = (threadIdx.x >> 5) - 2;
+    const int a = (int)((uintptr_t)data & 3);
+    const int N = n + 2 * smax, ntap = 1 + 2 * ns;
+    const int PP = (N + TRK_WORKERS - 1) / TRK_WORKERS;
+    const int p0 = t * PP, p1 = min(p0 + PP, N);
+    const unsigned int lt = (1u << lane) - 1u;
+    /* (a) */
+    {
+        trk_cursor_t cur;
+        int prev = -1, vprev = 0;
+        if (p0 < N) {
+            if (p0 == 0) cur.start(sm->icode, sm->code.nseg, 0);
+            else { cur.start(sm->icode, sm->code.nseg, p0 - 1); prev = cur.value_and_advance(p0 - 1); vprev = (int)sm->codetab[prev]; }
+        }
+        for (int i = 0; i < PP; i++) {
+            const int p = p0 + i;
+            bool has = false;
+            unsigned int entry = 0u;
+            if (p < p1) {
+                const int chip = cur.value_and_advance(p);
+                if (chip != prev) {
+                    const int v = (int)sm->codetab[chip];
+                    if (v != vprev && p > 0) { has = true; entry = (unsigned int)p | (vprev < v ? 0x80000000u : 0u); }
+                    prev = chip; vprev = v;              /* p == 0: first run, prefix(0) = 0 */
+                }
+            }
+            const unsigned int mask = __ballot_sync(0xffffffffu, has);
+            if (mask) {
+                int slot = 0;
+                if (lane == 0) slot = atomicAdd(&sm->qcount, __popc(mask));
+                slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(mask & lt);
+                if (has) { if (slot < wk.qcap) wk.queue[slot] = entry; else sm->err = 2; }
+            }
+        }
+        if (p0 < N && p1 == N) sm->vlast = vprev;
+    }
+    trk_bar_workers();
+    /* (b) */
+    const int qn = min(sm->qcount, wk.qcap);
+    for (int task = lane; task < 2 * ntap; task += 32) {
+        const int isQ = task >= ntap, tap = isQ ? task - ntap : task;
+        int off = 0;
+        if (tap > 0) { const int s = taps[(tap - 1) >> 1]; off = ((tap - 1) & 1) ? s : -s; }
+        unsigned int acc = 0u;
+        for (int e = wwarp; e < qn; e += TRK_WORKERS / 32) {
+            const unsigned int entry = wk.queue[e];
+            const int B = (int)(entry & 0x7fffffffu) - smax;
+            const unsigned int delta = (entry >> 31) ? 0xfffffffeu : 2u;        /* r_{q-1} - r_q */
+            acc += delta * trk_prefix_at<DTYPE>(wk, a, min(max(B - off, 0), n), isQ);
+        }
+        if (wwarp == 0) acc += (unsigned int)sm->vlast * trk_prefix_at<DTYPE>(wk, a, n, isQ);   /* r_last * P[n] */
+        if (acc) atomicAdd(&sm->sum[isQ ? SDRB200_MAXTAPS + tap : tap], acc);
+    }
 }
 
 #endif

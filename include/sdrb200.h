@@ -198,6 +198,9 @@ int  sdrb200_trk_enqueue(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nper
 int  sdrb200_trk_sync(sdrb200_trk_t *eng);
 int  sdrb200_trk_reset(sdrb200_trk_t *eng);     /* back to the hand-over state   */
 void *sdrb200_trk_cuda_stream(sdrb200_trk_t *eng);
+/* phase profile of channel 0 (clock cycles summed over the last run): go, NCO
+ * tables, table conversion, wipe-off + prefix sums, tap sums, epilogue, periods */
+int  sdrb200_trk_profile(sdrb200_trk_t *eng, int on, long long *out7);
 
 /* ------------------------------------------- single-call primitives (host I/O)
  * Same argument meaning as the reference functions named; buffers are HOST

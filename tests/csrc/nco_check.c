@@ -22,7 +22,10 @@ int check_carrier(double freq, double phi0, double ti, int n)
     p = phi;
     for (k = 0; k < n; k++, p += ps) {
         double v = nco_value(&t, k, &hint);
+        nco_iseg_t is;
         if (v != p) bad++;
+        nco_iseg_make(&t.seg[hint], &is);                 /* integer form: same (int) cast */
+        if (is.shift < 0 || (int)nco_iseg_trunc(&is, k) != (int)p) bad++;
     }
     if (p != t.x_end) bad++;
     prem = p * NCO_TWO_PI / 32.0;
@@ -47,6 +50,11 @@ int check_code(double coff, int smax, double ci, int len, int n)
         if (c >= len) c -= len;
         v = nco_value(&t, k, &hint);
         if (v != c) bad++;
+        {
+            nco_iseg_t is;
+            nco_iseg_make(&t.seg[hint], &is);
+            if (is.shift < 0 || (int)nco_iseg_trunc(&is, k) != (int)c) bad++;
+        }
     }
     if (c != t.x_end) bad++;
     if (c - smax * ci != nco_code_rem(t.x_end, smax, ci)) bad++;
