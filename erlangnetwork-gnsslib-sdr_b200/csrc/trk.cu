@@ -383,6 +383,11 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
     if (prof_on) t0 = trk_clock();
 
     for (int it = 0; it < nperiods; it++) {
+#ifdef TRK_DEBUG
+        if (threadIdx.x == 0) g_dbg_on = (it == 50);
+        __syncthreads();
+#endif
+        DBG(0);
         if (threadIdx.x == TRK_NCO_A) {
             /* sdrtracking(), src/sdrtrk.c:31-32 */
             st->currnsamp = nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
@@ -392,6 +397,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         __syncthreads();
         if (!sm->go) break;
         TRK_PT(0);
+        DBG(1);
         const int n = st->currnsamp;
         /* correlator(..., carrfreq, oldremcarr(=remcarr), codefreq, oldremcode(=remcode), ...) */
         long long w0 = 0;
@@ -403,6 +409,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         trk_convert_tables(&sm->t);
         __syncthreads();
         TRK_PT(2);
+        /* convert done */
         const int8_t *data = ifbuf + (size_t)(st->buffloc % capacity) * DTYPE;
         if (worker) {
             trk_mix_prefix<DTYPE>(&sm->t, data, n, wk);
@@ -411,11 +418,13 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             trk_carrier_rem(&sm->t);
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[9] += trk_clock() - w0;
         }
+        DBG(4);
         __syncthreads();
         TRK_PT(3);
         if (worker) trk_tap_sums<DTYPE>(&sm->t, wk, data, n, sm->taps, ns, smax);
         __syncthreads();
         TRK_PT(4);
+        DBG(9);
         if ((threadIdx.x >> 5) == (TRK_NCO_A >> 5))
             trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31);
         __syncthreads();
@@ -425,6 +434,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) dst[i] = src[i];
         }
         TRK_PT(5);
+        DBG(10);
         done++;
     }
     if (prof_on) { for (int i = 0; i < 6; i++) prof[i] = pt[i]; prof[6] = done; }
@@ -538,6 +548,10 @@ extern "C" int sdrb200_trk_profile(sdrb200_trk_t *e, int on, long long *out7)
     if (!on && e->d_prof) { cudaFree(e->d_prof); e->d_prof = NULL; }
     return SDRB200_OK;
 }
+
+#ifdef TRK_DEBUG
+extern "C" int sdrb200_trk_dbg(long long *out) { return cudaMemcpyFromSymbol(out, g_dbg, sizeof(long long) * 4096) == cudaSuccess ? 0 : -4; }
+#endif
 
 extern "C" int sdrb200_trk_reset(sdrb200_trk_t *e)
 {

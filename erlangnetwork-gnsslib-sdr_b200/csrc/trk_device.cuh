@@ -64,6 +64,8 @@ struct trk_smem_t {
     unsigned int carry[2];                  /* prefix carried between rounds       */
     int          lut[32];                   /* cos | sin << 16                     */
     int          qcount;                    /* run boundaries queued this period   */
+    int          nslow[2];                  /* rows / spans left to the cooperative path */
+    int          slow[2][128];
     int          vlast;                     /* replica value at the last position  */
     double   remc, remp;
     int32_t  err;
@@ -134,6 +136,17 @@ struct trk_cursor_t {
     }
 };
 
+/* (int) value of an NCO at an arbitrary index k (own segment search) */
+__device__ __forceinline__ int trk_value_at(const nco_iseg_t *seg, int nseg, int k)
+{
+    const nco_iseg_t *p = &seg[trk_iseg_find(seg, nseg, k)];
+    const int sh = p->shift;
+    if (sh >= 64) return 0;
+    const unsigned long long m = p->X0 + (unsigned long long)((long long)(k - p->k0) * p->D);
+    const int t = (int)(unsigned int)(m >> sh);
+    return p->neg ? -t : t;
+}
+
 /* ---- phase 0: constants of the CTA (once per launch) ------------------------ */
 __device__ __forceinline__ void trk_init_smem(trk_smem_t *sm)
 {
@@ -163,7 +176,7 @@ __device__ __forceinline__ void trk_build_tables(trk_smem_t *sm, double ti, int 
     __syncwarp();                       /* the NCO warps reach the CTA barrier converged */
     if (threadIdx.x < 2 * SDRB200_MAXTAPS) sm->sum[threadIdx.x] = 0u;
     if (threadIdx.x < 2) sm->carry[threadIdx.x] = 0u;
-    if (threadIdx.x == 2) sm->qcount = 0;
+    if (threadIdx.x == 2) { sm->qcount = 0; sm->nslow[0] = 0; sm->nslow[1] = 0; }
 }
 __device__ __forceinline__ void trk_convert_tables(trk_smem_t *sm)
 {
@@ -185,6 +198,16 @@ __device__ __forceinline__ void trk_carrier_rem(trk_smem_t *sm)
     __syncwarp();
 }
 
+
+/* optional per-warp time stamps (build with -DTRK_DEBUG): slot s, warp w -> g_dbg[s*32+w] */
+#ifdef TRK_DEBUG
+__device__ long long g_dbg[4096];
+__device__ int g_dbg_on;
+__device__ __forceinline__ long long dbg_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t)::"memory"); return t; }
+#define DBG(slot) do { if (g_dbg_on && blockIdx.x == 0 && (threadIdx.x & 31) == 0) g_dbg[(slot) * 32 + (threadIdx.x >> 5)] = dbg_clock(); } while (0)
+#else
+#define DBG(slot)
+#endif
 
 /* byte b of w, sign-extended: one PRMT with sign replication */
 __device__ __forceinline__ int trk_sbyte(unsigned int w, int b)
@@ -211,11 +234,13 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
     const unsigned int *wbase = (const unsigned int *)(addr - a);
     const int nbytes = n * DTYPE + a;
     const int rounds = (nbytes + TRK_ROUND_BYTES - 1) / TRK_ROUND_BYTES;
+    DBG(2);
     for (int r = 0; r < rounds; r++) {
         const int row = r * TRK_WORKERS + u;
         const int byte0 = row * TRK_SPAN;
         const int kfirst = (byte0 - a) / DTYPE;          /* exact: a is even for I/Q streams */
         unsigned int runI = 0u, runQ = 0u;
+        bool slow = false;
         if (byte0 < nbytes) {
             unsigned int w[TRK_SPAN / 4];
 #pragma unroll
@@ -224,26 +249,75 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
             trk_cursor_t cur;
             cur.start(sm->icarr, sm->carr.nseg, max(kfirst, 0));
             uint2 *rowp = wk.P2 + (size_t)row * RS;
-#pragma unroll
-            for (int j = 0; j < S; j++) {
-                const int kk = kfirst + j;
-                if ((unsigned int)kk < (unsigned int)n) {
-                    const int idx = cur.value_and_advance(kk) & SDRB200_CMASK;
-                    const int cs = sm->lut[idx];
-                    const int c = (int)(short)cs, sn = cs >> 16;
-                    if (DTYPE == 1) {
-                        const int x = TRK_BYTE(j);
-                        runI += (unsigned int)(c * x); runQ += (unsigned int)(sn * x);      /* sdrcmn.c:660-661 */
-                    } else {
-                        const int x0 = TRK_BYTE(2 * j), x1 = TRK_BYTE(2 * j + 1);
-                        runI += (unsigned int)(c * x0 - sn * x1);                           /* sdrcmn.c:654-655 */
-                        runQ += (unsigned int)(sn * x0 + c * x1);
-                    }
-                }
-                rowp[j] = make_uint2(runI, runQ);
+#define TRK_MIX(j, idx)                                                                             \
+            {                                                                                       \
+                const int cs = sm->lut[(idx) & SDRB200_CMASK];                                      \
+                const int c = (int)(short)cs, sn = cs >> 16;                                        \
+                if (DTYPE == 1) {                                                                   \
+                    const int x = TRK_BYTE(j);                                                      \
+                    runI += (unsigned int)(c * x); runQ += (unsigned int)(sn * x);   /* sdrcmn.c:660-661 */ \
+                } else {                                                                            \
+                    const int x0 = TRK_BYTE(2 * (j)), x1 = TRK_BYTE(2 * (j) + 1);                   \
+                    runI += (unsigned int)(c * x0 - sn * x1);                        /* sdrcmn.c:654-655 */ \
+                    runQ += (unsigned int)(sn * x0 + c * x1);                                       \
+                }                                                                                   \
             }
+            if (kfirst >= 0 && kfirst + S <= n && kfirst + S <= cur.next_k0) {
+                /* the whole row lies in one NCO segment: branch-free, incremental phase */
+                unsigned long long m = cur.m;
+                const unsigned long long D = (unsigned long long)cur.D;
+                const int sh = cur.shift, ng = cur.negm;
+#pragma unroll
+                for (int j = 0; j < S; j++) {
+                    const int tt = (int)(unsigned int)(m >> sh);
+                    TRK_MIX(j, (tt ^ ng) - ng)
+                    rowp[j] = make_uint2(runI, runQ);
+                    m += D;
+                }
+            } else slow = true;
+#undef TRK_MIX
 #undef TRK_BYTE
         }
+        /* rows that touch the window edges or more than one NCO segment go to a shared
+         * list; every warp then takes rows from it round-robin, one LANE per sample (own
+         * segment search, samples re-read from global memory) and a shuffle scan forms
+         * the running sums.  Such rows cluster at the window start (low binades), so
+         * sharing them keeps one warp from becoming the tail of the phase.            */
+        if (slow) {
+            const int i = atomicAdd(&sm->nslow[0], 1);
+            if (i < 128) sm->slow[0][i] = row; else sm->err = 3;
+        }
+        trk_bar_workers();
+        {
+            const int ns_ = min(sm->nslow[0], 128);
+            for (int it = warp - 2; it < ns_; it += TRK_WORKERS / 32) {
+                const int srow = sm->slow[0][it];
+                const int kk = (srow * TRK_SPAN - a) / DTYPE + lane;
+                unsigned int I = 0u, Q = 0u;
+                if (lane < S && (unsigned int)kk < (unsigned int)n) {
+                    const int cs = sm->lut[trk_value_at(sm->icarr, sm->carr.nseg, kk) & SDRB200_CMASK];
+                    const int c = (int)(short)cs, sn = cs >> 16;
+                    if (DTYPE == 1) {
+                        const int x = data[kk];
+                        I = (unsigned int)(c * x); Q = (unsigned int)(sn * x);
+                    } else {
+                        const int x0 = data[2 * kk], x1 = data[2 * kk + 1];
+                        I = (unsigned int)(c * x0 - sn * x1); Q = (unsigned int)(sn * x0 + c * x1);
+                    }
+                }
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const unsigned int uI = __shfl_up_sync(0xffffffffu, I, o), uQ = __shfl_up_sync(0xffffffffu, Q, o);
+                    if (lane >= o) { I += uI; Q += uQ; }
+                }
+                if (lane < S) wk.P2[(size_t)srow * RS + lane] = make_uint2(I, Q);
+                if (lane == S - 1) wk.base[srow] = make_uint2(I, Q);      /* row total, picked up by the owner */
+            }
+        }
+        trk_bar_workers();
+        if (slow) { const uint2 tt = wk.base[row]; runI = tt.x; runQ = tt.y; }
+        if (u == 0) sm->nslow[0] = 0;                     /* next round */
+        DBG(3);
         /* block-wide exclusive scan of the row totals over the worker warps 2..31 */
         unsigned int incI = runI, incQ = runQ;
 #pragma unroll
@@ -305,38 +379,72 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
     const int N = n + 2 * smax, ntap = 1 + 2 * ns;
     const int PP = (N + TRK_WORKERS - 1) / TRK_WORKERS;
     const int p0 = t * PP, p1 = min(p0 + PP, N);
-    const unsigned int lt = (1u << lane) - 1u;
     /* (a) */
+    DBG(5);
     {
-        trk_cursor_t cur;
-        int prev = -1, vprev = 0;
+        bool slow = false;
         if (p0 < N) {
-            if (p0 == 0) cur.start(sm->icode, sm->code.nseg, 0);
-            else { cur.start(sm->icode, sm->code.nseg, p0 - 1); prev = cur.value_and_advance(p0 - 1); vprev = (int)sm->codetab[prev]; }
-        }
-        for (int i = 0; i < PP; i++) {
-            const int p = p0 + i;
-            bool has = false;
-            unsigned int entry = 0u;
-            if (p < p1) {
-                const int chip = cur.value_and_advance(p);
-                if (chip != prev) {
-                    const int v = (int)sm->codetab[chip];
-                    if (v != vprev && p > 0) { has = true; entry = (unsigned int)p | (vprev < v ? 0x80000000u : 0u); }
-                    prev = chip; vprev = v;              /* p == 0: first run, prefix(0) = 0 */
+            trk_cursor_t cur;
+            slow = true;
+            if (p0 > 0) {
+                cur.start(sm->icode, sm->code.nseg, p0 - 1);
+                if (p1 <= cur.next_k0 && cur.negm == 0 && cur.D > 0) {
+                    /* the span and its left neighbour lie in one segment of a rising code
+                     * phase: chips prev+1 .. clast start inside the span; the start of chip c
+                     * is the smallest j with (m + j*D) >> sh >= c, found from a floating-point
+                     * estimate and corrected with exact integer tests                        */
+                    slow = false;
+                    const unsigned long long D = (unsigned long long)cur.D;
+                    const int prev = (int)(unsigned int)(cur.m >> cur.shift);
+                    const int clast = (int)(unsigned int)((cur.m + (unsigned long long)(p1 - p0) * D) >> cur.shift);
+                    const float invD = 1.0f / (float)cur.D;
+                    int vprev = (int)sm->codetab[prev];
+                    for (int c = prev + 1; c <= clast; c++) {
+                        const unsigned long long target = (unsigned long long)c << cur.shift;
+                        long long j = (long long)((float)(target - cur.m) * invD);
+                        j = max(1ll, min(j, (long long)(p1 - p0)));
+                        while (j > 1 && cur.m + (unsigned long long)(j - 1) * D >= target) j--;
+                        while (cur.m + (unsigned long long)j * D < target) j++;
+                        const int v = (int)sm->codetab[c];
+                        if (v != vprev) {
+                            const int slot = atomicAdd(&sm->qcount, 1);
+                            if (slot < wk.qcap) wk.queue[slot] = (unsigned int)(p0 - 1 + (int)j) | (vprev < v ? 0x80000000u : 0u);
+                            else sm->err = 2;
+                        }
+                        vprev = v;
+                    }
+                    if (p1 == N) sm->vlast = vprev;
                 }
             }
-            const unsigned int mask = __ballot_sync(0xffffffffu, has);
-            if (mask) {
-                int slot = 0;
-                if (lane == 0) slot = atomicAdd(&sm->qcount, __popc(mask));
-                slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(mask & lt);
-                if (has) { if (slot < wk.qcap) wk.queue[slot] = entry; else sm->err = 2; }
+        }
+        /* spans at the window start or across NCO segments: shared list, then every warp
+         * takes spans round-robin with one LANE per position                            */
+        if (slow) {
+            const int i = atomicAdd(&sm->nslow[1], 1);
+            if (i < 128) sm->slow[1][i] = t; else sm->err = 3;
+        }
+        trk_bar_workers();
+        const int ns_ = min(sm->nslow[1], 128);
+        for (int it = wwarp; it < ns_; it += TRK_WORKERS / 32) {
+            const int q0 = sm->slow[1][it] * PP, q1 = min(q0 + PP, N);
+            for (int pb = q0; pb < q1; pb += 32) {
+                const int p = pb + lane;
+                if (p < q1) {
+                    const int v = (int)sm->codetab[trk_value_at(sm->icode, sm->code.nseg, p)];
+                    const int vl = (p > 0) ? (int)sm->codetab[trk_value_at(sm->icode, sm->code.nseg, p - 1)] : v;
+                    if (v != vl) {
+                        const int slot = atomicAdd(&sm->qcount, 1);
+                        if (slot < wk.qcap) wk.queue[slot] = (unsigned int)p | (vl < v ? 0x80000000u : 0u);
+                        else sm->err = 2;
+                    }
+                    if (p == N - 1) sm->vlast = v;
+                }
             }
         }
-        if (p0 < N && p1 == N) sm->vlast = vprev;
     }
+    DBG(6);
     trk_bar_workers();
+    DBG(7);
     /* (b) */
     const int qn = min(sm->qcount, wk.qcap);
     for (int task = lane; task < 2 * ntap; task += 32) {
@@ -344,6 +452,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         int off = 0;
         if (tap > 0) { const int s = taps[(tap - 1) >> 1]; off = ((tap - 1) & 1) ? s : -s; }
         unsigned int acc = 0u;
+#pragma unroll 4
         for (int e = wwarp; e < qn; e += TRK_WORKERS / 32) {
             const unsigned int entry = wk.queue[e];
             const int B = (int)(entry & 0x7fffffffu) - smax;
@@ -353,6 +462,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         if (wwarp == 0) acc += (unsigned int)sm->vlast * trk_prefix_at<DTYPE>(wk, a, n, isQ);   /* r_last * P[n] */
         if (acc) atomicAdd(&sm->sum[isQ ? SDRB200_MAXTAPS + tap : tap], acc);
     }
+    DBG(8);
 }
 
 #endif
