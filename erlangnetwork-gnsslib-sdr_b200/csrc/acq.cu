@@ -28,6 +28,8 @@
 #include "sdrb200_internal.h"
 #include "nco_exact.h"
 #include "fft_device.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 /* the carrier table (src/sdrcmn.c:641-646), float copies for the wipe-off */
 __constant__ float c_cosf[32] = {32,31,30,27,23,18,12,6,0,-6,-12,-18,-23,-27,-30,-31,-32,-31,-30,-27,-23,-18,-12,-6,0,6,12,18,23,27,30,31};
@@ -54,7 +56,9 @@ struct sdrb200_acq {
     float2 *d_Cs;                    /* [nprn][R][L]                          */
     float2 *d_S;                     /* [chunk][nfreq][R][L] scratch          */
     float  *d_P;                     /* [nprn][nfreq][n_eff]                  */
-    acq_rowstat_t *d_row;            /* [nprn][nfreq]                         */
+    acq_rowstat_t *d_row;            /* [nprn][nfreq] (legacy path only)      */
+    unsigned long long *d_key;       /* [nprn] argmax keys (fused path)       */
+    int fused, keep_power;
     sdrb200_acq_result_t *d_res, *h_res;
     int *d_frozen;
     double *d_freq;
@@ -305,6 +309,209 @@ __global__ void k_final(const acq_rowstat_t *__restrict__ rows, int nfreq, const
     }
 }
 
+/* ---------------------------------------------------- fused cluster kernel
+ * One thread-block CLUSTER of R CTAs per (PRN, bin) row.  CTA q forms the
+ * spectrum product and the inverse L-point sub-transform of residue class q
+ * (cpxconv, src/sdrcmn.c:236-242), scales by W_M^(-t q) and leaves the result in
+ * its own shared memory.  After a cluster barrier every CTA gathers an L/R-wide
+ * slice of all R sub-transforms through distributed shared memory and finishes
+ * the radix-R butterfly for the lag blocks that are kept (lags < n <= M/2 need
+ * only R/2 of the R outputs), so neither the sub-transforms nor - for a single
+ * integration - the power matrix ever go to HBM.
+ *
+ * mode 0 (search): power (+ optional accumulation into P, cpxconv flagsum,
+ *   src/sdrcmn.c:244-246) and the PRN's global argmax as one 64-bit atomicMax
+ *   key = power bits : ~flat index, i.e. maxvd()'s first-index-wins over the
+ *   reference's [bin][lag] layout (src/sdracq.c:76-77, sdrcmn.c:461-476).
+ * mode 1 (peak): only the winning row of every PRN (recomputed, or read back
+ *   from P when P is kept): masked mean and second maximum around the known
+ *   peak, C/N0, peak ratio, decision, early-exit freeze (src/sdracq.c:79-94,
+ *   38-42).                                                                   */
+struct acq_rowc_args {
+    const float2 *Xs, *Cs, *tw;
+    float *P;                               /* NULL: power matrix not kept       */
+    unsigned long long *key;                /* [nprn]                            */
+    const int *frozen_in; int *frozen;
+    sdrb200_acq_result_t *res;
+    const double *freq;
+    double ctime, thresh;
+    int nfreq, n_eff, nsampchip, first_step, step, mode;
+    float invM2;
+};
+
+struct acq_part_t { double sum; int cnt; float max2; };
+
+struct acq_sink_t {
+    /* mode 0 */
+    unsigned long long best;
+    unsigned int flat0;                     /* f * n_eff                         */
+    /* mode 1 */
+    double sum; int cnt; float max2; int exs, exe;
+    float *Prow; int n_eff, mode, first_step;
+    __device__ __forceinline__ void put(int t, float pw)
+    {
+        if (t >= n_eff) return;
+        if (mode == 0) {
+            if (Prow) { if (!first_step) pw += Prow[t]; Prow[t] = pw; }
+            const unsigned long long k = ((unsigned long long)__float_as_uint(pw) << 32) |
+                                         (unsigned long long)(0xffffffffu - (flat0 + (unsigned int)t));
+            if (k > best) best = k;
+        } else {
+            const bool inc = (exs <= exe) ? (t < exs || t > exe) : (t < exs && t > exe);
+            if (inc) { sum += (double)pw; cnt++; }
+            if ((inc || t == 0) && pw > max2) max2 = pw;          /* maxvd seeds with data[0] */
+        }
+    }
+};
+
+template <int L, int R>
+__global__ void __launch_bounds__(L / 16, (L <= 4096) ? 4 : (L <= 8192 ? 2 : 1))
+k_rowc(const acq_rowc_args A)
+{
+    extern __shared__ float2 fsm[];
+    __shared__ unsigned long long s_key[32];
+    __shared__ acq_part_t s_part[32];
+    __shared__ acq_part_t s_cta;
+    constexpr int T = L / 16;
+    constexpr int M = L * R;
+    constexpr int NA = (R >= 2) ? R / 2 : 1;          /* lag blocks kept          */
+    constexpr int J = 16 / R;                         /* slice columns per thread */
+    const int q = blockIdx.x, p = blockIdx.z, tid = threadIdx.x;
+    const int lane = tid & 31, warp = tid >> 5;
+    cg::cluster_group cluster = cg::this_cluster();
+    if (A.frozen_in[p]) return;                       /* whole cluster leaves     */
+    int f = blockIdx.y, codei = 0;
+    float maxp = 0.f;
+    if (A.mode == 1) {
+        const unsigned long long k = A.key[p];
+        const unsigned int flat = k ? 0xffffffffu - (unsigned int)(k & 0xffffffffu) : 0u;
+        f = (int)(flat / (unsigned int)A.n_eff);
+        codei = (int)(flat - (unsigned int)f * (unsigned int)A.n_eff);
+        maxp = __uint_as_float((unsigned int)(k >> 32));
+    }
+    acq_sink_t sk;
+    sk.best = 0ull; sk.flat0 = (unsigned int)f * (unsigned int)A.n_eff;
+    sk.sum = 0.0; sk.cnt = 0; sk.max2 = -1.f;
+    sk.exs = codei - 2 * A.nsampchip; if (sk.exs < 0) sk.exs += A.n_eff;          /* src/sdracq.c:81-82 */
+    sk.exe = codei + 2 * A.nsampchip; if (sk.exe >= A.n_eff) sk.exe -= A.n_eff;
+    sk.Prow = A.P ? A.P + ((size_t)p * A.nfreq + f) * A.n_eff : nullptr;
+    sk.n_eff = A.n_eff; sk.mode = A.mode; sk.first_step = A.first_step;
+
+    if (A.mode == 1 && A.P) {
+        /* the accumulated row is in HBM: read this CTA's share of it */
+        for (int t = q * T + tid; t < A.n_eff; t += R * T) sk.put(t, sk.Prow[t]);
+    } else {
+        const float2 *x = A.Xs + ((size_t)f * R + q) * L;
+        const float2 *c = A.Cs + ((size_t)p * R + q) * L;
+        float2 v[16];
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[e] = cmulc(__ldg(&x[tid + e * T]), __ldg(&c[tid + e * T]));
+        cta_fft<L, +1>(v, fsm, A.tw, R);
+        if constexpr (R == 1) {
+#pragma unroll
+            for (int e = 0; e < 16; e++)
+                sk.put(tid + e * T, (v[e].x * v[e].x + v[e].y * v[e].y) * A.invM2);
+        } else {
+            /* z_q[t'] = W_M^(-t' q) y_q[t'] into own shared memory */
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                const int tp = tid + e * T;
+                float2 z = v[e];
+                if (q != 0) z = cmulc(z, __ldg(&A.tw[(q * tp) & (M - 1)]));
+                fsm[tp] = z;
+            }
+            cluster.sync();
+            const float2 *zs[R];
+#pragma unroll
+            for (int r = 0; r < R; r++) zs[r] = cluster.map_shared_rank(fsm, r);
+#pragma unroll
+            for (int j = 0; j < J; j++) {
+                const int tp = q * (L / R) + tid + j * T;
+                float2 z[R];
+#pragma unroll
+                for (int r = 0; r < R; r++) z[r] = zs[r][tp];
+                float2 y[NA];
+                if constexpr (R == 2) {
+                    y[0] = cadd(z[0], z[1]);
+                } else if constexpr (R == 4) {
+                    y[0] = cadd(cadd(z[0], z[2]), cadd(z[1], z[3]));
+                    y[1] = cadd(csub(z[0], z[2]), crot<+1>(csub(z[1], z[3])));
+                } else {
+                    /* R == 8: even / odd 4-point transforms, then W_8^(-a) */
+                    float2 e0 = z[0], e1 = z[2], e2 = z[4], e3 = z[6];
+                    float2 o0 = z[1], o1 = z[3], o2 = z[5], o3 = z[7];
+                    fft4<+1>(e0, e1, e2, e3);
+                    fft4<+1>(o0, o1, o2, o3);
+                    y[0] = cadd(e0, o0);
+                    y[1] = cadd(e1, cw16<+1, 2>(o1));
+                    y[2] = cadd(e2, cw16<+1, 4>(o2));
+                    y[3] = cadd(e3, cw16<+1, 6>(o3));
+                }
+#pragma unroll
+                for (int a = 0; a < NA; a++)
+                    sk.put(tp + L * a, (y[a].x * y[a].x + y[a].y * y[a].y) * A.invM2);
+            }
+        }
+    }
+
+    if (A.mode == 0) {
+        unsigned long long b = sk.best;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+            if (ob > b) b = ob;
+        }
+        if (lane == 0) s_key[warp] = b;
+        __syncthreads();
+        if (warp == 0) {
+            b = (lane < T / 32) ? s_key[lane] : 0ull;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+                if (ob > b) b = ob;
+            }
+            if (lane == 0 && b) atomicMax(&A.key[p], b);
+        }
+        if (R > 1) cluster.sync();                    /* peers may still be reading fsm */
+        return;
+    }
+
+    /* mode 1: reduce the masked statistics over the CTA, then over the cluster */
+    double sum = sk.sum; int cnt = sk.cnt; float m2 = sk.max2;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    }
+    if (lane == 0) { s_part[warp].sum = sum; s_part[warp].cnt = cnt; s_part[warp].max2 = m2; }
+    __syncthreads();
+    if (tid == 0) {
+        const int nw = (T + 31) / 32;
+        for (int w = 1; w < nw; w++) { sum += s_part[w].sum; cnt += s_part[w].cnt; m2 = fmaxf(m2, s_part[w].max2); }
+        s_cta.sum = sum; s_cta.cnt = cnt; s_cta.max2 = m2;
+    }
+    cluster.sync();
+    if (q == 0 && tid == 0) {
+        for (int r = 1; r < R; r++) {
+            const acq_part_t *o = cluster.map_shared_rank(&s_cta, r);
+            sum += o->sum; cnt += o->cnt; m2 = fmaxf(m2, o->max2);
+        }
+        sdrb200_acq_result_t o;
+        o.maxp = (double)maxp; o.maxp2 = (double)m2;
+        o.meanp = sum / (double)cnt;                               /* meanvd, sdrcmn.c:487-497 */
+        o.cn0 = 10 * log10(o.maxp / o.meanp / A.ctime);            /* sdracq.c:84 */
+        o.peakr = o.maxp / o.maxp2;                                /* sdracq.c:88 */
+        o.codei = codei; o.freqi = f; o.acqfreq = A.freq[f];
+        o.acquired = (o.peakr > A.thresh) ? 1 : 0;
+        o.nintg = A.step + 1;
+        A.res[p] = o;
+        if (o.acquired) A.frozen[p] = 1;
+        A.key[p] = 0ull;                                           /* next integration step */
+    }
+    cluster.sync();
+}
+
 /* ------------------------------------------------------------- host side */
 template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int nitems, const int8_t *src,
                                        size_t item_stride, int dtype, int nlive, const uint8_t *cidx,
@@ -337,6 +544,36 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
     return SDRB200_OK;
 }
 
+template <int L, int R> static int launch_rowc(cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
+{
+    const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowc<L, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(R, nfreq_grid, nprn);
+    cfg.blockDim = dim3(L / 16, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = R; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_rowc<L, R>, A));
+    sdrb200_count_launch(1);
+    return SDRB200_OK;
+}
+
+static int launch_rowc_any(int L, int R, cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
+{
+#define RC(LL, RR) if (L == LL && R == RR) return launch_rowc<LL, RR>(st, A, nfreq_grid, nprn);
+    RC(512, 1) RC(1024, 1) RC(2048, 1) RC(4096, 1)
+    RC(1024, 2) RC(2048, 2) RC(4096, 2) RC(8192, 2) RC(16384, 2)
+    RC(1024, 4) RC(2048, 4) RC(4096, 4) RC(8192, 4) RC(16384, 4)
+    RC(1024, 8) RC(2048, 8) RC(4096, 8) RC(8192, 8) RC(16384, 8)
+#undef RC
+    sdrb200_set_error("acquisition: no fused kernel for L=%d R=%d", L, R);
+    return SDRB200_EINVAL;
+}
+
 #define ACQ_DISPATCH_L(Lval, CALL)                                             \
     switch (Lval) {                                                            \
     case 256:   { constexpr int LL = 256;   rc = CALL; } break;                \
@@ -352,7 +589,7 @@ extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
 {
     if (!a) return;
     cudaFree(a->d_tw); cudaFree(a->d_cidx); cudaFree(a->d_Xs); cudaFree(a->d_Cs); cudaFree(a->d_S);
-    cudaFree(a->d_P); cudaFree(a->d_row); cudaFree(a->d_res); cudaFree(a->d_frozen); cudaFree(a->d_freq);
+    cudaFree(a->d_P); cudaFree(a->d_row); cudaFree(a->d_key); cudaFree(a->d_res); cudaFree(a->d_frozen); cudaFree(a->d_freq);
     cudaFree(a->d_hostwin);
     if (a->h_res) cudaFreeHost(a->h_res);
     if (a->h_pin) cudaFreeHost(a->h_pin);
@@ -364,12 +601,17 @@ extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
 
 extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)a->st : NULL; }
 
-static int acq_sub_length(int M)
+/* M = R * L.  Up to R = 8 the R sub-transforms of a row are finished inside one
+ * thread-block cluster (k_rowc); longer windows (20 ms coherent blocks) use the
+ * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
+static void acq_choose(int M, int *L, int *R, int *fused)
 {
-    int lsub = 8192;
+    int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
+    if (lsub > 16384) lsub = 8192;                                   /* scratch path */
     const char *env = getenv("SDRB200_LSUB");
-    if (env) { int v = atoi(env); if (v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) lsub = v; }
-    return M < lsub ? M : lsub;
+    if (env) { int v = atoi(env); if ((v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) && v <= M) lsub = v; }
+    *L = lsub; *R = M / lsub;
+    *fused = (*R <= 8 && !getenv("SDRB200_ACQ_SCRATCH")) ? 1 : 0;
 }
 
 extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *cfg)
@@ -386,9 +628,8 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     if (a->cfg.threshold <= 0) a->cfg.threshold = 3.0;           /* ACQTH */
     a->n_eff = cfg->nsamp * a->cfg.ncoh;
     a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
-    a->M = 256; while (a->M < a->m_ref) a->M <<= 1;
-    a->L = acq_sub_length(a->M);
-    a->R = a->M / a->L;
+    a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
+    acq_choose(a->M, &a->L, &a->R, &a->fused);
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }
     a->h_freq = (double *)malloc(sizeof(double) * nfreq);
@@ -408,9 +649,12 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     ACQ_ALLOC(a->d_cidx, (size_t)nfreq * a->m_ref);
     ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)nfreq * M);
     ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
-    if (a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * nfreq * M);
-    ACQ_ALLOC(a->d_P, sizeof(float) * (size_t)nprn * nfreq * n_eff);
-    ACQ_ALLOC(a->d_row, sizeof(acq_rowstat_t) * (size_t)nprn * nfreq);
+    if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * nfreq * M);
+    /* the power matrix is kept in HBM only when it has to be: accumulation over
+     * several integrations, the scratch path, or on request (sdrb200_acq_keep_power) */
+    if (!a->fused || a->cfg.intg > 1) ACQ_ALLOC(a->d_P, sizeof(float) * (size_t)nprn * nfreq * n_eff);
+    if (!a->fused) ACQ_ALLOC(a->d_row, sizeof(acq_rowstat_t) * (size_t)nprn * nfreq);
+    ACQ_ALLOC(a->d_key, sizeof(unsigned long long) * nprn);
     ACQ_ALLOC(a->d_res, sizeof(sdrb200_acq_result_t) * nprn);
     ACQ_ALLOC(a->d_frozen, sizeof(int) * nprn);
     ACQ_ALLOC(a->d_freq, sizeof(double) * nfreq);
@@ -531,6 +775,7 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
     if (a->timing) { int rc2 = acq_timing_collect(a); if (rc2) return rc2; }
     SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_frozen, 0, sizeof(int) * c->nprn, a->st));
     SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_res, 0, sizeof(sdrb200_acq_result_t) * c->nprn, a->st));
+    SDRB200_CUDA_TRY(cudaMemsetAsync(a->d_key, 0, sizeof(unsigned long long) * c->nprn, a->st));
     for (int step = 0; step < c->intg; step++) {
         const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
         const int8_t *win = base + pos * c->dtype;
@@ -539,6 +784,25 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
                                              a->m_ref, scale, a->d_tw, a->d_Xs)));
         if (rc) return rc;
         ACQ_T1(a, 0);
+        if (a->fused) {
+            acq_rowc_args A;
+            A.Xs = a->d_Xs; A.Cs = a->d_Cs; A.tw = a->d_tw; A.P = a->d_P; A.key = a->d_key;
+            A.frozen_in = a->d_frozen; A.frozen = a->d_frozen; A.res = a->d_res; A.freq = a->d_freq;
+            A.ctime = c->ctime; A.thresh = c->threshold; A.nfreq = c->nfreq; A.n_eff = a->n_eff;
+            A.nsampchip = c->nsampchip; A.first_step = (step == 0); A.step = step;
+            A.invM2 = 1.0f / ((float)a->M * (float)a->M);
+            A.mode = 0;
+            ACQ_T0(a);
+            rc = launch_rowc_any(a->L, a->R, a->st, A, c->nfreq, c->nprn);
+            if (rc) return rc;
+            ACQ_T1(a, 1);
+            A.mode = 1;
+            ACQ_T0(a);
+            rc = launch_rowc_any(a->L, a->R, a->st, A, 1, c->nprn);
+            if (rc) return rc;
+            ACQ_T1(a, 3);
+            continue;
+        }
         for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
             const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
             ACQ_T0(a);
@@ -617,9 +881,26 @@ extern "C" int sdrb200_acq_run_host(sdrb200_acq_t *a, const int8_t *host_if, uin
     return sdrb200_acq_fetch(a, results);
 }
 
+extern "C" int sdrb200_acq_keep_power(sdrb200_acq_t *a, int on)
+{
+    if (!a) return SDRB200_EINVAL;
+    if (on && !a->d_P) {
+        SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+        const size_t bytes = sizeof(float) * (size_t)a->cfg.nprn * a->cfg.nfreq * a->n_eff;
+        if (cudaMalloc((void **)&a->d_P, bytes) != cudaSuccess) {
+            cudaGetLastError(); sdrb200_set_error("acq_keep_power: cudaMalloc(%zu) failed", bytes); return SDRB200_ENOMEM;
+        }
+    } else if (!on && a->d_P && a->fused && a->cfg.intg == 1) {
+        SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+        cudaFree(a->d_P); a->d_P = NULL;
+    }
+    return SDRB200_OK;
+}
+
 extern "C" int sdrb200_acq_power(sdrb200_acq_t *a, int prn_index, double *power)
 {
     if (!a || !power || prn_index < 0 || prn_index >= a->cfg.nprn) return SDRB200_EINVAL;
+    if (!a->d_P) { sdrb200_set_error("acq_power: the power matrix is not kept (call sdrb200_acq_keep_power first)"); return SDRB200_EINVAL; }
     const size_t n = (size_t)a->cfg.nfreq * a->n_eff;
     float *h = (float *)malloc(sizeof(float) * n);
     if (!h) return SDRB200_ENOMEM;

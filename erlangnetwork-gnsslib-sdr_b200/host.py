@@ -195,7 +195,7 @@ class Acquisition:
     (src/sdracq.c:14-95, src/sdrcmn.c:738-773)."""
 
     def __init__(self, f_sf, dtype, nsamp, nsampchip, ctime, freq, codes, crate,
-                 intg=10, ncoh=1, threshold=3.0):
+                 intg=10, ncoh=1, threshold=3.0, keep_power=False):
         self.freq = np.ascontiguousarray(freq, np.float64)
         self.codes = np.ascontiguousarray(codes, np.int8)
         assert self.codes.ndim == 2
@@ -206,6 +206,12 @@ class Acquisition:
                      crate=crate, codes=_p(self.codes, _i8p), intg=intg, ncoh=ncoh, threshold=threshold)
         self.h = C.c_void_p()
         check(lib.sdrb200_acq_create(C.byref(self.h), C.byref(cfg)), "acq_create")
+        if keep_power:
+            self.keep_power(True)
+
+    def keep_power(self, on: bool):
+        """Store the power matrix in HBM too, so that power() can read it back."""
+        check(lib.sdrb200_acq_keep_power(self.h, int(bool(on))), "acq_keep_power")
 
     def _results(self, arr):
         return [dict(acquired=r.acquired, freqi=r.freqi, codei=r.codei, nintg=r.nintg,

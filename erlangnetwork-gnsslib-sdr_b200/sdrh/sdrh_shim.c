@@ -140,7 +140,10 @@ static sdrb200_acq_t *plan_of(sdrch_t *sdr)
             c.ctime = sdr->ctime; c.nfreq = sdr->acq.nfreq; c.freq = sdr->acq.freq; c.nprn = 1;
             c.clen = sdr->clen; c.crate = sdr->crate; c.codes = code; c.intg = sdr->acq.intg;
             c.ncoh = 1; c.threshold = ACQTH;
-            if (sdrb200_acq_create(&plan, &c) == SDRB200_OK) { g_plan[slot].key = sdr; g_plan[slot].plan = plan; }
+            if (sdrb200_acq_create(&plan, &c) == SDRB200_OK) {
+                g_plan[slot].key = sdr; g_plan[slot].plan = plan;
+                if (sdrb200_sdrh_fill_power) sdrb200_acq_keep_power(plan, 1);
+            }
             else plan = NULL;
             free(code);
         }
@@ -186,6 +189,7 @@ uint64_t sdracquisition(sdrch_t *sdr, double *power)     /* src/sdracq.c:14-62 *
     for (i = 0; i < intg; i++)
         rcvgetbuff(&sdrini, buffloc + (uint64_t)i * nsamp, 2 * nsamp, sdr->ftype, dt,
                    data + (size_t)i * nsamp * dt);
+    if (power && sdrb200_sdrh_fill_power) sdrb200_acq_keep_power(plan, 1);
     rc = sdrb200_acq_run_host(plan, (const int8_t *)data, (uint64_t)(intg + 1) * nsamp, &r);
     if (rc) {
         fail("sdracquisition", rc);

@@ -136,12 +136,18 @@ int  sdrb200_acq_enqueue(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_
 int  sdrb200_acq_fetch(sdrb200_acq_t *plan, sdrb200_acq_result_t *results);
 void *sdrb200_acq_cuda_stream(sdrb200_acq_t *plan);
 /* per-kernel CUDA-event timing of the enqueued launches; kernel classes:
- * 0 forward (wipe-off + FFT), 1 row (spectrum product + inverse FFT),
- * 2 combine (power, accumulation, row statistics), 3 decision                 */
+ * 0 forward (wipe-off + FFT), 1 row search (spectrum product, inverse FFT,
+ * power, argmax), 2 combine (scratch path only, windows > 8 sub-transforms),
+ * 3 peak statistics + decision                                                 */
 int  sdrb200_acq_set_timing(sdrb200_acq_t *plan, int on);
 int  sdrb200_acq_kernel_ms(sdrb200_acq_t *plan, double *ms4, long long *cnt4);
+/* The [nprn][nfreq][nsamp] power matrix stays on chip unless it has to be
+ * accumulated over several integrations (intg > 1).  keep_power(plan, 1) makes
+ * the plan store it in HBM as well, so that it can be read back for plotting
+ * (the `power` argument of sdracquisition, src/sdracq.c:14, sdrplot.c).        */
+int  sdrb200_acq_keep_power(sdrb200_acq_t *plan, int on);
 /* copy the accumulated power matrix of one PRN to the host: [nfreq][nsamp]
- * doubles (the `power` argument of sdracquisition)                           */
+ * doubles; EINVAL when the matrix is not kept                                */
 int  sdrb200_acq_power(sdrb200_acq_t *plan, int prn_index, double *power);
 
 /* ----------------------------------------------------------------- tracking

@@ -30,7 +30,8 @@ def _check(sdr, oracle, cfg, fs, f_if, dtype, prns, cfgo, intg, power_prn=None):
     ref, pw = oracle.acquire(cfgo, host, avail, prns, want_power=power_prn is not None)
     codes = np.stack([sdr.gencode(p)[0] for p in prns])
     freq = _grid(cfgo, f_if)
-    acq = sdr.Acquisition(fs, dtype, nsamp, int(nsamp / 1023), 1e-3, freq, codes, 1.023e6, intg=intg)
+    acq = sdr.Acquisition(fs, dtype, nsamp, int(nsamp / 1023), 1e-3, freq, codes, 1.023e6, intg=intg,
+                          keep_power=power_prn is not None)
     buffloc0 = avail - need                                     # src/sdracq.c:24-26
     got = acq.run(st, buffloc0)
     for r, g, p in zip(ref, got, prns):

@@ -27,7 +27,7 @@ def test_golden_acquisition(sdr):
     prns = [int(p) for p in g["prns"]]
     codes = np.stack([sdr.gencode(p)[0] for p in prns])
     freq = np.array([util.IF1 + (i - 35) * 200.0 for i in range(71)])
-    acq = sdr.Acquisition(util.FS1, 1, 16368, 16, 1e-3, freq, codes, 1.023e6, intg=2)
+    acq = sdr.Acquisition(util.FS1, 1, 16368, 16, 1e-3, freq, codes, 1.023e6, intg=2, keep_power=True)
     b0 = 65536 - 3 * 16368
     got = acq.run_host(g["if_data"][b0:], 3 * 16368)
     for i, (row, r) in enumerate(zip(g["result"], got)):
