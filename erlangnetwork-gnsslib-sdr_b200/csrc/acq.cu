@@ -90,40 +90,140 @@ k_fwd(const int8_t *__restrict__ src, size_t item_stride, int dtype, int nlive,
     const int M = L * R;
     const int8_t *d = src + (SRC == 1 ? (size_t)item * item_stride : 0);
     const uint8_t *ci = (SRC == 0) ? cidx + (size_t)item * cidx_stride : nullptr;
+    /* the 32-entry carrier table lives one entry per lane: a lookup is one shuffle
+     * (a __constant__ table would serialise on the 32 different indices of a warp) */
+    const float lut_c = c_cosf[tid & 31], lut_s = c_sinf[tid & 31];
     float2 v[16];
 #pragma unroll
-    for (int e = 0; e < 16; e++) {
-        const int b = tid + e * T;
-        float2 acc = make_float2(0.f, 0.f);
-        for (int a = 0; a < R; a++) {
-            const int t = L * a + b;
-            if (t < nlive) {
-                float2 x;
-                if (SRC == 0) {
-                    const int idx = ci[t];
-                    const float c = c_cosf[idx], s = c_sinf[idx];
-                    if (dtype == 1) {
-                        const float s0 = (float)d[t];
-                        x = make_float2(c * s0 * scale, s * s0 * scale);
-                    } else {
-                        const float s0 = (float)d[2 * t], s1 = (float)d[2 * t + 1];
-                        x = make_float2((c * s0 - s * s1) * scale, (s * s0 + c * s1) * scale);
-                    }
-                } else {
-                    x = make_float2((float)d[t], 0.f);
-                }
-                if (a != 0 && q != 0) x = cmul(x, __ldg(&tw[(size_t)((a * q) % R) * L]));
-                acc = cadd(acc, x);
+    for (int e = 0; e < 16; e++) v[e] = make_float2(0.f, 0.f);
+    /* residue-class sums: outer loop over the R blocks (one uniform twiddle each),
+     * inner loop unrolled so that the 16 (or 32) byte loads of a block are in flight
+     * together                                                                       */
+    for (int a = 0; a < R; a++) {
+        const float2 wa = (a != 0 && q != 0) ? __ldg(&tw[(size_t)((a * q) % R) * L]) : make_float2(1.f, 0.f);
+        /* this lane's entry of the block's table: carrier LUT x input scale x W_R^(a q) */
+        const float2 g = cmul(make_float2(lut_c * scale, lut_s * scale), wa);
+        int idx[16]; int s0[16], s1[16];
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            /* branch-free: clamp the address, zero the sample past the window, so that
+             * all loads of the block are issued back to back                        */
+            const int t = L * a + tid + e * T;
+            const bool live = t < nlive;
+            const int tc = live ? t : nlive - 1;
+            idx[e] = (SRC == 0) ? (int)ci[tc] : 0;
+            if (SRC == 0 && dtype != 1) {
+                const int v0 = d[2 * tc], v1 = d[2 * tc + 1];
+                s0[e] = live ? v0 : 0; s1[e] = live ? v1 : 0;
+            } else {
+                const int v0 = d[tc];
+                s0[e] = live ? v0 : 0; s1[e] = 0;
             }
         }
-        if (q != 0) acc = cmul(acc, __ldg(&tw[(size_t)b * q]));
-        v[e] = acc;
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            if (SRC == 0) {
+                const float gx = __shfl_sync(0xffffffffu, g.x, idx[e]), gy = __shfl_sync(0xffffffffu, g.y, idx[e]);
+                const float f0 = (float)s0[e];
+                v[e].x = fmaf(f0, gx, v[e].x); v[e].y = fmaf(f0, gy, v[e].y);
+                if (dtype != 1) {                      /* (s0 + i s1) * g */
+                    const float f1 = (float)s1[e];
+                    v[e].x = fmaf(-f1, gy, v[e].x); v[e].y = fmaf(f1, gx, v[e].y);
+                }
+            } else {
+                const float f0 = (float)s0[e];
+                v[e].x = fmaf(f0, wa.x, v[e].x); v[e].y = fmaf(f0, wa.y, v[e].y);
+            }
+        }
+    }
+    if (q != 0) {
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[e] = cmul(v[e], __ldg(&tw[(size_t)(tid + e * T) * q]));
     }
     cta_fft<L, -1>(v, fsm, tw, R);
     float2 *o = out + ((size_t)item * R + q) * L;
 #pragma unroll
     for (int e = 0; e < 16; e++) o[tid + e * T] = v[e];
     (void)M;
+}
+
+/* forward transform of the IF window for one (Doppler bin, q): mixcarr + cpxcpx
+ * (src/sdrcmn.c:650-662, 185-195) fused into the residue-class sums of the
+ * four-step transform.  The window is walked in R blocks of L samples; every
+ * block (samples and carrier-table indices) is fetched with 16-byte loads, one
+ * block ahead of its use, and re-read per thread from shared memory.  The 32-entry
+ * carrier table x input scale x W_R^(a q) is held one entry per lane, so a lookup
+ * is a shuffle and a sample costs two FMAs.                                     */
+template <int L>
+__global__ void __launch_bounds__(L / 16, (L <= 4096) ? 4 : (L <= 8192 ? 2 : 1))
+k_fwd_if(const int8_t *__restrict__ win, int dtype, int nlive, const uint8_t *__restrict__ cidx,
+         int cidx_stride, float scale, const float2 *__restrict__ tw, int R, float2 *__restrict__ out)
+{
+    extern __shared__ float2 fsm[];
+    constexpr int T = L / 16;
+    const int q = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    /* staging behind the FFT buffer: 2 x (samples: 2L + 32 bytes, indices: L bytes) */
+    unsigned char *stage = (unsigned char *)(fsm + FFT_SMEM_ELEMS(L));
+    constexpr int SD = 2 * L + 32, SB = SD + L;
+    const size_t g = (size_t)win;
+    const int off = (int)(g & 15);
+    const uint4 *wal = (const uint4 *)(g - off);
+    const uint4 *cal = (const uint4 *)(cidx + (size_t)f * cidx_stride);
+    const int live_bytes = nlive * dtype + off;           /* relative to wal          */
+    const int nd = L * dtype / 16;                        /* sample chunks per block  */
+    const float lut_c = c_cosf[tid & 31] * scale, lut_s = c_sinf[tid & 31] * scale;
+    const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
+    uint4 pd0, pd1, pd2, pi;
+    auto fetch = [&](int a) {
+        /* chunks a*nd + {tid, tid + T, (tid == 0) nd}: L*dtype + 16 bytes cover the
+         * misalignment; anything past the live window reads as zero                */
+        const int c0 = a * nd + tid;
+        pd0 = (c0 * 16 < live_bytes) ? __ldg(&wal[c0]) : zero4;
+        pd1 = (dtype == 2 && (c0 + T) * 16 < live_bytes) ? __ldg(&wal[c0 + T]) : zero4;
+        pd2 = (tid == 0 && (a * nd + nd) * 16 < live_bytes) ? __ldg(&wal[a * nd + nd]) : zero4;
+        pi = ((a * T + tid) * 16 < nlive) ? __ldg(&cal[a * T + tid]) : zero4;
+    };
+    float2 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = make_float2(0.f, 0.f);
+    const int nblk = (nlive + L - 1) / L;                  /* blocks that hold samples */
+    fetch(0);
+    for (int a = 0; a < nblk; a++) {
+        unsigned char *sd = stage + (a & 1) * SB, *si = sd + SD;
+        ((uint4 *)sd)[tid] = pd0;
+        if (dtype == 2) ((uint4 *)sd)[tid + T] = pd1;
+        if (tid == 0) ((uint4 *)sd)[nd] = pd2;
+        ((uint4 *)si)[tid] = pi;
+        __syncthreads();
+        if (a + 1 < nblk) fetch(a + 1);
+        const float2 wa = (a != 0 && q != 0) ? __ldg(&tw[(size_t)((a * q) % R) * L]) : make_float2(1.f, 0.f);
+        const float2 g2 = cmul(make_float2(lut_c, lut_s), wa);
+        const signed char *sds = (const signed char *)sd + off;
+#pragma unroll
+        for (int e = 0; e < 16; e++) {
+            const int b = tid + e * T;
+            const bool live = L * a + b < nlive;
+            const int idx = si[b];
+            const float gx = __shfl_sync(0xffffffffu, g2.x, idx), gy = __shfl_sync(0xffffffffu, g2.y, idx);
+            if (dtype == 1) {
+                const float f0 = live ? (float)sds[b] : 0.f;
+                v[e].x = fmaf(f0, gx, v[e].x); v[e].y = fmaf(f0, gy, v[e].y);
+            } else {                                       /* (s0 + i s1) * g */
+                const float f0 = live ? (float)sds[2 * b] : 0.f, f1 = live ? (float)sds[2 * b + 1] : 0.f;
+                v[e].x = fmaf(f0, gx, v[e].x); v[e].y = fmaf(f0, gy, v[e].y);
+                v[e].x = fmaf(-f1, gy, v[e].x); v[e].y = fmaf(f1, gx, v[e].y);
+            }
+        }
+    }
+    if (q != 0) {
+#pragma unroll
+        for (int e = 0; e < 16; e++) v[e] = cmul(v[e], __ldg(&tw[(size_t)(tid + e * T) * q]));
+    }
+    __syncthreads();
+    cta_fft<L, -1>(v, fsm, tw, R);
+    float2 *o = out + ((size_t)f * R + q) * L;
+#pragma unroll
+    for (int e = 0; e < 16; e++) o[tid + e * T] = v[e];
 }
 
 /* per-row statistics over a power row held in global memory; all threads of
@@ -331,40 +431,21 @@ struct acq_rowc_args {
     const float2 *Xs, *Cs, *tw;
     float *P;                               /* NULL: power matrix not kept       */
     unsigned long long *key;                /* [nprn]                            */
-    const int *frozen_in; int *frozen;
+    int *frozen;
     sdrb200_acq_result_t *res;
     const double *freq;
     double ctime, thresh;
-    int nfreq, n_eff, nsampchip, first_step, step, mode;
+    int nfreq, n_eff, nsampchip, first_step, step;
     float invM2;
 };
 
 struct acq_part_t { double sum; int cnt; float max2; };
 
-struct acq_sink_t {
-    /* mode 0 */
-    unsigned long long best;
-    unsigned int flat0;                     /* f * n_eff                         */
-    /* mode 1 */
-    double sum; int cnt; float max2; int exs, exe;
-    float *Prow; int n_eff, mode, first_step;
-    __device__ __forceinline__ void put(int t, float pw)
-    {
-        if (t >= n_eff) return;
-        if (mode == 0) {
-            if (Prow) { if (!first_step) pw += Prow[t]; Prow[t] = pw; }
-            const unsigned long long k = ((unsigned long long)__float_as_uint(pw) << 32) |
-                                         (unsigned long long)(0xffffffffu - (flat0 + (unsigned int)t));
-            if (k > best) best = k;
-        } else {
-            const bool inc = (exs <= exe) ? (t < exs || t > exe) : (t < exs && t > exe);
-            if (inc) { sum += (double)pw; cnt++; }
-            if ((inc || t == 0) && pw > max2) max2 = pw;          /* maxvd seeds with data[0] */
-        }
-    }
-};
+__device__ __forceinline__ void cl_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cl_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cl_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 
-template <int L, int R>
+template <int L, int R, int MODE>
 __global__ void __launch_bounds__(L / 16, (L <= 4096) ? 4 : (L <= 8192 ? 2 : 1))
 k_rowc(const acq_rowc_args A)
 {
@@ -373,54 +454,55 @@ k_rowc(const acq_rowc_args A)
     __shared__ acq_part_t s_part[32];
     __shared__ acq_part_t s_cta;
     constexpr int T = L / 16;
-    constexpr int M = L * R;
     constexpr int NA = (R >= 2) ? R / 2 : 1;          /* lag blocks kept          */
     constexpr int J = 16 / R;                         /* slice columns per thread */
+    constexpr int NOUT = (R == 1) ? 16 : NA * J;
     const int q = blockIdx.x, p = blockIdx.z, tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
     cg::cluster_group cluster = cg::this_cluster();
-    if (A.frozen_in[p]) return;                       /* whole cluster leaves     */
+    if (A.frozen[p]) return;                          /* whole cluster leaves     */
     int f = blockIdx.y, codei = 0;
     float maxp = 0.f;
-    if (A.mode == 1) {
+    if (MODE == 1) {
         const unsigned long long k = A.key[p];
         const unsigned int flat = k ? 0xffffffffu - (unsigned int)(k & 0xffffffffu) : 0u;
         f = (int)(flat / (unsigned int)A.n_eff);
         codei = (int)(flat - (unsigned int)f * (unsigned int)A.n_eff);
         maxp = __uint_as_float((unsigned int)(k >> 32));
     }
-    acq_sink_t sk;
-    sk.best = 0ull; sk.flat0 = (unsigned int)f * (unsigned int)A.n_eff;
-    sk.sum = 0.0; sk.cnt = 0; sk.max2 = -1.f;
-    sk.exs = codei - 2 * A.nsampchip; if (sk.exs < 0) sk.exs += A.n_eff;          /* src/sdracq.c:81-82 */
-    sk.exe = codei + 2 * A.nsampchip; if (sk.exe >= A.n_eff) sk.exe -= A.n_eff;
-    sk.Prow = A.P ? A.P + ((size_t)p * A.nfreq + f) * A.n_eff : nullptr;
-    sk.n_eff = A.n_eff; sk.mode = A.mode; sk.first_step = A.first_step;
-
-    if (A.mode == 1 && A.P) {
-        /* the accumulated row is in HBM: read this CTA's share of it */
-        for (int t = q * T + tid; t < A.n_eff; t += R * T) sk.put(t, sk.Prow[t]);
+    /* outputs of this thread in increasing lag order: pw[i] <-> lag tout(i) */
+    float pw[NOUT];
+    auto tout = [&](int i) -> int {
+        if (R == 1) return tid + i * T;
+        return q * (L / R) + tid + (i % J) * T + L * (i / J);
+    };
+    bool from_hbm = (MODE == 1 && A.P != nullptr);
+    if (from_hbm) {
+        /* the accumulated row is in HBM already: read this CTA's share of it */
+        const float *Prow = A.P + ((size_t)p * A.nfreq + f) * A.n_eff;
+#pragma unroll
+        for (int i = 0; i < NOUT; i++) { const int t = tout(i); pw[i] = (t < A.n_eff) ? Prow[t] : 0.f; }
     } else {
         const float2 *x = A.Xs + ((size_t)f * R + q) * L;
         const float2 *c = A.Cs + ((size_t)p * R + q) * L;
         float2 v[16];
+        float2 w[fft_plan_t<L>::N16];
+        cta_fft_twiddles<L>(A.tw, R, w);
 #pragma unroll
         for (int e = 0; e < 16; e++) v[e] = cmulc(__ldg(&x[tid + e * T]), __ldg(&c[tid + e * T]));
-        cta_fft<L, +1>(v, fsm, A.tw, R);
+        cta_fft_pre<L, +1>(v, fsm, w);
         if constexpr (R == 1) {
 #pragma unroll
-            for (int e = 0; e < 16; e++)
-                sk.put(tid + e * T, (v[e].x * v[e].x + v[e].y * v[e].y) * A.invM2);
+            for (int e = 0; e < 16; e++) pw[e] = (v[e].x * v[e].x + v[e].y * v[e].y) * A.invM2;
         } else {
-            /* z_q[t'] = W_M^(-t' q) y_q[t'] into own shared memory */
+            /* y_q[t'] into own shared memory; W_M^(-t' q) is applied by the reader */
 #pragma unroll
-            for (int e = 0; e < 16; e++) {
-                const int tp = tid + e * T;
-                float2 z = v[e];
-                if (q != 0) z = cmulc(z, __ldg(&A.tw[(q * tp) & (M - 1)]));
-                fsm[tp] = z;
-            }
-            cluster.sync();
+            for (int e = 0; e < 16; e++) fsm[tid + e * T] = v[e];
+            float2 wj[J];
+#pragma unroll
+            for (int j = 0; j < J; j++) wj[j] = __ldg(&A.tw[q * (L / R) + tid + j * T]);
+            cl_arrive_release();
+            cl_wait();
             const float2 *zs[R];
 #pragma unroll
             for (int r = 0; r < R; r++) zs[r] = cluster.map_shared_rank(fsm, r);
@@ -430,6 +512,13 @@ k_rowc(const acq_rowc_args A)
                 float2 z[R];
 #pragma unroll
                 for (int r = 0; r < R; r++) z[r] = zs[r][tp];
+                /* z_r *= W_M^(-t' r) = conj(w)^r */
+                float2 wp = wj[j];
+#pragma unroll
+                for (int r = 1; r < R; r++) {
+                    z[r] = cmulc(z[r], wp);
+                    if (r + 1 < R) wp = cmul(wp, wj[j]);
+                }
                 float2 y[NA];
                 if constexpr (R == 2) {
                     y[0] = cadd(z[0], z[1]);
@@ -448,14 +537,28 @@ k_rowc(const acq_rowc_args A)
                     y[3] = cadd(e3, cw16<+1, 6>(o3));
                 }
 #pragma unroll
-                for (int a = 0; a < NA; a++)
-                    sk.put(tp + L * a, (y[a].x * y[a].x + y[a].y * y[a].y) * A.invM2);
+                for (int a = 0; a < NA; a++) pw[a * J + j] = (y[a].x * y[a].x + y[a].y * y[a].y) * A.invM2;
             }
+            cl_arrive_relaxed();                      /* done with the peers' shared memory */
         }
     }
 
-    if (A.mode == 0) {
-        unsigned long long b = sk.best;
+    if (MODE == 0) {
+        float *Prow = A.P ? A.P + ((size_t)p * A.nfreq + f) * A.n_eff : nullptr;
+        float bv = -1.f; int bt = 0;
+#pragma unroll
+        for (int i = 0; i < NOUT; i++) {
+            const int t = tout(i);
+            if (t < A.n_eff) {
+                float x = pw[i];
+                if (Prow) { if (!A.first_step) x += Prow[t]; Prow[t] = x; }     /* cpxconv flagsum */
+                if (x > bv) { bv = x; bt = t; }
+            }
+        }
+        unsigned long long b = 0ull;
+        if (bv >= 0.f)
+            b = ((unsigned long long)__float_as_uint(bv) << 32) |
+                (unsigned long long)(0xffffffffu - ((unsigned int)f * (unsigned int)A.n_eff + (unsigned int)bt));
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
@@ -472,12 +575,23 @@ k_rowc(const acq_rowc_args A)
             }
             if (lane == 0 && b) atomicMax(&A.key[p], b);
         }
-        if (R > 1) cluster.sync();                    /* peers may still be reading fsm */
+        if (R > 1) cl_wait();                         /* peers may still be reading fsm */
         return;
     }
 
-    /* mode 1: reduce the masked statistics over the CTA, then over the cluster */
-    double sum = sk.sum; int cnt = sk.cnt; float m2 = sk.max2;
+    /* MODE 1: masked statistics around the known peak (src/sdracq.c:79-88) */
+    int exs = codei - 2 * A.nsampchip; if (exs < 0) exs += A.n_eff;
+    int exe = codei + 2 * A.nsampchip; if (exe >= A.n_eff) exe -= A.n_eff;
+    double sum = 0.0; int cnt = 0; float m2 = -1.f;
+#pragma unroll
+    for (int i = 0; i < NOUT; i++) {
+        const int t = tout(i);
+        if (t < A.n_eff) {
+            const bool inc = (exs <= exe) ? (t < exs || t > exe) : (t < exs && t > exe);
+            if (inc) { sum += (double)pw[i]; cnt++; }
+            if ((inc || t == 0) && pw[i] > m2) m2 = pw[i];          /* maxvd seeds with data[0] */
+        }
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         sum += __shfl_xor_sync(0xffffffffu, sum, o);
@@ -491,7 +605,9 @@ k_rowc(const acq_rowc_args A)
         for (int w = 1; w < nw; w++) { sum += s_part[w].sum; cnt += s_part[w].cnt; m2 = fmaxf(m2, s_part[w].max2); }
         s_cta.sum = sum; s_cta.cnt = cnt; s_cta.max2 = m2;
     }
-    cluster.sync();
+    if (R > 1 && !from_hbm) cl_wait();                /* closes the arrive.relaxed above */
+    cl_arrive_release();
+    cl_wait();
     if (q == 0 && tid == 0) {
         for (int r = 1; r < R; r++) {
             const acq_part_t *o = cluster.map_shared_rank(&s_cta, r);
@@ -509,7 +625,8 @@ k_rowc(const acq_rowc_args A)
         if (o.acquired) A.frozen[p] = 1;
         A.key[p] = 0ull;                                           /* next integration step */
     }
-    cluster.sync();
+    cl_arrive_relaxed();
+    cl_wait();
 }
 
 /* ------------------------------------------------------------- host side */
@@ -520,8 +637,9 @@ template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     dim3 grid(R, nitems);
     if (src_kind == 0) {
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd<L, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_fwd<L, 0><<<grid, L / 16, smem, st>>>(src, item_stride, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
+        const size_t smem2 = smem + 2 * (size_t)(3 * L + 32);
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_if<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+        k_fwd_if<L><<<grid, L / 16, smem2, st>>>(src, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
     } else {
         SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd<L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_fwd<L, 1><<<grid, L / 16, smem, st>>>(src, item_stride, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
@@ -544,10 +662,10 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
     return SDRB200_OK;
 }
 
-template <int L, int R> static int launch_rowc(cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
+template <int L, int R, int MODE> static int launch_rowc(cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
-    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowc<L, R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowc<L, R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(R, nfreq_grid, nprn);
     cfg.blockDim = dim3(L / 16, 1, 1);
@@ -557,14 +675,15 @@ template <int L, int R> static int launch_rowc(cudaStream_t st, const acq_rowc_a
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = R; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
-    SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_rowc<L, R>, A));
+    SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_rowc<L, R, MODE>, A));
     sdrb200_count_launch(1);
     return SDRB200_OK;
 }
 
-static int launch_rowc_any(int L, int R, cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
+static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
 {
-#define RC(LL, RR) if (L == LL && R == RR) return launch_rowc<LL, RR>(st, A, nfreq_grid, nprn);
+#define RC(LL, RR) if (L == LL && R == RR) return mode ? launch_rowc<LL, RR, 1>(st, A, nfreq_grid, nprn) \
+                                                       : launch_rowc<LL, RR, 0>(st, A, nfreq_grid, nprn);
     RC(512, 1) RC(1024, 1) RC(2048, 1) RC(4096, 1)
     RC(1024, 2) RC(2048, 2) RC(4096, 2) RC(8192, 2) RC(16384, 2)
     RC(1024, 4) RC(2048, 4) RC(4096, 4) RC(8192, 4) RC(16384, 4)
@@ -646,7 +765,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
         cudaGetLastError(); sdrb200_set_error("acq_create: cudaMalloc(%zu) failed", (size_t)(bytes)); rc = SDRB200_ENOMEM; }
     if (cudaStreamCreateWithFlags(&a->st, cudaStreamNonBlocking) != cudaSuccess) rc = SDRB200_ECUDA;
     ACQ_ALLOC(a->d_tw, sizeof(float2) * M);
-    ACQ_ALLOC(a->d_cidx, (size_t)nfreq * a->m_ref);
+    ACQ_ALLOC(a->d_cidx, (size_t)nfreq * M);                    /* row stride M: 16-byte aligned rows */
     ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)nfreq * M);
     ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
     if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * nfreq * M);
@@ -676,7 +795,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
      * (src/sdrcmn.c:761) has phi0 = 0 and a fixed grid, so the index sequence is a
      * constant of the configuration; it is generated with the exact NCO replay. */
     {
-        uint8_t *h = (uint8_t *)malloc((size_t)nfreq * a->m_ref);
+        uint8_t *h = (uint8_t *)calloc((size_t)nfreq, (size_t)M);
         nco_table_t *tb = (nco_table_t *)malloc(sizeof(nco_table_t));
         const double ti = 1 / cfg->f_sf;
         for (int f = 0; f < nfreq && rc == SDRB200_OK; f++) {
@@ -684,11 +803,11 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
             nco_carrier_init(a->h_freq[f], 0.0, ti, &phi, &ps);
             if (nco_walk(phi, ps, a->m_ref, 0.0, tb)) { sdrb200_set_error("acq_create: NCO table overflow"); rc = SDRB200_ERANGE; break; }
             int32_t hint = 0;
-            uint8_t *row = h + (size_t)f * a->m_ref;
+            uint8_t *row = h + (size_t)f * M;
             for (int t = 0; t < a->m_ref; t++) row[t] = (uint8_t)(((int)nco_value(tb, t, &hint)) & SDRB200_CMASK);
         }
         if (rc == SDRB200_OK) {
-            cudaMemcpyAsync(a->d_cidx, h, (size_t)nfreq * a->m_ref, cudaMemcpyHostToDevice, a->st);
+            cudaMemcpyAsync(a->d_cidx, h, (size_t)nfreq * M, cudaMemcpyHostToDevice, a->st);
             cudaMemcpyAsync(a->d_freq, a->h_freq, sizeof(double) * nfreq, cudaMemcpyHostToDevice, a->st);
             cudaStreamSynchronize(a->st);
         }
@@ -781,24 +900,22 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         const int8_t *win = base + pos * c->dtype;
         ACQ_T0(a);
         ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
-                                             a->m_ref, scale, a->d_tw, a->d_Xs)));
+                                             a->M, scale, a->d_tw, a->d_Xs)));
         if (rc) return rc;
         ACQ_T1(a, 0);
         if (a->fused) {
             acq_rowc_args A;
             A.Xs = a->d_Xs; A.Cs = a->d_Cs; A.tw = a->d_tw; A.P = a->d_P; A.key = a->d_key;
-            A.frozen_in = a->d_frozen; A.frozen = a->d_frozen; A.res = a->d_res; A.freq = a->d_freq;
+            A.frozen = a->d_frozen; A.res = a->d_res; A.freq = a->d_freq;
             A.ctime = c->ctime; A.thresh = c->threshold; A.nfreq = c->nfreq; A.n_eff = a->n_eff;
             A.nsampchip = c->nsampchip; A.first_step = (step == 0); A.step = step;
             A.invM2 = 1.0f / ((float)a->M * (float)a->M);
-            A.mode = 0;
             ACQ_T0(a);
-            rc = launch_rowc_any(a->L, a->R, a->st, A, c->nfreq, c->nprn);
+            rc = launch_rowc_any(a->L, a->R, 0, a->st, A, c->nfreq, c->nprn);
             if (rc) return rc;
             ACQ_T1(a, 1);
-            A.mode = 1;
             ACQ_T0(a);
-            rc = launch_rowc_any(a->L, a->R, a->st, A, 1, c->nprn);
+            rc = launch_rowc_any(a->L, a->R, 1, a->st, A, 1, c->nprn);
             if (rc) return rc;
             ACQ_T1(a, 3);
             continue;
@@ -840,7 +957,7 @@ extern "C" int sdrb200_acq_enqueue(sdrb200_acq_t *a, const sdrb200_stream_t *s, 
                           (unsigned long long)buffloc0, (unsigned long long)need, (unsigned long long)s->count);
         return SDRB200_ERANGE;
     }
-    if ((size_t)a->m_ref * a->cfg.dtype > SDRB200_STREAM_GUARD) { sdrb200_set_error("acq_run: window exceeds the ring guard"); return SDRB200_EINVAL; }
+    if ((size_t)a->m_ref * a->cfg.dtype + 32 > SDRB200_STREAM_GUARD) { sdrb200_set_error("acq_run: window exceeds the ring guard"); return SDRB200_EINVAL; }
     return acq_steps(a, s->d_buf, s->capacity, buffloc0);
 }
 

@@ -136,14 +136,34 @@ template <int L> struct fft_plan_t {
 /* L-point transform by the whole CTA (blockDim.x == L/16).
  * tw: forward twiddles exp(-2*pi*i*k/N) for a table of N = L*tw_stride entries
  * sm: FFT_SMEM_ELEMS(L) float2 of shared memory
- * Contains __syncthreads(); must be called by all threads of the CTA.         */
+ * Contains __syncthreads(); must be called by all threads of the CTA.
+ * The per-pass base twiddles depend on the thread index only; cta_fft_twiddles
+ * fetches them so that a caller can issue the loads early (together with its
+ * own operand loads) and cta_fft_pre consumes them.                            */
+template <int L>
+__device__ __forceinline__ void cta_fft_twiddles(const float2 *__restrict__ tw, int tw_stride,
+                                                 float2 (&w)[fft_plan_t<L>::N16])
+{
+    using P = fft_plan_t<L>;
+    const int tid = threadIdx.x;
+    int s = 1;
+#pragma unroll
+    for (int pass = 0; pass < P::N16; pass++) {
+        const int ps = tid - (tid & (s - 1));
+        if (!((pass == P::N16 - 1) && (P::RL == 1))) w[pass] = __ldg(&tw[(size_t)ps * tw_stride]);
+        else w[pass] = make_float2(1.f, 0.f);
+        s *= 16;
+    }
+}
+
 template <int L, int SIGN>
-__device__ __forceinline__ void cta_fft(float2 (&v)[16], float2 *sm, const float2 *__restrict__ tw,
-                                        int tw_stride)
+__device__ __forceinline__ void cta_fft_pre(float2 (&v)[16], float2 *sm, const float2 (&w)[fft_plan_t<L>::N16])
 {
     using P = fft_plan_t<L>;
     constexpr int T = P::T;
     const int tid = threadIdx.x;
+    /* gather address of element e: FFT_PAD(tid + e*T) = gbase + e*(T + T/16), T % 16 == 0 */
+    float2 *const gbase = sm + tid + (tid >> 4);
     int s = 1;
 #pragma unroll
     for (int pass = 0; pass < P::N16; pass++) {
@@ -152,8 +172,9 @@ __device__ __forceinline__ void cta_fft(float2 (&v)[16], float2 *sm, const float
         if (!last) {
             const int q = tid & (s - 1);
             const int ps = tid - q;                               /* p*s */
-            if (ps != 0) {
-                float2 w1 = __ldg(&tw[(size_t)ps * tw_stride]);
+            {
+                /* unconditional: threads with ps == 0 multiply by 1 (no divergent path) */
+                float2 w1 = w[pass];
                 if (SIGN > 0) w1.y = -w1.y;
                 float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1), w4 = cmul(w2, w2);
                 float2 w5 = cmul(w4, w1), w6 = cmul(w3, w3), w7 = cmul(w4, w3), w8 = cmul(w4, w4);
@@ -164,18 +185,30 @@ __device__ __forceinline__ void cta_fft(float2 (&v)[16], float2 *sm, const float
                 float2 w13 = cmul(w8, w5), w14 = cmul(w7, w7), w15 = cmul(w8, w7);
                 v[13] = cmul(v[13], w13); v[14] = cmul(v[14], w14); v[15] = cmul(v[15], w15);
             }
-            /* scatter: y[q + s*(16p + u)] */
-            const int base = q + 16 * ps;
+            /* scatter: y[q + s*(16p + u)]; with idx = q + 16*ps + s*u and q < s:
+             * s == 1:  FFT_PAD(idx) = 17*tid + u
+             * s >= 16: FFT_PAD(idx) = q + (q >> 4) + 17*ps + u*(s + s/16)        */
+            float2 *const sbase = sm + ((s == 1) ? 17 * tid : q + (q >> 4) + 17 * ps);
+            const int sstep = (s == 1) ? 1 : s + s / 16;
 #pragma unroll
-            for (int u = 0; u < 16; u++) sm[FFT_PAD(base + s * u)] = v[u];
+            for (int u = 0; u < 16; u++) sbase[sstep * u] = v[u];
             __syncthreads();
 #pragma unroll
-            for (int e = 0; e < 16; e++) v[e] = sm[FFT_PAD(tid + e * T)];
+            for (int e = 0; e < 16; e++) v[e] = gbase[e * (T + T / 16)];
             __syncthreads();
         }
         s *= 16;
     }
     if (P::RL > 1) fft_tail<SIGN, P::RL>(v);
+}
+
+template <int L, int SIGN>
+__device__ __forceinline__ void cta_fft(float2 (&v)[16], float2 *sm, const float2 *__restrict__ tw,
+                                        int tw_stride)
+{
+    float2 w[fft_plan_t<L>::N16];
+    cta_fft_twiddles<L>(tw, tw_stride, w);
+    cta_fft_pre<L, SIGN>(v, sm, w);
 }
 
 #endif
