@@ -149,77 +149,95 @@ k_fwd(const int8_t *__restrict__ src, size_t item_stride, int dtype, int nlive,
 
 /* forward transform of the IF window for one (Doppler bin, q): mixcarr + cpxcpx
  * (src/sdrcmn.c:650-662, 185-195) fused into the residue-class sums of the
- * four-step transform.  The window is walked in R blocks of L samples; every
- * block (samples and carrier-table indices) is fetched with 16-byte loads, one
- * block ahead of its use, and re-read per thread from shared memory.  The 32-entry
- * carrier table x input scale x W_R^(a q) is held one entry per lane, so a lookup
- * is a shuffle and a sample costs two FMAs.                                     */
-template <int L>
+ * four-step transform.  The window is walked in R blocks of L samples.  In this
+ * phase a thread owns 16 CONSECUTIVE samples of the block: its samples and their
+ * carrier-table indices arrive as 16-byte loads (fetched one block ahead) and are
+ * picked apart in registers.  The 32-entry carrier table x input scale x W_R^(a q)
+ * is held one entry per lane, so a lookup is a shuffle and a sample costs two
+ * FMAs.  One pass through shared memory then hands the sums over in the order
+ * the CTA transform wants (element e of thread tid <-> b = tid + e*T).          */
+__device__ __forceinline__ int acq_sbyte(unsigned int w, int j)      /* sign-extended byte j */
+{
+    return (int)(w << (24 - 8 * j)) >> 24;
+}
+
+template <int L, int DT>
 __global__ void __launch_bounds__(L / 16, (L <= 4096) ? 4 : (L <= 8192 ? 2 : 1))
-k_fwd_if(const int8_t *__restrict__ win, int dtype, int nlive, const uint8_t *__restrict__ cidx,
+k_fwd_if(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict__ cidx,
          int cidx_stride, float scale, const float2 *__restrict__ tw, int R, float2 *__restrict__ out)
 {
     extern __shared__ float2 fsm[];
     constexpr int T = L / 16;
+    constexpr int NW = 4 * DT;                            /* sample words per thread and block */
     const int q = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
-    /* staging behind the FFT buffer: 2 x (samples: 2L + 32 bytes, indices: L bytes) */
-    unsigned char *stage = (unsigned char *)(fsm + FFT_SMEM_ELEMS(L));
-    constexpr int SD = 2 * L + 32, SB = SD + L;
     const size_t g = (size_t)win;
-    const int off = (int)(g & 15);
+    const int off = (int)(g & 15), wo = off >> 2, bo8 = 8 * (off & 3);
     const uint4 *wal = (const uint4 *)(g - off);
     const uint4 *cal = (const uint4 *)(cidx + (size_t)f * cidx_stride);
-    const int live_bytes = nlive * dtype + off;           /* relative to wal          */
-    const int nd = L * dtype / 16;                        /* sample chunks per block  */
+    const int live_bytes = nlive * DT + off;              /* relative to wal */
     const float lut_c = c_cosf[tid & 31] * scale, lut_s = c_sinf[tid & 31] * scale;
     const uint4 zero4 = make_uint4(0u, 0u, 0u, 0u);
-    uint4 pd0, pd1, pd2, pi;
+    uint4 pd[DT + 1], pi;
     auto fetch = [&](int a) {
-        /* chunks a*nd + {tid, tid + T, (tid == 0) nd}: L*dtype + 16 bytes cover the
-         * misalignment; anything past the live window reads as zero                */
-        const int c0 = a * nd + tid;
-        pd0 = (c0 * 16 < live_bytes) ? __ldg(&wal[c0]) : zero4;
-        pd1 = (dtype == 2 && (c0 + T) * 16 < live_bytes) ? __ldg(&wal[c0 + T]) : zero4;
-        pd2 = (tid == 0 && (a * nd + nd) * 16 < live_bytes) ? __ldg(&wal[a * nd + nd]) : zero4;
+        /* chunks (a*T + tid)*DT + {0..DT}: the extra one covers the misalignment;
+         * anything past the live window reads as zero                              */
+        const int c0 = (a * T + tid) * DT;
+#pragma unroll
+        for (int i = 0; i <= DT; i++) pd[i] = ((c0 + i) * 16 < live_bytes) ? __ldg(&wal[c0 + i]) : zero4;
         pi = ((a * T + tid) * 16 < nlive) ? __ldg(&cal[a * T + tid]) : zero4;
     };
-    float2 v[16];
+    float2 u[16];
 #pragma unroll
-    for (int e = 0; e < 16; e++) v[e] = make_float2(0.f, 0.f);
+    for (int k = 0; k < 16; k++) u[k] = make_float2(0.f, 0.f);
     const int nblk = (nlive + L - 1) / L;                  /* blocks that hold samples */
     fetch(0);
     for (int a = 0; a < nblk; a++) {
-        unsigned char *sd = stage + (a & 1) * SB, *si = sd + SD;
-        ((uint4 *)sd)[tid] = pd0;
-        if (dtype == 2) ((uint4 *)sd)[tid + T] = pd1;
-        if (tid == 0) ((uint4 *)sd)[nd] = pd2;
-        ((uint4 *)si)[tid] = pi;
-        __syncthreads();
+        /* realign: drop `off` bytes from the front of the DT+1 chunks */
+        unsigned int w[4 * (DT + 1) + 1];
+#pragma unroll
+        for (int i = 0; i <= DT; i++) { w[4 * i] = pd[i].x; w[4 * i + 1] = pd[i].y; w[4 * i + 2] = pd[i].z; w[4 * i + 3] = pd[i].w; }
+        w[4 * (DT + 1)] = 0u;
+        unsigned int t2[NW + 2], t1[NW + 1], sw[NW];
+#pragma unroll
+        for (int i = 0; i < NW + 2; i++) t2[i] = (wo & 2) ? w[i + 2] : w[i];
+#pragma unroll
+        for (int i = 0; i < NW + 1; i++) t1[i] = (wo & 1) ? t2[i + 1] : t2[i];
+#pragma unroll
+        for (int i = 0; i < NW; i++) sw[i] = __funnelshift_r(t1[i], t1[i + 1], bo8);
+        const unsigned int iw[4] = {pi.x, pi.y, pi.z, pi.w};
+        const int tb = L * a + 16 * tid;                   /* first sample of this thread */
         if (a + 1 < nblk) fetch(a + 1);
         const float2 wa = (a != 0 && q != 0) ? __ldg(&tw[(size_t)((a * q) % R) * L]) : make_float2(1.f, 0.f);
         const float2 g2 = cmul(make_float2(lut_c, lut_s), wa);
-        const signed char *sds = (const signed char *)sd + off;
 #pragma unroll
-        for (int e = 0; e < 16; e++) {
-            const int b = tid + e * T;
-            const bool live = L * a + b < nlive;
-            const int idx = si[b];
+        for (int k = 0; k < 16; k++) {
+            const int idx = (int)((iw[k >> 2] >> (8 * (k & 3))) & 0xffu);
             const float gx = __shfl_sync(0xffffffffu, g2.x, idx), gy = __shfl_sync(0xffffffffu, g2.y, idx);
-            if (dtype == 1) {
-                const float f0 = live ? (float)sds[b] : 0.f;
-                v[e].x = fmaf(f0, gx, v[e].x); v[e].y = fmaf(f0, gy, v[e].y);
+            const bool live = tb + k < nlive;
+            if (DT == 1) {
+                const float f0 = live ? (float)acq_sbyte(sw[k >> 2], k & 3) : 0.f;
+                u[k].x = fmaf(f0, gx, u[k].x); u[k].y = fmaf(f0, gy, u[k].y);
             } else {                                       /* (s0 + i s1) * g */
-                const float f0 = live ? (float)sds[2 * b] : 0.f, f1 = live ? (float)sds[2 * b + 1] : 0.f;
-                v[e].x = fmaf(f0, gx, v[e].x); v[e].y = fmaf(f0, gy, v[e].y);
-                v[e].x = fmaf(-f1, gy, v[e].x); v[e].y = fmaf(f1, gx, v[e].y);
+                const unsigned int ww = sw[k >> 1];
+                const float f0 = live ? (float)acq_sbyte(ww, 2 * (k & 1)) : 0.f;
+                const float f1 = live ? (float)acq_sbyte(ww, 2 * (k & 1) + 1) : 0.f;
+                u[k].x = fmaf(f0, gx, u[k].x); u[k].y = fmaf(f0, gy, u[k].y);
+                u[k].x = fmaf(-f1, gy, u[k].x); u[k].y = fmaf(f1, gx, u[k].y);
             }
         }
     }
+    /* hand over: u[k] <-> b = 16*tid + k  ->  v[e] <-> b = tid + e*T */
+#pragma unroll
+    for (int k = 0; k < 16; k++) fsm[17 * tid + k] = u[k];            /* FFT_PAD(16*tid + k) */
+    __syncthreads();
+    float2 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = fsm[FFT_PAD(tid + e * T)];
+    __syncthreads();
     if (q != 0) {
 #pragma unroll
         for (int e = 0; e < 16; e++) v[e] = cmul(v[e], __ldg(&tw[(size_t)(tid + e * T) * q]));
     }
-    __syncthreads();
     cta_fft<L, -1>(v, fsm, tw, R);
     float2 *o = out + ((size_t)f * R + q) * L;
 #pragma unroll
@@ -498,10 +516,14 @@ k_rowc(const acq_rowc_args A)
             /* y_q[t'] into own shared memory; W_M^(-t' q) is applied by the reader */
 #pragma unroll
             for (int e = 0; e < 16; e++) fsm[tid + e * T] = v[e];
+            /* publish: CTA barrier, then ONE thread issues the cluster-scope release fence
+             * (every thread doing it costs a memory barrier per warp), relaxed arrive by all */
+            __syncthreads();
+            if (tid == 0) asm volatile("fence.acq_rel.cluster;" ::: "memory");
+            cl_arrive_relaxed();
             float2 wj[J];
 #pragma unroll
             for (int j = 0; j < J; j++) wj[j] = __ldg(&A.tw[q * (L / R) + tid + j * T]);
-            cl_arrive_release();
             cl_wait();
             const float2 *zs[R];
 #pragma unroll
@@ -637,9 +659,13 @@ template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     dim3 grid(R, nitems);
     if (src_kind == 0) {
-        const size_t smem2 = smem + 2 * (size_t)(3 * L + 32);
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_if<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-        k_fwd_if<L><<<grid, L / 16, smem2, st>>>(src, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
+        if (dtype == 1) {
+            SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_if<L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_fwd_if<L, 1><<<grid, L / 16, smem, st>>>(src, nlive, cidx, cidx_stride, scale, tw, R, out);
+        } else {
+            SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_if<L, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_fwd_if<L, 2><<<grid, L / 16, smem, st>>>(src, nlive, cidx, cidx_stride, scale, tw, R, out);
+        }
     } else {
         SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd<L, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_fwd<L, 1><<<grid, L / 16, smem, st>>>(src, item_stride, dtype, nlive, cidx, cidx_stride, scale, tw, R, out);
