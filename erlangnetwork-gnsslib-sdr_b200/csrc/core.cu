@@ -304,3 +304,57 @@ extern "C" int sdrb200_l2_flush(void *cuda_stream)
     SDRB200_CUDA_TRY(cudaMemsetAsync(g_flush_buf, ++v & 0xff, k_flush_bytes, (cudaStream_t)cuda_stream));
     return SDRB200_OK;
 }
+
+/* issue-rate micro-benchmarks for the ALU rooflines of DESIGN.md: 8 independent
+ * chains per thread of fp32 FMA (kind 0) or int32 multiply-add (kind 1), every
+ * SM filled; returns operations per second counting one FMA / one MAD as 2 ops */
+template <int KIND>
+__global__ void __launch_bounds__(256) k_alu_peak(float *out, int iters, float a, int ia)
+{
+    float f[8]; int n[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { f[i] = (float)(threadIdx.x + i); n[i] = threadIdx.x + i; }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 16; r++)
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (KIND == 0) f[i] = fmaf(f[i], a, 1.0f);
+                else n[i] = n[i] * ia + 1;
+            }
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += (KIND == 0) ? f[i] : (float)n[i];
+    if (s == 12345.678f) out[0] = s;                     /* keeps the chains alive */
+}
+
+extern "C" int sdrb200_alu_peak(int kind, double *ops_per_s)
+{
+    if (!ops_per_s || (kind != 0 && kind != 1)) return SDRB200_EINVAL;
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    cudaDeviceProp pr; int dev = 0;
+    SDRB200_CUDA_TRY(cudaGetDevice(&dev));
+    SDRB200_CUDA_TRY(cudaGetDeviceProperties(&pr, dev));
+    float *d = NULL;
+    SDRB200_CUDA_TRY(cudaMalloc(&d, 64));
+    cudaEvent_t e0, e1;
+    SDRB200_CUDA_TRY(cudaEventCreate(&e0)); SDRB200_CUDA_TRY(cudaEventCreate(&e1));
+    const int grid = pr.multiProcessorCount * 8, iters = 1024;
+    double best = 0.0;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(e0, 0);
+        if (kind == 0) k_alu_peak<0><<<grid, 256>>>(d, iters, 0.999f, 3);
+        else k_alu_peak<1><<<grid, 256>>>(d, iters, 0.999f, 3);
+        cudaEventRecord(e1, 0);
+        cudaEventSynchronize(e1);
+        float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1);
+        const double ops = 2.0 * (double)grid * 256.0 * (double)iters * 16.0 * 8.0 / (ms * 1e-3);
+        if (rep > 0 && ops > best) best = ops;
+    }
+    sdrb200_count_launch(4);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    *ops_per_s = best;
+    return SDRB200_OK;
+}

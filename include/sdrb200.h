@@ -48,6 +48,9 @@ void sdrb200_evt_destroy(void *evt);
 int  sdrb200_evt_record(void *evt, void *cuda_stream);
 int  sdrb200_evt_elapsed_ms(void *start, void *stop, float *ms);  /* waits for stop */
 int  sdrb200_l2_flush(void *cuda_stream);
+/* issue-rate micro-benchmark for the ALU rooflines: kind 0 fp32 FMA, kind 1 int32
+ * multiply-add; operations per second, one FMA / MAD counted as 2 operations   */
+int  sdrb200_alu_peak(int kind, double *ops_per_s);
 int  sdrb200_device_sync(void);
 
 /* code types: same numeric values as the reference (src/sdr.h:205-212)      */
