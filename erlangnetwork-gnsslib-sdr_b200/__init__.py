@@ -107,3 +107,4 @@ def loop_coeffs(dllb: float, pllb: float, fllb: float) -> Loop:
 
 
 from .host import *  # noqa: E402,F401,F403  (convenience wrappers)
+from . import shard  # noqa: E402,F401

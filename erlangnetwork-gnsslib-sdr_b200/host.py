@@ -201,6 +201,7 @@ class Acquisition:
         assert self.codes.ndim == 2
         self.nprn, clen = self.codes.shape
         self.nsamp, self.nfreq = nsamp, len(self.freq)
+        self.n_eff = nsamp * max(int(ncoh), 1)               # lags per row (coherent block length)
         cfg = AcqCfg(f_sf=f_sf, dtype=dtype, nsamp=nsamp, nsampchip=nsampchip, ctime=ctime,
                      nfreq=len(self.freq), freq=_p(self.freq, _dp), nprn=self.nprn, clen=clen,
                      crate=crate, codes=_p(self.codes, _i8p), intg=intg, ncoh=ncoh, threshold=threshold)
@@ -238,9 +239,9 @@ class Acquisition:
         return self._results(res)
 
     def power(self, prn_index: int) -> np.ndarray:
-        out = np.zeros(self.nfreq * self.nsamp)
+        out = np.zeros(self.nfreq * self.n_eff)
         check(lib.sdrb200_acq_power(self.h, int(prn_index), _p(out, _dp)), "acq_power")
-        return out.reshape(self.nfreq, self.nsamp)
+        return out.reshape(self.nfreq, self.n_eff)
 
     @property
     def cuda_stream(self) -> int:
