@@ -309,21 +309,35 @@ def run_b200(args):
     host_pin = torch.empty(need, dtype=torch.int8, pin_memory=True)
     host_np = host_pin.numpy()
     host_np[:] = st.read(b0, need)
-    tuples = None
+    # result tuples land in pinned host memory; at N > 1 they go straight back to the GPU
+    # for one NCCL all-gather of the per-shard tuples (north_star: the only collective)
+    rbytes = NPRN * C.sizeof(sdr.AcqResult)
+    res_pin = torch.empty(rbytes, dtype=torch.uint8, pin_memory=True)
+    res_ptr = C.cast(res_pin.data_ptr(), C.POINTER(sdr.AcqResult))
+    host_ptr = C.cast(host_pin.data_ptr(), C.POINTER(C.c_int8))
+    if dist is not None:
+        res_dev = torch.empty(rbytes, dtype=torch.uint8, device="cuda")
+        res_all = torch.empty(world * rbytes, dtype=torch.uint8, device="cuda")
+
+    def e2e_step():
+        sdr.check(lib.sdrb200_acq_run_host(acq.h, host_ptr, C.c_uint64(need), res_ptr), "acq_run_host")
+        if dist is not None:
+            res_dev.copy_(res_pin, non_blocking=True)
+            dist.all_gather_into_tensor(res_all, res_dev)
+            torch.cuda.synchronize()
+
     for _ in range(max(W, 3)):
-        r2 = acq.run_host(host_np, need)
+        e2e_step()
     barrier()
     t0 = time.perf_counter()
     for _ in range(K):
-        r2 = acq.run_host(host_np, need)
-        if dist is not None:
-            t = torch.tensor([[r["acquired"], r["freqi"], r["codei"], r["peakr"], r["cn0"]] for r in r2],
-                             dtype=torch.float64, device="cuda")
-            tuples = [torch.empty_like(t) for _ in range(world)]
-            dist.all_gather(tuples, t)                   # NCCL over NVLink: per-shard peak tuples
-            torch.cuda.synchronize()
+        e2e_step()
     barrier()
     t_e2e = time.perf_counter() - t0
+    r2 = acq._results((sdr.AcqResult * NPRN).from_buffer_copy(bytes(res_pin.numpy())))
+    if dist is not None:
+        mine = res_all.cpu().numpy()[rank * rbytes:(rank + 1) * rbytes]
+        assert bytes(mine) == bytes(res_pin.numpy()), "gathered tuples differ from the local shard"
     assert [(r["acquired"], r["freqi"], r["codei"]) for r in r2] == \
            [(r["acquired"], r["freqi"], r["codei"]) for r in res], "host-buffer path disagrees with resident path"
 
@@ -438,7 +452,7 @@ def run_b200(args):
         "tracking": trk_obj,
     }
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -485,10 +499,29 @@ def run_reference(args):
         "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """stdout carries exactly ONE JSON line: everything libraries print on fd 1 (NCCL's
+    version banner, for one) is sent to stderr; emit() writes to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def main():
+    guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
