@@ -58,8 +58,13 @@ def main():
 
     # ---- codes: every L1CA/SBAS PRN and the G1 code, packed to bits ---------------
     codes = np.stack([o.gencode(p, 1)[0] for p in range(1, 211)])
-    np.savez_compressed(os.path.join(HERE, "codes.npz"), l1ca=np.packbits(codes > 0, axis=1))
-    # (the reference cannot emit G1: gencode() has no CTYPE_G1 case, src/sdrcode.c:523-539)
+    # G1: gencode() has no CTYPE_G1 case in this fork (src/sdrcode.c:523-539); the static
+    # generator gencode_G1G2 (src/sdrcode.c:426-444) is reached through oracle/g1_wrap.c
+    import ctypes as C
+    g1 = np.zeros(511, np.int16)
+    cr = C.c_double()
+    assert o.lib.oh_gencode_g1_static(g1.ctypes.data_as(C.POINTER(C.c_short)), C.byref(cr)) == 511 and cr.value == 0.511e6
+    np.savez_compressed(os.path.join(HERE, "codes.npz"), l1ca=np.packbits(codes > 0, axis=1), g1=g1.astype(np.int8))
 
     # ---- FFT-domain primitives on small, non power-of-two sizes ---------------------
     f = {}

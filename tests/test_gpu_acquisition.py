@@ -138,3 +138,43 @@ def test_acq_coherent_blocks_scratch_path(sdr, oracle):
     # a multi-period replica repeats its peak every code period, so the peak RATIO is ~1.2 by
     # construction; what must hold is the Doppler bin of the visible PRN
     assert got[0]["freqi"] == 4 and got[0]["maxp"] > 5 * got[1]["maxp"]
+
+
+def test_acq_glonass_g1_fdma(sdr):
+    """config 3 style: GLONASS G1 (511 chips, FDMA channels k * 562.5 kHz), I/Q at 20 MS/s,
+    10 non-coherent integrations; M = 65536 = 8 x 8192 (cluster of 8 CTAs of 512 threads).
+    This fork's gencode() has no CTYPE_G1 case (src/sdrcode.c:523-539), so the reference
+    build cannot run the channel; the oracle here is the port, whose G1 code is pinned to
+    the reference's static gencode_G1G2 (tests/test_oracle_port.py) and whose acquisition
+    is pinned bit-for-bit to the reference on L1CA."""
+    if not ob.have_port():
+        pytest.skip("oracle port not built")
+    oracle = ob.port()
+    fs, nsamp = 20.0e6, 20000
+    rng = np.random.default_rng(0xB2000003)
+    chans = [-1, 0, 2]                                   # frequency numbers present
+    sats = [dict(prn=1, cn0=float(rng.uniform(44, 47)), doppler=k * 562500.0 + float(rng.uniform(-3000, 3000)),
+                 code_phase=float(rng.uniform(0, 511 * 10)), carr_phase=float(rng.uniform(0, 1)), rate=0.0,
+                 nav_on=0) for k in chans]
+    cfg = sdr.make_ifgen(fs, 0.0, 1.602e9, 2, sats, sigma=2.5, seed=0xB2000003, crate=0.511e6, clen=511, bitlen=10)
+    intg = 10
+    need = (intg + 1) * nsamp
+    avail = 65536 * (need // 65536 + 1)                 # whole front-end blocks, src/sdrrcv.c:469-495
+    st = sdr.Stream(2, avail)
+    st.push_ifgen(cfg, avail)
+    host = st.read(0, avail)
+    cfgo = ob.OhCfg(f_sf=fs, f_if=0.0, f_cf=1.602e9, dtype=2, corrn=4, corrd=1, corrp=1)
+    cfgo.dllb[:] = [5.0, 2.0]; cfgo.pllb[:] = [30.0, 20.0]; cfgo.fllb[:] = [200.0, 50.0]
+    ks = chans + [4]                                     # one absent channel
+    ref, _ = oracle.acquire(cfgo, host, avail, ks, ctypes=[20] * len(ks))
+    code, crate = sdr.gencode(1, 20)
+    assert len(code) == 511 and crate == 0.511e6
+    b0 = avail - need
+    for k, r in zip(ks, ref):
+        freq = np.array([0.0 + (i - 35) * 200.0 + 562500.0 * k for i in range(71)])      # src/sdrinit.c:633-635
+        acq = sdr.Acquisition(fs, 2, nsamp, int(nsamp / 511), 1e-3, freq, code[None, :], crate, intg=intg)
+        g = acq.run(st, b0)[0]
+        assert (r.acquired, r.freqi, r.codei, r.nintg_used) == (g["acquired"], g["freqi"], g["codei"], g["nintg"]), (k, g)
+        assert abs(r.peakr - g["peakr"]) <= 1e-3 * r.peakr and abs(r.cn0 - g["cn0"]) <= 0.01
+        assert r.acqfreq == g["acqfreq"]
+    assert [r.acquired for r in ref] == [1, 1, 1, 0]

@@ -56,6 +56,8 @@ def test_port_codes_golden(port):
     assert len(code) == 511 and crate == 0.511e6 and abs(int(code.sum())) == 1
     ac = np.array([np.dot(code, np.roll(code, k)) for k in range(1, 511)])
     assert np.all(ac == -1)                              # two-valued autocorrelation of an m-sequence
+    # the reference's static gencode_G1G2 (src/sdrcode.c:426-444), reached via oracle/g1_wrap.c
+    assert np.array_equal(code, g["g1"].astype(np.int16))
 
 
 def test_port_fft_primitives_golden(port):
