@@ -265,20 +265,196 @@ NCO_HD int64_t nco_iseg_trunc(const nco_iseg_t *s, int32_t k)
     return s->neg ? -t : t;
 }
 
+/* ---- integer walker ----------------------------------------------------------
+ * Same sequence as nco_walk, but the interior of a binade is handled on the 53-bit
+ * mantissas: with M(x) = |x| / ulp(binade), a steady run is M1 + j*D with the integer
+ * D = M(x2) - M(x1) taken from two REAL additions (so the rounding of the increment,
+ * including an exact tie, is whatever the hardware did), the run length is one
+ * integer division (float estimate + exact correction) and the step that leaves
+ * the binade is again a real addition.  Segments come out directly in integer form. */
+#define NCO_MANT(b) (((b) & 0x000FFFFFFFFFFFFFULL) | 0x0010000000000000ULL)
+
+NCO_HD uint32_t nco_udiv_est(uint64_t num, uint64_t den, uint32_t cap)
+{
+    /* floor(num / den) clamped to cap; den > 0 */
+#ifdef __CUDA_ARCH__
+    float q = __fdividef(__ull2float_rz(num), __ull2float_ru(den));
+#else
+    float q = (float)num / (float)den;
+#endif
+    uint64_t J;
+    int64_t r;
+    if (q >= (float)cap) {
+        /* cap * den may not fit: compare through the quotient side */
+        if (num / den >= cap) return cap;               /* rare: exact division */
+        J = num / den;
+        return (uint32_t)J;
+    }
+    J = (uint64_t)q;
+    r = (int64_t)(num - J * den);
+    while (r < 0) { J--; r += (int64_t)den; }
+    while (r >= (int64_t)den) { J++; r -= (int64_t)den; }
+    return J > cap ? cap : (uint32_t)J;
+}
+
+/* further steps a steady run can take from mantissa M1 (exponent field ex, sign of
+ * the values irrelevant) with signed mantissa increment D before it leaves its binade
+ * or violates the limit (limit_on 1: value < limit for growing positive values,
+ * 2: value > limit for shrinking positive values), clamped to maxj                */
+NCO_HD int32_t nco_ijump(uint64_t M1, int64_t D, int ex, int positive, int limit_on, double limit, int32_t maxj)
+{
+    uint64_t num;
+    if (maxj <= 0) return 0;
+    if (D == 0) return maxj;
+    if (D > 0) {
+        uint64_t Xmax = 0x001FFFFFFFFFFFFFULL;
+        if (limit_on == 1 && positive) {
+            const uint64_t bl = nco_bits(limit);
+            if ((int)((bl >> 52) & 0x7FF) == ex) { const uint64_t ml = NCO_MANT(bl) - 1; if (ml < Xmax) Xmax = ml; }
+        }
+        num = Xmax - M1;
+        return (int32_t)nco_udiv_est(num, (uint64_t)D, (uint32_t)maxj);
+    } else {
+        uint64_t Xmin = 0x0010000000000000ULL;
+        if (limit_on == 2 && positive) {
+            const uint64_t bl = nco_bits(limit);
+            if ((int)((bl >> 52) & 0x7FF) == ex) { const uint64_t ml = NCO_MANT(bl) + 1; if (ml > Xmin) Xmin = ml; }
+        }
+        num = M1 - Xmin;
+        return (int32_t)nco_udiv_est(num, (uint64_t)(-D), (uint32_t)maxj);
+    }
+}
+
+NCO_HD void nco_iseg_set(nco_iseg_t *o, int32_t k0, uint64_t bits, int64_t D)
+{
+    const int ex = (int)((bits >> 52) & 0x7FF);
+    o->k0 = k0; o->pad = 0;
+    o->neg = (int32_t)(bits >> 63);
+    if (ex == 0) { o->X0 = 0; o->D = 0; o->shift = 64; return; }       /* zero / subnormal: (int) gives 0 */
+    o->X0 = NCO_MANT(bits);
+    o->D = D;
+    {
+        const int sh = 52 - (ex - 1023);
+        o->shift = sh > 64 ? 64 : (sh < 0 ? -1 : sh);
+    }
+}
+
+/* integer-segment version of nco_walk: returns the number of segments written to
+ * seg[0..maxseg), -1 on overflow, -2 if a value is too large to truncate;
+ * *x_end = accumulator after the last addition                                    */
+NCO_HD int nco_walk_i(double x, double step, int32_t count, double wrap, nco_iseg_t *seg, int maxseg, double *x_end)
+{
+    int32_t k = 0, ns = 0, range_bad = 0;
+    const int lim = (wrap > 0.0) ? 1 : 0;
+#define NCO_IEMIT(K0, BITS, DD) do { if (ns < maxseg) { nco_iseg_set(&seg[ns], (K0), (BITS), (DD)); if (seg[ns].shift < 0) range_bad = 1; } ns++; } while (0)
+    /* constants of the fast chain (positive x growing by a positive normal step) */
+    const uint64_t bstep = nco_bits(step), bwrap = nco_bits(wrap);
+    const int ed = (int)((bstep >> 52) & 0x7FF), ewrap = (int)((bwrap >> 52) & 0x7FF);
+    const uint64_t Dm = NCO_MANT(bstep);
+    const int chain_ok = (step > 0.0) && ed > 0 && ed < 0x7FF;
+    while (k < count) {
+        double x1, x2;
+        uint64_t b0, b1, b2;
+        int64_t D0, D;
+        int32_t J;
+        if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
+        /* ---- fast chain: whole binades on the mantissa, no floating point.  For x in
+         * binade ex = ed + s (s >= 1) every addition rounds step to the same multiple
+         * D of ulp(x) unless step's low s bits are an exact tie; the addition that
+         * leaves the binade rounds (X + step/ulp) / 2 to nearest even.                */
+        while (chain_ok) {
+            const uint64_t bx = nco_bits(x);
+            const int ex = (int)(bx >> 52);                      /* sign bit set -> large -> s out of range */
+            const int sft = ex - ed;
+            uint64_t X, q, r, half, Dn, Xmax, num, rr;
+            uint32_t Jn;
+            float est;
+            if (sft < 1 || sft > 52) break;
+            X = NCO_MANT(bx);
+            q = Dm >> sft; r = Dm & ((1ULL << sft) - 1); half = 1ULL << (sft - 1);
+            if (r == half) break;                               /* tie: the generic path sorts out the parity */
+            Dn = q + (r > half ? 1 : 0);
+            Xmax = 0x001FFFFFFFFFFFFFULL;
+            if (lim && ex == ewrap) Xmax = NCO_MANT(bwrap) - 1;
+            if (X > Xmax) break;
+            num = Xmax - X;
+#ifdef __CUDA_ARCH__
+            est = __fdividef(__ull2float_rz(num), __ull2float_ru(Dn));
+#else
+            est = (float)num / (float)Dn;
+#endif
+            if (!(est < (float)(count - k - 3))) break;         /* the run reaches the end: generic tail */
+            Jn = (uint32_t)est;
+            rr = num - (uint64_t)Jn * Dn;
+            while ((int64_t)rr < 0) { Jn--; rr += Dn; }
+            while (rr >= Dn) { Jn++; rr -= Dn; }
+            if ((int32_t)Jn >= count - k - 3) break;
+            NCO_IEMIT(k, bx, (int64_t)Dn);
+            k += (int32_t)Jn + 1;
+            {
+                const uint64_t XJ = Xmax - rr;                   /* X + Jn*Dn */
+                if (Xmax != 0x001FFFFFFFFFFFFFULL) {
+                    /* stopped by the wrap limit: one real addition, then the wrap test above */
+                    x = NCO_ADD(nco_from_bits((bx & 0xFFF0000000000000ULL) | (XJ & 0x000FFFFFFFFFFFFFULL)), step);
+                    if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
+                } else {
+                    const uint64_t T = XJ + q, Th = T >> 1;
+                    const uint64_t Xn = Th + ((T & 1) & ((r != 0 ? 1 : 0) | (Th & 1)));
+                    x = nco_from_bits(((uint64_t)(ex + 1) << 52) | (Xn & 0x000FFFFFFFFFFFFFULL));
+                }
+            }
+        }
+        if (k >= count) break;
+        x1 = NCO_ADD(x, step);
+        b0 = nco_bits(x);
+        if (x1 == x) { NCO_IEMIT(k, b0, 0); k = count; break; }
+        if (k + 1 >= count || (lim && x1 >= wrap) || !nco_same_binade(x, x1)) {
+            NCO_IEMIT(k, b0, 0); k += 1; x = x1; continue;
+        }
+        b1 = nco_bits(x1);
+        D0 = (int64_t)NCO_MANT(b1) - (int64_t)NCO_MANT(b0);
+        x2 = NCO_ADD(x1, step);
+        if (k + 2 >= count || (lim && x2 >= wrap) || !nco_same_binade(x1, x2)) {
+            NCO_IEMIT(k, b0, D0); k += 2; x = x2; continue;
+        }
+        b2 = nco_bits(x2);
+        D = (int64_t)NCO_MANT(b2) - (int64_t)NCO_MANT(b1);
+        /* steady state from x1: mantissas M1 + j*D, j = 0..J, J >= 1 (x2 is j = 1) */
+        J = nco_ijump(NCO_MANT(b1), D, (int)((b1 >> 52) & 0x7FF), x1 > 0.0, lim, wrap, count - 2 - k);
+        if (D0 == D) NCO_IEMIT(k, b0, D);
+        else { NCO_IEMIT(k, b0, 0); NCO_IEMIT(k + 1, b1, D); }
+        {
+            const uint64_t MJ = NCO_MANT(b1) + (uint64_t)((int64_t)J * D);
+            const double xJ = nco_from_bits((b1 & 0xFFF0000000000000ULL) | (MJ & 0x000FFFFFFFFFFFFFULL));
+            x = NCO_ADD(xJ, step);
+        }
+        k += 2 + J;
+    }
+#undef NCO_IEMIT
+    *x_end = x;
+    if (range_bad) return -2;                  /* |value| >= 2^53: no integer index */
+    return (ns > maxseg) ? -1 : ns;
+}
+
 /* while (x > 2pi) x -= 2pi;   (src/sdrcmn.c:666-668), exactly */
 NCO_HD double nco_reduce_2pi(double x)
 {
     const double P = NCO_TWO_PI;
-    const double inv = 0.15915494309189535;      /* ~1/(2*pi) */
     while (x > P) {
-        double x1 = NCO_ADD(x, -P), x2, d;
+        double x1 = NCO_ADD(x, -P), x2;
+        uint64_t b1, b2;
+        int64_t D;
         int32_t J;
         if (!(x1 > P) || !nco_same_binade(x, x1)) { x = x1; continue; }
         x2 = NCO_ADD(x1, -P);
         if (!(x2 > P) || !nco_same_binade(x1, x2)) { x = x2; continue; }
-        d = NCO_ADD(x2, -x1);
-        J = nco_jump(x1, d, inv, 2, P, 0x7FFFFFF0, &x);
-        (void)J;
+        b1 = nco_bits(x1); b2 = nco_bits(x2);
+        D = (int64_t)NCO_MANT(b2) - (int64_t)NCO_MANT(b1);            /* < 0 */
+        J = nco_ijump(NCO_MANT(b1), D, (int)((b1 >> 52) & 0x7FF), 1, 2, P, 0x7FFFFFF0);
+        {
+            const uint64_t MJ = NCO_MANT(b1) + (uint64_t)((int64_t)J * D);
+            x = nco_from_bits((b1 & 0xFFF0000000000000ULL) | (MJ & 0x000FFFFFFFFFFFFFULL));
+        }
     }
     return x;
 }

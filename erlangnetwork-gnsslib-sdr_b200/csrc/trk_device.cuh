@@ -54,11 +54,12 @@
 static __constant__ int8_t c_cost[32] = SDRB200_COST_INIT;
 static __constant__ int8_t c_sint[32] = SDRB200_SINT_INIT;
 
+struct trk_ncohdr_t { int32_t nseg; int32_t pad; double x_end; };
+
 struct trk_smem_t {
-    nco_table_t carr;                       /* carrier NCO segments (double form)  */
-    nco_table_t code;                       /* code NCO segments                   */
-    nco_iseg_t  icarr[TRK_MAXSEG];          /* the same, integer form              */
-    nco_iseg_t  icode[TRK_MAXSEG];
+    trk_ncohdr_t carr, code;                /* segment counts, accumulators after the last addition */
+    nco_iseg_t  icarr[TRK_MAXSEG];          /* carrier NCO segments, integer form  */
+    nco_iseg_t  icode[TRK_MAXSEG];          /* code NCO segments                   */
     unsigned int sum[2 * SDRB200_MAXTAPS];  /* tap sums mod 2^32: I[0..], Q[MAXTAPS..] */
     unsigned int wtot[2][32];               /* per-warp totals of the block scan   */
     unsigned int carry[2];                  /* prefix carried between rounds       */
@@ -154,51 +155,11 @@ __device__ __forceinline__ void trk_init_smem(trk_smem_t *sm)
     if (threadIdx.x == 0) sm->err = 0;
 }
 
-/* ---- phase 1: NCO segment tables (two lanes) -------------------------------- *
- * Must be followed by __syncthreads(); then trk_convert_tables + __syncthreads. *
- * The carrier remainder (mixcarr's subtract loop, src/sdrcmn.c:665-668) is NOT  *
- * computed here: trk_carrier_rem() does it on the NCO lane while the workers    *
- * are busy.                                                                     */
-__device__ __forceinline__ void trk_build_tables(trk_smem_t *sm, double ti, int n, double freq, double phi0,
-                                                 double crate, double coff, int smax, int coden)
-{
-    if (threadIdx.x == TRK_NCO_A) {
-        double phi, ps;
-        nco_carrier_init(freq, phi0, ti, &phi, &ps);
-        if (nco_walk(phi, ps, n, 0.0, &sm->carr)) sm->err = 1;
-    }
-    if (threadIdx.x == TRK_NCO_B) {
-        double ci = __dmul_rn(ti, crate);                   /* ti*crate, sdrcmn.c:709 */
-        double c0 = nco_code_init(coff, smax, ci, coden);
-        if (nco_walk(c0, ci, n + 2 * smax, (double)coden, &sm->code)) sm->err = 1;
-        sm->remc = nco_code_rem(sm->code.x_end, smax, ci);
-    }
-    __syncwarp();                       /* the NCO warps reach the CTA barrier converged */
-    if (threadIdx.x < 2 * SDRB200_MAXTAPS) sm->sum[threadIdx.x] = 0u;
-    if (threadIdx.x < 2) sm->carry[threadIdx.x] = 0u;
-    if (threadIdx.x == 2) { sm->qcount = 0; sm->nslow[0] = 0; sm->nslow[1] = 0; }
-}
-__device__ __forceinline__ void trk_convert_tables(trk_smem_t *sm)
-{
-    const int t = threadIdx.x;
-    if (sm->carr.nseg > TRK_MAXSEG || sm->code.nseg > TRK_MAXSEG) { if (t == 0) sm->err = 1; return; }
-    if (t < sm->carr.nseg) {
-        nco_iseg_make(&sm->carr.seg[t], &sm->icarr[t]);
-        if (sm->icarr[t].shift < 0) sm->err = 1;
-    }
-    const int u = t - 256;
-    if (u >= 0 && u < sm->code.nseg) {
-        nco_iseg_make(&sm->code.seg[u], &sm->icode[u]);
-        if (sm->icode[u].shift < 0) sm->err = 1;
-    }
-}
-__device__ __forceinline__ void trk_carrier_rem(trk_smem_t *sm)
-{
-    if (threadIdx.x == TRK_NCO_A) sm->remp = nco_carrier_rem(sm->carr.x_end);
-    __syncwarp();
-}
-
-
+/* ---- phase 1: NCO segment tables (two lanes, one per NCO warp) -------------- *
+ * trk_zero_period clears the accumulators of the period; the two walks run on   *
+ * lane TRK_NCO_A (carrier) and TRK_NCO_B (code).  The carrier remainder         *
+ * (mixcarr's subtract loop, src/sdrcmn.c:665-668) is NOT computed here:         *
+ * trk_carrier_rem() does it on the NCO lane while the workers are busy.         */
 /* optional per-warp time stamps (build with -DTRK_DEBUG): slot s, warp w -> g_dbg[s*32+w] */
 #ifdef TRK_DEBUG
 __device__ long long g_dbg[4096];
@@ -208,6 +169,67 @@ __device__ __forceinline__ long long dbg_clock() { long long t; asm volatile("mo
 #else
 #define DBG(slot)
 #endif
+
+/* out of line on purpose: the walk is a long single-lane dependency chain on 64-bit
+ * values; keeping it out of the 1024-thread kernel body (64-register cap) avoids spills.
+ * (A warp-cooperative variant - per-binade constants precomputed one per lane and
+ * fetched by shuffle - was measured slower: the recurrence is latency-bound.)        */
+__device__ __noinline__ int trk_walk_call(double x, double step, int count, double wrap, nco_iseg_t *seg, double *x_end)
+{
+    return nco_walk_i(x, step, count, wrap, seg, TRK_MAXSEG, x_end);
+}
+__device__ __noinline__ double trk_rem_call(double x_end) { return nco_carrier_rem(x_end); }
+
+__device__ __forceinline__ void trk_zero_period(trk_smem_t *sm)
+{
+    if (threadIdx.x < 2 * SDRB200_MAXTAPS) sm->sum[threadIdx.x] = 0u;
+    if (threadIdx.x < 2) sm->carry[threadIdx.x] = 0u;
+    if (threadIdx.x == 2) { sm->qcount = 0; sm->nslow[0] = 0; sm->nslow[1] = 0; }
+}
+__device__ __forceinline__ void trk_walk_carrier(trk_smem_t *sm, double ti, int n, double freq, double phi0)
+{
+    if (threadIdx.x == TRK_NCO_A) {
+        double phi, ps, xe;
+        nco_carrier_init(freq, phi0, ti, &phi, &ps);
+        const int ns = trk_walk_call(phi, ps, n, 0.0, sm->icarr, &xe);
+        if (ns < 0) sm->err = 1;
+        sm->carr.nseg = ns < 0 ? 0 : ns; sm->carr.x_end = xe;
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void trk_walk_code(trk_smem_t *sm, double ti, int n, double crate, double coff,
+                                              int smax, int coden)
+{
+    if (threadIdx.x == TRK_NCO_B) {
+        double ci = __dmul_rn(ti, crate);                   /* ti*crate, sdrcmn.c:709 */
+        double c0 = nco_code_init(coff, smax, ci, coden), xe;
+        const int ns = trk_walk_call(c0, ci, n + 2 * smax, (double)coden, sm->icode, &xe);
+        if (ns < 0) sm->err = 1;
+        sm->code.nseg = ns < 0 ? 0 : ns; sm->code.x_end = xe;
+        sm->remc = nco_code_rem(xe, smax, ci);
+    }
+    __syncwarp();
+}
+/* all of phase 1, for callers that follow it with one __syncthreads() */
+__device__ __forceinline__ void trk_build_tables(trk_smem_t *sm, double ti, int n, double freq, double phi0,
+                                                 double crate, double coff, int smax, int coden)
+{
+    trk_zero_period(sm);
+    if ((threadIdx.x >> 5) == (TRK_NCO_A >> 5)) trk_walk_carrier(sm, ti, n, freq, phi0);
+    if ((threadIdx.x >> 5) == (TRK_NCO_B >> 5)) trk_walk_code(sm, ti, n, crate, coff, smax, coden);
+}
+/* split barriers of the period loop: the workers start mixing as soon as the carrier
+ * table exists (barrier 2: carrier warp + workers) and meet the code table before the
+ * tap sums (barrier 3: code warp + workers, also the mix -> taps barrier)            */
+__device__ __forceinline__ void trk_bar_carrier() { asm volatile("bar.sync 2, %0;" ::"n"(TRK_WORKERS + 32) : "memory"); }
+__device__ __forceinline__ void trk_bar_code()    { asm volatile("bar.sync 3, %0;" ::"n"(TRK_WORKERS + 32) : "memory"); }
+__device__ __forceinline__ void trk_carrier_rem(trk_smem_t *sm)
+{
+    if (threadIdx.x == TRK_NCO_A) sm->remp = trk_rem_call(sm->carr.x_end);
+    __syncwarp();
+}
+
+
 
 /* byte b of w, sign-extended: one PRMT with sign replication */
 __device__ __forceinline__ int trk_sbyte(unsigned int w, int b)

@@ -210,6 +210,9 @@ void *sdrb200_trk_cuda_stream(sdrb200_trk_t *eng);
 /* phase profile of channel 0 (clock cycles summed over the last run): go, NCO
  * tables, table conversion, wipe-off + prefix sums, tap sums, epilogue, periods */
 int  sdrb200_trk_profile(sdrb200_trk_t *eng, int on, long long *out7);
+/* self-test of the device NCO walk against the host walker on n random cases
+ * (mode 0-4, or -1 for a mix); *mismatches = cases that differ                 */
+int  sdrb200_nco_selftest(int n, unsigned long long seed, int mode, int *mismatches);
 
 /* ------------------------------------------- single-call primitives (host I/O)
  * Same argument meaning as the reference functions named; buffers are HOST

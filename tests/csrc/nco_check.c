@@ -11,6 +11,33 @@ static double urand(void)
     return (double)(rs >> 11) * (1.0 / 9007199254740992.0);
 }
 
+int max_isegments = 0;
+
+/* integer walker against the literal loop: (int) cast of every value and the end value */
+int check_walk_i(double x0, double step, int n, double wrap)
+{
+    static nco_iseg_t seg[NCO_MAXSEG];
+    double p = x0, xe;
+    int k, bad = 0, s = 0;
+    const int ns = nco_walk_i(x0, step, n, wrap, seg, NCO_MAXSEG, &xe);
+    if (ns < 0) return 1000000;
+    if (ns > max_isegments) max_isegments = ns;
+    for (k = 0; k < n; k++, p += step) {
+        if (wrap > 0.0 && p >= wrap) p -= wrap;
+        while (s + 1 < ns && seg[s + 1].k0 <= k) s++;
+        if (fabs(p) < 9.0e15) {
+            if (seg[s].shift < 0 || nco_iseg_trunc(&seg[s], k) != (int64_t)p) bad++;
+        }
+        if (seg[s].shift >= 0 && seg[s].shift <= 52 && fabs(p) >= 1.0) {
+            /* full value, not only its integer part */
+            const uint64_t m = seg[s].X0 + (uint64_t)((int64_t)(k - seg[s].k0) * seg[s].D);
+            if (ldexp((double)m, -seg[s].shift) != fabs(p)) bad++;
+        }
+    }
+    if (p != xe) bad++;
+    return bad;
+}
+
 /* returns mismatches; carrier NCO */
 int check_carrier(double freq, double phi0, double ti, int n)
 {
@@ -28,6 +55,7 @@ int check_carrier(double freq, double phi0, double ti, int n)
         if (is.shift < 0 || (int)nco_iseg_trunc(&is, k) != (int)p) bad++;
     }
     if (p != t.x_end) bad++;
+    bad += check_walk_i(phi, ps, n, 0.0);
     prem = p * NCO_TWO_PI / 32.0;
     while (prem > NCO_TWO_PI) prem -= NCO_TWO_PI;
     if (prem != nco_carrier_rem(t.x_end)) bad++;
@@ -57,6 +85,7 @@ int check_code(double coff, int smax, double ci, int len, int n)
         }
     }
     if (c != t.x_end) bad++;
+    bad += check_walk_i(c0, ci, N, (double)len);
     if (c - smax * ci != nco_code_rem(t.x_end, smax, ci)) bad++;
     return bad;
 }
@@ -102,6 +131,7 @@ int fuzz(unsigned long long seed, int iters, int mode)
                     for (k = 0; k < n; k++, p += step) if (nco_value(&t, k, &hint) != p) r++;
                     if (p != t.x_end) r++;
                     if (t.nseg > max_segments) max_segments = t.nseg;
+                    r += check_walk_i(x0, step, n, 0.0);
                 }
             }
         }
@@ -115,7 +145,18 @@ int main(int argc, char **argv)
 {
     int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
     for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
-    printf("max segments (mode 4) %d\n", max_segments);
+    printf("max segments (mode 4) %d, integer walker %d\n", max_segments, max_isegments);
+    {   /* 2*pi reduction against the literal loop */
+        int i, b2 = 0;
+        rs = 99;
+        for (i = 0; i < iters * 5; i++) {
+            double x = urand() * ldexp(1.0, (int)(urand() * 18)), y = x;
+            while (y > NCO_TWO_PI) y -= NCO_TWO_PI;
+            if (y != nco_reduce_2pi(x)) b2++;
+        }
+        printf("reduce_2pi: %d bad of %d\n", b2, iters * 5);
+        bad += b2;
+    }
     return bad != 0;
 }
 #endif

@@ -70,3 +70,14 @@ def test_stream_and_ifgen_device(sdr):
     assert np.array_equal(st2.read(65000, 60000), host[65000:125000])
     with pytest.raises(sdr.Error):
         st2.read(0, 10)
+
+
+def test_device_nco_walk_matches_host_walker(sdr):
+    """the device NCO walk of the tracking kernel (device arithmetic) against the host walker (which
+    tests/test_nco_exact.py fuzzes against the literal loops of src/sdrcmn.c:608-668):
+    carriers, codes with wrap, tie-heavy short mantissas, negative and zero steps."""
+    import ctypes as C
+    for mode in (0, 1, 2, 3, 4, -1):
+        bad = C.c_int(-1)
+        sdr.check(sdr.lib.sdrb200_nco_selftest(3000, C.c_ulonglong(0xB200 + mode + 7), mode, C.byref(bad)), "nco_selftest")
+        assert bad.value == 0, (mode, bad.value)
