@@ -345,6 +345,15 @@ struct trk_run_smem_t {
     sdrb200_trk_rec_t rec;
     int32_t taps[SDRB200_MAXCORRN];
     int32_t go, pad;
+    /* tables of the NEXT period, walked ahead while the workers are busy with this one
+     * (only when this period is known not to change the NCO frequencies) */
+    nco_iseg_t  nx_icarr[TRK_MAXSEG], nx_icode[TRK_MAXSEG];
+    trk_ncohdr_t nx_carr, nx_code;
+    double  nx_remc;
+    int32_t nx_n;               /* currnsamp the staged tables were walked for        */
+    int32_t nx_valid;           /* staged tables are complete                        */
+    int32_t spec_do;            /* this period: walk ahead                           */
+    int32_t have;               /* this period: tables came from the staging area    */
 };
 
 template <int DTYPE>
@@ -369,6 +378,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         for (int i = threadIdx.x; i < ch->clen; i += blockDim.x) sm->t.codetab[i] = ch->code[i];
         if (threadIdx.x < ch->corrn) sm->taps[threadIdx.x] = ch->corrp[threadIdx.x];
         trk_init_smem(&sm->t);
+        if (threadIdx.x == 0) { sm->nx_valid = 0; sm->nx_n = -1; sm->have = 0; sm->spec_do = 0; }
     }
     __syncthreads();
     const int ns = ch->corrn;
@@ -391,6 +401,19 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             st->currnsamp = nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
             sm->go = (st->currnsamp > 0 && st->currnsamp <= maxn &&
                       st->buffloc + (uint64_t)st->currnsamp <= avail) ? 1 : 0;
+            sm->have = (sm->nx_valid && sm->nx_n >= 0 && sm->nx_n == st->currnsamp) ? 1 : 0;
+            sm->nx_valid = 0;
+            /* Will this period's epilogue leave carrfreq/codefreq alone?  Once bit sync is
+             * reached (flagsync never drops), the loop filters run only when checkbit()
+             * raises swloop, which is a function of counters known now
+             * (src/sdrnav.c:241-262, src/sdrmain.c:271-280).                            */
+            int quiet = 0;
+            if (st->flagsync && ch->navrate > 1) {
+                const int rate = ch->navrate, biti = (int)(st->cnt % (uint64_t)rate), diffi = biti - st->synci;
+                const int navcnt = (diffi == 1 || diffi == -rate + 1) ? 1 : st->navcnt;
+                quiet = (navcnt % ch->loopms != 0) ? 1 : 0;
+            }
+            sm->spec_do = (quiet && it + 1 < nperiods) ? 1 : 0;
         }
         __syncthreads();
         if (!sm->go) break;
@@ -402,17 +425,69 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
         const int8_t *data = ifbuf + (size_t)(st->buffloc % capacity) * DTYPE;
         const int wid = threadIdx.x >> 5;
+        const int have = sm->have, spec_do = sm->spec_do;
+        if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) { prof[10] += have; prof[11] += spec_do; }
+        if (have) {
+            /* staged tables become the tables of this period */
+            if (threadIdx.x < TRK_MAXSEG) {
+                if (threadIdx.x < sm->nx_carr.nseg) sm->t.icarr[threadIdx.x] = sm->nx_icarr[threadIdx.x];
+            } else if (threadIdx.x < 2 * TRK_MAXSEG) {
+                const int u = threadIdx.x - TRK_MAXSEG;
+                if (u < sm->nx_code.nseg) sm->t.icode[u] = sm->nx_icode[u];
+            } else if (threadIdx.x == 2 * TRK_MAXSEG) {
+                sm->t.carr = sm->nx_carr; sm->t.code = sm->nx_code; sm->t.remc = sm->nx_remc;
+            }
+            __syncthreads();
+        }
         trk_zero_period(&sm->t);
         if (wid == (TRK_NCO_A >> 5)) {
-            trk_walk_carrier(&sm->t, ch->ti, n, st->carrfreq, st->remcarr);
+            if (!have) trk_walk_carrier(&sm->t, ch->ti, n, st->carrfreq, st->remcarr);
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[8] += trk_clock() - w0;
-            trk_bar_carrier();                          /* carrier table + cleared accumulators */
+            asm volatile("bar.arrive 2, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* carrier table + cleared accumulators: releases the workers */
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
             trk_carrier_rem(&sm->t);
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[9] += trk_clock() - w0;
+            /* remp is ready: the carrier warp's share of the end-of-correlation barrier.  It does
+             * not wait there - the epilogue runs on the code warp - so a walk-ahead can overlap it */
+            asm volatile("bar.arrive 5, %0;" ::"n"(TRK_THREADS) : "memory");
+            if (spec_do) {
+                asm volatile("bar.sync 4, 64;" ::: "memory");          /* remc of this period (code warp) */
+                if (threadIdx.x == TRK_NCO_A) {
+                    /* next period: frequencies unchanged, remainders are this period's results */
+                    const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
+                    int ok = (n2 > 0 && n2 <= maxn) ? 1 : 0;
+                    if (ok) {
+                        double phi, ps, xe;
+                        nco_carrier_init(st->carrfreq, sm->t.remp, ch->ti, &phi, &ps);
+                        const int nsg = trk_walk_call(phi, ps, n2, 0.0, sm->nx_icarr, &xe);
+                        if (nsg < 0) ok = 0;
+                        sm->nx_carr.nseg = nsg < 0 ? 0 : nsg; sm->nx_carr.x_end = xe;
+                    }
+                    sm->nx_n = ok ? n2 : -1;
+                }
+                __syncwarp();
+            }
         } else if (wid == (TRK_NCO_B >> 5)) {
-            trk_walk_code(&sm->t, ch->ti, n, st->codefreq, st->remcode, smax, ch->clen);
-            trk_bar_code();                             /* code table */
+            if (!have) trk_walk_code(&sm->t, ch->ti, n, st->codefreq, st->remcode, smax, ch->clen);
+            asm volatile("bar.arrive 3, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* code table: releases the workers' tap phase */
+            if (spec_do) asm volatile("bar.arrive 4, 64;" ::: "memory");               /* remc is final: the carrier warp may read it */
+            if (spec_do) {
+                if (threadIdx.x == TRK_NCO_B) {
+                    const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
+                    int ok = (n2 > 0 && n2 <= maxn) ? 1 : 0;
+                    if (ok) {
+                        const double ci = __dmul_rn(ch->ti, st->codefreq);
+                        const double c0 = nco_code_init(sm->t.remc, smax, ci, ch->clen);
+                        double xe;
+                        const int nsg = trk_walk_call(c0, ci, n2 + 2 * smax, (double)ch->clen, sm->nx_icode, &xe);
+                        if (nsg < 0) ok = 0;
+                        sm->nx_code.nseg = nsg < 0 ? 0 : nsg; sm->nx_code.x_end = xe;
+                        sm->nx_remc = nco_code_rem(xe, smax, ci);
+                    }
+                    sm->nx_valid = ok;                  /* the carrier warp's verdict is nx_n >= 0 */
+                }
+                __syncwarp();
+            }
         } else {
             trk_bar_carrier();
             TRK_PT(1);
@@ -422,10 +497,10 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             TRK_PT(3);
             trk_tap_sums<DTYPE>(&sm->t, wk, data, n, sm->taps, ns, smax);
         }
-        __syncthreads();
+        if (wid != (TRK_NCO_A >> 5)) asm volatile("bar.sync 5, %0;" ::"n"(TRK_THREADS) : "memory");
         TRK_PT(4);
         DBG(9);
-        if ((threadIdx.x >> 5) == (TRK_NCO_A >> 5))
+        if (wid == (TRK_NCO_B >> 5))
             trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31);
         __syncthreads();
         if (recs) {
@@ -542,7 +617,7 @@ extern "C" int sdrb200_trk_profile(sdrb200_trk_t *e, int on, long long *out7)
     }
     if (out7 && e->d_prof) {
         SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
-        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 10 * sizeof(long long), cudaMemcpyDeviceToHost));
+        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 12 * sizeof(long long), cudaMemcpyDeviceToHost));
         SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
     }
     if (!on && e->d_prof) { cudaFree(e->d_prof); e->d_prof = NULL; }
