@@ -347,7 +347,6 @@ struct trk_run_smem_t {
     int32_t go, pad;
     /* tables of the NEXT period, walked ahead while the workers are busy with this one
      * (only when this period is known not to change the NCO frequencies) */
-    nco_iseg_t  nx_icarr[TRK_MAXSEG], nx_icode[TRK_MAXSEG];
     trk_ncohdr_t nx_carr, nx_code;
     double  nx_remc;
     int32_t nx_n;               /* currnsamp the staged tables were walked for        */
@@ -398,18 +397,28 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         DBG(0);
         if (threadIdx.x == TRK_NCO_A) {
             /* sdrtracking(), src/sdrtrk.c:31-32 */
-            st->currnsamp = nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
+            /* staged tables were walked for exactly this state (frequencies untouched since,
+             * remainders = the staged inputs), so their sample count is this period's */
+            const int staged = (sm->nx_valid && sm->nx_n >= 0) ? 1 : 0;
+            st->currnsamp = staged ? sm->nx_n : nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
             sm->go = (st->currnsamp > 0 && st->currnsamp <= maxn &&
                       st->buffloc + (uint64_t)st->currnsamp <= avail) ? 1 : 0;
-            sm->have = (sm->nx_valid && sm->nx_n >= 0 && sm->nx_n == st->currnsamp) ? 1 : 0;
+            sm->have = staged;
             sm->nx_valid = 0;
+            if (staged) {                               /* staged tables become the tables of this period */
+                sm->t.icarr = (sm->t.icarr == sm->t.segs[0]) ? sm->t.segs[2] : sm->t.segs[0];
+                sm->t.icode = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
+                sm->t.carr = sm->nx_carr; sm->t.code = sm->nx_code; sm->t.remc = sm->nx_remc;
+            }
             /* Will this period's epilogue leave carrfreq/codefreq alone?  Once bit sync is
              * reached (flagsync never drops), the loop filters run only when checkbit()
              * raises swloop, which is a function of counters known now
              * (src/sdrnav.c:241-262, src/sdrmain.c:271-280).                            */
             int quiet = 0;
             if (st->flagsync && ch->navrate > 1) {
-                const int rate = ch->navrate, biti = (int)(st->cnt % (uint64_t)rate), diffi = biti - st->synci;
+                const int rate = ch->navrate;
+                const int biti = (st->cnt >> 32) ? (int)(st->cnt % (uint64_t)rate) : (int)((uint32_t)st->cnt % (uint32_t)rate);
+                const int diffi = biti - st->synci;
                 const int navcnt = (diffi == 1 || diffi == -rate + 1) ? 1 : st->navcnt;
                 quiet = (navcnt % ch->loopms != 0) ? 1 : 0;
             }
@@ -427,18 +436,6 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         const int wid = threadIdx.x >> 5;
         const int have = sm->have, spec_do = sm->spec_do;
         if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) { prof[10] += have; prof[11] += spec_do; }
-        if (have) {
-            /* staged tables become the tables of this period */
-            if (threadIdx.x < TRK_MAXSEG) {
-                if (threadIdx.x < sm->nx_carr.nseg) sm->t.icarr[threadIdx.x] = sm->nx_icarr[threadIdx.x];
-            } else if (threadIdx.x < 2 * TRK_MAXSEG) {
-                const int u = threadIdx.x - TRK_MAXSEG;
-                if (u < sm->nx_code.nseg) sm->t.icode[u] = sm->nx_icode[u];
-            } else if (threadIdx.x == 2 * TRK_MAXSEG) {
-                sm->t.carr = sm->nx_carr; sm->t.code = sm->nx_code; sm->t.remc = sm->nx_remc;
-            }
-            __syncthreads();
-        }
         trk_zero_period(&sm->t);
         if (wid == (TRK_NCO_A >> 5)) {
             if (!have) trk_walk_carrier(&sm->t, ch->ti, n, st->carrfreq, st->remcarr);
@@ -459,7 +456,8 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                     if (ok) {
                         double phi, ps, xe;
                         nco_carrier_init(st->carrfreq, sm->t.remp, ch->ti, &phi, &ps);
-                        const int nsg = trk_walk_call(phi, ps, n2, 0.0, sm->nx_icarr, &xe);
+                        nco_iseg_t *dst = (sm->t.icarr == sm->t.segs[0]) ? sm->t.segs[2] : sm->t.segs[0];
+                        const int nsg = trk_walk_call(phi, ps, n2, 0.0, dst, &xe);
                         if (nsg < 0) ok = 0;
                         sm->nx_carr.nseg = nsg < 0 ? 0 : nsg; sm->nx_carr.x_end = xe;
                     }
@@ -479,7 +477,8 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                         const double ci = __dmul_rn(ch->ti, st->codefreq);
                         const double c0 = nco_code_init(sm->t.remc, smax, ci, ch->clen);
                         double xe;
-                        const int nsg = trk_walk_call(c0, ci, n2 + 2 * smax, (double)ch->clen, sm->nx_icode, &xe);
+                        nco_iseg_t *dst = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
+                        const int nsg = trk_walk_call(c0, ci, n2 + 2 * smax, (double)ch->clen, dst, &xe);
                         if (nsg < 0) ok = 0;
                         sm->nx_code.nseg = nsg < 0 ? 0 : nsg; sm->nx_code.x_end = xe;
                         sm->nx_remc = nco_code_rem(xe, smax, ci);

@@ -58,8 +58,9 @@ struct trk_ncohdr_t { int32_t nseg; int32_t pad; double x_end; };
 
 struct trk_smem_t {
     trk_ncohdr_t carr, code;                /* segment counts, accumulators after the last addition */
-    nco_iseg_t  icarr[TRK_MAXSEG];          /* carrier NCO segments, integer form  */
-    nco_iseg_t  icode[TRK_MAXSEG];          /* code NCO segments                   */
+    nco_iseg_t  segs[4][TRK_MAXSEG];        /* segment storage: {carrier, code} x {this period, walked ahead} */
+    nco_iseg_t *icarr;                      /* carrier NCO segments of this period (segs[0] or segs[2]) */
+    nco_iseg_t *icode;                      /* code NCO segments of this period (segs[1] or segs[3])    */
     unsigned int sum[2 * SDRB200_MAXTAPS];  /* tap sums mod 2^32: I[0..], Q[MAXTAPS..] */
     unsigned int wtot[2][32];               /* per-warp totals of the block scan   */
     unsigned int carry[2];                  /* prefix carried between rounds       */
@@ -152,7 +153,7 @@ __device__ __forceinline__ int trk_value_at(const nco_iseg_t *seg, int nseg, int
 __device__ __forceinline__ void trk_init_smem(trk_smem_t *sm)
 {
     if (threadIdx.x < 32) sm->lut[threadIdx.x] = ((int)c_cost[threadIdx.x] & 0xffff) | ((int)c_sint[threadIdx.x] << 16);
-    if (threadIdx.x == 0) sm->err = 0;
+    if (threadIdx.x == 0) { sm->err = 0; sm->icarr = sm->segs[0]; sm->icode = sm->segs[1]; }
 }
 
 /* ---- phase 1: NCO segment tables (two lanes, one per NCO warp) -------------- *
