@@ -37,6 +37,7 @@ for _p in (ROOT, os.path.join(ROOT, "tests")):
 FS, F_IF, F_CF, NSAMP, NFREQ, NPRN = 16.368e6, 4.092e6, 1575.42e6, 16368, 71, 32
 CELLS_PER_STEP = NPRN * NFREQ * NSAMP
 AVAIL = 65536                                   # samples "in the ring" at acquisition time
+AVAIL10 = 3 * 65536                             # ... for the 10-integration hand-over acquisition
 TRK_PRNS = [1, 3, 6, 9, 11, 14, 17, 19, 22, 25, 28, 31]
 WORKLOAD_ACQ = ("GPS L1CA acquisition, 32 PRN x 71 Doppler bins (+-7 kHz/200 Hz) x 16368 code phases, "
                 "real int8 IF 16.368 MS/s, 1 ms, intg=1 (BASELINE configs[0])")
@@ -53,13 +54,13 @@ def peaks():
 
 
 def scene(sdr, seed):
-    """12 visible PRNs at 49-52 dB-Hz with Doppler, Doppler rate and 50 bps data."""
+    """12 visible PRNs at 55-58 dB-Hz, Doppler within 30 Hz of a search bin (so that the 1 ms acquisition picks the right bin and every channel locks) with Doppler, Doppler rate and 50 bps data."""
     import numpy as np
     rng = np.random.default_rng(seed)
     sats = []
     for p in TRK_PRNS:
         b = int(rng.integers(-20, 21))
-        sats.append(dict(prn=p, cn0=float(rng.uniform(49, 52)), doppler=b * 200.0 + float(rng.uniform(-70, 70)),
+        sats.append(dict(prn=p, cn0=float(rng.uniform(55, 58)), doppler=b * 200.0 + float(rng.uniform(-30, 30)),
                          code_phase=float(rng.uniform(0, 1023 * 20)), carr_phase=float(rng.uniform(0, 1)),
                          rate=float(rng.uniform(-1, 1))))
     return sdr.make_ifgen(FS, F_IF, F_CF, 1, sats, sigma=24.0, seed=seed)
@@ -94,19 +95,19 @@ def _cpu_trk_worker(job):
     import oracle_bind as ob
     import sdrb200_pkg
     sdr = sdrb200_pkg.load()
-    total = AVAIL + (nper + 4) * NSAMP
+    total = AVAIL10 + (nper + 4) * NSAMP
     host = sdr.ifgen_host(scene(sdr, seed), 0, total)
     o = ob.best()
     devnull = os.open(os.devnull, os.O_WRONLY)
     saved = os.dup(1)
     os.dup2(devnull, 1)
     try:
-        cfg = ob.cfg_iffile(acq_intg=1)
+        cfg = ob.cfg_iffile(acq_intg=10)                     # ACQINTG_L1CA, src/sdr.h:140
         t0 = time.perf_counter()
-        o.acquire(cfg, host, AVAIL, [prn])
+        o.acquire(cfg, host, AVAIL10, [prn])
         t_acq = time.perf_counter() - t0
         t0 = time.perf_counter()
-        _, _, ntr = o.acq_track(cfg, host, AVAIL, [prn], nper)
+        _, _, ntr = o.acq_track(cfg, host, AVAIL10, [prn], nper)
         dt = time.perf_counter() - t0 - t_acq
     finally:
         os.dup2(saved, 1)
@@ -342,9 +343,16 @@ def run_b200(args):
            [(r["acquired"], r["freqi"], r["codei"]) for r in res], "host-buffer path disagrees with resident path"
 
     # ------------------------------------------------ tracking
-    got = {p: r for p, r in zip(prns, res)}
-    chans = [sdr.make_trk_chan(FS, F_IF, F_CF, 1, p, sdr.gencode(p)[0], b0 + got[p]["codei"], got[p]["acqfreq"],
-                               6, 3, 6, (5.0, 1.0), (30.0, 10.0), (200.0, 50.0))
+    # hand-over as the reference does it: acquisition with the default 10 non-coherent
+    # integrations and early exit (ACQINTG_L1CA, src/sdr.h:140; src/sdracq.c:29-43) on the
+    # window that ends at AVAIL10, then tracking starts at the acquired code phase
+    tcodes = np.stack([sdr.gencode(p)[0] for p in TRK_PRNS])
+    acq10 = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq, tcodes, 1.023e6, intg=10)
+    b10 = AVAIL10 - 11 * NSAMP                               # src/sdracq.c:24-26
+    got = {p: r for p, r in zip(TRK_PRNS, acq10.run(st, b10))}
+    chans = [sdr.make_trk_chan(FS, F_IF, F_CF, 1, p, sdr.gencode(p)[0],
+                               b10 + got[p]["codei"],                      # src/sdracq.c:53
+                               got[p]["acqfreq"], 6, 3, 6, (5.0, 1.0), (30.0, 10.0), (200.0, 50.0))
              for p in TRK_PRNS if got[p]["acquired"]]
     nch = len(chans)
     trk_obj = None
