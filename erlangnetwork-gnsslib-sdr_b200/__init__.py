@@ -21,6 +21,7 @@ lib = C.CDLL(LIB_PATH)
 
 OK, EINVAL, ENODEV, ENOMEM, ECUDA, ERANGE = 0, -1, -2, -3, -4, -5
 CTYPE_L1CA, CTYPE_G1, CTYPE_L1SBAS = 1, 20, 27
+FMT_RTLSDR, FMT_STEREO_FE1, FMT_STEREO_FE2, FMT_GN3S_2BIT, FMT_GN3S_4BIT = 1, 2, 3, 4, 5
 MAXCORRN = 16
 MAXTAPS = 1 + 2 * MAXCORRN
 IFGEN_MAXSAT = 16

@@ -184,7 +184,55 @@ extern "C" int sdrb200_ifgen_device(const void *vcfg, uint64_t k0, uint64_t n, v
     return ifgen_launch((const ifgen_cfg_t *)vcfg, k0, n, d_out, (cudaStream_t)cuda_stream);
 }
 
-static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifgen_cfg_t *gen, uint64_t n)
+/* packed front-end formats: every input byte holds one sample (real, or I and Q).
+ * The per-byte expansion tables restate the reference's unpack routines:
+ *   STEREO front end 1 (MAX2769, 2 bit real)  stereo_exp DTYPEI   src/rcv/stereo/stereo.c:163-174,192-196
+ *   STEREO front end 2 (MAX2112, 3+3 bit I/Q) stereo_exp DTYPEIQ  src/rcv/stereo/stereo.c:163-174,199-204
+ *   GN3S v3 2 bit real                        gn3s_exp_v3 mode 32/38  src/rcv/gn3s/gn3s.cpp:143-177
+ *   GN3S v3 4 bit I/Q                         gn3s_exp_v3 mode 36/42  src/rcv/gn3s/gn3s.cpp:143-177   */
+struct expand_lut_t { int8_t v[256][2]; };
+
+static int expand_lut_build(int fmt, expand_lut_t *t, int *outs)
+{
+    static const int8_t base1[4] = {-3, -1, +1, +3};
+    static const int8_t base2[8] = {+1, +3, +5, +7, -7, -5, -3, -1};
+    static const int8_t g2[4] = {1, -1, 3, -3};
+    static const int8_t gi4[16] = {1, -1, 0, 0, 3, -3, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    static const int8_t gq4[16] = {1, 0, -1, 0, 0, 0, 0, 0, 3, 0, -3, 0, 0, 0, 0, 0};
+    for (int r = 0; r < 256; r++) {
+        switch (fmt) {
+        case SDRB200_FMT_STEREO_FE1: t->v[r][0] = base1[(r >> 6) & 3]; t->v[r][1] = 0; *outs = 1; break;
+        case SDRB200_FMT_STEREO_FE2: t->v[r][0] = base2[(r >> 3) & 7]; t->v[r][1] = base2[r & 7]; *outs = 2; break;
+        case SDRB200_FMT_GN3S_2BIT:  t->v[r][0] = g2[r & 0x03]; t->v[r][1] = 0; *outs = 1; break;
+        case SDRB200_FMT_GN3S_4BIT:  t->v[r][0] = gi4[r & 0x05]; t->v[r][1] = gq4[r & 0x0A]; *outs = 2; break;
+        default: return SDRB200_EINVAL;
+        }
+    }
+    return SDRB200_OK;
+}
+
+/* one thread expands 16 packed bytes (one 16-byte load) into 16 or 32 samples */
+__global__ void k_expand_lut(const uint8_t *__restrict__ in, int8_t *__restrict__ out, size_t n, int outs,
+                             const expand_lut_t lut)
+{
+    __shared__ int8_t sl[256][2];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) { sl[i][0] = lut.v[i][0]; sl[i][1] = lut.v[i][1]; }
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * blockDim.x * 16;
+    for (size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < n; i += stride) {
+        const bool vec = (i + 16 <= n) && ((((size_t)(in + i)) & 15) == 0);
+        uint8_t b[16];
+        if (vec) *(uint4 *)b = *(const uint4 *)(in + i);
+        else for (int k = 0; k < 16; k++) b[k] = (i + k < n) ? in[i + k] : 0;
+        for (int k = 0; k < 16 && i + k < n; k++) {
+            if (outs == 1) out[i + k] = sl[b[k]][0];
+            else { out[2 * (i + k)] = sl[b[k]][0]; out[2 * (i + k) + 1] = sl[b[k]][1]; }
+        }
+    }
+}
+
+static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifgen_cfg_t *gen, uint64_t n,
+                       const expand_lut_t *lut = NULL, int outs = 0)
 {
     if (!s || (kind != 2 && !src)) { sdrb200_set_error("stream_push: bad argument"); return SDRB200_EINVAL; }
     cudaStream_t st = (cudaStream_t)s->cuda_stream;
@@ -207,6 +255,14 @@ static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifg
             sdrb200_count_launch(1);
             SDRB200_CUDA_TRY(cudaGetLastError());
             SDRB200_CUDA_TRY(cudaFreeAsync(tmp, st));
+        } else if (kind == 3) {
+            uint8_t *tmp = NULL;                         /* one packed byte per sample */
+            SDRB200_CUDA_TRY(cudaMallocAsync((void **)&tmp, chunk, st));
+            SDRB200_CUDA_TRY(cudaMemcpyAsync(tmp, (const uint8_t *)src + done, chunk, cudaMemcpyHostToDevice, st));
+            k_expand_lut<<<148 * 4, 256, 0, st>>>(tmp, dst, chunk, outs, *lut);
+            sdrb200_count_launch(1);
+            SDRB200_CUDA_TRY(cudaGetLastError());
+            SDRB200_CUDA_TRY(cudaFreeAsync(tmp, st));
         } else {
             int rc = ifgen_launch(gen, s->ifgen_next, chunk, dst, st);
             if (rc) return rc;
@@ -225,6 +281,17 @@ extern "C" int sdrb200_stream_push_host(sdrb200_stream_t *s, const int8_t *host,
 {
     return stream_push(s, 0, host, NULL, n);
 }
+extern "C" int sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_t *host, uint64_t n, int format)
+{
+    expand_lut_t lut;
+    int outs = 0;
+    if (!s || !host) { sdrb200_set_error("stream_push_packed: bad argument"); return SDRB200_EINVAL; }
+    if (format == SDRB200_FMT_RTLSDR) return sdrb200_stream_push_host_rtlsdr(s, host, n);
+    if (expand_lut_build(format, &lut, &outs)) { sdrb200_set_error("stream_push_packed: unknown format %d", format); return SDRB200_EINVAL; }
+    if (s->dtype != outs) { sdrb200_set_error("stream_push_packed: format %d yields dtype %d samples", format, outs); return SDRB200_EINVAL; }
+    return stream_push(s, 3, host, NULL, n, &lut, outs);
+}
+
 extern "C" int sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, uint64_t n)
 {
     if (s && s->dtype != 2) { sdrb200_set_error("rtlsdr samples are I/Q (dtype 2)"); return SDRB200_EINVAL; }

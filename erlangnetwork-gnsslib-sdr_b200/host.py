@@ -165,6 +165,13 @@ class Stream:
         check(lib.sdrb200_stream_push_host_rtlsdr(self.h, host.ctypes.data_as(C.POINTER(C.c_uint8)),
                                                   C.c_uint64(len(host) // 2)), "push_rtlsdr")
 
+    def push_packed(self, host: np.ndarray, fmt: int) -> None:
+        """one packed byte per sample: STEREO / GN3S front-end formats (FMT_* of sdrb200.h)."""
+        host = np.ascontiguousarray(host, np.uint8)
+        check(lib.sdrb200_stream_push_host_packed(self.h, host.ctypes.data_as(C.POINTER(C.c_uint8)),
+                                                  C.c_uint64(len(host) // 2 if int(fmt) == 1 else len(host)), int(fmt)),
+              "push_packed")                      # FMT_RTLSDR: two bytes (I, Q) per sample
+
     def push_ifgen(self, cfg: IfgenCfg, n: int) -> None:
         check(lib.sdrb200_stream_push_ifgen(self.h, C.byref(cfg), C.c_uint64(n)), "push_ifgen")
 

@@ -85,6 +85,16 @@ int  sdrb200_stream_push_host(sdrb200_stream_t *s, const int8_t *host, uint64_t 
 /* append n samples of RTL-SDR offset-binary u8 I/Q, converted on the device
  * by the rule of rtlsdr_exp(), src/rcv/rtlsdr/rtlsdr.c:136-142               */
 int  sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, uint64_t n);
+/* append n samples of a packed front-end format, ONE byte per sample, expanded on
+ * the device by the reference's tables: stereo_exp() (src/rcv/stereo/stereo.c:163-204)
+ * and gn3s_exp_v3() (src/rcv/gn3s/gn3s.cpp:143-177); FMT_RTLSDR forwards to the call
+ * above (dtype bytes per sample)                                               */
+#define SDRB200_FMT_RTLSDR      1
+#define SDRB200_FMT_STEREO_FE1  2   /* MAX2769, 2 bit real      -> dtype 1 */
+#define SDRB200_FMT_STEREO_FE2  3   /* MAX2112, 3+3 bit I/Q     -> dtype 2 */
+#define SDRB200_FMT_GN3S_2BIT   4   /* GN3S v3 modes 32/38      -> dtype 1 */
+#define SDRB200_FMT_GN3S_4BIT   5   /* GN3S v3 modes 36/42, I/Q -> dtype 2 */
+int  sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_t *host, uint64_t n, int format);
 /* append n samples produced on the device by the synthetic front end         */
 int  sdrb200_stream_push_ifgen(sdrb200_stream_t *s, const void *ifgen_cfg, uint64_t n);
 uint64_t sdrb200_stream_count(const sdrb200_stream_t *s);  /* samples pushed   */

@@ -46,6 +46,9 @@ double p_maxvd(const double *d, int n, int exs, int exe, int *ind);  /* sdrcmn.c
 double p_meanvd(const double *d, int n, int exs, int exe);           /* sdrcmn.c:487-497 */
 
 /* ---- codes (port_code.c) ---- */
+void   port_rtlsdr_exp(const unsigned char *buf, int n, signed char *out);            /* rcv/rtlsdr/rtlsdr.c:136-142 */
+void   port_stereo_exp(const unsigned char *buf, int n, int dtype, signed char *out); /* rcv/stereo/stereo.c:163-204 */
+int    port_gn3s_exp_v3(const unsigned char *buf, int n, int i_mode, signed char *out); /* rcv/gn3s/gn3s.cpp:143-177 */
 int    p_gencode(int prn, int ctype, short *code, double *crate);    /* sdrcode.c:101-154,426-444,523-539 */
 
 /* ---- channel model (port_acq.c / port_trk.c) ---- */

@@ -66,6 +66,12 @@ def main():
     assert o.lib.oh_gencode_g1_static(g1.ctypes.data_as(C.POINTER(C.c_short)), C.byref(cr)) == 511 and cr.value == 0.511e6
     np.savez_compressed(os.path.join(HERE, "codes.npz"), l1ca=np.packbits(codes > 0, axis=1), g1=g1.astype(np.int8))
 
+    # ---- front-end byte unpack: all 256 byte values through the reference's own
+    # rtlsdr_exp / stereo_exp / gn3s_exp_v3 (driver files compiled into oracle/_ref)
+    raw = np.arange(256, dtype=np.uint8)
+    np.savez_compressed(os.path.join(HERE, "ingest.npz"),
+                        **{f: o.unpack(f, raw) for f in ("rtlsdr", "stereo1", "stereo2", "gn3s2", "gn3s4")})
+
     # ---- FFT-domain primitives on small, non power-of-two sizes ---------------------
     f = {}
     for n in (12, 62, 1000):

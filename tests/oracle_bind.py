@@ -134,6 +134,24 @@ class Oracle:
                                   C.c_double(ci), int(n), out.ctypes.data_as(_sp))
         return out, rem
 
+    def unpack(self, fmt, raw):
+        """front-end byte unpack: 'rtlsdr', 'stereo1', 'stereo2', 'gn3s2', 'gn3s4' -> int8 samples.
+        The reference build calls the reference's own rtlsdr_exp / stereo_exp / gn3s_exp_v3."""
+        raw = np.ascontiguousarray(raw, np.uint8)
+        n = len(raw)
+        two = fmt in ("stereo2", "gn3s4")
+        out = np.zeros(n * (2 if two else 1), np.int8)
+        u8p, i8p = raw.ctypes.data_as(C.POINTER(C.c_uint8)), out.ctypes.data_as(_i8p)
+        ref = self.name == "reference"
+        if fmt == "rtlsdr":
+            (self.lib.rtlsdr_exp if ref else self.lib.port_rtlsdr_exp)(u8p, n, i8p)
+        elif fmt in ("stereo1", "stereo2"):
+            (self.lib.stereo_exp if ref else self.lib.port_stereo_exp)(u8p, n, 2 if two else 1, i8p)
+        else:
+            f = getattr(self.lib, "_Z11gn3s_exp_v3PhiiPc") if ref else self.lib.port_gn3s_exp_v3
+            f(u8p, n, 136 if two else 132, i8p)
+        return out
+
     def gencode(self, prn, ctype=1):
         buf = np.zeros(10230, np.int16)
         cr = C.c_double()

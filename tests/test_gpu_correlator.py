@@ -81,3 +81,31 @@ def test_device_nco_walk_matches_host_walker(sdr):
         bad = C.c_int(-1)
         sdr.check(sdr.lib.sdrb200_nco_selftest(3000, C.c_ulonglong(0xB200 + mode + 7), mode, C.byref(bad)), "nco_selftest")
         assert bad.value == 0, (mode, bad.value)
+
+
+def test_packed_front_end_formats_on_device(sdr, oracle):
+    """STEREO / GN3S / RTL-SDR bytes expanded on the device while they are
+    appended to the IF stream, against the reference's own unpack routines; ragged
+    lengths, unaligned starts and a ring wrap included."""
+    rng = np.random.default_rng(11)
+    for name, fmt, dtype in (("stereo1", sdr.FMT_STEREO_FE1, 1), ("stereo2", sdr.FMT_STEREO_FE2, 2),
+                             ("gn3s2", sdr.FMT_GN3S_2BIT, 1), ("gn3s4", sdr.FMT_GN3S_4BIT, 2)):
+        cap = 70000
+        st = sdr.Stream(dtype, cap)
+        pushed = []
+        for n in (1, 15, 16, 17, 4099, 50000, 33333):          # the last push wraps the ring
+            raw = rng.integers(0, 256, n).astype(np.uint8)
+            st.push_packed(raw, fmt)
+            pushed.append(raw)
+        allraw = np.concatenate(pushed)
+        want = oracle.unpack(name, allraw)
+        tot = len(allraw)
+        got = st.read(tot - 60000, 60000)
+        assert np.array_equal(got, want[(tot - 60000) * dtype:]), name
+        st.close()
+    st = sdr.Stream(2, 4096)
+    raw = rng.integers(0, 256, 2 * 3000).astype(np.uint8)
+    st.push_packed(raw, sdr.FMT_RTLSDR)
+    assert np.array_equal(st.read(0, 3000), oracle.unpack("rtlsdr", raw))
+    with pytest.raises(sdr.Error):
+        st.push_packed(raw[:100], sdr.FMT_STEREO_FE1)          # dtype mismatch is refused

@@ -123,3 +123,15 @@ def test_port_equals_reference_build(port):
     assert np.array_equal(_acq_rows(a1), _acq_rows(a2)) and n1 == n2
     for f in REC_FIELDS:
         assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
+
+
+def test_port_ingest_golden(port):
+    """front-end byte unpack (src/rcv/rtlsdr/rtlsdr.c:136-142, src/rcv/stereo/stereo.c:163-204,
+    src/rcv/gn3s/gn3s.cpp:143-177): every byte value, and the reference's own routines"""
+    g = np.load(os.path.join(G, "ingest.npz"))
+    raw = np.arange(256, dtype=np.uint8)
+    for f in ("rtlsdr", "stereo1", "stereo2", "gn3s2", "gn3s4"):
+        assert np.array_equal(port.unpack(f, raw), g[f]), f
+        if ob.have_ref():
+            big = np.random.default_rng(3).integers(0, 256, 5000).astype(np.uint8)
+            assert np.array_equal(port.unpack(f, big), ob.ref().unpack(f, big)), f
