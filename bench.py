@@ -373,6 +373,18 @@ def run_b200(args):
         trk.reset()
         _, nrec = trk.run(st, nper, want_records=False)
         done = sum(nrec)
+        phases = None
+        if args.trk_profile:
+            # cycle counters of channel 0, outside every timed region (sdrb200_trk_profile)
+            out = (C.c_longlong * 12)()
+            sdr.check(lib.sdrb200_trk_profile(trk.h, 1, None), "trk_profile")
+            trk.reset(); trk.enqueue(st, nper); trk.sync()
+            sdr.check(lib.sdrb200_trk_profile(trk.h, 0, out), "trk_profile")
+            names = ["go", "wait_carrier_table", "convert", "mix_prefix", "tap_sums", "epilogue"]
+            per = max(1, int(out[6]))
+            phases = {k: round(out[i] / per, 1) for i, k in enumerate(names)}
+            phases.update(periods=per, walk_carrier=round(out[8] / per, 1), carrier_rem=round(out[9] / per, 1),
+                          staged_periods=int(out[10]), walk_ahead_periods=int(out[11]), unit="cycles per period, channel 0")
         t_trk = sum(tms) / len(tms) * 1e-3
         # end to end: IF from pinned host memory -> device ring -> tracking -> per-channel record counts
         nbytes = int(nper + 8) * NSAMP + AVAIL
@@ -416,6 +428,8 @@ def run_b200(args):
                          "note": "latency-bound time recurrence per channel (DESIGN.md); HBM fraction reported as asked"},
             "cpu_baseline": cpu_trk,
         }
+        if phases:
+            trk_obj["phases"] = phases
     clk = clocks.stop()
 
     # ------------------------------------------------ reduce over ranks, print
@@ -539,6 +553,7 @@ def main():
     ap.add_argument("--trk-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-trk", action="store_true", help="skip the tracking half")
+    ap.add_argument("--trk-profile", action="store_true", help="add the per-phase cycle profile of channel 0")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3 if args.impl == "b200" else args.warmup

@@ -97,7 +97,10 @@ class TrkRec(C.Structure):
                 ("sumI0", C.c_double), ("sumQ0", C.c_double), ("codefreq", C.c_double),
                 ("codeErr", C.c_double), ("codeNco", C.c_double), ("carrfreq", C.c_double),
                 ("carrErr", C.c_double), ("carrNco", C.c_double), ("freqErr", C.c_double),
-                ("remcode", C.c_double), ("remcarr", C.c_double)]
+                ("remcode", C.c_double), ("remcarr", C.c_double),
+                ("L0", C.c_double), ("D0", C.c_double), ("S0", C.c_double), ("remcout0", C.c_double),
+                ("Isum", C.c_double), ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64),
+                ("flagobs", C.c_int32), ("pad2", C.c_int32)]
 
 
 def loop_coeffs(dllb: float, pllb: float, fllb: float) -> Loop:

@@ -516,10 +516,16 @@ k_rowc(const acq_rowc_args A)
             /* y_q[t'] into own shared memory; W_M^(-t' q) is applied by the reader */
 #pragma unroll
             for (int e = 0; e < 16; e++) fsm[tid + e * T] = v[e];
-            /* publish: CTA barrier, then ONE thread issues the cluster-scope release fence
-             * (every thread doing it costs a memory barrier per warp), relaxed arrive by all */
+            /* publish: the CTA barrier orders every thread's shared-memory stores before the
+             * arrive; the peers read the same physical shared memory (it is not cached), so
+             * the relaxed cluster barrier is enough and the cluster-scope fence
+             * (MEMBAR + L1 invalidate, 12 % of the stall samples in profiles/r1b) is left out.
+             * -DSDRB200_ROWC_FENCE puts it back; tests/test_gpu_acquisition.py
+             * test_acq_cluster_exchange_repeatable checks bit-identical power over repeats */
             __syncthreads();
+#ifdef SDRB200_ROWC_FENCE
             if (tid == 0) asm volatile("fence.acq_rel.cluster;" ::: "memory");
+#endif
             cl_arrive_relaxed();
             float2 wj[J];
 #pragma unroll

@@ -185,6 +185,11 @@ struct trk_state_t {
     int32_t biti, ocodei, synci, flagsync, swsync, swreset, swloop, navcnt, bit, flagloopfilter;
     int32_t currnsamp, pad;
     int32_t bitsync[32];
+    /* observables: slot [0] of sdrtrk_t L/D/S/remcout/codei/cntout, Isum (src/sdr.h:384-400),
+     * loopcnt of the channel thread (src/sdrmain.c:236,304) */
+    double L0, D0, S0, remcout0, Isum;
+    uint64_t obs_codei, obs_cnt;
+    int32_t flagremcarradd, loopcnt;
 };
 
 /* checksync(), src/sdrnav.c:198-233 */
@@ -314,6 +319,27 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
     if (mode == 1) trk_loops_warp(st, &ch->prm1, ch->ctime, ch, lane);
     else if (mode == 2) trk_loops_warp(st, &ch->prm2, (double)ch->loopms / 1000, ch, lane);
     __syncwarp();
+    /* setobsdata(), src/sdrtrk.c:160-209, called after the loop filters of a synchronised
+     * channel (src/sdrmain.c:285-304).  Only slot [0] of the interpolation stocks lives on
+     * the device.  The +0.5 cycle polarity term (:186-195) is gated by nav.flagsyncf (frame
+     * synchronisation, host side): it is a constant offset the host adds once.          */
+    int flagobs = 0;
+    if (mode == 2 && lane == 0) {
+        flagobs = (st->loopcnt % (100 / ch->loopms) == 0) ? 2 : 1;     /* SNSMOOTHMS, src/sdr.h:198 */
+        st->obs_codei = st->buffloc;
+        st->obs_cnt = st->cnt;
+        st->remcout0 = st->oldremcode * ch->f_sf / st->codefreq;
+        st->D0 = -(st->carrfreq - ch->f_if - ch->foffset);
+        if (!st->flagremcarradd) { st->L0 -= st->remcarr / (2.0 * TRK_PI); st->flagremcarradd = 1; }
+        st->L0 += st->D0 * ((double)(ch->loopms * st->currnsamp) / ch->f_sf);
+        st->Isum += fabs(st->sumI[0]);
+        if (flagobs == 2) {
+            st->S0 = 10 * log(st->Isum / 100.0 / 100.0) + log(500.0) + 5;
+            st->Isum = 0;
+        }
+        st->loopcnt++;
+    }
+    __syncwarp();
     if (rec) {
         for (int i = lane; i < ntap; i += 32) { rec->II[i] = st->II[i]; rec->QQ[i] = st->QQ[i]; }
         if (lane == 0) {
@@ -325,6 +351,9 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
             rec->codefreq = st->codefreq; rec->codeErr = st->codeErr; rec->codeNco = st->codeNco;
             rec->carrfreq = st->carrfreq; rec->carrErr = st->carrErr; rec->carrNco = st->carrNco;
             rec->freqErr = st->freqErr; rec->remcode = st->remcode; rec->remcarr = st->remcarr;
+            rec->L0 = st->L0; rec->D0 = st->D0; rec->S0 = st->S0; rec->remcout0 = st->remcout0;
+            rec->Isum = st->Isum; rec->obs_codei = st->obs_codei; rec->obs_cnt = st->obs_cnt;
+            rec->flagobs = flagobs; rec->pad2 = 0;
         }
     }
     __syncwarp();
@@ -385,7 +414,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
     int done = 0;
     /* optional phase profile (cycles, CTA 0, thread 0): go, tables, convert, mix, taps, epilogue */
     long long pt[6] = {0, 0, 0, 0, 0, 0}, t0 = 0;
-    const bool prof_on = prof != nullptr && blockIdx.x == 0 && threadIdx.x == 0;
+    const bool prof_on = prof != nullptr && blockIdx.x == 0 && threadIdx.x == 64;     /* first worker lane */
 #define TRK_PT(i) do { if (prof_on) { const long long t1 = trk_clock(); pt[i] += t1 - t0; t0 = t1; } } while (0)
     if (prof_on) t0 = trk_clock();
 

@@ -203,6 +203,13 @@ typedef struct {             /* one record per channel per code period          
     double   codefreq, codeErr, codeNco;
     double   carrfreq, carrErr, carrNco, freqErr;
     double   remcode, remcarr;
+    /* observables, newest slot of setobsdata() (src/sdrtrk.c:160-209; scheduling
+     * src/sdrmain.c:285-304): carrier phase L[0] (cycles, cumulative), Doppler D[0]
+     * (Hz), S[0], remcout[0] (samples), running |I| sum, codei[0], cntout[0].
+     * flagobs: 0 = setobsdata not due this period, 1 = ran, 2 = ran with snrflag   */
+    double   L0, D0, S0, remcout0, Isum;
+    uint64_t obs_codei, obs_cnt;
+    int32_t  flagobs, pad2;
 } sdrb200_trk_rec_t;
 
 typedef struct sdrb200_trk sdrb200_trk_t;

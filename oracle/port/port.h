@@ -77,6 +77,10 @@ typedef struct {
     int    rate, biti, ocodei, synci, flagsync, swsync, swreset, swloop, navcnt, bit;
     int    bitsync[32];
     double bitIP;
+    /* observables: sdrtrk_t L/D/S/remcout/codei/cntout slot [0], Isum, sdr.h:384-400 */
+    double L0, D0, S0, remcout0, Isum;
+    uint64_t obs_codei, obs_cnt;
+    int    flagremcarradd, loopcnt;
 } p_chan_t;
 
 typedef struct {                                   /* what the two INI files carry */
@@ -96,5 +100,6 @@ void     p_cumsumcorr(p_chan_t *c, int polarity);                            /* 
 void     p_clearcumsumcorr(p_chan_t *c);                                     /* sdrtrk.c:77-86 */
 void     p_pll(p_chan_t *c, const p_loop_t *prm, double dt);                 /* sdrtrk.c:94-125 */
 void     p_dll(p_chan_t *c, const p_loop_t *prm, double dt);                 /* sdrtrk.c:133-150 */
+void     p_setobsdata(p_chan_t *c, uint64_t buffloc, uint64_t cnt, int snrflag); /* sdrtrk.c:160-209 */
 
 #endif

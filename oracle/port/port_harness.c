@@ -64,7 +64,7 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
     p_cfg_t pc;
     p_chan_t *ch;
     uint64_t *buffloc, *cnt;
-    int i, k, active;
+    int i, k, active, flagobs = 0;
     if (avail % BLK || avail > nsamples) return -2;
     to_pcfg(cfg, &pc);
     ch = (p_chan_t *)calloc((size_t)nprn, sizeof(p_chan_t));
@@ -90,12 +90,17 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
             /* src/sdrmain.c:269-280 */
             p_cumsumcorr(c, 1);                              /* ocode[] is all ones */
             c->flagloopfilter = 0;
+            flagobs = 0;
             if (!c->flagsync) {
                 p_pll(c, &c->prm1, c->ctime); p_dll(c, &c->prm1, c->ctime);
                 c->flagloopfilter = 1;
             } else if (c->swloop) {
                 p_pll(c, &c->prm2, (double)c->loopms / 1000); p_dll(c, &c->prm2, (double)c->loopms / 1000);
                 c->flagloopfilter = 2;
+                /* src/sdrmain.c:285-304: SNSMOOTHMS = 100, src/sdr.h:198 */
+                flagobs = (c->loopcnt % (100 / c->loopms) == 0) ? 2 : 1;
+                p_setobsdata(c, buffloc[i], cnt[i], flagobs == 2);
+                c->loopcnt++;
             }
             r = &rec[(size_t)i * nperiods + ntracked[i]];
             r->cnt = cnt[i]; r->buffloc = buffloc[i]; r->currnsamp = c->currnsamp;
@@ -107,6 +112,8 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
             r->codefreq = c->codefreq; r->codeErr = c->codeErr; r->codeNco = c->codeNco;
             r->carrfreq = c->carrfreq; r->carrErr = c->carrErr; r->carrNco = c->carrNco;
             r->freqErr = c->freqErr; r->remcode = c->remcode; r->remcarr = c->remcarr;
+            r->L0 = c->L0; r->D0 = c->D0; r->S0 = c->S0; r->remcout0 = c->remcout0; r->Isum = c->Isum;
+            r->obs_codei = c->obs_codei; r->obs_cnt = c->obs_cnt; r->flagobs = flagobs;
             if (c->flagloopfilter) p_clearcumsumcorr(c);     /* src/sdrmain.c:310 */
             cnt[i]++;
             buffloc[i] += (uint64_t)c->currnsamp;

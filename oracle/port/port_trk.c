@@ -117,3 +117,27 @@ void p_dll(p_chan_t *c, const p_loop_t *prm, double dt)
     c->codefreq = c->crate - c->codeNco + (c->carrfreq - c->f_if - c->foffset) / (c->f_cf / c->crate);
     c->codeErr = codeErr;
 }
+
+/* setobsdata(), src/sdrtrk.c:160-209 - only slot [0] of the interpolation stocks is
+ * kept (the shiftdata() calls at :163-168 and :199-201 move history that the hot
+ * path never reads back).  The +0.5 cycle polarity term (:186-195) waits for
+ * nav.flagsyncf, which is set by frame synchronisation (src/sdrnav.c:46) - outside
+ * this path; the replay's random data bits never raise it.                      */
+void p_setobsdata(p_chan_t *c, uint64_t buffloc, uint64_t cnt, int snrflag)
+{
+    const double DPI = 2.0 * 3.1415926535897932;            /* src/sdr.h:103-104 */
+    c->obs_codei = buffloc;                                  /* :172 */
+    c->obs_cnt = cnt;                                        /* :173 */
+    c->remcout0 = c->oldremcode * c->f_sf / c->codefreq;     /* :174 */
+    c->D0 = -(c->carrfreq - c->f_if - c->foffset);           /* :177 */
+    if (!c->flagremcarradd) {                                /* :180-184 */
+        c->L0 -= c->remcarr / DPI;
+        c->flagremcarradd = 1;
+    }
+    c->L0 += c->D0 * (c->loopms * c->currnsamp / c->f_sf);   /* :197 */
+    c->Isum += fabs(c->sumI[0]);                             /* :199 */
+    if (snrflag) {
+        c->S0 = 10 * log(c->Isum / 100.0 / 100.0) + log(500.0) + 5;   /* :206 */
+        c->Isum = 0;
+    }
+}

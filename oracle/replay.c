@@ -186,7 +186,7 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
                  uint64_t avail, int nprn, const int *prn, const int *ctype,
                  int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked)
 {
-    int i, k, active;
+    int i, k, active, flagobs = 0;
     uint64_t *buffloc, *cnt, *loopcnt;
     if (avail % FILE_BUFFSIZE || avail > nsamples || nprn > MAXSAT) return -2;
     setup_ini(cfg);
@@ -223,6 +223,7 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
 
             cumsumcorr(&sdr->trk, sdr->nav.ocode[sdr->nav.ocodei]);
             sdr->trk.flagloopfilter = 0;
+            flagobs = 0;
             if (!sdr->nav.flagsync) {
                 pll(sdr, &sdr->trk.prm1, sdr->ctime);
                 dll(sdr, &sdr->trk.prm1, sdr->ctime);
@@ -231,10 +232,11 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
                 pll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
                 dll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
                 sdr->trk.flagloopfilter = 2;
-                if (loopcnt[i] % (SNSMOOTHMS / sdr->trk.loopms) == 0)
-                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 1);
-                else
-                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 0);
+                if (loopcnt[i] % (SNSMOOTHMS / sdr->trk.loopms) == 0) {
+                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 1); flagobs = 2;
+                } else {
+                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 0); flagobs = 1;
+                }
                 loopcnt[i]++;
             }
 
@@ -254,6 +256,9 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
             r->freqErr = sdr->trk.freqErr;
             r->remcode = sdr->trk.remcode; r->remcarr = sdr->trk.remcarr;
             r->L0 = sdr->trk.L[0];
+            r->D0 = sdr->trk.D[0]; r->S0 = sdr->trk.S[0]; r->remcout0 = sdr->trk.remcout[0];
+            r->Isum = sdr->trk.Isum; r->obs_codei = sdr->trk.codei[0]; r->obs_cnt = sdr->trk.cntout[0];
+            r->flagobs = flagobs;
 
             if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
             cnt[i]++;

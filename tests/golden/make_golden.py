@@ -18,9 +18,12 @@ import oracle_bind as ob  # noqa: E402
 import sdrb200_pkg  # noqa: E402
 import util  # noqa: E402
 
+OBS_FIELDS = ["cnt", "buffloc", "flagsync", "flagloopfilter", "sumI0", "carrfreq", "codefreq", "remcarr",
+              "L0", "D0", "S0", "remcout0", "Isum", "obs_codei", "obs_cnt", "flagobs"]
 REC_FIELDS = ["cnt", "buffloc", "currnsamp", "flagsync", "flagloopfilter", "swsync", "swloop", "synci",
               "biti", "bit", "II", "QQ", "sumI0", "sumQ0", "codefreq", "codeErr", "codeNco", "carrfreq",
-              "carrErr", "carrNco", "freqErr", "remcode", "remcarr"]
+              "carrErr", "carrNco", "freqErr", "remcode", "remcarr",
+              "L0", "D0", "S0", "remcout0", "Isum", "obs_codei", "obs_cnt", "flagobs"]
 
 
 def main():
@@ -110,6 +113,25 @@ def main():
     for fld in REC_FIELDS:
         out["rec_" + fld] = np.ascontiguousarray(rec[fld])
     np.savez_compressed(os.path.join(HERE, "trk_c5.npz"), **out)
+
+    # ---- observables (setobsdata, src/sdrtrk.c:160-209): a run long enough to pass bit sync.
+    # The IF (5.4 MB) is not stored: it is regenerated from the seeded generator and pinned
+    # by its CRC; the reference's records after bit sync are stored.
+    import zlib
+    cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000026)
+    nper = 4800
+    total = 65536 + (nper + 4) * 2048
+    host = sdr.ifgen_host(cfg, 0, total)
+    acq, rec, ntr = o.acq_track(ob.cfg_rtlsdr(acq_intg=2), host, 65536, vis, nper)
+    assert int(rec["flagobs"].max()) == 2
+    k0 = int(min(np.argmax(rec["flagobs"][c] > 0) for c in range(len(vis)))) - 5
+    out = dict(prns=np.array(vis), nper=nper, k0=k0, if_crc=np.uint32(zlib.crc32(host.tobytes())),
+               ntracked=np.array(ntr),
+               acq=np.array([[r.acquired, r.freqi, r.codei, r.nintg_used, r.acqfreq, r.peakr, r.cn0, r.maxp,
+                              r.buffloc] for r in acq]))
+    for fld in OBS_FIELDS:
+        out["rec_" + fld] = np.ascontiguousarray(rec[fld][:, k0:])
+    np.savez_compressed(os.path.join(HERE, "obs_c5.npz"), **out)
     for fn in sorted(os.listdir(HERE)):
         print(fn, os.path.getsize(os.path.join(HERE, fn)))
 

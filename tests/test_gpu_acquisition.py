@@ -178,3 +178,28 @@ def test_acq_glonass_g1_fdma(sdr):
         assert abs(r.peakr - g["peakr"]) <= 1e-3 * r.peakr and abs(r.cn0 - g["cn0"]) <= 0.01
         assert r.acqfreq == g["acqfreq"]
     assert [r.acquired for r in ref] == [1, 1, 1, 0]
+
+
+def test_acq_cluster_exchange_repeatable(sdr):
+    """The sub-transforms of a row cross the cluster through distributed shared memory
+    behind a CTA barrier and a relaxed cluster barrier (no cluster-scope fence).  A read
+    that overtook its producer would change power values: 60 repeated searches of the
+    same window must give the identical power matrix, bit for bit, and identical tuples."""
+    cfg, vis = util.scene_c1(sdr, nsats=4)
+    prns = vis + [2, 4, 5, 7]
+    nsamp, avail = 16368, 65536
+    st = sdr.Stream(1, avail)
+    st.push_ifgen(cfg, avail)
+    freq = np.array([util.IF1 + (i - 35) * 200.0 for i in range(71)])
+    codes = np.stack([sdr.gencode(p)[0] for p in prns])
+    acq = sdr.Acquisition(util.FS1, 1, nsamp, 16, 1e-3, freq, codes, 1.023e6, intg=1, keep_power=True)
+    b0 = avail - 2 * nsamp
+    first = acq.run(st, b0)
+    P0 = [acq.power(i).copy() for i in range(len(prns))]
+    plain = sdr.Acquisition(util.FS1, 1, nsamp, 16, 1e-3, freq, codes, 1.023e6, intg=1)
+    for rep in range(60):
+        assert acq.run(st, b0) == first
+        assert plain.run(st, b0) == first                       # register-only variant (no P)
+        if rep % 6 == 0:
+            for i in range(len(prns)):
+                assert np.array_equal(acq.power(i), P0[i]), (rep, i)

@@ -61,3 +61,29 @@ def test_golden_tracking(sdr):
         assert np.abs(rec[k]["QQ"][:n, :9] - g["rec_QQ"][i][:n, :9]).max() <= 508.0
         assert np.abs(rec[k]["carrfreq"][:n] - g["rec_carrfreq"][i][:n]).max() <= 1e-6
         assert np.abs(rec[k]["codefreq"][:n] - g["rec_codefreq"][i][:n]).max() <= 1e-6
+
+
+def test_golden_observables(sdr):
+    """setobsdata on the device (src/sdrtrk.c:160-209) against the reference's records after
+    bit sync; IF regenerated from the seeded generator on the device and pinned by its CRC."""
+    import zlib
+    g = np.load(os.path.join(G, "obs_c5.npz"))
+    prns, nper, k0 = [int(p) for p in g["prns"]], int(g["nper"]), int(g["k0"])
+    cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000026)
+    total = 65536 + (nper + 4) * 2048
+    st = sdr.Stream(2, total)
+    st.push_ifgen(cfg, total)
+    assert np.uint32(zlib.crc32(st.read(0, total).tobytes())) == g["if_crc"]
+    chans = [sdr.make_trk_chan(util.FS5, 0.0, util.CF, 2, p, sdr.gencode(p)[0], int(a[8]), a[4],
+                               4, 1, 1, (5.0, 2.0), (30.0, 20.0), (200.0, 50.0)) for p, a in zip(prns, g["acq"])]
+    rec, nrec = sdr.Tracking(chans).run(st, nper)
+    assert list(nrec) == [int(x) for x in g["ntracked"]]
+    for k in range(len(prns)):
+        r = rec[k][k0:]
+        for f in ("cnt", "buffloc", "flagsync", "flagloopfilter", "flagobs", "obs_codei", "obs_cnt"):
+            assert np.array_equal(r[f], g["rec_" + f][k]), f
+        assert int(r["flagobs"].max()) == 2
+        assert np.abs(r["D0"] - g["rec_D0"][k]).max() <= 5e-3            # follows carrfreq (rel 1e-9 of IF)
+        assert np.abs(r["L0"] - g["rec_L0"][k]).max() <= 2e-2            # integrates D0
+        assert np.abs(r["remcout0"] - g["rec_remcout0"][k]).max() <= 2e-5
+        assert np.abs(r["S0"] - g["rec_S0"][k]).max() <= 1e-6

@@ -35,6 +35,17 @@ def _compare(sdr, cfgo, acq, rec_o, ntr_o, rec_g, ntr_g, ntap):
             assert np.allclose(o[f], g[f], rtol=FREQ_RTOL, atol=0), (a.prn, f)
         for f in ("remcode", "remcarr"):
             assert np.abs(o[f] - g[f]).max() < 1e-6, (a.prn, f)
+        # observables (setobsdata, src/sdrtrk.c:160-209): scheduling and integer slots identical;
+        # float slots follow carrfreq/codefreq (rel 1e-9 of 4 MHz = 4 mHz), L0 integrates D0
+        for f in ("flagobs", "obs_codei", "obs_cnt"):
+            assert np.array_equal(o[f], g[f]), (a.prn, f)
+        assert o["flagobs"].max() == 2
+        assert np.abs(o["D0"] - g["D0"]).max() <= 5e-3, (a.prn, "D0")
+        assert np.abs(o["remcout0"] - g["remcout0"]).max() <= 2e-5, (a.prn, "remcout0")
+        assert np.abs(o["L0"] - g["L0"]).max() <= 2e-2, (a.prn, "L0", np.abs(o["L0"] - g["L0"]).max())
+        assert np.abs(o["S0"] - g["S0"]).max() <= 1e-6 and np.abs(o["Isum"] - g["Isum"]).max() <= IQ_TOL, (a.prn, "S0")
+        print(f"prn {a.prn}: obs max|dD0|={np.abs(o['D0'] - g['D0']).max():.2e} Hz, max|dL0|="
+              f"{np.abs(o['L0'] - g['L0']).max():.2e} cyc, max|dS0|={np.abs(o['S0'] - g['S0']).max():.2e}")
         exact = np.array_equal(o["II"][:, :ntap], g["II"][:, :ntap]) and np.array_equal(o["QQ"][:, :ntap], g["QQ"][:, :ntap])
         print(f"prn {a.prn}: {n} periods, I/Q bit-exact={exact}, max|dI|={dI}, "
               f"max|dcarrfreq|={np.abs(o['carrfreq'] - g['carrfreq']).max():.3e}")
@@ -67,9 +78,9 @@ def _run(sdr, oracle, cfg, prns, cfgo, nper, fs, dtype):
 
 def test_tracking_real_if(sdr, oracle):
     cfg, prns = util.scene_c1(sdr, nsats=3)
-    _run(sdr, oracle, cfg, prns, ob.cfg_iffile(acq_intg=1), 2600, util.FS1, 1)
+    _run(sdr, oracle, cfg, prns, ob.cfg_iffile(acq_intg=1), 4600, util.FS1, 1)
 
 
 def test_tracking_iq_rtlsdr_style(sdr, oracle):
     cfg, prns = util.scene_c5(sdr, nsats=4)
-    _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=2), 2600, util.FS5, 2)
+    _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=2), 4600, util.FS5, 2)

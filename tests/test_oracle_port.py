@@ -14,7 +14,8 @@ import util
 G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 REC_FIELDS = ["cnt", "buffloc", "currnsamp", "flagsync", "flagloopfilter", "swsync", "swloop", "synci",
               "biti", "bit", "II", "QQ", "sumI0", "sumQ0", "codefreq", "codeErr", "codeNco", "carrfreq",
-              "carrErr", "carrNco", "freqErr", "remcode", "remcarr"]
+              "carrErr", "carrNco", "freqErr", "remcode", "remcarr",
+              "L0", "D0", "S0", "remcout0", "Isum", "obs_codei", "obs_cnt", "flagobs"]
 
 
 @pytest.fixture(scope="module")
@@ -116,13 +117,33 @@ def test_port_equals_reference_build(port):
     import sdrb200_pkg
     sdr = sdrb200_pkg.load()
     cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000099)
-    nper = 60
+    nper = 4800                                   # past bit sync: setobsdata runs (flagobs)
     host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
     a1, r1, n1 = ref.acq_track(ob.cfg_rtlsdr(acq_intg=1), host, 65536, vis, nper)
     a2, r2, n2 = port.acq_track(ob.cfg_rtlsdr(acq_intg=1), host, 65536, vis, nper)
     assert np.array_equal(_acq_rows(a1), _acq_rows(a2)) and n1 == n2
     for f in REC_FIELDS:
         assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
+    assert int(r1["flagobs"].max()) == 2
+
+
+def test_port_observables_golden(port):
+    """setobsdata (src/sdrtrk.c:160-209) after bit sync: the port against the reference's
+    records; the IF is regenerated from the seeded generator and pinned by its CRC."""
+    import zlib
+    import sdrb200_pkg
+    sdr = sdrb200_pkg.load()
+    g = np.load(os.path.join(G, "obs_c5.npz"))
+    prns, nper, k0 = [int(p) for p in g["prns"]], int(g["nper"]), int(g["k0"])
+    cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000026)
+    assert vis == prns
+    host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
+    assert np.uint32(zlib.crc32(host.tobytes())) == g["if_crc"]
+    acq, rec, ntr = port.acq_track(ob.cfg_rtlsdr(acq_intg=2), host, 65536, prns, nper)
+    assert np.array_equal(np.array(ntr), g["ntracked"])
+    for f in [k[4:] for k in g.keys() if k.startswith("rec_")]:
+        assert np.array_equal(np.ascontiguousarray(rec[f][:, k0:]), g["rec_" + f]), f
+    assert int(g["rec_flagobs"].max()) == 2
 
 
 def test_port_ingest_golden(port):
