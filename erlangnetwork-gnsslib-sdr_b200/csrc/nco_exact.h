@@ -436,15 +436,203 @@ NCO_HD int nco_walk_i(double x, double step, int32_t count, double wrap, nco_ise
     return (ns > maxseg) ? -1 : ns;
 }
 
-/* while (x > 2pi) x -= 2pi;   (src/sdrcmn.c:666-668), exactly */
+/* while (x > 2pi) x -= 2pi;   (src/sdrcmn.c:666-668), exactly.
+ *
+ * Fast path: P = 2pi is a constant, so for x in binade 2^(2+s) (s >= 2, i.e. x >= 16) the
+ * subtraction is known in units of ulp(x) without probing: P / ulp = MP / 2^s = q + r/2^s
+ * (MP: 53-bit mantissa of P).  While the exact difference stays at or above the binade's
+ * lower border it is rounded on the same grid, so every step subtracts D = q (r < half) or
+ * q + 1 (r > half) from the mantissa X.  J = floor((X - 2^52 - 1) / D) such steps keep
+ * X - J*D >= 2^52 + 1, for which the exact difference (> X_j - 1/2) is provably inside
+ * the binade; one integer division replaces them.  The step that may leave the binade is a
+ * REAL subtraction.  An exact tie (r == half, binade [64,128) for this P) takes one real
+ * step first: its result is even, after which D is the even one of {q, q+1}.
+ * Everything else (x < 16, huge x) runs the generic probing loop.                        */
+/* per-binade constants of the fast path for P = 2*pi (mantissa 0x1921FB54442D18): entry s is
+ * D = P / ulp rounded for x in [2^(2+s), 2^(3+s)) - q + (r > half), or the even one of
+ * {q, q+1} for the tie binade - and a float reciprocal of D / 2^21 (biased low by 2^-22 so
+ * that the run-length estimate rarely overshoots).  tests/test_nco_exact.py recomputes them. */
+#define NCO_R2PI_TIES 0x10U   /* binades s whose rounding is an exact tie */
+static const uint64_t nco_r2pi_D_host[32] = {
+    0x001921FB54442D18ULL,
+    0x000C90FDAA22168CULL,
+    0x0006487ED5110B46ULL,
+    0x0003243F6A8885A3ULL,
+    0x0001921FB54442D2ULL,
+    0x0000C90FDAA22169ULL,
+    0x00006487ED5110B4ULL,
+    0x00003243F6A8885AULL,
+    0x00001921FB54442DULL,
+    0x00000C90FDAA2217ULL,
+    0x000006487ED5110BULL,
+    0x000003243F6A8886ULL,
+    0x000001921FB54443ULL,
+    0x000000C90FDAA221ULL,
+    0x0000006487ED5111ULL,
+    0x0000003243F6A888ULL,
+    0x0000001921FB5444ULL,
+    0x0000000C90FDAA22ULL,
+    0x00000006487ED511ULL,
+    0x00000003243F6A89ULL,
+    0x00000001921FB544ULL,
+    0x00000000C90FDAA2ULL,
+    0x000000006487ED51ULL,
+    0x000000003243F6A9ULL,
+    0x000000001921FB54ULL,
+    0x000000000C90FDAAULL,
+    0x0000000006487ED5ULL,
+    0x0000000003243F6BULL,
+    0x0000000001921FB5ULL,
+    0x0000000000C90FDBULL,
+    0x00000000006487EDULL,
+    0x00000000003243F7ULL
+};
+static const float nco_r2pi_rcp_host[32] = {
+    2.964491708e-10f,
+    5.928982305e-10f,
+    1.185796461e-09f,
+    2.371592922e-09f,
+    4.743185844e-09f,
+    9.486371688e-09f,
+    1.897274338e-08f,
+    3.794548675e-08f,
+    7.589097351e-08f,
+    1.517819470e-07f,
+    3.035638940e-07f,
+    6.071277880e-07f,
+    1.214255576e-06f,
+    2.428511152e-06f,
+    4.857022304e-06f,
+    9.714044609e-06f,
+    1.942808922e-05f,
+    3.885617843e-05f,
+    7.771235687e-05f,
+    1.554247137e-04f,
+    3.108494275e-04f,
+    6.216988550e-04f,
+    1.243397710e-03f,
+    2.486795420e-03f,
+    4.973590840e-03f,
+    9.947181679e-03f,
+    1.989436336e-02f,
+    3.978872672e-02f,
+    7.957745343e-02f,
+    1.591549069e-01f,
+    3.183098137e-01f,
+    6.366195679e-01f
+};
+#ifdef __CUDACC__
+static __device__ __constant__ uint64_t nco_r2pi_D_dev[32] = {
+    0x001921FB54442D18ULL,
+    0x000C90FDAA22168CULL,
+    0x0006487ED5110B46ULL,
+    0x0003243F6A8885A3ULL,
+    0x0001921FB54442D2ULL,
+    0x0000C90FDAA22169ULL,
+    0x00006487ED5110B4ULL,
+    0x00003243F6A8885AULL,
+    0x00001921FB54442DULL,
+    0x00000C90FDAA2217ULL,
+    0x000006487ED5110BULL,
+    0x000003243F6A8886ULL,
+    0x000001921FB54443ULL,
+    0x000000C90FDAA221ULL,
+    0x0000006487ED5111ULL,
+    0x0000003243F6A888ULL,
+    0x0000001921FB5444ULL,
+    0x0000000C90FDAA22ULL,
+    0x00000006487ED511ULL,
+    0x00000003243F6A89ULL,
+    0x00000001921FB544ULL,
+    0x00000000C90FDAA2ULL,
+    0x000000006487ED51ULL,
+    0x000000003243F6A9ULL,
+    0x000000001921FB54ULL,
+    0x000000000C90FDAAULL,
+    0x0000000006487ED5ULL,
+    0x0000000003243F6BULL,
+    0x0000000001921FB5ULL,
+    0x0000000000C90FDBULL,
+    0x00000000006487EDULL,
+    0x00000000003243F7ULL
+};
+static __device__ __constant__ float nco_r2pi_rcp_dev[32] = {
+    2.964491708e-10f,
+    5.928982305e-10f,
+    1.185796461e-09f,
+    2.371592922e-09f,
+    4.743185844e-09f,
+    9.486371688e-09f,
+    1.897274338e-08f,
+    3.794548675e-08f,
+    7.589097351e-08f,
+    1.517819470e-07f,
+    3.035638940e-07f,
+    6.071277880e-07f,
+    1.214255576e-06f,
+    2.428511152e-06f,
+    4.857022304e-06f,
+    9.714044609e-06f,
+    1.942808922e-05f,
+    3.885617843e-05f,
+    7.771235687e-05f,
+    1.554247137e-04f,
+    3.108494275e-04f,
+    6.216988550e-04f,
+    1.243397710e-03f,
+    2.486795420e-03f,
+    4.973590840e-03f,
+    9.947181679e-03f,
+    1.989436336e-02f,
+    3.978872672e-02f,
+    7.957745343e-02f,
+    1.591549069e-01f,
+    3.183098137e-01f,
+    6.366195679e-01f
+};
+#endif
+
 NCO_HD double nco_reduce_2pi(double x)
 {
     const double P = NCO_TWO_PI;
     while (x > P) {
-        double x1 = NCO_ADD(x, -P), x2;
+        double x1, x2;
         uint64_t b1, b2;
         int64_t D;
         int32_t J;
+        {
+            const uint64_t bx = nco_bits(x);
+            const int s = (int)(bx >> 52) - (1023 + 2);             /* x > P > 0: sign bit clear */
+            if ((unsigned int)(s - 2) <= 28u) {
+#ifdef __CUDA_ARCH__
+                const uint64_t Dq = nco_r2pi_D_dev[s]; const float rcp = nco_r2pi_rcp_dev[s];
+#else
+                const uint64_t Dq = nco_r2pi_D_host[s]; const float rcp = nco_r2pi_rcp_host[s];
+#endif
+                uint64_t X = NCO_MANT(bx);
+                if ((NCO_R2PI_TIES >> s) & 1u) {
+                    x1 = NCO_ADD(x, -P);
+                    if (!nco_same_binade(x, x1)) { x = x1; continue; }
+                    X = NCO_MANT(nco_bits(x1));                     /* even after the tie */
+                }
+                if (X > 0x0010000000000001ULL) {
+                    /* J = floor(num / Dq): float estimate from the top 31 bits, exact fix-up */
+                    const uint64_t num = X - 0x0010000000000001ULL;
+                    const uint32_t Jn = (uint32_t)((float)(uint32_t)(num >> 21) * rcp);
+                    int64_t rr = (int64_t)(num - (uint64_t)Jn * Dq);
+                    /* bounded corrections (loops here are turned into a 64-bit division by the
+                     * compiler); an estimate further off takes the exact remainder          */
+                    if (rr < 0) rr += (int64_t)Dq;
+                    if (rr >= (int64_t)Dq) rr -= (int64_t)Dq;
+                    if (rr >= (int64_t)Dq) rr -= (int64_t)Dq;
+                    if (rr < 0 || rr >= (int64_t)Dq) rr = (int64_t)(num % Dq);
+                    X = 0x0010000000000001ULL + (uint64_t)rr;
+                }
+                x = NCO_ADD(nco_from_bits((bx & 0xFFF0000000000000ULL) | (X & 0x000FFFFFFFFFFFFFULL)), -P);
+                continue;
+            }
+        }
+        x1 = NCO_ADD(x, -P);
         if (!(x1 > P) || !nco_same_binade(x, x1)) { x = x1; continue; }
         x2 = NCO_ADD(x1, -P);
         if (!(x2 > P) || !nco_same_binade(x1, x2)) { x = x2; continue; }

@@ -140,13 +140,10 @@ int fuzz(unsigned long long seed, int iters, int mode)
     return bad;
 }
 
-#ifdef NCO_MAIN
-int main(int argc, char **argv)
+/* 2*pi reduction (src/sdrcmn.c:666-668) against the literal loop: random and structured x */
+int fuzz_reduce(int n)
 {
-    int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
-    for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
-    printf("max segments (mode 4) %d, integer walker %d\n", max_segments, max_isegments);
-    {   /* 2*pi reduction against the literal loop */
+    const int iters = n / 5;
         int i, b2 = 0;
         rs = 99;
         for (i = 0; i < iters * 5; i++) {
@@ -154,9 +151,30 @@ int main(int argc, char **argv)
             while (y > NCO_TWO_PI) y -= NCO_TWO_PI;
             if (y != nco_reduce_2pi(x)) b2++;
         }
-        printf("reduce_2pi: %d bad of %d\n", b2, iters * 5);
-        bad += b2;
-    }
+        /* structured: mantissas just above a binade border, near multiples of 2*pi, large x */
+        for (i = 0; i < iters * 5; i++) {
+            const int e = 3 + (int)(urand() * 18);
+            double x, y;
+            switch (i % 4) {
+            case 0: x = ldexp(1.0, e) + ldexp(floor(urand() * 4096.0), e - 52); break;
+            case 1: x = floor(urand() * ldexp(1.0, e - 2)) * NCO_TWO_PI + (urand() - 0.5) * 1e-9; break;
+            case 2: x = ldexp(2.0, e) - ldexp(floor(urand() * 4096.0), e - 52); break;
+            default: x = ldexp(1.0 + urand(), e); break;
+            }
+            y = x;
+            while (y > NCO_TWO_PI) y -= NCO_TWO_PI;
+            if (y != nco_reduce_2pi(x)) b2++;
+        }
+    return b2;
+}
+
+#ifdef NCO_MAIN
+int main(int argc, char **argv)
+{
+    int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
+    for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
+    printf("max segments (mode 4) %d, integer walker %d\n", max_segments, max_isegments);
+    { int b2 = fuzz_reduce(iters * 5); printf("reduce_2pi: %d bad of %d\n", b2, iters * 10); bad += b2; }
     return bad != 0;
 }
 #endif

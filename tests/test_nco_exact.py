@@ -37,3 +37,10 @@ def test_nco_edge_cases(nco):
     assert nco.check_code(0.0, 0, 1.023e6 / 16.368e6, 1023, 3 * 16368) == 0   # three code periods
     assert nco.check_code(0.0, 0, 1.023e6 / 16.368e6, 1023, 327360) == -1     # table overflow is reported
     assert nco.check_code(510.5, 2, 0.511e6 / 20e6, 511, 20000) == 0    # GLONASS G1 at 20 MS/s
+
+
+def test_reduce_2pi_fuzz(nco):
+    """mixcarr's `while (prem > DPI) prem -= DPI` (src/sdrcmn.c:666-668): closed-form per-binade
+    jumps against the literal loop, random and structured arguments up to 2^21."""
+    nco.fuzz_reduce.restype = C.c_int
+    assert nco.fuzz_reduce(C.c_int(40000)) == 0
