@@ -430,6 +430,90 @@ def run_b200(args):
         }
         if phases:
             trk_obj["phases"] = phases
+    # ------------------------------------------------ config-5 style: many independent IF streams
+    # BASELINE configs[4]: RTL-SDR-like 8-bit I/Q at 2.048 MS/s, full acquisition + tracking per
+    # stream, streams sharded across the GPUs (8 per GPU of a 64-stream job).  Every plan and
+    # engine owns a CUDA stream; all of them are enqueued before the first wait, so the
+    # channels of all streams share the SMs.  Reported, not the headline.
+    streams_obj = None
+    if args.c5_streams > 0:
+        FS5, NS5 = 2.048e6, 2048
+        T5 = args.c5_seconds
+        nper5 = int(T5 * 1000) - 8
+        tot5 = 65536 + (nper5 + 8) * NS5
+        prn_pool = [2, 5, 7, 13, 19, 25, 29, 30, 4, 9, 16, 23]
+        freq5 = np.array([(i - 35) * 200.0 for i in range(NFREQ)])
+        codes5 = np.stack([sdr.gencode(p)[0] for p in range(1, NPRN + 1)])
+        s5, a5 = [], []
+        for k in range(args.c5_streams):
+            rng = np.random.default_rng(0xB2000500 + 64 * rank + k)
+            vis = sorted(rng.choice(prn_pool, size=8, replace=False).tolist())
+            sats = [dict(prn=int(p_), cn0=float(rng.uniform(52, 56)),
+                         doppler=float(int(rng.integers(-20, 21)) * 200.0 + rng.uniform(-30, 30)),
+                         code_phase=float(rng.uniform(0, 1023 * 20)), carr_phase=float(rng.uniform(0, 1)),
+                         rate=float(rng.uniform(-1, 1))) for p_ in vis]
+            stk = sdr.Stream(2, tot5)
+            stk.push_ifgen(sdr.make_ifgen(FS5, 0.0, F_CF, 2, sats, sigma=20.0, seed=0xB2000500 + 64 * rank + k), tot5)
+            s5.append(stk)
+            a5.append(sdr.Acquisition(FS5, 2, NS5, 2, 1e-3, freq5, codes5, 1.023e6, intg=10))
+        b5 = 65536 - 11 * NS5
+        for _ in range(2):                                   # warm
+            for ak, sk in zip(a5, s5): ak.enqueue(sk, b5)
+            got5 = [ak.fetch() for ak in a5]
+        barrier()
+        t0 = time.perf_counter()
+        for ak, sk in zip(a5, s5): ak.enqueue(sk, b5)
+        got5 = [ak.fetch() for ak in a5]
+        sdr.check(lib.sdrb200_device_sync(), "sync")
+        t_acq5 = time.perf_counter() - t0
+        steps5 = sum(max(r["nintg"] for r in g) for g in got5)          # integration steps actually run
+        engines = []
+        for g, sk in zip(got5, s5):
+            ch5 = [sdr.make_trk_chan(FS5, 0.0, F_CF, 2, p_, sdr.gencode(p_)[0], b5 + r["codei"], r["acqfreq"],
+                                     4, 1, 1, (5.0, 2.0), (30.0, 20.0), (200.0, 50.0))
+                   for p_, r in zip(range(1, NPRN + 1), g) if r["acquired"]]
+            engines.append(sdr.Tracking(ch5) if ch5 else None)
+        nch5 = sum(e.nch for e in engines if e)
+        for e, sk in zip(engines, s5):
+            if e: e.enqueue(sk, 200)
+        for e in engines:
+            if e: e.sync(); e.reset()
+        barrier()
+        t0 = time.perf_counter()
+        for e, sk in zip(engines, s5):
+            if e: e.enqueue(sk, nper5)
+        for e in engines:
+            if e: e.sync()
+        t_trk5 = time.perf_counter() - t0
+        done5 = 0
+        for e, sk in zip(engines, s5):
+            if e:
+                e.reset()
+        tv = [t_acq5, t_trk5]
+        if dist is not None:
+            tt = torch.tensor(tv, dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            tv = [float(tt[0]), float(tt[1])]
+            tn = torch.tensor([float(nch5), float(steps5)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tn)
+            nch5_all, steps5_all = float(tn[0]), float(tn[1])
+        else:
+            nch5_all, steps5_all = float(nch5), float(steps5)
+        streams_obj = {
+            "workload": f"{args.c5_streams} independent I/Q int8 streams per GPU at 2.048 MS/s (BASELINE configs[4] style): "
+                        f"32 PRN x 71 bins x 2048 acquisition (10 integrations, early exit) then {T5:g} s tracking "
+                        "of every acquired PRN, 9 taps",
+            "streams_per_gpu": args.c5_streams, "channels_tracked": nch5_all,
+            "acquisition": {"cells_per_s": NPRN * NFREQ * NS5 * steps5_all / tv[0], "ms": tv[0] * 1e3,
+                            "integration_steps": steps5_all},
+            "tracking": {"value": nch5_all * nper5 * 1e-3 / tv[1], "unit": "channel.s/s", "ms": tv[1] * 1e3,
+                         "us_per_code_period_per_channel": tv[1] * 1e6 / nper5},
+            "timing": "host clock around enqueue-all .. sync-all (several CUDA streams), device idle before",
+        }
+        for e in engines:
+            if e: e.close()
+        for ak in a5: ak.close()
+        for sk in s5: sk.close()
     clk = clocks.stop()
 
     # ------------------------------------------------ reduce over ranks, print
@@ -472,6 +556,7 @@ def run_b200(args):
         "clocks": clk,
         "acquired_prns": [p for p, r in zip(prns, res) if r["acquired"]],
         "tracking": trk_obj,
+        "streams_c5": streams_obj,
     }
     if rank == 0:
         emit(line)
@@ -553,6 +638,8 @@ def main():
     ap.add_argument("--trk-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-trk", action="store_true", help="skip the tracking half")
+    ap.add_argument("--c5-streams", type=int, default=8, help="config-5 style independent streams per GPU (0: skip)")
+    ap.add_argument("--c5-seconds", type=float, default=4.0)
     ap.add_argument("--trk-profile", action="store_true", help="add the per-phase cycle profile of channel 0")
     args = ap.parse_args()
     if args.warmup < 3:

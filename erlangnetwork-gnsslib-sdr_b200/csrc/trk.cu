@@ -406,6 +406,8 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         for (int i = threadIdx.x; i < ch->clen; i += blockDim.x) sm->t.codetab[i] = ch->code[i];
         if (threadIdx.x < ch->corrn) sm->taps[threadIdx.x] = ch->corrp[threadIdx.x];
         trk_init_smem(&sm->t);
+        /* record slots beyond the channel's taps are never written: keep them zero */
+        for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) ((uint32_t *)&sm->rec)[i] = 0u;
         if (threadIdx.x == 0) { sm->nx_valid = 0; sm->nx_n = -1; sm->have = 0; sm->spec_do = 0; }
     }
     __syncthreads();
