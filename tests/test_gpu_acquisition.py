@@ -203,3 +203,46 @@ def test_acq_cluster_exchange_repeatable(sdr):
         if rep % 6 == 0:
             for i in range(len(prns)):
                 assert np.array_equal(acq.power(i), P0[i]), (rep, i)
+
+
+def test_acq_weak_signal_full_size_coherent(sdr, oracle):
+    """config 4 at its real size: 20 ms coherent blocks (n = 327 360 lags, M = 2^20 = 128
+    sub-transforms of 8192: the largest transform the plan builds), 100 Hz Doppler step,
+    2 non-coherent steps, a 30 dB-Hz GPS PRN, an SBAS PRN (133) and an absent PRN, no data
+    transitions in the window.  Oracle: the reference's pcorrelator on a 20-period replica
+    with its own accumulation flag, bins limited to 5 to keep the CPU side short."""
+    ncoh, nsamp, fs = 20, 16368, util.FS1
+    n = ncoh * nsamp
+    sats = [dict(prn=9, cn0=31.0, doppler=1312.0, code_phase=311.4, carr_phase=0.3, rate=0.0, nav_on=0),
+            dict(prn=133, cn0=30.0, doppler=-2093.0, code_phase=875.2, carr_phase=0.7, rate=0.0, nav_on=0)]
+    cfg = sdr.make_ifgen(fs, util.IF1, util.CF, 1, sats, sigma=24.0, seed=0xB2000004)
+    intg = 2
+    avail = (intg + 1) * n + 4096
+    st = sdr.Stream(1, avail)
+    st.push_ifgen(cfg, avail)
+    host = st.read(0, avail)
+    b0 = avail - (intg + 1) * n
+    prns = [9, 133, 4]
+    ci = 1.023e6 / fs
+    for i, p in enumerate(prns):
+        dop = np.round((sats[i]["doppler"] if i < 2 else 0.0) / 100) * 100
+        freq = np.array([util.IF1 + dop + (k - 2) * 100.0 for k in range(5)])
+        code = sdr.gencode(p)[0]
+        acq = sdr.Acquisition(fs, 1, nsamp, 16, 1e-3, freq, code[None, :], 1.023e6, intg=intg, ncoh=ncoh,
+                              keep_power=True)
+        g = acq.run(st, b0)[0]
+        rep, _ = oracle.rescode(code.astype(np.int16), 0.0, 0, ci, n)
+        x = np.zeros(2 * n, np.complex64)
+        x[:n] = rep
+        X = oracle.cpxfft(x)
+        ref = oracle.pcorrelator(host[b0:b0 + 2 * n], 1, 1 / fs, n, freq, 1.023e6, 2 * n, X)
+        if g["nintg"] == 2:                                   # no early exit: second block accumulated
+            ref = oracle.pcorrelator(host[b0 + n:b0 + 3 * n], 1, 1 / fs, n, freq, 1.023e6, 2 * n, X, P=ref)
+        P = acq.power(0).ravel()
+        assert np.abs(P - ref).max() <= 2e-4 * ref.max(), p
+        flat = int(np.argmax(ref))
+        assert (g["freqi"], g["codei"]) == (flat // n, flat % n), (p, g)
+        if i < 2:
+            # the true Doppler bin, and a code phase equal to the injected delay modulo one period
+            assert g["freqi"] == 2, (p, g)
+            assert g["maxp"] > 8 * np.median(ref), p
