@@ -376,7 +376,7 @@ def run_b200(args):
         phases = None
         if args.trk_profile:
             # cycle counters of channel 0, outside every timed region (sdrb200_trk_profile)
-            out = (C.c_longlong * 12)()
+            out = (C.c_longlong * 16)()
             sdr.check(lib.sdrb200_trk_profile(trk.h, 1, None), "trk_profile")
             trk.reset(); trk.enqueue(st, nper); trk.sync()
             sdr.check(lib.sdrb200_trk_profile(trk.h, 0, out), "trk_profile")
@@ -384,7 +384,9 @@ def run_b200(args):
             per = max(1, int(out[6]))
             phases = {k: round(out[i] / per, 1) for i, k in enumerate(names)}
             phases.update(periods=per, walk_carrier=round(out[8] / per, 1), carrier_rem=round(out[9] / per, 1),
-                          staged_periods=int(out[10]), walk_ahead_periods=int(out[11]), unit="cycles per period, channel 0")
+                          staged_periods=int(out[10]), walk_ahead_periods=int(out[11]),
+                          epilogue_nav=round(out[12] / per, 1), epilogue_loops=round(out[13] / per, 1),
+                          epilogue_obs_rec=round(out[14] / per, 1), unit="cycles per period, channel 0")
         t_trk = sum(tms) / len(tms) * 1e-3
         # end to end: IF from pinned host memory -> device ring -> tracking -> per-channel record counts
         nbytes = int(nper + 8) * NSAMP + AVAIL

@@ -278,8 +278,11 @@ __device__ static void trk_loops_warp(trk_state_t *st, const sdrb200_loop_t *prm
 /* epilogue of one code period, executed by ONE warp: everything sdrtracking and
  * the sdrthread loop body do around correlator()                              */
 __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const trk_smem_t *sm,
-                                    sdrb200_trk_rec_t *rec, int lane)
+                                    sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr)
 {
+    long long e0 = 0;
+#define TRK_EP(i) do { if (ep && lane == 0) { const long long e1 = trk_clock(); ep[i] += e1 - e0; e0 = e1; } } while (0)
+    if (ep && lane == 0) e0 = trk_clock();
     const int ntap = 1 + 2 * ch->corrn;
     /* src/sdrtrk.c:35-38: the memcpy length 1+2*corrn*8 bytes covers 2*corrn doubles
      * (plus one stray byte of the next, which no consumer reads)               */
@@ -308,6 +311,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         if (st->flagsync) trk_checkbit(st->II[0], ch->loopms, st, rate);
     }
     __syncwarp();
+    TRK_EP(12);
     /* cumsumcorr(), src/sdrtrk.c:64-76 (overlay polarity is +1 for L1CA/SBAS/G1) */
     for (int i = lane; i < ntap; i += 32) {
         st->oldsumI[i] += st->oldI[i]; st->oldsumQ[i] += st->oldQ[i];
@@ -319,6 +323,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
     if (mode == 1) trk_loops_warp(st, &ch->prm1, ch->ctime, ch, lane);
     else if (mode == 2) trk_loops_warp(st, &ch->prm2, (double)ch->loopms / 1000, ch, lane);
     __syncwarp();
+    TRK_EP(13);
     /* setobsdata(), src/sdrtrk.c:160-209, called after the loop filters of a synchronised
      * channel (src/sdrmain.c:285-304).  Only slot [0] of the interpolation stocks lives on
      * the device.  The +0.5 cycle polarity term (:186-195) is gated by nav.flagsyncf (frame
@@ -366,6 +371,8 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         st->buffloc += (uint64_t)st->currnsamp;
     }
     __syncwarp();
+    TRK_EP(14);
+#undef TRK_EP
 }
 
 struct trk_run_smem_t {
@@ -422,7 +429,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
 
     for (int it = 0; it < nperiods; it++) {
 #ifdef TRK_DEBUG
-        if (threadIdx.x == 0) g_dbg_on = (it == 50);
+        if (threadIdx.x == 0) g_dbg_on = (it == nperiods - 12);
         __syncthreads();
 #endif
         DBG(0);
@@ -474,6 +481,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             asm volatile("bar.arrive 2, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* carrier table + cleared accumulators: releases the workers */
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
             trk_carrier_rem(&sm->t);
+            DBG(11);
             if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[9] += trk_clock() - w0;
             /* remp is ready: the carrier warp's share of the end-of-correlation barrier.  It does
              * not wait there - the epilogue runs on the code warp - so a walk-ahead can overlap it */
@@ -495,6 +503,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                     sm->nx_n = ok ? n2 : -1;
                 }
                 __syncwarp();
+                DBG(12);
             }
         } else if (wid == (TRK_NCO_B >> 5)) {
             if (!have) trk_walk_code(&sm->t, ch->ti, n, st->codefreq, st->remcode, smax, ch->clen);
@@ -517,6 +526,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                     sm->nx_valid = ok;                  /* the carrier warp's verdict is nx_n >= 0 */
                 }
                 __syncwarp();
+                DBG(13);
             }
         } else {
             trk_bar_carrier();
@@ -531,7 +541,9 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         TRK_PT(4);
         DBG(9);
         if (wid == (TRK_NCO_B >> 5))
-            trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31);
+            trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31,
+                         (prof && blockIdx.x == 0) ? prof : nullptr);
+        if (wid == (TRK_NCO_B >> 5)) DBG(14);
         __syncthreads();
         if (recs) {
             const uint32_t *src = (const uint32_t *)&sm->rec;
@@ -647,7 +659,7 @@ extern "C" int sdrb200_trk_profile(sdrb200_trk_t *e, int on, long long *out7)
     }
     if (out7 && e->d_prof) {
         SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
-        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 12 * sizeof(long long), cudaMemcpyDeviceToHost));
+        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
         SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
     }
     if (!on && e->d_prof) { cudaFree(e->d_prof); e->d_prof = NULL; }
