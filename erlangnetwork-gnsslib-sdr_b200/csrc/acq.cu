@@ -48,6 +48,7 @@ struct sdrb200_acq {
     sdrb200_acq_cfg_t cfg;
     int n_eff, m_ref, M, L, R;
     int chunk;                       /* PRNs per scratch chunk                */
+    int fchunk;                      /* Doppler bins per scratch chunk (nfreq unless one PRN is too large) */
     double *h_freq;
     cudaStream_t st;
     float2 *d_tw;                    /* [M] forward twiddles                  */
@@ -321,13 +322,13 @@ __device__ void acq_row_stats(const float *Prow, int n, int nsampchip,
 template <int L>
 __global__ void __launch_bounds__(L / 16)
 k_row(const float2 *__restrict__ Xs, const float2 *__restrict__ Cs, const float2 *__restrict__ tw,
-      int R, int nfreq, int prn0, float2 *__restrict__ S, float *__restrict__ P, int n_eff,
+      int R, int nfreq, int prn0, int f0, int nfc, float2 *__restrict__ S, float *__restrict__ P, int n_eff,
       int nsampchip, int first_step, float invM2, acq_rowstat_t *__restrict__ rows,
       const int *__restrict__ frozen)
 {
     extern __shared__ float2 fsm[];
     constexpr int T = L / 16;
-    const int q = blockIdx.x, f = blockIdx.y, pc = blockIdx.z, p = prn0 + pc, tid = threadIdx.x;
+    const int q = blockIdx.x, fl = blockIdx.y, f = f0 + fl, pc = blockIdx.z, p = prn0 + pc, tid = threadIdx.x;
     if (frozen[p]) return;
     const float2 *x = Xs + ((size_t)f * R + q) * L;
     const float2 *c = Cs + ((size_t)p * R + q) * L;
@@ -336,7 +337,7 @@ k_row(const float2 *__restrict__ Xs, const float2 *__restrict__ Cs, const float2
     for (int e = 0; e < 16; e++) v[e] = cmulc(__ldg(&x[tid + e * T]), __ldg(&c[tid + e * T]));
     cta_fft<L, +1>(v, fsm, tw, R);
     if (R > 1) {
-        float2 *o = S + (((size_t)pc * nfreq + f) * R + q) * L;
+        float2 *o = S + (((size_t)pc * nfc + fl) * R + q) * L;
 #pragma unroll
         for (int e = 0; e < 16; e++) o[tid + e * T] = v[e];
         return;
@@ -362,13 +363,13 @@ k_row(const float2 *__restrict__ Xs, const float2 *__restrict__ Cs, const float2
  * accumulation (cpxconv flagsum, src/sdrcmn.c:244-246) + row statistics        */
 __global__ void __launch_bounds__(1024)
 k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L, int nfreq, int prn0,
-       float *__restrict__ P, int n_eff, int nsampchip, int first_step, float invM2,
+       int f0, int nfc, float *__restrict__ P, int n_eff, int nsampchip, int first_step, float invM2,
        acq_rowstat_t *__restrict__ rows, const int *__restrict__ frozen)
 {
-    const int f = blockIdx.x, pc = blockIdx.y, p = prn0 + pc;
+    const int fl = blockIdx.x, f = f0 + fl, pc = blockIdx.y, p = prn0 + pc;
     if (frozen[p]) return;
     const int M = R * L;
-    const float2 *s = S + ((size_t)pc * nfreq + f) * (size_t)M;
+    const float2 *s = S + ((size_t)pc * nfc + fl) * (size_t)M;
     float *Prow = P + ((size_t)p * nfreq + f) * n_eff;
     float tmax = -1.f; int tidx = 0x7fffffff;
     for (int t = threadIdx.x; t < n_eff; t += blockDim.x) {
@@ -385,6 +386,148 @@ k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L
     }
     __syncthreads();
     acq_row_stats(Prow, n_eff, nsampchip, tmax, tidx, &rows[(size_t)p * nfreq + f]);
+}
+
+/* G-point inverse DFT in registers, natural order: z[a] = sum_g z[g] exp(+2 pi i a g / G) */
+template <int G> __device__ __forceinline__ void fft_small_inv(float2 (&z)[G])
+{
+    if constexpr (G == 2) {
+        const float2 a = z[0], b = z[1]; z[0] = cadd(a, b); z[1] = csub(a, b);
+    } else if constexpr (G == 4) {
+        fft4<+1>(z[0], z[1], z[2], z[3]);
+    } else if constexpr (G == 8) {
+        float2 e0 = z[0], e1 = z[2], e2 = z[4], e3 = z[6];
+        float2 o0 = z[1], o1 = z[3], o2 = z[5], o3 = z[7];
+        fft4<+1>(e0, e1, e2, e3);
+        fft4<+1>(o0, o1, o2, o3);
+        o1 = cw16<+1, 2>(o1); o2 = cw16<+1, 4>(o2); o3 = cw16<+1, 6>(o3);
+        z[0] = cadd(e0, o0); z[1] = cadd(e1, o1); z[2] = cadd(e2, o2); z[3] = cadd(e3, o3);
+        z[4] = csub(e0, o0); z[5] = csub(e1, o1); z[6] = csub(e2, o2); z[7] = csub(e3, o3);
+    } else {
+        static_assert(G == 16, "unsupported group count");
+        fft16<+1>(z);
+    }
+}
+
+/* recombination of the R = 16*G sub-transforms of a row as a real radix-R butterfly
+ * (replaces the direct O(R) sum per lag of k_comb): one CTA of G warps takes 32 consecutive
+ * t' of one (bin, PRN) row.  Thread (warp g, lane) loads y_q[t'] for q = g + G*j (coalesced:
+ * a warp reads 256 contiguous bytes per q), applies conj(W_M^(t' q)), transforms over j in
+ * registers (16 points), applies W_R^(a2 g), and after one shared-memory transpose finishes
+ * the G-point transform over g for its share of a2.  Output a = a2 + 16*a1 is lag
+ * t = t' + L*a: power, accumulation into P (cpxconv flagsum, src/sdrcmn.c:244-246) and the
+ * PRN's argmax key (power bits : ~flat index, as in k_rowc) follow.  Only lags < n_eff are
+ * formed.                                                                                */
+template <int G>
+__global__ void __launch_bounds__(32 * G)
+k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, int nfreq, int prn0, int f0,
+           int nfc, float *__restrict__ P, int n_eff, int first_step, float invM2,
+           unsigned long long *__restrict__ key, const int *__restrict__ frozen)
+{
+    extern __shared__ float2 xsm[];                       /* [16 a2][G g][32 lanes] */
+    __shared__ unsigned long long s_k[32];
+    constexpr int R = 16 * G, A2 = 16 / G;                /* a2 values finished per warp */
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int tp = blockIdx.x * 32 + lane, fl = blockIdx.y, f = f0 + fl, pc = blockIdx.z, p = prn0 + pc;
+    if (frozen[p]) return;
+    const int M = R * L;
+    const float2 *s = S + ((size_t)pc * nfc + fl) * (size_t)M;
+    float2 v[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) v[j] = __ldg(&s[(size_t)(g + G * j) * L + tp]);
+    {
+        /* conj(W_M^(t' (g + G j))) = wg * ws^j ; powers of ws by the doubling scheme of the
+         * CTA transform (depth 4), so the rounding error does not grow with j            */
+        float2 wg = __ldg(&tw[(tp * g) & (M - 1)]); wg.y = -wg.y;
+        float2 w1 = __ldg(&tw[(tp * G) & (M - 1)]); w1.y = -w1.y;
+        float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1), w4 = cmul(w2, w2);
+        float2 w5 = cmul(w4, w1), w6 = cmul(w3, w3), w7 = cmul(w4, w3), w8 = cmul(w4, w4);
+        float2 w9 = cmul(w8, w1), w10 = cmul(w5, w5), w11 = cmul(w8, w3), w12 = cmul(w6, w6);
+        float2 w13 = cmul(w8, w5), w14 = cmul(w7, w7), w15 = cmul(w8, w7);
+        v[0] = cmul(v[0], wg);
+        v[1] = cmul(v[1], cmul(w1, wg));   v[2] = cmul(v[2], cmul(w2, wg));   v[3] = cmul(v[3], cmul(w3, wg));
+        v[4] = cmul(v[4], cmul(w4, wg));   v[5] = cmul(v[5], cmul(w5, wg));   v[6] = cmul(v[6], cmul(w6, wg));
+        v[7] = cmul(v[7], cmul(w7, wg));   v[8] = cmul(v[8], cmul(w8, wg));   v[9] = cmul(v[9], cmul(w9, wg));
+        v[10] = cmul(v[10], cmul(w10, wg)); v[11] = cmul(v[11], cmul(w11, wg)); v[12] = cmul(v[12], cmul(w12, wg));
+        v[13] = cmul(v[13], cmul(w13, wg)); v[14] = cmul(v[14], cmul(w14, wg)); v[15] = cmul(v[15], cmul(w15, wg));
+    }
+    fft16<+1>(v);                                         /* over j: v[a2] = U_g[a2] */
+#pragma unroll
+    for (int a2 = 0; a2 < 16; a2++) {
+        float2 u = v[a2];
+        if (a2 > 0) { float2 w = __ldg(&tw[(size_t)(a2 * g) * L]); w.y = -w.y; u = cmul(u, w); }   /* W_R^(a2 g) */
+        xsm[(a2 * G + g) * 32 + lane] = u;
+    }
+    __syncthreads();
+    float *Prow = P + ((size_t)p * nfreq + f) * n_eff;
+    float bv = -1.f; int bt = 0;
+#pragma unroll
+    for (int i = 0; i < A2; i++) {
+        const int a2 = g * A2 + i;
+        float2 z[G];
+#pragma unroll
+        for (int gg = 0; gg < G; gg++) z[gg] = xsm[(a2 * G + gg) * 32 + lane];
+        fft_small_inv<G>(z);
+#pragma unroll
+        for (int a1 = 0; a1 < G; a1++) {
+            const int t = tp + L * (a2 + 16 * a1);
+            if (t < n_eff) {
+                float pw = (z[a1].x * z[a1].x + z[a1].y * z[a1].y) * invM2;
+                if (!first_step) pw += Prow[t];
+                Prow[t] = pw;
+                if (pw > bv || (pw == bv && t < bt)) { bv = pw; bt = t; }
+            }
+        }
+    }
+    unsigned long long b = 0ull;
+    if (bv >= 0.f)
+        b = ((unsigned long long)__float_as_uint(bv) << 32) |
+            (unsigned long long)(0xffffffffu - ((unsigned int)f * (unsigned int)n_eff + (unsigned int)bt));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+        if (ob > b) b = ob;
+    }
+    if (lane == 0) s_k[g] = b;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < G; w++) if (s_k[w] > b) b = s_k[w];
+        if (b) atomicMax(&key[p], b);
+    }
+}
+
+/* checkacquisition() on the scratch path: the winning row of every PRN is read back from
+ * the power matrix (masked mean, second maximum with the data[0] seed, C/N0, peak ratio,
+ * decision, early-exit freeze: src/sdracq.c:71-95, 38-42)                               */
+__global__ void __launch_bounds__(1024)
+k_peak_hbm(const float *__restrict__ P, unsigned long long *__restrict__ key, int nfreq, int n_eff, int nsampchip,
+           const double *__restrict__ freq, double ctime, double thresh, int step,
+           sdrb200_acq_result_t *__restrict__ res, int *__restrict__ frozen)
+{
+    __shared__ acq_rowstat_t s_row;
+    const int p = blockIdx.x;
+    if (frozen[p]) return;
+    const unsigned long long k = key[p];
+    const unsigned int flat = k ? 0xffffffffu - (unsigned int)(k & 0xffffffffu) : 0u;
+    const int f = (int)(flat / (unsigned int)n_eff), codei = (int)(flat - (unsigned int)f * (unsigned int)n_eff);
+    const float maxp = __uint_as_float((unsigned int)(k >> 32));
+    /* every thread proposes the known peak: the block argmax of acq_row_stats returns it */
+    acq_row_stats(P + ((size_t)p * nfreq + f) * n_eff, n_eff, nsampchip, maxp, codei, &s_row);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const acq_rowstat_t r = s_row;
+        sdrb200_acq_result_t o;
+        o.maxp = (double)r.maxp; o.maxp2 = (double)r.max2;
+        o.meanp = r.sum / (double)r.cnt;
+        o.cn0 = 10 * log10(o.maxp / o.meanp / ctime);
+        o.peakr = o.maxp / o.maxp2;
+        o.codei = r.codei; o.freqi = f; o.acqfreq = freq[f];
+        o.acquired = (o.peakr > thresh) ? 1 : 0;
+        o.nintg = step + 1;
+        res[p] = o;
+        if (o.acquired) frozen[p] = 1;
+        key[p] = 0ull;                                             /* next integration step */
+    }
 }
 
 /* checkacquisition() for one PRN from its row statistics (src/sdracq.c:71-95)
@@ -516,16 +659,14 @@ k_rowc(const acq_rowc_args A)
             /* y_q[t'] into own shared memory; W_M^(-t' q) is applied by the reader */
 #pragma unroll
             for (int e = 0; e < 16; e++) fsm[tid + e * T] = v[e];
-            /* publish: the CTA barrier orders every thread's shared-memory stores before the
-             * arrive; the peers read the same physical shared memory (it is not cached), so
-             * the relaxed cluster barrier is enough and the cluster-scope fence
-             * (MEMBAR + L1 invalidate, 12 % of the stall samples in profiles/r1b) is left out.
-             * -DSDRB200_ROWC_FENCE puts it back; tests/test_gpu_acquisition.py
-             * test_acq_cluster_exchange_repeatable checks bit-identical power over repeats */
+            /* publish: CTA barrier, then ONE thread issues the cluster-scope release fence
+             * (cumulative over the stores the barrier made visible to it; every thread doing
+             * it costs a memory barrier per warp), relaxed arrive by all.  Leaving the fence
+             * out is 5 % faster and NOT safe: remote reads were seen to overtake the stores
+             * (tests/test_gpu_acquisition.py::test_acq_cluster_exchange_repeatable failed once
+             * in four runs of 60 repeats without it).                                      */
             __syncthreads();
-#ifdef SDRB200_ROWC_FENCE
             if (tid == 0) asm volatile("fence.acq_rel.cluster;" ::: "memory");
-#endif
             cl_arrive_relaxed();
             float2 wj[J];
 #pragma unroll
@@ -681,17 +822,44 @@ template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int
     return SDRB200_OK;
 }
 
-template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int first_step)
+template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc,
+                                       int first_step)
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
-    dim3 grid(a->R, a->cfg.nfreq, nprn);
+    dim3 grid(a->R, nfc, nprn);
     const float invM2 = 1.0f / ((float)a->M * (float)a->M);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_row<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, a->d_S, a->d_P,
+    k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, f0, nfc, a->d_S, a->d_P,
                                          a->n_eff, a->cfg.nsampchip, first_step, invM2, a->d_row, a->d_frozen);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
+}
+
+/* radix-R recombination (R = 16 G, G = 2, 4, 8, 16); 0 if R has no such kernel */
+static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256; }
+template <int G> static int launch_comb_fft_g(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc,
+                                              int first_step)
+{
+    const size_t smem = sizeof(float2) * 16 * G * 32;
+    dim3 grid(a->L / 32, nfc, nprn);
+    const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_comb_fft<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_comb_fft<G><<<grid, 32 * G, smem, st>>>(a->d_S, a->d_tw, a->L, a->cfg.nfreq, prn0, f0, nfc, a->d_P, a->n_eff,
+                                              first_step, invM2, a->d_key, a->d_frozen);
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
+static int launch_comb_fft(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc, int first_step)
+{
+    switch (a->R) {
+    case 32:  return launch_comb_fft_g<2>(st, a, prn0, nprn, f0, nfc, first_step);
+    case 64:  return launch_comb_fft_g<4>(st, a, prn0, nprn, f0, nfc, first_step);
+    case 128: return launch_comb_fft_g<8>(st, a, prn0, nprn, f0, nfc, first_step);
+    case 256: return launch_comb_fft_g<16>(st, a, prn0, nprn, f0, nfc, first_step);
+    }
+    return SDRB200_EINVAL;
 }
 
 template <int L, int R, int MODE> static int launch_rowc(cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
@@ -791,6 +959,16 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
         size_t per_prn = (size_t)nfreq * M * sizeof(float2);
         size_t budget = (size_t)64 << 20;
         a->chunk = (int)(budget / per_prn); if (a->chunk < 1) a->chunk = 1; if (a->chunk > nprn) a->chunk = nprn;
+        /* one PRN's bins alone exceed the budget (20 ms coherent blocks: 8.4 MB per row):
+         * the chunk becomes a group of bins of one PRN                                  */
+        a->fchunk = nfreq;
+        if (per_prn > budget) {
+            a->fchunk = (int)(budget / ((size_t)M * sizeof(float2)));
+            if (a->fchunk < 1) a->fchunk = 1;
+            if (a->fchunk > nfreq) a->fchunk = nfreq;
+        }
+        const char *env = getenv("SDRB200_FCHUNK");
+        if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }
     }
     int rc = SDRB200_OK;
 #define ACQ_ALLOC(ptr, bytes) if (rc == SDRB200_OK && cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) { \
@@ -800,7 +978,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     ACQ_ALLOC(a->d_cidx, (size_t)nfreq * M);                    /* row stride M: 16-byte aligned rows */
     ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)nfreq * M);
     ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
-    if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * nfreq * M);
+    if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * a->fchunk * M);
     /* the power matrix is kept in HBM only when it has to be: accumulation over
      * several integrations, the scratch path, or on request (sdrb200_acq_keep_power) */
     if (!a->fused || a->cfg.intg > 1) ACQ_ALLOC(a->d_P, sizeof(float) * (size_t)nprn * nfreq * n_eff);
@@ -952,26 +1130,43 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
             ACQ_T1(a, 3);
             continue;
         }
+        /* scratch path: sub-transforms of a chunk of rows go through d_S (sized to stay in L2),
+         * then the radix-R recombination; SDRB200_ACQ_COMB_NAIVE selects the direct-sum
+         * combine with per-row statistics (kept as a cross-check)                        */
+        const int use_fft = (a->R > 1) && comb_fft_supported(a->R) && !getenv("SDRB200_ACQ_COMB_NAIVE");
         for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
             const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
-            ACQ_T0(a);
-            ACQ_DISPATCH_L(a->L, (launch_row<LL>(a->st, a, p0, np, step == 0)));
-            if (rc) return rc;
-            ACQ_T1(a, 1);
-            if (a->R > 1) {
-                dim3 grid(c->nfreq, np);
-                const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+            for (int f0 = 0; f0 < c->nfreq; f0 += a->fchunk) {
+                const int nfc = (c->nfreq - f0 < a->fchunk) ? c->nfreq - f0 : a->fchunk;
                 ACQ_T0(a);
-                k_comb<<<grid, 1024, 0, a->st>>>(a->d_S, a->d_tw, a->R, a->L, c->nfreq, p0, a->d_P, a->n_eff,
-                                                 c->nsampchip, step == 0, invM2, a->d_row, a->d_frozen);
-                sdrb200_count_launch(1);
-                SDRB200_CUDA_TRY(cudaGetLastError());
-                ACQ_T1(a, 2);
+                ACQ_DISPATCH_L(a->L, (launch_row<LL>(a->st, a, p0, np, f0, nfc, step == 0)));
+                if (rc) return rc;
+                ACQ_T1(a, 1);
+                if (a->R > 1) {
+                    ACQ_T0(a);
+                    if (use_fft) {
+                        rc = launch_comb_fft(a->st, a, p0, np, f0, nfc, step == 0);
+                        if (rc) return rc;
+                    } else {
+                        dim3 grid(nfc, np);
+                        const float invM2 = 1.0f / ((float)a->M * (float)a->M);
+                        k_comb<<<grid, 1024, 0, a->st>>>(a->d_S, a->d_tw, a->R, a->L, c->nfreq, p0, f0, nfc, a->d_P, a->n_eff,
+                                                         c->nsampchip, step == 0, invM2, a->d_row, a->d_frozen);
+                        sdrb200_count_launch(1);
+                        SDRB200_CUDA_TRY(cudaGetLastError());
+                    }
+                    ACQ_T1(a, 2);
+                }
             }
         }
         ACQ_T0(a);
-        k_final<<<c->nprn, 128, 0, a->st>>>(a->d_row, c->nfreq, a->d_freq, c->ctime, c->threshold, step,
-                                           a->d_res, a->d_frozen);
+        if (use_fft) {
+            k_peak_hbm<<<c->nprn, 1024, 0, a->st>>>(a->d_P, a->d_key, c->nfreq, a->n_eff, c->nsampchip, a->d_freq,
+                                                    c->ctime, c->threshold, step, a->d_res, a->d_frozen);
+        } else {
+            k_final<<<c->nprn, 128, 0, a->st>>>(a->d_row, c->nfreq, a->d_freq, c->ctime, c->threshold, step,
+                                               a->d_res, a->d_frozen);
+        }
         sdrb200_count_launch(1);
         SDRB200_CUDA_TRY(cudaGetLastError());
         ACQ_T1(a, 3);

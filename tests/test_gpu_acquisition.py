@@ -181,10 +181,10 @@ def test_acq_glonass_g1_fdma(sdr):
 
 
 def test_acq_cluster_exchange_repeatable(sdr):
-    """The sub-transforms of a row cross the cluster through distributed shared memory
-    behind a CTA barrier and a relaxed cluster barrier (no cluster-scope fence).  A read
-    that overtook its producer would change power values: 60 repeated searches of the
-    same window must give the identical power matrix, bit for bit, and identical tuples."""
+    """The sub-transforms of a row cross the cluster through distributed shared memory behind
+    a CTA barrier, one cluster-scope release fence and a relaxed cluster barrier.  A read that
+    overtook its producer changes power values (seen when the fence was left out): 60 repeated
+    searches of the same window must give the identical power matrix, bit for bit."""
     cfg, vis = util.scene_c1(sdr, nsats=4)
     prns = vis + [2, 4, 5, 7]
     nsamp, avail = 16368, 65536
@@ -197,7 +197,7 @@ def test_acq_cluster_exchange_repeatable(sdr):
     first = acq.run(st, b0)
     P0 = [acq.power(i).copy() for i in range(len(prns))]
     plain = sdr.Acquisition(util.FS1, 1, nsamp, 16, 1e-3, freq, codes, 1.023e6, intg=1)
-    for rep in range(60):
+    for rep in range(120):
         assert acq.run(st, b0) == first
         assert plain.run(st, b0) == first                       # register-only variant (no P)
         if rep % 6 == 0:
