@@ -388,25 +388,102 @@ k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L
     acq_row_stats(Prow, n_eff, nsampchip, tmax, tidx, &rows[(size_t)p * nfreq + f]);
 }
 
-/* G-point inverse DFT in registers, natural order: z[a] = sum_g z[g] exp(+2 pi i a g / G) */
-template <int G> __device__ __forceinline__ void fft_small_inv(float2 (&z)[G])
+/* G-point DFT in registers, natural order: z[a] = sum_g z[g] exp(SIGN 2 pi i a g / G) */
+template <int G, int SIGN> __device__ __forceinline__ void fft_small(float2 (&z)[G])
 {
     if constexpr (G == 2) {
         const float2 a = z[0], b = z[1]; z[0] = cadd(a, b); z[1] = csub(a, b);
     } else if constexpr (G == 4) {
-        fft4<+1>(z[0], z[1], z[2], z[3]);
+        fft4<SIGN>(z[0], z[1], z[2], z[3]);
     } else if constexpr (G == 8) {
         float2 e0 = z[0], e1 = z[2], e2 = z[4], e3 = z[6];
         float2 o0 = z[1], o1 = z[3], o2 = z[5], o3 = z[7];
-        fft4<+1>(e0, e1, e2, e3);
-        fft4<+1>(o0, o1, o2, o3);
-        o1 = cw16<+1, 2>(o1); o2 = cw16<+1, 4>(o2); o3 = cw16<+1, 6>(o3);
+        fft4<SIGN>(e0, e1, e2, e3);
+        fft4<SIGN>(o0, o1, o2, o3);
+        o1 = cw16<SIGN, 2>(o1); o2 = cw16<SIGN, 4>(o2); o3 = cw16<SIGN, 6>(o3);
         z[0] = cadd(e0, o0); z[1] = cadd(e1, o1); z[2] = cadd(e2, o2); z[3] = cadd(e3, o3);
         z[4] = csub(e0, o0); z[5] = csub(e1, o1); z[6] = csub(e2, o2); z[7] = csub(e3, o3);
     } else {
         static_assert(G == 16, "unsupported group count");
-        fft16<+1>(z);
+        fft16<SIGN>(z);
     }
+}
+
+/* Forward transform of long windows (R = 16 G sub-transforms, the scratch path) in two
+ * passes, decimation in frequency: X[R j + q] = FFT_L over t of  W_M^(t q) * sum_a x[t + L a] W_R^(a q).
+ * Pass 1 (k_fwd_split): carrier wipe-off (mixcarr table lookup, src/sdrcmn.c:650-662, and the
+ * 1/(32 m) scale of pcorrelator, :764) fused into the R-point transform over a for 32
+ * consecutive t per CTA - thread (warp g, lane) owns a = g + G j, 16 points in registers, then a
+ * shared-memory transpose and the G-point stage - times W_M^(t q), written as row q of the
+ * spectrum buffer.  Pass 2 (k_fft_rows): the L-point CTA transform of every row in place,
+ * which leaves X[R j + q] at [q][j], the layout the row kernels read.  (k_fwd_if, used up to
+ * R = 8, accumulates the R blocks per CTA: O(M R) per bin.)                                 */
+template <int G, int DT>
+__global__ void __launch_bounds__(32 * G)
+k_fwd_split(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict__ cidx, int cidx_stride,
+            float scale, const float2 *__restrict__ tw, int L, float2 *__restrict__ out)
+{
+    extern __shared__ float2 xsm[];                       /* [16 q2][G g][32 lanes] */
+    __shared__ float2 s_lut[32];
+    constexpr int R = 16 * G, A2 = 16 / G;
+    const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int t = blockIdx.x * 32 + lane, f = blockIdx.y;
+    const int M = R * L;
+    if (threadIdx.x < 32) s_lut[threadIdx.x] = make_float2(c_cosf[threadIdx.x] * scale, c_sinf[threadIdx.x] * scale);
+    __syncthreads();
+    const uint8_t *ci = cidx + (size_t)f * cidx_stride;
+    float2 v[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+        const int k = t + L * (g + G * j);
+        v[j] = make_float2(0.f, 0.f);
+        if (k < nlive) {
+            const float2 lu = s_lut[ci[k] & 31];
+            if (DT == 1) {
+                const float x = (float)win[k];
+                v[j] = make_float2(x * lu.x, x * lu.y);
+            } else {
+                const float x0 = (float)win[2 * k], x1 = (float)win[2 * k + 1];
+                v[j] = make_float2(x0 * lu.x - x1 * lu.y, x0 * lu.y + x1 * lu.x);
+            }
+        }
+    }
+    fft16<-1>(v);                                         /* over j: v[q2] = U_g[q2] */
+#pragma unroll
+    for (int q2 = 0; q2 < 16; q2++) {
+        float2 u = v[q2];
+        if (q2 > 0) u = cmul(u, __ldg(&tw[(size_t)(q2 * g) * L]));          /* W_R^(q2 g) */
+        xsm[(q2 * G + g) * 32 + lane] = u;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < A2; i++) {
+        const int q2 = g * A2 + i;
+        float2 z[G];
+#pragma unroll
+        for (int gg = 0; gg < G; gg++) z[gg] = xsm[(q2 * G + gg) * 32 + lane];
+        fft_small<G, -1>(z);
+#pragma unroll
+        for (int q1 = 0; q1 < G; q1++) {
+            const int q = q2 + 16 * q1;
+            out[((size_t)f * R + q) * L + t] = cmul(z[q1], __ldg(&tw[(t * q) & (M - 1)]));
+        }
+    }
+}
+
+template <int L>
+__global__ void __launch_bounds__(L / 16)
+k_fft_rows(float2 *__restrict__ X, const float2 *__restrict__ tw, int R)
+{
+    extern __shared__ float2 fsm[];
+    constexpr int T = L / 16;
+    float2 *row = X + ((size_t)blockIdx.y * R + blockIdx.x) * L;
+    float2 v[16];
+#pragma unroll
+    for (int e = 0; e < 16; e++) v[e] = row[threadIdx.x + e * T];
+    cta_fft<L, -1>(v, fsm, tw, R);
+#pragma unroll
+    for (int e = 0; e < 16; e++) row[threadIdx.x + e * T] = v[e];
 }
 
 /* recombination of the R = 16*G sub-transforms of a row as a real radix-R butterfly
@@ -467,7 +544,7 @@ k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, i
         float2 z[G];
 #pragma unroll
         for (int gg = 0; gg < G; gg++) z[gg] = xsm[(a2 * G + gg) * 32 + lane];
-        fft_small_inv<G>(z);
+        fft_small<G, +1>(z);
 #pragma unroll
         for (int a1 = 0; a1 < G; a1++) {
             const int t = tp + L * (a2 + 16 * a1);
@@ -836,6 +913,42 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
     return SDRB200_OK;
 }
 
+/* two-pass forward transform of the IF window for R = 16 G */
+template <int G> static int launch_fwd_split_g(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+{
+    const size_t smem = sizeof(float2) * 16 * G * 32;
+    dim3 grid(a->L / 32, a->cfg.nfreq);
+    if (a->cfg.dtype == 1) {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_split<G, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_fwd_split<G, 1><<<grid, 32 * G, smem, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+    } else {
+        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_split<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_fwd_split<G, 2><<<grid, 32 * G, smem, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+    }
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
+template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *a)
+{
+    const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fft_rows<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_fft_rows<L><<<dim3(a->R, a->cfg.nfreq), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R);
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
+static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+{
+    switch (a->R) {
+    case 32:  return launch_fwd_split_g<2>(st, a, win, scale);
+    case 64:  return launch_fwd_split_g<4>(st, a, win, scale);
+    case 128: return launch_fwd_split_g<8>(st, a, win, scale);
+    case 256: return launch_fwd_split_g<16>(st, a, win, scale);
+    }
+    return SDRB200_EINVAL;
+}
+
 /* radix-R recombination (R = 16 G, G = 2, 4, 8, 16); 0 if R has no such kernel */
 static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256; }
 template <int G> static int launch_comb_fft_g(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc,
@@ -1109,8 +1222,14 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
         const int8_t *win = base + pos * c->dtype;
         ACQ_T0(a);
-        ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
-                                             a->M, scale, a->d_tw, a->d_Xs)));
+        if (!a->fused && comb_fft_supported(a->R) && !getenv("SDRB200_ACQ_COMB_NAIVE")) {
+            rc = launch_fwd_split(a->st, a, win, scale);
+            if (rc) return rc;
+            ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a)));
+        } else {
+            ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
+                                                 a->M, scale, a->d_tw, a->d_Xs)));
+        }
         if (rc) return rc;
         ACQ_T1(a, 0);
         if (a->fused) {
