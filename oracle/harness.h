@@ -91,6 +91,13 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
                  uint64_t avail, int nprn, const int *prn, const int *ctype,
                  int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked);
 
+/* As oh_acq_track, but with the reference's threading model: one pthread per acquired
+ * channel runs the tracking loop (src/sdrmain.c:168-175, 231-315); the whole stream must
+ * fit the ring.  Only the builds of replay.c provide it (reference, b200 drop-in).        */
+int oh_acq_track_mt(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamples,
+                    uint64_t avail, int nprn, const int *prn, const int *ctype,
+                    int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked);
+
 /* Thin pass-throughs to single hot functions, for unit-level parity. */
 void oh_correlator(const signed char *data, int dtype, double ti, int n,
                    double freq, double phi0, double crate, double coff,

@@ -182,11 +182,69 @@ int oh_acquire(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsample
     return 0;
 }
 
+/* one code period of one channel: the body of the while loop of sdrthread()
+ * (src/sdrmain.c:264-312) plus the record; returns 1 if a period was tracked.
+ * rec points at the channel's own row of records.                                */
+static int track_period(sdrch_t *sdr, uint64_t *buffloc, uint64_t *cnt, uint64_t *loopcnt,
+                        oh_trkrec_t *rec, int *ntracked)
+{
+    oh_trkrec_t *r;
+    int k, flagobs = 0;
+    sdrtracking(sdr, (*buffloc), (*cnt));
+    if (!sdr->flagtrk) return 0;                 /* cannot happen after the feed */
+
+    cumsumcorr(&sdr->trk, sdr->nav.ocode[sdr->nav.ocodei]);
+    sdr->trk.flagloopfilter = 0;
+    flagobs = 0;
+    if (!sdr->nav.flagsync) {
+        pll(sdr, &sdr->trk.prm1, sdr->ctime);
+        dll(sdr, &sdr->trk.prm1, sdr->ctime);
+        sdr->trk.flagloopfilter = 1;
+    } else if (sdr->nav.swloop) {
+        pll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
+        dll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
+        sdr->trk.flagloopfilter = 2;
+        if ((*loopcnt) % (SNSMOOTHMS / sdr->trk.loopms) == 0) {
+            setobsdata(sdr, (*buffloc), (*cnt), &sdr->trk, 1); flagobs = 2;
+        } else {
+            setobsdata(sdr, (*buffloc), (*cnt), &sdr->trk, 0); flagobs = 1;
+        }
+        (*loopcnt)++;
+    }
+
+    r = &rec[*ntracked];
+    r->cnt = (*cnt); r->buffloc = (*buffloc); r->currnsamp = sdr->currnsamp;
+    r->flagsync = sdr->nav.flagsync; r->flagsyncf = sdr->nav.flagsyncf;
+    r->flagtow = sdr->nav.flagtow; r->flagdec = sdr->nav.flagdec;
+    r->flagloopfilter = sdr->trk.flagloopfilter;
+    r->swsync = sdr->nav.swsync; r->swloop = sdr->nav.swloop;
+    r->synci = sdr->nav.synci; r->biti = sdr->nav.biti; r->bit = sdr->nav.bit;
+    for (k = 0; k < 1 + 2 * sdr->trk.corrn && k < OH_MAXTAPS; k++) {
+        r->II[k] = sdr->trk.II[k]; r->QQ[k] = sdr->trk.QQ[k];
+    }
+    r->sumI0 = sdr->trk.sumI[0]; r->sumQ0 = sdr->trk.sumQ[0];
+    r->codefreq = sdr->trk.codefreq; r->codeErr = sdr->trk.codeErr; r->codeNco = sdr->trk.codeNco;
+    r->carrfreq = sdr->trk.carrfreq; r->carrErr = sdr->trk.carrErr; r->carrNco = sdr->trk.carrNco;
+    r->freqErr = sdr->trk.freqErr;
+    r->remcode = sdr->trk.remcode; r->remcarr = sdr->trk.remcarr;
+    r->L0 = sdr->trk.L[0];
+    r->D0 = sdr->trk.D[0]; r->S0 = sdr->trk.S[0]; r->remcout0 = sdr->trk.remcout[0];
+    r->Isum = sdr->trk.Isum; r->obs_codei = sdr->trk.codei[0]; r->obs_cnt = sdr->trk.cntout[0];
+    r->flagobs = flagobs;
+
+    if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
+    (*cnt)++;
+    (*buffloc) += sdr->currnsamp;
+    sdr->trk.buffloc = (*buffloc);
+    (*ntracked)++;
+    return 1;
+}
+
 int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamples,
                  uint64_t avail, int nprn, const int *prn, const int *ctype,
                  int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked)
 {
-    int i, k, active, flagobs = 0;
+    int i, active;
     uint64_t *buffloc, *cnt, *loopcnt;
     if (avail % FILE_BUFFSIZE || avail > nsamples || nprn > MAXSAT) return -2;
     setup_ini(cfg);
@@ -209,68 +267,71 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
         active = 0;
         for (i = 0; i < nprn; i++) {
             sdrch_t *sdr = &sdrch[i];
-            oh_trkrec_t *r;
             uint64_t need;
             if (!sdr->flagacq || ntracked[i] >= nperiods) continue;
             /* stop when the stream cannot supply another full window */
             if (buffloc[i] + 2 * (uint64_t)sdr->nsamp + 200 > nsamples) continue;
             need = (buffloc[i] + 2 * (uint64_t)sdr->nsamp) / FILE_BUFFSIZE + 2;
             if (need > sdrstat.buffcnt) ring_feed(cfg, need);
-
-            sdrtracking(sdr, buffloc[i], cnt[i]);
-            if (!sdr->flagtrk) continue;                 /* cannot happen after the feed */
-            active = 1;
-
-            cumsumcorr(&sdr->trk, sdr->nav.ocode[sdr->nav.ocodei]);
-            sdr->trk.flagloopfilter = 0;
-            flagobs = 0;
-            if (!sdr->nav.flagsync) {
-                pll(sdr, &sdr->trk.prm1, sdr->ctime);
-                dll(sdr, &sdr->trk.prm1, sdr->ctime);
-                sdr->trk.flagloopfilter = 1;
-            } else if (sdr->nav.swloop) {
-                pll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
-                dll(sdr, &sdr->trk.prm2, (double)sdr->trk.loopms / 1000);
-                sdr->trk.flagloopfilter = 2;
-                if (loopcnt[i] % (SNSMOOTHMS / sdr->trk.loopms) == 0) {
-                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 1); flagobs = 2;
-                } else {
-                    setobsdata(sdr, buffloc[i], cnt[i], &sdr->trk, 0); flagobs = 1;
-                }
-                loopcnt[i]++;
-            }
-
-            r = &rec[(size_t)i * nperiods + ntracked[i]];
-            r->cnt = cnt[i]; r->buffloc = buffloc[i]; r->currnsamp = sdr->currnsamp;
-            r->flagsync = sdr->nav.flagsync; r->flagsyncf = sdr->nav.flagsyncf;
-            r->flagtow = sdr->nav.flagtow; r->flagdec = sdr->nav.flagdec;
-            r->flagloopfilter = sdr->trk.flagloopfilter;
-            r->swsync = sdr->nav.swsync; r->swloop = sdr->nav.swloop;
-            r->synci = sdr->nav.synci; r->biti = sdr->nav.biti; r->bit = sdr->nav.bit;
-            for (k = 0; k < 1 + 2 * sdr->trk.corrn && k < OH_MAXTAPS; k++) {
-                r->II[k] = sdr->trk.II[k]; r->QQ[k] = sdr->trk.QQ[k];
-            }
-            r->sumI0 = sdr->trk.sumI[0]; r->sumQ0 = sdr->trk.sumQ[0];
-            r->codefreq = sdr->trk.codefreq; r->codeErr = sdr->trk.codeErr; r->codeNco = sdr->trk.codeNco;
-            r->carrfreq = sdr->trk.carrfreq; r->carrErr = sdr->trk.carrErr; r->carrNco = sdr->trk.carrNco;
-            r->freqErr = sdr->trk.freqErr;
-            r->remcode = sdr->trk.remcode; r->remcarr = sdr->trk.remcarr;
-            r->L0 = sdr->trk.L[0];
-            r->D0 = sdr->trk.D[0]; r->S0 = sdr->trk.S[0]; r->remcout0 = sdr->trk.remcout[0];
-            r->Isum = sdr->trk.Isum; r->obs_codei = sdr->trk.codei[0]; r->obs_cnt = sdr->trk.cntout[0];
-            r->flagobs = flagobs;
-
-            if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
-            cnt[i]++;
-            buffloc[i] += sdr->currnsamp;
-            sdr->trk.buffloc = buffloc[i];
-            ntracked[i]++;
+            active |= track_period(sdr, &buffloc[i], &cnt[i], &loopcnt[i], rec + (size_t)i * nperiods, &ntracked[i]);
         }
     } while (active);
 
     for (i = 0; i < nprn; i++) freesdrch(&sdrch[i]);
     ring_release();
     free(buffloc);
+    return 0;
+}
+
+/* The same run with the reference's threading model: after the (sequential) acquisitions
+ * the whole stream is in the ring and every acquired channel is tracked by its OWN pthread,
+ * as sdrthread() does (src/sdrmain.c:168-175, 231-315), all of them calling sdrtracking /
+ * cumsumcorr / pll / dll / setobsdata concurrently.                                       */
+typedef struct {
+    sdrch_t *sdr; uint64_t buffloc, cnt, loopcnt, nsamples;
+    oh_trkrec_t *rec; int *ntracked; int nperiods;
+} mt_arg_t;
+
+static void *mt_channel(void *p)
+{
+    mt_arg_t *a = (mt_arg_t *)p;
+    while (*a->ntracked < a->nperiods &&
+           a->buffloc + 2 * (uint64_t)a->sdr->nsamp + 200 <= a->nsamples) {
+        if (!track_period(a->sdr, &a->buffloc, &a->cnt, &a->loopcnt, a->rec, a->ntracked)) break;
+    }
+    return NULL;
+}
+
+int oh_acq_track_mt(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamples,
+                    uint64_t avail, int nprn, const int *prn, const int *ctype,
+                    int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked)
+{
+    int i;
+    pthread_t th[MAXSAT];
+    mt_arg_t arg[MAXSAT];
+    if (avail % FILE_BUFFSIZE || avail > nsamples || nprn > MAXSAT) return -2;
+    if ((nsamples + FILE_BUFFSIZE - 1) / FILE_BUFFSIZE + 2 > MEMBUFFLEN) return -4;   /* ring must hold it all */
+    setup_ini(cfg);
+    if (ring_setup(cfg, if_data, nsamples) < 0) return -1;
+    ring_feed(cfg, avail / FILE_BUFFSIZE);
+    memset(rec, 0, sizeof(oh_trkrec_t) * (size_t)nprn * nperiods);
+    for (i = 0; i < nprn; i++) {
+        sdrch_t *sdr = &sdrch[i];
+        memset(&acq[i], 0, sizeof(acq[i]));
+        ntracked[i] = 0;
+        if (channel_init(cfg, i + 1, prn[i], ctype[i], sdr) < 0) { ring_release(); return -3; }
+        memset(&arg[i], 0, sizeof(arg[i]));
+        arg[i].buffloc = do_acquire(sdr, &acq[i], NULL);
+        arg[i].sdr = sdr; arg[i].nsamples = nsamples; arg[i].rec = rec + (size_t)i * nperiods;
+        arg[i].ntracked = &ntracked[i]; arg[i].nperiods = nperiods;
+    }
+    ring_feed(cfg, (nsamples + FILE_BUFFSIZE - 1) / FILE_BUFFSIZE + 1);
+    for (i = 0; i < nprn; i++)
+        if (sdrch[i].flagacq) pthread_create(&th[i], NULL, mt_channel, &arg[i]);
+    for (i = 0; i < nprn; i++)
+        if (sdrch[i].flagacq) pthread_join(th[i], NULL);
+    for (i = 0; i < nprn; i++) freesdrch(&sdrch[i]);
+    ring_release();
     return 0;
 }
 

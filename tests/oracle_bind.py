@@ -93,7 +93,8 @@ class Oracle:
         assert rc == 0, f"oh_acquire rc={rc}"
         return list(out), power
 
-    def acq_track(self, cfg, if_data, avail, prns, nperiods, ctypes=None):
+    def acq_track(self, cfg, if_data, avail, prns, nperiods, ctypes=None, threaded=False):
+        """threaded=True: one pthread per channel (oh_acq_track_mt, replay builds only)"""
         if_data = np.ascontiguousarray(if_data, np.int8)
         n = len(prns)
         prn_a = (C.c_int * n)(*prns)
@@ -102,9 +103,10 @@ class Oracle:
         rec = np.zeros(n * nperiods, dtype=np.dtype(OhTrkRec))
         ntr = (C.c_int * n)()
         nsamples = len(if_data) // cfg.dtype
-        rc = self.lib.oh_acq_track(C.byref(cfg), if_data.ctypes.data_as(_i8p), C.c_uint64(nsamples),
-                                   C.c_uint64(avail), n, prn_a, ct_a, int(nperiods), acq,
-                                   rec.ctypes.data_as(C.POINTER(OhTrkRec)), ntr)
+        fn = self.lib.oh_acq_track_mt if threaded else self.lib.oh_acq_track
+        rc = fn(C.byref(cfg), if_data.ctypes.data_as(_i8p), C.c_uint64(nsamples),
+                C.c_uint64(avail), n, prn_a, ct_a, int(nperiods), acq,
+                rec.ctypes.data_as(C.POINTER(OhTrkRec)), ntr)
         assert rc == 0, f"oh_acq_track rc={rc}"
         return list(acq), rec.reshape(n, nperiods), list(ntr)
 

@@ -50,3 +50,25 @@ def test_dropin_acquire_and_track(sdr, both):
     for f in ("currnsamp", "buffloc", "flagsync", "flagloopfilter", "swloop", "synci", "bit", "II", "QQ",
               "carrfreq", "codefreq", "remcode", "remcarr"):
         assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
+
+
+def test_dropin_one_pthread_per_channel(sdr, both):
+    """The reference runs every channel in its own pthread (src/sdrmain.c:168-175): the same
+    replay with one thread per channel, all calling the drop-in's sdrtracking / correlator /
+    pll / dll concurrently, must reproduce the sequential run - and the reference's - bit for
+    bit (host libm on both sides), observables included."""
+    ref, drop = both
+    cfg, vis = util.scene_c5(sdr, nsats=6, seed=0xB2000032)
+    nper = 2600
+    host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
+    cfgo = ob.cfg_rtlsdr(acq_intg=3)
+    a0, r0, n0 = ref.acq_track(cfgo, host, 65536, vis, nper)
+    a1, r1, n1 = drop.acq_track(cfgo, host, 65536, vis, nper)
+    a2, r2, n2 = drop.acq_track(cfgo, host, 65536, vis, nper, threaded=True)
+    a3, r3, n3 = ref.acq_track(cfgo, host, 65536, vis, nper, threaded=True)
+    assert n0 == n1 == n2 == n3 and sum(a.acquired for a in a0) >= 5
+    for f in ("cnt", "currnsamp", "buffloc", "flagsync", "flagloopfilter", "swloop", "synci", "bit", "II", "QQ",
+              "carrfreq", "codefreq", "remcode", "remcarr", "L0", "D0", "flagobs"):
+        base = np.ascontiguousarray(r0[f])
+        for other in (r1, r2, r3):
+            assert np.array_equal(base, np.ascontiguousarray(other[f])), f
