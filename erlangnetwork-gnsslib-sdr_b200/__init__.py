@@ -100,7 +100,8 @@ class TrkRec(C.Structure):
                 ("remcode", C.c_double), ("remcarr", C.c_double),
                 ("L0", C.c_double), ("D0", C.c_double), ("S0", C.c_double), ("remcout0", C.c_double),
                 ("Isum", C.c_double), ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64),
-                ("flagobs", C.c_int32), ("pad2", C.c_int32)]
+                ("flagobs", C.c_int32), ("flagsyncf", C.c_int32), ("polarity", C.c_int32), ("flagtow", C.c_int32),
+                ("firstsf", C.c_uint64), ("firstsfcnt", C.c_uint64)]
 
 
 def loop_coeffs(dllb: float, pllb: float, fllb: float) -> Loop:

@@ -36,7 +36,8 @@
 
 typedef struct {
     int      prn;              /* code number (index into the code table)   */
-    int      nav_on;           /* 1: 50 bps random data, 0: all +1          */
+    int      nav_on;           /* 0: all +1, 1: 50 bps random data, 2: 50 bps GPS LNAV subframes
+                                * (preamble, TOW count, valid (32,26) parity in every word) */
     double   cn0_dbhz;         /* carrier-to-noise density                  */
     double   doppler_hz;       /* carrier Doppler at t=0                    */
     double   doppler_rate;     /* Hz/s                                      */
@@ -82,6 +83,35 @@ IFGEN_HD int ifgen_navbit(uint64_t nav_seed, int64_t bit)
     return (ifgen_mix64(nav_seed ^ (uint64_t)bit * 0xD6E8FEB86659FD93ULL) & 1) ? 1 : -1;
 }
 
+/* nav_on == 2: bit b of an endless train of GPS LNAV subframes (300 bits: ten 30-bit words,
+ * IS-GPS-200 20.3.5).  Word 1 starts with the preamble 10001011, word 2 carries a non-zero
+ * 17-bit TOW count and a subframe ID cycling 1..3, the other data bits are pseudo-random.
+ * The last two data bits of EVERY word are solved so that its parity bits D29 = D30 = 0 (what
+ * the real message does in words 2 and 10), which makes every word independent of its
+ * predecessor: a bit is a pure function of (seed, b).  Logical 1 is sent as -1, the sign
+ * convention of the reference's checkbit()/paritycheck_l1ca() (src/sdrnav.c:265-270,
+ * src/sdrnav_gps.c:141-166).                                                            */
+IFGEN_HD int ifgen_parity32(uint32_t v) { v ^= v >> 16; v ^= v >> 8; v ^= v >> 4; return (0x6996u >> (v & 15u)) & 1u; }
+IFGEN_HD int ifgen_lnavbit(uint64_t nav_seed, int64_t bit)
+{
+    const int64_t sf = bit / 300;
+    const int r = (int)(bit - sf * 300), wi = r / 30, k = r - wi * 30;      /* word, bit in word */
+    uint32_t w = (uint32_t)(ifgen_mix64(nav_seed ^ (uint64_t)(sf * 10 + wi) * 0xD6E8FEB86659FD93ULL) >> 20) & 0xFFFFFCu;
+    uint32_t word;
+    int d24, d23;
+    if (wi == 0) w = (w & 0x00FFFFu) | (0x8Bu << 16);                       /* preamble 10001011 */
+    if (wi == 1) {
+        const uint32_t tow = (uint32_t)((sf + 1 + (int64_t)(nav_seed & 0xFFFF)) % 100799) + 1;   /* 1..100799 */
+        w = (tow << 7) | ((uint32_t)(sf % 3 + 1) << 2);                     /* TOW | alert, AS = 0 | ID | t t */
+    }
+    d24 = ifgen_parity32(w & 0xAEC7CCu);                                    /* forces D29 = 0 */
+    d23 = ifgen_parity32(w & 0x2DEA24u) ^ d24;                              /* forces D30 = 0 */
+    w |= ((uint32_t)d23 << 1) | (uint32_t)d24;
+    word = (w << 6) | ((uint32_t)ifgen_parity32(w & 0xEC7CD2u) << 5) | ((uint32_t)ifgen_parity32(w & 0x763E69u) << 4)
+         | ((uint32_t)ifgen_parity32(w & 0xBB1F34u) << 3) | ((uint32_t)ifgen_parity32(w & 0x5D8F9Au) << 2);
+    return ((word >> (29 - k)) & 1u) ? -1 : 1;
+}
+
 /* one sample; codes = [nsat][IFGEN_MAXCLEN] of +-1; out[0]=I (or real), out[1]=Q */
 IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
                            uint64_t k, signed char *out)
@@ -100,7 +130,8 @@ IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
         int    d = 1;
         if (chip >= c->clen) chip = c->clen - 1;
         if (chip < 0) chip = 0;
-        if (sv->nav_on) d = ifgen_navbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        if (sv->nav_on == 2) d = ifgen_lnavbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        else if (sv->nav_on) d = ifgen_navbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
         cyc = sv->carr_phase + (c->f_if + fd) * t + 0.5 * fdr * t * t;
         fr  = cyc - floor(cyc);
         a   = c->amp[s] * (double)(d * codes[s * IFGEN_MAXCLEN + chip]);

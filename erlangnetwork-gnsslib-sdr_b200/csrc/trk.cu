@@ -190,6 +190,11 @@ struct trk_state_t {
     double L0, D0, S0, remcout0, Isum;
     uint64_t obs_codei, obs_cnt;
     int32_t flagremcarradd, loopcnt;
+    /* frame synchronisation (GPS L1CA): nav.fbits as a ring of 2 + 300 bits (fhead = oldest),
+     * flagsyncf, flagtow, polarity, firstsf, firstsfcnt (src/sdr.h:440-479) */
+    uint64_t firstsf, firstsfcnt;
+    int32_t fhead, flagsyncf, flagtow, polarity, flagpolarityadd, pad3;
+    int8_t  fbits[304];
 };
 
 /* checksync(), src/sdrnav.c:198-233 */
@@ -230,9 +235,55 @@ __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int 
     st->swloop = (st->navcnt % loopms == 0) ? 1 : 0;
     if (diffi == 0) {
         st->bit = (st->bitIP < 0) ? -1 : 1;
+        st->fbits[st->fhead] = (int8_t)st->bit;               /* shift left + append, sdrnav.c:272-275 */
+        st->fhead = (st->fhead + 1 == 302) ? 0 : st->fhead + 1;
         st->swsync = 1;
     }
     st->navcnt++;
+}
+
+/* paritycheck_l1ca(), src/sdrnav_gps.c:141-166 on +-1 values (b[0..1]: D29*, D30*) */
+__device__ static int trk_parity_l1ca(const int *b)
+{
+    int p[6], stat = 0;
+    p[0] = b[0]*b[2]*b[3]*b[4]*b[6]*b[7]*b[11]*b[12]*b[13]*b[14]*b[15]*b[18]*b[19]*b[21]*b[24];
+    p[1] = b[1]*b[3]*b[4]*b[5]*b[7]*b[8]*b[12]*b[13]*b[14]*b[15]*b[16]*b[19]*b[20]*b[22]*b[25];
+    p[2] = b[0]*b[2]*b[4]*b[5]*b[6]*b[8]*b[9]*b[13]*b[14]*b[15]*b[16]*b[17]*b[20]*b[21]*b[23];
+    p[3] = b[1]*b[3]*b[5]*b[6]*b[7]*b[9]*b[10]*b[14]*b[15]*b[16]*b[17]*b[18]*b[21]*b[22]*b[24];
+    p[4] = b[1]*b[2]*b[4]*b[6]*b[7]*b[8]*b[10]*b[11]*b[15]*b[16]*b[17]*b[18]*b[19]*b[22]*b[23]*b[25];
+    p[5] = b[0]*b[4]*b[6]*b[7]*b[9]*b[10]*b[11]*b[12]*b[14]*b[16]*b[20]*b[23]*b[24]*b[25];
+    for (int i = 0; i < 6; i++) stat += p[i] - b[26 + i];
+    return stat == 0;
+}
+
+/* findpreamble() + paritycheck() for GPS L1CA, src/sdrnav.c:373-411, 324-345 (predecodefec is
+ * a plain copy for L1CA, :296-299); called by one lane when a data bit has been decided     */
+__device__ __noinline__ static int trk_frame_sync_l1ca(trk_state_t *st)
+{
+    const int pre[8] = {1, -1, -1, -1, 1, -1, 1, 1};                      /* src/sdrinit.c:492 */
+    int corr = 0;
+    for (int i = 0; i < 8; i++) { int k = st->fhead + 2 + i; if (k >= 302) k -= 302; corr += (int)st->fbits[k] * pre[i]; }
+    if (abs(corr) != 8) return 0;
+    st->polarity = corr > 0 ? 1 : -1;                                     /* kept even if the parity fails */
+    int stat = 0, prev29 = 0, prev30 = 0;
+    {
+        int k0 = st->fhead, k1 = st->fhead + 1; if (k1 >= 302) k1 -= 302;
+        prev29 = st->polarity * (int)st->fbits[k0]; prev30 = st->polarity * (int)st->fbits[k1];
+    }
+    for (int w = 0; w < 10; w++) {
+        int b[32];
+        b[0] = prev29; b[1] = prev30;
+        for (int j = 0; j < 30; j++) {
+            int k = st->fhead + 2 + w * 30 + j; if (k >= 302) k -= 302;
+            b[2 + j] = st->polarity * (int)st->fbits[k];
+        }
+        /* the reference inverts bits 2..25 of its working copy in place; bits 30, 31 of this word
+         * (the next word's D29*, D30*) are parity bits and stay as received                   */
+        if (b[1] == -1) for (int j = 2; j < 26; j++) b[j] = -b[j];
+        stat += trk_parity_l1ca(b);
+        prev29 = b[30]; prev30 = b[31];
+    }
+    return stat == 10;
 }
 
 __device__ __forceinline__ long long trk_clock()
@@ -308,7 +359,16 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
         if (!st->flagsync && (double)st->cnt > cntth)
             st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
-        if (st->flagsync) trk_checkbit(st->II[0], ch->loopms, st, rate);
+        if (st->flagsync) {
+            trk_checkbit(st->II[0], ch->loopms, st, rate);
+            /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA: 20 code periods per bit).  What
+             * follows in the reference - decodenav and its reset when no TOW decodes, :60-83 -
+             * is the host's: the record carries flagsyncf, polarity, firstsf, firstsfcnt       */
+            if (st->swsync && rate == 20) {
+                if (!st->flagtow) st->flagsyncf = trk_frame_sync_l1ca(st);
+                if (st->flagsyncf && !st->flagtow) { st->firstsf = st->buffloc; st->firstsfcnt = st->cnt; st->flagtow = 1; }
+            }
+        }
     }
     __syncwarp();
     TRK_EP(12);
@@ -326,8 +386,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
     TRK_EP(13);
     /* setobsdata(), src/sdrtrk.c:160-209, called after the loop filters of a synchronised
      * channel (src/sdrmain.c:285-304).  Only slot [0] of the interpolation stocks lives on
-     * the device.  The +0.5 cycle polarity term (:186-195) is gated by nav.flagsyncf (frame
-     * synchronisation, host side): it is a constant offset the host adds once.          */
+     * the device.                                                                        */
     int flagobs = 0;
     if (mode == 2 && lane == 0) {
         flagobs = (st->loopcnt % (100 / ch->loopms) == 0) ? 2 : 1;     /* SNSMOOTHMS, src/sdr.h:198 */
@@ -336,6 +395,10 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         st->remcout0 = st->oldremcode * ch->f_sf / st->codefreq;
         st->D0 = -(st->carrfreq - ch->f_if - ch->foffset);
         if (!st->flagremcarradd) { st->L0 -= st->remcarr / (2.0 * TRK_PI); st->flagremcarradd = 1; }
+        if (st->flagsyncf && !st->flagpolarityadd) {            /* src/sdrtrk.c:186-195 */
+            if (st->polarity == 1) st->L0 += 0.5;
+            st->flagpolarityadd = 1;
+        }
         st->L0 += st->D0 * ((double)(ch->loopms * st->currnsamp) / ch->f_sf);
         st->Isum += fabs(st->sumI[0]);
         if (flagobs == 2) {
@@ -358,7 +421,8 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
             rec->freqErr = st->freqErr; rec->remcode = st->remcode; rec->remcarr = st->remcarr;
             rec->L0 = st->L0; rec->D0 = st->D0; rec->S0 = st->S0; rec->remcout0 = st->remcout0;
             rec->Isum = st->Isum; rec->obs_codei = st->obs_codei; rec->obs_cnt = st->obs_cnt;
-            rec->flagobs = flagobs; rec->pad2 = 0;
+            rec->flagobs = flagobs; rec->flagsyncf = st->flagsyncf; rec->polarity = st->polarity; rec->flagtow = st->flagtow;
+            rec->firstsf = st->firstsf; rec->firstsfcnt = st->firstsfcnt;
         }
     }
     __syncwarp();

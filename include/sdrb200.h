@@ -209,7 +209,12 @@ typedef struct {             /* one record per channel per code period          
      * flagobs: 0 = setobsdata not due this period, 1 = ran, 2 = ran with snrflag   */
     double   L0, D0, S0, remcout0, Isum;
     uint64_t obs_codei, obs_cnt;
-    int32_t  flagobs, pad2;
+    int32_t  flagobs;
+    /* frame synchronisation of GPS L1CA channels (findpreamble + paritycheck,
+     * src/sdrnav.c:43-58, 324-411): nav.flagsyncf, nav.polarity, nav.flagtow and the
+     * reference sample / counter of the first subframe (nav.firstsf, nav.firstsfcnt)   */
+    int32_t  flagsyncf, polarity, flagtow;
+    uint64_t firstsf, firstsfcnt;
 } sdrb200_trk_rec_t;
 
 typedef struct sdrb200_trk sdrb200_trk_t;

@@ -66,7 +66,8 @@ typedef struct {
     /* observables left by setobsdata (src/sdrtrk.c:160-209), newest slot [0] */
     double   D0, S0, remcout0, Isum;           /* trk.D[0], S[0], remcout[0], Isum */
     uint64_t obs_codei, obs_cnt;               /* trk.codei[0], cntout[0]     */
-    int      flagobs, pad;                     /* 0: not called this period, 1: called, 2: with snrflag */
+    int      flagobs;                          /* 0: not called this period, 1: called, 2: with snrflag */
+    int      polarity;                         /* nav.polarity (set by findpreamble)                    */
 } oh_trkrec_t;
 
 /* which implementation answered: "reference", "b200-dropin" or "port" */

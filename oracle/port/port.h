@@ -81,7 +81,13 @@ typedef struct {
     double L0, D0, S0, remcout0, Isum;
     uint64_t obs_codei, obs_cnt;
     int    flagremcarradd, loopcnt;
+    /* frame synchronisation: sdrnav_t fbits (flen + addflen = 302 for L1CA), flagsyncf,
+     * flagtow, polarity, firstsf, firstsfcnt (sdr.h:440-479) */
+    int    fbits[302];
+    int    flagsyncf, flagtow, polarity, flagpolarityadd;
+    uint64_t firstsf, firstsfcnt;
 } p_chan_t;
+#define P_FBITS 302
 
 typedef struct {                                   /* what the two INI files carry */
     double f_sf, f_if, f_cf;

@@ -105,6 +105,7 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
             r = &rec[(size_t)i * nperiods + ntracked[i]];
             r->cnt = cnt[i]; r->buffloc = buffloc[i]; r->currnsamp = c->currnsamp;
             r->flagsync = c->flagsync; r->flagloopfilter = c->flagloopfilter;
+            r->flagsyncf = c->flagsyncf; r->flagtow = c->flagtow; r->polarity = c->polarity;
             r->swsync = c->swsync; r->swloop = c->swloop; r->synci = c->synci;
             r->biti = c->biti; r->bit = c->bit;
             for (k = 0; k < 1 + 2 * c->corrn; k++) { r->II[k] = c->II[k]; r->QQ[k] = c->QQ[k]; }

@@ -31,8 +31,39 @@ static int bit_sync_step(double IP, double IPold, p_chan_t *c)
     return 0;
 }
 
-/* checkbit, src/sdrnav.c:241-282 (frame-bit shift register omitted: frame
- * decoding is outside the hot path) */
+/* paritycheck_l1ca, src/sdrnav_gps.c:141-166: bits[0..1] = D29*, D30* of the previous word,
+ * bits[2..31] the word, all +-1; the sum of differences is the reference's own test      */
+static int parity_l1ca(const int *b)
+{
+    int p[6], i, stat = 0;
+    p[0] = b[0]*b[2]*b[3]*b[4]*b[6]*b[7]*b[11]*b[12]*b[13]*b[14]*b[15]*b[18]*b[19]*b[21]*b[24];
+    p[1] = b[1]*b[3]*b[4]*b[5]*b[7]*b[8]*b[12]*b[13]*b[14]*b[15]*b[16]*b[19]*b[20]*b[22]*b[25];
+    p[2] = b[0]*b[2]*b[4]*b[5]*b[6]*b[8]*b[9]*b[13]*b[14]*b[15]*b[16]*b[17]*b[20]*b[21]*b[23];
+    p[3] = b[1]*b[3]*b[5]*b[6]*b[7]*b[9]*b[10]*b[14]*b[15]*b[16]*b[17]*b[18]*b[21]*b[22]*b[24];
+    p[4] = b[1]*b[2]*b[4]*b[6]*b[7]*b[8]*b[10]*b[11]*b[15]*b[16]*b[17]*b[18]*b[19]*b[22]*b[23]*b[25];
+    p[5] = b[0]*b[4]*b[6]*b[7]*b[9]*b[10]*b[11]*b[12]*b[14]*b[16]*b[20]*b[23]*b[24]*b[25];
+    for (i = 0; i < 6; i++) stat += p[i] - b[26 + i];
+    return stat == 0;
+}
+
+/* findpreamble + paritycheck for L1CA, src/sdrnav.c:373-411, 324-345 (predecodefec is a copy
+ * for L1CA, :296-299).  fbits: 2 + 300 bits, oldest first.                                */
+static int frame_sync_l1ca(p_chan_t *c)
+{
+    static const int pre[8] = {1, -1, -1, -1, 1, -1, 1, 1};              /* src/sdrinit.c:492 */
+    int bits[P_FBITS], corr = 0, i, j, stat = 0;
+    for (i = 0; i < 8; i++) corr += c->fbits[2 + i] * pre[i];
+    if (abs(corr) != 8) return 0;
+    c->polarity = corr > 0 ? 1 : -1;                                      /* set before the parity test */
+    for (i = 0; i < P_FBITS; i++) bits[i] = c->polarity * c->fbits[i];
+    for (i = 0; i < 10; i++) {
+        if (bits[i * 30 + 1] == -1) for (j = 2; j < 26; j++) bits[i * 30 + j] *= -1;
+        stat += parity_l1ca(&bits[i * 30]);
+    }
+    return stat == 10;
+}
+
+/* checkbit, src/sdrnav.c:241-282, including the frame-bit shift register (:272-275) */
 static void bit_decide(double IP, p_chan_t *c)
 {
     const int diffi = c->biti - c->synci;
@@ -40,7 +71,12 @@ static void bit_decide(double IP, p_chan_t *c)
     if (diffi == 1 || diffi == -c->rate + 1) { c->bitIP = IP; c->swreset = 1; c->navcnt = 1; }
     else c->bitIP += IP;
     c->swloop = (c->navcnt % c->loopms == 0) ? 1 : 0;
-    if (diffi == 0) { c->bit = (c->bitIP < 0) ? -1 : 1; c->swsync = 1; }
+    if (diffi == 0) {
+        c->bit = (c->bitIP < 0) ? -1 : 1;
+        memmove(&c->fbits[0], &c->fbits[1], sizeof(int) * (P_FBITS - 1));
+        c->fbits[P_FBITS - 1] = c->bit;
+        c->swsync = 1;
+    }
     c->navcnt++;
 }
 
@@ -69,7 +105,15 @@ void p_tracking(p_chan_t *c, const signed char *stream, uint64_t buffloc, uint64
     if (c->rate == 1 && cnt > 2000 / (c->ctime * 1000)) { c->synci = 0; c->flagsync = 1; }
     if (!c->flagsync && cnt > 2000 / (c->ctime * 1000))
         c->flagsync = bit_sync_step(c->II[0], c->oldI[0], c);
-    if (c->flagsync) bit_decide(c->II[0], c);
+    if (c->flagsync) {
+        bit_decide(c->II[0], c);
+        /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA; what follows it - decodenav and
+         * its reset when no TOW decodes, :60-83 - is outside this path)                     */
+        if (c->swsync && c->ctype == 1 && c->rate == 20) {
+            if (!c->flagtow) c->flagsyncf = frame_sync_l1ca(c);
+            if (c->flagsyncf && !c->flagtow) { c->firstsf = buffloc; c->firstsfcnt = cnt; c->flagtow = 1; }
+        }
+    }
 }
 
 /* src/sdrtrk.c:64-76 */
@@ -133,6 +177,10 @@ void p_setobsdata(p_chan_t *c, uint64_t buffloc, uint64_t cnt, int snrflag)
     if (!c->flagremcarradd) {                                /* :180-184 */
         c->L0 -= c->remcarr / DPI;
         c->flagremcarradd = 1;
+    }
+    if (c->flagsyncf && !c->flagpolarityadd) {               /* :186-195 */
+        if (c->polarity == 1) c->L0 += 0.5;
+        c->flagpolarityadd = 1;
     }
     c->L0 += c->D0 * (c->loopms * c->currnsamp / c->f_sf);   /* :197 */
     c->Isum += fabs(c->sumI[0]);                             /* :199 */

@@ -230,7 +230,7 @@ static int track_period(sdrch_t *sdr, uint64_t *buffloc, uint64_t *cnt, uint64_t
     r->L0 = sdr->trk.L[0];
     r->D0 = sdr->trk.D[0]; r->S0 = sdr->trk.S[0]; r->remcout0 = sdr->trk.remcout[0];
     r->Isum = sdr->trk.Isum; r->obs_codei = sdr->trk.codei[0]; r->obs_cnt = sdr->trk.cntout[0];
-    r->flagobs = flagobs;
+    r->flagobs = flagobs; r->polarity = sdr->nav.polarity;
 
     if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
     (*cnt)++;

@@ -39,7 +39,7 @@ class OhTrkRec(C.Structure):
                 ("carrErr", C.c_double), ("carrNco", C.c_double), ("freqErr", C.c_double),
                 ("remcode", C.c_double), ("remcarr", C.c_double), ("L0", C.c_double),
                 ("D0", C.c_double), ("S0", C.c_double), ("remcout0", C.c_double), ("Isum", C.c_double),
-                ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64), ("flagobs", C.c_int), ("pad", C.c_int)]
+                ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64), ("flagobs", C.c_int), ("polarity", C.c_int)]
 
 
 # the INI defaults of frontend/iffile.ini:29-48 and frontend/rtlsdr_L1.ini:29-48

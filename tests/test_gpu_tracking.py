@@ -84,3 +84,41 @@ def test_tracking_real_if(sdr, oracle):
 def test_tracking_iq_rtlsdr_style(sdr, oracle):
     cfg, prns = util.scene_c5(sdr, nsats=4)
     _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=2), 4600, util.FS5, 2)
+
+
+def test_tracking_frame_sync_lnav(sdr, oracle):
+    """Frame synchronisation on the device (findpreamble + paritycheck for GPS L1CA,
+    src/sdrnav.c:43-58, 324-411; paritycheck_l1ca, src/sdrnav_gps.c:141-166): IF carrying LNAV
+    subframes (preamble, TOW, valid parity; csrc/ifgen.h nav_on = 2).  The period at which the
+    preamble is accepted, the polarity it fixes and the +0.5 cycle term it adds to the carrier
+    phase observable (src/sdrtrk.c:186-195) must be the reference's."""
+    rng = np.random.default_rng(5)
+    prns = [2, 5, 7]
+    sats = [dict(prn=p, cn0=48.0, doppler=float(b * 200.0 + rng.uniform(-60, 60)),
+                 code_phase=float(rng.uniform(0, 1023 * 20)), carr_phase=float(rng.uniform(0, 1)), rate=0.3,
+                 nav_on=2, nav_seed=100 + p) for p, b in zip(prns, (3, -7, 11))]
+    cfg = sdr.make_ifgen(util.FS5, 0.0, util.CF, 2, sats, sigma=20.0, seed=0xB2000071)
+    nper = 13000
+    avail = 65536
+    total = avail + 2048 * (nper + 8)
+    st = sdr.Stream(2, total)
+    st.push_ifgen(cfg, total)
+    host = st.read(0, total)
+    cfgo = ob.cfg_rtlsdr(acq_intg=3)
+    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, prns, nper)
+    assert all(a.acquired for a in acq)
+    chans = [sdr.make_trk_chan(cfgo.f_sf, cfgo.f_if, cfgo.f_cf, 2, a.prn, sdr.gencode(a.prn)[0],
+                               a.buffloc, a.acqfreq, cfgo.corrn, cfgo.corrd, cfgo.corrp,
+                               list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb)) for a in acq]
+    rec_g, ntr_g = sdr.Tracking(chans).run(st, nper)
+    for ch, a in enumerate(acq):
+        n = min(ntr_o[ch], ntr_g[ch])
+        assert n == nper
+        o, g = rec_o[ch][:n], rec_g[ch][:n]
+        assert o["flagsyncf"].max() == 1, (a.prn, "the reference did not frame-sync")
+        for f in ("flagsync", "synci", "flagsyncf", "flagtow", "polarity", "flagobs"):
+            assert np.array_equal(o[f], g[f]), (a.prn, f, int(np.argmax(o[f] != g[f])))
+        k = int(np.argmax(o["flagsyncf"] > 0))
+        assert int(g["firstsfcnt"][-1]) == int(o["cnt"][k]) and int(g["firstsf"][-1]) == int(o["buffloc"][k])
+        assert np.abs(o["L0"] - g["L0"]).max() <= 2e-2, (a.prn, "L0")
+    assert sorted(int(r["polarity"][-1]) for r in rec_g) == [-1, -1, 1]      # the +0.5 term is exercised

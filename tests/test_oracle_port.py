@@ -156,3 +156,27 @@ def test_port_ingest_golden(port):
         if ob.have_ref():
             big = np.random.default_rng(3).integers(0, 256, 5000).astype(np.uint8)
             assert np.array_equal(port.unpack(f, big), ob.ref().unpack(f, big)), f
+
+
+def test_port_frame_sync_equals_reference_build(port):
+    """findpreamble + paritycheck + paritycheck_l1ca (src/sdrnav.c:324-411, src/sdrnav_gps.c:141-166)
+    and the polarity term of setobsdata (src/sdrtrk.c:186-195): IF with LNAV subframes
+    (csrc/ifgen.h nav_on = 2), port against the reference build, bit for bit."""
+    if not ob.have_ref():
+        pytest.skip("reference build absent (GPU box): the GPU test compares with the port there")
+    import sdrb200_pkg
+    sdr = sdrb200_pkg.load()
+    ref = ob.ref()
+    rng = np.random.default_rng(5)
+    prns = [2, 5]
+    sats = [dict(prn=p, cn0=48.0, doppler=float(b * 200.0 + rng.uniform(-60, 60)),
+                 code_phase=float(rng.uniform(0, 1023 * 20)), carr_phase=float(rng.uniform(0, 1)), rate=0.3,
+                 nav_on=2, nav_seed=100 + p) for p, b in zip(prns, (3, -7))]
+    cfg = sdr.make_ifgen(util.FS5, 0.0, util.CF, 2, sats, sigma=20.0, seed=0xB2000071)
+    nper = 12500
+    host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
+    a1, r1, n1 = ref.acq_track(ob.cfg_rtlsdr(acq_intg=3), host, 65536, prns, nper)
+    a2, r2, n2 = port.acq_track(ob.cfg_rtlsdr(acq_intg=3), host, 65536, prns, nper)
+    assert n1 == n2 and int(r1["flagsyncf"].max()) == 1
+    for f in REC_FIELDS + ["flagsyncf", "flagtow", "polarity"]:
+        assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
