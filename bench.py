@@ -299,7 +299,7 @@ def run_b200(args):
         sdr.check(lib.sdrb200_acq_kernel_ms(acq.h, ms4, c4), "kernel_ms")
     barrier()
     sdr.check(lib.sdrb200_acq_set_timing(acq.h, 0), "set_timing")
-    KNAMES = ["k_fwd_if", "k_rowc<search>", "k_comb", "k_rowc<peak>"]
+    KNAMES = ["k_fwd_split_small+k_fft_rows", "k_rowc<search>", "k_comb", "k_rowc<peak>"]
     kern = {n: {"ms_total": ms4[i], "launches": int(c4[i]),
                 "ms_per_launch": (ms4[i] / c4[i]) if c4[i] else None}
             for i, n in enumerate(KNAMES) if c4[i]}

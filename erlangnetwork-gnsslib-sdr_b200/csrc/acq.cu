@@ -471,6 +471,44 @@ k_fwd_split(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict
     }
 }
 
+/* the same first pass for the cluster path (R = 2, 4, 8 sub-transforms): one thread per t does
+ * the wipe-off of its R samples x[t + L a] and the whole R-point stage in registers.  Together
+ * with k_fft_rows it replaces k_fwd_if, whose CTAs each walk the entire window (R blocks, one
+ * dependent load per block: 31 us for 71 bins of 32768 points, latency-bound).             */
+template <int R, int DT>
+__global__ void __launch_bounds__(256)
+k_fwd_split_small(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict__ cidx, int cidx_stride,
+                  float scale, const float2 *__restrict__ tw, int L, float2 *__restrict__ out)
+{
+    __shared__ float2 s_lut[32];
+    const int t = blockIdx.x * 256 + threadIdx.x, f = blockIdx.y;
+    const int M = R * L;
+    if (threadIdx.x < 32) s_lut[threadIdx.x] = make_float2(c_cosf[threadIdx.x] * scale, c_sinf[threadIdx.x] * scale);
+    __syncthreads();
+    if (t >= L) return;
+    const uint8_t *ci = cidx + (size_t)f * cidx_stride;
+    float2 z[R];
+#pragma unroll
+    for (int a = 0; a < R; a++) {
+        const int k = t + L * a;
+        z[a] = make_float2(0.f, 0.f);
+        if (k < nlive) {
+            const float2 lu = s_lut[ci[k] & 31];
+            if (DT == 1) {
+                const float x = (float)win[k];
+                z[a] = make_float2(x * lu.x, x * lu.y);
+            } else {
+                const float x0 = (float)win[2 * k], x1 = (float)win[2 * k + 1];
+                z[a] = make_float2(x0 * lu.x - x1 * lu.y, x0 * lu.y + x1 * lu.x);
+            }
+        }
+    }
+    fft_small<R, -1>(z);
+#pragma unroll
+    for (int q = 0; q < R; q++)
+        out[((size_t)f * R + q) * L + t] = (q == 0) ? z[0] : cmul(z[q], __ldg(&tw[(t * q) & (M - 1)]));
+}
+
 template <int L>
 __global__ void __launch_bounds__(L / 16)
 k_fft_rows(float2 *__restrict__ X, const float2 *__restrict__ tw, int R)
@@ -938,9 +976,23 @@ template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
+template <int R> static int launch_fwd_split_small_r(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+{
+    dim3 grid((a->L + 255) / 256, a->cfg.nfreq);
+    if (a->cfg.dtype == 1)
+        k_fwd_split_small<R, 1><<<grid, 256, 0, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+    else
+        k_fwd_split_small<R, 2><<<grid, 256, 0, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+    sdrb200_count_launch(1);
+    SDRB200_CUDA_TRY(cudaGetLastError());
+    return SDRB200_OK;
+}
 static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
 {
     switch (a->R) {
+    case 2:   return launch_fwd_split_small_r<2>(st, a, win, scale);
+    case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale);
+    case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale);
     case 32:  return launch_fwd_split_g<2>(st, a, win, scale);
     case 64:  return launch_fwd_split_g<4>(st, a, win, scale);
     case 128: return launch_fwd_split_g<8>(st, a, win, scale);
@@ -1222,7 +1274,8 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
         const int8_t *win = base + pos * c->dtype;
         ACQ_T0(a);
-        if (!a->fused && comb_fft_supported(a->R) && !getenv("SDRB200_ACQ_COMB_NAIVE")) {
+        if (((a->fused && (a->R == 2 || a->R == 4 || a->R == 8) && !getenv("SDRB200_FWD_WALK")) ||
+             (!a->fused && comb_fft_supported(a->R))) && !getenv("SDRB200_ACQ_COMB_NAIVE")) {
             rc = launch_fwd_split(a->st, a, win, scale);
             if (rc) return rc;
             ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a)));
