@@ -116,6 +116,43 @@ def _cpu_trk_worker(job):
     return dt, ntr[0], o.name
 
 
+def _cpu_shipped_worker(job):
+    """the reference compiled as its own bin/Makefile does (-g, no -O, -DFFTMTX) and run with its
+    own threading model: acquisition by one thread (the channel threads' FFTs are serialised by
+    hfftmtx anyway), tracking with one pthread per channel (oh_acq_track_mt)."""
+    seed, nacq, nper = job
+    import oracle_bind as ob
+    import sdrb200_pkg
+    if not ob.have_ref_shipped():
+        return None
+    sdr = sdrb200_pkg.load()
+    o = ob.ref_shipped()
+    total = AVAIL10 + (nper + 4) * NSAMP
+    host = sdr.ifgen_host(scene(sdr, seed), 0, total)
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(1)
+    os.dup2(devnull, 1)
+    try:
+        t0 = time.perf_counter()
+        o.acquire(ob.cfg_iffile(acq_intg=1), host[:AVAIL], AVAIL, list(range(1, nacq + 1)))
+        t_acq = time.perf_counter() - t0
+        cfg = ob.cfg_iffile(acq_intg=10)
+        t0 = time.perf_counter()
+        o.acq_track(cfg, host, AVAIL10, TRK_PRNS, 1, threaded=True)
+        t_1 = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        _, _, ntr = o.acq_track(cfg, host, AVAIL10, TRK_PRNS, nper, threaded=True)
+        t_trk = time.perf_counter() - t0 - t_1
+    finally:
+        os.dup2(saved, 1)
+        os.close(devnull)
+        os.close(saved)
+    return {"acq_cells_per_s": nacq * NFREQ * NSAMP / t_acq, "acq_sample": f"{nacq} PRNs x 71 bins x 16368, one thread",
+            "trk_channel_s_per_s": sum(ntr) * 1e-3 / t_trk,
+            "trk_sample": f"{len(TRK_PRNS)} channels x {nper} code periods, one pthread per channel",
+            "flags": "-g -DFFTMTX, no -O (bin/Makefile:17,29); FFT shim at -O2 in place of the FFTW binary"}
+
+
 def cpu_pool(cores):
     import multiprocessing as mp
     return mp.get_context("spawn").Pool(cores)
@@ -228,6 +265,13 @@ def run_b200(args):
                        "single_core_value": tot * 1e-3 / per_core,
                        "sample": f"12 channels x {nper} code periods (2 s of IF), one process per channel, "
                                  f"tracking loop only ({wall:.1f} s wall incl. acquisition)"}
+            shipped = pool.apply(_cpu_shipped_worker, ((0xB2000000, 4, 600),))
+            if shipped:
+                cpu_acq["as_shipped"] = {"value": shipped["acq_cells_per_s"], "unit": "cells/s", "cores": 1,
+                                         "sample": shipped["acq_sample"], "flags": shipped["flags"]}
+                cpu_trk["as_shipped"] = {"value": shipped["trk_channel_s_per_s"], "unit": "channel.s/s",
+                                         "cores": min(cores, len(TRK_PRNS)), "sample": shipped["trk_sample"],
+                                         "flags": shipped["flags"]}
         finally:
             pool.close()
 

@@ -208,6 +208,18 @@ def have_ref() -> bool:
     return os.path.exists(REF_SO)
 
 
+REF_SHIPPED_SO = os.path.join(ROOT, "oracle", "_ref", "libreplay_ref_shipped.so")
+
+
+def have_ref_shipped() -> bool:
+    return os.path.exists(REF_SHIPPED_SO)
+
+
+def ref_shipped() -> Oracle:
+    """the reference compiled with its own bin/Makefile flags (-g, no -O, -DFFTMTX)"""
+    return Oracle(REF_SHIPPED_SO)
+
+
 def have_port() -> bool:
     return os.path.exists(PORT_SO)
 
