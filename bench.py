@@ -587,15 +587,19 @@ def run_b200(args):
                 r4 = acq4.fetch()
                 t4.append(e1.ms_since(e0))
             ms4 = sum(t4) / len(t4)
-            cells4 = args.c4_prns * nf4 * n4 * intg4
+            if dist is not None:                             # every rank searched its own stream
+                tt4 = torch.tensor([ms4], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt4, op=dist.ReduceOp.MAX)
+                ms4 = float(tt4[0])
+            cells4 = world * args.c4_prns * nf4 * n4 * intg4
             m4 = 1 << 20
-            a_bytes4 = intg4 * (2 * n4 + args.c4_prns * m4 * 8) + args.c4_prns * nf4 * n4 * 4 * (1 + 2 * (intg4 - 1))
+            a_bytes4 = world * (intg4 * (2 * n4 + args.c4_prns * m4 * 8) + args.c4_prns * nf4 * n4 * 4 * (1 + 2 * (intg4 - 1)))
             c4_obj = {"workload": f"{args.c4_prns} PRN x {nf4} bins (100 Hz) x {n4} lags, {ncoh4} ms coherent blocks "
                                   f"(M = 2^20), {intg4} non-coherent steps (BASELINE configs[3] style)",
                       "cells_per_s": cells4 / (ms4 * 1e-3), "ms_per_run": ms4, "ms_per_step": ms4 / intg4,
                       "algorithmic_bytes_per_run": a_bytes4,
-                      "hbm": {"achieved_GBps": a_bytes4 / (ms4 * 1e-3) / 1e9, "peak_GBps": hbm_peak,
-                              "frac": a_bytes4 / (ms4 * 1e-3) / 1e9 / hbm_peak,
+                      "hbm": {"achieved_GBps": a_bytes4 / (ms4 * 1e-3) / 1e9, "peak_GBps": hbm_peak * world,
+                              "frac": a_bytes4 / (ms4 * 1e-3) / 1e9 / (hbm_peak * world),
                               "model": "SURVEY 8(d): IF + code-spectrum bank + power matrix read/write per step"},
                       "l2": "flushed before every timed run", "peak_bins": [r["freqi"] for r in r4[:4]]}
             acq4.close()
