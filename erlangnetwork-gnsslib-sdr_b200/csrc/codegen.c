@@ -32,6 +32,8 @@ static const uint16_t k_g2_delay[210] = {
     173,900,30,500,935,556,373,85,652,310
 };
 
+const uint16_t *sdrb200_g2_delay_table(void) { return k_g2_delay; }
+
 /* run a 10-stage Fibonacci LFSR; taps is a bit mask over stages 1..10 (bit s-1) */
 static void lfsr10(uint32_t taps, uint8_t *out /*1023*/)
 {

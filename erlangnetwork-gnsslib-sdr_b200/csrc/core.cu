@@ -177,6 +177,75 @@ static int ifgen_launch(const ifgen_cfg_t *cfg_in, uint64_t k0, uint64_t n, void
     return SDRB200_OK;
 }
 
+/* ---- ranging codes on the device (gencode, src/sdrcode.c:101-154, 426-444, 523-539) ----
+ * One CTA per code.  C/A: lane 0 runs G1 (x^10+x^3+1), lane 1 runs G2 (x^10+x^9+x^8+x^6+x^3+x^2+1),
+ * both from all ones; chip i = G1[i] xor G2[(i - delay) mod 1023] with the reference's polarity
+ * (see csrc/codegen.c).  GLONASS ST code: x^9+x^5+1, output stage 7, 511 chips.            */
+__global__ void k_gencode(const int *__restrict__ prn, const unsigned short *__restrict__ delay, int ctype,
+                          int8_t *__restrict__ out, int stride)
+{
+    __shared__ unsigned char g[2][1024];
+    int8_t *o = out + (size_t)blockIdx.x * stride;
+    if (ctype == SDRB200_CTYPE_G1) {
+        if (threadIdx.x == 0) {
+            unsigned int reg = 0x1FF;
+            for (int i = 0; i < 511; i++) {
+                const unsigned int fb = ((reg >> 4) ^ (reg >> 8)) & 1u;
+                g[0][i] = (unsigned char)((reg >> 6) & 1u);
+                reg = ((reg << 1) | fb) & 0x1FF;
+            }
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < 511; i += blockDim.x) o[i] = g[0][i] ? 1 : -1;
+        return;
+    }
+    if (threadIdx.x < 2) {
+        const unsigned int taps = threadIdx.x == 0 ? ((1u << 2) | (1u << 9))
+                                                   : ((1u << 1) | (1u << 2) | (1u << 5) | (1u << 7) | (1u << 8) | (1u << 9));
+        unsigned int reg = 0x3FF;
+        for (int i = 0; i < 1023; i++) {
+            const unsigned int fb = (unsigned int)__popc(reg & taps) & 1u;
+            g[threadIdx.x][i] = (unsigned char)((reg >> 9) & 1u);
+            reg = ((reg << 1) | fb) & 0x3FF;
+        }
+    }
+    __syncthreads();
+    const int d = (int)delay[prn[blockIdx.x] - 1];
+    for (int i = threadIdx.x; i < 1023; i += blockDim.x) {
+        int k = i + 1023 - d; if (k >= 1023) k -= 1023;
+        o[i] = (g[0][i] ^ g[1][k]) ? 1 : -1;
+    }
+}
+
+extern "C" int sdrb200_gencode_device(int n, const int *prn, int ctype, int8_t *codes, int stride)
+{
+    const int len = (ctype == SDRB200_CTYPE_G1) ? 511 : 1023;
+    if (n < 1 || !prn || !codes || stride < len ||
+        (ctype != SDRB200_CTYPE_L1CA && ctype != SDRB200_CTYPE_L1SBAS && ctype != SDRB200_CTYPE_G1)) {
+        sdrb200_set_error("gencode_device: bad argument"); return SDRB200_EINVAL;
+    }
+    if (ctype != SDRB200_CTYPE_G1)
+        for (int i = 0; i < n; i++)
+            if (prn[i] < 1 || prn[i] > 210) { sdrb200_set_error("gencode_device: PRN %d out of range", prn[i]); return SDRB200_EINVAL; }
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    int *d_prn = NULL; unsigned short *d_delay = NULL; int8_t *d_out = NULL;
+    int rc = SDRB200_OK;
+    if (cudaMalloc((void **)&d_prn, sizeof(int) * n) != cudaSuccess || cudaMalloc((void **)&d_delay, sizeof(unsigned short) * 210) != cudaSuccess ||
+        cudaMalloc((void **)&d_out, (size_t)n * stride) != cudaSuccess) rc = SDRB200_ENOMEM;
+    if (rc == SDRB200_OK) {
+        cudaMemcpy(d_prn, prn, sizeof(int) * n, cudaMemcpyHostToDevice);
+        cudaMemcpy(d_delay, sdrb200_g2_delay_table(), sizeof(unsigned short) * 210, cudaMemcpyHostToDevice);
+        cudaMemset(d_out, 0, (size_t)n * stride);
+        k_gencode<<<n, 128>>>(d_prn, d_delay, ctype, d_out, stride);
+        sdrb200_count_launch(1);
+        if (cudaGetLastError() != cudaSuccess || cudaMemcpy(codes, d_out, (size_t)n * stride, cudaMemcpyDeviceToHost) != cudaSuccess) {
+            sdrb200_set_error("gencode_device: kernel failed"); rc = SDRB200_ECUDA;
+        }
+    } else sdrb200_set_error("gencode_device: cudaMalloc failed");
+    cudaFree(d_prn); cudaFree(d_delay); cudaFree(d_out);
+    return rc == SDRB200_OK ? len : rc;
+}
+
 extern "C" int sdrb200_ifgen_device(const void *vcfg, uint64_t k0, uint64_t n, void *d_out, void *cuda_stream)
 {
     if (!vcfg || !d_out) return SDRB200_EINVAL;

@@ -23,6 +23,7 @@ void sdrb200_count_launch(int n);
 /* codegen.c */
 int sdrb200_gencode_l1ca(int prn, int8_t *code);
 int sdrb200_gencode_g1(int8_t *code);
+const uint16_t *sdrb200_g2_delay_table(void);   /* [210] G2 delays, PRN 1..210 */
 
 /* device IF stream (core.cu) */
 struct sdrb200_stream {

@@ -8,7 +8,7 @@ import numpy as np
 from . import (AcqCfg, AcqResult, Error, IfgenCfg, IfgenSat, Loop, TrkChan, TrkRec,  # noqa: F401
                MAXCORRN, MAXTAPS, check, lib)
 
-__all__ = ["gencode", "make_ifgen", "ifgen_host", "correlator", "mixcarr", "rescode",
+__all__ = ["gencode", "gencode_device", "make_ifgen", "ifgen_host", "correlator", "mixcarr", "rescode",
            "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition",
            "Stream", "Acquisition", "Tracking", "device_count", "launch_count", "make_trk_chan"]
 
@@ -39,6 +39,16 @@ def gencode(prn: int, ctype: int = 1):
     if n <= 0:
         raise Error(f"gencode prn:{prn} ctype:{ctype}")
     return buf[:n].copy(), crate.value
+
+
+def gencode_device(prns, ctype: int = 1) -> np.ndarray:
+    """gencode on the GPU for a list of PRNs -> [n][len] int8 (sdrb200_gencode_device)."""
+    n = len(prns)
+    out = np.zeros((n, 1023), np.int8)
+    arr = (C.c_int * n)(*[int(p) for p in prns])
+    ln = lib.sdrb200_gencode_device(n, arr, int(ctype), _p(out, _i8p), 1023)
+    check(ln if ln < 0 else 0, "gencode_device")
+    return out[:, :ln]
 
 
 def make_ifgen(f_sf, f_if, f_cf, dtype, sats, sigma=24.0, seed=0xB2000000,

@@ -64,6 +64,10 @@ int  sdrb200_device_sync(void);
  * gencode(), src/sdrcode.c:523-539 (L1CA/SBAS 101-154; G1 426-444, which the
  * reference defines but never dispatches).  code: +-1, returns the length.   */
 int sdrb200_gencode(int prn, int ctype, int8_t *code, double *crate);
+/* the same tables generated on the GPU, one CTA per code (shift registers in two lanes, chips
+ * combined by the CTA): codes [n][stride] in HOST memory, stride >= 1023.  Returns the code
+ * length (1023 or 511).                                                                    */
+int sdrb200_gencode_device(int n, const int *prn, int ctype, int8_t *codes, int stride);
 
 /* ------------------------------------------------------- synthetic front end
  * The reference has no IF data in-tree; see csrc/ifgen.h for the model.

@@ -108,3 +108,19 @@ def test_pcorrelator_checkacquisition(sdr, oracle):
     P[1, 0] = 20.0
     ca = sdr.checkacquisition(P.ravel(), 2048, 3, 2, 1e-3)
     assert (ca["codei"], ca["freqi"]) == (1, 1) and abs(ca["peakr"] - 2.5) < 1e-12
+
+
+def test_gencode_on_device(sdr):
+    """gencode (src/sdrcode.c:101-154, 426-444) on the GPU: all 210 C/A-family PRNs (GPS, SBAS
+    120-158, QZSS) and the GLONASS ST code, chip for chip against the host tables, which
+    tests/test_host_cpu.py and tests/golden/codes.npz pin to the reference's generator."""
+    prns = list(range(1, 211))
+    dev = sdr.gencode_device(prns, 1)
+    assert dev.shape == (210, 1023)
+    for i, p in enumerate(prns):
+        assert np.array_equal(dev[i], sdr.gencode(p, 1)[0]), p
+    assert np.array_equal(sdr.gencode_device([133, 120], 27), np.stack([sdr.gencode(133, 27)[0], sdr.gencode(120, 27)[0]]))
+    g1 = sdr.gencode_device([1], 20)
+    assert g1.shape == (1, 511) and np.array_equal(g1[0], sdr.gencode(1, 20)[0])
+    with pytest.raises(sdr.Error):
+        sdr.gencode_device([211], 1)
