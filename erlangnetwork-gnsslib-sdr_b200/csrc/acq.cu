@@ -49,6 +49,8 @@ struct sdrb200_acq {
     int n_eff, m_ref, M, L, R;
     int chunk;                       /* PRNs per scratch chunk                */
     int fchunk;                      /* Doppler bins per scratch chunk (nfreq unless one PRN is too large) */
+    int split_fwd;                   /* forward transform in two passes (k_fwd_split* + k_fft_rows)        */
+    int comb_fft;                    /* scratch path: radix-R recombination + k_peak_hbm                   */
     double *h_freq;
     cudaStream_t st;
     float2 *d_tw;                    /* [M] forward twiddles                  */
@@ -1132,6 +1134,12 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
             if (a->fchunk < 1) a->fchunk = 1;
             if (a->fchunk > nfreq) a->fchunk = nfreq;
         }
+        /* experiment switches, read once per plan: SDRB200_ACQ_COMB_NAIVE (direct-sum combine and
+         * the walking forward kernel), SDRB200_FWD_WALK (walking forward kernel on the cluster path) */
+        const int naive = getenv("SDRB200_ACQ_COMB_NAIVE") != NULL;
+        a->comb_fft = (!a->fused && a->R > 1 && comb_fft_supported(a->R) && !naive) ? 1 : 0;
+        a->split_fwd = (a->comb_fft || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8) &&
+                                        !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }
     }
@@ -1274,8 +1282,7 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         const uint64_t pos = (buffloc0 + (uint64_t)step * a->n_eff) % capacity;
         const int8_t *win = base + pos * c->dtype;
         ACQ_T0(a);
-        if (((a->fused && (a->R == 2 || a->R == 4 || a->R == 8) && !getenv("SDRB200_FWD_WALK")) ||
-             (!a->fused && comb_fft_supported(a->R))) && !getenv("SDRB200_ACQ_COMB_NAIVE")) {
+        if (a->split_fwd) {
             rc = launch_fwd_split(a->st, a, win, scale);
             if (rc) return rc;
             ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a)));
@@ -1305,7 +1312,7 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         /* scratch path: sub-transforms of a chunk of rows go through d_S (sized to stay in L2),
          * then the radix-R recombination; SDRB200_ACQ_COMB_NAIVE selects the direct-sum
          * combine with per-row statistics (kept as a cross-check)                        */
-        const int use_fft = (a->R > 1) && comb_fft_supported(a->R) && !getenv("SDRB200_ACQ_COMB_NAIVE");
+        const int use_fft = a->comb_fft;
         for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
             const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
             for (int f0 = 0; f0 < c->nfreq; f0 += a->fchunk) {
