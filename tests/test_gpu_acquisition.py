@@ -246,3 +246,35 @@ def test_acq_weak_signal_full_size_coherent(sdr, oracle):
             # the true Doppler bin, and a code phase equal to the injected delay modulo one period
             assert g["freqi"] == 2, (p, g)
             assert g["maxp"] > 8 * np.median(ref), p
+
+
+@pytest.mark.parametrize("ncoh,dtype", [(10, 1), (40, 1), (40, 2)])
+def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype):
+    """The two-pass path at its other radices: 10 ms real (M = 2^19, R = 64, G = 4), 40 ms real
+    (M = 2^21, R = 256, G = 16) and 40 ms I/Q at 2.048 MS/s (M = 2^18, R = 32, G = 2, the I/Q
+    wipe-off of k_fwd_split), against the reference's pcorrelator on an ncoh-period replica."""
+    fs, f_if, nsamp, scene = (util.FS1, util.IF1, 16368, util.scene_c1) if dtype == 1 else (util.FS5, 0.0, 2048, util.scene_c5)
+    n = ncoh * nsamp
+    cfg, vis = scene(sdr, nsats=2, seed=0xB2000046 + ncoh)
+    for i in range(cfg.nsat):
+        cfg.sat[i].nav_on = 0
+    avail = 2 * n + 4096
+    st = sdr.Stream(dtype, avail)
+    st.push_ifgen(cfg, avail)
+    host = st.read(0, avail)
+    b0 = avail - 2 * n
+    dop = np.round(cfg.sat[0].doppler_hz / 100) * 100
+    freq = np.array([f_if + dop + (i - 1) * 100.0 for i in range(3)])
+    code = sdr.gencode(vis[0])[0]
+    acq = sdr.Acquisition(fs, dtype, nsamp, int(nsamp / 1023), 1e-3, freq, code[None, :], 1.023e6, intg=1, ncoh=ncoh,
+                          keep_power=True)
+    g = acq.run(st, b0)[0]
+    rep, _ = oracle.rescode(code.astype(np.int16), 0.0, 0, 1.023e6 / fs, n)
+    x = np.zeros(2 * n, np.complex64)
+    x[:n] = rep
+    ref = oracle.pcorrelator(host[b0 * dtype:(b0 + 2 * n) * dtype], dtype, 1 / fs, n, freq, 1.023e6, 2 * n, oracle.cpxfft(x))
+    P = acq.power(0).ravel()
+    assert np.abs(P - ref).max() <= 2e-4 * ref.max()
+    flat = int(np.argmax(ref))
+    assert (g["freqi"], g["codei"]) == (flat // n, flat % n)
+    assert g["freqi"] == 1
