@@ -573,6 +573,10 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             if (!have) trk_walk_code(&sm->t, ch->ti, n, st->codefreq, st->remcode, smax, ch->clen);
             asm volatile("bar.arrive 3, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* code table: releases the workers' tap phase */
             if (spec_do) asm volatile("bar.arrive 4, 64;" ::: "memory");               /* remc is final: the carrier warp may read it */
+            /* remc is final: the code warp's share of the end-of-correlation barrier.  Like the
+             * carrier warp it does not wait there - the epilogue runs on worker warp 2 - so its
+             * walk-ahead (the longest chain of a staged period) overlaps the epilogue          */
+            asm volatile("bar.arrive 5, %0;" ::"n"(TRK_THREADS) : "memory");
             if (spec_do) {
                 if (threadIdx.x == TRK_NCO_B) {
                     const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
@@ -601,13 +605,13 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             TRK_PT(3);
             trk_tap_sums<DTYPE>(&sm->t, wk, data, n, sm->taps, ns, smax);
         }
-        if (wid != (TRK_NCO_A >> 5)) asm volatile("bar.sync 5, %0;" ::"n"(TRK_THREADS) : "memory");
+        if (wid >= 2) asm volatile("bar.sync 5, %0;" ::"n"(TRK_THREADS) : "memory");
         TRK_PT(4);
         DBG(9);
-        if (wid == (TRK_NCO_B >> 5))
+        if (wid == 2)
             trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31,
                          (prof && blockIdx.x == 0) ? prof : nullptr);
-        if (wid == (TRK_NCO_B >> 5)) DBG(14);
+        if (wid == 2) DBG(14);
         __syncthreads();
         if (recs) {
             const uint32_t *src = (const uint32_t *)&sm->rec;
