@@ -369,17 +369,17 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
     }
 }
 
-/* sum_{i<k} m[i] for k in [0, n]: I (word 0) or Q (word 1) */
+/* both words of the same prefix: (sum I, sum Q) over samples [0, k) */
 template <int DTYPE>
-__device__ __forceinline__ unsigned int trk_prefix_at(const trk_work_t &wk, int a, int k, int isQ)
+__device__ __forceinline__ uint2 trk_prefix2_at(const trk_work_t &wk, int a, int k)
 {
     constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;
-    if (k <= 0) return 0u;
+    if (k <= 0) return make_uint2(0u, 0u);
     const int byte = (k - 1) * DTYPE + a;
     const int row = byte / TRK_SPAN;
     const int j = (byte - row * TRK_SPAN) / DTYPE;
-    const unsigned int *b = (const unsigned int *)wk.base, *p = (const unsigned int *)wk.P2;
-    return b[row * 2 + isQ] + p[((size_t)row * RS + j) * 2 + isQ];
+    const uint2 b = wk.base[row], p = wk.P2[(size_t)row * RS + j];
+    return make_uint2(b.x + p.x, b.y + p.y);
 }
 
 /* ---- phase 3 (workers): replica sign changes -> tap sums --------------------- *
@@ -468,22 +468,32 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
     DBG(6);
     trk_bar_workers();
     DBG(7);
-    /* (b) */
+    /* (b) one lane per (tap, queue entry): a lane reads the (I,Q) prefix pair of its position
+     * once and accumulates both sums, so a tap costs one lookup per entry; the 32 / ntap lane
+     * groups of a warp take consecutive entries                                            */
     const int qn = min(sm->qcount, wk.qcap);
-    for (int task = lane; task < 2 * ntap; task += 32) {
-        const int isQ = task >= ntap, tap = isQ ? task - ntap : task;
+    const int tpw = min(ntap, 32), G = 32 / tpw;
+    const int g = lane / tpw, tl = lane - g * tpw;
+    for (int tap0 = 0; tap0 < ntap; tap0 += tpw) {
+        const int tap = tap0 + tl;
+        if (g >= G || tap >= ntap) continue;
         int off = 0;
         if (tap > 0) { const int s = taps[(tap - 1) >> 1]; off = ((tap - 1) & 1) ? s : -s; }
-        unsigned int acc = 0u;
+        const int bias = smax + off;
+        unsigned int accI = 0u, accQ = 0u;
 #pragma unroll 4
-        for (int e = wwarp; e < qn; e += TRK_WORKERS / 32) {
+        for (int e = wwarp * G + g; e < qn; e += (TRK_WORKERS / 32) * G) {
             const unsigned int entry = wk.queue[e];
-            const int B = (int)(entry & 0x7fffffffu) - smax;
             const unsigned int delta = (entry >> 31) ? 0xfffffffeu : 2u;        /* r_{q-1} - r_q */
-            acc += delta * trk_prefix_at<DTYPE>(wk, a, min(max(B - off, 0), n), isQ);
+            const uint2 pf = trk_prefix2_at<DTYPE>(wk, a, min(max((int)(entry & 0x7fffffffu) - bias, 0), n));
+            accI += delta * pf.x; accQ += delta * pf.y;
         }
-        if (wwarp == 0) acc += (unsigned int)sm->vlast * trk_prefix_at<DTYPE>(wk, a, n, isQ);   /* r_last * P[n] */
-        if (acc) atomicAdd(&sm->sum[isQ ? SDRB200_MAXTAPS + tap : tap], acc);
+        if (wwarp == 0 && g == 0) {                                             /* r_last * P[n] */
+            const uint2 pf = trk_prefix2_at<DTYPE>(wk, a, n);
+            accI += (unsigned int)sm->vlast * pf.x; accQ += (unsigned int)sm->vlast * pf.y;
+        }
+        if (accI) atomicAdd(&sm->sum[tap], accI);
+        if (accQ) atomicAdd(&sm->sum[SDRB200_MAXTAPS + tap], accQ);
     }
     DBG(8);
 }
