@@ -430,7 +430,8 @@ def run_b200(args):
             phases.update(periods=per, walk_carrier=round(out[8] / per, 1), carrier_rem=round(out[9] / per, 1),
                           staged_periods=int(out[10]), walk_ahead_periods=int(out[11]),
                           epilogue_nav=round(out[12] / per, 1), epilogue_loops=round(out[13] / per, 1),
-                          epilogue_obs_rec=round(out[14] / per, 1), unit="cycles per period, channel 0")
+                          epilogue_obs_rec=round(out[14] / per, 1),
+                          code_walk_ahead=round(out[7] / per, 1), code_walk_call=round(out[15] / per, 1), unit="cycles per period, channel 0")
         t_trk = sum(tms) / len(tms) * 1e-3
         # end to end: IF from pinned host memory -> device ring -> tracking -> per-channel record counts
         nbytes = int(nper + 8) * NSAMP + AVAIL

@@ -579,6 +579,9 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
             asm volatile("bar.arrive 5, %0;" ::"n"(TRK_THREADS) : "memory");
             if (spec_do) {
                 if (threadIdx.x == TRK_NCO_B) {
+                    const bool pf = prof && blockIdx.x == 0;
+                    long long c0t = 0, c1t = 0;
+                    if (pf) c0t = trk_clock();
                     const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
                     int ok = (n2 > 0 && n2 <= maxn) ? 1 : 0;
                     if (ok) {
@@ -586,12 +589,15 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                         const double c0 = nco_code_init(sm->t.remc, smax, ci, ch->clen);
                         double xe;
                         nco_iseg_t *dst = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
+                        if (pf) c1t = trk_clock();
                         const int nsg = trk_walk_call(c0, ci, n2 + 2 * smax, (double)ch->clen, dst, &xe);
+                        if (pf) prof[15] += trk_clock() - c1t;
                         if (nsg < 0) ok = 0;
                         sm->nx_code.nseg = nsg < 0 ? 0 : nsg; sm->nx_code.x_end = xe;
                         sm->nx_remc = nco_code_rem(xe, smax, ci);
                     }
                     sm->nx_valid = ok;                  /* the carrier warp's verdict is nx_n >= 0 */
+                    if (pf) prof[7] += trk_clock() - c0t;
                 }
                 __syncwarp();
                 DBG(13);

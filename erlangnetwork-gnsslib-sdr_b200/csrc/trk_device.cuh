@@ -173,8 +173,12 @@ __device__ __forceinline__ long long dbg_clock() { long long t; asm volatile("mo
 
 /* out of line on purpose: the walk is a long single-lane dependency chain on 64-bit
  * values; keeping it out of the 1024-thread kernel body (64-register cap) avoids spills.
- * (A warp-cooperative variant - per-binade constants precomputed one per lane and
- * fetched by shuffle - was measured slower: the recurrence is latency-bound.)        */
+ * (Measured and dropped: a warp-cooperative variant with the per-binade constants
+ * precomputed one per lane and fetched by shuffle; the same constants in a shared-memory
+ * table built once per frequency; the fast chain as a separate tight function (125
+ * instead of ~200 instructions per binade).  None changed the ~21 k cycles of a code
+ * walk: the time is the dependent 64-bit integer/convert latency of one lane sharing its
+ * scheduler with seven busy worker warps, not the instruction count.)                 */
 __device__ __noinline__ int trk_walk_call(double x, double step, int count, double wrap, nco_iseg_t *seg, double *x_end)
 {
     return nco_walk_i(x, step, count, wrap, seg, TRK_MAXSEG, x_end);
