@@ -94,6 +94,19 @@ __device__ __forceinline__ trk_work_t trk_work_layout(unsigned int *w, int maxn,
     return k;
 }
 
+/* Worker warps in work order.  The two NCO lanes sit on warp schedulers 0 and 1 (warp id mod
+ * 4) and their dependency chains lose issue slots to every busy worker warp there
+ * (tools/walkbench.cu: a walk is 2.3x slower beside busy warps).  A code period fills ~820
+ * of the 960 worker threads, so the work order lists the warps of schedulers 2 and 3 first:
+ * the worker warps left without rows are then the ones that share a scheduler with an NCO
+ * lane.  Returns 2..31 like a warp id.                                                  */
+__device__ __forceinline__ int trk_worker_warp()
+{
+    const int w = threadIdx.x >> 5, s = w & 3;
+    const int pos = (s >= 2) ? (w >> 2) * 2 + (s - 2) : 16 + ((w >> 2) - 1) * 2 + s;
+    return pos + 2;
+}
+
 __device__ __forceinline__ void trk_bar_workers()
 {
     asm volatile("bar.sync 1, %0;" ::"n"(TRK_WORKERS) : "memory");
@@ -255,7 +268,7 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
                                                const trk_work_t &wk)
 {
     constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;     /* samples per row, row stride (pairs) */
-    const int u = threadIdx.x - 64, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = trk_worker_warp(), u = (warp - 2) * 32 + lane;
     const uintptr_t addr = (uintptr_t)data;
     const int a = (int)(addr & 3);
     const unsigned int *wbase = (const unsigned int *)(addr - a);
@@ -401,7 +414,7 @@ template <int DTYPE>
 __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &wk, const int8_t *data, int n,
                                              const int *taps, int ns, int smax)
 {
-    const int t = threadIdx.x - 64, lane = threadIdx.x & 31, wwarp = (threadIdx.x >> 5) - 2;
+    const int lane = threadIdx.x & 31, wwarp = trk_worker_warp() - 2, t = wwarp * 32 + lane;
     const int a = (int)((uintptr_t)data & 3);
     const int N = n + 2 * smax, ntap = 1 + 2 * ns;
     const int PP = (N + TRK_WORKERS - 1) / TRK_WORKERS;
