@@ -94,19 +94,6 @@ __device__ __forceinline__ trk_work_t trk_work_layout(unsigned int *w, int maxn,
     return k;
 }
 
-/* Worker warps in work order.  The two NCO lanes sit on warp schedulers 0 and 1 (warp id mod
- * 4) and their dependency chains lose issue slots to every busy worker warp there
- * (tools/walkbench.cu: a walk is 2.3x slower beside busy warps).  A code period fills ~820
- * of the 960 worker threads, so the work order lists the warps of schedulers 2 and 3 first:
- * the worker warps left without rows are then the ones that share a scheduler with an NCO
- * lane.  Returns 2..31 like a warp id.                                                  */
-__device__ __forceinline__ int trk_worker_warp()
-{
-    const int w = threadIdx.x >> 5, s = w & 3;
-    const int pos = (s >= 2) ? (w >> 2) * 2 + (s - 2) : 16 + ((w >> 2) - 1) * 2 + s;
-    return pos + 2;
-}
-
 __device__ __forceinline__ void trk_bar_workers()
 {
     asm volatile("bar.sync 1, %0;" ::"n"(TRK_WORKERS) : "memory");
@@ -191,7 +178,10 @@ __device__ __forceinline__ long long dbg_clock() { long long t; asm volatile("mo
  * table built once per frequency; the fast chain as a separate tight function (125
  * instead of ~200 instructions per binade).  None changed the ~21 k cycles of a code
  * walk: the time is the dependent 64-bit integer/convert latency of one lane sharing its
- * scheduler with seven busy worker warps, not the instruction count.)                 */
+ * scheduler with seven busy worker warps, not the instruction count.  Handing the rows
+ * to the worker warps of schedulers 2 and 3 first - so that the warps a period leaves
+ * idle sit beside the NCO lanes - shortened the lane chains by ~1 k cycles but not the
+ * period, and cost 7 % with 2048-sample periods (four busy warps on two schedulers).)  */
 __device__ __noinline__ int trk_walk_call(double x, double step, int count, double wrap, nco_iseg_t *seg, double *x_end)
 {
     return nco_walk_i(x, step, count, wrap, seg, TRK_MAXSEG, x_end);
@@ -268,7 +258,7 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
                                                const trk_work_t &wk)
 {
     constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;     /* samples per row, row stride (pairs) */
-    const int lane = threadIdx.x & 31, warp = trk_worker_warp(), u = (warp - 2) * 32 + lane;
+    const int u = threadIdx.x - 64, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uintptr_t addr = (uintptr_t)data;
     const int a = (int)(addr & 3);
     const unsigned int *wbase = (const unsigned int *)(addr - a);
@@ -414,7 +404,7 @@ template <int DTYPE>
 __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &wk, const int8_t *data, int n,
                                              const int *taps, int ns, int smax)
 {
-    const int lane = threadIdx.x & 31, wwarp = trk_worker_warp() - 2, t = wwarp * 32 + lane;
+    const int t = threadIdx.x - 64, lane = threadIdx.x & 31, wwarp = (threadIdx.x >> 5) - 2;
     const int a = (int)((uintptr_t)data & 3);
     const int N = n + 2 * smax, ntap = 1 + 2 * ns;
     const int PP = (N + TRK_WORKERS - 1) / TRK_WORKERS;
