@@ -453,6 +453,7 @@ struct trk_run_smem_t {
     int32_t nx_valid;           /* staged tables are complete                        */
     int32_t spec_do;            /* this period: walk ahead                           */
     int32_t have;               /* this period: tables came from the staging area    */
+    trk_chan_dev_t chc;         /* the channel's constants (all but the code: t.codetab has it) */
 };
 
 template <int DTYPE>
@@ -480,8 +481,13 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         /* record slots beyond the channel's taps are never written: keep them zero */
         for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) ((uint32_t *)&sm->rec)[i] = 0u;
         if (threadIdx.x == 0) { sm->nx_valid = 0; sm->nx_n = -1; sm->have = 0; sm->spec_do = 0; }
+        /* the serial sections (period start, epilogue, NCO lanes) read the channel constants
+         * many times per period: keep them in shared memory, not behind L1/L2            */
+        for (int i = threadIdx.x; i < (int)(offsetof(trk_chan_dev_t, code) / 4); i += blockDim.x)
+            ((uint32_t *)&sm->chc)[i] = ((const uint32_t *)ch)[i];
     }
     __syncthreads();
+    ch = &sm->chc;
     const int ns = ch->corrn;
     const int smax = sm->taps[ns - 1];
     int done = 0;
