@@ -352,13 +352,16 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         st->remcarr = sm->remp;
         /* sdrnavigation(), src/sdrnav.c:19-41 */
         const int rate = ch->navrate;
-        const double cntth = 2000 / (ch->ctime * 1000);
-        st->biti = (int)(st->cnt % (uint64_t)rate);
+        /* cnt % rate: 32-bit while cnt fits (a 64-bit remainder is a subroutine) */
+        st->biti = (st->cnt >> 32) ? (int)(st->cnt % (uint64_t)rate) : (int)((uint32_t)st->cnt % (uint32_t)rate);
         st->ocodei = st->biti - st->synci - 1;
         if (st->ocodei < 0) st->ocodei += rate;
-        if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
-        if (!st->flagsync && (double)st->cnt > cntth)
-            st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
+        if (rate == 1 || !st->flagsync) {               /* the 2 s threshold matters only here */
+            const double cntth = 2000 / (ch->ctime * 1000);
+            if (rate == 1 && (double)st->cnt > cntth) { st->synci = 0; st->flagsync = 1; }
+            if (!st->flagsync && (double)st->cnt > cntth)
+                st->flagsync = trk_checksync(st->II[0], st->oldI[0], st, ch->prn, rate);
+        }
         if (st->flagsync) {
             trk_checkbit(st->II[0], ch->loopms, st, rate);
             /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA: 20 code periods per bit).  What
