@@ -457,6 +457,8 @@ struct trk_run_smem_t {
     int32_t spec_do;            /* this period: walk ahead                           */
     int32_t have;               /* this period: tables came from the staging area    */
     trk_chan_dev_t chc;         /* the channel's constants (all but the code: t.codetab has it) */
+    unsigned long long boff;    /* st.buffloc % capacity, advanced by additions (a 64-bit remainder
+                                 * by every thread every period was 5 % of the kernel's instructions) */
 };
 
 template <int DTYPE>
@@ -493,7 +495,7 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
     ch = &sm->chc;
     const int ns = ch->corrn;
     const int smax = sm->taps[ns - 1];
-    int done = 0;
+    int done = 0, n_prev = 0;
     /* optional phase profile (cycles, CTA 0, thread 0): go, tables, convert, mix, taps, epilogue */
     long long pt[6] = {0, 0, 0, 0, 0, 0}, t0 = 0;
     const bool prof_on = prof != nullptr && blockIdx.x == 0 && threadIdx.x == 64;     /* first worker lane */
@@ -506,6 +508,16 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         __syncthreads();
 #endif
         DBG(0);
+        if (threadIdx.x == TRK_NCO_B) {
+            /* ring offset of this period's first sample, beside the carrier lane's decisions */
+            if (it == 0) sm->boff = st->buffloc % capacity;
+            else {                                      /* the epilogue added n_prev to buffloc */
+                unsigned long long b = sm->boff + (unsigned long long)n_prev;
+                if (b >= capacity) b -= capacity;
+                if (b >= capacity) b %= capacity;
+                sm->boff = b;
+            }
+        }
         if (threadIdx.x == TRK_NCO_A) {
             /* sdrtracking(), src/sdrtrk.c:31-32 */
             /* staged tables were walked for exactly this state (frequencies untouched since,
@@ -540,10 +552,11 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
         TRK_PT(0);
         DBG(1);
         const int n = st->currnsamp;
+        n_prev = n;
         /* correlator(..., carrfreq, oldremcarr(=remcarr), codefreq, oldremcode(=remcode), ...) */
         long long w0 = 0;
         if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
-        const int8_t *data = ifbuf + (size_t)(st->buffloc % capacity) * DTYPE;
+        const int8_t *data = ifbuf + (size_t)sm->boff * DTYPE;
         const int wid = threadIdx.x >> 5;
         const int have = sm->have, spec_do = sm->spec_do;
         if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) { prof[10] += have; prof[11] += spec_do; }
