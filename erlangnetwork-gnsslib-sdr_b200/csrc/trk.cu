@@ -517,6 +517,19 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                 if (b >= capacity) b %= capacity;
                 sm->boff = b;
             }
+            /* Will this period's epilogue leave carrfreq/codefreq alone?  Once bit sync is
+             * reached (flagsync never drops), the loop filters run only when checkbit()
+             * raises swloop, which is a function of counters known now
+             * (src/sdrnav.c:241-262, src/sdrmain.c:271-280).                            */
+            int quiet = 0;
+            if (st->flagsync && ch->navrate > 1) {
+                const int rate = ch->navrate;
+                const int biti = (st->cnt >> 32) ? (int)(st->cnt % (uint64_t)rate) : (int)((uint32_t)st->cnt % (uint32_t)rate);
+                const int diffi = biti - st->synci;
+                const int navcnt = (diffi == 1 || diffi == -rate + 1) ? 1 : st->navcnt;
+                quiet = (navcnt % ch->loopms != 0) ? 1 : 0;
+            }
+            sm->spec_do = (quiet && it + 1 < nperiods) ? 1 : 0;
         }
         if (threadIdx.x == TRK_NCO_A) {
             /* sdrtracking(), src/sdrtrk.c:31-32 */
@@ -533,19 +546,6 @@ k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ st
                 sm->t.icode = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
                 sm->t.carr = sm->nx_carr; sm->t.code = sm->nx_code; sm->t.remc = sm->nx_remc;
             }
-            /* Will this period's epilogue leave carrfreq/codefreq alone?  Once bit sync is
-             * reached (flagsync never drops), the loop filters run only when checkbit()
-             * raises swloop, which is a function of counters known now
-             * (src/sdrnav.c:241-262, src/sdrmain.c:271-280).                            */
-            int quiet = 0;
-            if (st->flagsync && ch->navrate > 1) {
-                const int rate = ch->navrate;
-                const int biti = (st->cnt >> 32) ? (int)(st->cnt % (uint64_t)rate) : (int)((uint32_t)st->cnt % (uint32_t)rate);
-                const int diffi = biti - st->synci;
-                const int navcnt = (diffi == 1 || diffi == -rate + 1) ? 1 : st->navcnt;
-                quiet = (navcnt % ch->loopms != 0) ? 1 : 0;
-            }
-            sm->spec_do = (quiet && it + 1 < nperiods) ? 1 : 0;
         }
         __syncthreads();
         if (!sm->go) break;
