@@ -647,6 +647,245 @@ NCO_HD double nco_reduce_2pi(double x)
     return x;
 }
 
+/* ==== lean double-domain walker (the tracking kernel's NCO lanes) ================
+ * Same sequences as nco_walk / nco_reduce_2pi, arranged so that the DEPENDENT chain per
+ * binade is ~8 floating-point operations and nothing else:
+ *
+ *   inside binade [2^e, 2^(e+1)) every addition of `step` adds d_e = step rounded to the
+ *   binade's grid (see the head of this file); d_e depends on step and e only, so a table
+ *   of d_e (and of 1/d_e, biased low) is built ONCE per step value - in parallel, one lane
+ *   per binade, off the chain (nco_steptab_entry).  An exact tie (step's dropped bits are
+ *   exactly half a grid unit) is resolved by the parity of x: one REAL addition makes the
+ *   mantissa even, after which the increment is the even one of {q, q+1} grid units.
+ *   The run length is floor(room * inv) with one exact upward correction; the addition that
+ *   leaves the binade (or reaches the wrap limit) is a REAL addition, so its rounding is
+ *   the hardware's.  Values outside the table's domain (x <= 0, step <= 0, x below step's
+ *   binade, subnormals) take the probing iteration of nco_walk.
+ * Segments come out in double form {k0, x0, d}; nco_wseg_make turns one into the integer
+ * form the correlator threads use.                                                      */
+#define NCO_STEPTAB_N 54
+typedef struct {
+    double   d[NCO_STEPTAB_N];      /* [s]: increment in binade ed + s, s = 1..52          */
+    double   inv[NCO_STEPTAB_N];    /* [s]: (1 / d[s]) * (1 - 2^-30)                       */
+    uint64_t ties;                  /* bit s: binade ed + s rounds step on an exact tie    */
+    int32_t  ed;                    /* biased exponent of step; 0: table unusable          */
+    int32_t  pad;
+} nco_steptab_t;
+
+/* entry s (1..52) of the table for `step` (> 0, normal): returns 0 if binade ed + s has no
+ * normal grid representation of the increment (never for receiver frequencies)           */
+NCO_HD int nco_steptab_entry(double step, int s, double *d, double *inv, int *tie)
+{
+    const uint64_t bstep = nco_bits(step);
+    const int ed = (int)((bstep >> 52) & 0x7FF);
+    const uint64_t Dm = NCO_MANT(bstep);
+    const uint64_t q = Dm >> s, r = Dm & ((1ULL << s) - 1), half = 1ULL << (s - 1);
+    uint64_t Dn;
+    const int eg = ed + s - 52;                         /* biased exponent of one grid unit */
+    *tie = (r == half);
+    if (r == half) Dn = q + (q & 1);                    /* the even one of {q, q+1}         */
+    else Dn = q + (r > half ? 1 : 0);
+    if (eg < 1 || eg > 2046 || ed + s > 2046) { *d = 0.0; *inv = 0.0; return 0; }
+    *d = NCO_MUL((double)(int64_t)Dn, nco_from_bits((uint64_t)eg << 52));      /* exact   */
+    *inv = NCO_MUL(NCO_DIV(1.0, *d), 0x1.fffffffcp-1);                          /* 1 - 2^-30 */
+    return 1;
+}
+NCO_HD void nco_steptab_build(double step, nco_steptab_t *t)
+{
+    const uint64_t bstep = nco_bits(step);
+    const int ed = (int)((bstep >> 52) & 0x7FF);
+    int s;
+    t->ties = 0; t->pad = 0;
+    t->ed = (step > 0.0 && ed > 0 && ed < 0x7FF) ? ed : 0;
+    t->d[0] = 0.0; t->inv[0] = 0.0; t->d[53] = 0.0; t->inv[53] = 0.0;
+    for (s = 1; s <= 52; s++) {
+        int tie = 0;
+        if (!t->ed || !nco_steptab_entry(step, s, &t->d[s], &t->inv[s], &tie)) { t->d[s] = 0.0; t->inv[s] = 0.0; }
+        if (tie) t->ties |= 1ULL << s;
+    }
+}
+
+#define NCO_DEMIT(K0, X0, DD) do { if (ns < maxseg) { nco_seg_t *sg_ = &seg[ns]; sg_->k0 = (K0); sg_->pad = 0; \
+                                    sg_->x0 = (X0); sg_->d = (DD); } ns++; } while (0)
+
+/* same contract as nco_walk_i, segments in double form; tab = table of `step` */
+NCO_HD int nco_walk_d(double x, double step, int32_t count, double wrap, const nco_steptab_t *tab,
+                      nco_seg_t *seg, int maxseg, double *x_end)
+{
+    int32_t k = 0, ns = 0;
+    const int lim = (wrap > 0.0) ? 1 : 0;
+    const int ed = tab->ed;
+    const int ewrap = (int)((nco_bits(wrap) >> 52) & 0x7FF);
+    double inv_generic = 0.0;
+    while (k < count) {
+        if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
+        {
+            const uint64_t bx = nco_bits(x);
+            const int ex = (int)(bx >> 52);                 /* sign set -> out of range below */
+            const int s = ex - ed;
+            if (ed && s >= 1 && s <= 52 && tab->d[s] != 0.0 && !(lim && ex > ewrap)) {
+                const double d = tab->d[s];
+                const double hi = nco_from_bits((uint64_t)(ex + 1) << 52);
+                const double top = (lim && ex == ewrap) ? wrap : hi;
+                double room, est, y, y2;
+                int32_t J, R;
+                if ((tab->ties >> s) & 1ULL) {
+                    /* parity step: one real addition, then the mantissa is even */
+                    const double x1 = NCO_ADD(x, step);
+                    if (k + 1 >= count || !(x1 < top)) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; continue; }
+                    if (nco_bits(x) & 1ULL) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; }
+                }
+                R = count - k;                              /* values still to describe (>= 1) */
+                room = NCO_ADD(top, -x);                    /* exact: both on the binade's grid */
+                est = NCO_MUL(room, tab->inv[s]);
+                J = (est >= (double)(R - 1)) ? R - 1 : (int32_t)est;
+                y = NCO_ADD(x, NCO_MUL((double)J, d));      /* exact */
+                while (J > 0 && !(y < top)) { J--; y = NCO_ADD(y, -d); }
+                while (J < R - 1) { y2 = NCO_ADD(y, d); if (!(y2 < top)) break; y = y2; J++; }
+                NCO_DEMIT(k, x, d);
+                k += J + 1;
+                x = NCO_ADD(y, step);                       /* leaves the run (or ends the walk): real */
+                continue;
+            }
+        }
+        /* probing iteration (nco_walk) */
+        {
+            double x1, x2, d;
+            int32_t J;
+            if (inv_generic == 0.0) inv_generic = nco_rcp_est(step);
+            x1 = NCO_ADD(x, step);
+            if (x1 == x) { NCO_DEMIT(k, x, 0.0); k = count; break; }
+            if (k + 1 >= count || (lim && x1 >= wrap) || !nco_same_binade(x, x1)) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; continue; }
+            x2 = NCO_ADD(x1, step);
+            if (k + 2 >= count || (lim && x2 >= wrap) || !nco_same_binade(x1, x2)) { NCO_DEMIT(k, x, NCO_ADD(x1, -x)); k += 2; x = x2; continue; }
+            d = NCO_ADD(x2, -x1);
+            J = nco_jump(x1, d, inv_generic, lim, wrap, count - 2 - k, &x2);
+            NCO_DEMIT(k, x, 0.0);
+            NCO_DEMIT(k + 1, x1, d);
+            x = NCO_ADD(x2, step);
+            k += 2 + J;
+        }
+    }
+    *x_end = x;
+    return (ns > maxseg) ? -1 : ns;
+}
+#undef NCO_DEMIT
+
+/* 2*pi per binade [2^(2+s), 2^(3+s)): rounded to the binade's grid (the even neighbour for the
+ * tie binade s = 4) and its reciprocal biased low by 2^-30; tests/test_nco_exact.py recomputes */
+#define NCO_R2PI_TABLES \
+    { 0x1.921fb54442d18p+2, 0x1.921fb54442d18p+2, 0x1.921fb54442d18p+2, 0x1.921fb54442d18p+2, \
+      0x1.921fb54442d20p+2, 0x1.921fb54442d20p+2, 0x1.921fb54442d00p+2, 0x1.921fb54442d00p+2, \
+      0x1.921fb54442d00p+2, 0x1.921fb54442e00p+2, 0x1.921fb54442c00p+2, 0x1.921fb54443000p+2, \
+      0x1.921fb54443000p+2, 0x1.921fb54442000p+2, 0x1.921fb54444000p+2, 0x1.921fb54440000p+2, \
+      0x1.921fb54440000p+2, 0x1.921fb54440000p+2, 0x1.921fb54440000p+2, 0x1.921fb54480000p+2, \
+      0x1.921fb54400000p+2, 0x1.921fb54400000p+2, 0x1.921fb54400000p+2, 0x1.921fb54800000p+2, \
+      0x1.921fb54000000p+2, 0x1.921fb54000000p+2, 0x1.921fb54000000p+2, 0x1.921fb58000000p+2, \
+      0x1.921fb50000000p+2, 0x1.921fb60000000p+2, 0x1.921fb40000000p+2, 0x1.921fb80000000p+2 }
+#define NCO_R2PI_INVS \
+    { 0x1.45f306d784bc1p-3, 0x1.45f306d784bc1p-3, 0x1.45f306d784bc1p-3, 0x1.45f306d784bc1p-3, \
+      0x1.45f306d784bbap-3, 0x1.45f306d784bbap-3, 0x1.45f306d784bd4p-3, 0x1.45f306d784bd4p-3, \
+      0x1.45f306d784bd4p-3, 0x1.45f306d784b05p-3, 0x1.45f306d784ca4p-3, 0x1.45f306d784966p-3, \
+      0x1.45f306d784966p-3, 0x1.45f306d78565ep-3, 0x1.45f306d783c6ep-3, 0x1.45f306d78704ep-3, \
+      0x1.45f306d78704ep-3, 0x1.45f306d78704ep-3, 0x1.45f306d78704ep-3, 0x1.45f306d753248p-3, \
+      0x1.45f306d7bae54p-3, 0x1.45f306d7bae54p-3, 0x1.45f306d7bae54p-3, 0x1.45f306d47cdf5p-3, \
+      0x1.45f306daf8eb3p-3, 0x1.45f306daf8eb3p-3, 0x1.45f306daf8eb3p-3, 0x1.45f306a7188c7p-3, \
+      0x1.45f3070ed94a0p-3, 0x1.45f3063f57cf2p-3, 0x1.45f307de5ac5dp-3, 0x1.45f304a054dcbp-3 }
+static const double nco_r2pi_Pd_host[32] = NCO_R2PI_TABLES;
+static const double nco_r2pi_inv_host[32] = NCO_R2PI_INVS;
+#ifdef __CUDACC__
+static __device__ __constant__ double nco_r2pi_Pd_dev[32] = NCO_R2PI_TABLES;
+static __device__ __constant__ double nco_r2pi_inv_dev[32] = NCO_R2PI_INVS;
+#endif
+
+/* while (x > 2pi) x -= 2pi, double-domain chain (same result as nco_reduce_2pi).  In binade
+ * 2^(2+s), s >= 1, a subtraction whose exact result stays at or above the binade's lower
+ * border lo is x - Pd[s]; J = floor((x - lo - ulp) / Pd) such steps keep x - J*Pd >= lo + ulp,
+ * for which the exact difference x - 2pi > x - Pd - ulp/2 is inside the binade.           */
+NCO_HD double nco_reduce_2pi_d(double x)
+{
+    const double P = NCO_TWO_PI;
+    while (x > P) {
+        const uint64_t bx = nco_bits(x);
+        const int s = (int)(bx >> 52) - (1023 + 2);
+        if ((unsigned int)(s - 1) <= 30u) {
+#ifdef __CUDA_ARCH__
+            const double Pd = nco_r2pi_Pd_dev[s], inv = nco_r2pi_inv_dev[s];
+#else
+            const double Pd = nco_r2pi_Pd_host[s], inv = nco_r2pi_inv_host[s];
+#endif
+            const double lo = nco_from_bits(bx & 0xFFF0000000000000ULL);
+            const double lo1 = nco_from_bits((bx & 0xFFF0000000000000ULL) | 1ULL);    /* lo + ulp */
+            double room, est, y, y2, J;
+            if ((NCO_R2PI_TIES >> s) & 1u) {
+                const double x1 = NCO_ADD(x, -P);
+                if (!(x1 >= lo)) { x = x1; continue; }
+                x = x1;                                     /* even mantissa from here on */
+            }
+            if (x >= lo1) {
+                room = NCO_ADD(x, -lo1);                    /* exact */
+                est = NCO_MUL(room, inv);
+                J = floor(est);
+                y = NCO_ADD(x, -NCO_MUL(J, Pd));            /* exact */
+                while (!(y >= lo1)) y = NCO_ADD(y, Pd);
+                for (;;) { y2 = NCO_ADD(y, -Pd); if (!(y2 >= lo1)) break; y = y2; }
+                x = y;
+            }
+            x = NCO_ADD(x, -P);                             /* may leave the binade: real */
+            continue;
+        }
+        x = NCO_ADD(x, -P);
+    }
+    return x;
+}
+
+/* ---- integer form of a segment for the correlator threads ------------------------
+ * (int)value mod 2^B for B = 5 (carrier table index) or 10 (chip index < 1024) sits in
+ * the TOP B bits of a 64-bit accumulator that advances by one wrapping addition per
+ * sample:  acc_j = M + j*D (mod 2^64),  t_j = acc_j >> (64 - B)  is |value_j| truncated,
+ * mod 2^B; negative values (neg) index as (-t) & (2^B - 1).                            */
+typedef struct {
+    int32_t  k0;
+    int32_t  neg;
+    uint64_t M;
+    uint64_t D;
+} nco_wseg_t;
+
+NCO_HD void nco_wseg_make(const nco_seg_t *sg, int B, nco_wseg_t *o, int *range_bad)
+{
+    const uint64_t bx = nco_bits(sg->x0), bd = nco_bits(sg->d);
+    const int ex = (int)((bx >> 52) & 0x7FF), edd = (int)((bd >> 52) & 0x7FF);
+    o->k0 = sg->k0; o->neg = (int32_t)(bx >> 63); o->M = 0; o->D = 0;
+    if (ex < 1023) return;                               /* |value| < 1 throughout: (int) gives 0 */
+    {
+        const int sh = 52 - (ex - 1023);                 /* value = mant >> sh                    */
+        const int L = 64 - B - sh;                       /* left shift that puts bit sh at 64 - B */
+        uint64_t X0 = NCO_MANT(bx), mag = 0;
+        if (sh < 0) { if (range_bad) *range_bad = 1; return; }      /* |value| >= 2^53 */
+        if (edd != 0) {
+            const uint64_t md = NCO_MANT(bd);
+            const int dsh = ex - edd;
+            mag = (dsh < 0) ? (md << 1) : (dsh > 63 ? 0 : (md >> dsh));
+        }
+        if (((bx >> 63) != (bd >> 63))) mag = (uint64_t)(-(int64_t)mag);
+        if (L >= 0) { o->M = (L > 63) ? 0 : (X0 << L); o->D = (L > 63) ? 0 : (mag << L); }
+        else {
+            /* sh > 64 - B cannot happen for ex >= 1023 (sh <= 52) */
+            o->M = X0 >> (-L); o->D = (uint64_t)((int64_t)mag >> (-L));
+        }
+    }
+}
+/* |(int)value| mod 2^B at index k, and the signed index mod 2^B */
+NCO_HD uint32_t nco_wseg_mag(const nco_wseg_t *w, int32_t k, int B)
+{
+    return (uint32_t)((w->M + (uint64_t)(int64_t)(k - w->k0) * w->D) >> (64 - B));
+}
+NCO_HD uint32_t nco_wseg_index(const nco_wseg_t *w, int32_t k, int B)
+{
+    const uint32_t t = nco_wseg_mag(w, k, B);
+    return (w->neg ? (0u - t) : t) & ((1u << B) - 1u);
+}
+
 /* ---- the reference's scalar prologue / epilogue arithmetic, step for step ---- */
 
 /* mixcarr: phi = phi0*CDIV/DPI ; ps = freq*CDIV*ti          src/sdrcmn.c:647-648 */
@@ -658,7 +897,7 @@ NCO_HD void nco_carrier_init(double freq, double phi0, double ti, double *phi, d
 /* mixcarr: prem = phi*DPI/CDIV ; while(prem>DPI) prem-=DPI  src/sdrcmn.c:665-668 */
 NCO_HD double nco_carrier_rem(double phi_end)
 {
-    return nco_reduce_2pi(NCO_DIV(NCO_MUL(phi_end, NCO_TWO_PI), 32.0));
+    return nco_reduce_2pi_d(NCO_DIV(NCO_MUL(phi_end, NCO_TWO_PI), 32.0));
 }
 /* rescode: coff-=smax*ci ; coff-=floor(coff/len)*len        src/sdrcmn.c:611-612 */
 NCO_HD double nco_code_init(double coff, int smax, double ci, int len)

@@ -38,6 +38,34 @@ int check_walk_i(double x0, double step, int n, double wrap)
     return bad;
 }
 
+int max_dsegments = 0;
+
+/* lean double-domain walker + correlator-thread segment form against the literal loop:
+ * every value, its truncated index mod 2^B, and the end value */
+int check_walk_d(double x0, double step, int n, double wrap, int B)
+{
+    static nco_seg_t seg[NCO_MAXSEG];
+    static nco_steptab_t tab;
+    nco_wseg_t w;
+    double p = x0, xe;
+    int k, bad = 0, s = -1, cur = 0, rb = 0, ns;
+    nco_steptab_build(step, &tab);
+    ns = nco_walk_d(x0, step, n, wrap, &tab, seg, NCO_MAXSEG, &xe);
+    if (ns < 0) return 1000000;
+    if (ns > max_dsegments) max_dsegments = ns;
+    for (k = 0; k < n; k++, p += step) {
+        if (wrap > 0.0 && p >= wrap) p -= wrap;
+        while (cur + 1 < ns && seg[cur + 1].k0 <= k) cur++;
+        if (cur != s) { s = cur; rb = 0; nco_wseg_make(&seg[s], B, &w, &rb); }
+        if (seg[s].x0 + (double)(k - seg[s].k0) * seg[s].d != p) bad++;
+        if (fabs(p) < 9.0e15) {
+            if (rb || nco_wseg_index(&w, k, B) != (uint32_t)(((int)(int64_t)p) & ((1 << B) - 1))) bad++;
+        }
+    }
+    if (p != xe) bad++;
+    return bad;
+}
+
 /* returns mismatches; carrier NCO */
 int check_carrier(double freq, double phi0, double ti, int n)
 {
@@ -56,6 +84,7 @@ int check_carrier(double freq, double phi0, double ti, int n)
     }
     if (p != t.x_end) bad++;
     bad += check_walk_i(phi, ps, n, 0.0);
+    bad += check_walk_d(phi, ps, n, 0.0, 5);
     prem = p * NCO_TWO_PI / 32.0;
     while (prem > NCO_TWO_PI) prem -= NCO_TWO_PI;
     if (prem != nco_carrier_rem(t.x_end)) bad++;
@@ -86,6 +115,7 @@ int check_code(double coff, int smax, double ci, int len, int n)
     }
     if (c != t.x_end) bad++;
     bad += check_walk_i(c0, ci, N, (double)len);
+    bad += check_walk_d(c0, ci, N, (double)len, 10);
     if (c - smax * ci != nco_code_rem(t.x_end, smax, ci)) bad++;
     return bad;
 }
@@ -132,6 +162,7 @@ int fuzz(unsigned long long seed, int iters, int mode)
                     if (p != t.x_end) r++;
                     if (t.nseg > max_segments) max_segments = t.nseg;
                     r += check_walk_i(x0, step, n, 0.0);
+                    r += check_walk_d(x0, step, n, 0.0, 5);
                 }
             }
         }
@@ -149,7 +180,7 @@ int fuzz_reduce(int n)
         for (i = 0; i < iters * 5; i++) {
             double x = urand() * ldexp(1.0, (int)(urand() * 18)), y = x;
             while (y > NCO_TWO_PI) y -= NCO_TWO_PI;
-            if (y != nco_reduce_2pi(x)) b2++;
+            if (y != nco_reduce_2pi(x) || y != nco_reduce_2pi_d(x)) b2++;
         }
         /* structured: mantissas just above a binade border, near multiples of 2*pi, large x */
         for (i = 0; i < iters * 5; i++) {
@@ -163,7 +194,7 @@ int fuzz_reduce(int n)
             }
             y = x;
             while (y > NCO_TWO_PI) y -= NCO_TWO_PI;
-            if (y != nco_reduce_2pi(x)) b2++;
+            if (y != nco_reduce_2pi(x) || y != nco_reduce_2pi_d(x)) b2++;
         }
     return b2;
 }
@@ -173,7 +204,7 @@ int main(int argc, char **argv)
 {
     int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
     for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
-    printf("max segments (mode 4) %d, integer walker %d\n", max_segments, max_isegments);
+    printf("max segments (mode 4) %d, integer walker %d, double walker %d\n", max_segments, max_isegments, max_dsegments);
     { int b2 = fuzz_reduce(iters * 5); printf("reduce_2pi: %d bad of %d\n", b2, iters * 10); bad += b2; }
     return bad != 0;
 }
