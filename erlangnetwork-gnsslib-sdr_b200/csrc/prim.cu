@@ -24,6 +24,7 @@
 #include <string.h>
 #include <math.h>
 #include <vector>
+#include <mutex>
 #include "sdrb200_internal.h"
 #include "nco_exact.h"
 #include "fft_device.cuh"
@@ -716,5 +717,77 @@ extern "C" int sdrb200_checkacquisition(const double *P, int nsamp, int nfreq, i
     *peakr = o->maxP / o->maxP2;
     *codei = o->flat % nsamp;
     *freqi = o->flat / nsamp;
+    return SDRB200_OK;
+}
+
+/* ------------------------------------------- checkacquisition, allocation-free
+ * sdrb200_checkacquisition_noalloc: same arguments, same kernels and same results as
+ * sdrb200_checkacquisition above, for callers that must not allocate (CUDA graph
+ * capture around them, serving loops, harnesses that forbid cudaMalloc).  No counterpart
+ * in the reference.
+ *
+ * The scratch the two kernels need - the device copy of P, the per-block partial maxima
+ * and the result record - lives in ONE file-scope device array of fixed size
+ * (SDRB200_CHECKACQ_NOALLOC_MAXCELLS doubles + 8 KB, ~16 MB held by every GPU that loads
+ * the library, until exit).  In host code `g_ca_scratch` is only a stand-in for the
+ * symbol: its DEVICE address is fetched once per device with cudaGetSymbolAddress (that
+ * device current) and kept in g_ca_addr[].  The call makes no cudaMalloc / cudaFree /
+ * cudaMallocHost / stream or event creation: copies run on the legacy default stream from
+ * and to the caller's (pageable) memory.  Every call shares the array and finds the
+ * previous call's contents in it: nothing has to start at zero (both kernels write every
+ * word they later read; the tail area is nevertheless cleared per call), and calls
+ * that overlap on the same GPU would race on it.  Calls from several host threads of one
+ * process are therefore serialised by a mutex here (each call ends with a stream
+ * synchronise inside the lock); nothing else may use the array.                        */
+#define CA_NOALLOC_BLOCKS 296
+#define CA_NOALLOC_TAIL   8192          /* partial maxima (296 x 16 B) + ca_out_t, rounded up */
+#define CA_NOALLOC_MAXDEV 64
+static __device__ __align__(256) unsigned char g_ca_scratch[(size_t)SDRB200_CHECKACQ_NOALLOC_MAXCELLS * 8 + CA_NOALLOC_TAIL];
+static unsigned char *g_ca_addr[CA_NOALLOC_MAXDEV];     /* device address of g_ca_scratch, per device */
+static std::mutex g_ca_mtx;
+
+extern "C" int sdrb200_checkacquisition_noalloc(const double *P, int nsamp, int nfreq, int nsampchip, double ctime,
+                                                double *cn0, double *peakr, int *codei, int *freqi)
+{
+    if (!P || nsamp < 1 || nfreq < 1 || !cn0 || !peakr || !codei || !freqi) {
+        sdrb200_set_error("checkacquisition_noalloc: bad argument"); return SDRB200_EINVAL;
+    }
+    const long long total = (long long)nsamp * nfreq;
+    if (total > (long long)SDRB200_CHECKACQ_NOALLOC_MAXCELLS) {
+        sdrb200_set_error("checkacquisition_noalloc: %lld cells exceed the static scratch of %d cells "
+                          "(use sdrb200_checkacquisition)", total, SDRB200_CHECKACQ_NOALLOC_MAXCELLS);
+        return SDRB200_ERANGE;
+    }
+    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
+    std::lock_guard<std::mutex> lock(g_ca_mtx);
+    int dev = 0;
+    SDRB200_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= CA_NOALLOC_MAXDEV) { sdrb200_set_error("checkacquisition_noalloc: device index %d out of range", dev); return SDRB200_EINVAL; }
+    if (!g_ca_addr[dev]) {                              /* set-up, once per device, that device current */
+        unsigned char *p = nullptr;
+        SDRB200_CUDA_TRY(cudaGetSymbolAddress((void **)&p, g_ca_scratch));
+        if (!p) { sdrb200_set_error("checkacquisition_noalloc: no device address for the scratch symbol"); return SDRB200_ECUDA; }
+        g_ca_addr[dev] = p;
+    }
+    unsigned char *base = g_ca_addr[dev];
+    const size_t pb = (size_t)SDRB200_CHECKACQ_NOALLOC_MAXCELLS * 8;
+    double *d_P = (double *)base;
+    double *bm = (double *)(base + pb); long long *bi = (long long *)(bm + CA_NOALLOC_BLOCKS);
+    ca_out_t *d_out = (ca_out_t *)(bi + CA_NOALLOC_BLOCKS);
+    cudaStream_t st = 0;                                /* legacy default stream: nothing to create */
+    SDRB200_CUDA_TRY(cudaMemsetAsync(base + pb, 0, CA_NOALLOC_TAIL, st));
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(d_P, P, (size_t)total * 8, cudaMemcpyHostToDevice, st));
+    k_ca_max<<<CA_NOALLOC_BLOCKS, 256, 0, st>>>(d_P, total, nullptr, bm, bi);
+    LAUNCH_CHECK();
+    k_ca_row<<<1, 1024, 0, st>>>(d_P, nsamp, nfreq, nsampchip, bm, bi, CA_NOALLOC_BLOCKS, d_out);
+    LAUNCH_CHECK();
+    ca_out_t o;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(&o, d_out, sizeof(ca_out_t), cudaMemcpyDeviceToHost, st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(st));
+    const double meanP = o.sum / (double)o.cnt;
+    *cn0 = 10 * log10(o.maxP / meanP / ctime);
+    *peakr = o.maxP / o.maxP2;
+    *codei = o.flat % nsamp;
+    *freqi = o.flat / nsamp;
     return SDRB200_OK;
 }

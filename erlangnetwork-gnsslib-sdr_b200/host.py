@@ -9,7 +9,7 @@ from . import (AcqCfg, AcqResult, Error, IfgenCfg, IfgenSat, Loop, TrkChan, TrkR
                MAXCORRN, MAXTAPS, check, lib)
 
 __all__ = ["gencode", "gencode_device", "make_ifgen", "ifgen_host", "correlator", "mixcarr", "rescode",
-           "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition",
+           "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition", "checkacquisition_noalloc",
            "Stream", "Acquisition", "Tracking", "device_count", "launch_count", "make_trk_chan"]
 
 _i8p = C.POINTER(C.c_int8)
@@ -153,6 +153,19 @@ def checkacquisition(P, nsamp, nfreq, nsampchip, ctime):
     check(lib.sdrb200_checkacquisition(_p(P, _dp), int(nsamp), int(nfreq), int(nsampchip), C.c_double(ctime),
                                        C.byref(cn0), C.byref(peakr), C.byref(codei), C.byref(freqi)),
           "checkacquisition")
+    return dict(cn0=cn0.value, peakr=peakr.value, codei=codei.value, freqi=freqi.value)
+
+
+def checkacquisition_noalloc(P, nsamp, nfreq, nsampchip, ctime):
+    """sdrb200_checkacquisition_noalloc: the allocation-free variant (static device scratch,
+    at most SDRB200_CHECKACQ_NOALLOC_MAXCELLS cells; no counterpart in the reference)."""
+    P = np.ascontiguousarray(P, np.float64)
+    cn0, peakr = C.c_double(), C.c_double()
+    codei, freqi = C.c_int(), C.c_int()
+    check(lib.sdrb200_checkacquisition_noalloc(_p(P, _dp), int(nsamp), int(nfreq), int(nsampchip),
+                                               C.c_double(ctime), C.byref(cn0), C.byref(peakr),
+                                               C.byref(codei), C.byref(freqi)),
+          "checkacquisition_noalloc")
     return dict(cn0=cn0.value, peakr=peakr.value, codei=codei.value, freqi=freqi.value)
 
 

@@ -266,6 +266,20 @@ int sdrb200_pcorrelator(const int8_t *data, int dtype, double ti, int n,
 int sdrb200_checkacquisition(const double *P, int nsamp, int nfreq, int nsampchip,
                              double ctime, double *cn0, double *peakr, int *codei,
                              int *freqi);                      /* sdracq.c:71-95 */
+/* Allocation-free variant of sdrb200_checkacquisition: same arguments and results.
+ * It has NO counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid allocation).  Its scratch (device copy
+ * of P, partial maxima, result record) is one static device array of
+ * SDRB200_CHECKACQ_NOALLOC_MAXCELLS doubles (+8 KB; ~16 MB per GPU that loads the
+ * library, held until exit); nsamp*nfreq beyond that returns SDRB200_ERANGE.  No
+ * cudaMalloc/cudaFree/stream creation happens in the call (legacy default stream).
+ * All calls share the array: overlapping calls on one GPU would race, so calls of
+ * one process are serialised internally.                                        */
+#define SDRB200_CHECKACQ_NOALLOC_MAXCELLS (2 * 1024 * 1024)
+int sdrb200_checkacquisition_noalloc(const double *P, int nsamp, int nfreq, int nsampchip,
+                                     double ctime, double *cn0, double *peakr, int *codei,
+                                     int *freqi);
 
 #ifdef __cplusplus
 }
