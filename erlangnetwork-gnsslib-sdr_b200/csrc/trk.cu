@@ -10,6 +10,7 @@
 #include <mutex>
 #include "sdrb200_internal.h"
 #include "trk_device.cuh"
+#include "trk_cluster.cuh"
 
 static std::once_flag g_lut_once;
 static int g_lut_rc = SDRB200_OK;
@@ -328,7 +329,8 @@ __device__ static void trk_loops_warp(trk_state_t *st, const sdrb200_loop_t *prm
 
 /* epilogue of one code period, executed by ONE warp: everything sdrtracking and
  * the sdrthread loop body do around correlator()                              */
-__device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const trk_smem_t *sm,
+__device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const unsigned int *sumI,
+                                    const unsigned int *sumQ, double remc, double remp,
                                     sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr)
 {
     long long e0 = 0;
@@ -341,15 +343,15 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
     __syncwarp();
     /* src/sdrtrk.c:40-43: correlator's II (cos sums) lands in trk.QQ, QQ (sin sums) in trk.II */
     for (int i = lane; i < ntap; i += 32) {
-        st->QQ[i] = (double)(int)sm->sum[i] * SDRB200_CSCALE;
-        st->II[i] = (double)(int)sm->sum[SDRB200_MAXTAPS + i] * SDRB200_CSCALE;
+        st->QQ[i] = (double)(int)sumI[i] * SDRB200_CSCALE;
+        st->II[i] = (double)(int)sumQ[i] * SDRB200_CSCALE;
     }
     __syncwarp();
     if (lane == 0) {
         st->oldremcode = st->remcode;
         st->oldremcarr = st->remcarr;
-        st->remcode = sm->remc;
-        st->remcarr = sm->remp;
+        st->remcode = remc;
+        st->remcarr = remp;
         /* sdrnavigation(), src/sdrnav.c:19-41 */
         const int rate = ch->navrate;
         /* cnt % rate: 32-bit while cnt fits (a 64-bit remainder is a subroutine) */
@@ -442,227 +444,13 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
 #undef TRK_EP
 }
 
-struct trk_run_smem_t {
-    trk_smem_t t;
-    trk_state_t st;
-    sdrb200_trk_rec_t rec;
-    int32_t taps[SDRB200_MAXCORRN];
-    int32_t go, pad;
-    /* tables of the NEXT period, walked ahead while the workers are busy with this one
-     * (only when this period is known not to change the NCO frequencies) */
-    trk_ncohdr_t nx_carr, nx_code;
-    double  nx_remc;
-    int32_t nx_n;               /* currnsamp the staged tables were walked for        */
-    int32_t nx_valid;           /* staged tables are complete                        */
-    int32_t spec_do;            /* this period: walk ahead                           */
-    int32_t have;               /* this period: tables came from the staging area    */
-    trk_chan_dev_t chc;         /* the channel's constants (all but the code: t.codetab has it) */
-    unsigned long long boff;    /* st.buffloc % capacity, advanced by additions (a 64-bit remainder
-                                 * by every thread every period was 5 % of the kernel's instructions) */
-};
-
-template <int DTYPE>
-__global__ void __launch_bounds__(TRK_THREADS, 1)
-k_trk_run(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ states,
-          const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods, int maxn, int qcap,
-          sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err,
-          long long *__restrict__ prof)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    trk_run_smem_t *sm = (trk_run_smem_t *)smem_raw;
-    const trk_work_t wk = trk_work_layout<DTYPE>((unsigned int *)(smem_raw + sizeof(trk_run_smem_t)), maxn, qcap);
-    const trk_chan_dev_t *ch = &chans[blockIdx.x];
-    trk_state_t *st = &sm->st;
-    const bool worker = threadIdx.x >= 64;
-
-    /* load channel state and constants */
-    {
-        const uint32_t *src = (const uint32_t *)&states[blockIdx.x];
-        uint32_t *dst = (uint32_t *)st;
-        for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += blockDim.x) dst[i] = src[i];
-        for (int i = threadIdx.x; i < ch->clen; i += blockDim.x) sm->t.codetab[i] = ch->code[i];
-        if (threadIdx.x < ch->corrn) sm->taps[threadIdx.x] = ch->corrp[threadIdx.x];
-        trk_init_smem(&sm->t);
-        /* record slots beyond the channel's taps are never written: keep them zero */
-        for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) ((uint32_t *)&sm->rec)[i] = 0u;
-        if (threadIdx.x == 0) { sm->nx_valid = 0; sm->nx_n = -1; sm->have = 0; sm->spec_do = 0; }
-        /* the serial sections (period start, epilogue, NCO lanes) read the channel constants
-         * many times per period: keep them in shared memory, not behind L1/L2            */
-        for (int i = threadIdx.x; i < (int)(offsetof(trk_chan_dev_t, code) / 4); i += blockDim.x)
-            ((uint32_t *)&sm->chc)[i] = ((const uint32_t *)ch)[i];
-    }
-    __syncthreads();
-    ch = &sm->chc;
-    const int ns = ch->corrn;
-    const int smax = sm->taps[ns - 1];
-    int done = 0, n_prev = 0;
-    /* optional phase profile (cycles, CTA 0, thread 0): go, tables, convert, mix, taps, epilogue */
-    long long pt[6] = {0, 0, 0, 0, 0, 0}, t0 = 0;
-    const bool prof_on = prof != nullptr && blockIdx.x == 0 && threadIdx.x == 64;     /* first worker lane */
-#define TRK_PT(i) do { if (prof_on) { const long long t1 = trk_clock(); pt[i] += t1 - t0; t0 = t1; } } while (0)
-    if (prof_on) t0 = trk_clock();
-
-    for (int it = 0; it < nperiods; it++) {
-#ifdef TRK_DEBUG
-        if (threadIdx.x == 0) g_dbg_on = (it == nperiods - 12);
-        __syncthreads();
-#endif
-        DBG(0);
-        if (threadIdx.x == TRK_NCO_B) {
-            /* ring offset of this period's first sample, beside the carrier lane's decisions */
-            if (it == 0) sm->boff = st->buffloc % capacity;
-            else {                                      /* the epilogue added n_prev to buffloc */
-                unsigned long long b = sm->boff + (unsigned long long)n_prev;
-                if (b >= capacity) b -= capacity;
-                if (b >= capacity) b %= capacity;
-                sm->boff = b;
-            }
-            /* Will this period's epilogue leave carrfreq/codefreq alone?  Once bit sync is
-             * reached (flagsync never drops), the loop filters run only when checkbit()
-             * raises swloop, which is a function of counters known now
-             * (src/sdrnav.c:241-262, src/sdrmain.c:271-280).                            */
-            int quiet = 0;
-            if (st->flagsync && ch->navrate > 1) {
-                const int rate = ch->navrate;
-                const int biti = (st->cnt >> 32) ? (int)(st->cnt % (uint64_t)rate) : (int)((uint32_t)st->cnt % (uint32_t)rate);
-                const int diffi = biti - st->synci;
-                const int navcnt = (diffi == 1 || diffi == -rate + 1) ? 1 : st->navcnt;
-                quiet = (navcnt % ch->loopms != 0) ? 1 : 0;
-            }
-            sm->spec_do = (quiet && it + 1 < nperiods) ? 1 : 0;
-        }
-        if (threadIdx.x == TRK_NCO_A) {
-            /* sdrtracking(), src/sdrtrk.c:31-32 */
-            /* staged tables were walked for exactly this state (frequencies untouched since,
-             * remainders = the staged inputs), so their sample count is this period's */
-            const int staged = (sm->nx_valid && sm->nx_n >= 0) ? 1 : 0;
-            st->currnsamp = staged ? sm->nx_n : nco_currnsamp(ch->clen, st->remcode, st->codefreq, ch->f_sf);
-            sm->go = (st->currnsamp > 0 && st->currnsamp <= maxn &&
-                      st->buffloc + (uint64_t)st->currnsamp <= avail) ? 1 : 0;
-            sm->have = staged;
-            sm->nx_valid = 0;
-            if (staged) {                               /* staged tables become the tables of this period */
-                sm->t.icarr = (sm->t.icarr == sm->t.segs[0]) ? sm->t.segs[2] : sm->t.segs[0];
-                sm->t.icode = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
-                sm->t.carr = sm->nx_carr; sm->t.code = sm->nx_code; sm->t.remc = sm->nx_remc;
-            }
-        }
-        __syncthreads();
-        if (!sm->go) break;
-        TRK_PT(0);
-        DBG(1);
-        const int n = st->currnsamp;
-        n_prev = n;
-        /* correlator(..., carrfreq, oldremcarr(=remcarr), codefreq, oldremcode(=remcode), ...) */
-        long long w0 = 0;
-        if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
-        const int8_t *data = ifbuf + (size_t)sm->boff * DTYPE;
-        const int wid = threadIdx.x >> 5;
-        const int have = sm->have, spec_do = sm->spec_do;
-        if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) { prof[10] += have; prof[11] += spec_do; }
-        trk_zero_period(&sm->t);
-        if (wid == (TRK_NCO_A >> 5)) {
-            if (!have) trk_walk_carrier(&sm->t, ch->ti, n, st->carrfreq, st->remcarr);
-            if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[8] += trk_clock() - w0;
-            asm volatile("bar.arrive 2, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* carrier table + cleared accumulators: releases the workers */
-            if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) w0 = trk_clock();
-            trk_carrier_rem(&sm->t);
-            DBG(11);
-            if (prof && blockIdx.x == 0 && threadIdx.x == TRK_NCO_A) prof[9] += trk_clock() - w0;
-            /* remp is ready: the carrier warp's share of the end-of-correlation barrier.  It does
-             * not wait there - the epilogue runs on the code warp - so a walk-ahead can overlap it */
-            asm volatile("bar.arrive 5, %0;" ::"n"(TRK_THREADS) : "memory");
-            if (spec_do) {
-                asm volatile("bar.sync 4, 64;" ::: "memory");          /* remc of this period (code warp) */
-                if (threadIdx.x == TRK_NCO_A) {
-                    /* next period: frequencies unchanged, remainders are this period's results */
-                    const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
-                    int ok = (n2 > 0 && n2 <= maxn) ? 1 : 0;
-                    if (ok) {
-                        double phi, ps, xe;
-                        nco_carrier_init(st->carrfreq, sm->t.remp, ch->ti, &phi, &ps);
-                        nco_iseg_t *dst = (sm->t.icarr == sm->t.segs[0]) ? sm->t.segs[2] : sm->t.segs[0];
-                        const int nsg = trk_walk_call(phi, ps, n2, 0.0, dst, &xe);
-                        if (nsg < 0) ok = 0;
-                        sm->nx_carr.nseg = nsg < 0 ? 0 : nsg; sm->nx_carr.x_end = xe;
-                    }
-                    sm->nx_n = ok ? n2 : -1;
-                }
-                __syncwarp();
-                DBG(12);
-            }
-        } else if (wid == (TRK_NCO_B >> 5)) {
-            if (!have) trk_walk_code(&sm->t, ch->ti, n, st->codefreq, st->remcode, smax, ch->clen);
-            asm volatile("bar.arrive 3, %0;" ::"n"(TRK_WORKERS + 32) : "memory");   /* code table: releases the workers' tap phase */
-            if (spec_do) asm volatile("bar.arrive 4, 64;" ::: "memory");               /* remc is final: the carrier warp may read it */
-            /* remc is final: the code warp's share of the end-of-correlation barrier.  Like the
-             * carrier warp it does not wait there - the epilogue runs on worker warp 2 - so its
-             * walk-ahead (the longest chain of a staged period) overlaps the epilogue          */
-            asm volatile("bar.arrive 5, %0;" ::"n"(TRK_THREADS) : "memory");
-            if (spec_do) {
-                if (threadIdx.x == TRK_NCO_B) {
-                    const bool pf = prof && blockIdx.x == 0;
-                    long long c0t = 0, c1t = 0;
-                    if (pf) c0t = trk_clock();
-                    const int n2 = nco_currnsamp(ch->clen, sm->t.remc, st->codefreq, ch->f_sf);
-                    int ok = (n2 > 0 && n2 <= maxn) ? 1 : 0;
-                    if (ok) {
-                        const double ci = __dmul_rn(ch->ti, st->codefreq);
-                        const double c0 = nco_code_init(sm->t.remc, smax, ci, ch->clen);
-                        double xe;
-                        nco_iseg_t *dst = (sm->t.icode == sm->t.segs[1]) ? sm->t.segs[3] : sm->t.segs[1];
-                        if (pf) c1t = trk_clock();
-                        const int nsg = trk_walk_call(c0, ci, n2 + 2 * smax, (double)ch->clen, dst, &xe);
-                        if (pf) prof[15] += trk_clock() - c1t;
-                        if (nsg < 0) ok = 0;
-                        sm->nx_code.nseg = nsg < 0 ? 0 : nsg; sm->nx_code.x_end = xe;
-                        sm->nx_remc = nco_code_rem(xe, smax, ci);
-                    }
-                    sm->nx_valid = ok;                  /* the carrier warp's verdict is nx_n >= 0 */
-                    if (pf) prof[7] += trk_clock() - c0t;
-                }
-                __syncwarp();
-                DBG(13);
-            }
-        } else {
-            trk_bar_carrier();
-            TRK_PT(1);
-            trk_mix_prefix<DTYPE>(&sm->t, data, n, wk);
-            DBG(4);
-            trk_bar_code();                             /* all prefix rows written; code table ready */
-            TRK_PT(3);
-            trk_tap_sums<DTYPE>(&sm->t, wk, data, n, sm->taps, ns, smax);
-        }
-        if (wid >= 2) asm volatile("bar.sync 5, %0;" ::"n"(TRK_THREADS) : "memory");
-        TRK_PT(4);
-        DBG(9);
-        if (wid == 2)
-            trk_epilogue(ch, st, &sm->t, recs ? &sm->rec : nullptr, threadIdx.x & 31,
-                         (prof && blockIdx.x == 0) ? prof : nullptr);
-        if (wid == 2) DBG(14);
-        __syncthreads();
-        if (recs) {
-            const uint32_t *src = (const uint32_t *)&sm->rec;
-            uint32_t *dst = (uint32_t *)&recs[(size_t)blockIdx.x * nperiods + it];
-            for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += blockDim.x) dst[i] = src[i];
-        }
-        TRK_PT(5);
-        DBG(10);
-        done++;
-    }
-    if (prof_on) { for (int i = 0; i < 6; i++) prof[i] = pt[i]; prof[6] = done; }
-    __syncthreads();
-    {
-        uint32_t *dst = (uint32_t *)&states[blockIdx.x];
-        const uint32_t *src = (const uint32_t *)st;
-        for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += blockDim.x) dst[i] = src[i];
-    }
-    if (threadIdx.x == 0) { nrec[blockIdx.x] = done; if (sm->t.err) *err = 1; }
-}
+#define TRK_NT_SMALL 384
+#include "trk_run_kernel.cuh"
 
 /* ------------------------------------------------------------- host side */
 struct sdrb200_trk {
     int nch, dtype, maxn, smax, maxtap, qcap;
+    int cl, ctrl_works;              /* cluster size per channel (0: not chosen yet); rank 0's team takes periods */
     cudaStream_t st;
     trk_chan_dev_t *h_chan, *d_chan;
     trk_state_t *h_state0, *d_state;
@@ -791,20 +579,61 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
             e->rec_cap = need;
         }
     }
-    size_t smem = sizeof(trk_run_smem_t) + sizeof(unsigned int) * TRK_WORK_WORDS(e->maxn, e->dtype, e->qcap);
+    size_t smem = sizeof(trk_cl_smem_t) + sizeof(unsigned int) * TRK_WORK_WORDS(e->maxn, e->dtype, e->qcap);
     if (smem > TRK_SMEM_LIMIT) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
     sdrb200_trk_rec_t *recs = with_rec ? e->d_rec : NULL;
-#define TRK_LAUNCH(DT)                                                                                    \
-    do {                                                                                                  \
-        SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_trk_run<DT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        k_trk_run<DT><<<e->nch, TRK_THREADS, smem, e->st>>>(e->d_chan, e->d_state, s->d_buf, s->capacity, s->count, \
-                                                            nperiods, e->maxn, e->qcap, recs, e->d_nrec, e->d_err, e->d_prof); \
-    } while (0)
-    if (e->dtype == 1) TRK_LAUNCH(1); else TRK_LAUNCH(2);
-#undef TRK_LAUNCH
+    /* CTA size: the small instantiation when one round of its worker team covers the period */
+    const int small = ((size_t)e->maxn * e->dtype + 3 <= (size_t)(TRK_NT_SMALL - TRK_T0) * TRK_SPAN) ? 1 : 0;
+    const int nt = small ? TRK_NT_SMALL : TRK_THREADS;
+    const void *fn = (e->dtype == 1) ? (small ? (const void *)k_trk_cl<1, TRK_NT_SMALL> : (const void *)k_trk_cl<1, TRK_THREADS>)
+                                     : (small ? (const void *)k_trk_cl<2, TRK_NT_SMALL> : (const void *)k_trk_cl<2, TRK_THREADS>);
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cudaLaunchAttribute at[1];
+    cfg.blockDim = dim3(nt); cfg.dynamicSmemBytes = smem; cfg.stream = e->st;
+    at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    if (!e->cl) {
+        /* cluster size: the largest of 8, 4, 2 whose clusters are all co-resident (so that every
+         * channel advances at once); beyond that one CTA per channel, scheduled in waves */
+        int cl = 1;
+        const char *env = getenv("SDRB200_TRK_CLUSTER");
+        if (env && atoi(env) >= 1 && atoi(env) <= 8) cl = atoi(env);
+        else {
+            for (int c = 8; c >= 2; c >>= 1) {
+                int nact = 0;
+                cfg.gridDim = dim3(e->nch * c); at[0].val.clusterDim.x = c;
+                if (cudaOccupancyMaxActiveClusters(&nact, fn, &cfg) == cudaSuccess && nact >= e->nch) { cl = c; break; }
+                cudaGetLastError();
+            }
+        }
+        e->cl = cl;
+        env = getenv("SDRB200_TRK_CTRL_WORKS");
+        e->ctrl_works = env ? atoi(env) : 0;
+    }
+    cfg.gridDim = dim3(e->nch * e->cl); at[0].val.clusterDim.x = e->cl;
+    {
+        const trk_chan_dev_t *a_ch = e->d_chan; trk_state_t *a_st = e->d_state; const int8_t *a_if = s->d_buf;
+        uint64_t a_cap = s->capacity, a_av = s->count; int a_np = nperiods, a_mx = e->maxn, a_qc = e->qcap;
+        int *a_nrec = e->d_nrec, *a_err = e->d_err, a_cw = e->ctrl_works; long long *a_prof = e->d_prof;
+        void *args[] = {&a_ch, &a_st, &a_if, &a_cap, &a_av, &a_np, &a_mx, &a_qc, &recs, &a_nrec, &a_err, &a_cw, &a_prof};
+        SDRB200_CUDA_TRY(cudaLaunchKernelExC(&cfg, fn, args));
+    }
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     e->last_nperiods = nperiods; e->last_with_rec = with_rec;
+    return SDRB200_OK;
+}
+
+/* cluster size per channel (1, 2, 4 or 8; 0 = choose at the next launch from the co-residency of
+ * this engine's channels alone) and whether rank 0's worker team takes periods too.  For callers
+ * that run several engines at once and know the total number of channels on the GPU.        */
+extern "C" int sdrb200_trk_set_cluster(sdrb200_trk_t *e, int cluster_size, int ctrl_works)
+{
+    if (!e || cluster_size < 0 || cluster_size > 8 || (cluster_size & (cluster_size - 1))) {
+        sdrb200_set_error("trk_set_cluster: cluster size must be 0, 1, 2, 4 or 8"); return SDRB200_EINVAL;
+    }
+    e->cl = cluster_size; e->ctrl_works = ctrl_works ? 1 : 0;
     return SDRB200_OK;
 }
 

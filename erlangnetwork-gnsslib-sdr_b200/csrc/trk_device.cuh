@@ -37,7 +37,6 @@
 #define TRK_NCO_A     0                      /* carrier NCO lane; warp 0 = epilogue warp */
 #define TRK_NCO_B     32                     /* code NCO lane (warp 1)             */
 #define TRK_SPAN      20                     /* bytes of IF owned by one worker per round */
-#define TRK_ROUND_BYTES (TRK_WORKERS * TRK_SPAN)
 #define TRK_MAXSEG    96                     /* NCO segments held on the device    */
 /* rows of the prefix store: one per 20-byte span of the (4-byte aligned) window */
 #define TRK_ROWS(nbytes) (((nbytes) + 3 + TRK_SPAN - 1) / TRK_SPAN + 1)
@@ -94,9 +93,10 @@ __device__ __forceinline__ trk_work_t trk_work_layout(unsigned int *w, int maxn,
     return k;
 }
 
+template <int NW>
 __device__ __forceinline__ void trk_bar_workers()
 {
-    asm volatile("bar.sync 1, %0;" ::"n"(TRK_WORKERS) : "memory");
+    asm volatile("bar.sync 1, %0;" ::"n"(NW) : "memory");
 }
 
 /* last segment with k0 <= k */
@@ -253,20 +253,22 @@ __device__ __forceinline__ int trk_sbyte(unsigned int w, int b)
  * words touching the window must be readable - the IF stream's guard and the    *
  * primitive's arena guarantee it).  Row u of wk.P2 receives the running (I,Q)   *
  * sums of worker u's samples, wk.base[u] the sums of all earlier rows.           */
-template <int DTYPE>
+/* NW worker threads, the first of them thread T0 of the CTA (defaults: the single-CTA layout) */
+template <int DTYPE, int NW = TRK_WORKERS, int T0 = 64>
 __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__restrict__ data, int n,
                                                const trk_work_t &wk)
 {
     constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;     /* samples per row, row stride (pairs) */
-    const int u = threadIdx.x - 64, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int ROUND_BYTES = NW * TRK_SPAN, NWARP = NW / 32;
+    const int u = threadIdx.x - T0, lane = threadIdx.x & 31, wwarp = u >> 5;
     const uintptr_t addr = (uintptr_t)data;
     const int a = (int)(addr & 3);
     const unsigned int *wbase = (const unsigned int *)(addr - a);
     const int nbytes = n * DTYPE + a;
-    const int rounds = (nbytes + TRK_ROUND_BYTES - 1) / TRK_ROUND_BYTES;
+    const int rounds = (nbytes + ROUND_BYTES - 1) / ROUND_BYTES;
     DBG(2);
     for (int r = 0; r < rounds; r++) {
-        const int row = r * TRK_WORKERS + u;
+        const int row = r * NW + u;
         const int byte0 = row * TRK_SPAN;
         const int kfirst = (byte0 - a) / DTYPE;          /* exact: a is even for I/Q streams */
         unsigned int runI = 0u, runQ = 0u;
@@ -317,10 +319,10 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
             const int i = atomicAdd(&sm->nslow[0], 1);
             if (i < 128) sm->slow[0][i] = row; else sm->err = 3;
         }
-        trk_bar_workers();
+        trk_bar_workers<NW>();
         {
             const int ns_ = min(sm->nslow[0], 128);
-            for (int it = warp - 2; it < ns_; it += TRK_WORKERS / 32) {
+            for (int it = wwarp; it < ns_; it += NWARP) {
                 const int srow = sm->slow[0][it];
                 const int kk = (srow * TRK_SPAN - a) / DTYPE + lane;
                 unsigned int I = 0u, Q = 0u;
@@ -344,34 +346,35 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
                 if (lane == S - 1) wk.base[srow] = make_uint2(I, Q);      /* row total, picked up by the owner */
             }
         }
-        trk_bar_workers();
+        trk_bar_workers<NW>();
         if (slow) { const uint2 tt = wk.base[row]; runI = tt.x; runQ = tt.y; }
         if (u == 0) sm->nslow[0] = 0;                     /* next round */
         DBG(3);
-        /* block-wide exclusive scan of the row totals over the worker warps 2..31 */
+        /* block-wide exclusive scan of the row totals over the worker warps */
         unsigned int incI = runI, incQ = runQ;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned int uI = __shfl_up_sync(0xffffffffu, incI, o), uQ = __shfl_up_sync(0xffffffffu, incQ, o);
             if (lane >= o) { incI += uI; incQ += uQ; }
         }
-        if (lane == 31) { sm->wtot[0][warp] = incI; sm->wtot[1][warp] = incQ; }
-        trk_bar_workers();
-        /* lane l holds the total of warp l (l >= 2); inclusive scan over lanes */
-        unsigned int wI = (lane >= 2) ? sm->wtot[0][lane] : 0u, wQ = (lane >= 2) ? sm->wtot[1][lane] : 0u;
+        if (lane == 31) { sm->wtot[0][wwarp] = incI; sm->wtot[1][wwarp] = incQ; }
+        trk_bar_workers<NW>();
+        /* lane l holds the total of worker warp l; inclusive scan over lanes */
+        unsigned int wI = (lane < NWARP) ? sm->wtot[0][lane] : 0u, wQ = (lane < NWARP) ? sm->wtot[1][lane] : 0u;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const unsigned int uI = __shfl_up_sync(0xffffffffu, wI, o), uQ = __shfl_up_sync(0xffffffffu, wQ, o);
             if (lane >= o) { wI += uI; wQ += uQ; }
         }
         const unsigned int allI = __shfl_sync(0xffffffffu, wI, 31), allQ = __shfl_sync(0xffffffffu, wQ, 31);
-        const unsigned int prevI = __shfl_sync(0xffffffffu, wI, warp - 1), prevQ = __shfl_sync(0xffffffffu, wQ, warp - 1);
+        unsigned int prevI = __shfl_sync(0xffffffffu, wI, (wwarp + 31) & 31), prevQ = __shfl_sync(0xffffffffu, wQ, (wwarp + 31) & 31);
+        if (wwarp == 0) { prevI = 0u; prevQ = 0u; }
         if (byte0 < nbytes + TRK_SPAN)
             wk.base[row] = make_uint2(sm->carry[0] + prevI + incI - runI, sm->carry[1] + prevQ + incQ - runQ);
         if (rounds > 1) {
-            trk_bar_workers();                           /* everyone has read wtot / carry */
+            trk_bar_workers<NW>();                       /* everyone has read wtot / carry */
             if (u == 0) { sm->carry[0] += allI; sm->carry[1] += allQ; }
-            trk_bar_workers();
+            trk_bar_workers<NW>();
         }
     }
 }
@@ -400,14 +403,14 @@ __device__ __forceinline__ uint2 trk_prefix2_at(const trk_work_t &wk, int a, int
  *      no cross-lane reduction and no divergence.                                *
  * Preceded by a CTA barrier (prefix rows complete), followed by one before       *
  * sm->sum is read.                                                               */
-template <int DTYPE>
+template <int DTYPE, int NW = TRK_WORKERS, int T0 = 64>
 __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &wk, const int8_t *data, int n,
                                              const int *taps, int ns, int smax)
 {
-    const int t = threadIdx.x - 64, lane = threadIdx.x & 31, wwarp = (threadIdx.x >> 5) - 2;
+    const int t = threadIdx.x - T0, lane = threadIdx.x & 31, wwarp = t >> 5;
     const int a = (int)((uintptr_t)data & 3);
     const int N = n + 2 * smax, ntap = 1 + 2 * ns;
-    const int PP = (N + TRK_WORKERS - 1) / TRK_WORKERS;
+    const int PP = (N + NW - 1) / NW;
     const int p0 = t * PP, p1 = min(p0 + PP, N);
     /* (a) */
     DBG(5);
@@ -453,9 +456,9 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
             const int i = atomicAdd(&sm->nslow[1], 1);
             if (i < 128) sm->slow[1][i] = t; else sm->err = 3;
         }
-        trk_bar_workers();
+        trk_bar_workers<NW>();
         const int ns_ = min(sm->nslow[1], 128);
-        for (int it = wwarp; it < ns_; it += TRK_WORKERS / 32) {
+        for (int it = wwarp; it < ns_; it += NW / 32) {
             const int q0 = sm->slow[1][it] * PP, q1 = min(q0 + PP, N);
             for (int pb = q0; pb < q1; pb += 32) {
                 const int p = pb + lane;
@@ -473,7 +476,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         }
     }
     DBG(6);
-    trk_bar_workers();
+    trk_bar_workers<NW>();
     DBG(7);
     /* (b) one lane per (tap, queue entry): a lane reads the (I,Q) prefix pair of its position
      * once and accumulates both sums, so a tap costs one lookup per entry; the 32 / ntap lane
@@ -489,7 +492,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         const int bias = smax + off;
         unsigned int accI = 0u, accQ = 0u;
 #pragma unroll 4
-        for (int e = wwarp * G + g; e < qn; e += (TRK_WORKERS / 32) * G) {
+        for (int e = wwarp * G + g; e < qn; e += (NW / 32) * G) {
             const unsigned int entry = wk.queue[e];
             const unsigned int delta = (entry >> 31) ? 0xfffffffeu : 2u;        /* r_{q-1} - r_q */
             const uint2 pf = trk_prefix2_at<DTYPE>(wk, a, min(max((int)(entry & 0x7fffffffu) - bias, 0), n));

@@ -1,0 +1,307 @@
+/* trk_run_kernel.cuh - k_trk_cl: the batched tracking kernel, one thread-block CLUSTER per
+ * channel (included by trk.cu after the epilogue functions).
+ *
+ * Every CTA has the same warp layout:
+ *   warp 0   carrier NCO lane   (control; active in cluster rank 0 only)
+ *   warp 1   code NCO lane      (control; rank 0 only)
+ *   warp 2   epilogue warp      (control; rank 0 only): cumsumcorr, bit/frame sync, pll/dll,
+ *            observables, record - everything around correlator() in sdrtracking() and the
+ *            sdrthread loop body (src/sdrtrk.c:31-47, src/sdrmain.c:264-312)
+ *   warps 3.. worker team: correlator() of one whole code period (src/sdrcmn.c:687-722)
+ * Code period q of the channel is correlated by the worker team of cluster rank
+ * r0 + q % W (W teams; r0 = 1 when rank 0 keeps its team idle so that its NCO lanes have the
+ * SM to themselves, else 0).  Each team owns two table slots, so period q may be handed out
+ * once period q - 2W has reported back.
+ *
+ * Why this shape: the NCO phases are a serial floating-point recurrence over periods
+ * (remcode/remcarr feed the next period), the correlation of a period is not.  After bit
+ * sync the loop filters touch carrfreq/codefreq only every loopms-th period
+ * (src/sdrnav.c:241-262, src/sdrmain.c:271-280), so in between the NCO lanes run ahead of
+ * the correlators and consecutive periods are correlated concurrently on different SMs.
+ */
+#define TRK_T0      96                       /* first worker thread                         */
+#define TRK_RING    16                       /* periods in flight: result / hand-over ring   */
+
+/* header of a table slot in a worker CTA, written remotely by the control warps */
+struct trk_slot_t {
+    int32_t ncarr;                           /* carrier segments (carrier lane)             */
+    int32_t ncode;                           /* code segments                               */
+    int32_t n;                               /* currnsamp                                   */
+    int32_t stop;                            /* no more periods: the team leaves            */
+    unsigned long long boff;                 /* ring offset of the period's first sample    */
+    int32_t q, pad;
+};
+
+/* what the NCO lanes hand to the epilogue warp for period q (slot q % TRK_RING) */
+struct trk_hand_t {
+    int32_t n, go, quiet, pad;
+    double  remc, remp;
+};
+
+struct trk_cl_smem_t {
+    trk_smem_t t;                            /* worker side: tables (2 slots x {carrier, code}), accumulators */
+    int32_t taps[SDRB200_MAXCORRN];
+    /* ---- worker side */
+    unsigned long long full[2];              /* mbarriers: slot s holds the tables of a period (64 arrivals) */
+    trk_slot_t slot[2];
+    /* ---- control side (rank 0) */
+    unsigned long long done[TRK_RING];       /* mbarriers: tap sums of period q arrived (32 arrivals) */
+    unsigned int res[TRK_RING][2 * SDRB200_MAXTAPS + 2];   /* tap sums mod 2^32 (I.., Q..), err */
+    trk_hand_t hand[TRK_RING];
+    volatile int seq_code;                   /* periods whose n/go the code lane has published   */
+    volatile int seq_remc;                   /* ... whose remc is in hand[]                     */
+    volatile int seq_remp;                   /* ... whose remp is in hand[] (carrier lane)      */
+    volatile int epi_count;                  /* periods the epilogue has finished               */
+    int32_t pad0;
+    nco_iseg_t walk[2][TRK_MAXSEG];          /* the lanes walk here, then copy out               */
+    trk_state_t st;
+    sdrb200_trk_rec_t rec;
+    trk_chan_dev_t chc;                      /* the channel's constants (code excluded: t.codetab) */
+};
+
+/* will the epilogue of the period that starts with these counters leave carrfreq/codefreq alone?
+ * Once bit sync is reached (flagsync never drops) the loop filters run only when checkbit()
+ * raises swloop, a function of counters (src/sdrnav.c:241-262, src/sdrmain.c:271-280).
+ * Advances navcnt the way checkbit does.                                                    */
+__device__ __forceinline__ int trk_quiet_forecast(unsigned long long cnt, int synci, int *navcnt, int rate, int loopms)
+{
+    const int biti = (cnt >> 32) ? (int)(cnt % (unsigned long long)rate) : (int)((uint32_t)cnt % (uint32_t)rate);
+    const int diffi = biti - synci;
+    const int nc = (diffi == 1 || diffi == -rate + 1) ? 1 : *navcnt;
+    *navcnt = nc + 1;
+    return (nc % loopms != 0) ? 1 : 0;
+}
+
+/* copy nseg segments from the lane's walk buffer to a table of the team's slot (all 32 lanes) */
+__device__ __forceinline__ void trk_push_table(const nco_iseg_t *src, int nseg, uint32_t dst_cluster_addr, int lane)
+{
+    const uint4 *s4 = (const uint4 *)src;
+    for (int i = lane; i < nseg * 2; i += 32) cl_st_v4(dst_cluster_addr + 16u * (uint32_t)i, s4[i]);
+}
+
+template <int DTYPE, int NT>
+__global__ void __launch_bounds__(NT, (NT >= 1024) ? 1 : 2)
+k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ states,
+         const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods, int maxn, int qcap,
+         sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err, int ctrl_works,
+         long long *__restrict__ prof)
+{
+    constexpr int NW = NT - TRK_T0, R = TRK_RING;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    trk_cl_smem_t *sm = (trk_cl_smem_t *)smem_raw;
+    const trk_work_t wk = trk_work_layout<DTYPE>((unsigned int *)(smem_raw + sizeof(trk_cl_smem_t)), maxn, qcap);
+    const int rank = (int)cl_rank(), CL = (int)cl_size();
+    const int chno = blockIdx.x / CL;
+    const int r0 = (ctrl_works || CL == 1) ? 0 : 1;     /* first rank whose worker team takes periods */
+    const int W = CL - r0;
+    const trk_chan_dev_t *chg = &chans[chno];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool ctrl = (rank == 0);
+    trk_state_t *st = &sm->st;
+
+    /* ---- set-up: every CTA holds the code and taps; rank 0 also the channel state */
+    for (int i = threadIdx.x; i < chg->clen; i += NT) sm->t.codetab[i] = chg->code[i];
+    if (threadIdx.x < chg->corrn) sm->taps[threadIdx.x] = chg->corrp[threadIdx.x];
+    trk_init_smem(&sm->t);
+    if (ctrl) {
+        const uint32_t *src = (const uint32_t *)&states[chno];
+        uint32_t *dst = (uint32_t *)st;
+        for (int i = threadIdx.x; i < (int)(sizeof(trk_state_t) / 4); i += NT) dst[i] = src[i];
+        /* record slots beyond the channel's taps are never written: keep them zero */
+        for (int i = threadIdx.x; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += NT) ((uint32_t *)&sm->rec)[i] = 0u;
+        for (int i = threadIdx.x; i < (int)(offsetof(trk_chan_dev_t, code) / 4); i += NT)
+            ((uint32_t *)&sm->chc)[i] = ((const uint32_t *)chg)[i];
+    }
+    if (threadIdx.x == 0) {
+        cl_mbar_init(&sm->full[0], 64); cl_mbar_init(&sm->full[1], 64);
+        for (int i = 0; i < R; i++) cl_mbar_init(&sm->done[i], 32);
+        sm->seq_code = 0; sm->seq_remc = 0; sm->seq_remp = 0; sm->epi_count = 0;
+        cl_fence_mbar_init();
+    }
+    __syncthreads();
+    cl_sync_all();
+    const trk_chan_dev_t *ch = &sm->chc;                 /* valid in rank 0 only */
+    const int ns = chg->corrn;
+    const int smax = sm->taps[ns - 1];
+
+    if (ctrl && wid == 1) {
+        /* ================= code NCO lane: decides n / go of every period, walks the code table */
+        double codefreq = 0.0, remc = 0.0;
+        unsigned long long buffloc = 0ull, boff = 0ull, cnt = 0ull;
+        int navcnt = 0, synci = 0, flagsync = 0, prev_quiet = 0, q = 0;
+        for (;; q++) {
+            int n = 0, go = 0, quiet = 0, nseg = 0;
+            if (lane == 0) {
+                if (q < nperiods) {
+                    if (q == 0 || !prev_quiet) {
+                        cl_flag_wait_ge(&sm->epi_count, q);          /* the loop filters of period q-1 have run */
+                        codefreq = st->codefreq; remc = st->remcode; cnt = st->cnt; navcnt = st->navcnt;
+                        synci = st->synci; flagsync = st->flagsync;
+                        if (q == 0) { buffloc = st->buffloc; boff = buffloc % capacity; }
+                    }
+                    n = nco_currnsamp(ch->clen, remc, codefreq, ch->f_sf);            /* src/sdrtrk.c:31-32 */
+                    go = (n > 0 && n <= maxn && buffloc + (unsigned long long)n <= avail) ? 1 : 0;
+                    if (go && flagsync && ch->navrate > 1) quiet = trk_quiet_forecast(cnt, synci, &navcnt, ch->navrate, ch->loopms);
+                }
+                /* flow control: the team's slot is free, the rings' slots are consumed */
+                if (q >= 2 * W) cl_mbar_wait(&sm->done[(q - 2 * W) % R], (uint32_t)(((q - 2 * W) / R) & 1));
+                if (q >= R) cl_flag_wait_ge(&sm->epi_count, q - R + 1);
+                sm->hand[q % R].n = n; sm->hand[q % R].go = go; sm->hand[q % R].quiet = quiet;
+                cl_flag_set(&sm->seq_code, q + 1);
+            }
+            go = __shfl_sync(0xffffffffu, go, 0);
+            if (!go) break;
+            n = __shfl_sync(0xffffffffu, n, 0);
+            double remc2 = 0.0;
+            if (lane == 0) {
+                const double ci = __dmul_rn(ch->ti, codefreq);                          /* ti*crate, sdrcmn.c:709 */
+                const double c0 = nco_code_init(remc, smax, ci, ch->clen);
+                double xe;
+                nseg = trk_walk_call(c0, ci, n + 2 * smax, (double)ch->clen, sm->walk[1], &xe);
+                if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
+                remc2 = nco_code_rem(xe, smax, ci);
+                sm->hand[q % R].remc = remc2;
+                cl_flag_set(&sm->seq_remc, q + 1);
+            }
+            nseg = __shfl_sync(0xffffffffu, nseg, 0);
+            __syncwarp();
+            {
+                const uint32_t tr = (uint32_t)(r0 + q % W);
+                const int slot = (q / W) & 1;
+                trk_push_table(sm->walk[1], nseg, cl_map(&sm->t.segs[2 * slot + 1][0], tr), lane);
+                if (lane == 0) {
+                    const uint32_t h = cl_map(&sm->slot[slot], tr);
+                    cl_st_u32(h + offsetof(trk_slot_t, ncode), (uint32_t)nseg);
+                    cl_st_u32(h + offsetof(trk_slot_t, n), (uint32_t)n);
+                    cl_st_u32(h + offsetof(trk_slot_t, stop), 0u);
+                    cl_st_u32(h + offsetof(trk_slot_t, boff), (uint32_t)boff);
+                    cl_st_u32(h + offsetof(trk_slot_t, boff) + 4, (uint32_t)(boff >> 32));
+                    cl_st_u32(h + offsetof(trk_slot_t, q), (uint32_t)q);
+                }
+                cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+            }
+            __syncwarp();                                    /* walk[1] is free again */
+            if (lane == 0) {
+                remc = remc2; buffloc += (unsigned long long)n; cnt++;
+                boff += (unsigned long long)n; if (boff >= capacity) boff -= capacity; if (boff >= capacity) boff %= capacity;
+                prev_quiet = quiet;
+            }
+        }
+        /* the teams leave: W more hand-outs that carry only the stop flag (this warp arrives for both lanes) */
+        for (int j = 0; j < W; j++) {
+            const int qq = q + j;
+            if (lane == 0 && j > 0 && qq >= 2 * W) cl_mbar_wait(&sm->done[(qq - 2 * W) % R], (uint32_t)(((qq - 2 * W) / R) & 1));
+            __syncwarp();
+            const uint32_t tr = (uint32_t)(r0 + qq % W);
+            const int slot = (qq / W) & 1;
+            if (lane == 0) cl_st_u32(cl_map(&sm->slot[slot], tr) + offsetof(trk_slot_t, stop), 1u);
+            __syncwarp();
+            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+        }
+    } else if (ctrl && wid == 0) {
+        /* ================= carrier NCO lane */
+        double carrfreq = 0.0, remp = 0.0;
+        int prev_quiet = 0;
+        for (int q = 0;; q++) {
+            int n = 0, go = 0, quiet = 0, nseg = 0;
+            double xe = 0.0;
+            if (lane == 0) {
+                cl_flag_wait_ge(&sm->seq_code, q + 1);
+                n = sm->hand[q % R].n; go = sm->hand[q % R].go; quiet = sm->hand[q % R].quiet;
+            }
+            go = __shfl_sync(0xffffffffu, go, 0);
+            if (!go) break;
+            if (lane == 0) {
+                if (q == 0 || !prev_quiet) {
+                    cl_flag_wait_ge(&sm->epi_count, q);
+                    carrfreq = st->carrfreq; remp = st->remcarr;
+                }
+                double phi, ps;
+                nco_carrier_init(carrfreq, remp, ch->ti, &phi, &ps);
+                nseg = trk_walk_call(phi, ps, n, 0.0, sm->walk[0], &xe);
+                if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
+            }
+            nseg = __shfl_sync(0xffffffffu, nseg, 0);
+            __syncwarp();
+            {
+                const uint32_t tr = (uint32_t)(r0 + q % W);
+                const int slot = (q / W) & 1;
+                trk_push_table(sm->walk[0], nseg, cl_map(&sm->t.segs[2 * slot][0], tr), lane);
+                if (lane == 0) cl_st_u32(cl_map(&sm->slot[slot], tr) + offsetof(trk_slot_t, ncarr), (uint32_t)nseg);
+                cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+            }
+            __syncwarp();
+            if (lane == 0) {
+                remp = trk_rem_call(xe);                       /* mixcarr's subtract loop, src/sdrcmn.c:665-668 */
+                sm->hand[q % R].remp = remp;
+                cl_flag_set(&sm->seq_remp, q + 1);
+                prev_quiet = quiet;
+            }
+        }
+    } else if (ctrl && wid == 2) {
+        /* ================= epilogue warp: periods in order, as their tap sums arrive */
+        int donep = 0, errw = 0;
+        for (int q = 0; q < nperiods; q++) {
+            cl_flag_wait_ge(&sm->seq_code, q + 1);
+            const trk_hand_t *hd = &sm->hand[q % R];
+            if (!hd->go) break;
+            cl_mbar_wait(&sm->done[q % R], (uint32_t)((q / R) & 1));
+            cl_flag_wait_ge(&sm->seq_remc, q + 1);
+            cl_flag_wait_ge(&sm->seq_remp, q + 1);
+            const unsigned int *res = sm->res[q % R];
+            if (lane == 0) { st->currnsamp = hd->n; if (res[2 * SDRB200_MAXTAPS]) errw = 1; }
+            __syncwarp();
+            trk_epilogue(ch, st, res, res + SDRB200_MAXTAPS, hd->remc, hd->remp, recs ? &sm->rec : nullptr, lane,
+                         (prof && chno == 0) ? prof : nullptr);
+            if (recs) {
+                const uint32_t *src = (const uint32_t *)&sm->rec;
+                uint32_t *dst = (uint32_t *)&recs[(size_t)chno * nperiods + q];
+                for (int i = lane; i < (int)(sizeof(sdrb200_trk_rec_t) / 4); i += 32) dst[i] = src[i];
+            }
+            __syncwarp();
+            if (lane == 0) cl_flag_set(&sm->epi_count, q + 1);
+            donep++;
+        }
+        __syncwarp();
+        {
+            uint32_t *dst = (uint32_t *)&states[chno];
+            const uint32_t *src = (const uint32_t *)st;
+            for (int i = lane; i < (int)(sizeof(trk_state_t) / 4); i += 32) dst[i] = src[i];
+        }
+        if (lane == 0) { nrec[chno] = donep; if (errw) atomicExch(err, 1); if (prof && chno == 0) prof[6] = donep; }
+    } else if (wid >= 3 && rank >= r0) {
+        /* ================= worker team: one whole code period per hand-out */
+        const int t = threadIdx.x - TRK_T0;
+        for (int i = 0;; i++) {
+            const int slot = i & 1;
+            cl_mbar_wait(&sm->full[slot], (uint32_t)((i >> 1) & 1));
+            const trk_slot_t *h = &sm->slot[slot];
+            if (h->stop) break;
+            const int n = h->n;
+            const int8_t *data = ifbuf + (size_t)h->boff * DTYPE;
+            if (t == 0) {
+                sm->t.icarr = sm->t.segs[2 * slot]; sm->t.icode = sm->t.segs[2 * slot + 1];
+                sm->t.carr.nseg = h->ncarr; sm->t.code.nseg = h->ncode;
+                sm->t.carry[0] = 0u; sm->t.carry[1] = 0u; sm->t.qcount = 0; sm->t.nslow[0] = 0; sm->t.nslow[1] = 0;
+            }
+            if (t < 2 * SDRB200_MAXTAPS) sm->t.sum[t] = 0u;
+            trk_bar_workers<NW>();
+            trk_mix_prefix<DTYPE, NW, TRK_T0>(&sm->t, data, n, wk);
+            trk_bar_workers<NW>();                       /* all prefix rows written */
+            trk_tap_sums<DTYPE, NW, TRK_T0>(&sm->t, wk, data, n, sm->taps, ns, smax);
+            trk_bar_workers<NW>();
+            if (t < 32) {
+                const int q = h->q;
+                const uint32_t dst = cl_map(&sm->res[q % R][0], 0);
+                for (int k = lane; k < 2 * SDRB200_MAXTAPS; k += 32) cl_st_u32(dst + 4u * (uint32_t)k, sm->t.sum[k]);
+                if (lane == 0) cl_st_u32(dst + 4u * (2 * SDRB200_MAXTAPS), (uint32_t)sm->t.err);
+                cl_mbar_arrive_remote(cl_map(&sm->done[q % R], 0));
+            }
+            trk_bar_workers<NW>();                       /* sums and header consumed before the next period resets them */
+        }
+    }
+    /* nobody leaves while a peer may still write into (or wait on) its shared memory */
+    __syncthreads();
+    cl_sync_all();
+}

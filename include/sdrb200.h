@@ -233,6 +233,13 @@ int  sdrb200_trk_enqueue(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nper
 int  sdrb200_trk_sync(sdrb200_trk_t *eng);
 int  sdrb200_trk_reset(sdrb200_trk_t *eng);     /* back to the hand-over state   */
 void *sdrb200_trk_cuda_stream(sdrb200_trk_t *eng);
+/* One thread-block cluster tracks one channel: rank 0's control warps replay the NCOs and
+ * run the loop filters (src/sdrtrk.c:31-47, src/sdrmain.c:264-312), the worker teams of
+ * the cluster correlate whole code periods (correlator(), src/sdrcmn.c:687-722).  The
+ * cluster size (1, 2, 4, 8) is chosen at the first launch so that all channels of THIS
+ * engine are co-resident; a caller that runs several engines at once can set it
+ * (0 = choose again).  ctrl_works: rank 0's worker team takes periods too.       */
+int  sdrb200_trk_set_cluster(sdrb200_trk_t *eng, int cluster_size, int ctrl_works);
 /* phase profile of channel 0 (clock cycles summed over the last run): go, NCO
  * tables, table conversion, wipe-off + prefix sums, tap sums, epilogue, periods */
 int  sdrb200_trk_profile(sdrb200_trk_t *eng, int on, long long *out7);
