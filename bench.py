@@ -424,14 +424,14 @@ def run_b200(args):
             sdr.check(lib.sdrb200_trk_profile(trk.h, 1, None), "trk_profile")
             trk.reset(); trk.enqueue(st, nper); trk.sync()
             sdr.check(lib.sdrb200_trk_profile(trk.h, 0, out), "trk_profile")
-            names = ["go", "wait_carrier_table", "convert", "mix_prefix", "tap_sums", "epilogue"]
             per = max(1, int(out[6]))
-            phases = {k: round(out[i] / per, 1) for i, k in enumerate(names)}
-            phases.update(periods=per, walk_carrier=round(out[8] / per, 1), carrier_rem=round(out[9] / per, 1),
-                          staged_periods=int(out[10]), walk_ahead_periods=int(out[11]),
-                          epilogue_nav=round(out[12] / per, 1), epilogue_loops=round(out[13] / per, 1),
-                          epilogue_obs_rec=round(out[14] / per, 1),
-                          code_walk_ahead=round(out[7] / per, 1), code_walk_call=round(out[15] / per, 1), unit="cycles per period, channel 0")
+            names = {0: "code_lane_table_and_walk", 1: "code_lane_waits_and_decisions", 2: "carrier_lane_table_and_walk",
+                     3: "carrier_lane_2pi_reduction", 4: "carrier_lane_waits", 11: "carrier_lane_push",
+                     5: "epilogue_warp_waiting_for_results", 12: "epilogue_nav", 13: "epilogue_loops", 14: "epilogue_obs_rec",
+                     7: "team0_mix_prefix", 8: "team0_boundaries_taps_report", 9: "team0_waiting_for_hand_out"}
+            phases = {v: round(out[k] / per, 1) for k, v in names.items()}
+            phases.update(periods=per, quiet_periods=int(out[10]),
+                          unit="cycles per period of channel 0 (team0_* per period of the channel, the team sees 1 in W)")
         t_trk = sum(tms) / len(tms) * 1e-3
         # end to end: IF from pinned host memory -> device ring -> tracking -> per-channel record counts
         nbytes = int(nper + 8) * NSAMP + AVAIL

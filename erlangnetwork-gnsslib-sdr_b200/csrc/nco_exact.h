@@ -648,8 +648,8 @@ NCO_HD double nco_reduce_2pi(double x)
 }
 
 /* ==== lean double-domain walker (the tracking kernel's NCO lanes) ================
- * Same sequences as nco_walk / nco_reduce_2pi, arranged so that the DEPENDENT chain per
- * binade is ~8 floating-point operations and nothing else:
+ * Same sequences as nco_walk / nco_reduce_2pi (nco_walk_l, nco_reduce_2pi_d below), arranged so
+ * that the DEPENDENT chain per binade is ~8 floating-point operations and nothing else:
  *
  *   inside binade [2^e, 2^(e+1)) every addition of `step` adds d_e = step rounded to the
  *   binade's grid (see the head of this file); d_e depends on step and e only, so a table
@@ -661,20 +661,20 @@ NCO_HD double nco_reduce_2pi(double x)
  *   leaves the binade (or reaches the wrap limit) is a REAL addition, so its rounding is
  *   the hardware's.  Values outside the table's domain (x <= 0, step <= 0, x below step's
  *   binade, subnormals) take the probing iteration of nco_walk.
- * Segments come out in double form {k0, x0, d}; nco_wseg_make turns one into the integer
- * form the correlator threads use.                                                      */
+ * Segments come out in the integer form the correlator threads use (nco_iseg_t).          */
 #define NCO_STEPTAB_N 54
 typedef struct {
-    double   d[NCO_STEPTAB_N];      /* [s]: increment in binade ed + s, s = 1..52          */
-    double   inv[NCO_STEPTAB_N];    /* [s]: (1 / d[s]) * (1 - 2^-30)                       */
-    uint64_t ties;                  /* bit s: binade ed + s rounds step on an exact tie    */
-    int32_t  ed;                    /* biased exponent of step; 0: table unusable          */
+    double   di[NCO_STEPTAB_N][2];  /* [s] = {d, inv}: increment in binade ed + s (s = 1..53; 53: |step| below
+                                     * one ulp) and (1 / d) * (1 - 2^-30); d = 0: entry unusable             */
+    uint64_t Dn[NCO_STEPTAB_N];     /* [s]: d in units of the binade's grid                                  */
+    uint64_t ties;                  /* bit s: binade ed + s rounds |step| on an exact tie                    */
+    int32_t  ed;                    /* biased exponent of step; 0: table unusable                            */
     int32_t  pad;
 } nco_steptab_t;
 
-/* entry s (1..52) of the table for `step` (> 0, normal): returns 0 if binade ed + s has no
- * normal grid representation of the increment (never for receiver frequencies)           */
-NCO_HD int nco_steptab_entry(double step, int s, double *d, double *inv, int *tie)
+/* entry s (1..53) of the table for `step` (any sign, normal): returns 0 if binade ed + s has no
+ * normal grid representation of the increment (never for receiver frequencies)              */
+NCO_HD int nco_steptab_entry(double step, int s, double *d, double *inv, int *tie, uint64_t *Dn_out)
 {
     const uint64_t bstep = nco_bits(step);
     const int ed = (int)((bstep >> 52) & 0x7FF);
@@ -685,7 +685,8 @@ NCO_HD int nco_steptab_entry(double step, int s, double *d, double *inv, int *ti
     *tie = (r == half);
     if (r == half) Dn = q + (q & 1);                    /* the even one of {q, q+1}         */
     else Dn = q + (r > half ? 1 : 0);
-    if (eg < 1 || eg > 2046 || ed + s > 2046) { *d = 0.0; *inv = 0.0; return 0; }
+    *Dn_out = Dn;
+    if (eg < 1 || eg > 2046 || ed + s > 2046 || Dn == 0) { *d = 0.0; *inv = 0.0; return 0; }
     *d = NCO_MUL((double)(int64_t)Dn, nco_from_bits((uint64_t)eg << 52));      /* exact   */
     *inv = NCO_MUL(NCO_DIV(1.0, *d), 0x1.fffffffcp-1);                          /* 1 - 2^-30 */
     return 1;
@@ -696,80 +697,195 @@ NCO_HD void nco_steptab_build(double step, nco_steptab_t *t)
     const int ed = (int)((bstep >> 52) & 0x7FF);
     int s;
     t->ties = 0; t->pad = 0;
-    t->ed = (step > 0.0 && ed > 0 && ed < 0x7FF) ? ed : 0;
-    t->d[0] = 0.0; t->inv[0] = 0.0; t->d[53] = 0.0; t->inv[53] = 0.0;
-    for (s = 1; s <= 52; s++) {
+    t->ed = (step != 0.0 && ed > 0 && ed < 0x7FF) ? ed : 0;       /* entries depend on |step| only */
+    t->di[0][0] = 0.0; t->di[0][1] = 0.0; t->Dn[0] = 0;
+    for (s = 1; s <= 53; s++) {
         int tie = 0;
-        if (!t->ed || !nco_steptab_entry(step, s, &t->d[s], &t->inv[s], &tie)) { t->d[s] = 0.0; t->inv[s] = 0.0; }
+        t->Dn[s] = 0;
+        if (!t->ed || !nco_steptab_entry(step, s, &t->di[s][0], &t->di[s][1], &tie, &t->Dn[s])) { t->di[s][0] = 0.0; t->di[s][1] = 0.0; }
         if (tie) t->ties |= 1ULL << s;
     }
 }
 
-#define NCO_DEMIT(K0, X0, DD) do { if (ns < maxseg) { nco_seg_t *sg_ = &seg[ns]; sg_->k0 = (K0); sg_->pad = 0; \
-                                    sg_->x0 = (X0); sg_->d = (DD); } ns++; } while (0)
+/* floor(v) for 0 <= v < 2^51 and v*w + c, on the fixed-latency FP64 pipe of the device */
+#ifdef __CUDA_ARCH__
+#define NCO_FLOOR51(v) (__dadd_rn(__dadd_rd((v), 4503599627370496.0), -4503599627370496.0))
+#define NCO_FMA(a, b, c) __fma_rn((a), (b), (c))
+#else
+#define NCO_FLOOR51(v) floor(v)
+#define NCO_FMA(a, b, c) ((a) * (b) + (c))          /* product and sum are exact where it is used */
+#endif
 
-/* same contract as nco_walk_i, segments in double form; tab = table of `step` */
-NCO_HD int nco_walk_d(double x, double step, int32_t count, double wrap, const nco_steptab_t *tab,
-                      nco_seg_t *seg, int maxseg, double *x_end)
+/* The walk in two stages.
+ * Stage 1, nco_walk_raw - the serial chain, kept to the bare recurrence: one RAW record per run
+ *   {bits of the run's first value, index of that value (as a double), kind}, kind 0 = a single
+ *   value, 1 = |x| growing by the table increment of its binade, 2 = shrinking by it.  It works on
+ *   the magnitude m = |x| so that one table (built for |step|) serves both signs:
+ *     growing   (x and step of one sign): values m + j*d stay on the binade's grid while < top
+ *               (top = next binade border, or the wrap limit inside its binade);
+ *     shrinking (opposite signs): values m - j*d stay on the grid while >= lo + ulp (then the
+ *               exact difference is still inside the binade);
+ *     J = floor(room * inv) with inv biased low by 2^-30: never too large, at most one too
+ *     small for runs shorter than 2^29 -> ONE upward correction, no loop;
+ *     the addition that leaves the run is a real one.  An exact tie takes one real step while
+ *     the mantissa is odd.  Everything else (|x| below the table, zero, subnormal, huge) is
+ *     stepped one real addition at a time.  The run that reaches `count` is cut afterwards, so
+ *     the loop carries no clamp.
+ * Stage 2, nco_raw_to_iseg - one record -> the integer segment the correlator threads use;
+ *   independent per record (the tracking kernel converts with one lane per record).          */
+typedef struct {
+    uint64_t bx;            /* bits of the first value of the run */
+    double   kf;            /* its index                          */
+    int32_t  kind, pad;
+} nco_raw_t;
+
+#define NCO_RAW_EMIT(BX, KF, KIND) do { if (ns < maxseg) { raw[ns].bx = (BX); raw[ns].kf = (KF); raw[ns].kind = (KIND); } ns++; } while (0)
+
+/* The common case - x > 0 growing by step > 0 (the carrier at IF, every code NCO) - as a tight
+ * loop: straight-line arithmetic, three branches per binade.  Leaves at the first value that
+ * needs anything else (|x| below the table, a tie with an odd mantissa, ...), or when the
+ * walk is complete (returns 1; *px is then the accumulator after the last addition).  `lim`
+ * is a literal at both call sites.                                                         */
+NCO_HD int nco_walk_tight(double *px, double *pKf, int32_t *pns, const double step, const double Cf, const double wrap,
+                          const int lim, const int ed, const int ewrap, const uint64_t ties,
+                          const nco_steptab_t *tab, nco_raw_t *raw, const int maxseg)
 {
-    int32_t k = 0, ns = 0;
-    const int lim = (wrap > 0.0) ? 1 : 0;
-    const int ed = tab->ed;
-    const int ewrap = (int)((nco_bits(wrap) >> 52) & 0x7FF);
-    double inv_generic = 0.0;
-    while (k < count) {
+    double x = *px, Kf = *pKf;
+    int32_t ns = *pns;
+    int ended = 0;
+    for (;;) {
+        const uint64_t bx = nco_bits(x);
+        const int ex = (int)(bx >> 52);                      /* x > 0 here */
+        const int s = ex - ed;
+        double d, inv, top, Jf, y, y2, Kn;
+        if ((unsigned int)(s - 1) >= 53u || (lim && ex > ewrap)) break;
+        d = tab->di[s][0]; inv = tab->di[s][1];
+        if (d == 0.0 || (((ties >> s) & bx) & 1ULL)) break;
+        top = (lim && ex == ewrap) ? wrap : nco_from_bits((uint64_t)(ex + 1) << 52);
+        Jf = NCO_FLOOR51(NCO_MUL(NCO_ADD(top, -x), inv));
+        y = NCO_FMA(Jf, d, x);
+        y2 = NCO_ADD(y, d);
+        Kn = NCO_ADD(Kf, NCO_ADD(Jf, 1.0));
+        if (y2 < top) { y = y2; Kn = NCO_ADD(Kn, 1.0); }
+        if (ns < maxseg) { raw[ns].bx = bx; raw[ns].kf = Kf; raw[ns].kind = 1; }
+        ns++;
+        if (Kn >= Cf) {                                      /* the walk ends inside (or with) this run */
+            y = NCO_FMA(NCO_ADD(NCO_ADD(Cf, -Kf), -1.0), d, x);
+            x = NCO_ADD(y, step);
+            Kf = Cf; ended = 1;
+            break;
+        }
+        Kf = Kn;
+        x = NCO_ADD(y, step);                                /* leaves the run: a real addition */
         if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
+        if (!(x > 0.0)) break;
+    }
+    *px = x; *pKf = Kf; *pns = ns;
+    return ended;
+}
+
+NCO_HD int nco_walk_raw(double x, double step, int32_t count, double wrap, const nco_steptab_t *tab,
+                        nco_raw_t *raw, int maxseg, double *x_end)
+{
+    int32_t ns = 0;
+    const int lim = (wrap > 0.0) ? 1 : 0;
+    const int ed = tab->ed;                                  /* table of |step| */
+    const int ewrap = (int)((nco_bits(wrap) >> 52) & 0x7FF);
+    const uint64_t ties = tab->ties;
+    const uint64_t sstep = nco_bits(step) >> 63;
+    const double Cf = (double)count;
+    double Kf = 0.0;
+    while (Kf < Cf) {
+        if (lim && x >= wrap) x = NCO_ADD(x, -wrap);
+        if (ed && step > 0.0 && x > 0.0) {
+            const int ended = lim ? nco_walk_tight(&x, &Kf, &ns, step, Cf, wrap, 1, ed, ewrap, ties, tab, raw, maxseg)
+                                  : nco_walk_tight(&x, &Kf, &ns, step, Cf, wrap, 0, ed, ewrap, ties, tab, raw, maxseg);
+            if (ended) break;
+            /* x is the next value to use (wrap already applied): one general iteration handles it */
+        }
         {
             const uint64_t bx = nco_bits(x);
-            const int ex = (int)(bx >> 52);                 /* sign set -> out of range below */
+            const uint64_t bm = bx & 0x7FFFFFFFFFFFFFFFULL;
+            const int ex = (int)(bm >> 52);
             const int s = ex - ed;
-            if (ed && s >= 1 && s <= 52 && tab->d[s] != 0.0 && !(lim && ex > ewrap)) {
-                const double d = tab->d[s];
-                const double hi = nco_from_bits((uint64_t)(ex + 1) << 52);
-                const double top = (lim && ex == ewrap) ? wrap : hi;
-                double room, est, y, y2;
-                int32_t J, R;
-                if ((tab->ties >> s) & 1ULL) {
-                    /* parity step: one real addition, then the mantissa is even */
-                    const double x1 = NCO_ADD(x, step);
-                    if (k + 1 >= count || !(x1 < top)) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; continue; }
-                    if (nco_bits(x) & 1ULL) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; }
+            const uint64_t neg = bx >> 63;
+            if (ed && (unsigned int)(s - 1) < 53u && !(lim && ex > ewrap)) {
+                const double d = tab->di[s][0], inv = tab->di[s][1];
+                const double m = nco_from_bits(bm);
+                const int growing = (neg == sstep);
+                if (d != 0.0 && !(((ties >> s) & 1ULL) && (bm & 1ULL))) {
+                    double Jf, y, y2, Kn;
+                    int up;
+                    if (growing) {
+                        const double top = (lim && ex == ewrap) ? wrap : nco_from_bits((uint64_t)(ex + 1) << 52);
+                        Jf = NCO_FLOOR51(NCO_MUL(NCO_ADD(top, -m), inv));
+                        y = NCO_FMA(Jf, d, m);
+                        y2 = NCO_ADD(y, d);
+                        up = (y2 < top);
+                    } else {
+                        const double lo1 = nco_from_bits(((uint64_t)ex << 52) | 1ULL);
+                        if (!(m >= lo1)) goto single;        /* on the border: the real subtraction decides */
+                        Jf = NCO_FLOOR51(NCO_MUL(NCO_ADD(m, -lo1), inv));
+                        y = NCO_FMA(Jf, -d, m);
+                        y2 = NCO_ADD(y, -d);
+                        up = (y2 >= lo1);
+                    }
+                    if (up) { y = y2; Jf = NCO_ADD(Jf, 1.0); }
+                    NCO_RAW_EMIT(bx, Kf, growing ? 1 : 2);
+                    Kn = NCO_ADD(Kf, NCO_ADD(Jf, 1.0));
+                    if (Kn > Cf) {                           /* the walk ends inside this run */
+                        const double Jc = NCO_ADD(NCO_ADD(Cf, -Kf), -1.0);
+                        y = NCO_FMA(Jc, growing ? d : -d, m);
+                        Kn = Cf;
+                    }
+                    Kf = Kn;
+                    x = NCO_ADD(neg ? -y : y, step);         /* leaves the run (or ends the walk): real */
+                    continue;
                 }
-                R = count - k;                              /* values still to describe (>= 1) */
-                room = NCO_ADD(top, -x);                    /* exact: both on the binade's grid */
-                est = NCO_MUL(room, tab->inv[s]);
-                J = (est >= (double)(R - 1)) ? R - 1 : (int32_t)est;
-                y = NCO_ADD(x, NCO_MUL((double)J, d));      /* exact */
-                while (J > 0 && !(y < top)) { J--; y = NCO_ADD(y, -d); }
-                while (J < R - 1) { y2 = NCO_ADD(y, d); if (!(y2 < top)) break; y = y2; J++; }
-                NCO_DEMIT(k, x, d);
-                k += J + 1;
-                x = NCO_ADD(y, step);                       /* leaves the run (or ends the walk): real */
-                continue;
             }
         }
-        /* probing iteration (nco_walk) */
+single:
         {
-            double x1, x2, d;
-            int32_t J;
-            if (inv_generic == 0.0) inv_generic = nco_rcp_est(step);
-            x1 = NCO_ADD(x, step);
-            if (x1 == x) { NCO_DEMIT(k, x, 0.0); k = count; break; }
-            if (k + 1 >= count || (lim && x1 >= wrap) || !nco_same_binade(x, x1)) { NCO_DEMIT(k, x, 0.0); k += 1; x = x1; continue; }
-            x2 = NCO_ADD(x1, step);
-            if (k + 2 >= count || (lim && x2 >= wrap) || !nco_same_binade(x1, x2)) { NCO_DEMIT(k, x, NCO_ADD(x1, -x)); k += 2; x = x2; continue; }
-            d = NCO_ADD(x2, -x1);
-            J = nco_jump(x1, d, inv_generic, lim, wrap, count - 2 - k, &x2);
-            NCO_DEMIT(k, x, 0.0);
-            NCO_DEMIT(k + 1, x1, d);
-            x = NCO_ADD(x2, step);
-            k += 2 + J;
+            const double x1 = NCO_ADD(x, step);
+            NCO_RAW_EMIT(nco_bits(x), Kf, 0);
+            if (x1 == x) { Kf = Cf; break; }                /* zero or sub-ulp step: never moves again */
+            Kf = NCO_ADD(Kf, 1.0);
+            x = x1;
         }
     }
     *x_end = x;
     return (ns > maxseg) ? -1 : ns;
 }
-#undef NCO_DEMIT
+#undef NCO_RAW_EMIT
+
+/* returns 0, or 1 if a value is too large to truncate (|value| >= 2^53) */
+NCO_HD int nco_raw_to_iseg(const nco_raw_t *r, const nco_steptab_t *tab, nco_iseg_t *o)
+{
+    const uint64_t bm = r->bx & 0x7FFFFFFFFFFFFFFFULL;
+    const int ex = (int)(bm >> 52);
+    if (r->kind == 0) { nco_iseg_set(o, (int32_t)r->kf, r->bx, 0); return o->shift < 0; }
+    {
+        const int sh = 1075 - ex;                            /* 52 - (ex - 1023) */
+        const int64_t Dn = (int64_t)tab->Dn[ex - tab->ed];
+        o->k0 = (int32_t)r->kf; o->pad = 0; o->neg = (int32_t)(r->bx >> 63); o->X0 = NCO_MANT(bm);
+        o->D = (r->kind == 1) ? Dn : -Dn;
+        o->shift = sh > 64 ? 64 : sh;
+        if (sh < 0) { o->shift = -1; return 1; }
+    }
+    return 0;
+}
+
+/* both stages in sequence (contract of nco_walk_i): host tests, device self-test */
+NCO_HD int nco_walk_l(double x, double step, int32_t count, double wrap, const nco_steptab_t *tab,
+                      nco_iseg_t *seg, int maxseg, double *x_end)
+{
+    nco_raw_t raw[NCO_MAXSEG];
+    int i, bad = 0;
+    const int ns = nco_walk_raw(x, step, count, wrap, tab, raw, maxseg < NCO_MAXSEG ? maxseg : NCO_MAXSEG, x_end);
+    if (ns < 0) return -1;
+    for (i = 0; i < ns; i++) bad |= nco_raw_to_iseg(&raw[i], tab, &seg[i]);
+    return bad ? -2 : ns;
+}
 
 /* 2*pi per binade [2^(2+s), 2^(3+s)): rounded to the binade's grid (the even neighbour for the
  * tie binade s = 4) and its reciprocal biased low by 2^-30; tests/test_nco_exact.py recomputes */
@@ -808,7 +924,7 @@ NCO_HD double nco_reduce_2pi_d(double x)
     while (x > P) {
         const uint64_t bx = nco_bits(x);
         const int s = (int)(bx >> 52) - (1023 + 2);
-        if ((unsigned int)(s - 1) <= 30u) {
+        if ((unsigned int)(s - 1) <= 26u) {                 /* x < 2^30: runs shorter than 2^29 */
 #ifdef __CUDA_ARCH__
             const double Pd = nco_r2pi_Pd_dev[s], inv = nco_r2pi_inv_dev[s];
 #else
@@ -816,20 +932,19 @@ NCO_HD double nco_reduce_2pi_d(double x)
 #endif
             const double lo = nco_from_bits(bx & 0xFFF0000000000000ULL);
             const double lo1 = nco_from_bits((bx & 0xFFF0000000000000ULL) | 1ULL);    /* lo + ulp */
-            double room, est, y, y2, J;
+            double y, y2, J;
             if ((NCO_R2PI_TIES >> s) & 1u) {
                 const double x1 = NCO_ADD(x, -P);
                 if (!(x1 >= lo)) { x = x1; continue; }
                 x = x1;                                     /* even mantissa from here on */
             }
             if (x >= lo1) {
-                room = NCO_ADD(x, -lo1);                    /* exact */
-                est = NCO_MUL(room, inv);
-                J = floor(est);
-                y = NCO_ADD(x, -NCO_MUL(J, Pd));            /* exact */
-                while (!(y >= lo1)) y = NCO_ADD(y, Pd);
-                for (;;) { y2 = NCO_ADD(y, -Pd); if (!(y2 >= lo1)) break; y = y2; }
-                x = y;
+                /* inv is biased low by 2^-30: J is never too large and (runs < 2^29) at most one
+                 * too small - as in nco_walk_l                                                */
+                J = NCO_FLOOR51(NCO_MUL(NCO_ADD(x, -lo1), inv));
+                y = NCO_FMA(J, -Pd, x);                     /* exact */
+                y2 = NCO_ADD(y, -Pd);
+                x = (y2 >= lo1) ? y2 : y;
             }
             x = NCO_ADD(x, -P);                             /* may leave the binade: real */
             continue;
@@ -837,53 +952,6 @@ NCO_HD double nco_reduce_2pi_d(double x)
         x = NCO_ADD(x, -P);
     }
     return x;
-}
-
-/* ---- integer form of a segment for the correlator threads ------------------------
- * (int)value mod 2^B for B = 5 (carrier table index) or 10 (chip index < 1024) sits in
- * the TOP B bits of a 64-bit accumulator that advances by one wrapping addition per
- * sample:  acc_j = M + j*D (mod 2^64),  t_j = acc_j >> (64 - B)  is |value_j| truncated,
- * mod 2^B; negative values (neg) index as (-t) & (2^B - 1).                            */
-typedef struct {
-    int32_t  k0;
-    int32_t  neg;
-    uint64_t M;
-    uint64_t D;
-} nco_wseg_t;
-
-NCO_HD void nco_wseg_make(const nco_seg_t *sg, int B, nco_wseg_t *o, int *range_bad)
-{
-    const uint64_t bx = nco_bits(sg->x0), bd = nco_bits(sg->d);
-    const int ex = (int)((bx >> 52) & 0x7FF), edd = (int)((bd >> 52) & 0x7FF);
-    o->k0 = sg->k0; o->neg = (int32_t)(bx >> 63); o->M = 0; o->D = 0;
-    if (ex < 1023) return;                               /* |value| < 1 throughout: (int) gives 0 */
-    {
-        const int sh = 52 - (ex - 1023);                 /* value = mant >> sh                    */
-        const int L = 64 - B - sh;                       /* left shift that puts bit sh at 64 - B */
-        uint64_t X0 = NCO_MANT(bx), mag = 0;
-        if (sh < 0) { if (range_bad) *range_bad = 1; return; }      /* |value| >= 2^53 */
-        if (edd != 0) {
-            const uint64_t md = NCO_MANT(bd);
-            const int dsh = ex - edd;
-            mag = (dsh < 0) ? (md << 1) : (dsh > 63 ? 0 : (md >> dsh));
-        }
-        if (((bx >> 63) != (bd >> 63))) mag = (uint64_t)(-(int64_t)mag);
-        if (L >= 0) { o->M = (L > 63) ? 0 : (X0 << L); o->D = (L > 63) ? 0 : (mag << L); }
-        else {
-            /* sh > 64 - B cannot happen for ex >= 1023 (sh <= 52) */
-            o->M = X0 >> (-L); o->D = (uint64_t)((int64_t)mag >> (-L));
-        }
-    }
-}
-/* |(int)value| mod 2^B at index k, and the signed index mod 2^B */
-NCO_HD uint32_t nco_wseg_mag(const nco_wseg_t *w, int32_t k, int B)
-{
-    return (uint32_t)((w->M + (uint64_t)(int64_t)(k - w->k0) * w->D) >> (64 - B));
-}
-NCO_HD uint32_t nco_wseg_index(const nco_wseg_t *w, int32_t k, int B)
-{
-    const uint32_t t = nco_wseg_mag(w, k, B);
-    return (w->neg ? (0u - t) : t) & ((1u << B) - 1u);
 }
 
 /* ---- the reference's scalar prologue / epilogue arithmetic, step for step ---- */
@@ -897,7 +965,7 @@ NCO_HD void nco_carrier_init(double freq, double phi0, double ti, double *phi, d
 /* mixcarr: prem = phi*DPI/CDIV ; while(prem>DPI) prem-=DPI  src/sdrcmn.c:665-668 */
 NCO_HD double nco_carrier_rem(double phi_end)
 {
-    return nco_reduce_2pi_d(NCO_DIV(NCO_MUL(phi_end, NCO_TWO_PI), 32.0));
+    return nco_reduce_2pi_d(NCO_MUL(NCO_MUL(phi_end, NCO_TWO_PI), 0.03125));   /* /32: an exact scaling */
 }
 /* rescode: coff-=smax*ci ; coff-=floor(coff/len)*len        src/sdrcmn.c:611-612 */
 NCO_HD double nco_code_init(double coff, int smax, double ci, int len)

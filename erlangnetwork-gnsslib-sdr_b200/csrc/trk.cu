@@ -674,9 +674,11 @@ __global__ void k_nco_selftest(const double *x, const double *step, const int *c
                                nco_iseg_t *segs, int *ns, double *xe)
 {
     const int c = blockIdx.x;
+    __shared__ nco_steptab_t tab;
     double e;
+    trk_steptab_warp(&tab, step[c], threadIdx.x);          /* launched with one warp */
     if (threadIdx.x != 0) return;
-    const int r = trk_walk_call(x[c], step[c], count[c], wrap[c], segs + (size_t)c * TRK_MAXSEG, &e);
+    const int r = nco_walk_l(x[c], step[c], count[c], wrap[c], &tab, segs + (size_t)c * TRK_MAXSEG, TRK_MAXSEG, &e);
     ns[c] = r; xe[c] = e;
 }
 

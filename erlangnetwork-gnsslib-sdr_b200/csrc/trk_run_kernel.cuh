@@ -2,12 +2,15 @@
  * channel (included by trk.cu after the epilogue functions).
  *
  * Every CTA has the same warp layout:
- *   warp 0   carrier NCO lane   (control; active in cluster rank 0 only)
+ *   warp 0   carrier NCO lane   (control; active in cluster rank 0 only): the serial chain only
  *   warp 1   code NCO lane      (control; rank 0 only)
  *   warp 2   epilogue warp      (control; rank 0 only): cumsumcorr, bit/frame sync, pll/dll,
  *            observables, record - everything around correlator() in sdrtracking() and the
  *            sdrthread loop body (src/sdrtrk.c:31-47, src/sdrmain.c:264-312)
- *   warps 3.. worker team: correlator() of one whole code period (src/sdrcmn.c:687-722)
+ *   warp 3/4 carrier / code table pushers (control; rank 0 only): turn the lanes' raw run
+ *            records into integer segments, one lane per record, and write them into the
+ *            worker team's slot
+ *   warps 5.. worker team: correlator() of one whole code period (src/sdrcmn.c:687-722)
  * Code period q of the channel is correlated by the worker team of cluster rank
  * r0 + q % W (W teams; r0 = 1 when rank 0 keeps its team idle so that its NCO lanes have the
  * SM to themselves, else 0).  Each team owns two table slots, so period q may be handed out
@@ -19,7 +22,7 @@
  * (src/sdrnav.c:241-262, src/sdrmain.c:271-280), so in between the NCO lanes run ahead of
  * the correlators and consecutive periods are correlated concurrently on different SMs.
  */
-#define TRK_T0      96                       /* first worker thread                         */
+#define TRK_T0      160                      /* first worker thread                         */
 #define TRK_RING    16                       /* periods in flight: result / hand-over ring   */
 
 /* header of a table slot in a worker CTA, written remotely by the control warps */
@@ -53,7 +56,11 @@ struct trk_cl_smem_t {
     volatile int seq_remp;                   /* ... whose remp is in hand[] (carrier lane)      */
     volatile int epi_count;                  /* periods the epilogue has finished               */
     int32_t pad0;
-    nco_iseg_t walk[2][TRK_MAXSEG];          /* the lanes walk here, then copy out               */
+    nco_raw_t raw[2][2][TRK_MAXSEG];         /* [lane][period parity]: run records of the walks  */
+    struct { int32_t ns, n, q, pad; unsigned long long boff; } rhdr[2][2];
+    volatile int raw_seq[2];                 /* periods whose raw table the lane has finished    */
+    volatile int pushed[2];                  /* periods the pusher has written to their team     */
+    nco_steptab_t tab[2];                    /* per-binade increments of the current carrier / code step */
     trk_state_t st;
     sdrb200_trk_rec_t rec;
     trk_chan_dev_t chc;                      /* the channel's constants (code excluded: t.codetab) */
@@ -72,11 +79,45 @@ __device__ __forceinline__ int trk_quiet_forecast(unsigned long long cnt, int sy
     return (nc % loopms != 0) ? 1 : 0;
 }
 
-/* copy nseg segments from the lane's walk buffer to a table of the team's slot (all 32 lanes) */
-__device__ __forceinline__ void trk_push_table(const nco_iseg_t *src, int nseg, uint32_t dst_cluster_addr, int lane)
+/* per-binade table of `step` (nco_exact.h, nco_walk_t), built by one warp: lane l fills the
+ * binades l+1 and l+33 (1..53); done only when the loop filters have changed the frequency          */
+__device__ __noinline__ void trk_steptab_warp(nco_steptab_t *t, double step, int lane)
 {
-    const uint4 *s4 = (const uint4 *)src;
-    for (int i = lane; i < nseg * 2; i += 32) cl_st_v4(dst_cluster_addr + 16u * (uint32_t)i, s4[i]);
+    const uint64_t b = nco_bits(step);
+    const int ed = (int)((b >> 52) & 0x7FF);
+    const bool ok = step != 0.0 && ed > 0 && ed < 0x7FF;      /* entries depend on |step| only */
+    unsigned long long ties = 0ull;
+    for (int s = lane + 1; s <= 53; s += 32) {
+        double d = 0.0, inv = 0.0; int tie = 0; uint64_t Dn = 0;
+        if (ok && !nco_steptab_entry(step, s, &d, &inv, &tie, &Dn)) { d = 0.0; inv = 0.0; }
+        t->di[s][0] = d; t->di[s][1] = inv; t->Dn[s] = Dn;
+        if (tie) ties |= 1ull << s;
+    }
+    for (int o = 16; o > 0; o >>= 1) ties |= __shfl_xor_sync(0xffffffffu, ties, o);
+    if (lane == 0) {
+        t->ties = ties; t->ed = ok ? ed : 0; t->pad = 0;
+        t->di[0][0] = 0.0; t->di[0][1] = 0.0; t->Dn[0] = 0;
+    }
+    __syncwarp();
+}
+__device__ __noinline__ int trk_walk_raw(double x, double step, int count, double wrap, const nco_steptab_t *tab,
+                                         nco_raw_t *raw, double *x_end)
+{
+    return nco_walk_raw(x, step, count, wrap, tab, raw, TRK_MAXSEG, x_end);
+}
+
+/* pusher warp: records of period q -> segments in the team's slot; returns 1 on a range error */
+__device__ __forceinline__ int trk_push_raw(const nco_raw_t *raw, int ns, const nco_steptab_t *tab, uint32_t dst_cluster_addr, int lane)
+{
+    int bad = 0;
+    for (int i = lane; i < ns; i += 32) {
+        nco_iseg_t o;
+        bad |= nco_raw_to_iseg(&raw[i], tab, &o);
+        const uint32_t a = dst_cluster_addr + 32u * (uint32_t)i;
+        cl_st_v4(a, make_uint4((uint32_t)o.k0, (uint32_t)o.shift, (uint32_t)o.X0, (uint32_t)(o.X0 >> 32)));
+        cl_st_v4(a + 16u, make_uint4((uint32_t)(uint64_t)o.D, (uint32_t)((uint64_t)o.D >> 32), (uint32_t)o.neg, 0u));
+    }
+    return bad;
 }
 
 template <int DTYPE, int NT>
@@ -98,6 +139,11 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool ctrl = (rank == 0);
     trk_state_t *st = &sm->st;
+    /* optional cycle profile of channel 0 (sdrb200_trk_profile): slot i accumulates the cycles since the last stamp */
+    const bool pf = (prof != nullptr) && chno == 0 && lane == 0;
+    long long pt0 = 0;
+#define TRK_PF(i) do { if (pf) { const long long t1_ = trk_clock(); atomicAdd((unsigned long long *)&prof[i], (unsigned long long)(t1_ - pt0)); pt0 = t1_; } } while (0)
+#define TRK_PF0() do { if (pf) pt0 = trk_clock(); } while (0)
 
     /* ---- set-up: every CTA holds the code and taps; rank 0 also the channel state */
     for (int i = threadIdx.x; i < chg->clen; i += NT) sm->t.codetab[i] = chg->code[i];
@@ -116,6 +162,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
         cl_mbar_init(&sm->full[0], 64); cl_mbar_init(&sm->full[1], 64);
         for (int i = 0; i < R; i++) cl_mbar_init(&sm->done[i], 32);
         sm->seq_code = 0; sm->seq_remc = 0; sm->seq_remp = 0; sm->epi_count = 0;
+        sm->raw_seq[0] = 0; sm->raw_seq[1] = 0; sm->pushed[0] = 0; sm->pushed[1] = 0;
         cl_fence_mbar_init();
     }
     __syncthreads();
@@ -129,8 +176,10 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
         double codefreq = 0.0, remc = 0.0;
         unsigned long long buffloc = 0ull, boff = 0ull, cnt = 0ull;
         int navcnt = 0, synci = 0, flagsync = 0, prev_quiet = 0, q = 0;
+        double tab_step = -1.0;                               /* step the table sm->tab[1] was built for */
         for (;; q++) {
             int n = 0, go = 0, quiet = 0, nseg = 0;
+            TRK_PF0();
             if (lane == 0) {
                 if (q < nperiods) {
                     if (q == 0 || !prev_quiet) {
@@ -148,45 +197,46 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 if (q >= R) cl_flag_wait_ge(&sm->epi_count, q - R + 1);
                 sm->hand[q % R].n = n; sm->hand[q % R].go = go; sm->hand[q % R].quiet = quiet;
                 cl_flag_set(&sm->seq_code, q + 1);
+                if (pf && quiet) prof[10] += 1;
             }
+            TRK_PF(1);                                       /* code lane: waits + period decisions */
             go = __shfl_sync(0xffffffffu, go, 0);
             if (!go) break;
             n = __shfl_sync(0xffffffffu, n, 0);
             double remc2 = 0.0;
+            {
+                const double ci_all = __shfl_sync(0xffffffffu, __dmul_rn(ch->ti, codefreq), 0);
+                if (ci_all != tab_step) {                     /* the pusher has finished with the old table: period q-1 is done */
+                    trk_steptab_warp(&sm->tab[1], ci_all, lane); tab_step = ci_all;
+                }
+            }
             if (lane == 0) {
                 const double ci = __dmul_rn(ch->ti, codefreq);                          /* ti*crate, sdrcmn.c:709 */
                 const double c0 = nco_code_init(remc, smax, ci, ch->clen);
                 double xe;
-                nseg = trk_walk_call(c0, ci, n + 2 * smax, (double)ch->clen, sm->walk[1], &xe);
+                if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);                     /* raw buffer q & 1 is free */
+                nseg = trk_walk_raw(c0, ci, n + 2 * smax, (double)ch->clen, &sm->tab[1], sm->raw[1][q & 1], &xe);
                 if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
                 remc2 = nco_code_rem(xe, smax, ci);
                 sm->hand[q % R].remc = remc2;
                 cl_flag_set(&sm->seq_remc, q + 1);
-            }
-            nseg = __shfl_sync(0xffffffffu, nseg, 0);
-            __syncwarp();
-            {
-                const uint32_t tr = (uint32_t)(r0 + q % W);
-                const int slot = (q / W) & 1;
-                trk_push_table(sm->walk[1], nseg, cl_map(&sm->t.segs[2 * slot + 1][0], tr), lane);
-                if (lane == 0) {
-                    const uint32_t h = cl_map(&sm->slot[slot], tr);
-                    cl_st_u32(h + offsetof(trk_slot_t, ncode), (uint32_t)nseg);
-                    cl_st_u32(h + offsetof(trk_slot_t, n), (uint32_t)n);
-                    cl_st_u32(h + offsetof(trk_slot_t, stop), 0u);
-                    cl_st_u32(h + offsetof(trk_slot_t, boff), (uint32_t)boff);
-                    cl_st_u32(h + offsetof(trk_slot_t, boff) + 4, (uint32_t)(boff >> 32));
-                    cl_st_u32(h + offsetof(trk_slot_t, q), (uint32_t)q);
-                }
-                cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
-            }
-            __syncwarp();                                    /* walk[1] is free again */
-            if (lane == 0) {
+                sm->rhdr[1][q & 1].ns = nseg; sm->rhdr[1][q & 1].n = n; sm->rhdr[1][q & 1].q = q; sm->rhdr[1][q & 1].boff = boff;
+                cl_flag_set(&sm->raw_seq[1], q + 1);
                 remc = remc2; buffloc += (unsigned long long)n; cnt++;
                 boff += (unsigned long long)n; if (boff >= capacity) boff -= capacity; if (boff >= capacity) boff %= capacity;
                 prev_quiet = quiet;
             }
+            __syncwarp();
+            TRK_PF(0);                                       /* code lane: table + walk */
         }
+        /* no more periods: the pusher leaves after the last real one */
+        if (lane == 0) {
+            if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);
+            sm->rhdr[1][q & 1].ns = -1;
+            cl_flag_set(&sm->raw_seq[1], q + 1);
+            cl_flag_wait_ge(&sm->pushed[1], q);              /* every real period is in its slot */
+        }
+        __syncwarp();
         /* the teams leave: W more hand-outs that carry only the stop flag (this warp arrives for both lanes) */
         for (int j = 0; j < W; j++) {
             const int qq = q + j;
@@ -201,48 +251,89 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
         }
     } else if (ctrl && wid == 0) {
         /* ================= carrier NCO lane */
-        double carrfreq = 0.0, remp = 0.0;
-        int prev_quiet = 0;
+        double carrfreq = 0.0, remp = 0.0, tab_step = -1.0;
+        int prev_quiet = 0, qlast = 0;
         for (int q = 0;; q++) {
             int n = 0, go = 0, quiet = 0, nseg = 0;
             double xe = 0.0;
+            TRK_PF0();
             if (lane == 0) {
                 cl_flag_wait_ge(&sm->seq_code, q + 1);
                 n = sm->hand[q % R].n; go = sm->hand[q % R].go; quiet = sm->hand[q % R].quiet;
             }
             go = __shfl_sync(0xffffffffu, go, 0);
             if (!go) break;
-            if (lane == 0) {
-                if (q == 0 || !prev_quiet) {
-                    cl_flag_wait_ge(&sm->epi_count, q);
-                    carrfreq = st->carrfreq; remp = st->remcarr;
-                }
+            if (lane == 0 && (q == 0 || !prev_quiet)) {
+                cl_flag_wait_ge(&sm->epi_count, q);
+                carrfreq = st->carrfreq; remp = st->remcarr;
+            }
+            TRK_PF(4);                                       /* carrier lane: waits */
+            {
                 double phi, ps;
                 nco_carrier_init(carrfreq, remp, ch->ti, &phi, &ps);
-                nseg = trk_walk_call(phi, ps, n, 0.0, sm->walk[0], &xe);
+                ps = __shfl_sync(0xffffffffu, ps, 0);
+                if (ps != tab_step) { trk_steptab_warp(&sm->tab[0], ps, lane); tab_step = ps; }
+            }
+            if (lane == 0) {
+                double phi, ps;
+                nco_carrier_init(carrfreq, remp, ch->ti, &phi, &ps);
+                if (q >= 2) cl_flag_wait_ge(&sm->pushed[0], q - 1);                     /* raw buffer q & 1 is free */
+                nseg = trk_walk_raw(phi, ps, n, 0.0, &sm->tab[0], sm->raw[0][q & 1], &xe);
                 if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
+                sm->rhdr[0][q & 1].ns = nseg; sm->rhdr[0][q & 1].q = q;
+                cl_flag_set(&sm->raw_seq[0], q + 1);
             }
-            nseg = __shfl_sync(0xffffffffu, nseg, 0);
-            __syncwarp();
-            {
-                const uint32_t tr = (uint32_t)(r0 + q % W);
-                const int slot = (q / W) & 1;
-                trk_push_table(sm->walk[0], nseg, cl_map(&sm->t.segs[2 * slot][0], tr), lane);
-                if (lane == 0) cl_st_u32(cl_map(&sm->slot[slot], tr) + offsetof(trk_slot_t, ncarr), (uint32_t)nseg);
-                cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
-            }
-            __syncwarp();
+            TRK_PF(2);                                       /* carrier lane: table + walk */
             if (lane == 0) {
                 remp = trk_rem_call(xe);                       /* mixcarr's subtract loop, src/sdrcmn.c:665-668 */
                 sm->hand[q % R].remp = remp;
                 cl_flag_set(&sm->seq_remp, q + 1);
                 prev_quiet = quiet;
             }
+            __syncwarp();
+            TRK_PF(3);                                       /* carrier lane: 2*pi reduction */
+            qlast = q + 1;
+        }
+        if (lane == 0) {                                     /* the pusher leaves after the last real period */
+            if (qlast >= 2) cl_flag_wait_ge(&sm->pushed[0], qlast - 1);
+            sm->rhdr[0][qlast & 1].ns = -1;
+            cl_flag_set(&sm->raw_seq[0], qlast + 1);
+        }
+        __syncwarp();
+    } else if (ctrl && (wid == 3 || wid == 4)) {
+        /* ================= table pushers: warp 3 carrier, warp 4 code */
+        const int k = wid - 3;
+        for (int q = 0;; q++) {
+            TRK_PF0();
+            cl_flag_wait_ge(&sm->raw_seq[k], q + 1);
+            const int nsg = sm->rhdr[k][q & 1].ns;
+            if (nsg < 0) break;
+            const uint32_t tr = (uint32_t)(r0 + q % W);
+            const int slot = (q / W) & 1;
+            if (trk_push_raw(sm->raw[k][q & 1], nsg, &sm->tab[k], cl_map(&sm->t.segs[2 * slot + k][0], tr), lane)) atomicExch(err, 1);
+            if (lane == 0) {
+                const uint32_t h = cl_map(&sm->slot[slot], tr);
+                if (k == 0) cl_st_u32(h + offsetof(trk_slot_t, ncarr), (uint32_t)nsg);
+                else {
+                    const unsigned long long bo = sm->rhdr[1][q & 1].boff;
+                    cl_st_u32(h + offsetof(trk_slot_t, ncode), (uint32_t)nsg);
+                    cl_st_u32(h + offsetof(trk_slot_t, n), (uint32_t)sm->rhdr[1][q & 1].n);
+                    cl_st_u32(h + offsetof(trk_slot_t, stop), 0u);
+                    cl_st_u32(h + offsetof(trk_slot_t, boff), (uint32_t)bo);
+                    cl_st_u32(h + offsetof(trk_slot_t, boff) + 4, (uint32_t)(bo >> 32));
+                    cl_st_u32(h + offsetof(trk_slot_t, q), (uint32_t)q);
+                }
+            }
+            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+            __syncwarp();
+            if (lane == 0) cl_flag_set(&sm->pushed[k], q + 1);
+            TRK_PF(11);                                      /* pushers (both add to one slot) */
         }
     } else if (ctrl && wid == 2) {
         /* ================= epilogue warp: periods in order, as their tap sums arrive */
         int donep = 0, errw = 0;
         for (int q = 0; q < nperiods; q++) {
+            TRK_PF0();
             cl_flag_wait_ge(&sm->seq_code, q + 1);
             const trk_hand_t *hd = &sm->hand[q % R];
             if (!hd->go) break;
@@ -250,6 +341,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             cl_flag_wait_ge(&sm->seq_remc, q + 1);
             cl_flag_wait_ge(&sm->seq_remp, q + 1);
             const unsigned int *res = sm->res[q % R];
+            TRK_PF(5);                                       /* epilogue warp: waiting for the period's results */
             if (lane == 0) { st->currnsamp = hd->n; if (res[2 * SDRB200_MAXTAPS]) errw = 1; }
             __syncwarp();
             trk_epilogue(ch, st, res, res + SDRB200_MAXTAPS, hd->remc, hd->remp, recs ? &sm->rec : nullptr, lane,
@@ -270,12 +362,16 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             for (int i = lane; i < (int)(sizeof(trk_state_t) / 4); i += 32) dst[i] = src[i];
         }
         if (lane == 0) { nrec[chno] = donep; if (errw) atomicExch(err, 1); if (prof && chno == 0) prof[6] = donep; }
-    } else if (wid >= 3 && rank >= r0) {
+    } else if (wid >= TRK_T0 / 32 && rank >= r0) {
         /* ================= worker team: one whole code period per hand-out */
         const int t = threadIdx.x - TRK_T0;
+        const bool pfw = (prof != nullptr) && chno == 0 && rank == r0 && t == 0;
+        long long wt0 = pfw ? trk_clock() : 0;
+#define TRK_PFW(i) do { if (pfw) { const long long t1_ = trk_clock(); prof[i] += t1_ - wt0; wt0 = t1_; } } while (0)
         for (int i = 0;; i++) {
             const int slot = i & 1;
             cl_mbar_wait(&sm->full[slot], (uint32_t)((i >> 1) & 1));
+            TRK_PFW(9);                                      /* team: waiting for a hand-out */
             const trk_slot_t *h = &sm->slot[slot];
             if (h->stop) break;
             const int n = h->n;
@@ -289,6 +385,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             trk_bar_workers<NW>();
             trk_mix_prefix<DTYPE, NW, TRK_T0>(&sm->t, data, n, wk);
             trk_bar_workers<NW>();                       /* all prefix rows written */
+            TRK_PFW(7);                                      /* team: wipe-off + prefix sums */
             trk_tap_sums<DTYPE, NW, TRK_T0>(&sm->t, wk, data, n, sm->taps, ns, smax);
             trk_bar_workers<NW>();
             if (t < 32) {
@@ -299,8 +396,12 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 cl_mbar_arrive_remote(cl_map(&sm->done[q % R], 0));
             }
             trk_bar_workers<NW>();                       /* sums and header consumed before the next period resets them */
+            TRK_PFW(8);                                      /* team: chip boundaries + tap sums + report */
         }
     }
+#undef TRK_PF
+#undef TRK_PF0
+#undef TRK_PFW
     /* nobody leaves while a peer may still write into (or wait on) its shared memory */
     __syncthreads();
     cl_sync_all();

@@ -38,28 +38,28 @@ int check_walk_i(double x0, double step, int n, double wrap)
     return bad;
 }
 
-int max_dsegments = 0;
+int max_tsegments = 0;
 
-/* lean double-domain walker + correlator-thread segment form against the literal loop:
- * every value, its truncated index mod 2^B, and the end value */
-int check_walk_d(double x0, double step, int n, double wrap, int B)
+/* the tracking kernel's walker (step table + integer segments out) against the literal loop */
+int check_walk_t(double x0, double step, int n, double wrap)
 {
-    static nco_seg_t seg[NCO_MAXSEG];
+    static nco_iseg_t seg[NCO_MAXSEG];
     static nco_steptab_t tab;
-    nco_wseg_t w;
     double p = x0, xe;
-    int k, bad = 0, s = -1, cur = 0, rb = 0, ns;
+    int k, bad = 0, s = 0, ns;
     nco_steptab_build(step, &tab);
-    ns = nco_walk_d(x0, step, n, wrap, &tab, seg, NCO_MAXSEG, &xe);
+    ns = nco_walk_l(x0, step, n, wrap, &tab, seg, NCO_MAXSEG, &xe);
     if (ns < 0) return 1000000;
-    if (ns > max_dsegments) max_dsegments = ns;
+    if (ns > max_tsegments) max_tsegments = ns;
     for (k = 0; k < n; k++, p += step) {
         if (wrap > 0.0 && p >= wrap) p -= wrap;
-        while (cur + 1 < ns && seg[cur + 1].k0 <= k) cur++;
-        if (cur != s) { s = cur; rb = 0; nco_wseg_make(&seg[s], B, &w, &rb); }
-        if (seg[s].x0 + (double)(k - seg[s].k0) * seg[s].d != p) bad++;
+        while (s + 1 < ns && seg[s + 1].k0 <= k) s++;
         if (fabs(p) < 9.0e15) {
-            if (rb || nco_wseg_index(&w, k, B) != (uint32_t)(((int)(int64_t)p) & ((1 << B) - 1))) bad++;
+            if (seg[s].shift < 0 || nco_iseg_trunc(&seg[s], k) != (int64_t)p) bad++;
+        }
+        if (seg[s].shift >= 0 && seg[s].shift <= 52 && fabs(p) >= 1.0) {
+            const uint64_t m = seg[s].X0 + (uint64_t)((int64_t)(k - seg[s].k0) * seg[s].D);
+            if (ldexp((double)m, -seg[s].shift) != fabs(p)) bad++;
         }
     }
     if (p != xe) bad++;
@@ -84,7 +84,7 @@ int check_carrier(double freq, double phi0, double ti, int n)
     }
     if (p != t.x_end) bad++;
     bad += check_walk_i(phi, ps, n, 0.0);
-    bad += check_walk_d(phi, ps, n, 0.0, 5);
+    bad += check_walk_t(phi, ps, n, 0.0);
     prem = p * NCO_TWO_PI / 32.0;
     while (prem > NCO_TWO_PI) prem -= NCO_TWO_PI;
     if (prem != nco_carrier_rem(t.x_end)) bad++;
@@ -115,7 +115,7 @@ int check_code(double coff, int smax, double ci, int len, int n)
     }
     if (c != t.x_end) bad++;
     bad += check_walk_i(c0, ci, N, (double)len);
-    bad += check_walk_d(c0, ci, N, (double)len, 10);
+    bad += check_walk_t(c0, ci, N, (double)len);
     if (c - smax * ci != nco_code_rem(t.x_end, smax, ci)) bad++;
     return bad;
 }
@@ -162,7 +162,7 @@ int fuzz(unsigned long long seed, int iters, int mode)
                     if (p != t.x_end) r++;
                     if (t.nseg > max_segments) max_segments = t.nseg;
                     r += check_walk_i(x0, step, n, 0.0);
-                    r += check_walk_d(x0, step, n, 0.0, 5);
+                    r += check_walk_t(x0, step, n, 0.0);
                 }
             }
         }
@@ -204,7 +204,7 @@ int main(int argc, char **argv)
 {
     int iters = argc > 1 ? atoi(argv[1]) : 2000, m, bad = 0;
     for (m = 0; m < 6; m++) { int b = fuzz(1234 + m, iters, m); printf("mode %d: %d bad of %d\n", m, b, iters); bad += b; }
-    printf("max segments (mode 4) %d, integer walker %d, double walker %d\n", max_segments, max_isegments, max_dsegments);
+    printf("max segments (mode 4) %d, integer walker %d, lean table walker %d\n", max_segments, max_isegments, max_tsegments);
     { int b2 = fuzz_reduce(iters * 5); printf("reduce_2pi: %d bad of %d\n", b2, iters * 10); bad += b2; }
     return bad != 0;
 }
