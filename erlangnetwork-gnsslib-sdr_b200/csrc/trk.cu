@@ -327,11 +327,14 @@ __device__ static void trk_loops_warp(trk_state_t *st, const sdrb200_loop_t *prm
     }
 }
 
+struct trk_lf_t { double carrfreq, codefreq; unsigned long long cnt; int32_t navcnt, synci, flagsync, pad; };
+
 /* epilogue of one code period, executed by ONE warp: everything sdrtracking and
  * the sdrthread loop body do around correlator()                              */
 __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const unsigned int *sumI,
                                     const unsigned int *sumQ, double remc, double remp,
-                                    sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr)
+                                    sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr,
+                                    trk_lf_t *lf = nullptr, volatile int *lf_flag = nullptr, int lf_val = 0)
 {
     long long e0 = 0;
 #define TRK_EP(i) do { if (ep && lane == 0) { const long long e1 = trk_clock(); ep[i] += e1 - e0; e0 = e1; } } while (0)
@@ -388,6 +391,13 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
     if (mode == 1) trk_loops_warp(st, &ch->prm1, ch->ctime, ch, lane);
     else if (mode == 2) trk_loops_warp(st, &ch->prm2, (double)ch->loopms / 1000, ch, lane);
     __syncwarp();
+    /* the NCO lanes wait for exactly this: new frequencies and the counters of the next period */
+    if (lf && lane == 0) {
+        lf->carrfreq = st->carrfreq; lf->codefreq = st->codefreq; lf->cnt = st->cnt + 1;
+        lf->navcnt = st->navcnt; lf->synci = st->synci; lf->flagsync = st->flagsync;
+        __threadfence_block();
+        *lf_flag = lf_val;
+    }
     TRK_EP(13);
     /* setobsdata(), src/sdrtrk.c:160-209, called after the loop filters of a synchronised
      * channel (src/sdrmain.c:285-304).  Only slot [0] of the interpolation stocks lives on

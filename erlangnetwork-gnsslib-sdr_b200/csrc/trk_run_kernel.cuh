@@ -45,7 +45,9 @@ struct trk_cl_smem_t {
     trk_smem_t t;                            /* worker side: tables (2 slots x {carrier, code}), accumulators */
     int32_t taps[SDRB200_MAXCORRN];
     /* ---- worker side */
-    unsigned long long full[2];              /* mbarriers: slot s holds the tables of a period (64 arrivals) */
+    unsigned long long fullh[2];             /* mbarriers per slot: header written (1 arrival),      */
+    unsigned long long fullc[2];             /*   carrier table written (32), code table written (32) */
+    unsigned long long fullk[2];
     trk_slot_t slot[2];
     /* ---- control side (rank 0) */
     unsigned long long done[TRK_RING];       /* mbarriers: tap sums of period q arrived (32 arrivals) */
@@ -55,6 +57,9 @@ struct trk_cl_smem_t {
     volatile int seq_remc;                   /* ... whose remc is in hand[]                     */
     volatile int seq_remp;                   /* ... whose remp is in hand[] (carrier lane)      */
     volatile int epi_count;                  /* periods the epilogue has finished               */
+    volatile int loops_count;                /* periods whose loop filters have run: lf is theirs */
+    volatile int hdr_seq;                    /* periods whose n / boff are in rhdr[1]            */
+    trk_lf_t lf;                             /* what the lanes need after the loop filters of a period */
     int32_t pad0;
     nco_raw_t raw[2][2][TRK_MAXSEG];         /* [lane][period parity]: run records of the walks  */
     struct { int32_t ns, n, q, pad; unsigned long long boff; } rhdr[2][2];
@@ -159,10 +164,10 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             ((uint32_t *)&sm->chc)[i] = ((const uint32_t *)chg)[i];
     }
     if (threadIdx.x == 0) {
-        cl_mbar_init(&sm->full[0], 64); cl_mbar_init(&sm->full[1], 64);
+        for (int i = 0; i < 2; i++) { cl_mbar_init(&sm->fullh[i], 1); cl_mbar_init(&sm->fullc[i], 32); cl_mbar_init(&sm->fullk[i], 32); }
         for (int i = 0; i < R; i++) cl_mbar_init(&sm->done[i], 32);
         sm->seq_code = 0; sm->seq_remc = 0; sm->seq_remp = 0; sm->epi_count = 0;
-        sm->raw_seq[0] = 0; sm->raw_seq[1] = 0; sm->pushed[0] = 0; sm->pushed[1] = 0;
+        sm->raw_seq[0] = 0; sm->raw_seq[1] = 0; sm->pushed[0] = 0; sm->pushed[1] = 0; sm->loops_count = 0; sm->hdr_seq = 0;
         cl_fence_mbar_init();
     }
     __syncthreads();
@@ -182,11 +187,14 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             TRK_PF0();
             if (lane == 0) {
                 if (q < nperiods) {
-                    if (q == 0 || !prev_quiet) {
-                        cl_flag_wait_ge(&sm->epi_count, q);          /* the loop filters of period q-1 have run */
+                    if (q == 0) {
                         codefreq = st->codefreq; remc = st->remcode; cnt = st->cnt; navcnt = st->navcnt;
                         synci = st->synci; flagsync = st->flagsync;
-                        if (q == 0) { buffloc = st->buffloc; boff = buffloc % capacity; }
+                        buffloc = st->buffloc; boff = buffloc % capacity;
+                    } else if (!prev_quiet) {
+                        cl_flag_wait_ge(&sm->loops_count, q);        /* the loop filters of period q-1 have run */
+                        codefreq = sm->lf.codefreq; cnt = sm->lf.cnt; navcnt = sm->lf.navcnt;
+                        synci = sm->lf.synci; flagsync = sm->lf.flagsync;
                     }
                     n = nco_currnsamp(ch->clen, remc, codefreq, ch->f_sf);            /* src/sdrtrk.c:31-32 */
                     go = (n > 0 && n <= maxn && buffloc + (unsigned long long)n <= avail) ? 1 : 0;
@@ -197,6 +205,9 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 if (q >= R) cl_flag_wait_ge(&sm->epi_count, q - R + 1);
                 sm->hand[q % R].n = n; sm->hand[q % R].go = go; sm->hand[q % R].quiet = quiet;
                 cl_flag_set(&sm->seq_code, q + 1);
+                if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);                     /* rhdr / raw buffer q & 1 is free */
+                sm->rhdr[1][q & 1].n = go ? n : -1; sm->rhdr[1][q & 1].q = q; sm->rhdr[1][q & 1].boff = boff;
+                cl_flag_set(&sm->hdr_seq, q + 1);                                       /* the pusher sends the header (or leaves) */
                 if (pf && quiet) prof[10] += 1;
             }
             TRK_PF(1);                                       /* code lane: waits + period decisions */
@@ -214,13 +225,12 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 const double ci = __dmul_rn(ch->ti, codefreq);                          /* ti*crate, sdrcmn.c:709 */
                 const double c0 = nco_code_init(remc, smax, ci, ch->clen);
                 double xe;
-                if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);                     /* raw buffer q & 1 is free */
                 nseg = trk_walk_raw(c0, ci, n + 2 * smax, (double)ch->clen, &sm->tab[1], sm->raw[1][q & 1], &xe);
                 if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
                 remc2 = nco_code_rem(xe, smax, ci);
                 sm->hand[q % R].remc = remc2;
                 cl_flag_set(&sm->seq_remc, q + 1);
-                sm->rhdr[1][q & 1].ns = nseg; sm->rhdr[1][q & 1].n = n; sm->rhdr[1][q & 1].q = q; sm->rhdr[1][q & 1].boff = boff;
+                sm->rhdr[1][q & 1].ns = nseg;
                 cl_flag_set(&sm->raw_seq[1], q + 1);
                 remc = remc2; buffloc += (unsigned long long)n; cnt++;
                 boff += (unsigned long long)n; if (boff >= capacity) boff -= capacity; if (boff >= capacity) boff %= capacity;
@@ -229,13 +239,8 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             __syncwarp();
             TRK_PF(0);                                       /* code lane: table + walk */
         }
-        /* no more periods: the pusher leaves after the last real one */
-        if (lane == 0) {
-            if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);
-            sm->rhdr[1][q & 1].ns = -1;
-            cl_flag_set(&sm->raw_seq[1], q + 1);
-            cl_flag_wait_ge(&sm->pushed[1], q);              /* every real period is in its slot */
-        }
+        /* no more periods (rhdr[1][q & 1].n = -1 told the pusher to leave) */
+        if (lane == 0) cl_flag_wait_ge(&sm->pushed[1], q);   /* every real period is in its slot */
         __syncwarp();
         /* the teams leave: W more hand-outs that carry only the stop flag (this warp arrives for both lanes) */
         for (int j = 0; j < W; j++) {
@@ -244,10 +249,11 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             __syncwarp();
             const uint32_t tr = (uint32_t)(r0 + qq % W);
             const int slot = (qq / W) & 1;
-            if (lane == 0) cl_st_u32(cl_map(&sm->slot[slot], tr) + offsetof(trk_slot_t, stop), 1u);
+            if (lane == 0) {
+                cl_st_u32(cl_map(&sm->slot[slot], tr) + offsetof(trk_slot_t, stop), 1u);
+                cl_mbar_arrive_remote(cl_map(&sm->fullh[slot], tr));
+            }
             __syncwarp();
-            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
-            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
         }
     } else if (ctrl && wid == 0) {
         /* ================= carrier NCO lane */
@@ -263,9 +269,9 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             }
             go = __shfl_sync(0xffffffffu, go, 0);
             if (!go) break;
-            if (lane == 0 && (q == 0 || !prev_quiet)) {
-                cl_flag_wait_ge(&sm->epi_count, q);
-                carrfreq = st->carrfreq; remp = st->remcarr;
+            if (lane == 0) {
+                if (q == 0) { carrfreq = st->carrfreq; remp = st->remcarr; }
+                else if (!prev_quiet) { cl_flag_wait_ge(&sm->loops_count, q); carrfreq = sm->lf.carrfreq; }
             }
             TRK_PF(4);                                       /* carrier lane: waits */
             {
@@ -305,26 +311,32 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
         const int k = wid - 3;
         for (int q = 0;; q++) {
             TRK_PF0();
-            cl_flag_wait_ge(&sm->raw_seq[k], q + 1);
-            const int nsg = sm->rhdr[k][q & 1].ns;
-            if (nsg < 0) break;
             const uint32_t tr = (uint32_t)(r0 + q % W);
             const int slot = (q / W) & 1;
-            if (trk_push_raw(sm->raw[k][q & 1], nsg, &sm->tab[k], cl_map(&sm->t.segs[2 * slot + k][0], tr), lane)) atomicExch(err, 1);
-            if (lane == 0) {
-                const uint32_t h = cl_map(&sm->slot[slot], tr);
-                if (k == 0) cl_st_u32(h + offsetof(trk_slot_t, ncarr), (uint32_t)nsg);
-                else {
+            if (k == 1) {                                    /* the header goes out as soon as n is known */
+                cl_flag_wait_ge(&sm->hdr_seq, q + 1);
+                if (sm->rhdr[1][q & 1].n < 0) break;
+                if (lane == 0) {
+                    const uint32_t h = cl_map(&sm->slot[slot], tr);
                     const unsigned long long bo = sm->rhdr[1][q & 1].boff;
-                    cl_st_u32(h + offsetof(trk_slot_t, ncode), (uint32_t)nsg);
                     cl_st_u32(h + offsetof(trk_slot_t, n), (uint32_t)sm->rhdr[1][q & 1].n);
                     cl_st_u32(h + offsetof(trk_slot_t, stop), 0u);
                     cl_st_u32(h + offsetof(trk_slot_t, boff), (uint32_t)bo);
                     cl_st_u32(h + offsetof(trk_slot_t, boff) + 4, (uint32_t)(bo >> 32));
                     cl_st_u32(h + offsetof(trk_slot_t, q), (uint32_t)q);
+                    cl_mbar_arrive_remote(cl_map(&sm->fullh[slot], tr));
                 }
+                __syncwarp();
             }
-            cl_mbar_arrive_remote(cl_map(&sm->full[slot], tr));
+            cl_flag_wait_ge(&sm->raw_seq[k], q + 1);
+            const int nsg = sm->rhdr[k][q & 1].ns;
+            if (nsg < 0) break;
+            if (trk_push_raw(sm->raw[k][q & 1], nsg, &sm->tab[k], cl_map(&sm->t.segs[2 * slot + k][0], tr), lane)) atomicExch(err, 1);
+            if (lane == 0) {
+                const uint32_t h = cl_map(&sm->slot[slot], tr);
+                cl_st_u32(h + (k == 0 ? offsetof(trk_slot_t, ncarr) : offsetof(trk_slot_t, ncode)), (uint32_t)nsg);
+            }
+            cl_mbar_arrive_remote(cl_map(k == 0 ? &sm->fullc[slot] : &sm->fullk[slot], tr));
             __syncwarp();
             if (lane == 0) cl_flag_set(&sm->pushed[k], q + 1);
             TRK_PF(11);                                      /* pushers (both add to one slot) */
@@ -345,7 +357,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             if (lane == 0) { st->currnsamp = hd->n; if (res[2 * SDRB200_MAXTAPS]) errw = 1; }
             __syncwarp();
             trk_epilogue(ch, st, res, res + SDRB200_MAXTAPS, hd->remc, hd->remp, recs ? &sm->rec : nullptr, lane,
-                         (prof && chno == 0) ? prof : nullptr);
+                         (prof && chno == 0) ? prof : nullptr, &sm->lf, &sm->loops_count, q + 1);
             if (recs) {
                 const uint32_t *src = (const uint32_t *)&sm->rec;
                 uint32_t *dst = (uint32_t *)&recs[(size_t)chno * nperiods + q];
@@ -370,21 +382,33 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
 #define TRK_PFW(i) do { if (pfw) { const long long t1_ = trk_clock(); prof[i] += t1_ - wt0; wt0 = t1_; } } while (0)
         for (int i = 0;; i++) {
             const int slot = i & 1;
-            cl_mbar_wait(&sm->full[slot], (uint32_t)((i >> 1) & 1));
-            TRK_PFW(9);                                      /* team: waiting for a hand-out */
+            const uint32_t par = (uint32_t)((i >> 1) & 1);
+            cl_mbar_wait(&sm->fullh[slot], par);
             const trk_slot_t *h = &sm->slot[slot];
             if (h->stop) break;
             const int n = h->n;
             const int8_t *data = ifbuf + (size_t)h->boff * DTYPE;
+            /* the samples of the next period, and of the next one this team will see, towards L2 */
+            {
+                const size_t off = (size_t)t * TRK_SPAN;
+                if (off < (size_t)n * DTYPE) {
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(data + (size_t)n * DTYPE + off));
+                    if (W > 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(data + (size_t)n * DTYPE * W + off));
+                }
+            }
+            cl_mbar_wait(&sm->fullc[slot], par);
+            TRK_PFW(9);                                      /* team: waiting for a hand-out */
             if (t == 0) {
                 sm->t.icarr = sm->t.segs[2 * slot]; sm->t.icode = sm->t.segs[2 * slot + 1];
-                sm->t.carr.nseg = h->ncarr; sm->t.code.nseg = h->ncode;
+                sm->t.carr.nseg = h->ncarr;
                 sm->t.carry[0] = 0u; sm->t.carry[1] = 0u; sm->t.qcount = 0; sm->t.nslow[0] = 0; sm->t.nslow[1] = 0;
             }
             if (t < 2 * SDRB200_MAXTAPS) sm->t.sum[t] = 0u;
             trk_bar_workers<NW>();
             trk_mix_prefix<DTYPE, NW, TRK_T0>(&sm->t, data, n, wk);
-            trk_bar_workers<NW>();                       /* all prefix rows written */
+            cl_mbar_wait(&sm->fullk[slot], par);
+            if (t == 0) sm->t.code.nseg = h->ncode;
+            trk_bar_workers<NW>();                       /* all prefix rows written; code table here */
             TRK_PFW(7);                                      /* team: wipe-off + prefix sums */
             trk_tap_sums<DTYPE, NW, TRK_T0>(&sm->t, wk, data, n, sm->taps, ns, smax);
             trk_bar_workers<NW>();
