@@ -433,6 +433,25 @@ def run_b200(args):
             phases.update(periods=per, quiet_periods=int(out[10]),
                           unit="cycles per period of channel 0 (team0_* per period of the channel, the team sees 1 in W)")
         t_trk = sum(tms) / len(tms) * 1e-3
+        # channel-count sweep: the same 12 hand-over states replicated over more channels of the same
+        # IF stream (every channel is still a full closed loop of its own), 4 s each
+        sweep = []
+        if not args.no_sweep:
+            per_sw = 4000
+            for nchs in (12, 64, 148, 512, 2048):
+                eng = sdr.Tracking([chans[i % nch] for i in range(nchs)])
+                s_sw = eng.cuda_stream
+                eng.enqueue(st, 100); eng.sync(); eng.reset()
+                barrier()
+                e0.record(s_sw); eng.enqueue(st, per_sw); e1.record(s_sw)
+                eng.sync()
+                ms_sw = e1.ms_since(e0)
+                _, nrec_sw = eng.run(st, 1, want_records=False)
+                eng.close()
+                b_sw = nchs * per_sw * (NSAMP + 704)
+                sweep.append({"channels": nchs, "channel_s_per_s": nchs * per_sw * 1e-3 / (ms_sw * 1e-3),
+                              "us_per_code_period_per_channel": ms_sw * 1e3 / per_sw,
+                              "hbm_frac": b_sw / (ms_sw * 1e-3) / 1e9 / hbm_peak})
         # end to end: IF from pinned host memory -> device ring -> tracking -> per-channel record counts
         nbytes = int(nper + 8) * NSAMP + AVAIL
         host_if = torch.empty(nbytes, dtype=torch.int8, pin_memory=True)
@@ -477,6 +496,9 @@ def run_b200(args):
         }
         if phases:
             trk_obj["phases"] = phases
+        if sweep:
+            trk_obj["channel_sweep"] = {"if_seconds": 4.0, "note": "per GPU; first 4 s of every channel (bit sync falls inside), "
+                                        "cluster size chosen per engine from co-residency", "points": sweep}
     # ------------------------------------------------ config-5 style: many independent IF streams
     # BASELINE configs[4]: RTL-SDR-like 8-bit I/Q at 2.048 MS/s, full acquisition + tracking per
     # stream, streams sharded across the GPUs (8 per GPU of a 64-stream job).  Every plan and
@@ -521,6 +543,13 @@ def run_b200(args):
                    for p_, r in zip(range(1, NPRN + 1), g) if r["acquired"]]
             engines.append(sdr.Tracking(ch5) if ch5 else None)
         nch5 = sum(e.nch for e in engines if e)
+        # all engines run at once: the cluster size follows the TOTAL number of channels on the GPU
+        # (the small CTA instantiation fits two per SM)
+        cl5 = 1
+        while cl5 < 8 and nch5 * cl5 * 2 <= 2 * max(sdr.lib.sdrb200_sm_count(), 1):
+            cl5 *= 2
+        for e in engines:
+            if e: e.set_cluster(cl5)
         for e, sk in zip(engines, s5):
             if e: e.enqueue(sk, 200)
         for e in engines:
@@ -553,7 +582,7 @@ def run_b200(args):
             "streams_per_gpu": args.c5_streams, "channels_tracked": nch5_all,
             "acquisition": {"cells_per_s": NPRN * NFREQ * NS5 * steps5_all / tv[0], "ms": tv[0] * 1e3,
                             "integration_steps": steps5_all},
-            "tracking": {"value": nch5_all * nper5 * 1e-3 / tv[1], "unit": "channel.s/s", "ms": tv[1] * 1e3,
+            "tracking": {"value": nch5_all * nper5 * 1e-3 / tv[1], "unit": "channel.s/s", "ms": tv[1] * 1e3, "cluster_size": cl5,
                          "us_per_code_period_per_channel": tv[1] * 1e6 / nper5},
             "timing": "host clock around enqueue-all .. sync-all (several CUDA streams), device idle before",
         }
@@ -732,6 +761,7 @@ def main():
     ap.add_argument("--c5-streams", type=int, default=8, help="config-5 style independent streams per GPU (0: skip)")
     ap.add_argument("--c5-seconds", type=float, default=4.0)
     ap.add_argument("--c4-prns", type=int, default=16, help="config-4 style 20 ms coherent search over this many PRNs (0: skip)")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the tracking channel-count sweep")
     ap.add_argument("--trk-profile", action="store_true", help="add the per-phase cycle profile of channel 0")
     args = ap.parse_args()
     if args.warmup < 3:

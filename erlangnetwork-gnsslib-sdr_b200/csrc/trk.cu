@@ -671,7 +671,15 @@ extern "C" int sdrb200_trk_run(sdrb200_trk_t *e, const sdrb200_stream_t *s, int 
         SDRB200_CUDA_TRY(cudaMemcpyAsync(rec, e->d_rec, sizeof(sdrb200_trk_rec_t) * (size_t)e->nch * nperiods,
                                          cudaMemcpyDeviceToHost, e->st));
     SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
-    if (h[e->nch]) { sdrb200_set_error("trk_run: NCO segment table overflow"); return SDRB200_ERANGE; }
+    if (h[e->nch]) {
+        const int code = h[e->nch];
+        SDRB200_CUDA_TRY(cudaMemsetAsync(e->d_err, 0, sizeof(int), e->st));
+        sdrb200_set_error(code == 2 ? "trk_run: a channel lags by more than the stream's capacity (samples overwritten)"
+                        : code == 3 ? "trk_run: code period outside the work area (currnsamp <= 0 or > nsamp + nsamp/64 + 16)"
+                                    : "trk_run: NCO segment table overflow");
+        if (nrec) memcpy(nrec, h, sizeof(int) * e->nch);
+        return SDRB200_ERANGE;
+    }
     if (nrec) memcpy(nrec, h, sizeof(int) * e->nch);
     return SDRB200_OK;
 }

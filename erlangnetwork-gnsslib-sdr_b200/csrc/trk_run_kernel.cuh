@@ -198,6 +198,11 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                     }
                     n = nco_currnsamp(ch->clen, remc, codefreq, ch->f_sf);            /* src/sdrtrk.c:31-32 */
                     go = (n > 0 && n <= maxn && buffloc + (unsigned long long)n <= avail) ? 1 : 0;
+                    /* a period that cannot run for another reason than "the stream ends here" is an error:
+                     * 2 = the ring no longer holds the window (the channel lags by more than the capacity),
+                     * 3 = currnsamp outside the CTA's work area (codefreq ran away)                        */
+                    if (go && avail - buffloc > capacity) { go = 0; atomicMax(err, 2); }
+                    if (!go && (n <= 0 || n > maxn)) atomicMax(err, 3);
                     if (go && flagsync && ch->navrate > 1) quiet = trk_quiet_forecast(cnt, synci, &navcnt, ch->navrate, ch->loopms);
                 }
                 /* flow control: the team's slot is free, the rings' slots are consumed */
@@ -226,7 +231,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 const double c0 = nco_code_init(remc, smax, ci, ch->clen);
                 double xe;
                 nseg = trk_walk_raw(c0, ci, n + 2 * smax, (double)ch->clen, &sm->tab[1], sm->raw[1][q & 1], &xe);
-                if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
+                if (nseg < 0) { nseg = 0; atomicMax(err, 1); }
                 remc2 = nco_code_rem(xe, smax, ci);
                 sm->hand[q % R].remc = remc2;
                 cl_flag_set(&sm->seq_remc, q + 1);
@@ -285,7 +290,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 nco_carrier_init(carrfreq, remp, ch->ti, &phi, &ps);
                 if (q >= 2) cl_flag_wait_ge(&sm->pushed[0], q - 1);                     /* raw buffer q & 1 is free */
                 nseg = trk_walk_raw(phi, ps, n, 0.0, &sm->tab[0], sm->raw[0][q & 1], &xe);
-                if (nseg < 0) { nseg = 0; atomicExch(err, 1); }
+                if (nseg < 0) { nseg = 0; atomicMax(err, 1); }
                 sm->rhdr[0][q & 1].ns = nseg; sm->rhdr[0][q & 1].q = q;
                 cl_flag_set(&sm->raw_seq[0], q + 1);
             }
@@ -331,7 +336,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             cl_flag_wait_ge(&sm->raw_seq[k], q + 1);
             const int nsg = sm->rhdr[k][q & 1].ns;
             if (nsg < 0) break;
-            if (trk_push_raw(sm->raw[k][q & 1], nsg, &sm->tab[k], cl_map(&sm->t.segs[2 * slot + k][0], tr), lane)) atomicExch(err, 1);
+            if (trk_push_raw(sm->raw[k][q & 1], nsg, &sm->tab[k], cl_map(&sm->t.segs[2 * slot + k][0], tr), lane)) atomicMax(err, 1);
             if (lane == 0) {
                 const uint32_t h = cl_map(&sm->slot[slot], tr);
                 cl_st_u32(h + (k == 0 ? offsetof(trk_slot_t, ncarr) : offsetof(trk_slot_t, ncode)), (uint32_t)nsg);
@@ -373,7 +378,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             const uint32_t *src = (const uint32_t *)st;
             for (int i = lane; i < (int)(sizeof(trk_state_t) / 4); i += 32) dst[i] = src[i];
         }
-        if (lane == 0) { nrec[chno] = donep; if (errw) atomicExch(err, 1); if (prof && chno == 0) prof[6] = donep; }
+        if (lane == 0) { nrec[chno] = donep; if (errw) atomicMax(err, 1); if (prof && chno == 0) prof[6] = donep; }
     } else if (wid >= TRK_T0 / 32 && rank >= r0) {
         /* ================= worker team: one whole code period per hand-out */
         const int t = threadIdx.x - TRK_T0;

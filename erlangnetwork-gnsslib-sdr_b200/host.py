@@ -321,6 +321,10 @@ class Tracking:
     def reset(self):
         check(lib.sdrb200_trk_reset(self.h), "trk_reset")
 
+    def set_cluster(self, cluster_size: int, ctrl_works: bool = False):
+        """cluster size per channel (0: choose at the next launch, else 1, 2, 4, 8)."""
+        check(lib.sdrb200_trk_set_cluster(self.h, int(cluster_size), int(bool(ctrl_works))), "trk_set_cluster")
+
     @property
     def cuda_stream(self) -> int:
         lib.sdrb200_trk_cuda_stream.restype = C.c_void_p
