@@ -70,33 +70,32 @@ def scene(sdr, seed):
 def _cpu_acq_worker(job):
     """one process: the reference's sdracquisition for a list of PRNs."""
     seed, prns = job
-    import numpy as np
     import oracle_bind as ob
-    import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
-    host = sdr.ifgen_host(scene(sdr, seed), 0, AVAIL)
+    host = cached_if(seed, AVAIL)                         # made before the clock starts (pool initializer)
     o = ob.best()
     devnull = os.open(os.devnull, os.O_WRONLY)
     saved = os.dup(1)
     os.dup2(devnull, 1)                                   # the reference printf()s per channel
     try:
+        o.fft_seconds(reset=True)
         t0 = time.perf_counter()
         res, _ = o.acquire(ob.cfg_iffile(acq_intg=1), host, AVAIL, list(prns))
         dt = time.perf_counter() - t0
+        fft_s = o.fft_seconds(reset=True)
     finally:
         os.dup2(saved, 1)
         os.close(devnull)
         os.close(saved)
-    return dt, [(r.prn, r.acquired, r.freqi, r.codei) for r in res], o.name
+    with open("/proc/self/maps") as f:
+        mapped = "libsdrb200" in f.read()              # must stay False: the CPU legs run on oracle/ libraries only
+    return dt, [(r.prn, r.acquired, r.freqi, r.codei) for r in res], o.name, fft_s, mapped
 
 
 def _cpu_trk_worker(job):
     seed, prn, nper = job
     import oracle_bind as ob
-    import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
     total = AVAIL10 + (nper + 4) * NSAMP
-    host = sdr.ifgen_host(scene(sdr, seed), 0, total)
+    host = cached_if(seed, total)
     o = ob.best()
     devnull = os.open(os.devnull, os.O_WRONLY)
     saved = os.dup(1)
@@ -107,13 +106,19 @@ def _cpu_trk_worker(job):
         o.acquire(cfg, host, AVAIL10, [prn])
         t_acq = time.perf_counter() - t0
         t0 = time.perf_counter()
-        _, _, ntr = o.acq_track(cfg, host, AVAIL10, [prn], nper)
+        acq, rec, ntr = o.acq_track(cfg, host, AVAIL10, [prn], nper)
         dt = time.perf_counter() - t0 - t_acq
     finally:
         os.dup2(saved, 1)
         os.close(devnull)
         os.close(saved)
-    return dt, ntr[0], o.name
+    n = ntr[0]
+    r = rec[0][:n]
+    keep = {"prn": prn, "acquired": acq[0].acquired, "freqi": acq[0].freqi, "codei": acq[0].codei, "n": n,
+            "currnsamp": r["currnsamp"].copy(), "II": r["II"][:, :13].copy(), "QQ": r["QQ"][:, :13].copy(),
+            "flagsync": r["flagsync"].copy(), "synci": r["synci"].copy(), "bit": r["bit"].copy(),
+            "swsync": r["swsync"].copy(), "carrfreq": r["carrfreq"].copy(), "codefreq": r["codefreq"].copy()}
+    return dt, n, o.name, keep
 
 
 def _cpu_shipped_worker(job):
@@ -122,13 +127,11 @@ def _cpu_shipped_worker(job):
     hfftmtx anyway), tracking with one pthread per channel (oh_acq_track_mt)."""
     seed, nacq, nper = job
     import oracle_bind as ob
-    import sdrb200_pkg
     if not ob.have_ref_shipped():
         return None
-    sdr = sdrb200_pkg.load()
     o = ob.ref_shipped()
     total = AVAIL10 + (nper + 4) * NSAMP
-    host = sdr.ifgen_host(scene(sdr, seed), 0, total)
+    host = cached_if(seed, total)
     devnull = os.open(os.devnull, os.O_WRONLY)
     saved = os.dup(1)
     os.dup2(devnull, 1)
@@ -153,9 +156,32 @@ def _cpu_shipped_worker(job):
             "flags": "-g -DFFTMTX, no -O (bin/Makefile:17,29); FFT shim at -O2 in place of the FFTW binary"}
 
 
-def cpu_pool(cores):
+_IF_CACHE = {}
+
+
+def cached_if(seed, n):
+    """host IF of the bench scene, samples [0, n): generated once per process by the CPU generator
+    (oracle/libifgen.so - the CPU legs never map the product library) and kept."""
+    import testkit
+    have = _IF_CACHE.get(seed)
+    if have is None or len(have) < n:
+        have = testkit.ifgen_host(scene(testkit, seed), 0, n)
+        _IF_CACHE[seed] = have
+    return have[:n]
+
+
+def _pool_init(seed, n):
+    cached_if(seed, n)
+
+
+def cpu_pool(cores, seed=None, n=0):
+    """worker processes; with a seed every worker generates its copy of the IF while it starts,
+    i.e. before any clock of the CPU legs runs."""
     import multiprocessing as mp
-    return mp.get_context("spawn").Pool(cores)
+    ctx = mp.get_context("spawn")
+    if seed is None:
+        return ctx.Pool(cores)
+    return ctx.Pool(cores, initializer=_pool_init, initargs=(seed, n))
 
 
 def cpu_acq_step(pool, cores, seed, prns):
@@ -244,15 +270,20 @@ def run_b200(args):
 
     # CPU baseline first (rank 0, N=1 only), before CUDA is initialised in this process
     cpu_acq = cpu_trk = None
+    ref_acq = ref_trk = host_par = None                  # what the GPU path is checked against (outside all clocks)
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
-        pool = cpu_pool(cores)
+        pool = cpu_pool(cores, 0xB2000000, AVAIL10 + 2004 * NSAMP)
         try:
             prns = list(range(1, NPRN + 1))
             cpu_acq_step(pool, cores, 0xB2000000, prns[:cores])         # warm (page in, FFT plans)
             dt, out = cpu_acq_step(pool, cores, 0xB2000000, prns)
+            ref_acq = {t[0]: t[1:] for w in out for t in w[1]}          # prn -> (acquired, freqi, codei)
+            fft_s = [w[3] for w in out if w[3] is not None]
             cpu_acq = {"value": CELLS_PER_STEP / dt, "unit": "cells/s", "cores": min(cores, NPRN),
-                       "kind": oracle_kind(), "impl": oracle_label(),
+                       "kind": oracle_kind(), "impl": oracle_label(), "fft": "shim",
+                       "fftw3f_on_this_host": __import__("ctypes.util").util.find_library("fftw3f"),
+                       "fft_share_of_cpu_time": (sum(fft_s) / sum(w[0] for w in out)) if fft_s else None,
                        "sample": f"1 full step (32 PRN x 71 bins x 16368), {dt:.2f} s wall on {min(cores, NPRN)} processes"}
             nper = 2000
             t0 = time.perf_counter()
@@ -260,6 +291,8 @@ def run_b200(args):
             wall = time.perf_counter() - t0
             tot = sum(r[1] for r in res)
             per_core = sum(r[0] for r in res)
+            ref_trk = [r[3] for r in res]
+            host_par = pool.apply(cached_if, (0xB2000000, AVAIL10 + (nper + 4) * NSAMP))   # the bytes the CPU legs ran on
             cpu_trk = {"value": tot * 1e-3 / max(r[0] for r in res), "unit": "channel.s/s",
                        "cores": min(cores, len(TRK_PRNS)), "kind": oracle_kind(), "impl": oracle_label(),
                        "single_core_value": tot * 1e-3 / per_core,
@@ -276,7 +309,8 @@ def run_b200(args):
             pool.close()
 
     import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
+    import testkit
+    sdr = testkit.attach(sdrb200_pkg.load())
     lib = sdr.lib
     if sdr.device_count() < 1:
         raise SystemExit("bench.py: no CUDA device (libsdrb200 has no CPU fallback)")
@@ -287,6 +321,7 @@ def run_b200(args):
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     sdr.check(lib.sdrb200_set_device(local), "set_device")
+    testkit.set_device(local)
 
     def barrier():
         if dist is not None:
@@ -294,9 +329,8 @@ def run_b200(args):
         sdr.check(lib.sdrb200_device_sync(), "sync")
 
     # ALU issue peaks of this GPU (micro-benchmark in the library), for the second roofline
-    pk = C.c_double()
-    sdr.check(lib.sdrb200_alu_peak(0, C.byref(pk)), "alu_peak"); fp32_peak = pk.value / 1e12
-    sdr.check(lib.sdrb200_alu_peak(1, C.byref(pk)), "alu_peak"); int32_peak = pk.value / 1e12
+    fp32_peak = testkit.alu_peak(0) / 1e12
+    int32_peak = testkit.alu_peak(1) / 1e12
 
     # ------------------------------------------------------------ data
     seed = 0xB2000000 + rank
@@ -499,6 +533,57 @@ def run_b200(args):
         if sweep:
             trk_obj["channel_sweep"] = {"if_seconds": 4.0, "note": "per GPU; first 4 s of every channel (bit sync falls inside), "
                                         "cluster size chosen per engine from co-residency", "points": sweep}
+    # ------------------------------------------------ parity of the two headline configs, outside every clock
+    # The CPU legs above ran the reference on host-generated IF; the same bytes go through the
+    # CUDA path here and every decision is compared (the timed runs use the device-generated
+    # copy of the same scene, which may differ from it in isolated samples by one LSB).
+    parity = {"parity_checked": False, "why": "CPU legs skipped (--no-cpu or N > 1)"}
+    if ref_acq is not None and host_par is not None:
+        stp = sdr.Stream(1, len(host_par))
+        stp.push(host_par)
+        gp = acq.run(stp, b0)
+        bad = [(p, ref_acq[p], (g["acquired"], g["freqi"], g["codei"])) for p, g in zip(prns, gp)
+               if tuple(ref_acq[p]) != (g["acquired"], g["freqi"], g["codei"])]
+        if bad:
+            raise SystemExit(f"bench.py: acquisition parity FAILED against the reference (prn, ref, gpu): {bad[:4]}")
+        parity = {"parity_checked": True, "oracle": oracle_kind(),
+                  "acquisition": f"32 PRN: acquired / freqi / codei equal the reference's on the same IF bytes "
+                                 f"({sum(1 for p in prns if ref_acq[p][0])} acquired)"}
+        if ref_trk and not args.no_trk:
+            g10 = {p: r for p, r in zip(TRK_PRNS, acq10.run(stp, b10))}
+            nperp = min(r["n"] for r in ref_trk)
+            chp, refs = [], []
+            for r in ref_trk:
+                g = g10[r["prn"]]
+                if (r["acquired"], r["freqi"], r["codei"]) != (g["acquired"], g["freqi"], g["codei"]):
+                    raise SystemExit(f"bench.py: hand-over parity FAILED for PRN {r['prn']}: ref "
+                                     f"{(r['acquired'], r['freqi'], r['codei'])} gpu {(g['acquired'], g['freqi'], g['codei'])}")
+                if g["acquired"]:
+                    chp.append(sdr.make_trk_chan(FS, F_IF, F_CF, 1, r["prn"], sdr.gencode(r["prn"])[0], b10 + g["codei"],
+                                                 g["acqfreq"], 6, 3, 6, (5.0, 1.0), (30.0, 10.0), (200.0, 50.0)))
+                    refs.append(r)
+            trp = sdr.Tracking(chp)
+            recp, nrp = trp.run(stp, nperp)
+            dII = dcf = 0.0
+            for k, r in enumerate(refs):
+                n_ = min(nrp[k], r["n"], nperp)
+                if n_ < nperp:
+                    raise SystemExit(f"bench.py: tracking parity FAILED: PRN {r['prn']} ran {n_} of {nperp} periods")
+                g = recp[k][:n_]
+                for key in ("currnsamp", "flagsync", "synci", "swsync"):
+                    if not np.array_equal(g[key], r[key][:n_]):
+                        raise SystemExit(f"bench.py: tracking parity FAILED: PRN {r['prn']} field {key}")
+                if not np.array_equal(g["bit"][g["swsync"] == 1], r["bit"][:n_][r["swsync"][:n_] == 1]):
+                    raise SystemExit(f"bench.py: tracking parity FAILED: PRN {r['prn']} nav bits differ")
+                dII = max(dII, float(np.abs(g["II"][:, :13] - r["II"][:n_]).max()), float(np.abs(g["QQ"][:, :13] - r["QQ"][:n_]).max()))
+                dcf = max(dcf, float(np.abs(g["carrfreq"] - r["carrfreq"][:n_]).max()))
+            if dII > 508.0:
+                raise SystemExit(f"bench.py: tracking parity FAILED: max |dII| {dII} > 508 (two flipped samples per tap)")
+            parity["tracking"] = (f"{len(refs)} channels x {nperp} code periods: currnsamp, flagsync, synci, swsync, nav bits equal; "
+                                  f"max |dII,dQQ| = {dII:g} (bound 508), max |dcarrfreq| = {dcf:.3g} Hz")
+            trp.close()
+        stp.close()
+
     # ------------------------------------------------ config-5 style: many independent IF streams
     # BASELINE configs[4]: RTL-SDR-like 8-bit I/Q at 2.048 MS/s, full acquisition + tracking per
     # stream, streams sharded across the GPUs (8 per GPU of a 64-stream job).  Every plan and
@@ -672,6 +757,7 @@ def run_b200(args):
                              "model": "SURVEY 8(d): 170 flop per cell"},
                      "note": "compulsory-traffic model: the path is FFT/shared-memory bound, not HBM bound (DESIGN.md)"},
         "cpu_baseline": cpu_acq,
+        "parity": parity, "parity_checked": parity["parity_checked"],
         "clocks": clk,
         "acquired_prns": [p for p, r in zip(prns, res) if r["acquired"]],
         "tracking": trk_obj,
@@ -691,7 +777,7 @@ def run_reference(args):
         return
     cores = os.cpu_count() or 1
     K, W = args.steps, args.warmup
-    pool = cpu_pool(cores)
+    pool = cpu_pool(cores, 0xB2000000, AVAIL)             # every worker holds the IF before a clock starts
     prns = list(range(1, NPRN + 1))
     try:
         dt, _ = cpu_acq_step(pool, cores, 0xB2000000, prns[:min(cores, NPRN)])     # calibrate
@@ -705,10 +791,12 @@ def run_reference(args):
         sub = prns[:nsub]
         for _ in range(W):
             cpu_acq_step(pool, cores, 0xB2000000, sub)
-        t = 0.0
+        t, fft_t, cpu_t, mapped = 0.0, 0.0, 0.0, False
         for _ in range(K):
             dt, out = cpu_acq_step(pool, cores, 0xB2000000, sub)
             t += dt
+            fft_t += sum(w[3] or 0.0 for w in out); cpu_t += sum(w[0] for w in out)
+            mapped = mapped or any(w[4] for w in out)
     finally:
         pool.close()
     cells = nsub * NFREQ * NSAMP
@@ -722,7 +810,11 @@ def run_reference(args):
         "impl": "reference",
         "config": {"workload": WORKLOAD_ACQ, "sample": sample},
         "cpu_baseline": {"value": v, "unit": "cells/s", "cores": used, "kind": oracle_kind(),
-                         "impl": oracle_label(), "sample": sample},
+                         "impl": oracle_label(), "sample": sample, "fft": "shim",
+                         "fftw3f_on_this_host": __import__("ctypes.util").util.find_library("fftw3f"),
+                         "fft_share_of_cpu_time": (fft_t / cpu_t) if cpu_t > 0 and fft_t > 0 else None,
+                         "if_generated": "before the clock (pool initializer, oracle/libifgen.so)",
+                         "product_library_mapped": bool(mapped)},
         "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

@@ -24,7 +24,6 @@ CTYPE_L1CA, CTYPE_G1, CTYPE_L1SBAS = 1, 20, 27
 FMT_RTLSDR, FMT_STEREO_FE1, FMT_STEREO_FE2, FMT_GN3S_2BIT, FMT_GN3S_4BIT = 1, 2, 3, 4, 5
 MAXCORRN = 16
 MAXTAPS = 1 + 2 * MAXCORRN
-IFGEN_MAXSAT = 16
 
 
 class Error(RuntimeError):
@@ -44,21 +43,6 @@ def check(rc: int, what: str = "") -> None:
 
 
 # ----------------------------------------------------------------- structs
-class IfgenSat(C.Structure):
-    _fields_ = [("prn", C.c_int), ("nav_on", C.c_int), ("cn0_dbhz", C.c_double),
-                ("doppler_hz", C.c_double), ("doppler_rate", C.c_double),
-                ("code_phase", C.c_double), ("carr_phase", C.c_double),
-                ("nav_seed", C.c_uint64)]
-
-
-class IfgenCfg(C.Structure):
-    _fields_ = [("f_sf", C.c_double), ("f_if", C.c_double), ("f_cf", C.c_double),
-                ("crate", C.c_double), ("sigma", C.c_double), ("dtype", C.c_int),
-                ("clen", C.c_int), ("bitlen", C.c_int), ("nsat", C.c_int),
-                ("seed", C.c_uint64), ("sat", IfgenSat * IFGEN_MAXSAT),
-                ("amp", C.c_double * IFGEN_MAXSAT)]
-
-
 class AcqCfg(C.Structure):
     _fields_ = [("f_sf", C.c_double), ("dtype", C.c_int), ("nsamp", C.c_int),
                 ("nsampchip", C.c_int), ("ctime", C.c_double), ("nfreq", C.c_int),

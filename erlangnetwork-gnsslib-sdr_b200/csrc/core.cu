@@ -14,7 +14,6 @@
 #include <string.h>
 #include <atomic>
 #include "sdrb200_internal.h"
-#include "ifgen.h"
 
 static thread_local char g_err[512] = "";
 static std::atomic<uint64_t> g_launches{0};
@@ -107,7 +106,7 @@ static int mirror_guard(sdrb200_stream_t *s, size_t off, size_t len)
     return SDRB200_OK;
 }
 
-/* generic chunked append; src_kind 0: host int8, 1: host rtlsdr u8, 2: ifgen */
+/* generic chunked append; src_kind 0: host int8, 1: host rtlsdr u8, 2: device int8, 3: host packed bytes */
 __global__ void k_rtlsdr_expand(const uint8_t *__restrict__ in, int8_t *__restrict__ out, size_t n)
 {
     /* rtlsdr_exp: (char)(buf-127.5), src/rcv/rtlsdr/rtlsdr.c:136-142.
@@ -115,66 +114,6 @@ __global__ void k_rtlsdr_expand(const uint8_t *__restrict__ in, int8_t *__restri
     size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     size_t stride = (size_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) out[i] = (int8_t)(int)((float)in[i] - 127.5f);
-}
-
-__global__ void k_ifgen(ifgen_cfg_t cfg, const signed char *__restrict__ codes,
-                        uint64_t k0, uint64_t n, signed char *__restrict__ out)
-{
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (; i < n; i += stride) {
-        signed char v[2];
-        ifgen_sample(&cfg, codes, k0 + i, v);
-        if (cfg.dtype == 2) { out[2 * i] = v[0]; out[2 * i + 1] = v[1]; }
-        else out[i] = v[0];
-    }
-}
-
-static int ifgen_codes(const ifgen_cfg_t *c, signed char *codes /*[MAXSAT][MAXCLEN]*/)
-{
-    memset(codes, 0, (size_t)IFGEN_MAXSAT * IFGEN_MAXCLEN);
-    if (c->nsat < 0 || c->nsat > IFGEN_MAXSAT || c->clen < 1 || c->clen > IFGEN_MAXCLEN) {
-        sdrb200_set_error("ifgen: bad nsat/clen"); return SDRB200_EINVAL;
-    }
-    for (int s = 0; s < c->nsat; s++) {
-        int8_t tmp[IFGEN_MAXCLEN];
-        int len = (c->clen == 511) ? sdrb200_gencode_g1(tmp) : sdrb200_gencode_l1ca(c->sat[s].prn, tmp);
-        if (len != c->clen) { sdrb200_set_error("ifgen: code length mismatch"); return SDRB200_EINVAL; }
-        memcpy(codes + (size_t)s * IFGEN_MAXCLEN, tmp, (size_t)len);
-    }
-    return SDRB200_OK;
-}
-
-extern "C" int sdrb200_ifgen_host(const void *vcfg, uint64_t k0, uint64_t n, int8_t *out)
-{
-    if (!vcfg || !out) return SDRB200_EINVAL;
-    ifgen_cfg_t c = *(const ifgen_cfg_t *)vcfg;
-    static thread_local signed char codes[IFGEN_MAXSAT * IFGEN_MAXCLEN];
-    int rc = ifgen_codes(&c, codes);
-    if (rc) return rc;
-    ifgen_prepare(&c);
-    for (uint64_t i = 0; i < n; i++) ifgen_sample(&c, codes, k0 + i, (signed char *)out + i * c.dtype);
-    return SDRB200_OK;
-}
-
-static int ifgen_launch(const ifgen_cfg_t *cfg_in, uint64_t k0, uint64_t n, void *d_out, cudaStream_t st)
-{
-    ifgen_cfg_t c = *cfg_in;
-    signed char codes[IFGEN_MAXSAT * IFGEN_MAXCLEN];
-    int rc = ifgen_codes(&c, codes);
-    if (rc) return rc;
-    ifgen_prepare(&c);
-    signed char *d_codes = NULL;
-    SDRB200_CUDA_TRY(cudaMallocAsync((void **)&d_codes, sizeof(codes), st));
-    SDRB200_CUDA_TRY(cudaMemcpyAsync(d_codes, codes, sizeof(codes), cudaMemcpyHostToDevice, st));
-    /* codes[] is on the stack: make the copy complete before returning */
-    SDRB200_CUDA_TRY(cudaStreamSynchronize(st));
-    int blocks = 148 * 8;
-    k_ifgen<<<blocks, 256, 0, st>>>(c, d_codes, k0, n, (signed char *)d_out);
-    sdrb200_count_launch(1);
-    SDRB200_CUDA_TRY(cudaGetLastError());
-    SDRB200_CUDA_TRY(cudaFreeAsync(d_codes, st));
-    return SDRB200_OK;
 }
 
 /* ---- ranging codes on the device (gencode, src/sdrcode.c:101-154, 426-444, 523-539) ----
@@ -246,12 +185,6 @@ extern "C" int sdrb200_gencode_device(int n, const int *prn, int ctype, int8_t *
     return rc == SDRB200_OK ? len : rc;
 }
 
-extern "C" int sdrb200_ifgen_device(const void *vcfg, uint64_t k0, uint64_t n, void *d_out, void *cuda_stream)
-{
-    if (!vcfg || !d_out) return SDRB200_EINVAL;
-    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
-    return ifgen_launch((const ifgen_cfg_t *)vcfg, k0, n, d_out, (cudaStream_t)cuda_stream);
-}
 
 /* packed front-end formats: every input byte holds one sample (real, or I and Q).
  * The per-byte expansion tables restate the reference's unpack routines:
@@ -300,10 +233,10 @@ __global__ void k_expand_lut(const uint8_t *__restrict__ in, int8_t *__restrict_
     }
 }
 
-static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifgen_cfg_t *gen, uint64_t n,
+static int stream_push(sdrb200_stream_t *s, int kind, const void *src, uint64_t n,
                        const expand_lut_t *lut = NULL, int outs = 0)
 {
-    if (!s || (kind != 2 && !src)) { sdrb200_set_error("stream_push: bad argument"); return SDRB200_EINVAL; }
+    if (!s || !src) { sdrb200_set_error("stream_push: bad argument"); return SDRB200_EINVAL; }
     cudaStream_t st = (cudaStream_t)s->cuda_stream;
     const size_t bps = (size_t)s->dtype;
     uint64_t done = 0;
@@ -333,9 +266,8 @@ static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifg
             SDRB200_CUDA_TRY(cudaGetLastError());
             SDRB200_CUDA_TRY(cudaFreeAsync(tmp, st));
         } else {
-            int rc = ifgen_launch(gen, s->ifgen_next, chunk, dst, st);
-            if (rc) return rc;
-            s->ifgen_next += chunk;
+            SDRB200_CUDA_TRY(cudaMemcpyAsync(dst, (const int8_t *)src + done * bps, chunk * bps,
+                                             cudaMemcpyDeviceToDevice, st));
         }
         int rc = mirror_guard(s, pos * bps, chunk * bps);
         if (rc) return rc;
@@ -348,7 +280,7 @@ static int stream_push(sdrb200_stream_t *s, int kind, const void *src, const ifg
 
 extern "C" int sdrb200_stream_push_host(sdrb200_stream_t *s, const int8_t *host, uint64_t n)
 {
-    return stream_push(s, 0, host, NULL, n);
+    return stream_push(s, 0, host, n);
 }
 extern "C" int sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_t *host, uint64_t n, int format)
 {
@@ -358,19 +290,19 @@ extern "C" int sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_
     if (format == SDRB200_FMT_RTLSDR) return sdrb200_stream_push_host_rtlsdr(s, host, n);
     if (expand_lut_build(format, &lut, &outs)) { sdrb200_set_error("stream_push_packed: unknown format %d", format); return SDRB200_EINVAL; }
     if (s->dtype != outs) { sdrb200_set_error("stream_push_packed: format %d yields dtype %d samples", format, outs); return SDRB200_EINVAL; }
-    return stream_push(s, 3, host, NULL, n, &lut, outs);
+    return stream_push(s, 3, host, n, &lut, outs);
 }
 
 extern "C" int sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, uint64_t n)
 {
     if (s && s->dtype != 2) { sdrb200_set_error("rtlsdr samples are I/Q (dtype 2)"); return SDRB200_EINVAL; }
-    return stream_push(s, 1, host, NULL, n);
+    return stream_push(s, 1, host, n);
 }
-extern "C" int sdrb200_stream_push_ifgen(sdrb200_stream_t *s, const void *cfg, uint64_t n)
+/* IF that is already in device memory (another kernel produced it, or a DMA engine wrote it):
+ * appended with a device-to-device copy on the stream's own CUDA stream                   */
+extern "C" int sdrb200_stream_push_device(sdrb200_stream_t *s, const int8_t *d_src, uint64_t n)
 {
-    if (!cfg) return SDRB200_EINVAL;
-    if (s && ((const ifgen_cfg_t *)cfg)->dtype != s->dtype) { sdrb200_set_error("ifgen dtype != stream dtype"); return SDRB200_EINVAL; }
-    return stream_push(s, 2, NULL, (const ifgen_cfg_t *)cfg, n);
+    return stream_push(s, 2, d_src, n);
 }
 
 extern "C" int sdrb200_stream_read(const sdrb200_stream_t *s, uint64_t buffloc, uint64_t n, int8_t *host)
@@ -441,56 +373,3 @@ extern "C" int sdrb200_l2_flush(void *cuda_stream)
     return SDRB200_OK;
 }
 
-/* issue-rate micro-benchmarks for the ALU rooflines of DESIGN.md: 8 independent
- * chains per thread of fp32 FMA (kind 0) or int32 multiply-add (kind 1), every
- * SM filled; returns operations per second counting one FMA / one MAD as 2 ops */
-template <int KIND>
-__global__ void __launch_bounds__(256) k_alu_peak(float *out, int iters, float a, int ia)
-{
-    float f[8]; int n[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) { f[i] = (float)(threadIdx.x + i); n[i] = threadIdx.x + i; }
-    for (int it = 0; it < iters; it++) {
-#pragma unroll
-        for (int r = 0; r < 16; r++)
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                if (KIND == 0) f[i] = fmaf(f[i], a, 1.0f);
-                else n[i] = n[i] * ia + 1;
-            }
-    }
-    float s = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; i++) s += (KIND == 0) ? f[i] : (float)n[i];
-    if (s == 12345.678f) out[0] = s;                     /* keeps the chains alive */
-}
-
-extern "C" int sdrb200_alu_peak(int kind, double *ops_per_s)
-{
-    if (!ops_per_s || (kind != 0 && kind != 1)) return SDRB200_EINVAL;
-    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
-    cudaDeviceProp pr; int dev = 0;
-    SDRB200_CUDA_TRY(cudaGetDevice(&dev));
-    SDRB200_CUDA_TRY(cudaGetDeviceProperties(&pr, dev));
-    float *d = NULL;
-    SDRB200_CUDA_TRY(cudaMalloc(&d, 64));
-    cudaEvent_t e0, e1;
-    SDRB200_CUDA_TRY(cudaEventCreate(&e0)); SDRB200_CUDA_TRY(cudaEventCreate(&e1));
-    const int grid = pr.multiProcessorCount * 8, iters = 1024;
-    double best = 0.0;
-    for (int rep = 0; rep < 4; rep++) {
-        cudaEventRecord(e0, 0);
-        if (kind == 0) k_alu_peak<0><<<grid, 256>>>(d, iters, 0.999f, 3);
-        else k_alu_peak<1><<<grid, 256>>>(d, iters, 0.999f, 3);
-        cudaEventRecord(e1, 0);
-        cudaEventSynchronize(e1);
-        float ms = 0.f; cudaEventElapsedTime(&ms, e0, e1);
-        const double ops = 2.0 * (double)grid * 256.0 * (double)iters * 16.0 * 8.0 / (ms * 1e-3);
-        if (rep > 0 && ops > best) best = ops;
-    }
-    sdrb200_count_launch(4);
-    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
-    SDRB200_CUDA_TRY(cudaGetLastError());
-    *ops_per_s = best;
-    return SDRB200_OK;
-}

@@ -32,7 +32,6 @@ struct sdrb200_stream {
     uint64_t  count;        /* samples pushed so far                             */
     int8_t   *d_buf;        /* capacity*dtype + guard bytes                      */
     void     *cuda_stream;  /* cudaStream_t used for pushes                      */
-    uint64_t  ifgen_next;   /* next synthetic sample index                       */
 };
 #define SDRB200_STREAM_GUARD (4u << 20)     /* mirrored bytes past the ring end   */
 

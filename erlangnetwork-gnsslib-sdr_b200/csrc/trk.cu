@@ -683,88 +683,3 @@ extern "C" int sdrb200_trk_run(sdrb200_trk_t *e, const sdrb200_stream_t *s, int 
     if (nrec) memcpy(nrec, h, sizeof(int) * e->nch);
     return SDRB200_OK;
 }
-
-/* ---- self-test of the device NCO walk (tests/test_gpu_correlator.py) ----
- * n random (start, step, count, wrap) cases, one CTA each, against the host walker
- * nco_walk_i (itself fuzzed against the literal loops by tests/csrc/nco_check.c):
- * every truncated value and the final accumulator must agree.                       */
-__global__ void k_nco_selftest(const double *x, const double *step, const int *count, const double *wrap,
-                               nco_iseg_t *segs, int *ns, double *xe)
-{
-    const int c = blockIdx.x;
-    __shared__ nco_steptab_t tab;
-    double e;
-    trk_steptab_warp(&tab, step[c], threadIdx.x);          /* launched with one warp */
-    if (threadIdx.x != 0) return;
-    const int r = nco_walk_l(x[c], step[c], count[c], wrap[c], &tab, segs + (size_t)c * TRK_MAXSEG, TRK_MAXSEG, &e);
-    ns[c] = r; xe[c] = e;
-}
-
-extern "C" int sdrb200_nco_selftest(int n, unsigned long long seed, int mode, int *mismatches)
-{
-    if (n < 1 || !mismatches) return SDRB200_EINVAL;
-    if (sdrb200_ensure_device()) return SDRB200_ENODEV;
-    double *hx = (double *)malloc(sizeof(double) * n * 3), *hs = hx + n, *hw = hs + n;
-    int *hc = (int *)malloc(sizeof(int) * n);
-    unsigned long long rs = seed;
-    auto urand = [&]() { rs = rs * 6364136223846793005ULL + 1442695040888963407ULL; return (double)(rs >> 11) * (1.0 / 9007199254740992.0); };
-    for (int i = 0; i < n; i++) {
-        const int m = (mode < 0) ? i % 5 : mode;
-        if (m == 0) {            /* IF carrier */
-            double phi, ps; nco_carrier_init(4.092e6 + (urand() - 0.5) * 2e4, urand() * NCO_TWO_PI, 1.0 / 16.368e6, &phi, &ps);
-            hx[i] = phi; hs[i] = ps; hw[i] = 0.0; hc[i] = 16360 + (int)(urand() * 20);
-        } else if (m == 1) {     /* baseband carrier, both signs */
-            double phi, ps; nco_carrier_init((urand() - 0.5) * 2e4, urand() * NCO_TWO_PI, 1.0 / 2.048e6, &phi, &ps);
-            hx[i] = phi; hs[i] = ps; hw[i] = 0.0; hc[i] = 2040 + (int)(urand() * 20);
-        } else if (m == 2) {     /* code, 16.368 MS/s */
-            const double ci = (1.0 / 16.368e6) * (1.023e6 + (urand() - 0.5) * 20.0);
-            hx[i] = nco_code_init(urand() * 1023.0, 18, ci, 1023); hs[i] = ci; hw[i] = 1023.0; hc[i] = 16396 + (int)(urand() * 20);
-        } else if (m == 3) {     /* code, 2.048 MS/s and G1 */
-            const int len = (urand() < 0.5) ? 1023 : 511;
-            const double ci = (1.0 / 2.048e6) * ((len == 1023 ? 1.023e6 : 0.511e6) + (urand() - 0.5) * 20.0);
-            hx[i] = nco_code_init(urand() * len, 4, ci, len); hs[i] = ci; hw[i] = (double)len; hc[i] = 2048 + (int)(urand() * 20);
-        } else {                 /* short mantissas: exact ties in many binades, negative steps, zero */
-            double st = ldexp(floor(urand() * 4096.0) + 0.5, -(int)(urand() * 12));
-            if (urand() < 0.3) st = -st;
-            if (urand() < 0.05) st = 0.0;
-            hx[i] = ldexp(floor(urand() * 65536.0), -(int)(urand() * 20)); hs[i] = st; hw[i] = 0.0; hc[i] = 3000 + (int)(urand() * 3000);
-        }
-    }
-    double *dx = NULL, *dxe = NULL; int *dc = NULL, *dns = NULL; nco_iseg_t *dseg = NULL;
-    int rc = SDRB200_OK, bad = 0;
-    if (cudaMalloc(&dx, sizeof(double) * n * 3) != cudaSuccess || cudaMalloc(&dxe, sizeof(double) * n) != cudaSuccess ||
-        cudaMalloc(&dc, sizeof(int) * n) != cudaSuccess || cudaMalloc(&dns, sizeof(int) * n) != cudaSuccess ||
-        cudaMalloc(&dseg, sizeof(nco_iseg_t) * TRK_MAXSEG * (size_t)n) != cudaSuccess) rc = SDRB200_ENOMEM;
-    nco_iseg_t *hseg = (nco_iseg_t *)malloc(sizeof(nco_iseg_t) * TRK_MAXSEG * (size_t)n);
-    int *hns = (int *)malloc(sizeof(int) * n);
-    double *hxe = (double *)malloc(sizeof(double) * n);
-    if (rc == SDRB200_OK) {
-        cudaMemcpy(dx, hx, sizeof(double) * n * 3, cudaMemcpyHostToDevice);
-        cudaMemcpy(dc, hc, sizeof(int) * n, cudaMemcpyHostToDevice);
-        k_nco_selftest<<<n, 32>>>(dx, dx + n, dc, dx + 2 * n, dseg, dns, dxe);
-        sdrb200_count_launch(1);
-        if (cudaDeviceSynchronize() != cudaSuccess) { sdrb200_set_error("nco_selftest: %s", cudaGetErrorString(cudaGetLastError())); rc = SDRB200_ECUDA; }
-        cudaMemcpy(hseg, dseg, sizeof(nco_iseg_t) * TRK_MAXSEG * (size_t)n, cudaMemcpyDeviceToHost);
-        cudaMemcpy(hns, dns, sizeof(int) * n, cudaMemcpyDeviceToHost);
-        cudaMemcpy(hxe, dxe, sizeof(double) * n, cudaMemcpyDeviceToHost);
-    }
-    for (int i = 0; i < n && rc == SDRB200_OK; i++) {
-        static nco_iseg_t ref[NCO_MAXSEG];
-        double xe;
-        const int nr = nco_walk_i(hx[i], hs[i], hc[i], hw[i], ref, NCO_MAXSEG, &xe);
-        const nco_iseg_t *g = hseg + (size_t)i * TRK_MAXSEG;
-        int a = 0, b = 0, miss = 0;
-        if (nr < 0 || hns[i] < 0 || hns[i] > TRK_MAXSEG) { bad += (nr < 0 && hns[i] < 0) ? 0 : 1; continue; }
-        if (memcmp(&xe, &hxe[i], sizeof(double)) != 0) miss = 1;
-        for (int k = 0; k < hc[i] && !miss; k++) {
-            while (a + 1 < nr && ref[a + 1].k0 <= k) a++;
-            while (b + 1 < hns[i] && g[b + 1].k0 <= k) b++;
-            if (nco_iseg_trunc(&ref[a], k) != nco_iseg_trunc(&g[b], k)) miss = 1;
-        }
-        bad += miss;
-    }
-    cudaFree(dx); cudaFree(dxe); cudaFree(dc); cudaFree(dns); cudaFree(dseg);
-    free(hx); free(hc); free(hseg); free(hns); free(hxe);
-    *mismatches = bad;
-    return rc;
-}

@@ -5,10 +5,10 @@ import ctypes as C
 
 import numpy as np
 
-from . import (AcqCfg, AcqResult, Error, IfgenCfg, IfgenSat, Loop, TrkChan, TrkRec,  # noqa: F401
+from . import (AcqCfg, AcqResult, Error, Loop, TrkChan, TrkRec,  # noqa: F401
                MAXCORRN, MAXTAPS, check, lib)
 
-__all__ = ["gencode", "gencode_device", "make_ifgen", "ifgen_host", "correlator", "mixcarr", "rescode",
+__all__ = ["gencode", "gencode_device", "correlator", "mixcarr", "rescode",
            "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition", "checkacquisition_noalloc",
            "Stream", "Acquisition", "Tracking", "device_count", "launch_count", "make_trk_chan"]
 
@@ -49,26 +49,6 @@ def gencode_device(prns, ctype: int = 1) -> np.ndarray:
     ln = lib.sdrb200_gencode_device(n, arr, int(ctype), _p(out, _i8p), 1023)
     check(ln if ln < 0 else 0, "gencode_device")
     return out[:, :ln]
-
-
-def make_ifgen(f_sf, f_if, f_cf, dtype, sats, sigma=24.0, seed=0xB2000000,
-               crate=1.023e6, clen=1023, bitlen=20) -> IfgenCfg:
-    """sats: list of dicts(prn, cn0, doppler, rate, code_phase, carr_phase, nav_on, nav_seed)."""
-    c = IfgenCfg()
-    c.f_sf, c.f_if, c.f_cf, c.crate, c.sigma = f_sf, f_if, f_cf, crate, sigma
-    c.dtype, c.clen, c.bitlen, c.nsat, c.seed = dtype, clen, bitlen, len(sats), seed
-    for i, s in enumerate(sats):
-        c.sat[i] = IfgenSat(prn=s["prn"], nav_on=s.get("nav_on", 1), cn0_dbhz=s["cn0"],
-                            doppler_hz=s["doppler"], doppler_rate=s.get("rate", 0.0),
-                            code_phase=s["code_phase"], carr_phase=s.get("carr_phase", 0.0),
-                            nav_seed=s.get("nav_seed", 1000 + s["prn"]))
-    return c
-
-
-def ifgen_host(cfg: IfgenCfg, k0: int, n: int) -> np.ndarray:
-    out = np.empty(n * cfg.dtype, np.int8)
-    check(lib.sdrb200_ifgen_host(C.byref(cfg), C.c_uint64(k0), C.c_uint64(n), _p(out, _i8p)), "ifgen_host")
-    return out
 
 
 # ------------------------------------------------------ single-call primitives
@@ -195,8 +175,9 @@ class Stream:
                                                   C.c_uint64(len(host) // 2 if int(fmt) == 1 else len(host)), int(fmt)),
               "push_packed")                      # FMT_RTLSDR: two bytes (I, Q) per sample
 
-    def push_ifgen(self, cfg: IfgenCfg, n: int) -> None:
-        check(lib.sdrb200_stream_push_ifgen(self.h, C.byref(cfg), C.c_uint64(n)), "push_ifgen")
+    def push_device(self, d_ptr: int, n: int) -> None:
+        """n samples that are already in device memory at address d_ptr (device-to-device append)."""
+        check(lib.sdrb200_stream_push_device(self.h, C.c_void_p(d_ptr), C.c_uint64(n)), "push_device")
 
     @property
     def count(self) -> int:

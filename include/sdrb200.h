@@ -48,9 +48,6 @@ void sdrb200_evt_destroy(void *evt);
 int  sdrb200_evt_record(void *evt, void *cuda_stream);
 int  sdrb200_evt_elapsed_ms(void *start, void *stop, float *ms);  /* waits for stop */
 int  sdrb200_l2_flush(void *cuda_stream);
-/* issue-rate micro-benchmark for the ALU rooflines: kind 0 fp32 FMA, kind 1 int32
- * multiply-add; operations per second, one FMA / MAD counted as 2 operations   */
-int  sdrb200_alu_peak(int kind, double *ops_per_s);
 int  sdrb200_device_sync(void);
 
 /* code types: same numeric values as the reference (src/sdr.h:205-212)      */
@@ -68,14 +65,6 @@ int sdrb200_gencode(int prn, int ctype, int8_t *code, double *crate);
  * combined by the CTA): codes [n][stride] in HOST memory, stride >= 1023.  Returns the code
  * length (1023 or 511).                                                                    */
 int sdrb200_gencode_device(int n, const int *prn, int ctype, int8_t *codes, int stride);
-
-/* ------------------------------------------------------- synthetic front end
- * The reference has no IF data in-tree; see csrc/ifgen.h for the model.
- * cfg is an ifgen_cfg_t (csrc/ifgen.h); passed as void* to keep this header
- * free of the generator's types.  k0 = first sample index, n = samples.      */
-int sdrb200_ifgen_host(const void *ifgen_cfg, uint64_t k0, uint64_t n, int8_t *out);
-int sdrb200_ifgen_device(const void *ifgen_cfg, uint64_t k0, uint64_t n, void *d_out,
-                         void *cuda_stream);
 
 /* --------------------------------------------------------- device IF stream
  * Device-resident counterpart of the reference's ring buffer sdrstat.buff and
@@ -99,8 +88,10 @@ int  sdrb200_stream_push_host_rtlsdr(sdrb200_stream_t *s, const uint8_t *host, u
 #define SDRB200_FMT_GN3S_2BIT   4   /* GN3S v3 modes 32/38      -> dtype 1 */
 #define SDRB200_FMT_GN3S_4BIT   5   /* GN3S v3 modes 36/42, I/Q -> dtype 2 */
 int  sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_t *host, uint64_t n, int format);
-/* append n samples produced on the device by the synthetic front end         */
-int  sdrb200_stream_push_ifgen(sdrb200_stream_t *s, const void *ifgen_cfg, uint64_t n);
+/* append n samples that are already in DEVICE memory (produced by another kernel or
+ * written by a DMA engine); no counterpart in the reference, whose front ends fill a
+ * host ring (src/sdrrcv.c:300-404)                                            */
+int  sdrb200_stream_push_device(sdrb200_stream_t *s, const int8_t *d_src, uint64_t n);
 uint64_t sdrb200_stream_count(const sdrb200_stream_t *s);  /* samples pushed   */
 /* copy n samples starting at absolute index `buffloc` back to the host
  * (the rcvgetbuff contract)                                                   */
@@ -243,9 +234,6 @@ int  sdrb200_trk_set_cluster(sdrb200_trk_t *eng, int cluster_size, int ctrl_work
 /* phase profile of channel 0 (clock cycles summed over the last run): go, NCO
  * tables, table conversion, wipe-off + prefix sums, tap sums, epilogue, periods */
 int  sdrb200_trk_profile(sdrb200_trk_t *eng, int on, long long *out7);
-/* self-test of the device NCO walk against the host walker on n random cases
- * (mode 0-4, or -1 for a mix); *mismatches = cases that differ                 */
-int  sdrb200_nco_selftest(int n, unsigned long long seed, int mode, int *mismatches);
 
 /* ------------------------------------------- single-call primitives (host I/O)
  * Same argument meaning as the reference functions named; buffers are HOST

@@ -16,7 +16,8 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def sdr():
     import sdrb200_pkg
-    return sdrb200_pkg.load()
+    import testkit
+    return testkit.attach(sdrb200_pkg.load())
 
 
 @pytest.fixture(scope="session")

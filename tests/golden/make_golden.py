@@ -27,7 +27,8 @@ REC_FIELDS = ["cnt", "buffloc", "currnsamp", "flagsync", "flagloopfilter", "swsy
 
 
 def main():
-    sdr = sdrb200_pkg.load()
+    import testkit
+    sdr = testkit.attach(sdrb200_pkg.load())
     o = ob.ref()
     assert o.name == "reference"
     rng = np.random.default_rng(0xB200)

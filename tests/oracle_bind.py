@@ -93,6 +93,15 @@ class Oracle:
         assert rc == 0, f"oh_acquire rc={rc}"
         return list(out), power
 
+    def fft_seconds(self, reset=True):
+        """seconds spent inside the FFT shim's fftwf_execute_dft in this process (reference builds
+        only; None for the port, which calls its FFT directly)."""
+        f = getattr(self.lib, "oracle_fft_seconds", None)
+        if f is None:
+            return None
+        f.restype = C.c_double
+        return float(f(1 if reset else 0))
+
     def acq_track(self, cfg, if_data, avail, prns, nperiods, ctypes=None, threaded=False):
         """threaded=True: one pthread per channel (oh_acq_track_mt, replay builds only)"""
         if_data = np.ascontiguousarray(if_data, np.int8)

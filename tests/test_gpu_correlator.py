@@ -76,11 +76,10 @@ def test_device_nco_walk_matches_host_walker(sdr):
     """the device NCO walk of the tracking kernel (device arithmetic) against the host walker (which
     tests/test_nco_exact.py fuzzes against the literal loops of src/sdrcmn.c:608-668):
     carriers, codes with wrap, tie-heavy short mantissas, negative and zero steps."""
-    import ctypes as C
+    import testkit
     for mode in (0, 1, 2, 3, 4, -1):
-        bad = C.c_int(-1)
-        sdr.check(sdr.lib.sdrb200_nco_selftest(3000, C.c_ulonglong(0xB200 + mode + 7), mode, C.byref(bad)), "nco_selftest")
-        assert bad.value == 0, (mode, bad.value)
+        bad = testkit.nco_selftest(3000, 0xB200 + mode + 7, mode)
+        assert bad == 0, (mode, bad)
 
 
 def test_packed_front_end_formats_on_device(sdr, oracle):

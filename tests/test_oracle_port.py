@@ -115,7 +115,8 @@ def test_port_equals_reference_build(port):
             assert all(np.array_equal(np.asarray(x), np.asarray(y)) for x, y in zip(r, p))
     # a short closed-loop run through acquisition, bit sync pre-phase and the loop filters
     import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
+    import testkit
+    sdr = testkit.attach(sdrb200_pkg.load())
     cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000099)
     nper = 4800                                   # past bit sync: setobsdata runs (flagobs)
     host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
@@ -132,7 +133,8 @@ def test_port_observables_golden(port):
     records; the IF is regenerated from the seeded generator and pinned by its CRC."""
     import zlib
     import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
+    import testkit
+    sdr = testkit.attach(sdrb200_pkg.load())
     g = np.load(os.path.join(G, "obs_c5.npz"))
     prns, nper, k0 = [int(p) for p in g["prns"]], int(g["nper"]), int(g["k0"])
     cfg, vis = util.scene_c5(sdr, nsats=2, seed=0xB2000026)
@@ -161,11 +163,12 @@ def test_port_ingest_golden(port):
 def test_port_frame_sync_equals_reference_build(port):
     """findpreamble + paritycheck + paritycheck_l1ca (src/sdrnav.c:324-411, src/sdrnav_gps.c:141-166)
     and the polarity term of setobsdata (src/sdrtrk.c:186-195): IF with LNAV subframes
-    (csrc/ifgen.h nav_on = 2), port against the reference build, bit for bit."""
+    (tests/testkit/ifgen.h nav_on = 2), port against the reference build, bit for bit."""
     if not ob.have_ref():
         pytest.skip("reference build absent (GPU box): the GPU test compares with the port there")
     import sdrb200_pkg
-    sdr = sdrb200_pkg.load()
+    import testkit
+    sdr = testkit.attach(sdrb200_pkg.load())
     ref = ob.ref()
     rng = np.random.default_rng(5)
     prns = [2, 5]
