@@ -395,27 +395,31 @@ def run_b200(args):
     res_ptr = C.cast(res_pin.data_ptr(), C.POINTER(sdr.AcqResult))
     host_ptr = C.cast(host_pin.data_ptr(), C.POINTER(C.c_int8))
     if dist is not None:
-        res_dev = torch.empty(rbytes, dtype=torch.uint8, device="cuda")
-        res_all = torch.empty(world * rbytes, dtype=torch.uint8, device="cuda")
+        # the per-step tuples also stay in a device ring [K][nprn]; ONE all-gather per K steps takes
+        # them from device memory (round 1 bounced every step's tuples host -> device and gathered
+        # them per 0.33 ms step, which cost 25 % at N = 8)
+        res_ring = torch.empty((max(K, 3), rbytes), dtype=torch.uint8, device="cuda")
+        res_all = torch.empty((world, max(K, 3), rbytes), dtype=torch.uint8, device="cuda")
 
-    def e2e_step():
-        sdr.check(lib.sdrb200_acq_run_host(acq.h, host_ptr, C.c_uint64(need), res_ptr), "acq_run_host")
+    def e2e_steps(nsteps):
+        for i in range(nsteps):
+            sdr.check(lib.sdrb200_acq_run_host(acq.h, host_ptr, C.c_uint64(need), res_ptr), "acq_run_host")
+            if dist is not None:
+                acq.copy_results_device(res_ring[i].data_ptr())
         if dist is not None:
-            res_dev.copy_(res_pin, non_blocking=True)
-            dist.all_gather_into_tensor(res_all, res_dev)
+            acq.sync()
+            dist.all_gather_into_tensor(res_all.view(-1), res_ring.view(-1))
             torch.cuda.synchronize()
 
-    for _ in range(max(W, 3)):
-        e2e_step()
+    e2e_steps(3)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(K):
-        e2e_step()
+    e2e_steps(K)
     barrier()
     t_e2e = time.perf_counter() - t0
     r2 = acq._results((sdr.AcqResult * NPRN).from_buffer_copy(bytes(res_pin.numpy())))
     if dist is not None:
-        mine = res_all.cpu().numpy()[rank * rbytes:(rank + 1) * rbytes]
+        mine = res_all[rank, K - 1].cpu().numpy()
         assert bytes(mine) == bytes(res_pin.numpy()), "gathered tuples differ from the local shard"
     assert [(r["acquired"], r["freqi"], r["codei"]) for r in r2] == \
            [(r["acquired"], r["freqi"], r["codei"]) for r in res], "host-buffer path disagrees with resident path"
@@ -718,6 +722,158 @@ def run_b200(args):
                               "model": "SURVEY 8(d): IF + code-spectrum bank + power matrix read/write per step"},
                       "l2": "flushed before every timed run", "peak_bins": [r["freqi"] for r in r4[:4]]}
             acq4.close()
+    # ------------------------------------------------ the partition north_star names: ONE search over N GPUs
+    # (a) strong scaling: BASELINE configs[3] at its full size - 51 PRN (GPS 1-32 + SBAS 120-138) x 141 bins
+    #     (100 Hz) x 327 360 lags (20 ms coherent, M = 2^20) x 10 non-coherent steps with the reference's
+    #     early exit - split by PRN slab; every rank searches the SAME IF stream; the tuples are gathered
+    #     ONCE per search from device memory (sdrb200_acq_results_device) with one NCCL all-gather.
+    # (b) Doppler slabs for PRNs < GPUs: 4 PRN x 71 bins, 4 integrations, bins split over the ranks,
+    #     per-step histories gathered once, early exit replayed (shard.merge_doppler_slabs).
+    strong_obj = dslab_obj = None
+    if args.strong_prns > 0:
+        ncoh4, nf4, intg4 = 20, 141, args.strong_steps
+        n4 = ncoh4 * NSAMP
+        tot4 = (intg4 + 1) * n4 + 65536
+        prns4 = (list(range(1, 33)) + list(range(120, 139)))[:args.strong_prns]
+        rng4 = np.random.default_rng(0xB2000400)
+        sats4 = [dict(prn=p_, cn0=float(c_), doppler=float(int(rng4.integers(-60, 61)) * 100.0 + rng4.uniform(-20, 20)),
+                      code_phase=float(rng4.uniform(0, 1023 * 20)), carr_phase=float(rng4.uniform(0, 1)), rate=0.0, nav_on=0)
+                 for p_, c_ in ((3, 42.0), (11, 38.0), (17, 45.0), (25, 33.0), (31, 36.0), (133, 40.0), (122, 34.0)) if p_ in prns4]
+        st4 = sdr.Stream(1, tot4)
+        st4.push_ifgen(sdr.make_ifgen(FS, F_IF, F_CF, 1, sats4, sigma=24.0, seed=0xB2000400), tot4)     # same stream on every rank
+        freq4 = np.array([F_IF + (i - nf4 // 2) * 100.0 for i in range(nf4)])
+        mine4 = sdr.shard.prn_slab(prns4, rank, world)
+        width4 = -(-len(prns4) // world)
+        rb = C.sizeof(sdr.AcqResult)
+        plan4 = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq4,
+                                np.stack([sdr.gencode(p_)[0] for p_ in mine4]), 1.023e6, intg=intg4, ncoh=ncoh4) if mine4 else None
+        loc4 = torch.zeros(width4 * rb, dtype=torch.uint8, device="cuda")
+        all4 = torch.zeros(world * width4 * rb, dtype=torch.uint8, device="cuda")
+        s4s = plan4.cuda_stream if plan4 else 0
+
+        def strong_search():
+            if plan4:
+                plan4.enqueue(st4, 0)
+                plan4.copy_results_device(loc4.data_ptr())
+                plan4.sync()
+            if dist is not None:
+                dist.all_gather_into_tensor(all4, loc4)
+                torch.cuda.synchronize()
+
+        strong_search()                                      # warm
+        t_s, t_k = [], []
+        for _ in range(2):
+            if plan4: sdr.check(lib.sdrb200_l2_flush(C.c_void_p(s4s)), "l2_flush")
+            barrier()
+            t0 = time.perf_counter()
+            if plan4: e0.record(s4s)
+            strong_search()
+            if plan4: e1.record(s4s)
+            barrier()
+            t_s.append(time.perf_counter() - t0)
+            t_k.append(e1.ms_since(e0) if plan4 else 0.0)
+        ts4 = min(t_s)
+        if dist is not None:
+            tt = torch.tensor([ts4], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            ts4 = float(tt[0])
+            gathered = all4.cpu().numpy().reshape(world, width4 * rb)
+            merged4 = []
+            for r_ in range(world):
+                n_r = len(sdr.shard.prn_slab(prns4, r_, world))
+                merged4 += sdr.Acquisition.results_from_bytes(gathered[r_, :n_r * rb])
+        else:
+            merged4 = sdr.Acquisition.results_from_bytes(loc4.cpu().numpy()[:len(mine4) * rb])
+        if plan4: plan4.close()
+        eq4 = None
+        if rank == 0 and world > 1:
+            # the unsharded search on rank 0, outside the clock: the merged tuples must equal it exactly
+            whole4 = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq4,
+                                     np.stack([sdr.gencode(p_)[0] for p_ in prns4]), 1.023e6, intg=intg4, ncoh=ncoh4)
+            want4 = whole4.run(st4, 0)
+            whole4.close()
+            if want4 != merged4:
+                raise SystemExit("bench.py: PRN-slab search differs from the unsharded search")
+            eq4 = True
+        steps_run = max(m_["nintg"] for m_ in merged4)
+        strong_obj = {"workload": f"ONE search, {len(prns4)} PRN (GPS 1-32 + SBAS 120-138) x {nf4} bins (100 Hz) x {n4} lags, "
+                                  f"{ncoh4} ms coherent (M = 2^20), up to {intg4} non-coherent steps with early exit (BASELINE configs[3])",
+                      "scaling": "strong", "partition": "PRN slabs, one NCCL all-gather of the tuples per search from device memory",
+                      "n_gpus": world, "prns_per_gpu": [len(sdr.shard.prn_slab(prns4, r_, world)) for r_ in range(world)],
+                      "ms_per_search": ts4 * 1e3, "ms_search_kernels_this_rank": min(t_k),
+                      "cells_per_s": len(prns4) * nf4 * n4 * steps_run / ts4, "integration_steps_run": steps_run,
+                      "acquired_prns": [p_ for p_, m_ in zip(prns4, merged4) if m_["acquired"]],
+                      "note_acquired": "checkacquisition's +-2-chip exclusion (src/sdracq.c:78-83) does not cover the code-period "
+                                       "replicas of the peak inside a 20 ms block, so the peak ratio stays near 1 at this size; "
+                                       "the decisions that are compared are (freqi, codei, maxp)",
+                      "found_bins": {str(p_): [m_["freqi"], m_["codei"] % NSAMP] for p_, m_ in zip(prns4, merged4)
+                                     if p_ in (3, 11, 17, 25, 31, 133, 122)},
+                      "true_bins": {str(s_["prn"]): int(round(s_["doppler"] / 100.0)) + nf4 // 2 for s_ in sats4},
+                      "merged_equals_unsharded": eq4,
+                      "hbm_model_bytes": len(prns4) * nf4 * n4 * 4 * (2 * steps_run - 1),
+                      "hbm_frac": len(prns4) * nf4 * n4 * 4 * (2 * steps_run - 1) / ts4 / 1e9 / (hbm_peak * world)}
+        st4.close()
+        if world > 1:
+            prnsd = [1, 3, 11, 2]                             # fewer PRNs than GPUs: the Doppler grid is what shards
+            intgd = 4
+            bd = sdr.shard.doppler_slab(NFREQ, rank, world)
+            codesd = np.stack([sdr.gencode(p_)[0] for p_ in prnsd])
+            bd0 = AVAIL10 - (intgd + 1) * NSAMP
+            rbh = intgd * len(prnsd) * rb
+            loch = torch.zeros(rbh, dtype=torch.uint8, device="cuda")
+            allh = torch.zeros(world * rbh, dtype=torch.uint8, device="cuda")
+            pland = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq[bd.start:bd.stop], codesd, 1.023e6,
+                                    intg=intgd, threshold=1e30) if len(bd) else None
+            if pland: pland.set_history(True)
+            # every rank holds the same scene in `st` only at N = 1; here each rank has its own stream, so the
+            # slab search runs on a common stream made for it
+            std = sdr.Stream(1, AVAIL10 + 65536)
+            std.push_ifgen(scene(sdr, 0xB2000000), AVAIL10 + 65536)
+
+            def dslab_search():
+                if pland:
+                    pland.enqueue(std, bd0)
+                    pland.sync()
+                    loch.copy_(torch.as_tensor(pland.history_device(intgd), device="cuda"))
+                dist.all_gather_into_tensor(allh, loch)
+                torch.cuda.synchronize()
+
+            dslab_search()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(K):
+                dslab_search()
+            barrier()
+            td = (time.perf_counter() - t0) / K
+            tt = torch.tensor([td], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            td = float(tt[0])
+            gh = allh.cpu().numpy().reshape(world, rbh)
+            hists, offs = [], []
+            for r_ in range(world):
+                b_ = sdr.shard.doppler_slab(NFREQ, r_, world)
+                if len(b_) == 0:
+                    continue
+                flat = sdr.Acquisition.results_from_bytes(gh[r_])
+                hists.append([flat[i * len(prnsd):(i + 1) * len(prnsd)] for i in range(intgd)])
+                offs.append(b_.start)
+            mergedd = sdr.shard.merge_doppler_slabs(hists, offs, NSAMP, 3.0)
+            eqd = None
+            if rank == 0:
+                wholed = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq, codesd, 1.023e6, intg=intgd)
+                wantd = wholed.run(std, bd0)
+                wholed.close()
+                keys = ("acquired", "freqi", "codei", "nintg", "acqfreq", "peakr", "cn0", "maxp", "maxp2")
+                if [[m_[k_] for k_ in keys] for m_ in mergedd] != [[w_[k_] for k_ in keys] for w_ in wantd]:
+                    raise SystemExit("bench.py: Doppler-slab search differs from the unsharded search")
+                eqd = True
+            if pland: pland.close()
+            std.close()
+            dslab_obj = {"workload": f"ONE search, {len(prnsd)} PRN x {NFREQ} bins x {NSAMP} lags, {intgd} integrations, bins split over the GPUs",
+                         "scaling": "strong", "partition": "Doppler slabs, per-step tuples gathered once per search (device memory), early exit replayed",
+                         "n_gpus": world, "bins_per_gpu": [len(sdr.shard.doppler_slab(NFREQ, r_, world)) for r_ in range(world)],
+                         "ms_per_search": td * 1e3, "cells_per_s": len(prnsd) * NFREQ * NSAMP * intgd / td,
+                         "merged_equals_unsharded": eqd}
     clk = clocks.stop()
 
     # ------------------------------------------------ reduce over ranks, print
@@ -763,6 +919,8 @@ def run_b200(args):
         "tracking": trk_obj,
         "streams_c5": streams_obj,
         "coherent_c4": c4_obj,
+        "strong_scaling_c4": strong_obj,
+        "doppler_slabs": dslab_obj,
     }
     if rank == 0:
         emit(line)
@@ -852,7 +1010,9 @@ def main():
     ap.add_argument("--no-trk", action="store_true", help="skip the tracking half")
     ap.add_argument("--c5-streams", type=int, default=8, help="config-5 style independent streams per GPU (0: skip)")
     ap.add_argument("--c5-seconds", type=float, default=4.0)
-    ap.add_argument("--c4-prns", type=int, default=16, help="config-4 style 20 ms coherent search over this many PRNs (0: skip)")
+    ap.add_argument("--c4-prns", type=int, default=0, help="config-4 style 20 ms coherent search over this many PRNs (0: skip)")
+    ap.add_argument("--strong-prns", type=int, default=51, help="strong-scaling search (BASELINE configs[3]) over this many PRNs (0: skip)")
+    ap.add_argument("--strong-steps", type=int, default=10, help="non-coherent steps of the strong-scaling search")
     ap.add_argument("--no-sweep", action="store_true", help="skip the tracking channel-count sweep")
     ap.add_argument("--trk-profile", action="store_true", help="add the per-phase cycle profile of channel 0")
     args = ap.parse_args()

@@ -63,6 +63,7 @@ struct sdrb200_acq {
     unsigned long long *d_key;       /* [nprn] argmax keys (fused path)       */
     int fused, keep_power;
     sdrb200_acq_result_t *d_res, *h_res;
+    sdrb200_acq_result_t *d_hist;    /* [intg][nprn] tuples after every integration step (Doppler-slab searches) */
     int *d_frozen;
     double *d_freq;
     int8_t *d_hostwin; size_t hostwin_cap;   /* staging for run_host          */
@@ -1075,7 +1076,7 @@ extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
 {
     if (!a) return;
     cudaFree(a->d_tw); cudaFree(a->d_cidx); cudaFree(a->d_Xs); cudaFree(a->d_Cs); cudaFree(a->d_S);
-    cudaFree(a->d_P); cudaFree(a->d_row); cudaFree(a->d_key); cudaFree(a->d_res); cudaFree(a->d_frozen); cudaFree(a->d_freq);
+    cudaFree(a->d_P); cudaFree(a->d_row); cudaFree(a->d_key); cudaFree(a->d_res); cudaFree(a->d_hist); cudaFree(a->d_frozen); cudaFree(a->d_freq);
     cudaFree(a->d_hostwin);
     if (a->h_res) cudaFreeHost(a->h_res);
     if (a->h_pin) cudaFreeHost(a->h_pin);
@@ -1307,6 +1308,9 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
             rc = launch_rowc_any(a->L, a->R, 1, a->st, A, 1, c->nprn);
             if (rc) return rc;
             ACQ_T1(a, 3);
+            if (a->d_hist)
+                SDRB200_CUDA_TRY(cudaMemcpyAsync(a->d_hist + (size_t)step * c->nprn, a->d_res, sizeof(sdrb200_acq_result_t) * c->nprn,
+                                                 cudaMemcpyDeviceToDevice, a->st));
             continue;
         }
         /* scratch path: sub-transforms of a chunk of rows go through d_S (sized to stay in L2),
@@ -1349,6 +1353,9 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         sdrb200_count_launch(1);
         SDRB200_CUDA_TRY(cudaGetLastError());
         ACQ_T1(a, 3);
+        if (a->d_hist)
+            SDRB200_CUDA_TRY(cudaMemcpyAsync(a->d_hist + (size_t)step * c->nprn, a->d_res, sizeof(sdrb200_acq_result_t) * c->nprn,
+                                             cudaMemcpyDeviceToDevice, a->st));
     }
     return SDRB200_OK;
 }
@@ -1374,6 +1381,49 @@ extern "C" int sdrb200_acq_fetch(sdrb200_acq_t *a, sdrb200_acq_result_t *results
                                      cudaMemcpyDeviceToHost, a->st));
     SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
     memcpy(results, a->h_res, sizeof(sdrb200_acq_result_t) * a->cfg.nprn);
+    return SDRB200_OK;
+}
+
+/* ---- multi-GPU plumbing: results stay on the device until ONE collective gathers them ---- */
+extern "C" const void *sdrb200_acq_results_device(sdrb200_acq_t *a) { return a ? (const void *)a->d_res : NULL; }
+
+extern "C" int sdrb200_acq_copy_results_device(sdrb200_acq_t *a, void *d_dst)
+{
+    if (!a || !d_dst) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(d_dst, a->d_res, sizeof(sdrb200_acq_result_t) * a->cfg.nprn, cudaMemcpyDeviceToDevice, a->st));
+    return SDRB200_OK;
+}
+
+extern "C" int sdrb200_acq_sync(sdrb200_acq_t *a)
+{
+    if (!a) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+    return SDRB200_OK;
+}
+
+/* per-step history: a Doppler SLAB of a search cannot take the reference's early exit by itself
+ * (src/sdracq.c:29-43 tests the peak of the WHOLE grid after every integration), so a slab plan
+ * runs every step (threshold set out of reach by the caller) and keeps the tuple of each step;
+ * the owner of the search replays the early exit over the slabs' histories (shard.merge_doppler_slabs) */
+extern "C" int sdrb200_acq_set_history(sdrb200_acq_t *a, int on)
+{
+    if (!a) return SDRB200_EINVAL;
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+    if (on && !a->d_hist) {
+        const size_t bytes = sizeof(sdrb200_acq_result_t) * (size_t)a->cfg.intg * a->cfg.nprn;
+        if (cudaMalloc((void **)&a->d_hist, bytes) != cudaSuccess) { cudaGetLastError(); sdrb200_set_error("acq_set_history: cudaMalloc failed"); return SDRB200_ENOMEM; }
+        SDRB200_CUDA_TRY(cudaMemset(a->d_hist, 0, bytes));
+    } else if (!on && a->d_hist) { cudaFree(a->d_hist); a->d_hist = NULL; }
+    return SDRB200_OK;
+}
+extern "C" const void *sdrb200_acq_history_device(sdrb200_acq_t *a) { return a ? (const void *)a->d_hist : NULL; }
+extern "C" int sdrb200_acq_fetch_history(sdrb200_acq_t *a, sdrb200_acq_result_t *hist)
+{
+    if (!a || !hist) return SDRB200_EINVAL;
+    if (!a->d_hist) { sdrb200_set_error("acq_fetch_history: history is off (sdrb200_acq_set_history)"); return SDRB200_EINVAL; }
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(hist, a->d_hist, sizeof(sdrb200_acq_result_t) * (size_t)a->cfg.intg * a->cfg.nprn,
+                                     cudaMemcpyDeviceToHost, a->st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
     return SDRB200_OK;
 }
 

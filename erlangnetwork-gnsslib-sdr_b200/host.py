@@ -10,7 +10,7 @@ from . import (AcqCfg, AcqResult, Error, Loop, TrkChan, TrkRec,  # noqa: F401
 
 __all__ = ["gencode", "gencode_device", "correlator", "mixcarr", "rescode",
            "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition", "checkacquisition_noalloc",
-           "Stream", "Acquisition", "Tracking", "device_count", "launch_count", "make_trk_chan"]
+           "Stream", "Acquisition", "Tracking", "DeviceBytes", "device_count", "launch_count", "make_trk_chan"]
 
 _i8p = C.POINTER(C.c_int8)
 _dp = C.POINTER(C.c_double)
@@ -149,6 +149,18 @@ def checkacquisition_noalloc(P, nsamp, nfreq, nsampchip, ctime):
     return dict(cn0=cn0.value, peakr=peakr.value, codei=codei.value, freqi=freqi.value)
 
 
+class DeviceBytes:
+    """A span of device memory owned by the library, exposed through the CUDA array interface
+    so that torch.as_tensor(span, device="cuda") wraps it without a copy (for NCCL)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        if not ptr:
+            raise Error("device buffer not available")
+        self.ptr, self.nbytes = int(ptr), int(nbytes)
+        self.__cuda_array_interface__ = {"shape": (self.nbytes,), "typestr": "|u1", "data": (self.ptr, False),
+                                         "version": 2, "strides": None}
+
+
 # --------------------------------------------------------------- IF stream
 class Stream:
     """Device-resident IF buffer with absolute sample indexing (rcvgetbuff
@@ -248,6 +260,47 @@ class Acquisition:
         res = (AcqResult * self.nprn)()
         check(lib.sdrb200_acq_fetch(self.h, res), "acq_fetch")
         return self._results(res)
+
+    # ---- multi-GPU plumbing: tuples stay in device memory until one collective gathers them
+    RESULT_BYTES = C.sizeof(AcqResult)
+
+    def sync(self):
+        check(lib.sdrb200_acq_sync(self.h), "acq_sync")
+
+    def results_device(self) -> "DeviceBytes":
+        """the [nprn] tuples of the last enqueue, in place in device memory (no copy)."""
+        lib.sdrb200_acq_results_device.restype = C.c_void_p
+        return DeviceBytes(lib.sdrb200_acq_results_device(self.h), self.nprn * self.RESULT_BYTES)
+
+    def copy_results_device(self, d_ptr: int):
+        """enqueue a device-to-device copy of the tuples to caller memory on the plan's stream."""
+        check(lib.sdrb200_acq_copy_results_device(self.h, C.c_void_p(d_ptr)), "acq_copy_results_device")
+
+    def set_history(self, on: bool = True):
+        """keep the tuples of every integration step (Doppler-slab searches)."""
+        self.intg = getattr(self, "intg", None)
+        check(lib.sdrb200_acq_set_history(self.h, int(bool(on))), "acq_set_history")
+
+    def history_device(self, intg: int) -> "DeviceBytes":
+        lib.sdrb200_acq_history_device.restype = C.c_void_p
+        return DeviceBytes(lib.sdrb200_acq_history_device(self.h), intg * self.nprn * self.RESULT_BYTES)
+
+    def fetch_history(self, intg: int):
+        """[intg][nprn] dicts."""
+        arr = (AcqResult * (intg * self.nprn))()
+        check(lib.sdrb200_acq_fetch_history(self.h, arr), "acq_fetch_history")
+        flat = self._results(arr)
+        return [flat[i * self.nprn:(i + 1) * self.nprn] for i in range(intg)]
+
+    @staticmethod
+    def results_from_bytes(buf) -> list:
+        """tuples from raw bytes (a gathered buffer): list of dicts."""
+        raw = bytes(buf)
+        n = len(raw) // C.sizeof(AcqResult)
+        arr = (AcqResult * n).from_buffer_copy(raw)
+        return [dict(acquired=r.acquired, freqi=r.freqi, codei=r.codei, nintg=r.nintg,
+                     acqfreq=r.acqfreq, peakr=r.peakr, cn0=r.cn0, maxp=r.maxp, maxp2=r.maxp2,
+                     meanp=r.meanp) for r in arr]
 
     def power(self, prn_index: int) -> np.ndarray:
         out = np.zeros(self.nfreq * self.n_eff)

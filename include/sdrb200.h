@@ -143,6 +143,22 @@ int  sdrb200_acq_run_host(sdrb200_acq_t *plan, const int8_t *host_if, uint64_t n
 int  sdrb200_acq_enqueue(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t buffloc0);
 int  sdrb200_acq_fetch(sdrb200_acq_t *plan, sdrb200_acq_result_t *results);
 void *sdrb200_acq_cuda_stream(sdrb200_acq_t *plan);
+/* Multi-GPU plumbing (north_star: PRN / Doppler slabs per GPU, NCCL only to gather the
+ * per-shard peak tuples; rows of pcorrelator are independent, src/sdrcmn.c:759-768, the
+ * per-PRN reduction is checkacquisition, src/sdracq.c:71-95).
+ * results_device: the [nprn] tuples of the last enqueue in DEVICE memory (valid once the
+ * plan's stream has passed them), so that one collective can gather them without a host
+ * bounce; copy_results_device enqueues a copy into caller memory on the plan's stream.  */
+const void *sdrb200_acq_results_device(sdrb200_acq_t *plan);
+int  sdrb200_acq_copy_results_device(sdrb200_acq_t *plan, void *d_dst);
+int  sdrb200_acq_sync(sdrb200_acq_t *plan);
+/* Doppler slabs: a plan that holds only some bins of the grid cannot take the early exit of
+ * sdracquisition (src/sdracq.c:29-43 tests the peak of the WHOLE grid after every
+ * integration).  With history on the plan keeps the tuples of every step [intg][nprn];
+ * the caller sets cfg.threshold out of reach and replays the early exit over all slabs.  */
+int  sdrb200_acq_set_history(sdrb200_acq_t *plan, int on);
+const void *sdrb200_acq_history_device(sdrb200_acq_t *plan);
+int  sdrb200_acq_fetch_history(sdrb200_acq_t *plan, sdrb200_acq_result_t *hist);
 /* per-kernel CUDA-event timing of the enqueued launches; kernel classes:
  * 0 forward (wipe-off + FFT), 1 row search (spectrum product, inverse FFT,
  * power, argmax), 2 combine (scratch path only, windows > 8 sub-transforms),

@@ -180,6 +180,42 @@ def test_acq_glonass_g1_fdma(sdr):
     assert [r.acquired for r in ref] == [1, 1, 1, 0]
 
 
+def test_acq_doppler_slabs_equal_unsharded(sdr):
+    """SURVEY 8e, fewer PRNs than GPUs: the Doppler grid is cut into slabs, every slab plan runs all
+    integration steps and keeps its per-step tuples, and shard.merge_doppler_slabs replays
+    checkacquisition's argmax over the whole grid (src/sdracq.c:76-88) and sdracquisition's early exit
+    (src/sdracq.c:29-43).  Must equal the unsharded search exactly (every field), for 2, 3 and 4
+    slabs, with signals that are acquired after different numbers of integrations."""
+    cfg, vis = util.scene_c1(sdr, nsats=4, seed=0xB2000011)
+    for i in range(cfg.nsat):
+        cfg.sat[i].cn0_dbhz = 40.0 + 1.5 * i
+    prns = vis + [8]
+    nsamp, intg = 16368, 4
+    avail = 65536 * 2
+    st = sdr.Stream(1, avail)
+    st.push_ifgen(cfg, avail)
+    freq = np.array([util.IF1 + (i - 35) * 200.0 for i in range(71)])
+    codes = np.stack([sdr.gencode(p)[0] for p in prns])
+    b0 = avail - (intg + 1) * nsamp
+    whole = sdr.Acquisition(util.FS1, 1, nsamp, 16, 1e-3, freq, codes, 1.023e6, intg=intg)
+    want = whole.run(st, b0)
+    assert len({w["nintg"] for w in want}) > 1                     # the early exit is exercised
+    for world in (2, 3, 4):
+        hists, offs = [], []
+        for r in range(world):
+            b = sdr.shard.doppler_slab(len(freq), r, world)
+            plan = sdr.Acquisition(util.FS1, 1, nsamp, 16, 1e-3, freq[b.start:b.stop], codes, 1.023e6, intg=intg, threshold=1e30)
+            plan.set_history(True)
+            plan.enqueue(st, b0)
+            hists.append(plan.fetch_history(intg))
+            offs.append(b.start)
+            plan.close()
+        merged = sdr.shard.merge_doppler_slabs(hists, offs, nsamp, threshold=3.0)     # ACQTH
+        for m, w in zip(merged, want):
+            for k in ("acquired", "freqi", "codei", "nintg", "acqfreq", "peakr", "cn0", "maxp", "maxp2"):
+                assert m[k] == w[k], (world, k, m, w)
+
+
 def test_acq_cluster_exchange_repeatable(sdr):
     """The sub-transforms of a row cross the cluster through distributed shared memory behind
     a CTA barrier, one cluster-scope release fence and a relaxed cluster barrier.  A read that
