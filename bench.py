@@ -664,7 +664,47 @@ def run_b200(args):
             nch5_all, steps5_all = float(tn[0]), float(tn[1])
         else:
             nch5_all, steps5_all = float(nch5), float(steps5)
+        # the whole job of BASELINE configs[4] under ONE clock: acquisition of every stream, hand-over on
+        # the host (tuples out, channel tables in, tracking engines created), tracking of every acquired PRN
+        for e in engines:
+            if e: e.close()
+        barrier()
+        t0 = time.perf_counter()
+        for ak, sk in zip(a5, s5): ak.enqueue(sk, b5)
+        gotf = [ak.fetch() for ak in a5]
+        engf = []
+        for g, sk in zip(gotf, s5):
+            chf = [sdr.make_trk_chan(FS5, 0.0, F_CF, 2, p_, codes5[p_ - 1], b5 + r["codei"], r["acqfreq"],
+                                     4, 1, 1, (5.0, 2.0), (30.0, 20.0), (200.0, 50.0))
+                   for p_, r in zip(range(1, NPRN + 1), g) if r["acquired"]]
+            ef = sdr.Tracking(chf) if chf else None
+            if ef: ef.set_cluster(cl5); ef.enqueue(sk, nper5)
+            engf.append(ef)
+        donef = 0
+        for ef in engf:
+            if ef: ef.sync()
+        barrier()
+        t_full5 = time.perf_counter() - t0
+        for ef, sk in zip(engf, s5):
+            if ef:
+                _, nrf = ef.run(sk, 1, want_records=False)      # one more period: every channel is still alive
+                donef += ef.nch
+        if dist is not None:
+            tt = torch.tensor([t_full5], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t_full5 = float(tt[0])
+            tn2 = torch.tensor([float(donef)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tn2)
+            donef_all = float(tn2[0])
+        else:
+            donef_all = float(donef)
+        engines = engf
         streams_obj = {
+            "full_job": {"what": "acquisition + hand-over + tracking of every stream under one clock (plans and IF resident; "
+                                 "tracking engines are created inside the clock)",
+                         "ms": t_full5 * 1e3, "streams": world * args.c5_streams, "if_seconds_per_stream": T5,
+                         "stream_seconds_per_s": world * args.c5_streams * T5 / t_full5,
+                         "channel_s_per_s": donef_all * nper5 * 1e-3 / t_full5, "channels": donef_all},
             "workload": f"{args.c5_streams} independent I/Q int8 streams per GPU at 2.048 MS/s (BASELINE configs[4] style): "
                         f"32 PRN x 71 bins x 2048 acquisition (10 integrations, early exit) then {T5:g} s tracking "
                         "of every acquired PRN, 9 taps",
@@ -679,6 +719,56 @@ def run_b200(args):
             if e: e.close()
         for ak in a5: ak.close()
         for sk in s5: sk.close()
+    # ------------------------------------------------ BASELINE configs[2]: GLONASS G1 FDMA acquisition
+    # 14 frequency channels (k = -7..6, 562.5 kHz apart) x 101 bins (+-10 kHz / 200 Hz) x 20000 code
+    # phases, I/Q int8 at 20 MS/s (stereo_L1G1 style), 10 non-coherent integrations (M = 65536 =
+    # 8 x 8192: the fused cluster path).  One plan per channel (its own Doppler grid, src/sdrinit.c:633-635),
+    # all enqueued before the first wait.  Parity: tests/test_gpu_headline.py::test_c3_*.
+    c3_obj = None
+    if args.c3:
+        fs3, ns3, nf3, intg3 = 20.0e6, 20000, 101, 10
+        rng3 = np.random.default_rng(0xB2000300 + rank)
+        ks3 = list(range(-7, 7))
+        sats3 = [dict(prn=1, cn0=float(rng3.uniform(46, 50)), doppler=k_ * 562500.0 + float(rng3.uniform(-9000, 9000)),
+                      code_phase=float(rng3.uniform(0, 511 * 10)), carr_phase=float(rng3.uniform(0, 1)), rate=0.0, nav_on=0)
+                 for k_ in (-7, -4, -1, 0, 2, 5, 6)]
+        need3 = (intg3 + 1) * ns3
+        avail3 = 65536 * (need3 // 65536 + 1)
+        st3 = sdr.Stream(2, avail3)
+        st3.push_ifgen(sdr.make_ifgen(fs3, 0.0, 1.602e9, 2, sats3, sigma=2.5, seed=0xB2000300 + rank, crate=0.511e6, clen=511, bitlen=10), avail3)
+        code3, crate3 = sdr.gencode(1, 20)
+        plans3 = [sdr.Acquisition(fs3, 2, ns3, int(ns3 / 511), 1e-3,
+                                  np.array([(i - nf3 // 2) * 200.0 + 562500.0 * k_ for i in range(nf3)]),
+                                  code3[None, :], crate3, intg=intg3, threshold=1e30) for k_ in ks3]   # every step runs
+        b3 = avail3 - need3
+        for _ in range(2):
+            for pl in plans3: pl.enqueue(st3, b3)
+            g3 = [pl.fetch()[0] for pl in plans3]
+        t3 = []
+        for _ in range(3):
+            sdr.check(lib.sdrb200_l2_flush(C.c_void_p(plans3[0].cuda_stream)), "l2_flush")
+            barrier()
+            t0 = time.perf_counter()
+            for pl in plans3: pl.enqueue(st3, b3)
+            for pl in plans3: pl.sync()
+            t3.append(time.perf_counter() - t0)
+        g3 = [pl.fetch()[0] for pl in plans3]
+        t3m = min(t3)
+        if dist is not None:
+            tt = torch.tensor([t3m], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            t3m = float(tt[0])
+        cells3 = world * len(ks3) * nf3 * ns3 * intg3
+        c3_obj = {"workload": f"GLONASS G1 FDMA: {len(ks3)} channels x {nf3} bins x {ns3} code phases x {intg3} integrations, "
+                              "I/Q int8 at 20 MS/s (BASELINE configs[2]); one IF stream per GPU",
+                  "cells_per_s": cells3 / t3m, "ms_per_search": t3m * 1e3,
+                  "peak_ratio_per_channel": {str(k_): round(g_["peakr"], 2) for k_, g_ in zip(ks3, g3)},
+                  "channels_with_signal": [-7, -4, -1, 0, 2, 5, 6],
+                  "hbm": {"model": "SURVEY 8(d): IF + code spectrum + power matrix read/write per step",
+                          "frac": world * len(ks3) * (intg3 * (2 * ns3 * 2 + 65536 * 8) + nf3 * ns3 * 4 * (2 * intg3 - 1)) / t3m / 1e9 / (hbm_peak * world)},
+                  "timing": "host clock around enqueue-all .. sync-all (14 CUDA streams), L2 flushed before"}
+        for pl in plans3: pl.close()
+        st3.close()
     # ------------------------------------------------ config-4 style: long coherent blocks
     # BASELINE configs[3]: weak-signal search, 100 Hz Doppler step (141 bins), 20 ms coherent
     # blocks (n = 327 360 lags, M = 2^20: the two-pass path k_fwd_split/k_fft_rows/k_row/
@@ -919,6 +1009,7 @@ def run_b200(args):
         "tracking": trk_obj,
         "streams_c5": streams_obj,
         "coherent_c4": c4_obj,
+        "glonass_c3": c3_obj,
         "strong_scaling_c4": strong_obj,
         "doppler_slabs": dslab_obj,
     }
@@ -1009,8 +1100,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-trk", action="store_true", help="skip the tracking half")
     ap.add_argument("--c5-streams", type=int, default=8, help="config-5 style independent streams per GPU (0: skip)")
-    ap.add_argument("--c5-seconds", type=float, default=4.0)
+    ap.add_argument("--c5-seconds", type=float, default=10.0)
     ap.add_argument("--c4-prns", type=int, default=0, help="config-4 style 20 ms coherent search over this many PRNs (0: skip)")
+    ap.add_argument("--no-c3", dest="c3", action="store_false", help="skip the GLONASS G1 FDMA acquisition object")
     ap.add_argument("--strong-prns", type=int, default=51, help="strong-scaling search (BASELINE configs[3]) over this many PRNs (0: skip)")
     ap.add_argument("--strong-steps", type=int, default=10, help="non-coherent steps of the strong-scaling search")
     ap.add_argument("--no-sweep", action="store_true", help="skip the tracking channel-count sweep")

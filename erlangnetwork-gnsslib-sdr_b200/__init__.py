@@ -85,7 +85,16 @@ class TrkRec(C.Structure):
                 ("L0", C.c_double), ("D0", C.c_double), ("S0", C.c_double), ("remcout0", C.c_double),
                 ("Isum", C.c_double), ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64),
                 ("flagobs", C.c_int32), ("flagsyncf", C.c_int32), ("polarity", C.c_int32), ("flagtow", C.c_int32),
-                ("firstsf", C.c_uint64), ("firstsfcnt", C.c_uint64)]
+                ("firstsf", C.c_uint64), ("firstsfcnt", C.c_uint64), ("obs_dcnt", C.c_int64)]
+
+
+OBSINTERPN = 80
+
+
+class TrkObs(C.Structure):
+    _fields_ = [("L", C.c_double * OBSINTERPN), ("D", C.c_double * OBSINTERPN), ("S", C.c_double * OBSINTERPN),
+                ("remcout", C.c_double * OBSINTERPN), ("codei", C.c_uint64 * OBSINTERPN),
+                ("cntout", C.c_uint64 * OBSINTERPN), ("codeisum", C.c_uint64 * OBSINTERPN)]
 
 
 def loop_coeffs(dllb: float, pllb: float, fllb: float) -> Loop:

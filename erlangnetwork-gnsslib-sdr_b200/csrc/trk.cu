@@ -190,6 +190,7 @@ struct trk_state_t {
      * loopcnt of the channel thread (src/sdrmain.c:236,304) */
     double L0, D0, S0, remcout0, Isum;
     uint64_t obs_codei, obs_cnt;
+    int64_t obs_dcnt;
     int32_t flagremcarradd, loopcnt;
     /* frame synchronisation (GPS L1CA): nav.fbits as a ring of 2 + 300 bits (fhead = oldest),
      * flagsyncf, flagtow, polarity, firstsf, firstsfcnt (src/sdr.h:440-479) */
@@ -327,6 +328,15 @@ __device__ static void trk_loops_warp(trk_state_t *st, const sdrb200_loop_t *prm
     }
 }
 
+/* the interpolation stocks of setobsdata (src/sdrtrk.c:160-209, src/sdr.h:384-391) per channel, in
+ * global memory, as RINGS: the reference shifts 80-element arrays on every call, here the newest
+ * element sits at `head` and a fetch unrolls the ring newest-first                            */
+struct trk_obsstock_t {
+    double   L[SDRB200_OBSINTERPN], D[SDRB200_OBSINTERPN], remcout[SDRB200_OBSINTERPN], S[SDRB200_OBSINTERPN];
+    uint64_t codei[SDRB200_OBSINTERPN], cntout[SDRB200_OBSINTERPN], codeisum[SDRB200_OBSINTERPN];
+    int32_t  head, shead;
+};
+
 struct trk_lf_t { double carrfreq, codefreq; unsigned long long cnt; int32_t navcnt, synci, flagsync, pad; };
 
 /* epilogue of one code period, executed by ONE warp: everything sdrtracking and
@@ -334,7 +344,8 @@ struct trk_lf_t { double carrfreq, codefreq; unsigned long long cnt; int32_t nav
 __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, const unsigned int *sumI,
                                     const unsigned int *sumQ, double remc, double remp,
                                     sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr,
-                                    trk_lf_t *lf = nullptr, volatile int *lf_flag = nullptr, int lf_val = 0)
+                                    trk_lf_t *lf = nullptr, volatile int *lf_flag = nullptr, int lf_val = 0,
+                                    trk_obsstock_t *obs = nullptr)
 {
     long long e0 = 0;
 #define TRK_EP(i) do { if (ep && lane == 0) { const long long e1 = trk_clock(); ep[i] += e1 - e0; e0 = e1; } } while (0)
@@ -407,6 +418,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         flagobs = (st->loopcnt % (100 / ch->loopms) == 0) ? 2 : 1;     /* SNSMOOTHMS, src/sdr.h:198 */
         st->obs_codei = st->buffloc;
         st->obs_cnt = st->cnt;
+        st->obs_dcnt = (int64_t)(st->cnt - st->firstsfcnt);       /* (cnt - nav.firstsfcnt) of trk.tow[0] */
         st->remcout0 = st->oldremcode * ch->f_sf / st->codefreq;
         st->D0 = -(st->carrfreq - ch->f_if - ch->foffset);
         if (!st->flagremcarradd) { st->L0 -= st->remcarr / (2.0 * TRK_PI); st->flagremcarradd = 1; }
@@ -419,6 +431,17 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         if (flagobs == 2) {
             st->S0 = 10 * log(st->Isum / 100.0 / 100.0) + log(500.0) + 5;
             st->Isum = 0;
+        }
+        if (obs) {                                            /* shiftdata(...) of src/sdrtrk.c:163-168, 199-201 */
+            const int h = (obs->head + SDRB200_OBSINTERPN - 1) % SDRB200_OBSINTERPN;
+            obs->L[h] = st->L0; obs->D[h] = st->D0; obs->remcout[h] = st->remcout0;
+            obs->codei[h] = st->obs_codei; obs->cntout[h] = st->obs_cnt;
+            obs->head = h;
+            if (flagobs == 2) {
+                const int sh = (obs->shead + SDRB200_OBSINTERPN - 1) % SDRB200_OBSINTERPN;
+                obs->S[sh] = st->S0; obs->codeisum[sh] = st->buffloc;
+                obs->shead = sh;
+            }
         }
         st->loopcnt++;
     }
@@ -437,7 +460,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
             rec->L0 = st->L0; rec->D0 = st->D0; rec->S0 = st->S0; rec->remcout0 = st->remcout0;
             rec->Isum = st->Isum; rec->obs_codei = st->obs_codei; rec->obs_cnt = st->obs_cnt;
             rec->flagobs = flagobs; rec->flagsyncf = st->flagsyncf; rec->polarity = st->polarity; rec->flagtow = st->flagtow;
-            rec->firstsf = st->firstsf; rec->firstsfcnt = st->firstsfcnt;
+            rec->firstsf = st->firstsf; rec->firstsfcnt = st->firstsfcnt; rec->obs_dcnt = st->obs_dcnt;
         }
     }
     __syncwarp();
@@ -465,6 +488,7 @@ struct sdrb200_trk {
     trk_chan_dev_t *h_chan, *d_chan;
     trk_state_t *h_state0, *d_state;
     sdrb200_trk_rec_t *d_rec; size_t rec_cap;       /* records */
+    trk_obsstock_t *d_obs;                          /* [nch] interpolation stocks */
     int *d_nrec, *d_err;
     long long *d_prof;               /* phase profile of CTA 0 (NULL: off) */
     int last_nperiods, last_with_rec;
@@ -521,6 +545,7 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
     if (cudaStreamCreateWithFlags(&e->st, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMalloc((void **)&e->d_chan, sizeof(trk_chan_dev_t) * nch) != cudaSuccess ||
         cudaMalloc((void **)&e->d_state, sizeof(trk_state_t) * nch) != cudaSuccess ||
+        cudaMalloc((void **)&e->d_obs, sizeof(trk_obsstock_t) * nch) != cudaSuccess ||
         cudaMalloc((void **)&e->d_nrec, sizeof(int) * (nch + 1)) != cudaSuccess) {
         sdrb200_set_error("trk_create: device allocation failed");
         sdrb200_trk_destroy(e); return SDRB200_ENOMEM;
@@ -529,6 +554,7 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
     cudaMemcpyAsync(e->d_chan, e->h_chan, sizeof(trk_chan_dev_t) * nch, cudaMemcpyHostToDevice, e->st);
     cudaMemcpyAsync(e->d_state, e->h_state0, sizeof(trk_state_t) * nch, cudaMemcpyHostToDevice, e->st);
     cudaMemsetAsync(e->d_nrec, 0, sizeof(int) * (nch + 1), e->st);
+    cudaMemsetAsync(e->d_obs, 0, sizeof(trk_obsstock_t) * nch, e->st);
     SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
     *out = e;
     return SDRB200_OK;
@@ -537,7 +563,7 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
 extern "C" void sdrb200_trk_destroy(sdrb200_trk_t *e)
 {
     if (!e) return;
-    cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_rec); cudaFree(e->d_nrec); cudaFree(e->d_prof);
+    cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_obs); cudaFree(e->d_rec); cudaFree(e->d_nrec); cudaFree(e->d_prof);
     if (e->st) cudaStreamDestroy(e->st);
     free(e->h_chan); free(e->h_state0); free(e);
 }
@@ -568,6 +594,7 @@ extern "C" int sdrb200_trk_reset(sdrb200_trk_t *e)
 {
     if (!e) return SDRB200_EINVAL;
     SDRB200_CUDA_TRY(cudaMemcpyAsync(e->d_state, e->h_state0, sizeof(trk_state_t) * e->nch, cudaMemcpyHostToDevice, e->st));
+    SDRB200_CUDA_TRY(cudaMemsetAsync(e->d_obs, 0, sizeof(trk_obsstock_t) * e->nch, e->st));
     SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
     return SDRB200_OK;
 }
@@ -626,7 +653,8 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
         const trk_chan_dev_t *a_ch = e->d_chan; trk_state_t *a_st = e->d_state; const int8_t *a_if = s->d_buf;
         uint64_t a_cap = s->capacity, a_av = s->count; int a_np = nperiods, a_mx = e->maxn, a_qc = e->qcap;
         int *a_nrec = e->d_nrec, *a_err = e->d_err, a_cw = e->ctrl_works; long long *a_prof = e->d_prof;
-        void *args[] = {&a_ch, &a_st, &a_if, &a_cap, &a_av, &a_np, &a_mx, &a_qc, &recs, &a_nrec, &a_err, &a_cw, &a_prof};
+        trk_obsstock_t *a_obs = e->d_obs;
+        void *args[] = {&a_ch, &a_st, &a_if, &a_cap, &a_av, &a_np, &a_mx, &a_qc, &recs, &a_nrec, &a_err, &a_cw, &a_prof, &a_obs};
         SDRB200_CUDA_TRY(cudaLaunchKernelExC(&cfg, fn, args));
     }
     sdrb200_count_launch(1);
@@ -650,6 +678,22 @@ extern "C" int sdrb200_trk_set_cluster(sdrb200_trk_t *e, int cluster_size, int c
 extern "C" int sdrb200_trk_enqueue(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods)
 {
     return trk_launch(e, s, nperiods, 0);
+}
+
+/* the stocks of one channel, newest first - the arrays sdrsync.c interpolates (src/sdrsync.c:96-121) */
+extern "C" int sdrb200_trk_fetch_obs(sdrb200_trk_t *e, int ch, sdrb200_trk_obs_t *out)
+{
+    if (!e || !out || ch < 0 || ch >= e->nch) { sdrb200_set_error("trk_fetch_obs: bad argument"); return SDRB200_EINVAL; }
+    trk_obsstock_t h;
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(&h, e->d_obs + ch, sizeof(h), cudaMemcpyDeviceToHost, e->st));
+    SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    for (int j = 0; j < SDRB200_OBSINTERPN; j++) {
+        const int k = (h.head + j) % SDRB200_OBSINTERPN, ks = (h.shead + j) % SDRB200_OBSINTERPN;
+        out->L[j] = h.L[k]; out->D[j] = h.D[k]; out->remcout[j] = h.remcout[k];
+        out->codei[j] = h.codei[k]; out->cntout[j] = h.cntout[k];
+        out->S[j] = h.S[ks]; out->codeisum[j] = h.codeisum[ks];
+    }
+    return SDRB200_OK;
 }
 
 extern "C" int sdrb200_trk_sync(sdrb200_trk_t *e)

@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(NT, (NT >= 1024) ? 1 : 2)
 k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ states,
          const int8_t *__restrict__ ifbuf, uint64_t capacity, uint64_t avail, int nperiods, int maxn, int qcap,
          sdrb200_trk_rec_t *__restrict__ recs, int *__restrict__ nrec, int *__restrict__ err, int ctrl_works,
-         long long *__restrict__ prof)
+         long long *__restrict__ prof, trk_obsstock_t *__restrict__ obsst)
 {
     constexpr int NW = NT - TRK_T0, R = TRK_RING;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -362,7 +362,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             if (lane == 0) { st->currnsamp = hd->n; if (res[2 * SDRB200_MAXTAPS]) errw = 1; }
             __syncwarp();
             trk_epilogue(ch, st, res, res + SDRB200_MAXTAPS, hd->remc, hd->remp, recs ? &sm->rec : nullptr, lane,
-                         (prof && chno == 0) ? prof : nullptr, &sm->lf, &sm->loops_count, q + 1);
+                         (prof && chno == 0) ? prof : nullptr, &sm->lf, &sm->loops_count, q + 1, obsst ? &obsst[chno] : nullptr);
             if (recs) {
                 const uint32_t *src = (const uint32_t *)&sm->rec;
                 uint32_t *dst = (uint32_t *)&recs[(size_t)chno * nperiods + q];

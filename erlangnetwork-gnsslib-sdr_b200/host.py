@@ -5,12 +5,12 @@ import ctypes as C
 
 import numpy as np
 
-from . import (AcqCfg, AcqResult, Error, Loop, TrkChan, TrkRec,  # noqa: F401
+from . import (AcqCfg, AcqResult, Error, Loop, TrkChan, TrkObs, TrkRec,  # noqa: F401
                MAXCORRN, MAXTAPS, check, lib)
 
 __all__ = ["gencode", "gencode_device", "correlator", "mixcarr", "rescode",
            "cpxfft", "cpxconv", "cpxpspec", "pcorrelator", "checkacquisition", "checkacquisition_noalloc",
-           "Stream", "Acquisition", "Tracking", "DeviceBytes", "device_count", "launch_count", "make_trk_chan"]
+           "Stream", "Acquisition", "Tracking", "DeviceBytes", "device_count", "launch_count", "make_trk_chan", "trk_log"]
 
 _i8p = C.POINTER(C.c_int8)
 _dp = C.POINTER(C.c_double)
@@ -355,6 +355,12 @@ class Tracking:
     def reset(self):
         check(lib.sdrb200_trk_reset(self.h), "trk_reset")
 
+    def fetch_obs(self, ch: int) -> dict:
+        """the 80-deep interpolation stocks of one channel, newest first (setobsdata, src/sdrtrk.c:160-209)."""
+        o = TrkObs()
+        check(lib.sdrb200_trk_fetch_obs(self.h, int(ch), C.byref(o)), "trk_fetch_obs")
+        return {k: np.array(getattr(o, k)) for k in ("L", "D", "S", "remcout", "codei", "cntout", "codeisum")}
+
     def set_cluster(self, cluster_size: int, ctrl_works: bool = False):
         """cluster size per channel (0: choose at the next launch, else 1, 2, 4, 8)."""
         check(lib.sdrb200_trk_set_cluster(self.h, int(cluster_size), int(bool(ctrl_works))), "trk_set_cluster")
@@ -374,6 +380,24 @@ class Tracking:
             self.close()
         except Exception:
             pass
+
+
+def trk_log(recs, corrn: int, corrd: int, ctime=1e-3, firstsftow=0.0, flagdec=0) -> str:
+    """the reference's tracking log (writelog_header + writelog, src/sdrout.c:386-436) of one channel's
+    records: header and one CSV line per code period."""
+    buf = C.create_string_buffer(4096)
+    n = lib.sdrb200_trk_log_header(int(corrn), int(corrd), buf, C.c_size_t(4096))
+    if n < 0:
+        raise Error("trk_log_header failed")
+    out = [buf.raw[:n].decode()]
+    recs = np.ascontiguousarray(recs)
+    for i in range(len(recs)):
+        n = lib.sdrb200_trk_log_line(recs[i:i + 1].ctypes.data_as(C.POINTER(TrkRec)), int(corrn), C.c_double(firstsftow),
+                                     C.c_double(ctime), int(flagdec), buf, C.c_size_t(4096))
+        if n < 0:
+            raise Error("trk_log_line failed")
+        out.append(buf.raw[:n].decode())
+    return "".join(out)
 
 
 def make_trk_chan(f_sf, f_if, f_cf, dtype, prn, code, buffloc, acqfreq, corrn, corrd, corrp,

@@ -226,7 +226,21 @@ typedef struct {             /* one record per channel per code period          
      * reference sample / counter of the first subframe (nav.firstsf, nav.firstsfcnt)   */
     int32_t  flagsyncf, polarity, flagtow;
     uint64_t firstsf, firstsfcnt;
+    /* cnt - nav.firstsfcnt at the last setobsdata call: trk.tow[0] = nav.firstsftow + obs_dcnt * ctime
+     * (src/sdrtrk.c:170-171); firstsftow is the host's (decodenav)                                  */
+    int64_t  obs_dcnt;
 } sdrb200_trk_rec_t;
+
+/* the interpolation stocks setobsdata keeps per channel (src/sdrtrk.c:160-209, src/sdr.h:384-391:
+ * L, D, S, remcout, codei, cntout, codeisum; OBSINTERPN = 80 deep, newest first) - what
+ * syncthread interpolates pseudorange, carrier phase and Doppler from (src/sdrsync.c:96-121).
+ * tow[] is not kept on the device: it is nav.firstsftow + (cntout[] - nav.firstsfcnt) * ctime
+ * (src/sdrtrk.c:170-171) and firstsftow comes from the host's decodenav.                    */
+#define SDRB200_OBSINTERPN 80
+typedef struct {
+    double   L[SDRB200_OBSINTERPN], D[SDRB200_OBSINTERPN], S[SDRB200_OBSINTERPN], remcout[SDRB200_OBSINTERPN];
+    uint64_t codei[SDRB200_OBSINTERPN], cntout[SDRB200_OBSINTERPN], codeisum[SDRB200_OBSINTERPN];
+} sdrb200_trk_obs_t;
 
 typedef struct sdrb200_trk sdrb200_trk_t;
 int  sdrb200_trk_create(sdrb200_trk_t **eng, int nch, const sdrb200_trk_chan_t *chan);
@@ -238,6 +252,14 @@ int  sdrb200_trk_run(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nperiods
 /* launch-only variant for timing (records stay on the device)                  */
 int  sdrb200_trk_enqueue(sdrb200_trk_t *eng, const sdrb200_stream_t *s, int nperiods);
 int  sdrb200_trk_sync(sdrb200_trk_t *eng);
+int  sdrb200_trk_fetch_obs(sdrb200_trk_t *eng, int channel, sdrb200_trk_obs_t *out);
+/* the reference's tracking log (writelog_header / writelog, src/sdrout.c:386-436) from a record:
+ * one CSV line into buf (returns its length, or -1 if it does not fit).  corrn/corrd/corrp as in
+ * sdrini (trk.corrx is rebuilt from them, src/sdrinit.c:455-468); firstsftow and flagdec come
+ * from the host's decodenav (0 until a subframe is decoded); ctime = code period (s).        */
+int  sdrb200_trk_log_header(int corrn, int corrd, char *buf, size_t cap);
+int  sdrb200_trk_log_line(const sdrb200_trk_rec_t *rec, int corrn, double firstsftow, double ctime, int flagdec,
+                          char *buf, size_t cap);
 int  sdrb200_trk_reset(sdrb200_trk_t *eng);     /* back to the hand-over state   */
 void *sdrb200_trk_cuda_stream(sdrb200_trk_t *eng);
 /* One thread-block cluster tracks one channel: rank 0's control warps replay the NCOs and

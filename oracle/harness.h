@@ -99,6 +99,21 @@ int oh_acq_track_mt(const oh_cfg_t *cfg, const signed char *if_data, uint64_t ns
                     uint64_t avail, int nprn, const int *prn, const int *ctype,
                     int nperiods, oh_acq_t *acq, oh_trkrec_t *rec, int *ntracked);
 
+/* ---- observables; replay builds only -------------------------------------------
+ * the 80-deep interpolation stocks setobsdata shifts (src/sdrtrk.c:160-209, src/sdr.h:384-391),
+ * newest first, as they stand after the last oh_acq_track run                                  */
+#define OH_OBSINTERPN 80
+typedef struct {
+    double   L[OH_OBSINTERPN], D[OH_OBSINTERPN], S[OH_OBSINTERPN], remcout[OH_OBSINTERPN];
+    uint64_t codei[OH_OBSINTERPN], cntout[OH_OBSINTERPN], codeisum[OH_OBSINTERPN];
+} oh_stocks_t;
+int oh_last_stocks(int channel_index, oh_stocks_t *out);
+/* syncthread's use of the stocks (src/sdrsync.c:96-121) with the reference's uint64todouble/interp1 */
+int oh_interp_obs(const oh_stocks_t *st, uint64_t sampbase, double samprefd, double *L, double *D);
+/* write the reference's own tracking log (writelog, src/sdrout.c:386-436) of channel number
+ * `chno` (1-based, sdr->no) during the next oh_acq_track; NULL closes it                      */
+int oh_set_logfile(const char *path, int chno);
+
 /* Thin pass-throughs to single hot functions, for unit-level parity. */
 void oh_correlator(const signed char *data, int dtype, double ti, int n,
                    double freq, double phi0, double crate, double coff,

@@ -185,6 +185,49 @@ int oh_acquire(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsample
 /* one code period of one channel: the body of the while loop of sdrthread()
  * (src/sdrmain.c:264-312) plus the record; returns 1 if a period was tracked.
  * rec points at the channel's own row of records.                                */
+/* optional: the reference's own tracking log (writelog, src/sdrout.c:412-436), one file for the
+ * channel whose number is g_log_ch, written where sdrthread writes it (src/sdrmain.c:307-308) */
+static FILE *g_log_fp = NULL;
+static int   g_log_ch = -1;
+int oh_set_logfile(const char *path, int chno)
+{
+    if (g_log_fp) { fclose(g_log_fp); g_log_fp = NULL; }
+    g_log_ch = -1;
+    if (!path) return 0;
+    g_log_fp = fopen(path, "w");
+    if (!g_log_fp) return -1;
+    g_log_ch = chno;
+    return 0;
+}
+
+/* the interpolation stocks setobsdata fills (src/sdrtrk.c:160-209), kept after a run for oh_last_stocks */
+static oh_stocks_t g_stocks[MAXSAT];
+static void keep_stocks(const sdrch_t *sdr, int i)
+{
+    oh_stocks_t *o = &g_stocks[i];
+    memcpy(o->L, sdr->trk.L, sizeof(o->L)); memcpy(o->D, sdr->trk.D, sizeof(o->D));
+    memcpy(o->S, sdr->trk.S, sizeof(o->S)); memcpy(o->remcout, sdr->trk.remcout, sizeof(o->remcout));
+    memcpy(o->codei, sdr->trk.codei, sizeof(o->codei)); memcpy(o->cntout, sdr->trk.cntout, sizeof(o->cntout));
+    memcpy(o->codeisum, sdr->trk.codeisum, sizeof(o->codeisum));
+}
+int oh_last_stocks(int i, oh_stocks_t *out)
+{
+    if (i < 0 || i >= MAXSAT || !out) return -1;
+    *out = g_stocks[i];
+    return 0;
+}
+/* what syncthread does with the stocks of one channel (src/sdrsync.c:96-121): carrier phase and
+ * Doppler interpolated at the reference sample, with the reference's own uint64todouble/interp1 */
+int oh_interp_obs(const oh_stocks_t *st, uint64_t sampbase, double samprefd, double *L, double *D)
+{
+    double codeid[OBSINTERPN];
+    oh_stocks_t t = *st;
+    uint64todouble(t.codei, sampbase, OBSINTERPN, codeid);
+    *L = interp1(codeid, t.L, OBSINTERPN, samprefd);
+    *D = interp1(codeid, t.D, OBSINTERPN, samprefd);
+    return 0;
+}
+
 static int track_period(sdrch_t *sdr, uint64_t *buffloc, uint64_t *cnt, uint64_t *loopcnt,
                         oh_trkrec_t *rec, int *ntracked)
 {
@@ -232,6 +275,10 @@ static int track_period(sdrch_t *sdr, uint64_t *buffloc, uint64_t *cnt, uint64_t
     r->Isum = sdr->trk.Isum; r->obs_codei = sdr->trk.codei[0]; r->obs_cnt = sdr->trk.cntout[0];
     r->flagobs = flagobs; r->polarity = sdr->nav.polarity;
 
+    if (g_log_fp && sdr->no == g_log_ch) {
+        if (*ntracked == 0) writelog_header(g_log_fp, &sdr->trk);
+        writelog(g_log_fp, &sdr->trk, &sdr->nav);
+    }
     if (sdr->trk.flagloopfilter) clearcumsumcorr(&sdr->trk);
     (*cnt)++;
     (*buffloc) += sdr->currnsamp;
@@ -277,7 +324,8 @@ int oh_acq_track(const oh_cfg_t *cfg, const signed char *if_data, uint64_t nsamp
         }
     } while (active);
 
-    for (i = 0; i < nprn; i++) freesdrch(&sdrch[i]);
+    for (i = 0; i < nprn; i++) { keep_stocks(&sdrch[i], i); freesdrch(&sdrch[i]); }
+    if (g_log_fp) fflush(g_log_fp);
     ring_release();
     free(buffloc);
     return 0;

@@ -42,6 +42,11 @@ class OhTrkRec(C.Structure):
                 ("obs_codei", C.c_uint64), ("obs_cnt", C.c_uint64), ("flagobs", C.c_int), ("polarity", C.c_int)]
 
 
+class OhStocks(C.Structure):
+    _fields_ = [("L", C.c_double * 80), ("D", C.c_double * 80), ("S", C.c_double * 80), ("remcout", C.c_double * 80),
+                ("codei", C.c_uint64 * 80), ("cntout", C.c_uint64 * 80), ("codeisum", C.c_uint64 * 80)]
+
+
 # the INI defaults of frontend/iffile.ini:29-48 and frontend/rtlsdr_L1.ini:29-48
 def cfg_iffile(**kw) -> OhCfg:
     c = OhCfg(f_sf=16.368e6, f_if=4.092e6, f_cf=1575.42e6, dtype=1, corrn=6, corrd=3, corrp=6)
@@ -92,6 +97,29 @@ class Oracle:
                                  C.c_uint64(avail), n, prn_a, ct_a, out, pp)
         assert rc == 0, f"oh_acquire rc={rc}"
         return list(out), power
+
+    # ---- observables (reference builds of replay.c only)
+    def set_logfile(self, path, chno=1):
+        """the reference's own writelog output of channel number chno during the next acq_track"""
+        rc = self.lib.oh_set_logfile(path.encode() if path else None, int(chno))
+        assert rc == 0, "oh_set_logfile"
+
+    def last_stocks(self, i):
+        """stocks of channel index i after the last acq_track: dict of 80-element arrays, newest first"""
+        o = OhStocks()
+        assert self.lib.oh_last_stocks(int(i), C.byref(o)) == 0
+        return {k: np.array(getattr(o, k)) for k in ("L", "D", "S", "remcout", "codei", "cntout", "codeisum")}
+
+    def interp_obs(self, stocks, sampbase, samprefd):
+        """syncthread's interpolation (src/sdrsync.c:96-121) with the reference's own interp1"""
+        o = OhStocks()
+        for k in ("L", "D", "S", "remcout", "codei", "cntout", "codeisum"):
+            arr = getattr(o, k)
+            for j, v in enumerate(stocks[k]):
+                arr[j] = int(v) if k in ("codei", "cntout", "codeisum") else float(v)
+        L, D = C.c_double(), C.c_double()
+        assert self.lib.oh_interp_obs(C.byref(o), C.c_uint64(int(sampbase)), C.c_double(samprefd), C.byref(L), C.byref(D)) == 0
+        return L.value, D.value
 
     def fft_seconds(self, reset=True):
         """seconds spent inside the FFT shim's fftwf_execute_dft in this process (reference builds
