@@ -964,6 +964,46 @@ def run_b200(args):
                          "n_gpus": world, "bins_per_gpu": [len(sdr.shard.doppler_slab(NFREQ, r_, world)) for r_ in range(world)],
                          "ms_per_search": td * 1e3, "cells_per_s": len(prnsd) * NFREQ * NSAMP * intgd / td,
                          "merged_equals_unsharded": eqd}
+    # ------------------------------------------------ the sdr.h drop-in against the reference, same replay
+    # oracle/_ref/libreplay_b200.so = the reference's cold objects + its channel-thread loop with every hot
+    # sdr.h symbol bound to libsdrb200_sdrh.so; libreplay_ref.so = all reference.  Same IF bytes, the
+    # reference's threading model (one pthread per channel), 12 channels (BASELINE configs[1] scene).
+    dropin_obj = None
+    if rank == 0 and world == 1 and host_par is not None and not args.no_dropin:
+        import oracle_bind as ob
+        if ob.have_ref() and ob.have_dropin():
+            nperd = 2000
+            cfgd = ob.cfg_iffile(acq_intg=10)
+
+            def _quiet(fn):
+                devnull = os.open(os.devnull, os.O_WRONLY); saved = os.dup(1); os.dup2(devnull, 1)
+                try:
+                    return fn()
+                finally:
+                    os.dup2(saved, 1); os.close(devnull); os.close(saved)
+
+            def _run(o):
+                t0 = time.perf_counter()
+                _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, 1, threaded=True))
+                t_a = time.perf_counter() - t0                      # 12 acquisitions + one period
+                t0 = time.perf_counter()
+                _, _, ntr = _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, nperd, threaded=True))
+                t_all = time.perf_counter() - t0
+                return t_a, max(t_all - t_a, 1e-9), sum(ntr)
+            od, orf = ob.dropin(), ob.ref()
+            od.set_lookahead(True)
+            _run(od)                                               # warm: plans, engines, mirror
+            served0 = od.lookahead_served()
+            ta_d, tt_d, n_d = _run(od)
+            served = od.lookahead_served() - served0
+            ta_r, tt_r, n_r = _run(orf)
+            dropin_obj = {"what": "reference channel-thread loop (one pthread per channel) with the hot sdr.h symbols from "
+                                  "libsdrb200_sdrh.so, against the all-reference build; same IF bytes, same host",
+                          "channels": len(TRK_PRNS), "code_periods_per_channel": nperd,
+                          "tracking_channel_s_per_s": {"dropin": n_d * 1e-3 / tt_d, "reference": n_r * 1e-3 / tt_r,
+                                                       "ratio": (n_d / tt_d) / (n_r / tt_r)},
+                          "acquisition_12_channels_ms": {"dropin": ta_d * 1e3, "reference": ta_r * 1e3},
+                          "periods_served_from_engine_records": served, "host_cores": os.cpu_count()}
     clk = clocks.stop()
 
     # ------------------------------------------------ reduce over ranks, print
@@ -1012,6 +1052,7 @@ def run_b200(args):
         "glonass_c3": c3_obj,
         "strong_scaling_c4": strong_obj,
         "doppler_slabs": dslab_obj,
+        "dropin": dropin_obj,
     }
     if rank == 0:
         emit(line)
@@ -1105,6 +1146,7 @@ def main():
     ap.add_argument("--no-c3", dest="c3", action="store_false", help="skip the GLONASS G1 FDMA acquisition object")
     ap.add_argument("--strong-prns", type=int, default=51, help="strong-scaling search (BASELINE configs[3]) over this many PRNs (0: skip)")
     ap.add_argument("--strong-steps", type=int, default=10, help="non-coherent steps of the strong-scaling search")
+    ap.add_argument("--no-dropin", action="store_true", help="skip the drop-in vs reference replay object")
     ap.add_argument("--no-sweep", action="store_true", help="skip the tracking channel-count sweep")
     ap.add_argument("--trk-profile", action="store_true", help="add the per-phase cycle profile of channel 0")
     args = ap.parse_args()

@@ -305,6 +305,15 @@ extern "C" int sdrb200_stream_push_device(sdrb200_stream_t *s, const int8_t *d_s
     return stream_push(s, 2, d_src, n);
 }
 
+/* advance the absolute sample index by n without storing samples (their content is undefined):
+ * lets a mirror of a long-running host ring start at the first sample anybody will ask for   */
+extern "C" int sdrb200_stream_skip(sdrb200_stream_t *s, uint64_t n)
+{
+    if (!s) return SDRB200_EINVAL;
+    s->count += n;
+    return SDRB200_OK;
+}
+
 extern "C" int sdrb200_stream_read(const sdrb200_stream_t *s, uint64_t buffloc, uint64_t n, int8_t *host)
 {
     if (!s || !host) return SDRB200_EINVAL;

@@ -489,6 +489,10 @@ struct sdrb200_trk {
     trk_state_t *h_state0, *d_state;
     sdrb200_trk_rec_t *d_rec; size_t rec_cap;       /* records */
     trk_obsstock_t *d_obs;                          /* [nch] interpolation stocks */
+    sdrb200_trk_rec_t *h_rec; size_t h_rec_cap;     /* pinned staging: a device-to-host copy into pageable memory
+                                                     * blocks inside the runtime and serialises the launches of
+                                                     * other host threads (one engine per channel thread in the drop-in) */
+    int *h_nrec;
     int *d_nrec, *d_err;
     long long *d_prof;               /* phase profile of CTA 0 (NULL: off) */
     int last_nperiods, last_with_rec;
@@ -563,6 +567,8 @@ extern "C" int sdrb200_trk_create(sdrb200_trk_t **out, int nch, const sdrb200_tr
 extern "C" void sdrb200_trk_destroy(sdrb200_trk_t *e)
 {
     if (!e) return;
+    if (e->h_rec) cudaFreeHost(e->h_rec);
+    if (e->h_nrec) cudaFreeHost(e->h_nrec);
     cudaFree(e->d_chan); cudaFree(e->d_state); cudaFree(e->d_obs); cudaFree(e->d_rec); cudaFree(e->d_nrec); cudaFree(e->d_prof);
     if (e->st) cudaStreamDestroy(e->st);
     free(e->h_chan); free(e->h_state0); free(e);
@@ -708,13 +714,20 @@ extern "C" int sdrb200_trk_run(sdrb200_trk_t *e, const sdrb200_stream_t *s, int 
 {
     int rc = trk_launch(e, s, nperiods, rec != NULL);
     if (rc) return rc;
-    int h[1 + 4096];
-    if (e->nch > 4096) { sdrb200_set_error("trk_run: too many channels"); return SDRB200_EINVAL; }
+    if (!e->h_nrec) SDRB200_CUDA_TRY(cudaMallocHost((void **)&e->h_nrec, sizeof(int) * (size_t)(e->nch + 1)));
+    int *h = e->h_nrec;
+    const size_t nrecs = (size_t)e->nch * nperiods;
+    if (rec && nrecs > e->h_rec_cap) {
+        if (e->h_rec) cudaFreeHost(e->h_rec);
+        e->h_rec = NULL; e->h_rec_cap = 0;
+        SDRB200_CUDA_TRY(cudaMallocHost((void **)&e->h_rec, sizeof(sdrb200_trk_rec_t) * nrecs));
+        e->h_rec_cap = nrecs;
+    }
     SDRB200_CUDA_TRY(cudaMemcpyAsync(h, e->d_nrec, sizeof(int) * (e->nch + 1), cudaMemcpyDeviceToHost, e->st));
     if (rec)
-        SDRB200_CUDA_TRY(cudaMemcpyAsync(rec, e->d_rec, sizeof(sdrb200_trk_rec_t) * (size_t)e->nch * nperiods,
-                                         cudaMemcpyDeviceToHost, e->st));
+        SDRB200_CUDA_TRY(cudaMemcpyAsync(e->h_rec, e->d_rec, sizeof(sdrb200_trk_rec_t) * nrecs, cudaMemcpyDeviceToHost, e->st));
     SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
+    if (rec) memcpy(rec, e->h_rec, sizeof(sdrb200_trk_rec_t) * nrecs);
     if (h[e->nch]) {
         const int code = h[e->nch];
         SDRB200_CUDA_TRY(cudaMemsetAsync(e->d_err, 0, sizeof(int), e->st));

@@ -202,7 +202,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                      * 2 = the ring no longer holds the window (the channel lags by more than the capacity),
                      * 3 = currnsamp outside the CTA's work area (codefreq ran away)                        */
                     if (go && avail - buffloc > capacity) { go = 0; atomicMax(err, 2); }
-                    if (!go && (n <= 0 || n > maxn)) atomicMax(err, 3);
+                    if (!go && (n <= 0 || n > maxn)) { atomicMax(err, 3); }
                     if (go && flagsync && ch->navrate > 1) quiet = trk_quiet_forecast(cnt, synci, &navcnt, ch->navrate, ch->loopms);
                 }
                 /* flow control: the team's slot is free, the rings' slots are consumed */

@@ -92,6 +92,8 @@ int  sdrb200_stream_push_host_packed(sdrb200_stream_t *s, const uint8_t *host, u
  * written by a DMA engine); no counterpart in the reference, whose front ends fill a
  * host ring (src/sdrrcv.c:300-404)                                            */
 int  sdrb200_stream_push_device(sdrb200_stream_t *s, const int8_t *d_src, uint64_t n);
+/* advance the absolute index by n samples without storing any (content undefined)             */
+int  sdrb200_stream_skip(sdrb200_stream_t *s, uint64_t n);
 uint64_t sdrb200_stream_count(const sdrb200_stream_t *s);  /* samples pushed   */
 /* copy n samples starting at absolute index `buffloc` back to the host
  * (the rcvgetbuff contract)                                                   */

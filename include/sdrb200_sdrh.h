@@ -14,7 +14,7 @@
  *
  * A maintainer of the reference links it instead of sdracq.o / sdrtrk.o and the
  * hot half of sdrcmn.o (INTEGRATION.md shows the Makefile lines).  Besides the
- * sdr.h names it exports three helpers:
+ * sdr.h names it exports five helpers:
  */
 #ifndef SDRB200_SDRH_H
 #define SDRB200_SDRH_H
@@ -28,6 +28,13 @@ int  sdrb200_sdrh_last_nintg(void);
  * the caller's `power` (the reference plots it, src/sdrmain.c:258-261); 0: skip
  * the 8*nfreq*nsamp-byte device-to-host copy                                    */
 extern int sdrb200_sdrh_fill_power;
+/* 1 (default): sdrtracking() runs the batched engine a chunk of code periods ahead on the samples
+ * that have arrived (one mirror IF stream per GPU and front-end type, fed with rcvgetbuff) and
+ * serves the per-period calls - and pll()/dll() - from its records; 0: one correlator call per
+ * period.  Channel n runs on GPU (n - 1) % number of GPUs.                                  */
+extern int sdrb200_sdrh_lookahead;
+/* code periods sdrtracking() has served from the batched engine's records so far (all channels) */
+unsigned long long sdrb200_sdrh_lookahead_served(void);
 /* free the cached device plan of one channel (NULL: all); call before
  * freesdrch() if channels are re-initialised with different parameters          */
 void sdrb200_sdrh_release(const void *sdrch);

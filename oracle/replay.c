@@ -63,6 +63,11 @@ static int ring_setup(const oh_cfg_t *cfg, const signed char *src, uint64_t nsam
     uint64_t blocks = (nsamples + FILE_BUFFSIZE - 1) / FILE_BUFFSIZE + 2;
     if (blocks > MEMBUFFLEN) blocks = MEMBUFFLEN;
     ring_release();
+#ifdef OH_NO_PCORR_WRAP
+    /* drop-in build: a new "recording" starts - what quitsdr()/startsdr() mean for a receiver.  The
+     * product keeps device-side state per channel and a mirror of the ring: tell it to start over */
+    { extern void sdrb200_sdrh_release(const void *); sdrb200_sdrh_release(NULL); }
+#endif
     sdrstat.buff = (unsigned char *)malloc((size_t)cfg->dtype * FILE_BUFFSIZE * blocks);
     if (!sdrstat.buff) return -1;
     g_ringblocks = blocks;

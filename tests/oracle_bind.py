@@ -98,6 +98,17 @@ class Oracle:
         assert rc == 0, f"oh_acquire rc={rc}"
         return list(out), power
 
+    def set_lookahead(self, on: bool):
+        """drop-in build only: sdrb200_sdrh_lookahead of libsdrb200_sdrh.so (1: sdrtracking served from
+        the batched engine's records, 0: one correlator call per code period)"""
+        lib = C.CDLL(os.path.join(ROOT, "erlangnetwork-gnsslib-sdr_b200", "libsdrb200_sdrh.so"))
+        C.c_int.in_dll(lib, "sdrb200_sdrh_lookahead").value = 1 if on else 0
+
+    def lookahead_served(self) -> int:
+        lib = C.CDLL(os.path.join(ROOT, "erlangnetwork-gnsslib-sdr_b200", "libsdrb200_sdrh.so"))
+        lib.sdrb200_sdrh_lookahead_served.restype = C.c_ulonglong
+        return int(lib.sdrb200_sdrh_lookahead_served())
+
     # ---- observables (reference builds of replay.c only)
     def set_logfile(self, path, chno=1):
         """the reference's own writelog output of channel number chno during the next acq_track"""

@@ -3,7 +3,13 @@ cold objects (sdrinit, sdrnav*, sdrrcv, sdrcode, ...) and the same replay of its
 channel thread as the oracle, but every hot sdr.h symbol (sdracquisition,
 sdrtracking, correlator, pcorrelator, cpxfft, pll, dll, ...) resolves to
 libsdrb200_sdrh.so, i.e. to the CUDA library.  Its results are compared with
-the all-reference build on the same IF."""
+the all-reference build on the same IF.
+
+The drop-in's sdrtracking has two modes (sdrb200_sdrh_lookahead): the per-period path (one correlator
+call per code period; loop filters by the host's libm -> the closed loop is BIT-identical to the
+reference's) and the look-ahead path (the batched engine runs a chunk of periods ahead on the device
+and the per-period calls, pll and dll are served from its records -> loop filters by the device's
+libm: integer-class quantities equal, float class within the closed-loop tolerances of DESIGN.md 2)."""
 import numpy as np
 import pytest
 
@@ -34,41 +40,66 @@ def test_dropin_initsdrch_code_spectrum(both):
     assert np.abs(xr - xd).max() <= 2e-5 * np.abs(xr).max()
 
 
-def test_dropin_acquire_and_track(sdr, both):
+FLOAT_CLASS = {"carrfreq": 1e-9, "codefreq": 1e-9}          # relative
+ABS_CLASS = {"remcode": 1e-6, "remcarr": 1e-6, "II": 508.0, "QQ": 508.0, "L0": 2e-2, "D0": 5e-3}
+
+
+def _same(f, a, b, exact):
+    a, b = np.ascontiguousarray(a), np.ascontiguousarray(b)
+    if exact or (f not in FLOAT_CLASS and f not in ABS_CLASS):
+        return np.array_equal(a, b)
+    if f in FLOAT_CLASS:
+        return np.allclose(a, b, rtol=FLOAT_CLASS[f], atol=0)
+    return float(np.abs(a - b).max()) <= ABS_CLASS[f]
+
+
+@pytest.mark.parametrize("lookahead", [False, True])
+def test_dropin_acquire_and_track(sdr, both, lookahead):
     ref, drop = both
+    drop.set_lookahead(lookahead)
     cfg, vis = util.scene_c5(sdr, nsats=3, seed=0xB2000031)
     nper = 400
     host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
     cfgo = ob.cfg_rtlsdr(acq_intg=3)
     a1, r1, n1 = ref.acq_track(cfgo, host, 65536, vis, nper)
+    served0 = drop.lookahead_served()
     a2, r2, n2 = drop.acq_track(cfgo, host, 65536, vis, nper)
     assert n1 == n2
+    # the mode under test is the one that ran: every period came from the engine's records, or none did
+    assert drop.lookahead_served() - served0 == (sum(n2) if lookahead else 0)
     for x, y in zip(a1, a2):
         assert (x.acquired, x.freqi, x.codei, x.nintg_used, x.buffloc) == (y.acquired, y.freqi, y.codei, y.nintg_used, y.buffloc)
         assert abs(x.peakr - y.peakr) <= 1e-3 * x.peakr and abs(x.cn0 - y.cn0) <= 0.01
-    # same host libm on both sides and bit-exact correlator sums: the closed loop is identical
+    # per-period path: same host libm on both sides and bit-exact correlator sums, the closed loop is identical;
+    # look-ahead path: the device's libm closes the loop
     for f in ("currnsamp", "buffloc", "flagsync", "flagloopfilter", "swloop", "synci", "bit", "II", "QQ",
               "carrfreq", "codefreq", "remcode", "remcarr"):
-        assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
+        assert _same(f, r1[f], r2[f], exact=not lookahead), f
+    drop.set_lookahead(True)
 
 
-def test_dropin_one_pthread_per_channel(sdr, both):
+@pytest.mark.parametrize("lookahead", [False, True])
+def test_dropin_one_pthread_per_channel(sdr, both, lookahead):
     """The reference runs every channel in its own pthread (src/sdrmain.c:168-175): the same
     replay with one thread per channel, all calling the drop-in's sdrtracking / correlator /
     pll / dll concurrently, must reproduce the sequential run - and the reference's - bit for
     bit (host libm on both sides), observables included."""
     ref, drop = both
+    drop.set_lookahead(lookahead)
     cfg, vis = util.scene_c5(sdr, nsats=6, seed=0xB2000032)
     nper = 2600
     host = sdr.ifgen_host(cfg, 0, 65536 + (nper + 4) * 2048)
     cfgo = ob.cfg_rtlsdr(acq_intg=3)
     a0, r0, n0 = ref.acq_track(cfgo, host, 65536, vis, nper)
     a1, r1, n1 = drop.acq_track(cfgo, host, 65536, vis, nper)
+    served0 = drop.lookahead_served()
     a2, r2, n2 = drop.acq_track(cfgo, host, 65536, vis, nper, threaded=True)
+    assert drop.lookahead_served() - served0 == (sum(n2) if lookahead else 0)
     a3, r3, n3 = ref.acq_track(cfgo, host, 65536, vis, nper, threaded=True)
     assert n0 == n1 == n2 == n3 and sum(a.acquired for a in a0) >= 5
     for f in ("cnt", "currnsamp", "buffloc", "flagsync", "flagloopfilter", "swloop", "synci", "bit", "II", "QQ",
               "carrfreq", "codefreq", "remcode", "remcarr", "L0", "D0", "flagobs"):
-        base = np.ascontiguousarray(r0[f])
-        for other in (r1, r2, r3):
-            assert np.array_equal(base, np.ascontiguousarray(other[f])), f
+        assert np.array_equal(np.ascontiguousarray(r0[f]), np.ascontiguousarray(r3[f])), f
+        for other in (r1, r2):
+            assert _same(f, r0[f], other[f], exact=not lookahead), f
+    drop.set_lookahead(True)
