@@ -524,7 +524,7 @@ def run_b200(args):
                     "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4 * (nch + 1)},
             "roofline": {"bound": "hbm", "achieved": a_bytes / t_trk / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": a_bytes / t_trk / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "k_trk_run", "algorithmic_bytes_per_launch": a_bytes,
+                         "kernel": "k_trk_cl", "algorithmic_bytes_per_launch": a_bytes,
                          "alu": {"bound": "int32 multiply-add issue", "unit": "Tops/s", "peak": int32_peak,
                                  "achieved": done * NSAMP * 28 * 2 / t_trk / 1e12,
                                  "frac": done * NSAMP * 28 * 2 / t_trk / 1e12 / int32_peak,

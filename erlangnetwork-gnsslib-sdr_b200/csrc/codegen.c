@@ -11,7 +11,9 @@
  * reference's polarity: logic 0 -> -1 ... the reference emits
  * code = -G1*G2 in +-1 arithmetic with registers initialised to -1, i.e.
  * (g1 xor g2) == 1  ->  +1 ... see c/a_chip() below, verified chip-for-chip
- * against the reference generator in tests/test_codegen.py.
+ * against the reference generator: tests/test_oracle_port.py (all 210 PRNs and G1 against
+ * the reference build), tests/golden/codes.npz (the same on machines without the reference) and
+ * tests/test_gpu_primitives.py::test_gencode_on_device (the device twin against this file).
  */
 #include <stdint.h>
 #include <string.h>
