@@ -347,7 +347,9 @@ def run_b200(args):
     s_acq = acq.cuda_stream
     K, W = args.steps, args.warmup
 
-    clocks = ClockSampler(local)
+    # one nvidia-smi poller per box (rank 0 watches its own GPU): eight of them polling every 100 ms
+    # perturb the host-side legs of the other ranks
+    clocks = ClockSampler(local) if rank == 0 else None
     launches0 = sdr.launch_count()
     # ------------------------------------------------ acquisition, HBM-resident
     for _ in range(W):
@@ -355,7 +357,7 @@ def run_b200(args):
     e0, e1 = Evt(sdr), Evt(sdr)
     ms4, c4 = (C.c_double * 4)(), (C.c_longlong * 4)()
     barrier()
-    clocks.mark()
+    if clocks: clocks.mark()
     launches_t0 = sdr.launch_count()
     step_ms = []
     for _ in range(K):
@@ -983,13 +985,19 @@ def run_b200(args):
                     os.dup2(saved, 1); os.close(devnull); os.close(saved)
 
             def _run(o):
-                t0 = time.perf_counter()
-                _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, 1, threaded=True))
-                t_a = time.perf_counter() - t0                      # 12 acquisitions + one period
-                t0 = time.perf_counter()
-                _, _, ntr = _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, nperd, threaded=True))
-                t_all = time.perf_counter() - t0
-                return t_a, max(t_all - t_a, 1e-9), sum(ntr)
+                # tracking time = difference of two replays that share the same 12 acquisitions
+                # (best of 3 each: the acquisitions dominate the short one)
+                nshort = 200
+                ts, tl, ntl = [], [], 0
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    _, _, nts = _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, nshort, threaded=True))
+                    ts.append(time.perf_counter() - t0)
+                    t0 = time.perf_counter()
+                    _, _, ntr = _quiet(lambda: o.acq_track(cfgd, host_par, AVAIL10, TRK_PRNS, nperd, threaded=True))
+                    tl.append(time.perf_counter() - t0)
+                    ntl = sum(ntr) - sum(nts)
+                return min(ts), max(min(tl) - min(ts), 1e-6), ntl
             od, orf = ob.dropin(), ob.ref()
             od.set_lookahead(True)
             _run(od)                                               # warm: plans, engines, mirror
@@ -1002,9 +1010,10 @@ def run_b200(args):
                           "channels": len(TRK_PRNS), "code_periods_per_channel": nperd,
                           "tracking_channel_s_per_s": {"dropin": n_d * 1e-3 / tt_d, "reference": n_r * 1e-3 / tt_r,
                                                        "ratio": (n_d / tt_d) / (n_r / tt_r)},
-                          "acquisition_12_channels_ms": {"dropin": ta_d * 1e3, "reference": ta_r * 1e3},
+                          "acquisition_plus_200_periods_ms": {"dropin": ta_d * 1e3, "reference": ta_r * 1e3},
+                          "timing": "tracking = (replay of 2000 periods) - (replay of 200 periods), best of 3 each, host clock",
                           "periods_served_from_engine_records": served, "host_cores": os.cpu_count()}
-    clk = clocks.stop()
+    clk = clocks.stop() if clocks else None
 
     # ------------------------------------------------ reduce over ranks, print
     tmax, te2e = t_acq, t_e2e
