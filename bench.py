@@ -460,7 +460,7 @@ def run_b200(args):
         phases = None
         if args.trk_profile:
             # cycle counters of channel 0, outside every timed region (sdrb200_trk_profile)
-            out = (C.c_longlong * 16)()
+            out = (C.c_longlong * 32)()
             sdr.check(lib.sdrb200_trk_profile(trk.h, 1, None), "trk_profile")
             trk.reset(); trk.enqueue(st, nper); trk.sync()
             sdr.check(lib.sdrb200_trk_profile(trk.h, 0, out), "trk_profile")
@@ -468,8 +468,14 @@ def run_b200(args):
             names = {0: "code_lane_table_and_walk", 1: "code_lane_waits_and_decisions", 2: "carrier_lane_table_and_walk",
                      3: "carrier_lane_2pi_reduction", 4: "carrier_lane_waits", 11: "carrier_lane_push",
                      5: "epilogue_warp_waiting_for_results", 12: "epilogue_nav", 13: "epilogue_loops", 14: "epilogue_obs_rec",
-                     7: "team0_mix_prefix", 8: "team0_boundaries_taps_report", 9: "team0_waiting_for_hand_out"}
+                     7: "team0_dot_products", 8: "team0_report", 9: "team0_waiting_for_hand_out"}
             phases = {v: round(out[k] / per, 1) for k, v in names.items()}
+            tp = max(1, int(out[31]))
+            sub = {26: "loads_wait_carrier_table", 16: "carrier_words", 27: "wait_code_table", 21: "code_bits", 22: "bar_code_bits",
+                   25: "tap_dot_products", 24: "bar_partials"}
+            phases["team0_per_own_period"] = {v: round(out[k] / tp, 1) for k, v in sub.items()}
+            phases["team0_per_own_period"].update(period_total=round(out[7] / tp, 1), report=round(out[8] / tp, 1),
+                                                  waiting=round(out[9] / tp, 1), periods=tp)
             phases.update(periods=per, quiet_periods=int(out[10]),
                           unit="cycles per period of channel 0 (team0_* per period of the channel, the team sees 1 in W)")
         t_trk = sum(tms) / len(tms) * 1e-3

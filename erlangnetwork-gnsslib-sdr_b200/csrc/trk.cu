@@ -10,6 +10,7 @@
 #include <mutex>
 #include "sdrb200_internal.h"
 #include "trk_device.cuh"
+#include "trk_dot.cuh"
 #include "trk_cluster.cuh"
 
 static std::once_flag g_lut_once;
@@ -580,13 +581,13 @@ extern "C" int sdrb200_trk_profile(sdrb200_trk_t *e, int on, long long *out7)
 {
     if (!e) return SDRB200_EINVAL;
     if (on && !e->d_prof) {
-        SDRB200_CUDA_TRY(cudaMalloc((void **)&e->d_prof, 16 * sizeof(long long)));
-        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
+        SDRB200_CUDA_TRY(cudaMalloc((void **)&e->d_prof, 32 * sizeof(long long)));
+        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 32 * sizeof(long long)));
     }
     if (out7 && e->d_prof) {
         SDRB200_CUDA_TRY(cudaStreamSynchronize(e->st));
-        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 16 * sizeof(long long), cudaMemcpyDeviceToHost));
-        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 16 * sizeof(long long)));
+        SDRB200_CUDA_TRY(cudaMemcpy(out7, e->d_prof, 32 * sizeof(long long), cudaMemcpyDeviceToHost));
+        SDRB200_CUDA_TRY(cudaMemset(e->d_prof, 0, 32 * sizeof(long long)));
     }
     if (!on && e->d_prof) { cudaFree(e->d_prof); e->d_prof = NULL; }
     return SDRB200_OK;
@@ -622,12 +623,13 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
             e->rec_cap = need;
         }
     }
-    size_t smem = sizeof(trk_cl_smem_t) + sizeof(unsigned int) * TRK_WORK_WORDS(e->maxn, e->dtype, e->qcap);
-    if (smem > TRK_SMEM_LIMIT) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
     sdrb200_trk_rec_t *recs = with_rec ? e->d_rec : NULL;
     /* CTA size: the small instantiation when one round of its worker team covers the period */
     const int small = ((size_t)e->maxn * e->dtype + 3 <= (size_t)(TRK_NT_SMALL - TRK_T0) * TRK_SPAN) ? 1 : 0;
     const int nt = small ? TRK_NT_SMALL : TRK_THREADS;
+    size_t smem = ((sizeof(trk_cl_smem_t) + 15) & ~(size_t)15) +
+                  sizeof(unsigned int) * TRKD_WORK_WORDS(e->maxn, 2 * e->smax, (nt - TRK_T0) / 32);
+    if (smem > TRK_SMEM_LIMIT) { sdrb200_set_error("trk_run: code period too long for one CTA"); return SDRB200_EINVAL; }
     const void *fn = (e->dtype == 1) ? (small ? (const void *)k_trk_cl<1, TRK_NT_SMALL> : (const void *)k_trk_cl<1, TRK_THREADS>)
                                      : (small ? (const void *)k_trk_cl<2, TRK_NT_SMALL> : (const void *)k_trk_cl<2, TRK_THREADS>);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

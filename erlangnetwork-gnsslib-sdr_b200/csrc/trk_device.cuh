@@ -93,6 +93,16 @@ __device__ __forceinline__ trk_work_t trk_work_layout(unsigned int *w, int maxn,
     return k;
 }
 
+/* optional cycle stamps inside the worker phases (one thread of one team; pfp == NULL: off) */
+struct trk_wprof_t { long long *p; long long t0; };
+__device__ __forceinline__ void trk_wstamp(trk_wprof_t *w, int i)
+{
+    if (w && w->p) {
+        long long t1; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t1)::"memory");
+        atomicAdd((unsigned long long *)&w->p[i], (unsigned long long)(t1 - w->t0)); w->t0 = t1;   /* RED: no stall */
+    }
+}
+
 template <int NW>
 __device__ __forceinline__ void trk_bar_workers()
 {
@@ -256,7 +266,7 @@ __device__ __forceinline__ int trk_sbyte(unsigned int w, int b)
 /* NW worker threads, the first of them thread T0 of the CTA (defaults: the single-CTA layout) */
 template <int DTYPE, int NW = TRK_WORKERS, int T0 = 64>
 __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__restrict__ data, int n,
-                                               const trk_work_t &wk)
+                                               const trk_work_t &wk, trk_wprof_t *wp = nullptr)
 {
     constexpr int S = TRK_SPAN / DTYPE, RS = S + 1;     /* samples per row, row stride (pairs) */
     constexpr int ROUND_BYTES = NW * TRK_SPAN, NWARP = NW / 32;
@@ -280,6 +290,7 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
 #define TRK_BYTE(j) trk_sbyte(w[(j) >> 2], (j) & 3)
             trk_cursor_t cur;
             cur.start(sm->icarr, sm->carr.nseg, max(kfirst, 0));
+            trk_wstamp(wp, 26);
             uint2 *rowp = wk.P2 + (size_t)row * RS;
 #define TRK_MIX(j, idx)                                                                             \
             {                                                                                       \
@@ -319,7 +330,9 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
             const int i = atomicAdd(&sm->nslow[0], 1);
             if (i < 128) sm->slow[0][i] = row; else sm->err = 3;
         }
+        trk_wstamp(wp, 16);
         trk_bar_workers<NW>();
+        trk_wstamp(wp, 17);
         {
             const int ns_ = min(sm->nslow[0], 128);
             for (int it = wwarp; it < ns_; it += NWARP) {
@@ -346,7 +359,9 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
                 if (lane == S - 1) wk.base[srow] = make_uint2(I, Q);      /* row total, picked up by the owner */
             }
         }
+        trk_wstamp(wp, 18);
         trk_bar_workers<NW>();
+        trk_wstamp(wp, 19);
         if (slow) { const uint2 tt = wk.base[row]; runI = tt.x; runQ = tt.y; }
         if (u == 0) sm->nslow[0] = 0;                     /* next round */
         DBG(3);
@@ -376,6 +391,7 @@ __device__ __forceinline__ void trk_mix_prefix(trk_smem_t *sm, const int8_t *__r
             if (u == 0) { sm->carry[0] += allI; sm->carry[1] += allQ; }
             trk_bar_workers<NW>();
         }
+        trk_wstamp(wp, 20);
     }
 }
 
@@ -405,7 +421,7 @@ __device__ __forceinline__ uint2 trk_prefix2_at(const trk_work_t &wk, int a, int
  * sm->sum is read.                                                               */
 template <int DTYPE, int NW = TRK_WORKERS, int T0 = 64>
 __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &wk, const int8_t *data, int n,
-                                             const int *taps, int ns, int smax)
+                                             const int *taps, int ns, int smax, trk_wprof_t *wp = nullptr)
 {
     const int t = threadIdx.x - T0, lane = threadIdx.x & 31, wwarp = t >> 5;
     const int a = (int)((uintptr_t)data & 3);
@@ -421,6 +437,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
             slow = true;
             if (p0 > 0) {
                 cur.start(sm->icode, sm->code.nseg, p0 - 1);
+                trk_wstamp(wp, 27);
                 if (p1 <= cur.next_k0 && cur.negm == 0 && cur.D > 0) {
                     /* the span and its left neighbour lie in one segment of a rising code
                      * phase: chips prev+1 .. clast start inside the span; the start of chip c
@@ -456,7 +473,9 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
             const int i = atomicAdd(&sm->nslow[1], 1);
             if (i < 128) sm->slow[1][i] = t; else sm->err = 3;
         }
+        trk_wstamp(wp, 21);
         trk_bar_workers<NW>();
+        trk_wstamp(wp, 22);
         const int ns_ = min(sm->nslow[1], 128);
         for (int it = wwarp; it < ns_; it += NW / 32) {
             const int q0 = sm->slow[1][it] * PP, q1 = min(q0 + PP, N);
@@ -476,7 +495,9 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         }
     }
     DBG(6);
+    trk_wstamp(wp, 23);
     trk_bar_workers<NW>();
+    trk_wstamp(wp, 24);
     DBG(7);
     /* (b) one lane per (tap, queue entry): a lane reads the (I,Q) prefix pair of its position
      * once and accumulates both sums, so a tap costs one lookup per entry; the 32 / ntap lane
@@ -505,6 +526,7 @@ __device__ __forceinline__ void trk_tap_sums(trk_smem_t *sm, const trk_work_t &w
         if (accI) atomicAdd(&sm->sum[tap], accI);
         if (accQ) atomicAdd(&sm->sum[SDRB200_MAXTAPS + tap], accQ);
     }
+    trk_wstamp(wp, 25);
     DBG(8);
 }
 

@@ -22,6 +22,9 @@
  * (src/sdrnav.c:241-262, src/sdrmain.c:271-280), so in between the NCO lanes run ahead of
  * the correlators and consecutive periods are correlated concurrently on different SMs.
  */
+#ifndef TRK_PROF_THREAD
+#define TRK_PROF_THREAD 416                  /* worker whose cycle stamps sdrb200_trk_profile reports */
+#endif
 #define TRK_T0      160                      /* first worker thread                         */
 #define TRK_RING    16                       /* periods in flight: result / hand-over ring   */
 
@@ -135,7 +138,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
     constexpr int NW = NT - TRK_T0, R = TRK_RING;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     trk_cl_smem_t *sm = (trk_cl_smem_t *)smem_raw;
-    const trk_work_t wk = trk_work_layout<DTYPE>((unsigned int *)(smem_raw + sizeof(trk_cl_smem_t)), maxn, qcap);
+    const trkd_work_t wk = trkd_work_layout((unsigned int *)(smem_raw + ((sizeof(trk_cl_smem_t) + 15) & ~(size_t)15)), NW / 32);
     const int rank = (int)cl_rank(), CL = (int)cl_size();
     const int chno = blockIdx.x / CL;
     const int r0 = (ctrl_works || CL == 1) ? 0 : 1;     /* first rank whose worker team takes periods */
@@ -154,6 +157,8 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
     for (int i = threadIdx.x; i < chg->clen; i += NT) sm->t.codetab[i] = chg->code[i];
     if (threadIdx.x < chg->corrn) sm->taps[threadIdx.x] = chg->corrp[threadIdx.x];
     trk_init_smem(&sm->t);
+    __syncthreads();
+    trkd_init<DTYPE>(wk, &sm->t, chg->clen, sm->taps, chg->corrn, NT);
     if (ctrl) {
         const uint32_t *src = (const uint32_t *)&states[chno];
         uint32_t *dst = (uint32_t *)st;
@@ -213,7 +218,7 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 if (q >= 2) cl_flag_wait_ge(&sm->pushed[1], q - 1);                     /* rhdr / raw buffer q & 1 is free */
                 sm->rhdr[1][q & 1].n = go ? n : -1; sm->rhdr[1][q & 1].q = q; sm->rhdr[1][q & 1].boff = boff;
                 cl_flag_set(&sm->hdr_seq, q + 1);                                       /* the pusher sends the header (or leaves) */
-                if (pf && quiet) prof[10] += 1;
+                if (pf && quiet) atomicAdd((unsigned long long *)&prof[10], 1ull);
             }
             TRK_PF(1);                                       /* code lane: waits + period decisions */
             go = __shfl_sync(0xffffffffu, go, 0);
@@ -382,9 +387,10 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
     } else if (wid >= TRK_T0 / 32 && rank >= r0) {
         /* ================= worker team: one whole code period per hand-out */
         const int t = threadIdx.x - TRK_T0;
-        const bool pfw = (prof != nullptr) && chno == 0 && rank == r0 && t == 0;
+        const bool pfw = (prof != nullptr) && chno == 0 && rank == r0 && t == TRK_PROF_THREAD;
         long long wt0 = pfw ? trk_clock() : 0;
-#define TRK_PFW(i) do { if (pfw) { const long long t1_ = trk_clock(); prof[i] += t1_ - wt0; wt0 = t1_; } } while (0)
+        trk_wprof_t wpf; wpf.p = pfw ? prof : nullptr; wpf.t0 = wt0;
+#define TRK_PFW(i) do { if (pfw) { const long long t1_ = trk_clock(); atomicAdd((unsigned long long *)&prof[i], (unsigned long long)(t1_ - wt0)); wt0 = t1_; wpf.t0 = t1_; } } while (0)
         for (int i = 0;; i++) {
             const int slot = i & 1;
             const uint32_t par = (uint32_t)((i >> 1) & 1);
@@ -401,22 +407,14 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                     if (W > 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(data + (size_t)n * DTYPE * W + off));
                 }
             }
-            cl_mbar_wait(&sm->fullc[slot], par);
             TRK_PFW(9);                                      /* team: waiting for a hand-out */
-            if (t == 0) {
-                sm->t.icarr = sm->t.segs[2 * slot]; sm->t.icode = sm->t.segs[2 * slot + 1];
-                sm->t.carr.nseg = h->ncarr;
-                sm->t.carry[0] = 0u; sm->t.carry[1] = 0u; sm->t.qcount = 0; sm->t.nslow[0] = 0; sm->t.nslow[1] = 0;
-            }
-            if (t < 2 * SDRB200_MAXTAPS) sm->t.sum[t] = 0u;
-            trk_bar_workers<NW>();
-            trk_mix_prefix<DTYPE, NW, TRK_T0>(&sm->t, data, n, wk);
-            cl_mbar_wait(&sm->fullk[slot], par);
-            if (t == 0) sm->t.code.nseg = h->ncode;
-            trk_bar_workers<NW>();                       /* all prefix rows written; code table here */
-            TRK_PFW(7);                                      /* team: wipe-off + prefix sums */
-            trk_tap_sums<DTYPE, NW, TRK_T0>(&sm->t, wk, data, n, sm->taps, ns, smax);
-            trk_bar_workers<NW>();
+            if (pfw) atomicAdd((unsigned long long *)&prof[31], 1ull);
+            trkd_period<DTYPE, TRK_SPAN, NW, TRK_T0>(&sm->t, wk, data, n, ns, smax, i & 1, 0, 1,
+                                           sm->t.segs[2 * slot], sm->t.segs[2 * slot + 1],
+                                           [&]() -> int { cl_mbar_wait(&sm->fullc[slot], par); return h->ncarr; },
+                                           [&]() -> int { cl_mbar_wait(&sm->fullk[slot], par); return h->ncode; }, &wpf);
+            trk_bar_workers<NW>();                       /* sm->t.sum complete */
+            TRK_PFW(7);                                      /* team: the period's dot products */
             if (t < 32) {
                 const int q = h->q;
                 const uint32_t dst = cl_map(&sm->res[q % R][0], 0);
@@ -424,7 +422,6 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
                 if (lane == 0) cl_st_u32(dst + 4u * (2 * SDRB200_MAXTAPS), (uint32_t)sm->t.err);
                 cl_mbar_arrive_remote(cl_map(&sm->done[q % R], 0));
             }
-            trk_bar_workers<NW>();                       /* sums and header consumed before the next period resets them */
             TRK_PFW(8);                                      /* team: chip boundaries + tap sums + report */
         }
     }
