@@ -20,20 +20,66 @@
 #define FFT_PAD(i) ((i) + ((i) >> 4))
 #define FFT_SMEM_ELEMS(L) ((L) + ((L) >> 4) + 16)
 
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+/* Packed fp32 arithmetic of sm_100a: add/sub/mul/fma.rn.f32x2 work on a 64-bit register
+ * pair and compile to FADD2 / FMUL2 / FFMA2, whose operand modifiers (half swap, scalar
+ * broadcast, per-half negation) ptxas derives from the float2 shuffles written below - so a
+ * complex add is ONE instruction and a complex multiply TWO (FMUL2 + FFMA2) instead of 2 and 4.
+ * The kernel is issue/latency bound, not fp32-pipe bound, so halving the instruction count of
+ * the butterflies is what counts (tools/f32x2bench.cu measures the rates).                    */
+__device__ __forceinline__ float2 f2add(float2 a, float2 b)
+{
+    float2 r;
+    asm("{.reg .b64 ra, rb, rc; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; add.rn.f32x2 rc, ra, rb; mov.b64 {%0,%1}, rc;}"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return r;
+}
+__device__ __forceinline__ float2 f2sub(float2 a, float2 b)
+{
+    float2 r;
+    asm("{.reg .b64 ra, rb, rc; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; sub.rn.f32x2 rc, ra, rb; mov.b64 {%0,%1}, rc;}"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return r;
+}
+__device__ __forceinline__ float2 f2mul(float2 a, float2 b)
+{
+    float2 r;
+    asm("{.reg .b64 ra, rb, rc; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mul.rn.f32x2 rc, ra, rb; mov.b64 {%0,%1}, rc;}"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+    return r;
+}
+__device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c)
+{
+    float2 r;
+    asm("{.reg .b64 ra, rb, rc, rd; mov.b64 ra, {%2,%3}; mov.b64 rb, {%4,%5}; mov.b64 rc, {%6,%7}; "
+        "fma.rn.f32x2 rd, ra, rb, rc; mov.b64 {%0,%1}, rd;}"
+        : "=f"(r.x), "=f"(r.y) : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y), "f"(c.x), "f"(c.y));
+    return r;
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return f2add(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return f2sub(a, b); }
+/* a * b = b.x * a + b.y * (i a) */
 __device__ __forceinline__ float2 cmul(float2 a, float2 b)
 {
-    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+    return f2fma(make_float2(-a.y, a.x), make_float2(b.y, b.y), f2mul(make_float2(b.x, b.x), a));
 }
-__device__ __forceinline__ float2 cmulc(float2 a, float2 b)      /* a * conj(b) */
+/* a * conj(b) = b.x * a + b.y * (-i a) */
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b)
 {
-    return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
+    return f2fma(make_float2(a.y, -a.x), make_float2(b.y, b.y), f2mul(make_float2(b.x, b.x), a));
 }
 /* multiply by SIGN*i : SIGN=-1 -> (y,-x) ; SIGN=+1 -> (-y,x) */
 template <int SIGN> __device__ __forceinline__ float2 crot(float2 a)
 {
     return SIGN < 0 ? make_float2(a.y, -a.x) : make_float2(-a.y, a.x);
+}
+/* c + SIGN*i*d and c - SIGN*i*d as one FFMA2 each (multiplier (1,1), swap and half negation as modifiers) */
+template <int SIGN> __device__ __forceinline__ float2 caddrot(float2 c, float2 d)
+{
+    return f2fma(make_float2(d.y, d.x), SIGN < 0 ? make_float2(1.f, -1.f) : make_float2(-1.f, 1.f), c);
+}
+template <int SIGN> __device__ __forceinline__ float2 csubrot(float2 c, float2 d)
+{
+    return f2fma(make_float2(d.y, d.x), SIGN < 0 ? make_float2(-1.f, 1.f) : make_float2(1.f, -1.f), c);
 }
 /* exp(SIGN * 2*pi*i * K/16) as a compile-time constant */
 template <int SIGN, int K> __device__ __forceinline__ float2 cw16(float2 a)
@@ -52,7 +98,7 @@ template <int SIGN, int K> __device__ __forceinline__ float2 cw16(float2 a)
     if (k == 8) return make_float2(-a.x, -a.y);
     if (k == 12) return crot<-SIGN>(a);
     const float c = C[k], s = (SIGN < 0) ? -S[k] : S[k];
-    return make_float2(a.x * c - a.y * s, a.x * s + a.y * c);
+    return f2fma(make_float2(-a.y, a.x), make_float2(s, s), f2mul(make_float2(c, c), a));
 }
 
 /* 4-point DFT in place on (a0,a1,a2,a3): b_u = sum_t a_t w4^(t*u), w4 = SIGN*i */
@@ -60,11 +106,11 @@ template <int SIGN>
 __device__ __forceinline__ void fft4(float2 &a0, float2 &a1, float2 &a2, float2 &a3)
 {
     float2 s02 = cadd(a0, a2), d02 = csub(a0, a2);
-    float2 s13 = cadd(a1, a3), d13 = crot<SIGN>(csub(a1, a3));
+    float2 s13 = cadd(a1, a3), d13 = csub(a1, a3);
     a0 = cadd(s02, s13);
     a2 = csub(s02, s13);
-    a1 = cadd(d02, d13);
-    a3 = csub(d02, d13);
+    a1 = caddrot<SIGN>(d02, d13);
+    a3 = csubrot<SIGN>(d02, d13);
 }
 
 /* 16-point DFT: v[u] = sum_t v[t] w16^(t*u), natural order in and out.
