@@ -22,12 +22,14 @@
  *   k_comb  recombine, |.|^2, accumulate P, per-row max / masked mean / 2nd max
  *   k_final per-PRN argmax over bins, C/N0, peak ratio, early-exit freeze
  */
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
 #include "sdrb200_internal.h"
 #include "nco_exact.h"
 #include "fft_device.cuh"
+#include "trk_cluster.cuh"
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -62,6 +64,9 @@ struct sdrb200_acq {
     acq_rowstat_t *d_row;            /* [nprn][nfreq] (legacy path only)      */
     unsigned long long *d_key;       /* [nprn] argmax keys (fused path)       */
     int fused, keep_power;
+    int push;                        /* k_rowd (bulk-copy exchange) instead of k_roww (remote loads)        */
+    int warp32;                      /* M = 32 x 1024: one warp per sub-transform (k_roww)                  */
+    int rowp_ncl;                    /* k_roww / k_rowd: clusters launched (co-resident on this GPU)         */
     sdrb200_acq_result_t *d_res, *h_res;
     sdrb200_acq_result_t *d_hist;    /* [intg][nprn] tuples after every integration step (Doppler-slab searches) */
     int *d_frozen;
@@ -406,6 +411,8 @@ template <int G, int SIGN> __device__ __forceinline__ void fft_small(float2 (&z)
         o1 = cw16<SIGN, 2>(o1); o2 = cw16<SIGN, 4>(o2); o3 = cw16<SIGN, 6>(o3);
         z[0] = cadd(e0, o0); z[1] = cadd(e1, o1); z[2] = cadd(e2, o2); z[3] = cadd(e3, o3);
         z[4] = csub(e0, o0); z[5] = csub(e1, o1); z[6] = csub(e2, o2); z[7] = csub(e3, o3);
+    } else if constexpr (G == 32) {
+        fft32<SIGN, false>(z);
     } else {
         static_assert(G == 16, "unsupported group count");
         fft16<SIGN>(z);
@@ -512,9 +519,24 @@ k_fwd_split_small(const int8_t *__restrict__ win, int nlive, const uint8_t *__re
         out[((size_t)f * R + q) * L + t] = (q == 0) ? z[0] : cmul(z[q], __ldg(&tw[(t * q) & (M - 1)]));
 }
 
+/* operand order of the warp kernels (k_roww / k_rowd): lane l of a warp owns the points l + 32 e;
+ * points e = 2h and 2h + 1 of a lane are stored next to each other so that one 16-byte load
+ * fetches both: position of point j = (j >> 6) * 64 + (j & 31) * 2 + ((j >> 5) & 1)            */
+__host__ __device__ __forceinline__ int acq_pair_pos(int j) { return (j >> 6) * 64 + (j & 31) * 2 + ((j >> 5) & 1); }
+
+/* one-time reordering of the code-spectrum bank into that order (rows of 1024 points) */
+__global__ void __launch_bounds__(1024)
+k_pair_order(float2 *__restrict__ X)
+{
+    float2 *row = X + (size_t)blockIdx.x * 1024;
+    const float2 v = row[threadIdx.x];
+    __syncthreads();
+    row[acq_pair_pos(threadIdx.x)] = v;
+}
+
 template <int L>
 __global__ void __launch_bounds__(L / 16)
-k_fft_rows(float2 *__restrict__ X, const float2 *__restrict__ tw, int R)
+k_fft_rows(float2 *__restrict__ X, const float2 *__restrict__ tw, int R, int pair_order)
 {
     extern __shared__ float2 fsm[];
     constexpr int T = L / 16;
@@ -523,6 +545,12 @@ k_fft_rows(float2 *__restrict__ X, const float2 *__restrict__ tw, int R)
 #pragma unroll
     for (int e = 0; e < 16; e++) v[e] = row[threadIdx.x + e * T];
     cta_fft<L, -1>(v, fsm, tw, R);
+    if (pair_order) {                                   /* layout of the warp kernels, see acq_pair_pos */
+        __syncthreads();                                /* in place: every thread has loaded its points */
+#pragma unroll
+        for (int e = 0; e < 16; e++) row[acq_pair_pos(threadIdx.x + e * T)] = v[e];
+        return;
+    }
 #pragma unroll
     for (int e = 0; e < 16; e++) row[threadIdx.x + e * T] = v[e];
 }
@@ -916,6 +944,506 @@ k_rowc(const acq_rowc_args A)
     cl_wait();
 }
 
+#define ROWP_MAXPRN 1024
+
+/* ------------------------------------------------ one warp per sub-transform
+ * k_roww: M = 32 x 1024.  A cluster of 8 CTAs x 4 warps owns a row; every WARP transforms one of
+ * the 32 residue classes by itself (warp_fft1024: 32 points per lane, one transpose through the
+ * warp's own shared-memory tile, no CTA barrier inside the transform), and every thread finishes
+ * ONE column t' of the radix-32 recombination - 32 remote 8-byte loads, twiddles, a 32-point
+ * transform of which only the 16 outputs below M/2 are formed (lags < n <= M/2).
+ * Against the 8 x 4096 split this trades one shared-memory exchange per point for a longer
+ * register butterfly: 32 instead of 48 bytes of shared-memory traffic per point, a third fewer
+ * instructions (the pruned stage is 5 of 15 radix-2 levels instead of 3), two CTA barriers per row
+ * instead of six.  The clusters are persistent (as many as the GPU holds at once, each walking a
+ * contiguous run of rows numbered over the PRNs still searched, src/sdracq.c:38-42) and rows are
+ * pipelined over two tiles per warp:
+ *   warp, row i (tile b = i & 1): operands -> product -> first 32-point pass in registers,
+ *        wait FREE[b]  (every warp of the cluster has gathered row i-2 out of the tiles b),
+ *        transpose + second pass through tile b, results left there, release-arrive READY[b] at all
+ *        eight CTAs; wait READY[1-b], gather column t' of row i-1 from the 32 tiles (1-b), recombine,
+ *        power, argmax in registers until the PRN changes, arrive FREE[1-b] at all eight CTAs.
+ * READY/FREE are mbarriers counting one arrival per warp of the cluster; a warp only waits for what
+ * its peers did a whole sub-transform ago, and there is no CTA barrier in the loop.
+ * MODE 1 is checkacquisition for the winning row of each PRN (one cluster per PRN).            */
+template <int MODE>
+__global__ void __launch_bounds__(128, 3)
+k_roww(const acq_rowc_args A, int nprn)
+{
+    extern __shared__ __align__(16) float2 psm[];         /* [2 buffers][4 warps][WFFT_TILE] */
+    __shared__ __align__(8) unsigned long long s_ready[2], s_free[2];
+    __shared__ unsigned short s_act[ROWP_MAXPRN];
+    __shared__ int s_na;
+    __shared__ acq_part_t s_part[4];
+    __shared__ acq_part_t s_cta;
+    constexpr int CS = 8, WPC = 4, R = CS * WPC, L = 1024, NT = 32 * WPC, NA = R / 2, BUF = WPC * WFFT_TILE;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t c = cl_rank();
+    const int cid = blockIdx.x / CS, ncl = gridDim.x / CS;
+    const int q = (int)c * WPC + warp;                    /* residue class of this warp */
+    const int tcol = (int)c * (L / CS) + tid;             /* column t' of this thread   */
+
+    if (MODE == 1) { if (A.frozen[cid]) return; }         /* whole cluster leaves */
+    if (tid < 32) {
+        int na = 0;
+        if (MODE == 0) {
+            for (int base = 0; base < nprn; base += 32) {
+                const int p = base + lane;
+                const bool on = (p < nprn) && !A.frozen[p];
+                const unsigned m = __ballot_sync(0xffffffffu, on);
+                if (on) s_act[na + __popc(m & ((1u << lane) - 1u))] = (unsigned short)p;
+                na += __popc(m);
+            }
+        }
+        if (lane == 0) {
+            s_na = na;
+            cl_mbar_init(&s_ready[0], R); cl_mbar_init(&s_ready[1], R);      /* one arrival per WARP of the cluster */
+            cl_mbar_init(&s_free[0], R);  cl_mbar_init(&s_free[1], R);
+            cl_fence_mbar_init();
+        }
+    }
+    __syncthreads();
+    cl_sync_all();
+
+    int r0, r1, codei = 0, fpk = 0;
+    float maxp = 0.f;
+    bool from_hbm = false;
+    if (MODE == 0) {
+        const int nrows = s_na * A.nfreq;
+        const int rpc = (nrows + ncl - 1) / ncl;
+        r0 = cid * rpc; r1 = min(r0 + rpc, nrows);
+    } else {
+        const unsigned long long k = A.key[cid];
+        const unsigned int flat = k ? 0xffffffffu - (unsigned int)(k & 0xffffffffu) : 0u;
+        fpk = (int)(flat / (unsigned int)A.n_eff);
+        codei = (int)(flat - (unsigned int)fpk * (unsigned int)A.n_eff);
+        maxp = __uint_as_float((unsigned int)(k >> 32));
+        from_hbm = (A.P != nullptr);
+        r0 = 0; r1 = from_hbm ? 0 : 1;
+    }
+
+    float2 w1 = __ldg(&A.tw[lane * R]); w1.y = -w1.y;     /* exp(+2 pi i lane / 1024)      */
+    const float2 wc = __ldg(&A.tw[tcol]);                 /* W_M^(t'), used conjugated     */
+
+    float bv = -1.f; unsigned int bflat = 0; int pcur = -1;
+    auto flush = [&]() {
+        unsigned long long b = 0ull;
+        if (bv >= 0.f) b = ((unsigned long long)__float_as_uint(bv) << 32) | (unsigned long long)(0xffffffffu - bflat);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+            if (ob > b) b = ob;
+        }
+        if (lane == 0 && b && pcur >= 0) atomicMax(&A.key[pcur], b);
+        bv = -1.f; bflat = 0;
+    };
+
+    float pw[NA];                                         /* MODE 1 keeps the row's powers */
+    int pp = 0, pf = 0, i = 0;
+    for (int r = r0; r <= r1 && r0 < r1; r++, i++) {
+        const int b = i & 1;
+        int p = 0, f = 0;
+        if (r < r1) {
+            if (MODE == 0) { const int pa = r / A.nfreq; f = r - pa * A.nfreq; p = s_act[pa]; }
+            else { p = cid; f = fpk; }
+            float2 *tile = psm + (b * WPC + warp) * WFFT_TILE;
+            const float2 *x = A.Xs + ((size_t)f * R + q) * L;
+            const float2 *cc = A.Cs + ((size_t)p * R + q) * L;
+            float2 v[32];
+#pragma unroll
+            for (int h = 0; h < 16; h++) {                /* pair order: points 2h, 2h+1 of this lane in 16 bytes */
+                const float4 xa = __ldg((const float4 *)x + 32 * h + lane), ca = __ldg((const float4 *)cc + 32 * h + lane);
+                v[2 * h] = cmulc(make_float2(xa.x, xa.y), make_float2(ca.x, ca.y));
+                v[2 * h + 1] = cmulc(make_float2(xa.z, xa.w), make_float2(ca.z, ca.w));
+            }
+            warp_fft1024<+1>(v, tile, w1, [&]() { if (i >= 2) cl_mbar_wait(&s_free[b], (uint32_t)(((i >> 1) - 1) & 1)); });
+#pragma unroll
+            for (int e = 0; e < 32; e++) tile[lane + 32 * e] = v[e];
+            /* the warp publishes its own tile: no CTA barrier anywhere in the row loop */
+            __syncwarp();
+            if (lane < CS) cl_mbar_arrive_remote(cl_map(&s_ready[b], (uint32_t)lane));
+        }
+        if (i >= 1) {
+            const int pb = b ^ 1;
+            cl_mbar_wait(&s_ready[pb], (uint32_t)(((i - 1) >> 1) & 1));
+            float2 z[32];
+            const uint32_t mine = cl_smem_u32(psm + pb * BUF + tcol);
+#pragma unroll
+            for (int rr = 0; rr < CS; rr++) {
+                uint32_t base;
+                asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(base) : "r"(mine), "r"(rr));
+#pragma unroll
+                for (int ww = 0; ww < WPC; ww++) {
+                    float2 t;
+                    asm volatile("ld.shared::cluster.v2.f32 {%0, %1}, [%2];" : "=f"(t.x), "=f"(t.y)
+                                 : "r"(base + (uint32_t)(ww * WFFT_TILE * sizeof(float2))) : "memory");
+                    z[rr * WPC + ww] = t;
+                }
+            }
+            twiddle32<true>(z, wc);                       /* z_q *= conj(W_M^(t'))^q */
+            fft32<+1, true>(z);
+#pragma unroll
+            for (int a = 0; a < NA; a++) pw[a] = (z[a].x * z[a].x + z[a].y * z[a].y) * A.invM2;
+            /* this warp's share of FREE for all eight owners.  Reads-before-arrive only, so the light
+             * arrive (release at CTA scope) is enough - but the loads must have RETURNED in every lane,
+             * and ptxas hoists an arrive that does not depend on them right behind the loads (repeated
+             * searches then differed).  pw[0] depends on all 32 loads of a lane and the vote on every
+             * lane's pw[0]; the arrival count 1 + (a power is negative: never) is computed from it.    */
+            const uint32_t one = 1u + (__ballot_sync(0xffffffffu, pw[0] < 0.f) != 0u);
+            if (lane < CS) cl_mbar_arrive_remote_light(cl_map(&s_free[pb], (uint32_t)lane), one);
+
+            if (MODE == 0) {
+                if (pp != pcur) { flush(); pcur = pp; }
+                /* branch-free: lags at or beyond n_eff get power -1 and never win; the accumulating path
+                 * (cpxconv flagsum, src/sdrcmn.c:244-246) is a uniform branch around the whole loop     */
+                if (A.P) {
+                    float *Prow = A.P + ((size_t)pp * A.nfreq + pf) * A.n_eff;
+#pragma unroll
+                    for (int a = 0; a < NA; a++) {
+                        const int t = tcol + L * a;
+                        if (t < A.n_eff) { float xw = pw[a]; if (!A.first_step) xw += Prow[t]; Prow[t] = xw; pw[a] = xw; }
+                        else pw[a] = -1.f;
+                    }
+                } else {
+#pragma unroll
+                    for (int a = NA / 2; a < NA; a++) pw[a] = (tcol + L * a < A.n_eff) ? pw[a] : -1.f;   /* n_eff > M/4 */
+                }
+                float lv = -1.f; int la = 0;
+#pragma unroll
+                for (int a = 0; a < NA; a++) { const bool up = pw[a] > lv; lv = up ? pw[a] : lv; la = up ? a : la; }
+                if (lv > bv) { bv = lv; bflat = (unsigned int)pf * (unsigned int)A.n_eff + (unsigned int)(tcol + L * la); }
+            }
+        }
+        pp = p; pf = f;
+    }
+    if (MODE == 0) {
+        flush();
+        cl_sync_all();                                    /* nobody leaves while a peer may still read */
+        return;
+    }
+
+    /* MODE 1: masked statistics around the known peak (src/sdracq.c:79-88) */
+    if (from_hbm) {
+        const float *Prow = A.P + ((size_t)cid * A.nfreq + fpk) * A.n_eff;
+#pragma unroll
+        for (int a = 0; a < NA; a++) { const int t = tcol + L * a; pw[a] = (t < A.n_eff) ? Prow[t] : 0.f; }
+    }
+    int exs = codei - 2 * A.nsampchip; if (exs < 0) exs += A.n_eff;
+    int exe = codei + 2 * A.nsampchip; if (exe >= A.n_eff) exe -= A.n_eff;
+    double sum = 0.0; int cnt = 0; float m2 = -1.f;
+#pragma unroll
+    for (int a = 0; a < NA; a++) {
+        const int t = tcol + L * a;
+        if (t < A.n_eff) {
+            const bool inc = (exs <= exe) ? (t < exs || t > exe) : (t < exs && t > exe);
+            if (inc) { sum += (double)pw[a]; cnt++; }
+            if ((inc || t == 0) && pw[a] > m2) m2 = pw[a];            /* maxvd seeds with data[0] */
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    }
+    if (lane == 0) { s_part[warp].sum = sum; s_part[warp].cnt = cnt; s_part[warp].max2 = m2; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < WPC; w++) { sum += s_part[w].sum; cnt += s_part[w].cnt; m2 = fmaxf(m2, s_part[w].max2); }
+        s_cta.sum = sum; s_cta.cnt = cnt; s_cta.max2 = m2;
+    }
+    cl_sync_all();
+    if (c == 0 && tid == 0) {
+        for (uint32_t rr = 1; rr < CS; rr++) {
+            const uint32_t ad = cl_map(&s_cta, rr);
+            double os; int oc; float om;
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(os) : "r"(ad) : "memory");
+            asm volatile("ld.shared::cluster.s32 %0, [%1];" : "=r"(oc) : "r"(ad + 8) : "memory");
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(om) : "r"(ad + 12) : "memory");
+            sum += os; cnt += oc; m2 = fmaxf(m2, om);
+        }
+        sdrb200_acq_result_t o;
+        o.maxp = (double)maxp; o.maxp2 = (double)m2;
+        o.meanp = sum / (double)cnt;                               /* meanvd, sdrcmn.c:487-497 */
+        o.cn0 = 10 * log10(o.maxp / o.meanp / A.ctime);            /* sdracq.c:84 */
+        o.peakr = o.maxp / o.maxp2;                                /* sdracq.c:88 */
+        o.codei = codei; o.freqi = fpk; o.acqfreq = A.freq[fpk];
+        o.acquired = (o.peakr > A.thresh) ? 1 : 0;
+        o.nintg = A.step + 1;
+        A.res[cid] = o;
+        if (o.acquired) A.frozen[cid] = 1;
+        A.key[cid] = 0ull;                                         /* next integration step */
+    }
+    cl_sync_all();
+}
+
+/* ------------------------------------------------ bulk-copy exchange
+ * k_rowd: the same warp-per-sub-transform arithmetic as k_roww, but the sub-transforms are PUSHED:
+ * a cluster is 4 CTAs x 8 warps (one CTA per SM, every SM loaded alike); a warp leaves its 1024
+ * results in its tile and one lane sends the four 2 KB slices to the four CTAs of the cluster with
+ * cp.async.bulk (shared::cta -> shared::cluster, UBLKCP), each copy completing bytes on the
+ * receiver's READY mbarrier.  No cluster-scope fence (the release of a generic store to remote
+ * readers is a MEMBAR.GPU per warp and row: 13 % of k_roww's stall samples), no remote loads
+ * (8 % more): a thread reads its 32 inputs of the recombination from LOCAL shared memory.  Two
+ * receive buffers per CTA pipeline the rows; FREE mbarriers (32 warp arrivals) hand a buffer back to
+ * the producers.  With one CTA per SM the registers allow the operands of row i+1 to be loaded
+ * while row i-1 is recombined.                                                                   */
+__device__ __forceinline__ void bulk_push(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t mbar_cluster)
+{
+    asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(mbar_cluster) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(void *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(cl_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cta(void *bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(cl_smem_u32(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+
+#define ROWD_CS 4
+#define ROWD_WPC 8
+#define ROWD_SMEM (sizeof(float2) * (ROWD_WPC * WFFT_TILE + 2 * 32 * (1024 / ROWD_CS)))
+template <int MODE>
+__global__ void __launch_bounds__(32 * ROWD_WPC, 1)
+k_rowd(const acq_rowc_args A, int nprn)
+{
+    extern __shared__ __align__(16) float2 psm[];         /* [8 warps][WFFT_TILE] tiles, then recv[2][32][256] */
+    __shared__ __align__(8) unsigned long long s_ready[2], s_free[2];
+    __shared__ unsigned short s_act[ROWP_MAXPRN];
+    __shared__ int s_na;
+    __shared__ acq_part_t s_part[ROWD_WPC];
+    __shared__ acq_part_t s_cta;
+    constexpr int CS = ROWD_CS, WPC = ROWD_WPC, R = CS * WPC, L = 1024, NA = R / 2, NCOL = L / CS;
+    constexpr uint32_t SLICE = NCOL * sizeof(float2);     /* bytes one warp sends to one CTA */
+    static_assert(R == 32 && NCOL == 32 * WPC, "one column per thread");
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t c = cl_rank();
+    const int cid = blockIdx.x / CS, ncl = gridDim.x / CS;
+    const int q = (int)c * WPC + warp;                    /* residue class of this warp */
+    const int tcol = (int)c * NCOL + tid;                 /* column t' of this thread   */
+    float2 *tile = psm + warp * WFFT_TILE;
+    float2 *recv = psm + WPC * WFFT_TILE;
+
+    if (MODE == 1) { if (A.frozen[cid]) return; }         /* whole cluster leaves */
+    if (tid < 32) {
+        int na = 0;
+        if (MODE == 0) {
+            for (int base = 0; base < nprn; base += 32) {
+                const int p = base + lane;
+                const bool on = (p < nprn) && !A.frozen[p];
+                const unsigned m = __ballot_sync(0xffffffffu, on);
+                if (on) s_act[na + __popc(m & ((1u << lane) - 1u))] = (unsigned short)p;
+                na += __popc(m);
+            }
+        }
+        if (lane == 0) {
+            s_na = na;
+            cl_mbar_init(&s_ready[0], 1); cl_mbar_init(&s_ready[1], 1);      /* one arming arrival + 32 KB of copies */
+            cl_mbar_init(&s_free[0], R);  cl_mbar_init(&s_free[1], R);       /* one arrival per warp of the cluster  */
+            cl_fence_mbar_init();
+            mbar_expect_tx(&s_ready[0], R * SLICE);
+            mbar_expect_tx(&s_ready[1], R * SLICE);
+        }
+    }
+    __syncthreads();
+    cl_sync_all();
+
+    int r0, r1, codei = 0, fpk = 0;
+    float maxp = 0.f;
+    bool from_hbm = false;
+    if (MODE == 0) {
+        const int nrows = s_na * A.nfreq;
+        const int rpc = (nrows + ncl - 1) / ncl;
+        r0 = cid * rpc; r1 = min(r0 + rpc, nrows);
+    } else {
+        const unsigned long long k = A.key[cid];
+        const unsigned int flat = k ? 0xffffffffu - (unsigned int)(k & 0xffffffffu) : 0u;
+        fpk = (int)(flat / (unsigned int)A.n_eff);
+        codei = (int)(flat - (unsigned int)fpk * (unsigned int)A.n_eff);
+        maxp = __uint_as_float((unsigned int)(k >> 32));
+        from_hbm = (A.P != nullptr);
+        r0 = 0; r1 = from_hbm ? 0 : 1;
+    }
+
+    float2 w1 = __ldg(&A.tw[lane * R]); w1.y = -w1.y;     /* exp(+2 pi i lane / 1024)      */
+    const float2 wc = __ldg(&A.tw[tcol]);                 /* W_M^(t'), used conjugated     */
+
+    float bv = -1.f; unsigned int bflat = 0; int pcur = -1;
+    auto flush = [&]() {
+        unsigned long long b = 0ull;
+        if (bv >= 0.f) b = ((unsigned long long)__float_as_uint(bv) << 32) | (unsigned long long)(0xffffffffu - bflat);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long ob = __shfl_xor_sync(0xffffffffu, b, o);
+            if (ob > b) b = ob;
+        }
+        if (lane == 0 && b && pcur >= 0) atomicMax(&A.key[pcur], b);
+        bv = -1.f; bflat = 0;
+    };
+    auto row_of = [&](int r, int &p, int &f) {
+        if (MODE == 0) { const int pa = r / A.nfreq; f = r - pa * A.nfreq; p = s_act[pa]; }
+        else { p = cid; f = fpk; }
+    };
+
+    float pw[NA];                                         /* MODE 1 keeps the row's powers */
+    float4 xv[16], cv[16];                                /* operands of the coming row, pair order */
+    int pn = 0, fn = 0, pc = 0, fc = 0, pq = 0, fq = 0, i = 0;
+    if (r0 < r1) {
+        row_of(r0, pn, fn);
+        const float2 *x = A.Xs + ((size_t)fn * R + q) * L, *cc = A.Cs + ((size_t)pn * R + q) * L;
+#pragma unroll
+        for (int h = 0; h < 16; h++) { xv[h] = __ldg((const float4 *)x + 32 * h + lane); cv[h] = __ldg((const float4 *)cc + 32 * h + lane); }
+    }
+    for (int r = r0; r <= r1 && r0 < r1; r++, i++) {
+        const int b = i & 1;
+        pq = pc; fq = fc; pc = pn; fc = fn;
+        if (r < r1) {
+            float2 v[32];
+#pragma unroll
+            for (int h = 0; h < 16; h++) {
+                v[2 * h] = cmulc(make_float2(xv[h].x, xv[h].y), make_float2(cv[h].x, cv[h].y));
+                v[2 * h + 1] = cmulc(make_float2(xv[h].z, xv[h].w), make_float2(cv[h].z, cv[h].w));
+            }
+            /* the tile is the source of the previous row's copies: they must have read it */
+            warp_fft1024<+1>(v, tile, w1, [&]() { if (lane == 0) bulk_wait_read0(); __syncwarp(); });
+#pragma unroll
+            for (int e = 0; e < 32; e++) tile[lane + 32 * e] = v[e];
+            fence_proxy_async_smem();                     /* generic-proxy stores -> visible to the copy engine */
+            __syncwarp();
+            if (i >= 2) cl_mbar_wait(&s_free[b], (uint32_t)(((i >> 1) - 1) & 1));   /* receivers are done with buffer b */
+            if (lane == 0) {
+                const uint32_t src = cl_smem_u32(tile);
+                const uint32_t dst = cl_smem_u32(recv + ((size_t)(b * R + q)) * NCOL);
+                const uint32_t bar = cl_smem_u32(&s_ready[b]);
+#pragma unroll
+                for (int c2 = 0; c2 < CS; c2++) {
+                    uint32_t d, m;
+                    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(d) : "r"(dst), "r"(c2));
+                    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(m) : "r"(bar), "r"(c2));
+                    bulk_push(d, src + c2 * SLICE, SLICE, m);
+                }
+                bulk_commit();
+            }
+            if (r + 1 < r1) {                             /* operands of the next row fly during the recombination */
+                row_of(r + 1, pn, fn);
+                const float2 *x = A.Xs + ((size_t)fn * R + q) * L, *cc = A.Cs + ((size_t)pn * R + q) * L;
+#pragma unroll
+                for (int h = 0; h < 16; h++) { xv[h] = __ldg((const float4 *)x + 32 * h + lane); cv[h] = __ldg((const float4 *)cc + 32 * h + lane); }
+            }
+        }
+        if (i >= 1) {                                     /* row i-1 = (pq, fq), receive buffer pb */
+            const int pb = b ^ 1;
+            mbar_wait_cta(&s_ready[pb], (uint32_t)(((i - 1) >> 1) & 1));
+            float2 z[32];
+            const float2 *rb = recv + (size_t)(pb * R) * NCOL + tid;
+#pragma unroll
+            for (int qq = 0; qq < R; qq++) z[qq] = rb[qq * NCOL];
+            twiddle32<true>(z, wc);                       /* z_q *= conj(W_M^(t'))^q */
+            fft32<+1, true>(z);
+#pragma unroll
+            for (int a = 0; a < NA; a++) pw[a] = (z[a].x * z[a].x + z[a].y * z[a].y) * A.invM2;
+            /* this warp has read its part of buffer pb: tell the producer warps of all CTAs, and arm the
+             * buffer for the row after next (its copies start once FREE completes).  The arrival count
+             * is computed from every lane's pw[0] so that the arrive cannot be scheduled before the
+             * loads have returned (see k_roww).                                                      */
+            const uint32_t one = 1u + (__ballot_sync(0xffffffffu, pw[0] < 0.f) != 0u);
+            if (lane < CS) cl_mbar_arrive_remote_light(cl_map(&s_free[pb], (uint32_t)lane), one);
+            if (tid == 0 && r + 1 < r1) mbar_expect_tx(&s_ready[pb], R * SLICE);
+            if (MODE == 0) {
+                if (pq != pcur) { flush(); pcur = pq; }
+                /* branch-free: lags at or beyond n_eff get power -1 and never win; the accumulating path
+                 * (cpxconv flagsum, src/sdrcmn.c:244-246) is a uniform branch around the whole loop     */
+                if (A.P) {
+                    float *Prow = A.P + ((size_t)pq * A.nfreq + fq) * A.n_eff;
+#pragma unroll
+                    for (int a = 0; a < NA; a++) {
+                        const int t = tcol + L * a;
+                        if (t < A.n_eff) { float xw = pw[a]; if (!A.first_step) xw += Prow[t]; Prow[t] = xw; pw[a] = xw; }
+                        else pw[a] = -1.f;
+                    }
+                } else {
+#pragma unroll
+                    for (int a = NA / 2; a < NA; a++) pw[a] = (tcol + L * a < A.n_eff) ? pw[a] : -1.f;   /* n_eff > M/4 */
+                }
+                float lv = -1.f; int la = 0;
+#pragma unroll
+                for (int a = 0; a < NA; a++) { const bool up = pw[a] > lv; lv = up ? pw[a] : lv; la = up ? a : la; }
+                if (lv > bv) { bv = lv; bflat = (unsigned int)fq * (unsigned int)A.n_eff + (unsigned int)(tcol + L * la); }
+            }
+        }
+    }
+    if (lane == 0) bulk_wait0();                          /* my copies have landed before my shared memory goes away */
+    if (MODE == 0) {
+        flush();
+        cl_sync_all();
+        return;
+    }
+
+    /* MODE 1: masked statistics around the known peak (src/sdracq.c:79-88) */
+    if (from_hbm) {
+        const float *Prow = A.P + ((size_t)cid * A.nfreq + fpk) * A.n_eff;
+#pragma unroll
+        for (int a = 0; a < NA; a++) { const int t = tcol + L * a; pw[a] = (t < A.n_eff) ? Prow[t] : 0.f; }
+    }
+    int exs = codei - 2 * A.nsampchip; if (exs < 0) exs += A.n_eff;
+    int exe = codei + 2 * A.nsampchip; if (exe >= A.n_eff) exe -= A.n_eff;
+    double sum = 0.0; int cnt = 0; float m2 = -1.f;
+#pragma unroll
+    for (int a = 0; a < NA; a++) {
+        const int t = tcol + L * a;
+        if (t < A.n_eff) {
+            const bool inc = (exs <= exe) ? (t < exs || t > exe) : (t < exs && t > exe);
+            if (inc) { sum += (double)pw[a]; cnt++; }
+            if ((inc || t == 0) && pw[a] > m2) m2 = pw[a];            /* maxvd seeds with data[0] */
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        m2 = fmaxf(m2, __shfl_xor_sync(0xffffffffu, m2, o));
+    }
+    if (lane == 0) { s_part[warp].sum = sum; s_part[warp].cnt = cnt; s_part[warp].max2 = m2; }
+    __syncthreads();
+    if (tid == 0) {
+        for (int w = 1; w < WPC; w++) { sum += s_part[w].sum; cnt += s_part[w].cnt; m2 = fmaxf(m2, s_part[w].max2); }
+        s_cta.sum = sum; s_cta.cnt = cnt; s_cta.max2 = m2;
+    }
+    cl_sync_all();
+    if (c == 0 && tid == 0) {
+        for (uint32_t rr = 1; rr < CS; rr++) {
+            const uint32_t ad = cl_map(&s_cta, rr);
+            double os; int oc; float om;
+            asm volatile("ld.shared::cluster.f64 %0, [%1];" : "=d"(os) : "r"(ad) : "memory");
+            asm volatile("ld.shared::cluster.s32 %0, [%1];" : "=r"(oc) : "r"(ad + 8) : "memory");
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(om) : "r"(ad + 12) : "memory");
+            sum += os; cnt += oc; m2 = fmaxf(m2, om);
+        }
+        sdrb200_acq_result_t o;
+        o.maxp = (double)maxp; o.maxp2 = (double)m2;
+        o.meanp = sum / (double)cnt;                               /* meanvd, sdrcmn.c:487-497 */
+        o.cn0 = 10 * log10(o.maxp / o.meanp / A.ctime);            /* sdracq.c:84 */
+        o.peakr = o.maxp / o.maxp2;                                /* sdracq.c:88 */
+        o.codei = codei; o.freqi = fpk; o.acqfreq = A.freq[fpk];
+        o.acquired = (o.peakr > A.thresh) ? 1 : 0;
+        o.nintg = A.step + 1;
+        A.res[cid] = o;
+        if (o.acquired) A.frozen[cid] = 1;
+        A.key[cid] = 0ull;                                         /* next integration step */
+    }
+    cl_sync_all();
+}
+
 /* ------------------------------------------------------------- host side */
 template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int nitems, const int8_t *src,
                                        size_t item_stride, int dtype, int nlive, const uint8_t *cidx,
@@ -974,7 +1502,7 @@ template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fft_rows<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_fft_rows<L><<<dim3(a->R, a->cfg.nfreq), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R);
+    k_fft_rows<L><<<dim3(a->R, a->cfg.nfreq), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R, a->warp32 ? 1 : 0);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
@@ -996,7 +1524,7 @@ static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t 
     case 2:   return launch_fwd_split_small_r<2>(st, a, win, scale);
     case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale);
     case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale);
-    case 32:  return launch_fwd_split_g<2>(st, a, win, scale);
+    case 32:  return launch_fwd_split_g<2>(st, a, win, scale);   /* one thread per t with a 32-point register stage: 38 vs 34 us */
     case 64:  return launch_fwd_split_g<4>(st, a, win, scale);
     case 128: return launch_fwd_split_g<8>(st, a, win, scale);
     case 256: return launch_fwd_split_g<16>(st, a, win, scale);
@@ -1048,6 +1576,77 @@ template <int L, int R, int MODE> static int launch_rowc(cudaStream_t st, const 
     return SDRB200_OK;
 }
 
+template <int MODE> static int roww_config(cudaLaunchConfig_t *cfg, cudaLaunchAttribute *at, cudaStream_t st, int ncl)
+{
+    const size_t smem = 2 * 4 * sizeof(float2) * WFFT_TILE;
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_roww<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    *cfg = cudaLaunchConfig_t{};
+    cfg->gridDim = dim3(8 * ncl, 1, 1);
+    cfg->blockDim = dim3(128, 1, 1);
+    cfg->dynamicSmemBytes = smem;
+    cfg->stream = st;
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 8; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg->attrs = at; cfg->numAttrs = 1;
+    return SDRB200_OK;
+}
+static int roww_max_clusters(int *ncl)
+{
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    int rc = roww_config<0>(&cfg, at, 0, 1024);
+    if (rc) return rc;
+    int n = 0;
+    SDRB200_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, k_roww<0>, &cfg));
+    *ncl = n;
+    return SDRB200_OK;
+}
+/* mode 0: the search over ncl persistent clusters; mode 1: one cluster per PRN */
+static int launch_roww(int mode, cudaStream_t st, const acq_rowc_args &A, int nprn, int ncl)
+{
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    int rc = mode ? roww_config<1>(&cfg, at, st, nprn) : roww_config<0>(&cfg, at, st, ncl);
+    if (rc) return rc;
+    if (mode) SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_roww<1>, A, nprn));
+    else SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_roww<0>, A, nprn));
+    sdrb200_count_launch(1);
+    return SDRB200_OK;
+}
+
+template <int MODE> static int rowd_config(cudaLaunchConfig_t *cfg, cudaLaunchAttribute *at, cudaStream_t st, int ncl)
+{
+    const size_t smem = ROWD_SMEM;
+    SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowd<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    *cfg = cudaLaunchConfig_t{};
+    cfg->gridDim = dim3(ROWD_CS * ncl, 1, 1);
+    cfg->blockDim = dim3(32 * ROWD_WPC, 1, 1);
+    cfg->dynamicSmemBytes = smem;
+    cfg->stream = st;
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = ROWD_CS; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg->attrs = at; cfg->numAttrs = 1;
+    return SDRB200_OK;
+}
+static int rowd_max_clusters(int *ncl)
+{
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    int rc = rowd_config<0>(&cfg, at, 0, 1024);
+    if (rc) return rc;
+    int n = 0;
+    SDRB200_CUDA_TRY(cudaOccupancyMaxActiveClusters(&n, k_rowd<0>, &cfg));
+    *ncl = n;
+    return SDRB200_OK;
+}
+static int launch_rowd(int mode, cudaStream_t st, const acq_rowc_args &A, int nprn, int ncl)
+{
+    cudaLaunchConfig_t cfg; cudaLaunchAttribute at[1];
+    int rc = mode ? rowd_config<1>(&cfg, at, st, nprn) : rowd_config<0>(&cfg, at, st, ncl);
+    if (rc) return rc;
+    if (mode) SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_rowd<1>, A, nprn));
+    else SDRB200_CUDA_TRY(cudaLaunchKernelEx(&cfg, k_rowd<0>, A, nprn));
+    sdrb200_count_launch(1);
+    return SDRB200_OK;
+}
+
 static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_rowc_args &A, int nfreq_grid, int nprn)
 {
 #define RC(LL, RR) if (L == LL && R == RR) return mode ? launch_rowc<LL, RR, 1>(st, A, nfreq_grid, nprn) \
@@ -1091,7 +1690,7 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
 /* M = R * L.  Up to R = 8 the R sub-transforms of a row are finished inside one
  * thread-block cluster (k_rowc); longer windows (20 ms coherent blocks) use the
  * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
-static void acq_choose(int M, int *L, int *R, int *fused)
+static void acq_choose(int M, int *L, int *R, int *fused, int *warp32)
 {
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
     if (lsub > 16384) lsub = 8192;                                   /* scratch path */
@@ -1099,6 +1698,13 @@ static void acq_choose(int M, int *L, int *R, int *fused)
     if (env) { int v = atoi(env); if ((v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) && v <= M) lsub = v; }
     *L = lsub; *R = M / lsub;
     *fused = (*R <= 8 && !getenv("SDRB200_ACQ_SCRATCH")) ? 1 : 0;
+    /* M = 32768 as 32 sub-transforms of 1024 points, one WARP each (k_roww / k_rowd): measured
+     * alternatives to the 8 x 4096 cluster kernel, selected with SDRB200_ACQ_WARP=pull|push      */
+    *warp32 = 0;
+    const char *wsel = getenv("SDRB200_ACQ_WARP");
+    if (M == 32768 && *fused && !env && wsel && (!strcmp(wsel, "pull") || !strcmp(wsel, "push"))) {
+        *L = 1024; *R = 32; *warp32 = (wsel[1] == 'u' && wsel[2] == 's') ? 2 : 1;
+    }
 }
 
 extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *cfg)
@@ -1116,7 +1722,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->n_eff = cfg->nsamp * a->cfg.ncoh;
     a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
     a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
-    acq_choose(a->M, &a->L, &a->R, &a->fused);
+    acq_choose(a->M, &a->L, &a->R, &a->fused, &a->warp32);
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }
     a->h_freq = (double *)malloc(sizeof(double) * nfreq);
@@ -1139,12 +1745,26 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
          * the walking forward kernel), SDRB200_FWD_WALK (walking forward kernel on the cluster path) */
         const int naive = getenv("SDRB200_ACQ_COMB_NAIVE") != NULL;
         a->comb_fft = (!a->fused && a->R > 1 && comb_fft_supported(a->R) && !naive) ? 1 : 0;
-        a->split_fwd = (a->comb_fft || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8) &&
+        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8) &&
                                         !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }
     }
     int rc = SDRB200_OK;
+    /* the warp-per-sub-transform kernels are persistent: as many clusters as the GPU holds at once */
+    a->rowp_ncl = 0;
+    if (a->warp32 && nprn > ROWP_MAXPRN) { sdrb200_set_error("acq_create: more than %d PRNs in one plan", ROWP_MAXPRN); free(a->h_freq); free(a); return SDRB200_EINVAL; }
+    if (a->warp32) {
+        int ncl = 0;
+        a->push = (a->warp32 == 2);
+        int rc2 = a->push ? rowd_max_clusters(&ncl) : roww_max_clusters(&ncl);
+        if (rc2 || ncl < 1) { sdrb200_set_error("acq_create: k_roww cannot be resident"); free(a->h_freq); free(a); return SDRB200_ECUDA; }
+        const int rows = nprn * nfreq;
+        a->rowp_ncl = ncl < rows ? ncl : rows;
+        const char *env = getenv("SDRB200_ROWP_NCL");
+        if (env && atoi(env) >= 1 && atoi(env) <= ncl) a->rowp_ncl = atoi(env);
+        if (getenv("SDRB200_VERBOSE")) fprintf(stderr, "sdrb200: k_roww/k_rowd: %d co-resident clusters, %d used for %d rows\n", ncl, a->rowp_ncl, rows);
+    }
 #define ACQ_ALLOC(ptr, bytes) if (rc == SDRB200_OK && cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) { \
         cudaGetLastError(); sdrb200_set_error("acq_create: cudaMalloc(%zu) failed", (size_t)(bytes)); rc = SDRB200_ENOMEM; }
     if (cudaStreamCreateWithFlags(&a->st, cudaStreamNonBlocking) != cudaSuccess) rc = SDRB200_ECUDA;
@@ -1220,6 +1840,10 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
             else {
                 cudaMemcpyAsync(d_rc, h, (size_t)nprn * n_eff, cudaMemcpyHostToDevice, a->st);
                 ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(1, a->st, a->R, nprn, d_rc, (size_t)n_eff, 1, n_eff, NULL, 0, 1.0f, a->d_tw, a->d_Cs)));
+                if (rc == SDRB200_OK && a->warp32) {
+                    k_pair_order<<<nprn * a->R, 1024, 0, a->st>>>(a->d_Cs);
+                    if (cudaGetLastError() != cudaSuccess) rc = SDRB200_ECUDA;
+                }
                 cudaStreamSynchronize(a->st);
                 cudaFree(d_rc);
             }
@@ -1301,11 +1925,13 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
             A.nsampchip = c->nsampchip; A.first_step = (step == 0); A.step = step;
             A.invM2 = 1.0f / ((float)a->M * (float)a->M);
             ACQ_T0(a);
-            rc = launch_rowc_any(a->L, a->R, 0, a->st, A, c->nfreq, c->nprn);
+            if (a->warp32) rc = a->push ? launch_rowd(0, a->st, A, c->nprn, a->rowp_ncl) : launch_roww(0, a->st, A, c->nprn, a->rowp_ncl);
+            else rc = launch_rowc_any(a->L, a->R, 0, a->st, A, c->nfreq, c->nprn);
             if (rc) return rc;
             ACQ_T1(a, 1);
             ACQ_T0(a);
-            rc = launch_rowc_any(a->L, a->R, 1, a->st, A, 1, c->nprn);
+            if (a->warp32) rc = a->push ? launch_rowd(1, a->st, A, c->nprn, 0) : launch_roww(1, a->st, A, c->nprn, 0);
+            else rc = launch_rowc_any(a->L, a->R, 1, a->st, A, 1, c->nprn);
             if (rc) return rc;
             ACQ_T1(a, 3);
             if (a->d_hist)

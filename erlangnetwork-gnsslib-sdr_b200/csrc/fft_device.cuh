@@ -135,6 +135,79 @@ __device__ __forceinline__ void fft16(float2 (&v)[16])
 #undef FFT_SWAP
 }
 
+/* exp(SIGN * 2*pi*i * K/32) * a, K = 0..15 */
+template <int SIGN, int K> __device__ __forceinline__ float2 cw32(float2 a)
+{
+    constexpr float C[16] = {1.f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f,
+                             0.70710678118654752f, 0.55557023301960218f, 0.38268343236508977f, 0.19509032201612825f,
+                             0.f, -0.19509032201612825f, -0.38268343236508977f, -0.55557023301960218f,
+                             -0.70710678118654752f, -0.83146961230254524f, -0.92387953251128674f, -0.98078528040323043f};
+    constexpr float S[16] = {0.f, 0.19509032201612825f, 0.38268343236508977f, 0.55557023301960218f,
+                             0.70710678118654752f, 0.83146961230254524f, 0.92387953251128674f, 0.98078528040323043f,
+                             1.f, 0.98078528040323043f, 0.92387953251128674f, 0.83146961230254524f,
+                             0.70710678118654752f, 0.55557023301960218f, 0.38268343236508977f, 0.19509032201612825f};
+    static_assert(K >= 0 && K < 16, "cw32: K in 0..15");
+    if (K == 0) return a;
+    if (K == 8) return crot<SIGN>(a);
+    const float c = C[K], s = (SIGN < 0) ? -S[K] : S[K];
+    return f2fma(make_float2(-a.y, a.x), make_float2(s, s), f2mul(make_float2(c, c), a));
+}
+
+/* 32-point DFT in registers, natural order in and out: even/odd 16-point transforms and one
+ * radix-2 stage.  HALF: only outputs 0..15 are formed (v[16..31] are left undefined) - the
+ * recombination of 32 sub-transforms needs lags below half the transform length only.       */
+template <int SIGN, bool HALF>
+__device__ __forceinline__ void fft32(float2 (&v)[32])
+{
+    float2 e[16], o[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) { e[k] = v[2 * k]; o[k] = v[2 * k + 1]; }
+    fft16<SIGN>(e);
+    fft16<SIGN>(o);
+#define FFT32_OUT(K) { const float2 t = cw32<SIGN, K>(o[K]); v[K] = cadd(e[K], t); if (!HALF) v[K + 16] = csub(e[K], t); }
+    FFT32_OUT(0) FFT32_OUT(1) FFT32_OUT(2) FFT32_OUT(3) FFT32_OUT(4) FFT32_OUT(5) FFT32_OUT(6) FFT32_OUT(7)
+    FFT32_OUT(8) FFT32_OUT(9) FFT32_OUT(10) FFT32_OUT(11) FFT32_OUT(12) FFT32_OUT(13) FFT32_OUT(14) FFT32_OUT(15)
+#undef FFT32_OUT
+}
+
+/* v[k] *= w^k for k = 1..31: w^16 by four squarings, then one running power w^k that serves
+ * v[k] and (times w^16) v[k+16]; CONJ multiplies by the conjugates                          */
+template <bool CONJ>
+__device__ __forceinline__ void twiddle32(float2 (&v)[32], float2 w)
+{
+    const float2 w2 = cmul(w, w), w4 = cmul(w2, w2), w8 = cmul(w4, w4), w16 = cmul(w8, w8);
+    v[16] = CONJ ? cmulc(v[16], w16) : cmul(v[16], w16);
+    float2 wk = w;
+#pragma unroll
+    for (int k = 1; k < 16; k++) {
+        const float2 wh = cmul(wk, w16);
+        v[k] = CONJ ? cmulc(v[k], wk) : cmul(v[k], wk);
+        v[k + 16] = CONJ ? cmulc(v[k + 16], wh) : cmul(v[k + 16], wh);
+        if (k < 15) wk = cmul(wk, w);
+    }
+}
+
+/* 1024-point transform by ONE WARP: lane l holds v[e] = x[l + 32 e] on entry and X[l + 32 e] on
+ * exit.  x = 32-point transform over e in registers, twiddle W_1024^(l a), transpose through the
+ * warp's own 33 x 32 shared-memory tile (no CTA barrier), 32-point transform over l.
+ * w1 = exp(SIGN 2 pi i l / 1024) of this lane.  before_smem() as in cta_fft_pre_hook.        */
+#define WFFT_TILE 1056
+template <int SIGN, typename Hook>
+__device__ __forceinline__ void warp_fft1024(float2 (&v)[32], float2 *tile, float2 w1, Hook before_smem)
+{
+    const int lane = threadIdx.x & 31;
+    fft32<SIGN, false>(v);
+    twiddle32<false>(v, w1);
+    before_smem();
+#pragma unroll
+    for (int a = 0; a < 32; a++) tile[a * 33 + lane] = v[a];
+    __syncwarp();
+#pragma unroll
+    for (int l = 0; l < 32; l++) v[l] = tile[lane * 33 + l];
+    __syncwarp();
+    fft32<SIGN, false>(v);
+}
+
 /* final pass of radix RL (2, 4 or 8) over the 16 registers: 16/RL butterflies,
  * butterfly i uses elements e = i + t*(16/RL); no twiddles (m == 1).          */
 template <int SIGN, int RL>
@@ -202,8 +275,13 @@ __device__ __forceinline__ void cta_fft_twiddles(const float2 *__restrict__ tw, 
     }
 }
 
-template <int L, int SIGN>
-__device__ __forceinline__ void cta_fft_pre(float2 (&v)[16], float2 *sm, const float2 (&w)[fft_plan_t<L>::N16])
+struct fft_no_hook { __device__ __forceinline__ void operator()() const {} };
+
+/* before_smem() runs once, after the register part of the first pass and before the first write to
+ * sm: a caller whose buffer is still being read (by peer CTAs) waits there instead of up front    */
+template <int L, int SIGN, typename Hook>
+__device__ __forceinline__ void cta_fft_pre_hook(float2 (&v)[16], float2 *sm, const float2 (&w)[fft_plan_t<L>::N16],
+                                                 Hook before_smem)
 {
     using P = fft_plan_t<L>;
     constexpr int T = P::T;
@@ -236,6 +314,7 @@ __device__ __forceinline__ void cta_fft_pre(float2 (&v)[16], float2 *sm, const f
              * s >= 16: FFT_PAD(idx) = q + (q >> 4) + 17*ps + u*(s + s/16)        */
             float2 *const sbase = sm + ((s == 1) ? 17 * tid : q + (q >> 4) + 17 * ps);
             const int sstep = (s == 1) ? 1 : s + s / 16;
+            if (pass == 0) before_smem();
 #pragma unroll
             for (int u = 0; u < 16; u++) sbase[sstep * u] = v[u];
             __syncthreads();
@@ -246,6 +325,12 @@ __device__ __forceinline__ void cta_fft_pre(float2 (&v)[16], float2 *sm, const f
         s *= 16;
     }
     if (P::RL > 1) fft_tail<SIGN, P::RL>(v);
+}
+
+template <int L, int SIGN>
+__device__ __forceinline__ void cta_fft_pre(float2 (&v)[16], float2 *sm, const float2 (&w)[fft_plan_t<L>::N16])
+{
+    cta_fft_pre_hook<L, SIGN>(v, sm, w, fft_no_hook());
 }
 
 template <int L, int SIGN>

@@ -49,6 +49,14 @@ __device__ __forceinline__ void cl_mbar_arrive_remote(uint32_t cluster_addr)
 {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+/* the same without the cluster-scope release: for "I am done READING your shared memory" signals,
+ * where nothing this thread wrote has to become visible to the other side.  The instruction carries
+ * no dependency on the loads it follows and ptxas schedules it right behind them, before their data
+ * has returned: the caller passes a count (1) COMPUTED FROM the loaded data                        */
+__device__ __forceinline__ void cl_mbar_arrive_remote_light(uint32_t cluster_addr, uint32_t count)
+{
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_addr), "r"(count) : "memory");
+}
 __device__ __forceinline__ int cl_mbar_try_wait(void *bar, uint32_t parity)
 {
     uint32_t ok;
