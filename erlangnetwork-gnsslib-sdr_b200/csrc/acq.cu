@@ -1179,15 +1179,15 @@ k_roww(const acq_rowc_args A, int nprn)
 
 /* ------------------------------------------------ bulk-copy exchange
  * k_rowd: the same warp-per-sub-transform arithmetic as k_roww, but the sub-transforms are PUSHED:
- * a cluster is 4 CTAs x 8 warps (one CTA per SM, every SM loaded alike); a warp leaves its 1024
- * results in its tile and one lane sends the four 2 KB slices to the four CTAs of the cluster with
+ * a cluster is 8 CTAs x 4 warps (two CTAs per SM); a warp leaves its 1024
+ * results in its tile and one lane sends the eight 1 KB slices to the eight CTAs of the cluster with
  * cp.async.bulk (shared::cta -> shared::cluster, UBLKCP), each copy completing bytes on the
  * receiver's READY mbarrier.  No cluster-scope fence (the release of a generic store to remote
  * readers is a MEMBAR.GPU per warp and row: 13 % of k_roww's stall samples), no remote loads
  * (8 % more): a thread reads its 32 inputs of the recombination from LOCAL shared memory.  Two
  * receive buffers per CTA pipeline the rows; FREE mbarriers (32 warp arrivals) hand a buffer back to
- * the producers.  With one CTA per SM the registers allow the operands of row i+1 to be loaded
- * while row i-1 is recombined.                                                                   */
+ * the producers.  With eight warps per SM the registers allow the operands of row i+1 to be loaded
+ * while row i-1 is recombined.                                                                  */
 __device__ __forceinline__ void bulk_push(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t mbar_cluster)
 {
     asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -1210,11 +1210,11 @@ __device__ __forceinline__ void mbar_wait_cta(void *bar, uint32_t parity)
     } while (!ok);
 }
 
-#define ROWD_CS 4
-#define ROWD_WPC 8
+#define ROWD_CS 8
+#define ROWD_WPC 4
 #define ROWD_SMEM (sizeof(float2) * (ROWD_WPC * WFFT_TILE + 2 * 32 * (1024 / ROWD_CS)))
 template <int MODE>
-__global__ void __launch_bounds__(32 * ROWD_WPC, 1)
+__global__ void __launch_bounds__(32 * ROWD_WPC, 2)
 k_rowd(const acq_rowc_args A, int nprn)
 {
     extern __shared__ __align__(16) float2 psm[];         /* [8 warps][WFFT_TILE] tiles, then recv[2][32][256] */
@@ -1320,7 +1320,7 @@ k_rowd(const acq_rowc_args A, int nprn)
             for (int e = 0; e < 32; e++) tile[lane + 32 * e] = v[e];
             fence_proxy_async_smem();                     /* generic-proxy stores -> visible to the copy engine */
             __syncwarp();
-            if (i >= 2) cl_mbar_wait(&s_free[b], (uint32_t)(((i >> 1) - 1) & 1));   /* receivers are done with buffer b */
+            if (i >= 2) mbar_wait_cta(&s_free[b], (uint32_t)(((i >> 1) - 1) & 1));  /* receivers are done with buffer b (no data rides on FREE: CTA-scope wait) */
             if (lane == 0) {
                 const uint32_t src = cl_smem_u32(tile);
                 const uint32_t dst = cl_smem_u32(recv + ((size_t)(b * R + q)) * NCOL);
