@@ -745,36 +745,61 @@ def run_b200(args):
         st3 = sdr.Stream(2, avail3)
         st3.push_ifgen(sdr.make_ifgen(fs3, 0.0, 1.602e9, 2, sats3, sigma=2.5, seed=0xB2000300 + rank, crate=0.511e6, clen=511, bitlen=10), avail3)
         code3, crate3 = sdr.gencode(1, 20)
-        plans3 = [sdr.Acquisition(fs3, 2, ns3, int(ns3 / 511), 1e-3,
-                                  np.array([(i - nf3 // 2) * 200.0 + 562500.0 * k_ for i in range(nf3)]),
-                                  code3[None, :], crate3, intg=intg3, threshold=1e30) for k_ in ks3]   # every step runs
+        grids3 = np.array([[(i - nf3 // 2) * 200.0 + 562500.0 * k_ for i in range(nf3)] for k_ in ks3])   # src/sdrinit.c:633-635
         b3 = avail3 - need3
-        for _ in range(2):
-            for pl in plans3: pl.enqueue(st3, b3)
-            g3 = [pl.fetch()[0] for pl in plans3]
-        t3 = []
-        for _ in range(3):
-            sdr.check(lib.sdrb200_l2_flush(C.c_void_p(plans3[0].cuda_stream)), "l2_flush")
-            barrier()
-            t0 = time.perf_counter()
-            for pl in plans3: pl.enqueue(st3, b3)
-            for pl in plans3: pl.sync()
-            t3.append(time.perf_counter() - t0)
-        g3 = [pl.fetch()[0] for pl in plans3]
-        t3m = min(t3)
-        if dist is not None:
-            tt = torch.tensor([t3m], dtype=torch.float64, device="cuda")
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            t3m = float(tt[0])
+
+        def _time3(plans):
+            for _ in range(2):
+                for pl in plans: pl.enqueue(st3, b3)
+                for pl in plans: pl.sync()
+            ts = []
+            for _ in range(3):
+                sdr.check(lib.sdrb200_l2_flush(C.c_void_p(plans[0].cuda_stream)), "l2_flush")
+                barrier()
+                t0 = time.perf_counter()
+                for pl in plans: pl.enqueue(st3, b3)
+                for pl in plans: pl.sync()
+                ts.append(time.perf_counter() - t0)
+            tm = min(ts)
+            if dist is not None:
+                tt = torch.tensor([tm], dtype=torch.float64, device="cuda")
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                tm = float(tt[0])
+            return tm
+        # ONE plan: the G1 code once per channel, every channel over its own Doppler grid (cfg.grid_per_prn)
+        one3 = sdr.Acquisition(fs3, 2, ns3, int(ns3 / 511), 1e-3, grids3, np.repeat(code3[None, :], len(ks3), 0), crate3,
+                               intg=intg3, threshold=1e30)                                              # every step runs
+        t3m = _time3([one3])
+        g3 = one3.fetch()
+        # per-kernel share of one search (events around every launch; adds their cost)
+        sdr.check(lib.sdrb200_acq_set_timing(one3.h, 1), "set_timing")
+        one3.enqueue(st3, b3); one3.sync()
+        ms4_3 = (C.c_double * 4)(); c4_3 = (C.c_longlong * 4)()
+        sdr.check(lib.sdrb200_acq_kernel_ms(one3.h, ms4_3, c4_3), "kernel_ms")
+        sdr.check(lib.sdrb200_acq_set_timing(one3.h, 0), "set_timing")
+        kern3 = {"forward (k_fwd_split_small + k_fft_rows)": ms4_3[0], "k_rowc<search>": ms4_3[1], "k_rowc<peak>": ms4_3[3]}
+        # round-1/2 arrangement for comparison: one plan per channel on 14 CUDA streams
+        plans3 = [sdr.Acquisition(fs3, 2, ns3, int(ns3 / 511), 1e-3, grids3[i], code3[None, :], crate3, intg=intg3, threshold=1e30)
+                  for i in range(len(ks3))]
+        t3p = _time3(plans3)
+        g3p = [pl.fetch()[0] for pl in plans3]
+        for a_, b_ in zip(g3, g3p):
+            if (a_["freqi"], a_["codei"], a_["nintg"]) != (b_["freqi"], b_["codei"], b_["nintg"]):
+                raise SystemExit("bench.py: batched GLONASS plan disagrees with the per-channel plans")
         cells3 = world * len(ks3) * nf3 * ns3 * intg3
         c3_obj = {"workload": f"GLONASS G1 FDMA: {len(ks3)} channels x {nf3} bins x {ns3} code phases x {intg3} integrations, "
                               "I/Q int8 at 20 MS/s (BASELINE configs[2]); one IF stream per GPU",
                   "cells_per_s": cells3 / t3m, "ms_per_search": t3m * 1e3,
+                  "plan": "one plan, 14 replicas x their own 101-bin grid (grid_per_prn): 4 launches per integration",
+                  "kernel_ms_per_search": {k_: round(v_, 3) for k_, v_ in kern3.items()},
+                  "one_plan_per_channel": {"cells_per_s": cells3 / t3p, "ms_per_search": t3p * 1e3,
+                                           "note": "14 plans on 14 CUDA streams (the arrangement of the earlier runs); tuples equal"},
                   "peak_ratio_per_channel": {str(k_): round(g_["peakr"], 2) for k_, g_ in zip(ks3, g3)},
                   "channels_with_signal": [-7, -4, -1, 0, 2, 5, 6],
                   "hbm": {"model": "SURVEY 8(d): IF + code spectrum + power matrix read/write per step",
                           "frac": world * len(ks3) * (intg3 * (2 * ns3 * 2 + 65536 * 8) + nf3 * ns3 * 4 * (2 * intg3 - 1)) / t3m / 1e9 / (hbm_peak * world)},
-                  "timing": "host clock around enqueue-all .. sync-all (14 CUDA streams), L2 flushed before"}
+                  "timing": "host clock around enqueue .. sync, L2 flushed before"}
+        one3.close()
         for pl in plans3: pl.close()
         st3.close()
     # ------------------------------------------------ config-4 style: long coherent blocks

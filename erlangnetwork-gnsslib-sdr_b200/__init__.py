@@ -48,7 +48,7 @@ class AcqCfg(C.Structure):
                 ("nsampchip", C.c_int), ("ctime", C.c_double), ("nfreq", C.c_int),
                 ("freq", C.POINTER(C.c_double)), ("nprn", C.c_int), ("clen", C.c_int),
                 ("crate", C.c_double), ("codes", C.POINTER(C.c_int8)), ("intg", C.c_int),
-                ("ncoh", C.c_int), ("threshold", C.c_double)]
+                ("ncoh", C.c_int), ("threshold", C.c_double), ("grid_per_prn", C.c_int)]
 
 
 class AcqResult(C.Structure):

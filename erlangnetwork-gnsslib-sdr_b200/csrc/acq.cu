@@ -49,6 +49,7 @@ struct acq_rowstat_t {
 struct sdrb200_acq {
     sdrb200_acq_cfg_t cfg;
     int n_eff, m_ref, M, L, R;
+    int nfx;                         /* wipe-off grids held: nfreq, or nprn * nfreq when every replica has its own (cfg.grid_per_prn) */
     int chunk;                       /* PRNs per scratch chunk                */
     int fchunk;                      /* Doppler bins per scratch chunk (nfreq unless one PRN is too large) */
     int split_fwd;                   /* forward transform in two passes (k_fwd_split* + k_fft_rows)        */
@@ -744,6 +745,7 @@ struct acq_rowc_args {
     double ctime, thresh;
     int nfreq, n_eff, nsampchip, first_step, step;
     float invM2;
+    int xs;                                 /* spectra of replica p start at bin p * xs (0: one grid for all) */
 };
 
 struct acq_part_t { double sum; int cnt; float max2; };
@@ -790,7 +792,7 @@ k_rowc(const acq_rowc_args A)
 #pragma unroll
         for (int i = 0; i < NOUT; i++) { const int t = tout(i); pw[i] = (t < A.n_eff) ? Prow[t] : 0.f; }
     } else {
-        const float2 *x = A.Xs + ((size_t)f * R + q) * L;
+        const float2 *x = A.Xs + ((size_t)(p * A.xs + f) * R + q) * L;
         const float2 *c = A.Cs + ((size_t)p * R + q) * L;
         float2 v[16];
         float2 w[fft_plan_t<L>::N16];
@@ -933,7 +935,7 @@ k_rowc(const acq_rowc_args A)
         o.meanp = sum / (double)cnt;                               /* meanvd, sdrcmn.c:487-497 */
         o.cn0 = 10 * log10(o.maxp / o.meanp / A.ctime);            /* sdracq.c:84 */
         o.peakr = o.maxp / o.maxp2;                                /* sdracq.c:88 */
-        o.codei = codei; o.freqi = f; o.acqfreq = A.freq[f];
+        o.codei = codei; o.freqi = f; o.acqfreq = A.freq[p * A.xs + f];
         o.acquired = (o.peakr > A.thresh) ? 1 : 0;
         o.nintg = A.step + 1;
         A.res[p] = o;
@@ -1486,7 +1488,7 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
 template <int G> static int launch_fwd_split_g(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
 {
     const size_t smem = sizeof(float2) * 16 * G * 32;
-    dim3 grid(a->L / 32, a->cfg.nfreq);
+    dim3 grid(a->L / 32, a->nfx);
     if (a->cfg.dtype == 1) {
         SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_split<G, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_fwd_split<G, 1><<<grid, 32 * G, smem, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
@@ -1502,14 +1504,14 @@ template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fft_rows<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_fft_rows<L><<<dim3(a->R, a->cfg.nfreq), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R, a->warp32 ? 1 : 0);
+    k_fft_rows<L><<<dim3(a->R, a->nfx), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R, a->warp32 ? 1 : 0);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
 template <int R> static int launch_fwd_split_small_r(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
 {
-    dim3 grid((a->L + 255) / 256, a->cfg.nfreq);
+    dim3 grid((a->L + 255) / 256, a->nfx);
     if (a->cfg.dtype == 1)
         k_fwd_split_small<R, 1><<<grid, 256, 0, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
     else
@@ -1690,6 +1692,16 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
 /* M = R * L.  Up to R = 8 the R sub-transforms of a row are finished inside one
  * thread-block cluster (k_rowc); longer windows (20 ms coherent blocks) use the
  * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
+static void acq_choose(int M, int *L, int *R, int *fused, int *warp32);
+static void acq_choose_plain(int M, int *L, int *R, int *fused)
+{
+    int w = 0;
+    const char *keep = getenv("SDRB200_ACQ_WARP");
+    char saved[16] = "";
+    if (keep) { strncpy(saved, keep, sizeof(saved) - 1); unsetenv("SDRB200_ACQ_WARP"); }
+    acq_choose(M, L, R, fused, &w);
+    if (keep) setenv("SDRB200_ACQ_WARP", saved, 1);
+}
 static void acq_choose(int M, int *L, int *R, int *fused, int *warp32)
 {
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
@@ -1724,9 +1736,16 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
     acq_choose(a->M, &a->L, &a->R, &a->fused, &a->warp32);
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
+    /* one wipe-off grid per replica (GLONASS FDMA: every channel has its own carrier, src/sdrinit.c:633-635):
+     * the rows of replica p read the spectra of bins p * nfreq .. ; fused cluster kernel only */
+    a->nfx = cfg->grid_per_prn ? nprn * nfreq : nfreq;
+    if (cfg->grid_per_prn && (!a->fused || a->warp32)) {
+        if (a->warp32) { a->warp32 = 0; acq_choose_plain(a->M, &a->L, &a->R, &a->fused); }
+        if (!a->fused) { sdrb200_set_error("acq_create: grid_per_prn needs the fused path (window of at most 8 sub-transforms)"); free(a); return SDRB200_EINVAL; }
+    }
     if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }
-    a->h_freq = (double *)malloc(sizeof(double) * nfreq);
-    memcpy(a->h_freq, cfg->freq, sizeof(double) * nfreq);
+    a->h_freq = (double *)malloc(sizeof(double) * a->nfx);
+    memcpy(a->h_freq, cfg->freq, sizeof(double) * a->nfx);
     a->cfg.freq = a->h_freq; a->cfg.codes = NULL;
     /* scratch chunking: keep S within ~64 MB so that it stays L2-resident */
     {
@@ -1769,8 +1788,8 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
         cudaGetLastError(); sdrb200_set_error("acq_create: cudaMalloc(%zu) failed", (size_t)(bytes)); rc = SDRB200_ENOMEM; }
     if (cudaStreamCreateWithFlags(&a->st, cudaStreamNonBlocking) != cudaSuccess) rc = SDRB200_ECUDA;
     ACQ_ALLOC(a->d_tw, sizeof(float2) * M);
-    ACQ_ALLOC(a->d_cidx, (size_t)nfreq * M);                    /* row stride M: 16-byte aligned rows */
-    ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)nfreq * M);
+    ACQ_ALLOC(a->d_cidx, (size_t)a->nfx * M);                   /* row stride M: 16-byte aligned rows */
+    ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)a->nfx * M);
     ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
     if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * a->fchunk * M);
     /* the power matrix is kept in HBM only when it has to be: accumulation over
@@ -1780,7 +1799,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     ACQ_ALLOC(a->d_key, sizeof(unsigned long long) * nprn);
     ACQ_ALLOC(a->d_res, sizeof(sdrb200_acq_result_t) * nprn);
     ACQ_ALLOC(a->d_frozen, sizeof(int) * nprn);
-    ACQ_ALLOC(a->d_freq, sizeof(double) * nfreq);
+    ACQ_ALLOC(a->d_freq, sizeof(double) * a->nfx);
     if (rc == SDRB200_OK && cudaMallocHost((void **)&a->h_res, sizeof(sdrb200_acq_result_t) * nprn) != cudaSuccess) rc = SDRB200_ENOMEM;
     if (rc) { sdrb200_acq_destroy(a); return rc; }
 
@@ -1799,10 +1818,10 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
      * (src/sdrcmn.c:761) has phi0 = 0 and a fixed grid, so the index sequence is a
      * constant of the configuration; it is generated with the exact NCO replay. */
     {
-        uint8_t *h = (uint8_t *)calloc((size_t)nfreq, (size_t)M);
+        uint8_t *h = (uint8_t *)calloc((size_t)a->nfx, (size_t)M);
         nco_table_t *tb = (nco_table_t *)malloc(sizeof(nco_table_t));
         const double ti = 1 / cfg->f_sf;
-        for (int f = 0; f < nfreq && rc == SDRB200_OK; f++) {
+        for (int f = 0; f < a->nfx && rc == SDRB200_OK; f++) {
             double phi, ps;
             nco_carrier_init(a->h_freq[f], 0.0, ti, &phi, &ps);
             if (nco_walk(phi, ps, a->m_ref, 0.0, tb)) { sdrb200_set_error("acq_create: NCO table overflow"); rc = SDRB200_ERANGE; break; }
@@ -1811,8 +1830,8 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
             for (int t = 0; t < a->m_ref; t++) row[t] = (uint8_t)(((int)nco_value(tb, t, &hint)) & SDRB200_CMASK);
         }
         if (rc == SDRB200_OK) {
-            cudaMemcpyAsync(a->d_cidx, h, (size_t)nfreq * M, cudaMemcpyHostToDevice, a->st);
-            cudaMemcpyAsync(a->d_freq, a->h_freq, sizeof(double) * nfreq, cudaMemcpyHostToDevice, a->st);
+            cudaMemcpyAsync(a->d_cidx, h, (size_t)a->nfx * M, cudaMemcpyHostToDevice, a->st);
+            cudaMemcpyAsync(a->d_freq, a->h_freq, sizeof(double) * a->nfx, cudaMemcpyHostToDevice, a->st);
             cudaStreamSynchronize(a->st);
         }
         free(h); free(tb);
@@ -1912,7 +1931,7 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
             if (rc) return rc;
             ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a)));
         } else {
-            ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, c->nfreq, win, 0, c->dtype, a->m_ref, a->d_cidx,
+            ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, a->nfx, win, 0, c->dtype, a->m_ref, a->d_cidx,
                                                  a->M, scale, a->d_tw, a->d_Xs)));
         }
         if (rc) return rc;
@@ -1922,6 +1941,7 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
             A.Xs = a->d_Xs; A.Cs = a->d_Cs; A.tw = a->d_tw; A.P = a->d_P; A.key = a->d_key;
             A.frozen = a->d_frozen; A.res = a->d_res; A.freq = a->d_freq;
             A.ctime = c->ctime; A.thresh = c->threshold; A.nfreq = c->nfreq; A.n_eff = a->n_eff;
+            A.xs = c->grid_per_prn ? c->nfreq : 0;
             A.nsampchip = c->nsampchip; A.first_step = (step == 0); A.step = step;
             A.invM2 = 1.0f / ((float)a->M * (float)a->M);
             ACQ_T0(a);

@@ -4,6 +4,7 @@
  * sdrb200_trk_*       <-> sdrtracking() src/sdrtrk.c:15-54 + cumsumcorr/pll/dll
  *                         src/sdrtrk.c:64-150 + bit sync src/sdrnav.c:15-41,198-282
  */
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <math.h>
@@ -624,8 +625,19 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
         }
     }
     sdrb200_trk_rec_t *recs = with_rec ? e->d_rec : NULL;
-    /* CTA size: the small instantiation when one round of its worker team covers the period */
-    const int small = ((size_t)e->maxn * e->dtype + 3 <= (size_t)(TRK_NT_SMALL - TRK_T0) * TRK_SPAN) ? 1 : 0;
+    /* CTA size: the small instantiation when one round of its worker team covers the period, and - the
+     * team takes a longer period in several rounds - when the channels need more than two waves of the
+     * large one anyway: a channel is a latency chain, so two small CTAs per SM carry more channels at once
+     * (2048 channels x 16 368 samples: 9.6 k -> 11.8 k channel.s/s; at 148 channels the large CTA wins,
+     * 8.2 k against 5.9 k).  SDRB200_TRK_SMALL=0/1 overrides.                                         */
+    int small = ((size_t)e->maxn * e->dtype + 3 <= (size_t)(TRK_NT_SMALL - TRK_T0) * TRK_SPAN) ? 1 : 0;
+    {
+        int nsm = 148, dev = 0;
+        if (!small && cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && e->nch >= 2 * nsm) small = 1;
+        cudaGetLastError();
+        const char *env = getenv("SDRB200_TRK_SMALL"); if (env) small = atoi(env) ? 1 : 0;
+    }
     const int nt = small ? TRK_NT_SMALL : TRK_THREADS;
     size_t smem = ((sizeof(trk_cl_smem_t) + 15) & ~(size_t)15) +
                   sizeof(unsigned int) * TRKD_WORK_WORDS(e->maxn, 2 * e->smax, (nt - TRK_T0) / 32);
@@ -657,6 +669,10 @@ static int trk_launch(sdrb200_trk_t *e, const sdrb200_stream_t *s, int nperiods,
         e->ctrl_works = env ? atoi(env) : 0;
     }
     cfg.gridDim = dim3(e->nch * e->cl); at[0].val.clusterDim.x = e->cl;
+    if (getenv("SDRB200_VERBOSE")) {
+        int nact = 0; cudaOccupancyMaxActiveClusters(&nact, fn, &cfg); cudaGetLastError();
+        fprintf(stderr, "sdrb200: k_trk_cl: %d channels, %d threads, cluster %d, %zu B shared memory, %d clusters co-resident\n", e->nch, nt, e->cl, smem, nact);
+    }
     {
         const trk_chan_dev_t *a_ch = e->d_chan; trk_state_t *a_st = e->d_state; const int8_t *a_if = s->d_buf;
         uint64_t a_cap = s->capacity, a_av = s->count; int a_np = nperiods, a_mx = e->maxn, a_qc = e->qcap;

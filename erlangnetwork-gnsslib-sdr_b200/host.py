@@ -223,11 +223,16 @@ class Acquisition:
         self.codes = np.ascontiguousarray(codes, np.int8)
         assert self.codes.ndim == 2
         self.nprn, clen = self.codes.shape
-        self.nsamp, self.nfreq = nsamp, len(self.freq)
+        # freq [nfreq]: one Doppler grid for all replicas; freq [nprn][nfreq]: one grid per replica
+        # (GLONASS FDMA channels, each around its own carrier, src/sdrinit.c:633-635)
+        per_prn = self.freq.ndim == 2
+        assert not per_prn or self.freq.shape[0] == self.nprn
+        self.nsamp, self.nfreq = nsamp, self.freq.shape[-1]
         self.n_eff = nsamp * max(int(ncoh), 1)               # lags per row (coherent block length)
         cfg = AcqCfg(f_sf=f_sf, dtype=dtype, nsamp=nsamp, nsampchip=nsampchip, ctime=ctime,
-                     nfreq=len(self.freq), freq=_p(self.freq, _dp), nprn=self.nprn, clen=clen,
-                     crate=crate, codes=_p(self.codes, _i8p), intg=intg, ncoh=ncoh, threshold=threshold)
+                     nfreq=self.nfreq, freq=_p(self.freq, _dp), nprn=self.nprn, clen=clen,
+                     crate=crate, codes=_p(self.codes, _i8p), intg=intg, ncoh=ncoh, threshold=threshold,
+                     grid_per_prn=int(per_prn))
         self.h = C.c_void_p()
         check(lib.sdrb200_acq_create(C.byref(self.h), C.byref(cfg)), "acq_create")
         if keep_power:

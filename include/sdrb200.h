@@ -118,6 +118,9 @@ typedef struct {
     int    intg;             /* max non-coherent integrations (acq.intg)       */
     int    ncoh;             /* code periods per coherent block (1 = reference)*/
     double threshold;        /* peak-ratio threshold (ACQTH, src/sdr.h:147)    */
+    int    grid_per_prn;     /* 0: the nfreq bins are shared by all replicas; 1: freq is [nprn][nfreq],
+                              * replica p is searched over its own bins (GLONASS FDMA channels, each with
+                              * its own carrier, src/sdrinit.c:633-635); windows of <= 8 sub-transforms */
 } sdrb200_acq_cfg_t;
 
 typedef struct {

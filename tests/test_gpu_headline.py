@@ -197,3 +197,12 @@ def test_c3_glonass_14_channels_101_bins(sdr):
         acq.close()
     # which of the weak channels clear the threshold is the reference's call (equal above); none is invented
     assert set(acquired) <= set(present) and len(acquired) >= 4
+    # the same 14 searches as ONE plan: the G1 code once per channel, every channel over its own grid
+    # (freq [14][101], cfg.grid_per_prn) - one launch sequence per integration instead of fourteen
+    grids = np.array([[(i - nf // 2) * 200.0 + 562500.0 * k for i in range(nf)] for k in ks])
+    acq = sdr.Acquisition(fs, 2, nsamp, int(nsamp / 511), 1e-3, grids, np.repeat(code[None, :], len(ks), 0), crate, intg=intg)
+    for k, g in zip(ks, acq.run(st, b0)):
+        r = ref[k]
+        assert r[:4] == (g["acquired"], g["freqi"], g["codei"], g["nintg"]), (k, r, g)
+        assert abs(r[4] - g["peakr"]) <= 1e-3 * r[4] and abs(r[5] - g["cn0"]) <= 0.01 and r[6] == g["acqfreq"]
+    acq.close()
