@@ -1692,17 +1692,7 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
 /* M = R * L.  Up to R = 8 the R sub-transforms of a row are finished inside one
  * thread-block cluster (k_rowc); longer windows (20 ms coherent blocks) use the
  * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
-static void acq_choose(int M, int *L, int *R, int *fused, int *warp32);
-static void acq_choose_plain(int M, int *L, int *R, int *fused)
-{
-    int w = 0;
-    const char *keep = getenv("SDRB200_ACQ_WARP");
-    char saved[16] = "";
-    if (keep) { strncpy(saved, keep, sizeof(saved) - 1); unsetenv("SDRB200_ACQ_WARP"); }
-    acq_choose(M, L, R, fused, &w);
-    if (keep) setenv("SDRB200_ACQ_WARP", saved, 1);
-}
-static void acq_choose(int M, int *L, int *R, int *fused, int *warp32)
+static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *warp32)
 {
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
     if (lsub > 16384) lsub = 8192;                                   /* scratch path */
@@ -1714,7 +1704,7 @@ static void acq_choose(int M, int *L, int *R, int *fused, int *warp32)
      * alternatives to the 8 x 4096 cluster kernel, selected with SDRB200_ACQ_WARP=pull|push      */
     *warp32 = 0;
     const char *wsel = getenv("SDRB200_ACQ_WARP");
-    if (M == 32768 && *fused && !env && wsel && (!strcmp(wsel, "pull") || !strcmp(wsel, "push"))) {
+    if (allow_warp && M == 32768 && *fused && !env && wsel && (!strcmp(wsel, "pull") || !strcmp(wsel, "push"))) {
         *L = 1024; *R = 32; *warp32 = (wsel[1] == 'u' && wsel[2] == 's') ? 2 : 1;
     }
 }
@@ -1734,14 +1724,14 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->n_eff = cfg->nsamp * a->cfg.ncoh;
     a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
     a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
-    acq_choose(a->M, &a->L, &a->R, &a->fused, &a->warp32);
+    acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     /* one wipe-off grid per replica (GLONASS FDMA: every channel has its own carrier, src/sdrinit.c:633-635):
      * the rows of replica p read the spectra of bins p * nfreq .. ; fused cluster kernel only */
     a->nfx = cfg->grid_per_prn ? nprn * nfreq : nfreq;
-    if (cfg->grid_per_prn && (!a->fused || a->warp32)) {
-        if (a->warp32) { a->warp32 = 0; acq_choose_plain(a->M, &a->L, &a->R, &a->fused); }
-        if (!a->fused) { sdrb200_set_error("acq_create: grid_per_prn needs the fused path (window of at most 8 sub-transforms)"); free(a); return SDRB200_EINVAL; }
+    if (cfg->grid_per_prn && !a->fused) {
+        sdrb200_set_error("acq_create: grid_per_prn needs the fused path (window of at most 8 sub-transforms)");
+        free(a); return SDRB200_EINVAL;
     }
     if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }
     a->h_freq = (double *)malloc(sizeof(double) * a->nfx);

@@ -226,7 +226,11 @@ __device__ static int trk_checksync(double IP, double IPold, trk_state_t *st, in
     return 0;
 }
 
-/* checkbit(), src/sdrnav.c:241-282 (fbits shift register is kept on the host) */
+/* length of nav.fbits (flen + addflen, src/sdr.h:159-174): 302 for GPS L1CA, 200 for GLONASS G1
+ * (told apart by nav.rate, 20 against 10 code periods per unit; SBAS is not synchronised here) */
+__device__ __forceinline__ int trk_fbits_len(int rate) { return rate == 10 ? 200 : 302; }
+
+/* checkbit(), src/sdrnav.c:241-282; nav.fbits is a ring (fhead = oldest) */
 __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int rate)
 {
     int diffi = st->biti - st->synci;
@@ -240,7 +244,7 @@ __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int 
     if (diffi == 0) {
         st->bit = (st->bitIP < 0) ? -1 : 1;
         st->fbits[st->fhead] = (int8_t)st->bit;               /* shift left + append, sdrnav.c:272-275 */
-        st->fhead = (st->fhead + 1 == 302) ? 0 : st->fhead + 1;
+        st->fhead = (st->fhead + 1 == trk_fbits_len(rate)) ? 0 : st->fhead + 1;
         st->swsync = 1;
     }
     st->navcnt++;
@@ -288,6 +292,22 @@ __device__ __noinline__ static int trk_frame_sync_l1ca(trk_state_t *st)
         prev29 = b[30]; prev30 = b[31];
     }
     return stat == 10;
+}
+
+/* findpreamble() for GLONASS G1, src/sdrnav.c:394-400: the 30-unit time mark closes the string,
+ * so it is looked for at the END of the 200-unit register (predecodefec is a plain copy, :296-299;
+ * paritycheck() accepts every G1 string, :357-359)                                              */
+__device__ __noinline__ static int trk_frame_sync_g1(trk_state_t *st)
+{
+    const unsigned int tm = 0x3E375096u;                  /* pre_g1, src/sdrinit.c:494-496: bit set = -1, first unit in bit 29 */
+    int corr = 0;
+    for (int i = 0; i < 30; i++) {
+        int k = st->fhead + 170 + i; if (k >= 200) k -= 200;
+        corr += (int)st->fbits[k] * (((tm >> (29 - i)) & 1u) ? -1 : 1);
+    }
+    if (abs(corr) != 30) return 0;
+    st->polarity = corr > 0 ? 1 : -1;
+    return 1;
 }
 
 __device__ __forceinline__ long long trk_clock()
@@ -382,11 +402,12 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         }
         if (st->flagsync) {
             trk_checkbit(st->II[0], ch->loopms, st, rate);
-            /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA: 20 code periods per bit).  What
+            /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA: 20 code periods per bit, subframe
+             * preamble + parity; GLONASS G1: 10 code periods per unit, time mark of the string).  What
              * follows in the reference - decodenav and its reset when no TOW decodes, :60-83 -
              * is the host's: the record carries flagsyncf, polarity, firstsf, firstsfcnt       */
-            if (st->swsync && rate == 20) {
-                if (!st->flagtow) st->flagsyncf = trk_frame_sync_l1ca(st);
+            if (st->swsync && (rate == 20 || rate == 10)) {
+                if (!st->flagtow) st->flagsyncf = (rate == 20) ? trk_frame_sync_l1ca(st) : trk_frame_sync_g1(st);
                 if (st->flagsyncf && !st->flagtow) { st->firstsf = st->buffloc; st->firstsfcnt = st->cnt; st->flagtow = 1; }
             }
         }

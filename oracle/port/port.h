@@ -88,6 +88,7 @@ typedef struct {
     uint64_t firstsf, firstsfcnt;
 } p_chan_t;
 #define P_FBITS 302
+int p_frame_sync_g1(const int *reg200, int *polarity);    /* port_trk.c */
 
 typedef struct {                                   /* what the two INI files carry */
     double f_sf, f_if, f_cf;

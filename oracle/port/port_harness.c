@@ -167,3 +167,7 @@ int oh_codefft(int prn, int ctype, double f_sf, float *xcode, int *nsamp, int *n
     p_chan_free(&c);
     return 0;
 }
+
+/* unit-level hook: the port's GLONASS string sync on a 200-unit register (pinned against the
+ * reference's findpreamble() by tests/test_oracle_port.py through oh_ref_framesync)        */
+int oh_port_framesync_g1(const int *reg200, int *polarity) { return p_frame_sync_g1(reg200, polarity); }

@@ -63,6 +63,19 @@ static int frame_sync_l1ca(p_chan_t *c)
     return stat == 10;
 }
 
+/* findpreamble for GLONASS G1, src/sdrnav.c:394-400: the time mark pre_g1 (src/sdrinit.c:494-496)
+ * at the END of the flen = 200 register, i.e. the last 200 entries of fbits here; paritycheck()
+ * accepts every G1 string (:357-359), predecodefec is a copy (:296-299)                     */
+int p_frame_sync_g1(const int *reg200, int *polarity)
+{
+    static const int pre[30] = {-1,-1,-1,-1,-1, 1, 1, 1,-1,-1, 1,-1,-1,-1, 1,-1, 1,-1, 1, 1, 1, 1,-1, 1, 1,-1, 1,-1,-1, 1};
+    int corr = 0, i;
+    for (i = 0; i < 30; i++) corr += reg200[200 - 30 + i] * pre[i];
+    if (abs(corr) != 30) return 0;
+    *polarity = corr > 0 ? 1 : -1;
+    return 1;
+}
+
 /* checkbit, src/sdrnav.c:241-282, including the frame-bit shift register (:272-275) */
 static void bit_decide(double IP, p_chan_t *c)
 {
@@ -107,10 +120,10 @@ void p_tracking(p_chan_t *c, const signed char *stream, uint64_t buffloc, uint64
         c->flagsync = bit_sync_step(c->II[0], c->oldI[0], c);
     if (c->flagsync) {
         bit_decide(c->II[0], c);
-        /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA; what follows it - decodenav and
+        /* frame synchronisation, src/sdrnav.c:43-58 (GPS L1CA, GLONASS G1; what follows it - decodenav and
          * its reset when no TOW decodes, :60-83 - is outside this path)                     */
-        if (c->swsync && c->ctype == 1 && c->rate == 20) {
-            if (!c->flagtow) c->flagsyncf = frame_sync_l1ca(c);
+        if (c->swsync && ((c->ctype == 1 && c->rate == 20) || (c->ctype == 20 && c->rate == 10))) {
+            if (!c->flagtow) c->flagsyncf = (c->ctype == 1) ? frame_sync_l1ca(c) : p_frame_sync_g1(&c->fbits[P_FBITS - 200], &c->polarity);
             if (c->flagsyncf && !c->flagtow) { c->firstsf = buffloc; c->firstsfcnt = cnt; c->flagtow = 1; }
         }
     }

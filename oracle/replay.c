@@ -466,3 +466,22 @@ int oh_codefft(int prn, int ctype, double f_sf, float *xcode, int *nsamp, int *n
     freesdrch(&tmp);
     return 0;
 }
+
+/* unit-level hook for the frame synchronisation of one code type: the reference's own initnavstruct()
+ * (flen, addflen, prelen, prebits, src/sdrinit.c:489-568), predecodefec() and findpreamble()
+ * (src/sdrnav.c:288-411) on a caller-supplied nav.fbits register of flen + addflen entries.
+ * Returns findpreamble()'s result, *polarity as it left it; -1 on a wrong length / init failure. */
+int oh_ref_framesync(int ctype, int prn, const int *fbits, int n, int *polarity)
+{
+    sdrnav_t nav;
+    int r;
+    memset(&nav, 0, sizeof(nav));
+    if (initnavstruct(sys_of(ctype), ctype, prn, &nav) < 0) return -1;
+    if (n != nav.flen + nav.addflen) return -1;
+    memcpy(nav.fbits, fbits, sizeof(int) * (size_t)n);
+    predecodefec(&nav);
+    r = findpreamble(&nav);
+    if (polarity) *polarity = nav.polarity;
+    free(nav.bitsync); free(nav.fbits); free(nav.fbitsdec); free(nav.ocode);
+    return r;
+}

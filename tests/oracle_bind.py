@@ -212,6 +212,20 @@ class Oracle:
             return None, 0.0
         return buf[:n].copy(), cr.value
 
+    def framesync(self, ctype, prn, fbits):
+        """(found, polarity) of the frame synchronisation on one nav.fbits register: the reference's
+        findpreamble() after its own initnavstruct()/predecodefec() (oracle/_ref), or the port's
+        GLONASS string sync (ctype 20, 200 units)."""
+        fb = np.ascontiguousarray(fbits, np.int32)
+        pol = C.c_int(0)
+        ip = C.POINTER(C.c_int)
+        if hasattr(self.lib, "oh_ref_framesync"):
+            r = self.lib.oh_ref_framesync(int(ctype), int(prn), fb.ctypes.data_as(ip), int(len(fb)), C.byref(pol))
+        else:
+            assert ctype == 20 and len(fb) == 200
+            r = self.lib.oh_port_framesync_g1(fb.ctypes.data_as(ip), C.byref(pol))
+        return int(r), pol.value
+
     def codefft(self, prn, ctype, f_sf):
         nsamp, nfft = C.c_int(), C.c_int()
         self.lib.oh_codefft(int(prn), int(ctype), C.c_double(f_sf), None, C.byref(nsamp), C.byref(nfft))

@@ -122,3 +122,49 @@ def test_tracking_frame_sync_lnav(sdr, oracle):
         assert int(g["firstsfcnt"][-1]) == int(o["cnt"][k]) and int(g["firstsf"][-1]) == int(o["buffloc"][k])
         assert np.abs(o["L0"] - g["L0"]).max() <= 2e-2, (a.prn, "L0")
     assert sorted(int(r["polarity"][-1]) for r in rec_g) == [-1, -1, 1]      # the +0.5 term is exercised
+
+
+def test_tracking_string_sync_glonass_g1(sdr):
+    """GLONASS G1 string synchronisation on the device (findpreamble for CTYPE_G1, src/sdrnav.c:394-411:
+    the 30-unit time mark at the end of the 200-unit register, 10 code periods per unit, loop interval
+    10 ms): IF carrying strings with the time mark (tests/testkit/ifgen.h nav_on = 3), one satellite sent
+    inverted.  This fork cannot dispatch a G1 channel (src/sdrcode.c:523-539), so the oracle is the port,
+    whose string sync is pinned to the reference's findpreamble() in tests/test_oracle_port.py and whose
+    tracking loop is pinned to the reference on L1CA.  The period at which the mark is accepted, the
+    polarity and the hand-over (firstsf, firstsfcnt) must be equal."""
+    if not ob.have_port():
+        pytest.skip("oracle port not built")
+    oracle = ob.port()
+    fs, nsamp = 5.11e6, 5110                                   # 10 samples per chip, I/Q
+    rng = np.random.default_rng(0xB20000C1)
+    ks = [-1, 2]                                               # frequency numbers
+    sats = [dict(prn=1, cn0=49.0, doppler=float(rng.uniform(-2500, 2500)), carr_offset=k * 562500.0,
+                 code_phase=float(rng.uniform(0, 511 * 10)), carr_phase=float(rng.uniform(0, 1)), rate=0.2,
+                 nav_on=3, nav_seed=(7 + i) | (i << 16)) for i, k in enumerate(ks)]
+    cfg = sdr.make_ifgen(fs, 0.0, 1.602e9, 2, sats, sigma=3.0, seed=0xB20000C1, crate=0.511e6, clen=511, bitlen=10)
+    nper = 8200
+    avail = 65536 * 2
+    total = avail + nsamp * (nper + 8)
+    st = sdr.Stream(2, total)
+    st.push_ifgen(cfg, total)
+    host = st.read(0, total)
+    cfgo = ob.OhCfg(f_sf=fs, f_if=0.0, f_cf=1.602e9, dtype=2, corrn=4, corrd=1, corrp=1, acq_intg=4)
+    cfgo.dllb[:] = [5.0, 2.0]; cfgo.pllb[:] = [30.0, 20.0]; cfgo.fllb[:] = [200.0, 50.0]
+    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, ks, nper, ctypes=[20] * len(ks))
+    assert all(a.acquired for a in acq)
+    code = sdr.gencode(1, 20)[0]
+    chans = [sdr.make_trk_chan(fs, 0.0, 1.602e9 + 562500.0 * k, 2, k, code, a.buffloc, a.acqfreq, cfgo.corrn, cfgo.corrd,
+                               cfgo.corrp, list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb), ctype=20,
+                               foffset=562500.0 * k) for k, a in zip(ks, acq)]
+    rec_g, ntr_g = sdr.Tracking(chans).run(st, nper)
+    pols = []
+    for ch, k in enumerate(ks):
+        assert ntr_o[ch] == nper and ntr_g[ch] == nper
+        o, g = rec_o[ch], rec_g[ch]
+        assert o["flagsyncf"].max() == 1, (k, "the oracle did not find the time mark")
+        for f in ("currnsamp", "flagsync", "synci", "flagsyncf", "flagtow", "polarity"):
+            assert np.array_equal(o[f], g[f]), (k, f, int(np.argmax(o[f] != g[f])))
+        i0 = int(np.argmax(o["flagsyncf"] > 0))
+        assert int(g["firstsfcnt"][-1]) == int(o["cnt"][i0]) and int(g["firstsf"][-1]) == int(o["buffloc"][i0])
+        pols.append(int(g["polarity"][-1]))
+    assert all(p in (-1, 1) for p in pols)                      # which sign the PLL locked to is the oracle's call (equal above)

@@ -183,3 +183,34 @@ def test_port_frame_sync_equals_reference_build(port):
     assert n1 == n2 and int(r1["flagsyncf"].max()) == 1
     for f in REC_FIELDS + ["flagsyncf", "flagtow", "polarity"]:
         assert np.array_equal(np.ascontiguousarray(r1[f]), np.ascontiguousarray(r2[f])), f
+
+
+def test_port_glonass_string_sync_against_reference(port):
+    """GLONASS G1 string synchronisation (src/sdrnav.c:394-411 with the parameters of
+    src/sdrinit.c:546-559): the port's restatement against the reference's own findpreamble() on
+    the same 200-unit registers - the time mark at the end of the register (both polarities), one
+    unit off, one unit wrong, and random registers."""
+    if not ob.have_ref():
+        pytest.skip("reference build not present")
+    ref = ob.ref()
+    pre = np.array([-1, -1, -1, -1, -1, 1, 1, 1, -1, -1, 1, -1, -1, -1, 1, -1, 1, -1, 1, 1,
+                    1, 1, -1, 1, 1, -1, 1, -1, -1, 1], np.int32)
+    rng = np.random.default_rng(0x61)
+    cases = []
+    for pol in (1, -1):
+        reg = rng.choice(np.array([-1, 1], np.int32), 200)
+        reg[170:] = pol * pre
+        cases.append(reg.copy())
+        cases.append(np.roll(reg, -1))                   # the mark one unit early
+        bad = reg.copy(); bad[170 + int(rng.integers(0, 30))] *= -1
+        cases.append(bad)                                # one unit of the mark wrong
+    cases += [rng.choice(np.array([-1, 1], np.int32), 200) for _ in range(200)]
+    cases.append(np.zeros(200, np.int32))                # the register before any bit has arrived
+    found = 0
+    for reg in cases:
+        r, p = ref.framesync(20, 1, reg), port.framesync(20, 1, reg)
+        assert r[0] == p[0], (r, p)
+        if r[0]:
+            assert r[1] == p[1]
+            found += 1
+    assert found == 2

@@ -24,7 +24,7 @@ class IfgenSat(C.Structure):
     _fields_ = [("prn", C.c_int), ("nav_on", C.c_int), ("cn0_dbhz", C.c_double),
                 ("doppler_hz", C.c_double), ("doppler_rate", C.c_double),
                 ("code_phase", C.c_double), ("carr_phase", C.c_double),
-                ("nav_seed", C.c_uint64)]
+                ("nav_seed", C.c_uint64), ("carr_offset_hz", C.c_double)]
 
 
 class IfgenCfg(C.Structure):
@@ -37,7 +37,7 @@ class IfgenCfg(C.Structure):
 
 def make_ifgen(f_sf, f_if, f_cf, dtype, sats, sigma=24.0, seed=0xB2000000,
                crate=1.023e6, clen=1023, bitlen=20) -> IfgenCfg:
-    """sats: list of dicts(prn, cn0, doppler, rate, code_phase, carr_phase, nav_on, nav_seed)."""
+    """sats: list of dicts(prn, cn0, doppler, rate, code_phase, carr_phase, nav_on, nav_seed, carr_offset)."""
     c = IfgenCfg()
     c.f_sf, c.f_if, c.f_cf, c.crate, c.sigma = f_sf, f_if, f_cf, crate, sigma
     c.dtype, c.clen, c.bitlen, c.nsat, c.seed = dtype, clen, bitlen, len(sats), seed
@@ -45,7 +45,8 @@ def make_ifgen(f_sf, f_if, f_cf, dtype, sats, sigma=24.0, seed=0xB2000000,
         c.sat[i] = IfgenSat(prn=s["prn"], nav_on=s.get("nav_on", 1), cn0_dbhz=s["cn0"],
                             doppler_hz=s["doppler"], doppler_rate=s.get("rate", 0.0),
                             code_phase=s["code_phase"], carr_phase=s.get("carr_phase", 0.0),
-                            nav_seed=s.get("nav_seed", 1000 + s["prn"]))
+                            nav_seed=s.get("nav_seed", 1000 + s["prn"]),
+                            carr_offset_hz=s.get("carr_offset", 0.0))
     return c
 
 

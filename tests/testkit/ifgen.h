@@ -37,13 +37,15 @@
 typedef struct {
     int      prn;              /* code number (index into the code table)   */
     int      nav_on;           /* 0: all +1, 1: 50 bps random data, 2: 50 bps GPS LNAV subframes
-                                * (preamble, TOW count, valid (32,26) parity in every word) */
+                                * (preamble, TOW count, valid (32,26) parity in every word),
+                                * 3: GLONASS strings (random 10 ms units + the 30-unit time mark) */
     double   cn0_dbhz;         /* carrier-to-noise density                  */
     double   doppler_hz;       /* carrier Doppler at t=0                    */
     double   doppler_rate;     /* Hz/s                                      */
     double   code_phase;       /* chips at sample 0, in [0, clen*bitlen)    */
     double   carr_phase;       /* cycles at sample 0                        */
     uint64_t nav_seed;         /* data bit b = hash(nav_seed, b) & 1        */
+    double   carr_offset_hz;   /* added to the carrier only (FDMA channel offset): no code Doppler */
 } ifgen_sat_t;
 
 typedef struct {
@@ -112,6 +114,23 @@ IFGEN_HD int ifgen_lnavbit(uint64_t nav_seed, int64_t bit)
     return ((word >> (29 - k)) & 1u) ? -1 : 1;
 }
 
+/* nav_on == 3: unit u (one 10 ms half-symbol, bitlen = 10 code periods) of an endless train of
+ * GLONASS strings: 200 units = 2 s, the first 170 pseudo-random (the 85 data bits in meander
+ * form are not decoded on this path), the last 30 the time mark the reference's findpreamble()
+ * looks for at the end of its 200-unit register (pre_g1, src/sdrinit.c:494-496,
+ * src/sdrnav.c:396-400).  nav_seed bit 16 set: the whole train is sent inverted.             */
+IFGEN_HD int ifgen_g1bit(uint64_t nav_seed, int64_t unit)
+{
+    const int64_t st = (unit >= 0) ? unit / 200 : -((-unit + 199) / 200);
+    const int r = (int)(unit - st * 200);
+    const int inv = ((nav_seed >> 16) & 1) ? -1 : 1;
+    if (r >= 170) {
+        const unsigned int tm = 0x3E375096u;              /* 111110001101110101000010010110, MSB first */
+        return (((tm >> (29 - (r - 170))) & 1u) ? -1 : 1) * inv;
+    }
+    return ifgen_navbit(nav_seed, unit) * inv;
+}
+
 /* one sample; codes = [nsat][IFGEN_MAXCLEN] of +-1; out[0]=I (or real), out[1]=Q */
 IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
                            uint64_t k, signed char *out)
@@ -130,9 +149,10 @@ IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
         int    d = 1;
         if (chip >= c->clen) chip = c->clen - 1;
         if (chip < 0) chip = 0;
-        if (sv->nav_on == 2) d = ifgen_lnavbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        if (sv->nav_on == 3) d = ifgen_g1bit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        else if (sv->nav_on == 2) d = ifgen_lnavbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
         else if (sv->nav_on) d = ifgen_navbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
-        cyc = sv->carr_phase + (c->f_if + fd) * t + 0.5 * fdr * t * t;
+        cyc = sv->carr_phase + (c->f_if + fd + sv->carr_offset_hz) * t + 0.5 * fdr * t * t;
         fr  = cyc - floor(cyc);
         a   = c->amp[s] * (double)(d * codes[s * IFGEN_MAXCLEN + chip]);
         xi += a * cos(6.283185307179586 * fr);
