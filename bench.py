@@ -522,6 +522,16 @@ def run_b200(args):
             done_all, done2_all = float(tn[0]), float(tn[1])
         else:
             done_all, done2_all = float(done), float(sum(nrec2))
+        # DRAM bytes of one k_trk_cl launch: the ncu capture is a 2 s launch (profiles/r2d_ncu_full_trk_summary.csv:
+        # the 12 channels read ONE IF stream, which comes from DRAM once), scaled to this launch's IF seconds
+        trk_traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                per_s = json.load(f).get("k_trk_cl_per_if_second")
+            if per_s:
+                trk_traffic = int(per_s * args.trk_seconds)
+        except Exception:
+            pass
         trk_obj = {
             "metric": "tracking channel.s/s (channels x seconds of IF per wall second)",
             "value": done_all * 1e-3 / trk_tmax, "unit": "channel.s/s", "config": {"workload": WORKLOAD_TRK,
@@ -531,7 +541,7 @@ def run_b200(args):
             "e2e": {"value": done2_all * 1e-3 / t_trk_e2e, "unit": "channel.s/s",
                     "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4 * (nch + 1)},
             "roofline": {"bound": "hbm", "achieved": a_bytes / t_trk / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": a_bytes / t_trk / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": a_bytes / t_trk / 1e9 / hbm_peak, "traffic": trk_traffic, "peak_source": peak_src,
                          "kernel": "k_trk_cl", "algorithmic_bytes_per_launch": a_bytes,
                          "alu": {"bound": "int32 multiply-add issue", "unit": "Tops/s", "peak": int32_peak,
                                  "achieved": done * NSAMP * 28 * 2 / t_trk / 1e12,
