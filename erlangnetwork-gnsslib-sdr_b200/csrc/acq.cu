@@ -842,6 +842,11 @@ k_rowc(const acq_rowc_args A)
                 } else if constexpr (R == 4) {
                     y[0] = cadd(cadd(z[0], z[2]), cadd(z[1], z[3]));
                     y[1] = cadd(csub(z[0], z[2]), crot<+1>(csub(z[1], z[3])));
+                } else if constexpr (R == 16) {
+                    /* 16-point inverse transform; only y[0..7] are used (lags < n <= M/2) */
+                    fft16<+1>(z);
+#pragma unroll
+                    for (int a = 0; a < NA; a++) y[a] = z[a];
                 } else {
                     /* R == 8: even / odd 4-point transforms, then W_8^(-a) */
                     float2 e0 = z[0], e1 = z[2], e2 = z[4], e3 = z[6];
@@ -1485,51 +1490,56 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
 }
 
 /* two-pass forward transform of the IF window for R = 16 G */
-template <int G> static int launch_fwd_split_g(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+template <int G> static int launch_fwd_split_g(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale, int f0, int nfc)
 {
     const size_t smem = sizeof(float2) * 16 * G * 32;
-    dim3 grid(a->L / 32, a->nfx);
+    dim3 grid(a->L / 32, nfc);
+    const uint8_t *cidx = a->d_cidx + (size_t)f0 * a->M;
+    float2 *xs = a->d_Xs + (size_t)f0 * a->M;
     if (a->cfg.dtype == 1) {
         SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_split<G, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_fwd_split<G, 1><<<grid, 32 * G, smem, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+        k_fwd_split<G, 1><<<grid, 32 * G, smem, st>>>(win, a->m_ref, cidx, a->M, scale, a->d_tw, a->L, xs);
     } else {
         SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fwd_split<G, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_fwd_split<G, 2><<<grid, 32 * G, smem, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+        k_fwd_split<G, 2><<<grid, 32 * G, smem, st>>>(win, a->m_ref, cidx, a->M, scale, a->d_tw, a->L, xs);
     }
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
-template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *a)
+template <int L> static int launch_fft_rows(cudaStream_t st, const sdrb200_acq *a, int f0, int nfc)
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_fft_rows<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_fft_rows<L><<<dim3(a->R, a->nfx), L / 16, smem, st>>>(a->d_Xs, a->d_tw, a->R, a->warp32 ? 1 : 0);
+    k_fft_rows<L><<<dim3(a->R, nfc), L / 16, smem, st>>>(a->d_Xs + (size_t)f0 * a->M, a->d_tw, a->R, a->warp32 ? 1 : 0);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
-template <int R> static int launch_fwd_split_small_r(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+template <int R> static int launch_fwd_split_small_r(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale, int f0, int nfc)
 {
-    dim3 grid((a->L + 255) / 256, a->nfx);
+    dim3 grid((a->L + 255) / 256, nfc);
+    const uint8_t *cidx = a->d_cidx + (size_t)f0 * a->M;
+    float2 *xs = a->d_Xs + (size_t)f0 * a->M;
     if (a->cfg.dtype == 1)
-        k_fwd_split_small<R, 1><<<grid, 256, 0, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+        k_fwd_split_small<R, 1><<<grid, 256, 0, st>>>(win, a->m_ref, cidx, a->M, scale, a->d_tw, a->L, xs);
     else
-        k_fwd_split_small<R, 2><<<grid, 256, 0, st>>>(win, a->m_ref, a->d_cidx, a->M, scale, a->d_tw, a->L, a->d_Xs);
+        k_fwd_split_small<R, 2><<<grid, 256, 0, st>>>(win, a->m_ref, cidx, a->M, scale, a->d_tw, a->L, xs);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
-static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale)
+static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t *win, float scale, int f0, int nfc)
 {
     switch (a->R) {
-    case 2:   return launch_fwd_split_small_r<2>(st, a, win, scale);
-    case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale);
-    case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale);
-    case 32:  return launch_fwd_split_g<2>(st, a, win, scale);   /* one thread per t with a 32-point register stage: 38 vs 34 us */
-    case 64:  return launch_fwd_split_g<4>(st, a, win, scale);
-    case 128: return launch_fwd_split_g<8>(st, a, win, scale);
-    case 256: return launch_fwd_split_g<16>(st, a, win, scale);
+    case 2:   return launch_fwd_split_small_r<2>(st, a, win, scale, f0, nfc);
+    case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale, f0, nfc);
+    case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale, f0, nfc);
+    case 16:  return launch_fwd_split_small_r<16>(st, a, win, scale, f0, nfc);
+    case 32:  return launch_fwd_split_g<2>(st, a, win, scale, f0, nfc);   /* one thread per t with a 32-point register stage: 38 vs 34 us */
+    case 64:  return launch_fwd_split_g<4>(st, a, win, scale, f0, nfc);
+    case 128: return launch_fwd_split_g<8>(st, a, win, scale, f0, nfc);
+    case 256: return launch_fwd_split_g<16>(st, a, win, scale, f0, nfc);
     }
     return SDRB200_EINVAL;
 }
@@ -1564,6 +1574,7 @@ template <int L, int R, int MODE> static int launch_rowc(cudaStream_t st, const 
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowc<L, R, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (R > 8) SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_rowc<L, R, MODE>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(R, nfreq_grid, nprn);
     cfg.blockDim = dim3(L / 16, 1, 1);
@@ -1657,6 +1668,7 @@ static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_ro
     RC(1024, 2) RC(2048, 2) RC(4096, 2) RC(8192, 2) RC(16384, 2)
     RC(1024, 4) RC(2048, 4) RC(4096, 4) RC(8192, 4) RC(16384, 4)
     RC(1024, 8) RC(2048, 8) RC(4096, 8) RC(8192, 8) RC(16384, 8)
+    RC(4096, 16)
 #undef RC
     sdrb200_set_error("acquisition: no fused kernel for L=%d R=%d", L, R);
     return SDRB200_EINVAL;
@@ -1698,8 +1710,11 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
     if (lsub > 16384) lsub = 8192;                                   /* scratch path */
     const char *env = getenv("SDRB200_LSUB");
     if (env) { int v = atoi(env); if ((v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) && v <= M) lsub = v; }
+    /* M = 65536 (GLONASS at 20 MS/s): 16 x 4096 in a cluster of 16 CTAs (non-portable size) keeps the
+     * 256-thread CTAs and four of them per SM; SDRB200_ACQ_R8 selects 8 x 8192 (512 threads, two per SM) */
+    if (M == 65536 && !env && !getenv("SDRB200_ACQ_R8")) lsub = 4096;
     *L = lsub; *R = M / lsub;
-    *fused = (*R <= 8 && !getenv("SDRB200_ACQ_SCRATCH")) ? 1 : 0;
+    *fused = (*R <= 16 && (*R <= 8 || *L == 4096) && !getenv("SDRB200_ACQ_SCRATCH")) ? 1 : 0;
     /* M = 32768 as 32 sub-transforms of 1024 points, one WARP each (k_roww / k_rowd): measured
      * alternatives to the 8 x 4096 cluster kernel, selected with SDRB200_ACQ_WARP=pull|push      */
     *warp32 = 0;
@@ -1754,7 +1769,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
          * the walking forward kernel), SDRB200_FWD_WALK (walking forward kernel on the cluster path) */
         const int naive = getenv("SDRB200_ACQ_COMB_NAIVE") != NULL;
         a->comb_fft = (!a->fused && a->R > 1 && comb_fft_supported(a->R) && !naive) ? 1 : 0;
-        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8) &&
+        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8 || a->R == 16) &&
                                         !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }
@@ -1917,9 +1932,12 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
         const int8_t *win = base + pos * c->dtype;
         ACQ_T0(a);
         if (a->split_fwd) {
-            rc = launch_fwd_split(a->st, a, win, scale);
+            /* (tried: the two passes over groups of bins that fit the L2, so that the rows pass overwrites
+             * the first pass's output on chip - GLONASS forward 5.4 -> 6.7 ms per search, the smaller grids
+             * cost more than the write traffic they save)                                               */
+            rc = launch_fwd_split(a->st, a, win, scale, 0, a->nfx);
             if (rc) return rc;
-            ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a)));
+            ACQ_DISPATCH_L(a->L, (launch_fft_rows<LL>(a->st, a, 0, a->nfx)));
         } else {
             ACQ_DISPATCH_L(a->L, (launch_fwd<LL>(0, a->st, a->R, a->nfx, win, 0, c->dtype, a->m_ref, a->d_cidx,
                                                  a->M, scale, a->d_tw, a->d_Xs)));
