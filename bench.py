@@ -655,6 +655,8 @@ def run_b200(args):
         cl5 = 1
         while cl5 < 8 and nch5 * cl5 * 2 <= 2 * max(sdr.lib.sdrb200_sm_count(), 1):
             cl5 *= 2
+        if os.environ.get("BENCH_C5_CLUSTER"):                       # A/B runs
+            cl5 = int(os.environ["BENCH_C5_CLUSTER"])
         for e in engines:
             if e: e.set_cluster(cl5)
         for e, sk in zip(engines, s5):

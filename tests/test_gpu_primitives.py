@@ -29,6 +29,10 @@ def test_mixcarr_rescode_bitexact(sdr, oracle):
 
 
 def test_dot_and_cpxcpx_bitexact(sdr):
+    """dot_21/22/23 (src/sdrcmn.c:287-354) and cpxcpx (:185-195) as single calls.  Oracle: numpy int64 /
+    float32 arithmetic written out here, NOT the reference build - the integer sums are exact in any order
+    and the cpxcpx products are single float32 operations, so nothing can differ; the reference's own
+    functions are exercised on the same paths by the drop-in tests (tests/test_gpu_dropin.py)."""
     import ctypes as C
     rng = np.random.default_rng(22)
     n = 16371
