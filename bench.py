@@ -418,7 +418,44 @@ def run_b200(args):
     t0 = time.perf_counter()
     e2e_steps(K)
     barrier()
+    t_e2e_single = time.perf_counter() - t0
+    # the same work with TWO plans in flight (sdrb200_acq_enqueue_host / sdrb200_acq_fetch): every step still
+    # copies its own input from pinned host memory and reads its own tuples back, but the copy and the launches
+    # of step i+1 are queued behind step i instead of waiting for its results - the batched form of the
+    # reference's one acquisition thread per channel
+    acq_b = sdr.Acquisition(FS, 1, NSAMP, int(NSAMP / 1023), 1e-3, freq, codes, 1.023e6, intg=1)
+    host_pin_b = torch.empty(need, dtype=torch.int8, pin_memory=True)
+    host_pin_b.numpy()[:] = host_np
+    host_ptr_b = C.cast(host_pin_b.data_ptr(), C.POINTER(C.c_int8))
+    res_b = (sdr.AcqResult * NPRN)()
+    plans2 = [(acq, host_ptr, res_ptr), (acq_b, host_ptr_b, res_b)]
+
+    def e2e_steps_2(nsteps):
+        for i in range(min(2, nsteps)):
+            pl, hp, _ = plans2[i & 1]
+            sdr.check(lib.sdrb200_acq_enqueue_host(pl.h, hp, C.c_uint64(need)), "acq_enqueue_host")
+        for i in range(nsteps):
+            pl, hp, rp = plans2[i & 1]
+            sdr.check(lib.sdrb200_acq_fetch(pl.h, rp), "acq_fetch")
+            if dist is not None:
+                pl.copy_results_device(res_ring[i].data_ptr())
+            if i + 2 < nsteps:
+                sdr.check(lib.sdrb200_acq_enqueue_host(pl.h, hp, C.c_uint64(need)), "acq_enqueue_host")
+        if dist is not None:
+            acq.sync(); acq_b.sync()
+            dist.all_gather_into_tensor(res_all.view(-1), res_ring.view(-1))
+            torch.cuda.synchronize()
+
+    e2e_steps_2(4)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps_2(K)
+    barrier()
     t_e2e = time.perf_counter() - t0
+    rb = acq._results(res_b)
+    assert [(r["acquired"], r["freqi"], r["codei"]) for r in rb] == \
+           [(r["acquired"], r["freqi"], r["codei"]) for r in res], "two-plan host-buffer path disagrees with resident path"
+    acq_b.close()
     r2 = acq._results((sdr.AcqResult * NPRN).from_buffer_copy(bytes(res_pin.numpy())))
     if dist is not None:
         mine = res_all[rank, K - 1].cpu().numpy()
@@ -1059,11 +1096,11 @@ def run_b200(args):
     clk = clocks.stop() if clocks else None
 
     # ------------------------------------------------ reduce over ranks, print
-    tmax, te2e = t_acq, t_e2e
+    tmax, te2e, te2e1 = t_acq, t_e2e, t_e2e_single
     if dist is not None:
-        tt = torch.tensor([t_acq, t_e2e], dtype=torch.float64, device="cuda")
+        tt = torch.tensor([t_acq, t_e2e, t_e2e_single], dtype=torch.float64, device="cuda")
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        tmax, te2e = float(tt[0]), float(tt[1])
+        tmax, te2e, te2e1 = float(tt[0]), float(tt[1]), float(tt[2])
     dom = max(kern, key=lambda n: kern[n]["ms_total"])
     per_launch_units = CELLS_PER_STEP * K / max(kern[dom]["launches"], 1)
     a_bytes = 0.226 * per_launch_units                      # 8.41e6 B / 37 188 096 cells
@@ -1084,7 +1121,10 @@ def run_b200(args):
                    "l2": "flushed between timed iterations (384 MB memset)", "multi_gpu": "one IF stream per rank"},
         "e2e": {"value": world * CELLS_PER_STEP * K / te2e, "unit": "cells/s", "h2d_bytes_per_step": need,
                 "d2h_bytes_per_step": NPRN * C.sizeof(sdr.AcqResult),
-                "api": "sdrb200_acq_run_host (pinned host IF in, result tuples out)"},
+                "api": "sdrb200_acq_enqueue_host + sdrb200_acq_fetch on two plans (pinned host IF in and result tuples out "
+                       "every step; step i+1 is queued while step i runs)",
+                "single_call": {"value": world * CELLS_PER_STEP * K / te2e1, "unit": "cells/s",
+                                "api": "sdrb200_acq_run_host: one blocking call per step"}},
         "gpu_launches": int(launches_timed),
         "kernels": kern,
         "roofline": {"bound": "hbm", "achieved": a_bytes / dur / 1e9, "peak": hbm_peak, "unit": "GB/s",

@@ -2089,6 +2089,25 @@ extern "C" int sdrb200_acq_run(sdrb200_acq_t *a, const sdrb200_stream_t *s, uint
     return sdrb200_acq_fetch(a, results);
 }
 
+/* the first half of sdrb200_acq_run_host: H2D copy and all integration steps enqueued on the plan's
+ * stream, no wait - a caller with several plans (the reference runs one thread per channel) keeps the
+ * next search's copy and launches behind the current one and collects with sdrb200_acq_fetch()     */
+extern "C" int sdrb200_acq_enqueue_host(sdrb200_acq_t *a, const int8_t *host_if, uint64_t nsamples)
+{
+    if (!a || !host_if) { sdrb200_set_error("acq_enqueue_host: bad argument"); return SDRB200_EINVAL; }
+    const uint64_t need = (uint64_t)(a->cfg.intg + 1) * a->n_eff;
+    if (nsamples < need) { sdrb200_set_error("acq_enqueue_host: need %llu samples", (unsigned long long)need); return SDRB200_ERANGE; }
+    const size_t bytes = (size_t)need * a->cfg.dtype;
+    if (bytes + 512 > a->hostwin_cap) {
+        SDRB200_CUDA_TRY(cudaStreamSynchronize(a->st));
+        cudaFree(a->d_hostwin); a->d_hostwin = NULL; a->hostwin_cap = 0;
+        if (cudaMalloc((void **)&a->d_hostwin, bytes + 512) != cudaSuccess) { cudaGetLastError(); return SDRB200_ENOMEM; }
+        a->hostwin_cap = bytes + 512;
+    }
+    SDRB200_CUDA_TRY(cudaMemcpyAsync(a->d_hostwin + 256, host_if, bytes, cudaMemcpyHostToDevice, a->st));
+    return acq_steps(a, a->d_hostwin + 256, ~(uint64_t)0, 0);
+}
+
 extern "C" int sdrb200_acq_run_host(sdrb200_acq_t *a, const int8_t *host_if, uint64_t nsamples,
                                     sdrb200_acq_result_t *results)
 {

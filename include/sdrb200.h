@@ -143,6 +143,11 @@ int  sdrb200_acq_run(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t bu
  * H2D copy is part of the call (the end-to-end path)                          */
 int  sdrb200_acq_run_host(sdrb200_acq_t *plan, const int8_t *host_if, uint64_t nsamples,
                           sdrb200_acq_result_t *results);
+/* the same without the wait: H2D copy and the integration steps enqueued on the plan's stream; the
+ * caller collects with sdrb200_acq_fetch().  With two plans a caller keeps one search's copy and
+ * launches behind the other's - the batched form of the reference's one acquisition thread per
+ * channel (src/sdrmain.c:144-149, src/sdracq.c:14-62)                                          */
+int  sdrb200_acq_enqueue_host(sdrb200_acq_t *plan, const int8_t *host_if, uint64_t nsamples);
 /* launch-only variant for timing: enqueue on the plan's stream, no sync, no
  * D2H; results are fetched with sdrb200_acq_fetch()                           */
 int  sdrb200_acq_enqueue(sdrb200_acq_t *plan, const sdrb200_stream_t *s, uint64_t buffloc0);
