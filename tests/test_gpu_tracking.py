@@ -51,18 +51,18 @@ def _compare(sdr, cfgo, acq, rec_o, ntr_o, rec_g, ntr_g, ntap):
               f"max|dcarrfreq|={np.abs(o['carrfreq'] - g['carrfreq']).max():.3e}")
 
 
-def _run(sdr, oracle, cfg, prns, cfgo, nper, fs, dtype):
+def _run(sdr, oracle, cfg, prns, cfgo, nper, fs, dtype, ctype=1):
     nsamp = int(fs * 1e-3)
     avail = 65536 * ((3 * nsamp) // 65536 + 1)
     total = avail + nsamp * (nper + 8)
     st = sdr.Stream(dtype, total)
     st.push_ifgen(cfg, total)
     host = st.read(0, total)
-    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, prns, nper)
+    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, prns, nper, ctypes=[ctype] * len(prns))
     assert all(a.acquired for a in acq)
-    chans = [sdr.make_trk_chan(cfgo.f_sf, cfgo.f_if, cfgo.f_cf, dtype, a.prn, sdr.gencode(a.prn)[0],
+    chans = [sdr.make_trk_chan(cfgo.f_sf, cfgo.f_if, cfgo.f_cf, dtype, a.prn, sdr.gencode(a.prn, ctype)[0],
                                a.buffloc, a.acqfreq, cfgo.corrn, cfgo.corrd, cfgo.corrp,
-                               list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb)) for a in acq]
+                               list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb), ctype=ctype) for a in acq]
     eng = sdr.Tracking(chans)
     rec_g, ntr_g = eng.run(st, nper)
     _compare(sdr, cfgo, acq, rec_o, ntr_o, rec_g, ntr_g, 1 + 2 * cfgo.corrn)
@@ -84,6 +84,19 @@ def test_tracking_real_if(sdr, oracle):
 def test_tracking_iq_rtlsdr_style(sdr, oracle):
     cfg, prns = util.scene_c5(sdr, nsats=4)
     _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=2), 4600, util.FS5, 2)
+
+
+def test_tracking_sbas_l1(sdr, oracle):
+    """SBAS L1 channels (CTYPE_L1SBAS: the C/A-family codes 120-158, 500 symbols/s = 2 code periods per
+    symbol, loop interval 2 ms, src/sdr.h:154,165; bit sync takes the 'keyed on PRN > 5' branch of
+    checksync, src/sdrnav.c:203-215): the same closed-loop parity as the L1CA tests, against the reference
+    build.  Frame synchronisation of SBAS (Viterbi) is the host's."""
+    rng = np.random.default_rng(0x5BA5)
+    prns = [122, 133]
+    sats = [dict(prn=p, cn0=47.0, doppler=float(rng.uniform(-2500, 2500)), code_phase=float(rng.uniform(0, 1023 * 2)),
+                 carr_phase=float(rng.uniform(0, 1)), rate=0.2, nav_on=1, nav_seed=500 + p) for p in prns]
+    cfg = sdr.make_ifgen(util.FS5, 0.0, util.CF, 2, sats, sigma=20.0, seed=0xB2005BA5, bitlen=2)
+    _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=3), 4000, util.FS5, 2, ctype=27)
 
 
 def test_tracking_frame_sync_lnav(sdr, oracle):
