@@ -197,8 +197,8 @@ struct trk_state_t {
     /* frame synchronisation (GPS L1CA): nav.fbits as a ring of 2 + 300 bits (fhead = oldest),
      * flagsyncf, flagtow, polarity, firstsf, firstsfcnt (src/sdr.h:440-479) */
     uint64_t firstsf, firstsfcnt;
-    int32_t fhead, flagsyncf, flagtow, polarity, flagpolarityadd, pad3;
-    int8_t  fbits[304];
+    int32_t fhead, flagsyncf, flagtow, polarity, flagpolarityadd, flagpol;
+    int8_t  fbits[1520];                     /* 302 (L1CA), 200 (G1) or 1512 (SBAS L1) entries in use */
 };
 
 /* checksync(), src/sdrnav.c:198-233 */
@@ -227,8 +227,8 @@ __device__ static int trk_checksync(double IP, double IPold, trk_state_t *st, in
 }
 
 /* length of nav.fbits (flen + addflen, src/sdr.h:159-174): 302 for GPS L1CA, 200 for GLONASS G1
- * (told apart by nav.rate, 20 against 10 code periods per unit; SBAS is not synchronised here) */
-__device__ __forceinline__ int trk_fbits_len(int rate) { return rate == 10 ? 200 : 302; }
+ * 1512 for SBAS L1 (told apart by nav.rate: 20, 10, 2 code periods per unit) */
+__device__ __forceinline__ int trk_fbits_len(int rate) { return rate == 10 ? 200 : (rate == 2 ? 1512 : 302); }
 
 /* checkbit(), src/sdrnav.c:241-282; nav.fbits is a ring (fhead = oldest) */
 __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int rate)
@@ -242,7 +242,8 @@ __device__ static void trk_checkbit(double IP, int loopms, trk_state_t *st, int 
     }
     st->swloop = (st->navcnt % loopms == 0) ? 1 : 0;
     if (diffi == 0) {
-        st->bit = (st->bitIP < 0) ? -1 : 1;
+        const int pol = st->flagpol ? -1 : 1;                 /* set by a failed SBAS parity check, sdrnav.c:264-270, 405-407 */
+        st->bit = (st->bitIP < 0) ? -pol : pol;
         st->fbits[st->fhead] = (int8_t)st->bit;               /* shift left + append, sdrnav.c:272-275 */
         st->fhead = (st->fhead + 1 == trk_fbits_len(rate)) ? 0 : st->fhead + 1;
         st->swsync = 1;
@@ -310,6 +311,86 @@ __device__ __noinline__ static int trk_frame_sync_g1(trk_state_t *st)
     return 1;
 }
 
+/* SBAS L1 frame synchronisation by the whole epilogue warp: predecodefec() - the K = 7 rate-1/2 Viterbi
+ * decoder of lib/ka9q-fec/viterbi27_port.c over the 1512 symbols of nav.fbits, started from scratch at
+ * every symbol as the reference does (src/sdrnav.c:300-321) - then findpreamble() for two consecutive
+ * preambles (:383-389) and paritycheck() with CRC-24Q (:347-356).
+ * One lane per butterfly (viterbi27_port.c:127-141): lane i holds the path metrics of states i and
+ * i + 32, produces those of 2i and 2i + 1 and their two decision bits; the metrics move to their
+ * next owners with four shuffles, the decision words (states 0..31 / 32..63, decision_t.w[0..1] of
+ * which only the low 32 bits are ever set) are OR-reduced into vdec[step][2].  unsigned arithmetic and
+ * the signed comparison exactly as in the C source; no renormalisation there either (756 x 510 fits).
+ * Chain-back from state 0 by lane 0 (:76-104).  Returns findpreamble()'s value; sets polarity, flagpol. */
+__device__ __noinline__ static int trk_frame_sync_sbas(trk_state_t *st, unsigned int *vdec, int lane)
+{
+    constexpr int NSYM = 1512, NSTEP = NSYM / 2, NBITS = 750;
+    const unsigned int b0 = (__popc((2u * lane) & 0x6Du) & 1) ? 255u : 0u;      /* set_viterbi27_polynomial_port */
+    const unsigned int b1 = (__popc((2u * lane) & 0x4Fu) & 1) ? 255u : 0u;
+    unsigned int lo = (lane == 0) ? 0u : 63u, hi = 63u;                         /* init_viterbi27_port, start state 0 */
+    int k = st->fhead;
+    for (int step = 0; step < NSTEP; step++) {
+        const unsigned int s0 = (st->fbits[k] == 1) ? 0u : 255u;                /* enc[i] = fbits == 1 ? 0 : 255 */
+        k = (k + 1 == NSYM) ? 0 : k + 1;
+        const unsigned int s1 = (st->fbits[k] == 1) ? 0u : 255u;
+        k = (k + 1 == NSYM) ? 0 : k + 1;
+        const unsigned int metric = (b0 ^ s0) + (b1 ^ s1);
+        unsigned int m0 = lo + metric, m1 = hi + (510u - metric);
+        const unsigned int d0 = ((int)(m0 - m1) > 0) ? 1u : 0u;
+        const unsigned int n0 = d0 ? m1 : m0;
+        m0 -= (metric + metric - 510u);
+        m1 += (metric + metric - 510u);
+        const unsigned int d1 = ((int)(m0 - m1) > 0) ? 1u : 0u;
+        const unsigned int n1 = d1 ? m1 : m0;
+        const unsigned int x = (d0 << ((2 * lane) & 31)) | (d1 << ((2 * lane + 1) & 31));
+        const unsigned int w0 = __reduce_or_sync(0xffffffffu, lane < 16 ? x : 0u);
+        const unsigned int w1 = __reduce_or_sync(0xffffffffu, lane >= 16 ? x : 0u);
+        if (lane == 0) { vdec[2 * step] = w0; vdec[2 * step + 1] = w1; }
+        const int src = lane >> 1;
+        const unsigned int a0 = __shfl_sync(0xffffffffu, n0, src), a1 = __shfl_sync(0xffffffffu, n1, src);
+        const unsigned int c0 = __shfl_sync(0xffffffffu, n0, 16 + src), c1 = __shfl_sync(0xffffffffu, n1, 16 + src);
+        lo = (lane & 1) ? a1 : a0;
+        hi = (lane & 1) ? c1 : c0;
+    }
+    __syncwarp();
+    int found = 0;
+    if (lane == 0) {
+        /* chainback_viterbi27_port(fec, dec, 750, 0): decisions are read 6 steps past the data bit */
+        unsigned int dbits[24];                                                 /* decoded bit n at dbits[n >> 5] bit n & 31 */
+        for (int i = 0; i < 24; i++) dbits[i] = 0u;
+        unsigned int e = 0u;
+        for (int n = NBITS - 1; n >= 0; n--) {
+            const unsigned int sidx = e >> 2;
+            const unsigned int kk = (vdec[2 * (n + 6) + (sidx >> 5)] >> (sidx & 31u)) & 1u;
+            e = (e >> 1) | (kk << 7);
+            dbits[n >> 5] |= kk << (n & 31);
+        }
+        auto bit = [&](int n) -> int { return (int)((dbits[n >> 5] >> (n & 31)) & 1u); };     /* fbitsdec = bit ? -1 : 1 */
+        const int pre[16] = {1, -1, 1, -1, 1, 1, -1, -1, -1, 1, 1, -1, -1, 1, -1, 1};         /* pre_sbs[0..15], src/sdrinit.c:498-499 */
+        int corr = 0;
+        for (int i = 0; i < 8; i++) {
+            corr += (bit(i) ? -1 : 1) * pre[i];
+            corr += (bit(250 + i) ? -1 : 1) * pre[8 + i];
+        }
+        if (abs(corr) == 16) {
+            st->polarity = corr > 0 ? 1 : -1;
+            /* paritycheck(): the 226 message bits right-aligned in 29 bytes, CRC-24Q against the next 24;
+             * a byte's bit is 1 where polarity * fbitsdec < 0 (bits2byte, src/sdrnav.c:154-171)         */
+            const unsigned int flip = (st->polarity < 0) ? 1u : 0u;
+            unsigned int crc = 0u, want = 0u;
+            for (int i = 0; i < 6 + 226; i++) {
+                const unsigned int b = (i < 6) ? 0u : ((unsigned int)bit(i - 6) ^ flip);
+                crc ^= b << 23;
+                crc = (crc & 0x800000u) ? ((crc << 1) ^ 0x1864CFBu) : (crc << 1);
+                crc &= 0xFFFFFFu;
+            }
+            for (int i = 0; i < 24; i++) want = (want << 1) | ((unsigned int)bit(226 + i) ^ flip);
+            if (crc == want) found = 1;
+            else if (st->polarity == 1) st->flagpol = 1;
+        }
+    }
+    return __shfl_sync(0xffffffffu, found, 0);
+}
+
 __device__ __forceinline__ long long trk_clock()
 {
     long long t;
@@ -367,7 +448,7 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
                                     const unsigned int *sumQ, double remc, double remp,
                                     sdrb200_trk_rec_t *rec, int lane, long long *ep = nullptr,
                                     trk_lf_t *lf = nullptr, volatile int *lf_flag = nullptr, int lf_val = 0,
-                                    trk_obsstock_t *obs = nullptr)
+                                    trk_obsstock_t *obs = nullptr, unsigned int *vdec = nullptr)
 {
     long long e0 = 0;
 #define TRK_EP(i) do { if (ep && lane == 0) { const long long e1 = trk_clock(); ep[i] += e1 - e0; e0 = e1; } } while (0)
@@ -413,6 +494,19 @@ __device__ static void trk_epilogue(const trk_chan_dev_t *ch, trk_state_t *st, c
         }
     }
     __syncwarp();
+    /* SBAS L1 (2 code periods per symbol): the same place in sdrnavigation(), but the Viterbi decoder is work
+     * for the whole warp */
+    if (ch->navrate == 2 && vdec) {
+        const int need = __shfl_sync(0xffffffffu, (st->flagsync && st->swsync && !st->flagtow) ? 1 : 0, 0);
+        if (need) {
+            const int r = trk_frame_sync_sbas(st, vdec, lane);
+            if (lane == 0) {
+                st->flagsyncf = r;
+                if (r) { st->firstsf = st->buffloc; st->firstsfcnt = st->cnt; st->flagtow = 1; }
+            }
+            __syncwarp();
+        }
+    }
     TRK_EP(12);
     /* cumsumcorr(), src/sdrtrk.c:64-76 (overlay polarity is +1 for L1CA/SBAS/G1) */
     for (int i = lane; i < ntap; i += 32) {

@@ -70,6 +70,7 @@ struct trk_cl_smem_t {
     volatile int pushed[2];                  /* periods the pusher has written to their team     */
     nco_steptab_t tab[2];                    /* per-binade increments of the current carrier / code step */
     trk_state_t st;
+    unsigned int vdec[2 * 756];              /* decision words of the SBAS Viterbi decoder (trk_frame_sync_sbas) */
     sdrb200_trk_rec_t rec;
     trk_chan_dev_t chc;                      /* the channel's constants (code excluded: t.codetab) */
 };
@@ -367,7 +368,8 @@ k_trk_cl(const trk_chan_dev_t *__restrict__ chans, trk_state_t *__restrict__ sta
             if (lane == 0) { st->currnsamp = hd->n; if (res[2 * SDRB200_MAXTAPS]) errw = 1; }
             __syncwarp();
             trk_epilogue(ch, st, res, res + SDRB200_MAXTAPS, hd->remc, hd->remp, recs ? &sm->rec : nullptr, lane,
-                         (prof && chno == 0) ? prof : nullptr, &sm->lf, &sm->loops_count, q + 1, obsst ? &obsst[chno] : nullptr);
+                         (prof && chno == 0) ? prof : nullptr, &sm->lf, &sm->loops_count, q + 1, obsst ? &obsst[chno] : nullptr,
+                         sm->vdec);
             if (recs) {
                 const uint32_t *src = (const uint32_t *)&sm->rec;
                 uint32_t *dst = (uint32_t *)&recs[(size_t)chno * nperiods + q];

@@ -207,8 +207,9 @@ typedef struct {
     int    corrp[SDRB200_MAXCORRN]; /* trk.corrp[] tap offsets (samples)        */
     int    ne, nl;           /* trk.ne, trk.nl                                  */
     int    loopms;           /* trk.loopms                                      */
-    int    navrate;          /* nav.rate (code periods per data bit); frame sync on the device for
-                              * 20 (GPS L1CA subframes) and 10 (GLONASS G1 strings, src/sdrnav.c:394-400) */
+    int    navrate;          /* nav.rate (code periods per data bit); frame sync on the device for 20 (GPS L1CA
+                              * subframes), 10 (GLONASS G1 strings) and 2 (SBAS L1: Viterbi, preambles, CRC-24Q;
+                              * src/sdrnav.c:288-411) */
     sdrb200_loop_t prm1, prm2;
     const int8_t *code;      /* [clen] +-1                                      */
     /* state handed over by acquisition (src/sdracq.c:51-56)                    */

@@ -99,6 +99,49 @@ def test_tracking_sbas_l1(sdr, oracle):
     _run(sdr, oracle, cfg, prns, ob.cfg_rtlsdr(acq_intg=3), 4000, util.FS5, 2, ctype=27)
 
 
+def test_tracking_frame_sync_sbas(sdr):
+    """SBAS L1 frame synchronisation on the device: the K = 7 Viterbi decoder of predecodefec() over the 1512-symbol
+    register at every symbol, two consecutive preambles, CRC-24Q (src/sdrnav.c:300-321, 347-356, 383-411,
+    lib/ka9q-fec/viterbi27_port.c).  IF carrying convolutionally encoded type-12 messages with valid CRC
+    (tests/testkit/ifgen.h nav_on = 4), one satellite sent inverted.  Oracle: the reference build itself (this fork
+    runs SBAS channels).  The symbol at which the preambles are accepted, the polarity, flagtow and the hand-over
+    (firstsf, firstsfcnt) must be the reference's."""
+    if not ob.have_ref():
+        pytest.skip("reference build not present (the port has no SBAS frame sync)")
+    oracle = ob.ref()
+    rng = np.random.default_rng(0x5BA6)
+    prns = [122, 133, 138]
+    sats = [dict(prn=p, cn0=49.0, doppler=float(rng.uniform(-2500, 2500)), code_phase=float(rng.uniform(0, 1023 * 2)),
+                 carr_phase=float(rng.uniform(0, 1)), rate=0.2, nav_on=4, nav_seed=(900 + p) | ((i & 1) << 16))
+            for i, p in enumerate(prns)]
+    cfg = sdr.make_ifgen(util.FS5, 0.0, util.CF, 2, sats, sigma=20.0, seed=0xB2005BA6, bitlen=2)
+    nper = 10500
+    avail = 65536
+    total = avail + 2048 * (nper + 8)
+    st = sdr.Stream(2, total)
+    st.push_ifgen(cfg, total)
+    host = st.read(0, total)
+    cfgo = ob.cfg_rtlsdr(acq_intg=3)
+    acq, rec_o, ntr_o = oracle.acq_track(cfgo, host, avail, prns, nper, ctypes=[27] * len(prns))
+    assert all(a.acquired for a in acq)
+    chans = [sdr.make_trk_chan(cfgo.f_sf, cfgo.f_if, cfgo.f_cf, 2, a.prn, sdr.gencode(a.prn, 27)[0],
+                               a.buffloc, a.acqfreq, cfgo.corrn, cfgo.corrd, cfgo.corrp,
+                               list(cfgo.dllb), list(cfgo.pllb), list(cfgo.fllb), ctype=27) for a in acq]
+    rec_g, ntr_g = sdr.Tracking(chans).run(st, nper)
+    synced = 0
+    for ch, a in enumerate(acq):
+        assert ntr_o[ch] == nper and ntr_g[ch] == nper
+        o, g = rec_o[ch], rec_g[ch]
+        for f in ("currnsamp", "flagsync", "synci", "flagsyncf", "flagtow", "polarity"):
+            assert np.array_equal(o[f], g[f]), (a.prn, f, int(np.argmax(o[f] != g[f])))
+        if o["flagsyncf"].max() == 1:                       # the reference's 2-period bit sync can lock across symbols
+            synced += 1
+            k = int(np.argmax(o["flagsyncf"] > 0))
+            assert int(g["firstsfcnt"][-1]) == int(o["cnt"][k]) and int(g["firstsf"][-1]) == int(o["buffloc"][k])
+            print(f"prn {a.prn}: frame sync at period {k}, polarity {int(g['polarity'][-1])}")
+    assert synced >= 2, "the reference did not frame-sync on at least two of the three satellites"
+
+
 def test_tracking_frame_sync_lnav(sdr, oracle):
     """Frame synchronisation on the device (findpreamble + paritycheck for GPS L1CA,
     src/sdrnav.c:43-58, 324-411; paritycheck_l1ca, src/sdrnav_gps.c:141-166): IF carrying LNAV

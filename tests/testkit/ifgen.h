@@ -38,7 +38,8 @@ typedef struct {
     int      prn;              /* code number (index into the code table)   */
     int      nav_on;           /* 0: all +1, 1: 50 bps random data, 2: 50 bps GPS LNAV subframes
                                 * (preamble, TOW count, valid (32,26) parity in every word),
-                                * 3: GLONASS strings (random 10 ms units + the 30-unit time mark) */
+                                * 3: GLONASS strings (random 10 ms units + the 30-unit time mark),
+                                * 4: SBAS L1 messages (preamble, type 12, CRC-24Q, rate-1/2 K = 7 code) */
     double   cn0_dbhz;         /* carrier-to-noise density                  */
     double   doppler_hz;       /* carrier Doppler at t=0                    */
     double   doppler_rate;     /* Hz/s                                      */
@@ -131,6 +132,55 @@ IFGEN_HD int ifgen_g1bit(uint64_t nav_seed, int64_t unit)
     return ifgen_navbit(nav_seed, unit) * inv;
 }
 
+/* nav_on == 4: symbol s (500 symbols/s, bitlen = 2 code periods) of an endless train of SBAS L1 messages as the
+ * reference's receiver expects them (src/sdrnav.c:300-321, 347-356, 383-389; src/sdrnav_sbs.c:88-141): 250-bit
+ * messages = 8-bit preamble (0x53, 0x9A, 0xC6 in turn), message type 12 (the only one whose decoding yields the
+ * week, without which the reference drops its frame sync again), 212 pseudo-random bits, CRC-24Q over the 226 bits
+ * right-aligned in 29 bytes; rate-1/2 K = 7 convolutional code in the order of the ka9q decoder the reference
+ * links (encstate = encstate << 1 | bit; symbols parity(encstate & 0x6d), parity(encstate & 0x4f),
+ * lib/ka9q-fec/fec.h:13-14, viterbi27_port.c:48-56); data bit / symbol 0 is sent as +1, 1 as -1
+ * (enc[i] = fbits == 1 ? 0 : 255, src/sdrnav.c:304-305).  nav_seed bit 16 set: the train is sent inverted.  */
+IFGEN_HD unsigned int ifgen_crc24q_bits(unsigned int crc, int bit)
+{
+    crc ^= (unsigned int)bit << 23;
+    crc = (crc & 0x800000u) ? ((crc << 1) ^ 0x1864CFBu) : (crc << 1);
+    return crc & 0xFFFFFFu;
+}
+IFGEN_HD int ifgen_sbas_databit(uint64_t seed, int64_t m, int j)          /* j < 226 */
+{
+    if (j < 8) { const unsigned int pre[3] = {0x53u, 0x9Au, 0xC6u}; return (int)((pre[(int)(m % 3)] >> (7 - j)) & 1u); }
+    if (j < 14) return (12 >> (13 - j)) & 1;
+    return (int)(ifgen_mix64(seed ^ (uint64_t)(m * 256 + j) * 0xD6E8FEB86659FD93ULL) & 1u);
+}
+IFGEN_HD int ifgen_sbas_msgbit(uint64_t seed, int64_t m, int j, unsigned int *crc_cache, int64_t *crc_m)
+{
+    if (j < 226) return ifgen_sbas_databit(seed, m, j);
+    if (*crc_m != m) {
+        unsigned int crc = 0;
+        int i;
+        for (i = 0; i < 6; i++) crc = ifgen_crc24q_bits(crc, 0);          /* right alignment: 6 leading zero bits */
+        for (i = 0; i < 226; i++) crc = ifgen_crc24q_bits(crc, ifgen_sbas_databit(seed, m, i));
+        *crc_cache = crc; *crc_m = m;
+    }
+    return (int)((*crc_cache >> (23 - (j - 226))) & 1u);
+}
+IFGEN_HD int ifgen_sbassym(uint64_t nav_seed, int64_t sym)
+{
+    const int inv = ((nav_seed >> 16) & 1) ? -1 : 1;
+    unsigned int reg = 0, crc = 0, v;
+    int64_t crc_m = -1, b, i;
+    int which;
+    if (sym < 0) return inv;
+    b = sym >> 1; which = (int)(sym & 1);
+    for (i = b - 6; i <= b; i++) {
+        int bit = 0;
+        if (i >= 0) { const int64_t m = i / 250; bit = ifgen_sbas_msgbit(nav_seed, m, (int)(i - m * 250), &crc, &crc_m); }
+        reg = (reg << 1) | (unsigned int)bit;
+    }
+    v = reg & (which ? 0x4Fu : 0x6Du);
+    return ifgen_parity32(v) ? -inv : inv;
+}
+
 /* one sample; codes = [nsat][IFGEN_MAXCLEN] of +-1; out[0]=I (or real), out[1]=Q */
 IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
                            uint64_t k, signed char *out)
@@ -149,7 +199,8 @@ IFGEN_HD void ifgen_sample(const ifgen_cfg_t *c, const signed char *codes,
         int    d = 1;
         if (chip >= c->clen) chip = c->clen - 1;
         if (chip < 0) chip = 0;
-        if (sv->nav_on == 3) d = ifgen_g1bit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        if (sv->nav_on == 4) d = ifgen_sbassym(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
+        else if (sv->nav_on == 3) d = ifgen_g1bit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
         else if (sv->nav_on == 2) d = ifgen_lnavbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
         else if (sv->nav_on) d = ifgen_navbit(sv->nav_seed, (int64_t)floor(per / (double)c->bitlen));
         cyc = sv->carr_phase + (c->f_if + fd + sv->carr_offset_hz) * t + 0.5 * fdr * t * t;
