@@ -1707,7 +1707,9 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
 static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *warp32)
 {
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
-    if (lsub > 16384) lsub = 8192;                                   /* scratch path */
+    /* two-pass path: 256-thread CTAs (L = 4096) as long as the recombination has a kernel for M / 4096 sub-transforms
+     * (config 4, M = 2^20 = 256 x 4096: 706 -> 619 ms per search against 128 x 8192; 64 x 16384: 820 ms) */
+    if (lsub > 16384) lsub = (M / 4096 <= 256) ? 4096 : (M / 8192 <= 256 ? 8192 : 16384);
     const char *env = getenv("SDRB200_LSUB");
     if (env) { int v = atoi(env); if ((v == 1024 || v == 2048 || v == 4096 || v == 8192 || v == 16384) && v <= M) lsub = v; }
     /* M = 65536 (GLONASS at 20 MS/s): 16 x 4096 in a cluster of 16 CTAs (non-portable size) keeps the
