@@ -1754,10 +1754,14 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->h_freq = (double *)malloc(sizeof(double) * a->nfx);
     memcpy(a->h_freq, cfg->freq, sizeof(double) * a->nfx);
     a->cfg.freq = a->h_freq; a->cfg.codes = NULL;
-    /* scratch chunking: keep S within ~64 MB so that it stays L2-resident */
+    /* scratch chunking.  Round 1 kept S within 64 MB "so that it stays L2-resident"; measured at config-4 size
+     * the opposite holds - 8 rows per launch pair 618 ms, 16: 564, 36: 530, 141 (a whole PRN, 1.2 GB of scratch in
+     * HBM): 493 ms, two or more PRNs per chunk the same - large grids matter more than where the scratch lives.
+     * SDRB200_SCRATCH_MB overrides the 1.5 GB budget.                                                       */
     {
         size_t per_prn = (size_t)nfreq * M * sizeof(float2);
-        size_t budget = (size_t)64 << 20;
+        size_t budget = (size_t)1536 << 20;
+        { const char *env = getenv("SDRB200_SCRATCH_MB"); if (env && atoi(env) >= 8) budget = (size_t)atoi(env) << 20; }
         a->chunk = (int)(budget / per_prn); if (a->chunk < 1) a->chunk = 1; if (a->chunk > nprn) a->chunk = nprn;
         /* one PRN's bins alone exceed the budget (20 ms coherent blocks: 8.4 MB per row):
          * the chunk becomes a group of bins of one PRN                                  */
