@@ -945,6 +945,17 @@ def run_b200(args):
             t_s.append(time.perf_counter() - t0)
             t_k.append(e1.ms_since(e0) if plan4 else 0.0)
         ts4 = min(t_s)
+        kern4 = None
+        if plan4:                                            # per-kernel share of one search on this rank (event pairs)
+            sdr.check(lib.sdrb200_acq_set_timing(plan4.h, 1), "set_timing")
+            plan4.enqueue(st4, 0); plan4.sync()
+            ms4_4 = (C.c_double * 4)(); c4_4 = (C.c_longlong * 4)()
+            sdr.check(lib.sdrb200_acq_kernel_ms(plan4.h, ms4_4, c4_4), "kernel_ms")
+            sdr.check(lib.sdrb200_acq_set_timing(plan4.h, 0), "set_timing")
+            tot4_ms = max(sum(ms4_4[i] for i in range(4)), 1e-9)   # the plan keeps 256 event pairs: shares of those, not totals
+            kern4 = {"forward (k_fwd_split + k_fft_rows)": round(ms4_4[0] / tot4_ms, 3), "k_row": round(ms4_4[1] / tot4_ms, 3),
+                     "k_comb_fft": round(ms4_4[2] / tot4_ms, 3), "k_peak_hbm": round(ms4_4[3] / tot4_ms, 3),
+                     "unit": "share of the timed launches (first 256 of the search)"}
         if dist is not None:
             tt = torch.tensor([ts4], dtype=torch.float64, device="cuda")
             dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -971,6 +982,7 @@ def run_b200(args):
         strong_obj = {"workload": f"ONE search, {len(prns4)} PRN (GPS 1-32 + SBAS 120-138) x {nf4} bins (100 Hz) x {n4} lags, "
                                   f"{ncoh4} ms coherent (M = 2^20), up to {intg4} non-coherent steps with early exit (BASELINE configs[3])",
                       "scaling": "strong", "partition": "PRN slabs, one NCCL all-gather of the tuples per search from device memory",
+                      "kernel_share_this_rank": kern4,
                       "n_gpus": world, "prns_per_gpu": [len(sdr.shard.prn_slab(prns4, r_, world)) for r_ in range(world)],
                       "ms_per_search": ts4 * 1e3, "ms_search_kernels_this_rank": min(t_k),
                       "cells_per_s": len(prns4) * nf4 * n4 * steps_run / ts4, "integration_steps_run": steps_run,

@@ -5,7 +5,7 @@ env $e timeout 500 python bench.py --no-cpu --no-trk --c5-streams 0 --no-c3 --no
 python - <<P
 import json
 d=json.loads([x for x in open('gpurun_out/c4_$i.json') if x.startswith('{')][-1])
-c=d['strong_scaling_c4']; print('  C4 %.1f G cells/s %.1f ms per search, found bins %s' % (c['cells_per_s']/1e9, c['ms_per_search'], c['found_bins'] == {k:[v, c['found_bins'][k][1]] for k,v in c['true_bins'].items()}))
+c=d["strong_scaling_c4"]; print(c.get("kernel_share_this_rank")); print('  C4 %.1f G cells/s %.1f ms per search, found bins %s' % (c['cells_per_s']/1e9, c['ms_per_search'], c['found_bins'] == {k:[v, c['found_bins'][k][1]] for k,v in c['true_bins'].items()}))
 P
 i=$((i+1))
 done
