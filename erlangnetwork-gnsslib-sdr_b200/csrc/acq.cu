@@ -337,7 +337,9 @@ k_row(const float2 *__restrict__ Xs, const float2 *__restrict__ Cs, const float2
 {
     extern __shared__ float2 fsm[];
     constexpr int T = L / 16;
-    const int q = blockIdx.x, fl = blockIdx.y, f = f0 + fl, pc = blockIdx.z, p = prn0 + pc, tid = threadIdx.x;
+    /* grid (PRNs of the chunk, R, bins): the CTAs that read the same slice of a spectrum - one per PRN - are
+     * scheduled next to each other, so that slice comes from HBM once per chunk instead of once per PRN */
+    const int pc = blockIdx.x, q = blockIdx.y, fl = blockIdx.z, f = f0 + fl, p = prn0 + pc, tid = threadIdx.x;
     if (frozen[p]) return;
     const float2 *x = Xs + ((size_t)f * R + q) * L;
     const float2 *c = Cs + ((size_t)p * R + q) * L;
@@ -1479,7 +1481,7 @@ template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, in
                                        int first_step)
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
-    dim3 grid(a->R, nfc, nprn);
+    dim3 grid(nprn, a->R, nfc);
     const float invM2 = 1.0f / ((float)a->M * (float)a->M);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_row<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, f0, nfc, a->d_S, a->d_P,
@@ -1756,11 +1758,11 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->cfg.freq = a->h_freq; a->cfg.codes = NULL;
     /* scratch chunking.  Round 1 kept S within 64 MB "so that it stays L2-resident"; measured at config-4 size
      * the opposite holds - 8 rows per launch pair 618 ms, 16: 564, 36: 530, 141 (a whole PRN, 1.2 GB of scratch in
-     * HBM): 493 ms, two or more PRNs per chunk the same - large grids matter more than where the scratch lives.
-     * SDRB200_SCRATCH_MB overrides the 1.5 GB budget.                                                       */
+     * HBM): 493 ms - large grids matter more than where the scratch lives.  With the PRNs of a chunk adjacent in the grid of k_row (a spectrum slice comes from HBM once per chunk) two PRNs
+     * per chunk give another 3-5 %: 3 GB budget, SDRB200_SCRATCH_MB overrides.                             */
     {
         size_t per_prn = (size_t)nfreq * M * sizeof(float2);
-        size_t budget = (size_t)1536 << 20;
+        size_t budget = (size_t)3072 << 20;
         { const char *env = getenv("SDRB200_SCRATCH_MB"); if (env && atoi(env) >= 8) budget = (size_t)atoi(env) << 20; }
         a->chunk = (int)(budget / per_prn); if (a->chunk < 1) a->chunk = 1; if (a->chunk > nprn) a->chunk = nprn;
         /* one PRN's bins alone exceed the budget (20 ms coherent blocks: 8.4 MB per row):
