@@ -46,6 +46,7 @@ struct acq_rowstat_t {
 };
 
 #define ACQ_MAXEV 256
+#define ACQ_MAXLANES 4
 struct sdrb200_acq {
     sdrb200_acq_cfg_t cfg;
     int n_eff, m_ref, M, L, R;
@@ -56,6 +57,9 @@ struct sdrb200_acq {
     int comb_fft;                    /* scratch path: radix-R recombination + k_peak_hbm                   */
     double *h_freq;
     cudaStream_t st;
+    int nlanes;                      /* two-pass path: chunks in flight at once (own streams and scratch slices) */
+    cudaStream_t lane_st[ACQ_MAXLANES];
+    cudaEvent_t lane_ev[ACQ_MAXLANES], ev_fork;
     float2 *d_tw;                    /* [M] forward twiddles                  */
     uint8_t *d_cidx;                 /* [nfreq][m_ref] carrier table indices  */
     float2 *d_Xs;                    /* [nfreq][R][L]                         */
@@ -387,7 +391,7 @@ k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L
         const int tl = t & (L - 1);
         float2 y = __ldg(&s[tl]);
         for (int q = 1; q < R; q++) {
-            float2 w = __ldg(&tw[(size_t)(((long long)t * q) & (M - 1))]);
+            float2 w = __ldg(&tw[(size_t)(((long long)t * q) % M)]);
             y = cadd(y, cmulc(__ldg(&s[(size_t)q * L + tl]), w));      /* * conj(W_M^(t q)) */
         }
         float pw = (y.x * y.x + y.y * y.y) * invM2;
@@ -399,10 +403,40 @@ k_comb(const float2 *__restrict__ S, const float2 *__restrict__ tw, int R, int L
     acq_row_stats(Prow, n_eff, nsampchip, tmax, tidx, &rows[(size_t)p * nfreq + f]);
 }
 
+/* 5-point DFT, z[a] = sum_g z[g] exp(SIGN 2 pi i a g / 5): the two conjugate pairs share their cosine and sine sums */
+template <int SIGN> __device__ __forceinline__ void fft5(float2 &x0, float2 &x1, float2 &x2, float2 &x3, float2 &x4)
+{
+    constexpr float C1 = 0.30901699437494742f, C2 = -0.80901699437494742f;      /* cos(2 pi / 5), cos(4 pi / 5) */
+    constexpr float S1 = SIGN * 0.95105651629515357f, S2 = SIGN * 0.58778525229247313f;
+    const float2 a1 = cadd(x1, x4), a2 = cadd(x2, x3), b1 = csub(x1, x4), b2 = csub(x2, x3);
+    const float2 e1 = make_float2(fmaf(C2, a2.x, fmaf(C1, a1.x, x0.x)), fmaf(C2, a2.y, fmaf(C1, a1.y, x0.y)));
+    const float2 e2 = make_float2(fmaf(C1, a2.x, fmaf(C2, a1.x, x0.x)), fmaf(C1, a2.y, fmaf(C2, a1.y, x0.y)));
+    /* i * (S1 b1 + S2 b2) and i * (S2 b1 - S1 b2) */
+    const float2 o1 = make_float2(-fmaf(S2, b2.y, S1 * b1.y), fmaf(S2, b2.x, S1 * b1.x));
+    const float2 o2 = make_float2(-fmaf(-S1, b2.y, S2 * b1.y), fmaf(-S1, b2.x, S2 * b1.x));
+    x0 = cadd(x0, cadd(a1, a2));
+    x1 = cadd(e1, o1); x4 = csub(e1, o1);
+    x2 = cadd(e2, o2); x3 = csub(e2, o2);
+}
+
 /* G-point DFT in registers, natural order: z[a] = sum_g z[g] exp(SIGN 2 pi i a g / G) */
 template <int G, int SIGN> __device__ __forceinline__ void fft_small(float2 (&z)[G])
 {
-    if constexpr (G == 2) {
+    if constexpr (G == 5) {
+        fft5<SIGN>(z[0], z[1], z[2], z[3], z[4]);
+    } else if constexpr (G == 10) {
+        /* g = 2 g1 + g2, a = a1 + 5 a2: two 5-point transforms, W_10^(a1), one radix-2 stage */
+        float2 e0 = z[0], e1 = z[2], e2 = z[4], e3 = z[6], e4 = z[8];
+        float2 o0 = z[1], o1 = z[3], o2 = z[5], o3 = z[7], o4 = z[9];
+        fft5<SIGN>(e0, e1, e2, e3, e4);
+        fft5<SIGN>(o0, o1, o2, o3, o4);
+        o1 = cmul(o1, make_float2(0.80901699437494742f, SIGN * 0.58778525229247313f));
+        o2 = cmul(o2, make_float2(0.30901699437494742f, SIGN * 0.95105651629515357f));
+        o3 = cmul(o3, make_float2(-0.30901699437494742f, SIGN * 0.95105651629515357f));
+        o4 = cmul(o4, make_float2(-0.80901699437494742f, SIGN * 0.58778525229247313f));
+        z[0] = cadd(e0, o0); z[1] = cadd(e1, o1); z[2] = cadd(e2, o2); z[3] = cadd(e3, o3); z[4] = cadd(e4, o4);
+        z[5] = csub(e0, o0); z[6] = csub(e1, o1); z[7] = csub(e2, o2); z[8] = csub(e3, o3); z[9] = csub(e4, o4);
+    } else if constexpr (G == 2) {
         const float2 a = z[0], b = z[1]; z[0] = cadd(a, b); z[1] = csub(a, b);
     } else if constexpr (G == 4) {
         fft4<SIGN>(z[0], z[1], z[2], z[3]);
@@ -438,7 +472,7 @@ k_fwd_split(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict
 {
     extern __shared__ float2 xsm[];                       /* [16 q2][G g][32 lanes] */
     __shared__ float2 s_lut[32];
-    constexpr int R = 16 * G, A2 = 16 / G;
+    constexpr int R = 16 * G, A2 = (16 + G - 1) / G;      /* q2 values finished per warp (G = 5, 10: the last round is partial) */
     const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
     const int t = blockIdx.x * 32 + lane, f = blockIdx.y;
     const int M = R * L;
@@ -471,7 +505,8 @@ k_fwd_split(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict
     __syncthreads();
 #pragma unroll
     for (int i = 0; i < A2; i++) {
-        const int q2 = g * A2 + i;
+        const int q2 = g + G * i;
+        if (q2 >= 16) break;
         float2 z[G];
 #pragma unroll
         for (int gg = 0; gg < G; gg++) z[gg] = xsm[(q2 * G + gg) * 32 + lane];
@@ -479,7 +514,7 @@ k_fwd_split(const int8_t *__restrict__ win, int nlive, const uint8_t *__restrict
 #pragma unroll
         for (int q1 = 0; q1 < G; q1++) {
             const int q = q2 + 16 * q1;
-            out[((size_t)f * R + q) * L + t] = cmul(z[q1], __ldg(&tw[(t * q) & (M - 1)]));
+            out[((size_t)f * R + q) * L + t] = cmul(z[q1], __ldg(&tw[t * q]));                 /* t q < L R = M */
         }
     }
 }
@@ -519,7 +554,7 @@ k_fwd_split_small(const int8_t *__restrict__ win, int nlive, const uint8_t *__re
     fft_small<R, -1>(z);
 #pragma unroll
     for (int q = 0; q < R; q++)
-        out[((size_t)f * R + q) * L + t] = (q == 0) ? z[0] : cmul(z[q], __ldg(&tw[(t * q) & (M - 1)]));
+        out[((size_t)f * R + q) * L + t] = (q == 0) ? z[0] : cmul(z[q], __ldg(&tw[t * q]));
 }
 
 /* operand order of the warp kernels (k_roww / k_rowd): lane l of a warp owns the points l + 32 e;
@@ -575,7 +610,7 @@ k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, i
 {
     extern __shared__ float2 xsm[];                       /* [16 a2][G g][32 lanes] */
     __shared__ unsigned long long s_k[32];
-    constexpr int R = 16 * G, A2 = 16 / G;                /* a2 values finished per warp */
+    constexpr int R = 16 * G, A2 = (16 + G - 1) / G;      /* a2 values finished per warp */
     const int lane = threadIdx.x & 31, g = threadIdx.x >> 5;
     const int tp = blockIdx.x * 32 + lane, fl = blockIdx.y, f = f0 + fl, pc = blockIdx.z, p = prn0 + pc;
     if (frozen[p]) return;
@@ -587,8 +622,8 @@ k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, i
     {
         /* conj(W_M^(t' (g + G j))) = wg * ws^j ; powers of ws by the doubling scheme of the
          * CTA transform (depth 4), so the rounding error does not grow with j            */
-        float2 wg = __ldg(&tw[(tp * g) & (M - 1)]); wg.y = -wg.y;
-        float2 w1 = __ldg(&tw[(tp * G) & (M - 1)]); w1.y = -w1.y;
+        float2 wg = __ldg(&tw[tp * g]); wg.y = -wg.y;                   /* tp g, tp G < L G <= M */
+        float2 w1 = __ldg(&tw[tp * G]); w1.y = -w1.y;
         float2 w2 = cmul(w1, w1), w3 = cmul(w2, w1), w4 = cmul(w2, w2);
         float2 w5 = cmul(w4, w1), w6 = cmul(w3, w3), w7 = cmul(w4, w3), w8 = cmul(w4, w4);
         float2 w9 = cmul(w8, w1), w10 = cmul(w5, w5), w11 = cmul(w8, w3), w12 = cmul(w6, w6);
@@ -612,7 +647,8 @@ k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, i
     float bv = -1.f; int bt = 0;
 #pragma unroll
     for (int i = 0; i < A2; i++) {
-        const int a2 = g * A2 + i;
+        const int a2 = g + G * i;
+        if (a2 >= 16) break;
         float2 z[G];
 #pragma unroll
         for (int gg = 0; gg < G; gg++) z[gg] = xsm[(a2 * G + gg) * 32 + lane];
@@ -1477,14 +1513,14 @@ template <int L> static int launch_fwd(int src_kind, cudaStream_t st, int R, int
     return SDRB200_OK;
 }
 
-template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc,
+template <int L> static int launch_row(cudaStream_t st, const sdrb200_acq *a, float2 *S, int prn0, int nprn, int f0, int nfc,
                                        int first_step)
 {
     const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
     dim3 grid(nprn, a->R, nfc);
     const float invM2 = 1.0f / ((float)a->M * (float)a->M);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_row<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, f0, nfc, a->d_S, a->d_P,
+    k_row<L><<<grid, L / 16, smem, st>>>(a->d_Xs, a->d_Cs, a->d_tw, a->R, a->cfg.nfreq, prn0, f0, nfc, S, a->d_P,
                                          a->n_eff, a->cfg.nsampchip, first_step, invM2, a->d_row, a->d_frozen);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
@@ -1542,32 +1578,36 @@ static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t 
     case 64:  return launch_fwd_split_g<4>(st, a, win, scale, f0, nfc);
     case 128: return launch_fwd_split_g<8>(st, a, win, scale, f0, nfc);
     case 256: return launch_fwd_split_g<16>(st, a, win, scale, f0, nfc);
+    case 80:  return launch_fwd_split_g<5>(st, a, win, scale, f0, nfc);   /* M = 5 * 2^k */
+    case 160: return launch_fwd_split_g<10>(st, a, win, scale, f0, nfc);
     }
     return SDRB200_EINVAL;
 }
 
-/* radix-R recombination (R = 16 G, G = 2, 4, 8, 16); 0 if R has no such kernel */
-static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256; }
-template <int G> static int launch_comb_fft_g(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc,
+/* radix-R recombination (R = 16 G, G = 2, 4, 8, 16 and 5, 10); 0 if R has no such kernel */
+static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256 || R == 80 || R == 160; }
+template <int G> static int launch_comb_fft_g(cudaStream_t st, const sdrb200_acq *a, const float2 *S, int prn0, int nprn, int f0, int nfc,
                                               int first_step)
 {
     const size_t smem = sizeof(float2) * 16 * G * 32;
     dim3 grid(a->L / 32, nfc, nprn);
     const float invM2 = 1.0f / ((float)a->M * (float)a->M);
     SDRB200_CUDA_TRY(cudaFuncSetAttribute(k_comb_fft<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_comb_fft<G><<<grid, 32 * G, smem, st>>>(a->d_S, a->d_tw, a->L, a->cfg.nfreq, prn0, f0, nfc, a->d_P, a->n_eff,
+    k_comb_fft<G><<<grid, 32 * G, smem, st>>>(S, a->d_tw, a->L, a->cfg.nfreq, prn0, f0, nfc, a->d_P, a->n_eff,
                                               first_step, invM2, a->d_key, a->d_frozen);
     sdrb200_count_launch(1);
     SDRB200_CUDA_TRY(cudaGetLastError());
     return SDRB200_OK;
 }
-static int launch_comb_fft(cudaStream_t st, const sdrb200_acq *a, int prn0, int nprn, int f0, int nfc, int first_step)
+static int launch_comb_fft(cudaStream_t st, const sdrb200_acq *a, const float2 *S, int prn0, int nprn, int f0, int nfc, int first_step)
 {
     switch (a->R) {
-    case 32:  return launch_comb_fft_g<2>(st, a, prn0, nprn, f0, nfc, first_step);
-    case 64:  return launch_comb_fft_g<4>(st, a, prn0, nprn, f0, nfc, first_step);
-    case 128: return launch_comb_fft_g<8>(st, a, prn0, nprn, f0, nfc, first_step);
-    case 256: return launch_comb_fft_g<16>(st, a, prn0, nprn, f0, nfc, first_step);
+    case 32:  return launch_comb_fft_g<2>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 64:  return launch_comb_fft_g<4>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 128: return launch_comb_fft_g<8>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 256: return launch_comb_fft_g<16>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 80:  return launch_comb_fft_g<5>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 160: return launch_comb_fft_g<10>(st, a, S, prn0, nprn, f0, nfc, first_step);
     }
     return SDRB200_EINVAL;
 }
@@ -1696,6 +1736,8 @@ extern "C" void sdrb200_acq_destroy(sdrb200_acq_t *a)
     if (a->h_res) cudaFreeHost(a->h_res);
     if (a->h_pin) cudaFreeHost(a->h_pin);
     if (a->ev0[0]) for (int i = 0; i < ACQ_MAXEV; i++) { cudaEventDestroy(a->ev0[i]); cudaEventDestroy(a->ev1[i]); }
+    for (int l = 0; l < ACQ_MAXLANES; l++) { if (a->lane_st[l]) cudaStreamDestroy(a->lane_st[l]); if (a->lane_ev[l]) cudaEventDestroy(a->lane_ev[l]); }
+    if (a->ev_fork) cudaEventDestroy(a->ev_fork);
     if (a->st) cudaStreamDestroy(a->st);
     free(a->h_freq);
     free(a);
@@ -1708,6 +1750,14 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
  * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
 static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *warp32)
 {
+    if (M % 5 == 0) {                                    /* 5 * 2^k: two-pass path only, see sdrb200_acq_create */
+        int l5 = 4096;
+        while (l5 < 16384 && M / l5 > 160) l5 <<= 1;
+        const char *e5 = getenv("SDRB200_LSUB");
+        if (e5 && (atoi(e5) == 4096 || atoi(e5) == 8192 || atoi(e5) == 16384) && (M / atoi(e5) == 80 || M / atoi(e5) == 160)) l5 = atoi(e5);
+        *L = l5; *R = M / l5; *fused = 0; *warp32 = 0;
+        return;
+    }
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
     /* two-pass path: 256-thread CTAs (L = 4096) as long as the recombination has a kernel for M / 4096 sub-transforms
      * (config 4, M = 2^20 = 256 x 4096: 706 -> 619 ms per search against 128 x 8192; 64 x 16384: 820 ms) */
@@ -1743,6 +1793,19 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     a->n_eff = cfg->nsamp * a->cfg.ncoh;
     a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
     a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
+    /* the correlation is linear for lags < n whenever the transform holds the 2 n samples of the window, so the
+     * length need not be a power of two: M = 5 * 2^k (0.625 of the next power of two) when the window fits it and the
+     * two-pass path has the radix (80 or 160 sub-transforms of 4096 .. 16384 points).  Config 4: 2 n = 654 720 <=
+     * 655 360 = 160 x 4096 instead of 2^20 - 37.5 % less arithmetic and traffic in every pass.
+     * SDRB200_ACQ_POW2 keeps the power of two.                                                                    */
+    if (!getenv("SDRB200_ACQ_POW2") && !cfg->grid_per_prn) {
+        const int m5 = a->M / 8 * 5;
+        if (m5 >= a->m_ref && m5 >= 80 * 4096) {
+            int l5 = 4096;
+            while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
+            if (m5 / l5 == 80 || m5 / l5 == 160) a->M = m5;
+        }
+    }
     acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     /* one wipe-off grid per replica (GLONASS FDMA: every channel has its own carrier, src/sdrinit.c:633-635):
@@ -1781,7 +1844,14 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
                                         !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }
+        a->nlanes = 1;
+        env = getenv("SDRB200_ACQ_LANES");
+        if (env && atoi(env) >= 1 && atoi(env) <= ACQ_MAXLANES) a->nlanes = atoi(env);
+        if (!a->comb_fft) a->nlanes = 1;
     }
+    if (getenv("SDRB200_VERBOSE"))
+        fprintf(stderr, "sdrb200: acquisition plan: window %d, transform %d = %d x %d, %s, %d PRN x %d bins per chunk, %d lane(s)\n",
+                a->m_ref, a->M, a->R, a->L, a->fused ? "cluster kernel" : "two-pass path", a->chunk, a->fchunk, a->nlanes);
     int rc = SDRB200_OK;
     /* the warp-per-sub-transform kernels are persistent: as many clusters as the GPU holds at once */
     a->rowp_ncl = 0;
@@ -1804,7 +1874,13 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     ACQ_ALLOC(a->d_cidx, (size_t)a->nfx * M);                   /* row stride M: 16-byte aligned rows */
     ACQ_ALLOC(a->d_Xs, sizeof(float2) * (size_t)a->nfx * M);
     ACQ_ALLOC(a->d_Cs, sizeof(float2) * (size_t)nprn * M);
-    if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->chunk * a->fchunk * M);
+    if (!a->fused && a->R > 1) ACQ_ALLOC(a->d_S, sizeof(float2) * (size_t)a->nlanes * a->chunk * a->fchunk * M);
+    if (rc == SDRB200_OK && a->nlanes > 1) {
+        if (cudaEventCreateWithFlags(&a->ev_fork, cudaEventDisableTiming) != cudaSuccess) rc = SDRB200_ECUDA;
+        for (int l = 0; l < a->nlanes && rc == SDRB200_OK; l++)
+            if (cudaStreamCreateWithFlags(&a->lane_st[l], cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&a->lane_ev[l], cudaEventDisableTiming) != cudaSuccess) rc = SDRB200_ECUDA;
+    }
     /* the power matrix is kept in HBM only when it has to be: accumulation over
      * several integrations, the scratch path, or on request (sdrb200_acq_keep_power) */
     if (!a->fused || a->cfg.intg > 1) ACQ_ALLOC(a->d_P, sizeof(float) * (size_t)nprn * nfreq * n_eff);
@@ -1979,18 +2055,30 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
          * then the radix-R recombination; SDRB200_ACQ_COMB_NAIVE selects the direct-sum
          * combine with per-row statistics (kept as a cross-check)                        */
         const int use_fft = a->comb_fft;
+        /* nlanes > 1: consecutive chunks go to different streams, each with its own slice of the scratch, so the
+         * sub-transform pass of one chunk fills the SMs the combine pass of another leaves idle in its tail
+         * (fork after the forward pass, join before the peak statistics)                                   */
+        const int lanes = (use_fft && !a->timing) ? a->nlanes : 1;
+        const size_t lane_elems = (size_t)a->chunk * a->fchunk * a->M;
+        int ci = 0;
+        if (lanes > 1) {
+            SDRB200_CUDA_TRY(cudaEventRecord(a->ev_fork, a->st));
+            for (int l = 0; l < lanes; l++) SDRB200_CUDA_TRY(cudaStreamWaitEvent(a->lane_st[l], a->ev_fork, 0));
+        }
         for (int p0 = 0; p0 < c->nprn; p0 += a->chunk) {
             const int np = (c->nprn - p0 < a->chunk) ? c->nprn - p0 : a->chunk;
-            for (int f0 = 0; f0 < c->nfreq; f0 += a->fchunk) {
+            for (int f0 = 0; f0 < c->nfreq; f0 += a->fchunk, ci++) {
                 const int nfc = (c->nfreq - f0 < a->fchunk) ? c->nfreq - f0 : a->fchunk;
+                cudaStream_t cst = (lanes > 1) ? a->lane_st[ci % lanes] : a->st;
+                float2 *S = a->d_S + ((lanes > 1) ? (size_t)(ci % lanes) * lane_elems : 0);
                 ACQ_T0(a);
-                ACQ_DISPATCH_L(a->L, (launch_row<LL>(a->st, a, p0, np, f0, nfc, step == 0)));
+                ACQ_DISPATCH_L(a->L, (launch_row<LL>(cst, a, S, p0, np, f0, nfc, step == 0)));
                 if (rc) return rc;
                 ACQ_T1(a, 1);
                 if (a->R > 1) {
                     ACQ_T0(a);
                     if (use_fft) {
-                        rc = launch_comb_fft(a->st, a, p0, np, f0, nfc, step == 0);
+                        rc = launch_comb_fft(cst, a, S, p0, np, f0, nfc, step == 0);
                         if (rc) return rc;
                     } else {
                         dim3 grid(nfc, np);
@@ -2004,6 +2092,11 @@ static int acq_steps(sdrb200_acq *a, const int8_t *base, uint64_t capacity, uint
                 }
             }
         }
+        if (lanes > 1)
+            for (int l = 0; l < lanes; l++) {
+                SDRB200_CUDA_TRY(cudaEventRecord(a->lane_ev[l], a->lane_st[l]));
+                SDRB200_CUDA_TRY(cudaStreamWaitEvent(a->st, a->lane_ev[l], 0));
+            }
         ACQ_T0(a);
         if (use_fft) {
             k_peak_hbm<<<c->nprn, 1024, 0, a->st>>>(a->d_P, a->d_key, c->nfreq, a->n_eff, c->nsampchip, a->d_freq,

@@ -241,9 +241,20 @@ def test_acq_cluster_exchange_repeatable(sdr):
                 assert np.array_equal(acq.power(i), P0[i]), (rep, i)
 
 
-def test_acq_weak_signal_full_size_coherent(sdr, oracle):
-    """config 4 at its real size: 20 ms coherent blocks (n = 327 360 lags, M = 2^20 = 128
-    sub-transforms of 8192: the largest transform the plan builds), 100 Hz Doppler step,
+@pytest.fixture
+def pow2_env(request, monkeypatch):
+    """SDRB200_ACQ_POW2 (read once, at plan creation) keeps the transform length a power of two."""
+    if request.param:
+        monkeypatch.setenv("SDRB200_ACQ_POW2", "1")
+    else:
+        monkeypatch.delenv("SDRB200_ACQ_POW2", raising=False)
+    return request.param
+
+
+@pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
+def test_acq_weak_signal_full_size_coherent(sdr, oracle, pow2_env):
+    """config 4 at its real size: 20 ms coherent blocks (n = 327 360 lags; M = 655 360 = 160
+    sub-transforms of 4096, radix 16 x 10 - or, with SDRB200_ACQ_POW2, 2^20 = 256 x 4096), 100 Hz Doppler step,
     2 non-coherent steps, a 30 dB-Hz GPS PRN, an SBAS PRN (133) and an absent PRN, no data
     transitions in the window.  Oracle: the reference's pcorrelator on a 20-period replica
     with its own accumulation flag, bins limited to 5 to keep the CPU side short."""
@@ -284,11 +295,14 @@ def test_acq_weak_signal_full_size_coherent(sdr, oracle):
             assert g["maxp"] > 8 * np.median(ref), p
 
 
+@pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
 @pytest.mark.parametrize("ncoh,dtype", [(10, 1), (40, 1), (40, 2)])
-def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype):
-    """The two-pass path at its other radices: 10 ms real (M = 2^19, R = 64, G = 4), 40 ms real
-    (M = 2^21, R = 256, G = 16) and 40 ms I/Q at 2.048 MS/s (M = 2^18, R = 32, G = 2, the I/Q
-    wipe-off of k_fwd_split), against the reference's pcorrelator on an ncoh-period replica."""
+def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype, pow2_env):
+    """The two-pass path at its other radices.  Power-of-two lengths (SDRB200_ACQ_POW2): 10 ms real
+    (M = 2^19, R = 128, G = 8), 40 ms real (M = 2^21, R = 256 x 8192, G = 16) and 40 ms I/Q at 2.048 MS/s
+    (M = 2^18, R = 64, G = 4, the I/Q wipe-off of k_fwd_split).  Default lengths: M = 5 * 2^16 = 80 x 4096
+    (G = 5), 5 * 2^18 = 160 x 8192 (G = 10) and, for the I/Q case, 2^18 again (5 * 2^15 has no radix).
+    Against the reference's pcorrelator on an ncoh-period replica."""
     fs, f_if, nsamp, scene = (util.FS1, util.IF1, 16368, util.scene_c1) if dtype == 1 else (util.FS5, 0.0, 2048, util.scene_c5)
     n = ncoh * nsamp
     cfg, vis = scene(sdr, nsats=2, seed=0xB2000046 + ncoh)
