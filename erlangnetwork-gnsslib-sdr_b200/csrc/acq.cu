@@ -801,8 +801,10 @@ k_rowc(const acq_rowc_args A)
     __shared__ acq_part_t s_part[32];
     __shared__ acq_part_t s_cta;
     constexpr int T = L / 16;
-    constexpr int NA = (R >= 2) ? R / 2 : 1;          /* lag blocks kept          */
-    constexpr int J = 16 / R;                         /* slice columns per thread */
+    constexpr int NA = (R >= 2) ? (R + 1) / 2 : 1;    /* lag blocks kept (lags < n <= M/2) */
+    constexpr int J = (16 + R - 1) / R;               /* slice columns per thread */
+    constexpr int CW = (L + R - 1) / R;               /* slice columns per CTA    */
+    constexpr bool EVEN = (16 % R) == 0;              /* R = 5, 10 (M = 5 * 2^k): the last round of columns is partial */
     constexpr int NOUT = (R == 1) ? 16 : NA * J;
     const int q = blockIdx.x, p = blockIdx.z, tid = threadIdx.x;
     const int lane = tid & 31, warp = tid >> 5;
@@ -821,7 +823,9 @@ k_rowc(const acq_rowc_args A)
     float pw[NOUT];
     auto tout = [&](int i) -> int {
         if (R == 1) return tid + i * T;
-        return q * (L / R) + tid + (i % J) * T + L * (i / J);
+        const int c = tid + (i % J) * T;
+        if (!EVEN && (c >= CW || q * CW + c >= L)) return 0x7fffffff;        /* no such column: never < n_eff */
+        return q * CW + c + L * (i / J);
     };
     bool from_hbm = (MODE == 1 && A.P != nullptr);
     if (from_hbm) {
@@ -856,14 +860,19 @@ k_rowc(const acq_rowc_args A)
             cl_arrive_relaxed();
             float2 wj[J];
 #pragma unroll
-            for (int j = 0; j < J; j++) wj[j] = __ldg(&A.tw[q * (L / R) + tid + j * T]);
+            for (int j = 0; j < J; j++) wj[j] = __ldg(&A.tw[q * CW + tid + j * T]);
             cl_wait();
             const float2 *zs[R];
 #pragma unroll
             for (int r = 0; r < R; r++) zs[r] = cluster.map_shared_rank(fsm, r);
 #pragma unroll
             for (int j = 0; j < J; j++) {
-                const int tp = q * (L / R) + tid + j * T;
+                const int tp = q * CW + tid + j * T;
+                if (!EVEN && (tid + j * T >= CW || tp >= L)) {
+#pragma unroll
+                    for (int a = 0; a < NA; a++) pw[a * J + j] = 0.f;
+                    continue;
+                }
                 float2 z[R];
 #pragma unroll
                 for (int r = 0; r < R; r++) z[r] = zs[r][tp];
@@ -880,6 +889,10 @@ k_rowc(const acq_rowc_args A)
                 } else if constexpr (R == 4) {
                     y[0] = cadd(cadd(z[0], z[2]), cadd(z[1], z[3]));
                     y[1] = cadd(csub(z[0], z[2]), crot<+1>(csub(z[1], z[3])));
+                } else if constexpr (R == 5 || R == 10) {
+                    fft_small<R, +1>(z);
+#pragma unroll
+                    for (int a = 0; a < NA; a++) y[a] = z[a];
                 } else if constexpr (R == 16) {
                     /* 16-point inverse transform; only y[0..7] are used (lags < n <= M/2) */
                     fft16<+1>(z);
@@ -1574,6 +1587,8 @@ static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t 
     case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale, f0, nfc);
     case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale, f0, nfc);
     case 16:  return launch_fwd_split_small_r<16>(st, a, win, scale, f0, nfc);
+    case 5:   return launch_fwd_split_small_r<5>(st, a, win, scale, f0, nfc);
+    case 10:  return launch_fwd_split_small_r<10>(st, a, win, scale, f0, nfc);
     case 32:  return launch_fwd_split_g<2>(st, a, win, scale, f0, nfc);   /* one thread per t with a 32-point register stage: 38 vs 34 us */
     case 64:  return launch_fwd_split_g<4>(st, a, win, scale, f0, nfc);
     case 128: return launch_fwd_split_g<8>(st, a, win, scale, f0, nfc);
@@ -1711,6 +1726,7 @@ static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_ro
     RC(1024, 4) RC(2048, 4) RC(4096, 4) RC(8192, 4) RC(16384, 4)
     RC(1024, 8) RC(2048, 8) RC(4096, 8) RC(8192, 8) RC(16384, 8)
     RC(4096, 16)
+    RC(4096, 5) RC(8192, 5) RC(4096, 10)                    /* M = 5 * 2^k */
 #undef RC
     sdrb200_set_error("acquisition: no fused kernel for L=%d R=%d", L, R);
     return SDRB200_EINVAL;
@@ -1756,6 +1772,9 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
         const char *e5 = getenv("SDRB200_LSUB");
         if (e5 && (atoi(e5) == 4096 || atoi(e5) == 8192 || atoi(e5) == 16384) && (M / atoi(e5) == 80 || M / atoi(e5) == 160)) l5 = atoi(e5);
         *L = l5; *R = M / l5; *fused = 0; *warp32 = 0;
+        if (M == 20480 || M == 40960) {
+            *L = (M == 40960 && getenv("SDRB200_ACQ_R5")) ? 8192 : 4096; *R = M / *L; *fused = 1;
+        }
         return;
     }
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
@@ -1798,13 +1817,15 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
      * two-pass path has the radix (80 or 160 sub-transforms of 4096 .. 16384 points).  Config 4: 2 n = 654 720 <=
      * 655 360 = 160 x 4096 instead of 2^20 - 37.5 % less arithmetic and traffic in every pass.
      * SDRB200_ACQ_POW2 keeps the power of two.                                                                    */
-    if (!getenv("SDRB200_ACQ_POW2") && !cfg->grid_per_prn) {
+    if (!getenv("SDRB200_ACQ_POW2")) {
         const int m5 = a->M / 8 * 5;
-        if (m5 >= a->m_ref && m5 >= 80 * 4096) {
+        if (m5 >= a->m_ref && m5 >= 80 * 4096 && !cfg->grid_per_prn) {
             int l5 = 4096;
             while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
             if (m5 / l5 == 80 || m5 / l5 == 160) a->M = m5;
         }
+        /* cluster kernel: 5 x 4096 (20 480) and 10 x 4096 (40 960: GLONASS at 20 MS/s, 2 n = 40 000) */
+        if (m5 >= a->m_ref && (m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) a->M = m5;
     }
     acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
@@ -1840,7 +1861,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
          * the walking forward kernel), SDRB200_FWD_WALK (walking forward kernel on the cluster path) */
         const int naive = getenv("SDRB200_ACQ_COMB_NAIVE") != NULL;
         a->comb_fft = (!a->fused && a->R > 1 && comb_fft_supported(a->R) && !naive) ? 1 : 0;
-        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8 || a->R == 16) &&
+        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8 || a->R == 16 || a->R == 5 || a->R == 10) &&
                                         !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }

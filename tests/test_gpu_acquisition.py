@@ -328,3 +328,46 @@ def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype, pow2_env):
     flat = int(np.argmax(ref))
     assert (g["freqi"], g["codei"]) == (flat // n, flat % n)
     assert g["freqi"] == 1
+
+
+@pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
+@pytest.mark.parametrize("fs,dtype", [(10.0e6, 1), (20.0e6, 2), (20.0e6, 1)])
+def test_acq_cluster_kernel_five_times_power_of_two(sdr, oracle, fs, dtype, pow2_env):
+    """Windows of 10 000 and 20 000 samples (1 ms at 10 and 20 MS/s): the cluster kernel runs them as
+    5 x 4096 = 20 480 and 10 x 4096 = 40 960 points (radix-5 / radix-10 recombination across the
+    cluster, the last round of slice columns partial) instead of 2^15 / 2^16; with SDRB200_ACQ_POW2
+    as 8 x 4096 / 16 x 4096.  Oracle: the reference's pcorrelator + argmax on the same window."""
+    nsamp = int(fs * 1e-3)
+    n = nsamp
+    f_if = 0.0 if dtype == 2 else fs / 4
+    sats = [dict(prn=7, cn0=47.0, doppler=1040.0, code_phase=400.3, carr_phase=0.2, rate=0.0, nav_on=0),
+            dict(prn=19, cn0=45.0, doppler=-2030.0, code_phase=77.7, carr_phase=1.1, rate=0.0, nav_on=0)]
+    cfg = sdr.make_ifgen(fs, f_if, util.CF, dtype, sats, sigma=24.0, seed=0xB2000050 + dtype)
+    avail = 2 * n + 4096
+    st = sdr.Stream(dtype, avail)
+    st.push_ifgen(cfg, avail)
+    host = st.read(0, avail)
+    b0 = avail - 2 * n
+    freq = np.array([f_if + (i - 5) * 500.0 for i in range(11)])
+    prns = [7, 19, 3]
+    codes = np.stack([sdr.gencode(p)[0] for p in prns])
+    acq = sdr.Acquisition(fs, dtype, nsamp, int(nsamp / 1023), 1e-3, freq, codes, 1.023e6, intg=1, keep_power=True)
+    got = acq.run(st, b0)
+    plain = sdr.Acquisition(fs, dtype, nsamp, int(nsamp / 1023), 1e-3, freq, codes, 1.023e6, intg=1)
+    assert plain.run(st, b0) == got                           # register-only search: same tuples
+    for i, p in enumerate(prns):
+        rep, _ = oracle.rescode(codes[i].astype(np.int16), 0.0, 0, 1.023e6 / fs, n)
+        x = np.zeros(2 * n, np.complex64)
+        x[:n] = rep
+        ref = oracle.pcorrelator(host[b0 * dtype:(b0 + 2 * n) * dtype], dtype, 1 / fs, n, freq, 1.023e6, 2 * n, oracle.cpxfft(x))
+        P = acq.power(i).ravel()
+        assert np.abs(P - ref).max() <= 2e-4 * ref.max(), p
+        flat = int(np.argmax(ref))
+        assert (got[i]["freqi"], got[i]["codei"]) == (flat // n, flat % n), (p, got[i])
+        row, c0, w = ref.reshape(len(freq), n)[flat // n], flat % n, 2 * int(nsamp / 1023)
+        keep = np.ones(n, bool)
+        keep[np.arange(c0 - w, c0 + w + 1) % n] = False                       # src/sdracq.c:81-82
+        peakr = row[c0] / max(row[keep].max(), row[0])
+        assert abs(got[i]["peakr"] - peakr) <= 1e-3 * peakr, (p, got[i])
+        assert got[i]["acquired"] == int(peakr > 3.0), (p, got[i])
+    assert got[0]["freqi"] == 7 and got[1]["freqi"] == 1 and got[0]["acquired"] == 1      # bins next to +1040 / -2030 Hz
