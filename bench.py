@@ -778,8 +778,8 @@ def run_b200(args):
         for sk in s5: sk.close()
     # ------------------------------------------------ BASELINE configs[2]: GLONASS G1 FDMA acquisition
     # 14 frequency channels (k = -7..6, 562.5 kHz apart) x 101 bins (+-10 kHz / 200 Hz) x 20000 code
-    # phases, I/Q int8 at 20 MS/s (stereo_L1G1 style), 10 non-coherent integrations (M = 65536 =
-    # 8 x 8192: the fused cluster path).  One plan per channel (its own Doppler grid, src/sdrinit.c:633-635),
+    # phases, I/Q int8 at 20 MS/s (stereo_L1G1 style), 10 non-coherent integrations (2 n = 40 000 <= M = 40 960 =
+    # 10 x 4096: the fused cluster path, radix-10 recombination).  One plan per channel (its own Doppler grid, src/sdrinit.c:633-635),
     # all enqueued before the first wait.  Parity: tests/test_gpu_headline.py::test_c3_*.
     c3_obj = None
     if args.c3:
@@ -846,14 +846,14 @@ def run_b200(args):
                   "peak_ratio_per_channel": {str(k_): round(g_["peakr"], 2) for k_, g_ in zip(ks3, g3)},
                   "channels_with_signal": [-7, -4, -1, 0, 2, 5, 6],
                   "hbm": {"model": "SURVEY 8(d): IF + code spectrum + power matrix read/write per step",
-                          "frac": world * len(ks3) * (intg3 * (2 * ns3 * 2 + 65536 * 8) + nf3 * ns3 * 4 * (2 * intg3 - 1)) / t3m / 1e9 / (hbm_peak * world)},
+                          "frac": world * len(ks3) * (intg3 * (2 * ns3 * 2 + 40960 * 8) + nf3 * ns3 * 4 * (2 * intg3 - 1)) / t3m / 1e9 / (hbm_peak * world)},
                   "timing": "host clock around enqueue .. sync, L2 flushed before"}
         one3.close()
         for pl in plans3: pl.close()
         st3.close()
     # ------------------------------------------------ config-4 style: long coherent blocks
     # BASELINE configs[3]: weak-signal search, 100 Hz Doppler step (141 bins), 20 ms coherent
-    # blocks (n = 327 360 lags, M = 2^20: the two-pass path k_fwd_split/k_fft_rows/k_row/
+    # blocks (n = 327 360 lags, M = 655 360 = 160 x 4096: the two-pass path k_fwd_split/k_fft_rows/k_row/
     # k_comb_fft through an L2-sized scratch), non-coherent accumulation in the power matrix.
     # A PRN slab of 16 (the 8-GPU share of 51 PRNs is 7) and 3 non-coherent steps; reported,
     # not the headline.
@@ -883,10 +883,10 @@ def run_b200(args):
                 dist.all_reduce(tt4, op=dist.ReduceOp.MAX)
                 ms4 = float(tt4[0])
             cells4 = world * args.c4_prns * nf4 * n4 * intg4
-            m4 = 1 << 20
+            m4 = 5 << 17                                     # transform length the plan chooses for 2 n = 654 720
             a_bytes4 = world * (intg4 * (2 * n4 + args.c4_prns * m4 * 8) + args.c4_prns * nf4 * n4 * 4 * (1 + 2 * (intg4 - 1)))
             c4_obj = {"workload": f"{args.c4_prns} PRN x {nf4} bins (100 Hz) x {n4} lags, {ncoh4} ms coherent blocks "
-                                  f"(M = 2^20), {intg4} non-coherent steps (BASELINE configs[3] style)",
+                                  f"(M = 655360), {intg4} non-coherent steps (BASELINE configs[3] style)",
                       "cells_per_s": cells4 / (ms4 * 1e-3), "ms_per_run": ms4, "ms_per_step": ms4 / intg4,
                       "algorithmic_bytes_per_run": a_bytes4,
                       "hbm": {"achieved_GBps": a_bytes4 / (ms4 * 1e-3) / 1e9, "peak_GBps": hbm_peak * world,
@@ -896,7 +896,7 @@ def run_b200(args):
             acq4.close()
     # ------------------------------------------------ the partition north_star names: ONE search over N GPUs
     # (a) strong scaling: BASELINE configs[3] at its full size - 51 PRN (GPS 1-32 + SBAS 120-138) x 141 bins
-    #     (100 Hz) x 327 360 lags (20 ms coherent, M = 2^20) x 10 non-coherent steps with the reference's
+    #     (100 Hz) x 327 360 lags (20 ms coherent, M = 655 360) x 10 non-coherent steps with the reference's
     #     early exit - split by PRN slab; every rank searches the SAME IF stream; the tuples are gathered
     #     ONCE per search from device memory (sdrb200_acq_results_device) with one NCCL all-gather.
     # (b) Doppler slabs for PRNs < GPUs: 4 PRN x 71 bins, 4 integrations, bins split over the ranks,
@@ -980,7 +980,7 @@ def run_b200(args):
             eq4 = True
         steps_run = max(m_["nintg"] for m_ in merged4)
         strong_obj = {"workload": f"ONE search, {len(prns4)} PRN (GPS 1-32 + SBAS 120-138) x {nf4} bins (100 Hz) x {n4} lags, "
-                                  f"{ncoh4} ms coherent (M = 2^20), up to {intg4} non-coherent steps with early exit (BASELINE configs[3])",
+                                  f"{ncoh4} ms coherent (M = 655360 = 160 x 4096), up to {intg4} non-coherent steps with early exit (BASELINE configs[3])",
                       "scaling": "strong", "partition": "PRN slabs, one NCCL all-gather of the tuples per search from device memory",
                       "kernel_share_this_rank": kern4,
                       "n_gpus": world, "prns_per_gpu": [len(sdr.shard.prn_slab(prns4, r_, world)) for r_ in range(world)],
