@@ -46,7 +46,7 @@ struct acq_rowstat_t {
 };
 
 #define ACQ_MAXEV 256
-#define ACQ_MAXLANES 4
+#define ACQ_MAXLANES 8
 struct sdrb200_acq {
     sdrb200_acq_cfg_t cfg;
     int n_eff, m_ref, M, L, R;
