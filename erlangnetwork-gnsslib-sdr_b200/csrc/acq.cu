@@ -1646,6 +1646,23 @@ template <int L, int R, int MODE> static int launch_rowc(cudaStream_t st, const 
     return SDRB200_OK;
 }
 
+/* clusters of more than 8 CTAs are a non-portable size: how many of them the device holds at once (0: none) */
+template <int L, int R> static int rowc_big_clusters(void)
+{
+    const size_t smem = sizeof(float2) * FFT_SMEM_ELEMS(L);
+    if (cudaFuncSetAttribute(k_rowc<L, R, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+        cudaFuncSetAttribute(k_rowc<L, R, 0>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { cudaGetLastError(); return 0; }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(R, 16, 1); cfg.blockDim = dim3(L / 16, 1, 1); cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = R; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, k_rowc<L, R, 0>, &cfg) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
 template <int MODE> static int roww_config(cudaLaunchConfig_t *cfg, cudaLaunchAttribute *at, cudaStream_t st, int ncl)
 {
     const size_t smem = 2 * 4 * sizeof(float2) * WFFT_TILE;
@@ -1828,6 +1845,9 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
         if (m5 >= a->m_ref && (m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) a->M = m5;
     }
     acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
+    /* a device (or partition) that cannot hold a cluster of 10 / 16 CTAs gets the portable split of the same length */
+    if (a->fused && a->R == 10 && a->L == 4096 && rowc_big_clusters<4096, 10>() < 1) { a->L = 8192; a->R = 5; }
+    if (a->fused && a->R == 16 && a->L == 4096 && rowc_big_clusters<4096, 16>() < 1) { a->L = 8192; a->R = 8; }
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     /* one wipe-off grid per replica (GLONASS FDMA: every channel has its own carrier, src/sdrinit.c:633-635):
      * the rows of replica p read the spectra of bins p * nfreq .. ; fused cluster kernel only */
