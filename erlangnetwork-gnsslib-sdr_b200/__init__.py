@@ -104,5 +104,14 @@ def loop_coeffs(dllb: float, pllb: float, fllb: float) -> Loop:
                 fllw=fllb / 0.25)
 
 
+def plan_shape(nsamp: int, ncoh: int = 1, grid_per_prn: bool = False) -> dict:
+    """Transform length and decomposition an acquisition plan will use for windows of nsamp*ncoh lags
+    (sdrb200_acq_plan_shape, host logic only): M = R sub-transforms of L points, fused = cluster kernel."""
+    M, L, R, fused = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    check(lib.sdrb200_acq_plan_shape(int(nsamp), int(ncoh), int(bool(grid_per_prn)), C.byref(M), C.byref(L), C.byref(R),
+                                     C.byref(fused)), "acq_plan_shape")
+    return {"M": M.value, "L": L.value, "R": R.value, "fused": bool(fused.value)}
+
+
 from .host import *  # noqa: E402,F401,F403  (convenience wrappers)
 from . import shard  # noqa: E402,F401

@@ -1814,6 +1814,40 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
     }
 }
 
+/* transform length for a window of m_ref = 2 n samples.  The correlation is linear for lags < n whenever the
+ * transform holds the window, so the length need not be a power of two: M = 5 * 2^k (0.625 of the next power of two)
+ * when the window fits it and there are kernels for it - 80 or 160 sub-transforms of 4096 .. 16384 points on the
+ * two-pass path (config 4: 2 n = 654 720 <= 655 360 = 160 x 4096 instead of 2^20, 37.5 % less arithmetic and traffic
+ * in every pass), 5 x 4096 and 10 x 4096 on the cluster path (GLONASS at 20 MS/s: 2 n = 40 000 <= 40 960).
+ * SDRB200_ACQ_POW2 keeps the power of two.                                                                        */
+static int acq_choose_len(int m_ref, int grid_per_prn)
+{
+    int M = 512;
+    while (M < m_ref) M <<= 1;
+    if (getenv("SDRB200_ACQ_POW2")) return M;
+    const int m5 = M / 8 * 5;
+    if (m5 < m_ref) return M;
+    if (m5 >= 80 * 4096 && !grid_per_prn) {
+        int l5 = 4096;
+        while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
+        if (m5 / l5 == 80 || m5 / l5 == 160) return m5;
+    }
+    if ((m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) return m5;
+    return M;
+}
+
+/* the decomposition a plan for nsamp x ncoh samples per window will use, without creating one (no device needed;
+ * on a device that cannot hold clusters of 10 / 16 CTAs the plan itself takes 5 x 8192 / 8 x 8192 instead) */
+extern "C" int sdrb200_acq_plan_shape(int nsamp, int ncoh, int grid_per_prn, int *M, int *L, int *R, int *fused)
+{
+    if (nsamp < 64 || !M || !L || !R || !fused) { sdrb200_set_error("acq_plan_shape: bad argument"); return SDRB200_EINVAL; }
+    if (ncoh < 1) ncoh = 1;
+    int w32 = 0;
+    *M = acq_choose_len(2 * nsamp * ncoh, grid_per_prn);
+    acq_choose(*M, 0, L, R, fused, &w32);
+    return SDRB200_OK;
+}
+
 extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *cfg)
 {
     if (!out || !cfg || !cfg->freq || !cfg->codes || cfg->nsamp < 64 || cfg->nfreq < 1 || cfg->nprn < 1 ||
@@ -1828,22 +1862,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     if (a->cfg.threshold <= 0) a->cfg.threshold = 3.0;           /* ACQTH */
     a->n_eff = cfg->nsamp * a->cfg.ncoh;
     a->m_ref = 2 * a->n_eff;                                      /* acq.nfft = 2*nsamp, sdrinit.c:625 */
-    a->M = 512; while (a->M < a->m_ref) a->M <<= 1;
-    /* the correlation is linear for lags < n whenever the transform holds the 2 n samples of the window, so the
-     * length need not be a power of two: M = 5 * 2^k (0.625 of the next power of two) when the window fits it and the
-     * two-pass path has the radix (80 or 160 sub-transforms of 4096 .. 16384 points).  Config 4: 2 n = 654 720 <=
-     * 655 360 = 160 x 4096 instead of 2^20 - 37.5 % less arithmetic and traffic in every pass.
-     * SDRB200_ACQ_POW2 keeps the power of two.                                                                    */
-    if (!getenv("SDRB200_ACQ_POW2")) {
-        const int m5 = a->M / 8 * 5;
-        if (m5 >= a->m_ref && m5 >= 80 * 4096 && !cfg->grid_per_prn) {
-            int l5 = 4096;
-            while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
-            if (m5 / l5 == 80 || m5 / l5 == 160) a->M = m5;
-        }
-        /* cluster kernel: 5 x 4096 (20 480) and 10 x 4096 (40 960: GLONASS at 20 MS/s, 2 n = 40 000) */
-        if (m5 >= a->m_ref && (m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) a->M = m5;
-    }
+    a->M = acq_choose_len(a->m_ref, cfg->grid_per_prn);
     acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
     /* a device (or partition) that cannot hold a cluster of 10 / 16 CTAs gets the portable split of the same length */
     if (a->fused && a->R == 10 && a->L == 4096 && rowc_big_clusters<4096, 10>() < 1) { a->L = 8192; a->R = 5; }
@@ -1853,7 +1872,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
      * the rows of replica p read the spectra of bins p * nfreq .. ; fused cluster kernel only */
     a->nfx = cfg->grid_per_prn ? nprn * nfreq : nfreq;
     if (cfg->grid_per_prn && !a->fused) {
-        sdrb200_set_error("acq_create: grid_per_prn needs the fused path (window of at most 8 sub-transforms)");
+        sdrb200_set_error("acq_create: grid_per_prn needs the cluster kernel (window of at most 16 sub-transforms)");
         free(a); return SDRB200_EINVAL;
     }
     if (a->R > 256) { sdrb200_set_error("acq_create: window too long"); free(a); return SDRB200_EINVAL; }

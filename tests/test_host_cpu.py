@@ -37,6 +37,32 @@ def test_no_cpu_fallback(sdr):
         sdr.Acquisition(2.048e6, 2, 2048, 2, 1e-3, np.zeros(3), np.ones((1, 1023), np.int8), 1.023e6)
 
 
+def test_plan_shapes_of_the_baseline_configs(sdr, monkeypatch):
+    """The transform a plan builds holds the 2n samples the reference transforms (acq.nfft = 2*nsamp,
+    src/sdrinit.c:625) and is the smallest of 2^k and 5*2^(k-3) with kernels; host logic, no device."""
+    for v in ("SDRB200_ACQ_POW2", "SDRB200_LSUB", "SDRB200_ACQ_SCRATCH", "SDRB200_ACQ_R5", "SDRB200_ACQ_R8", "SDRB200_ACQ_WARP"):
+        monkeypatch.delenv(v, raising=False)
+    want = {
+        (16368, 1, False): (32768, 4096, 8, True),       # C1: 2n = 32 736
+        (2048, 1, False): (4096, 4096, 1, True),         # C5
+        (20000, 1, True): (40960, 4096, 10, True),       # C3: 2n = 40 000, one grid per channel
+        (10000, 1, False): (20480, 4096, 5, True),
+        (16368, 20, False): (655360, 4096, 160, False),  # C4: 2n = 654 720
+        (16368, 10, False): (327680, 4096, 80, False),
+        (16368, 40, False): (1310720, 8192, 160, False),
+        (2048, 40, False): (262144, 4096, 64, False),    # 5 * 2^15 has no radix: power of two
+        (26000, 1, False): (65536, 4096, 16, True),      # 2n = 52 000 > 40 960
+    }
+    for (nsamp, ncoh, gpp), (M, L, R, fused) in want.items():
+        got = sdr.plan_shape(nsamp, ncoh, gpp)
+        assert (got["M"], got["L"], got["R"], got["fused"]) == (M, L, R, fused), ((nsamp, ncoh), got)
+        assert got["M"] >= 2 * nsamp * ncoh and got["M"] == got["L"] * got["R"]
+    monkeypatch.setenv("SDRB200_ACQ_POW2", "1")
+    assert sdr.plan_shape(16368, 20)["M"] == 1 << 20 and sdr.plan_shape(20000, 1, True)["M"] == 65536
+    with pytest.raises(sdr.Error):
+        sdr.plan_shape(8)
+
+
 def test_product_codes_match_oracle(sdr):
     """codegen.c (LFSR form) vs the oracle's +-1 register form, all 210 PRNs + G1"""
     o = ob.best()
