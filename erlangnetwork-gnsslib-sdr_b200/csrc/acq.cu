@@ -1743,7 +1743,7 @@ static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_ro
     RC(1024, 4) RC(2048, 4) RC(4096, 4) RC(8192, 4) RC(16384, 4)
     RC(1024, 8) RC(2048, 8) RC(4096, 8) RC(8192, 8) RC(16384, 8)
     RC(4096, 16)
-    RC(4096, 5) RC(8192, 5) RC(4096, 10)                    /* M = 5 * 2^k */
+    RC(1024, 5) RC(2048, 5) RC(4096, 5) RC(8192, 5) RC(4096, 10)        /* M = 5 * 2^k */
 #undef RC
     sdrb200_set_error("acquisition: no fused kernel for L=%d R=%d", L, R);
     return SDRB200_EINVAL;
@@ -1789,8 +1789,8 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
         const char *e5 = getenv("SDRB200_LSUB");
         if (e5 && (atoi(e5) == 4096 || atoi(e5) == 8192 || atoi(e5) == 16384) && (M / atoi(e5) == 80 || M / atoi(e5) == 160)) l5 = atoi(e5);
         *L = l5; *R = M / l5; *fused = 0; *warp32 = 0;
-        if (M == 20480 || M == 40960) {
-            *L = (M == 40960 && getenv("SDRB200_ACQ_R5")) ? 8192 : 4096; *R = M / *L; *fused = 1;
+        if (M == 5120 || M == 10240 || M == 20480 || M == 40960) {
+            *L = (M == 40960) ? (getenv("SDRB200_ACQ_R5") ? 8192 : 4096) : M / 5; *R = M / *L; *fused = 1;
         }
         return;
     }
@@ -1818,7 +1818,7 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
  * transform holds the window, so the length need not be a power of two: M = 5 * 2^k (0.625 of the next power of two)
  * when the window fits it and there are kernels for it - 80 or 160 sub-transforms of 4096 .. 16384 points on the
  * two-pass path (config 4: 2 n = 654 720 <= 655 360 = 160 x 4096 instead of 2^20, 37.5 % less arithmetic and traffic
- * in every pass), 5 x 4096 and 10 x 4096 on the cluster path (GLONASS at 20 MS/s: 2 n = 40 000 <= 40 960).
+ * in every pass), 5 x 1024 .. 5 x 4096 and 10 x 4096 on the cluster path (GLONASS at 20 MS/s: 2 n = 40 000 <= 40 960).
  * SDRB200_ACQ_POW2 keeps the power of two.                                                                        */
 static int acq_choose_len(int m_ref, int grid_per_prn)
 {
@@ -1832,7 +1832,7 @@ static int acq_choose_len(int m_ref, int grid_per_prn)
         while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
         if (m5 / l5 == 80 || m5 / l5 == 160) return m5;
     }
-    if ((m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) return m5;
+    if ((m5 == 5120 || m5 == 10240 || m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) return m5;
     return M;
 }
 

@@ -331,10 +331,10 @@ def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype, pow2_env):
 
 
 @pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
-@pytest.mark.parametrize("fs,dtype", [(10.0e6, 1), (20.0e6, 2), (20.0e6, 1)])
+@pytest.mark.parametrize("fs,dtype", [(10.0e6, 1), (20.0e6, 2), (20.0e6, 1), (5.0e6, 2), (2.5e6, 2)])
 def test_acq_cluster_kernel_five_times_power_of_two(sdr, oracle, fs, dtype, pow2_env):
-    """Windows of 10 000 and 20 000 samples (1 ms at 10 and 20 MS/s): the cluster kernel runs them as
-    5 x 4096 = 20 480 and 10 x 4096 = 40 960 points (radix-5 / radix-10 recombination across the
+    """Windows of 2 500 .. 20 000 samples (1 ms at 2.5 .. 20 MS/s): the cluster kernel runs them as
+    5 x 1024, 5 x 2048, 5 x 4096 = 20 480 and 10 x 4096 = 40 960 points (radix-5 / radix-10 recombination across the
     cluster, the last round of slice columns partial) instead of 2^15 / 2^16; with SDRB200_ACQ_POW2
     as 8 x 4096 / 16 x 4096.  Oracle: the reference's pcorrelator + argmax on the same window."""
     nsamp = int(fs * 1e-3)

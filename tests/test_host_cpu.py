@@ -47,6 +47,8 @@ def test_plan_shapes_of_the_baseline_configs(sdr, monkeypatch):
         (2048, 1, False): (4096, 4096, 1, True),         # C5
         (20000, 1, True): (40960, 4096, 10, True),       # C3: 2n = 40 000, one grid per channel
         (10000, 1, False): (20480, 4096, 5, True),
+        (5000, 1, False): (10240, 2048, 5, True),
+        (2500, 1, False): (5120, 1024, 5, True),
         (16368, 20, False): (655360, 4096, 160, False),  # C4: 2n = 654 720
         (16368, 10, False): (327680, 4096, 80, False),
         (16368, 40, False): (1310720, 8192, 160, False),
