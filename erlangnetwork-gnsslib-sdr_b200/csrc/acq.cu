@@ -653,8 +653,10 @@ k_comb_fft(const float2 *__restrict__ S, const float2 *__restrict__ tw, int L, i
 #pragma unroll
         for (int gg = 0; gg < G; gg++) z[gg] = xsm[(a2 * G + gg) * 32 + lane];
         fft_small<G, +1>(z);
+        /* lags < n <= M/2 = 8 G L: only a = a2 + 16 a1 < 8 G can be one, i.e. a1 < G/2 - the other half of the
+         * G-point stage is never formed (the compiler drops its butterflies with the loop)                    */
 #pragma unroll
-        for (int a1 = 0; a1 < G; a1++) {
+        for (int a1 = 0; a1 < (G + 1) / 2; a1++) {
             const int t = tp + L * (a2 + 16 * a1);
             if (t < n_eff) {
                 float pw = (z[a1].x * z[a1].x + z[a1].y * z[a1].y) * invM2;
