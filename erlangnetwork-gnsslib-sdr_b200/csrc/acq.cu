@@ -419,10 +419,48 @@ template <int SIGN> __device__ __forceinline__ void fft5(float2 &x0, float2 &x1,
     x2 = cadd(e2, o2); x3 = csub(e2, o2);
 }
 
+/* 3-point DFT, z[a] = sum_g z[g] exp(SIGN 2 pi i a g / 3) */
+template <int SIGN> __device__ __forceinline__ void fft3(float2 &x0, float2 &x1, float2 &x2)
+{
+    constexpr float S = SIGN * 0.86602540378443865f;                            /* sin(2 pi / 3) */
+    const float2 a = cadd(x1, x2), b = csub(x1, x2);
+    const float2 e = make_float2(fmaf(-0.5f, a.x, x0.x), fmaf(-0.5f, a.y, x0.y));
+    const float2 o = make_float2(-S * b.y, S * b.x);                            /* i S b */
+    x0 = cadd(x0, a); x1 = cadd(e, o); x2 = csub(e, o);
+}
+
 /* G-point DFT in registers, natural order: z[a] = sum_g z[g] exp(SIGN 2 pi i a g / G) */
 template <int G, int SIGN> __device__ __forceinline__ void fft_small(float2 (&z)[G])
 {
-    if constexpr (G == 5) {
+    if constexpr (G == 3) {
+        fft3<SIGN>(z[0], z[1], z[2]);
+    } else if constexpr (G == 6) {
+        /* g = 2 g1 + g2, a = a1 + 3 a2: two 3-point transforms, W_6^(a1), one radix-2 stage */
+        float2 e0 = z[0], e1 = z[2], e2 = z[4], o0 = z[1], o1 = z[3], o2 = z[5];
+        fft3<SIGN>(e0, e1, e2);
+        fft3<SIGN>(o0, o1, o2);
+        o1 = cmul(o1, make_float2(0.5f, SIGN * 0.86602540378443865f));
+        o2 = cmul(o2, make_float2(-0.5f, SIGN * 0.86602540378443865f));
+        z[0] = cadd(e0, o0); z[1] = cadd(e1, o1); z[2] = cadd(e2, o2);
+        z[3] = csub(e0, o0); z[4] = csub(e1, o1); z[5] = csub(e2, o2);
+    } else if constexpr (G == 12) {
+        /* g = 4 g1 + g2, a = a1 + 3 a2: four 3-point transforms over g1, W_12^(g2 a1), three 4-point transforms over g2 */
+        constexpr float H = 0.86602540378443865f;
+        float2 f[4][3];
+#pragma unroll
+        for (int g2 = 0; g2 < 4; g2++) { f[g2][0] = z[g2]; f[g2][1] = z[4 + g2]; f[g2][2] = z[8 + g2]; fft3<SIGN>(f[g2][0], f[g2][1], f[g2][2]); }
+        f[1][1] = cmul(f[1][1], make_float2(H, SIGN * 0.5f));                   /* W_12^1 */
+        f[1][2] = cmul(f[1][2], make_float2(0.5f, SIGN * H));                   /* W_12^2 */
+        f[2][1] = cmul(f[2][1], make_float2(0.5f, SIGN * H));                   /* W_12^2 */
+        f[2][2] = cmul(f[2][2], make_float2(-0.5f, SIGN * H));                  /* W_12^4 */
+        f[3][1] = make_float2(-SIGN * f[3][1].y, SIGN * f[3][1].x);             /* W_12^3 = SIGN i */
+        f[3][2] = make_float2(-f[3][2].x, -f[3][2].y);                          /* W_12^6 = -1 */
+#pragma unroll
+        for (int a1 = 0; a1 < 3; a1++) {
+            fft4<SIGN>(f[0][a1], f[1][a1], f[2][a1], f[3][a1]);
+            z[a1] = f[0][a1]; z[a1 + 3] = f[1][a1]; z[a1 + 6] = f[2][a1]; z[a1 + 9] = f[3][a1];
+        }
+    } else if constexpr (G == 5) {
         fft5<SIGN>(z[0], z[1], z[2], z[3], z[4]);
     } else if constexpr (G == 10) {
         /* g = 2 g1 + g2, a = a1 + 5 a2: two 5-point transforms, W_10^(a1), one radix-2 stage */
@@ -891,7 +929,7 @@ k_rowc(const acq_rowc_args A)
                 } else if constexpr (R == 4) {
                     y[0] = cadd(cadd(z[0], z[2]), cadd(z[1], z[3]));
                     y[1] = cadd(csub(z[0], z[2]), crot<+1>(csub(z[1], z[3])));
-                } else if constexpr (R == 5 || R == 10) {
+                } else if constexpr (R == 3 || R == 5 || R == 6 || R == 10 || R == 12) {
                     fft_small<R, +1>(z);
 #pragma unroll
                     for (int a = 0; a < NA; a++) y[a] = z[a];
@@ -1589,12 +1627,18 @@ static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t 
     case 4:   return launch_fwd_split_small_r<4>(st, a, win, scale, f0, nfc);
     case 8:   return launch_fwd_split_small_r<8>(st, a, win, scale, f0, nfc);
     case 16:  return launch_fwd_split_small_r<16>(st, a, win, scale, f0, nfc);
+    case 3:   return launch_fwd_split_small_r<3>(st, a, win, scale, f0, nfc);
+    case 6:   return launch_fwd_split_small_r<6>(st, a, win, scale, f0, nfc);
+    case 12:  return launch_fwd_split_small_r<12>(st, a, win, scale, f0, nfc);
     case 5:   return launch_fwd_split_small_r<5>(st, a, win, scale, f0, nfc);
     case 10:  return launch_fwd_split_small_r<10>(st, a, win, scale, f0, nfc);
     case 32:  return launch_fwd_split_g<2>(st, a, win, scale, f0, nfc);   /* one thread per t with a 32-point register stage: 38 vs 34 us */
     case 64:  return launch_fwd_split_g<4>(st, a, win, scale, f0, nfc);
     case 128: return launch_fwd_split_g<8>(st, a, win, scale, f0, nfc);
     case 256: return launch_fwd_split_g<16>(st, a, win, scale, f0, nfc);
+    case 48:  return launch_fwd_split_g<3>(st, a, win, scale, f0, nfc);   /* M = 3 * 2^k */
+    case 96:  return launch_fwd_split_g<6>(st, a, win, scale, f0, nfc);
+    case 192: return launch_fwd_split_g<12>(st, a, win, scale, f0, nfc);
     case 80:  return launch_fwd_split_g<5>(st, a, win, scale, f0, nfc);   /* M = 5 * 2^k */
     case 160: return launch_fwd_split_g<10>(st, a, win, scale, f0, nfc);
     }
@@ -1602,7 +1646,7 @@ static int launch_fwd_split(cudaStream_t st, const sdrb200_acq *a, const int8_t 
 }
 
 /* radix-R recombination (R = 16 G, G = 2, 4, 8, 16 and 5, 10); 0 if R has no such kernel */
-static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256 || R == 80 || R == 160; }
+static int comb_fft_supported(int R) { return R == 32 || R == 64 || R == 128 || R == 256 || R == 80 || R == 160 || R == 48 || R == 96 || R == 192; }
 template <int G> static int launch_comb_fft_g(cudaStream_t st, const sdrb200_acq *a, const float2 *S, int prn0, int nprn, int f0, int nfc,
                                               int first_step)
 {
@@ -1623,6 +1667,9 @@ static int launch_comb_fft(cudaStream_t st, const sdrb200_acq *a, const float2 *
     case 64:  return launch_comb_fft_g<4>(st, a, S, prn0, nprn, f0, nfc, first_step);
     case 128: return launch_comb_fft_g<8>(st, a, S, prn0, nprn, f0, nfc, first_step);
     case 256: return launch_comb_fft_g<16>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 48:  return launch_comb_fft_g<3>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 96:  return launch_comb_fft_g<6>(st, a, S, prn0, nprn, f0, nfc, first_step);
+    case 192: return launch_comb_fft_g<12>(st, a, S, prn0, nprn, f0, nfc, first_step);
     case 80:  return launch_comb_fft_g<5>(st, a, S, prn0, nprn, f0, nfc, first_step);
     case 160: return launch_comb_fft_g<10>(st, a, S, prn0, nprn, f0, nfc, first_step);
     }
@@ -1746,6 +1793,7 @@ static int launch_rowc_any(int L, int R, int mode, cudaStream_t st, const acq_ro
     RC(1024, 8) RC(2048, 8) RC(4096, 8) RC(8192, 8) RC(16384, 8)
     RC(4096, 16)
     RC(1024, 5) RC(2048, 5) RC(4096, 5) RC(8192, 5) RC(4096, 10)        /* M = 5 * 2^k */
+    RC(1024, 3) RC(2048, 3) RC(4096, 3) RC(4096, 6) RC(8192, 6) RC(4096, 12)  /* M = 3 * 2^k */
 #undef RC
     sdrb200_set_error("acquisition: no fused kernel for L=%d R=%d", L, R);
     return SDRB200_EINVAL;
@@ -1783,17 +1831,12 @@ extern "C" void *sdrb200_acq_cuda_stream(sdrb200_acq_t *a) { return a ? (void *)
 /* M = R * L.  Up to R = 8 the R sub-transforms of a row are finished inside one
  * thread-block cluster (k_rowc); longer windows (20 ms coherent blocks) use the
  * scratch path k_row + k_comb.  SDRB200_LSUB overrides L for experiments.       */
+static int acq_odd_shape(int m, int odd, int grid_per_prn, int *L, int *R, int *fused);
 static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *warp32)
 {
-    if (M % 5 == 0) {                                    /* 5 * 2^k: two-pass path only, see sdrb200_acq_create */
-        int l5 = 4096;
-        while (l5 < 16384 && M / l5 > 160) l5 <<= 1;
-        const char *e5 = getenv("SDRB200_LSUB");
-        if (e5 && (atoi(e5) == 4096 || atoi(e5) == 8192 || atoi(e5) == 16384) && (M / atoi(e5) == 80 || M / atoi(e5) == 160)) l5 = atoi(e5);
-        *L = l5; *R = M / l5; *fused = 0; *warp32 = 0;
-        if (M == 5120 || M == 10240 || M == 20480 || M == 40960) {
-            *L = (M == 40960) ? (getenv("SDRB200_ACQ_R5") ? 8192 : 4096) : M / 5; *R = M / *L; *fused = 1;
-        }
+    if (M % 5 == 0 || M % 3 == 0) {                      /* 5 * 2^k or 3 * 2^k, see acq_choose_len */
+        *warp32 = 0;
+        if (!acq_odd_shape(M, (M % 5 == 0) ? 5 : 3, 0, L, R, fused)) { *L = 4096; *R = M / 4096; *fused = 0; }
         return;
     }
     int lsub = (M <= 4096) ? M : (M / 8 > 4096 ? M / 8 : 4096);
@@ -1817,24 +1860,47 @@ static void acq_choose(int M, int allow_warp, int *L, int *R, int *fused, int *w
 }
 
 /* transform length for a window of m_ref = 2 n samples.  The correlation is linear for lags < n whenever the
- * transform holds the window, so the length need not be a power of two: M = 5 * 2^k (0.625 of the next power of two)
- * when the window fits it and there are kernels for it - 80 or 160 sub-transforms of 4096 .. 16384 points on the
+ * transform holds the window, so the length need not be a power of two: M = 5 * 2^k or 3 * 2^k (0.625 / 0.75 of the
+ * next power of two) when the window fits it and there are kernels for it - 80 or 160 sub-transforms of 4096 .. 16384 points on the
  * two-pass path (config 4: 2 n = 654 720 <= 655 360 = 160 x 4096 instead of 2^20, 37.5 % less arithmetic and traffic
  * in every pass), 5 x 1024 .. 5 x 4096 and 10 x 4096 on the cluster path (GLONASS at 20 MS/s: 2 n = 40 000 <= 40 960).
  * SDRB200_ACQ_POW2 keeps the power of two.                                                                        */
+/* 1 when length m = odd * 2^k (odd = 3 or 5) has kernels: *L, *R, *fused as acq_choose returns them */
+static int acq_odd_shape(int m, int odd, int grid_per_prn, int *L, int *R, int *fused)
+{
+    if (m % odd) return 0;
+    const int base = m / odd;                            /* a power of two */
+    if (!getenv("SDRB200_ACQ_SCRATCH")) {
+        /* cluster kernel: odd x 1024 .. odd x 4096, then 2 odd x 4096 and (factor 3) 12 x 4096 */
+        if (base == 1024 || base == 2048 || base == 4096) { *L = base; *R = odd; *fused = 1; return 1; }
+        if (base == 8192) {
+            *L = 4096; *R = 2 * odd; *fused = 1;
+            if ((odd == 5 && getenv("SDRB200_ACQ_R5")) ) { *L = 8192; *R = 5; }
+            return 1;
+        }
+        if (base == 16384 && odd == 3) { *L = 4096; *R = 12; *fused = 1; return 1; }
+    }
+    if (grid_per_prn) return 0;
+    /* two-pass path: 16 x odd or 32 x odd sub-transforms (and 64 x 3) of 4096 .. 16384 points */
+    const int rmax = (odd == 3) ? 192 : 160;
+    int l = 4096;
+    const char *e = getenv("SDRB200_LSUB");
+    if (e && (atoi(e) == 4096 || atoi(e) == 8192 || atoi(e) == 16384)) l = atoi(e);
+    else while (l < 16384 && m / l > rmax) l <<= 1;
+    const int r = m / l;
+    if (m % l == 0 && (r == 16 * odd || r == 32 * odd || (odd == 3 && r == 64 * odd))) { *L = l; *R = r; *fused = 0; return 1; }
+    return 0;
+}
+
 static int acq_choose_len(int m_ref, int grid_per_prn)
 {
     int M = 512;
     while (M < m_ref) M <<= 1;
     if (getenv("SDRB200_ACQ_POW2")) return M;
-    const int m5 = M / 8 * 5;
-    if (m5 < m_ref) return M;
-    if (m5 >= 80 * 4096 && !grid_per_prn) {
-        int l5 = 4096;
-        while (l5 < 16384 && m5 / l5 > 160) l5 <<= 1;
-        if (m5 / l5 == 80 || m5 / l5 == 160) return m5;
-    }
-    if ((m5 == 5120 || m5 == 10240 || m5 == 20480 || m5 == 40960) && !getenv("SDRB200_ACQ_SCRATCH")) return m5;
+    int l, r, f;
+    const int m5 = M / 8 * 5, m3 = M / 4 * 3;
+    if (m5 >= m_ref && acq_odd_shape(m5, 5, grid_per_prn, &l, &r, &f)) return m5;
+    if (m3 >= m_ref && acq_odd_shape(m3, 3, grid_per_prn, &l, &r, &f)) return m3;
     return M;
 }
 
@@ -1868,6 +1934,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
     acq_choose(a->M, !cfg->grid_per_prn, &a->L, &a->R, &a->fused, &a->warp32);   /* the warp kernels share one grid */
     /* a device (or partition) that cannot hold a cluster of 10 / 16 CTAs gets the portable split of the same length */
     if (a->fused && a->R == 10 && a->L == 4096 && rowc_big_clusters<4096, 10>() < 1) { a->L = 8192; a->R = 5; }
+    if (a->fused && a->R == 12 && a->L == 4096 && rowc_big_clusters<4096, 12>() < 1) { a->L = 8192; a->R = 6; }
     if (a->fused && a->R == 16 && a->L == 4096 && rowc_big_clusters<4096, 16>() < 1) { a->L = 8192; a->R = 8; }
     const int nfreq = cfg->nfreq, nprn = cfg->nprn, M = a->M, n_eff = a->n_eff;
     /* one wipe-off grid per replica (GLONASS FDMA: every channel has its own carrier, src/sdrinit.c:633-635):
@@ -1902,7 +1969,7 @@ extern "C" int sdrb200_acq_create(sdrb200_acq_t **out, const sdrb200_acq_cfg_t *
          * the walking forward kernel), SDRB200_FWD_WALK (walking forward kernel on the cluster path) */
         const int naive = getenv("SDRB200_ACQ_COMB_NAIVE") != NULL;
         a->comb_fft = (!a->fused && a->R > 1 && comb_fft_supported(a->R) && !naive) ? 1 : 0;
-        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8 || a->R == 16 || a->R == 5 || a->R == 10) &&
+        a->split_fwd = (a->comb_fft || a->warp32 || (a->fused && (a->R == 2 || a->R == 4 || a->R == 8 || a->R == 16 || a->R == 5 || a->R == 10 || a->R == 3 || a->R == 6 || a->R == 12) &&
                                         !getenv("SDRB200_FWD_WALK") && !naive)) ? 1 : 0;
         const char *env = getenv("SDRB200_FCHUNK");
         if (env && atoi(env) >= 1 && atoi(env) <= nfreq) { a->fchunk = atoi(env); a->chunk = 1; }

@@ -135,7 +135,7 @@ typedef struct {
 typedef struct sdrb200_acq sdrb200_acq_t;
 int  sdrb200_acq_create(sdrb200_acq_t **plan, const sdrb200_acq_cfg_t *cfg);
 /* Decomposition a plan for windows of nsamp*ncoh lags will use: transform length M = R sub-transforms of L points
- * (M is the smallest of 2^k and 5*2^(k-3) that holds the 2*nsamp*ncoh samples the reference transforms,
+ * (M is the smallest of 5*2^(k-3), 3*2^(k-2) and 2^k that holds the 2*nsamp*ncoh samples the reference transforms,
  * src/sdrinit.c:625, and has kernels), fused = 1 for the cluster kernel, 0 for the two-pass path.  Pure host
  * logic, no device needed.                                                                              */
 int  sdrb200_acq_plan_shape(int nsamp, int ncoh, int grid_per_prn, int *M, int *L, int *R, int *fused);

@@ -296,12 +296,13 @@ def test_acq_weak_signal_full_size_coherent(sdr, oracle, pow2_env):
 
 
 @pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
-@pytest.mark.parametrize("ncoh,dtype", [(10, 1), (40, 1), (40, 2)])
+@pytest.mark.parametrize("ncoh,dtype", [(10, 1), (40, 1), (40, 2), (6, 1), (12, 1), (24, 1)])
 def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype, pow2_env):
     """The two-pass path at its other radices.  Power-of-two lengths (SDRB200_ACQ_POW2): 10 ms real
     (M = 2^19, R = 128, G = 8), 40 ms real (M = 2^21, R = 256 x 8192, G = 16) and 40 ms I/Q at 2.048 MS/s
     (M = 2^18, R = 64, G = 4, the I/Q wipe-off of k_fwd_split).  Default lengths: M = 5 * 2^16 = 80 x 4096
-    (G = 5), 5 * 2^18 = 160 x 8192 (G = 10) and, for the I/Q case, 2^18 again (5 * 2^15 has no radix).
+    (G = 5), 5 * 2^18 = 160 x 8192 (G = 10) and, for the I/Q case, 3 * 2^16 = 48 x 4096 (G = 3; 5 * 2^15 has no radix);
+    ncoh = 6, 12, 24: M = 3 * 2^16, 2^17, 2^18 = 48, 96, 192 x 4096 (G = 3, 6, 12; 2^18 .. 2^20 with POW2).
     Against the reference's pcorrelator on an ncoh-period replica."""
     fs, f_if, nsamp, scene = (util.FS1, util.IF1, 16368, util.scene_c1) if dtype == 1 else (util.FS5, 0.0, 2048, util.scene_c5)
     n = ncoh * nsamp
@@ -331,10 +332,11 @@ def test_acq_two_pass_path_all_radices(sdr, oracle, ncoh, dtype, pow2_env):
 
 
 @pytest.mark.parametrize("pow2_env", [0, 1], indirect=True)
-@pytest.mark.parametrize("fs,dtype", [(10.0e6, 1), (20.0e6, 2), (20.0e6, 1), (5.0e6, 2), (2.5e6, 2)])
+@pytest.mark.parametrize("fs,dtype", [(10.0e6, 1), (20.0e6, 2), (20.0e6, 1), (5.0e6, 2), (2.5e6, 2),
+                                      (24.0e6, 2), (12.0e6, 1), (6.0e6, 2), (3.0e6, 2)])
 def test_acq_cluster_kernel_five_times_power_of_two(sdr, oracle, fs, dtype, pow2_env):
     """Windows of 2 500 .. 20 000 samples (1 ms at 2.5 .. 20 MS/s): the cluster kernel runs them as
-    5 x 1024, 5 x 2048, 5 x 4096 = 20 480 and 10 x 4096 = 40 960 points (radix-5 / radix-10 recombination across the
+    5 x 1024, 5 x 2048, 5 x 4096 = 20 480 and 10 x 4096 = 40 960 points, or 3 x 2048, 3 x 4096, 6 x 4096, 12 x 4096 (radix-5 / radix-10 recombination across the
     cluster, the last round of slice columns partial) instead of 2^15 / 2^16; with SDRB200_ACQ_POW2
     as 8 x 4096 / 16 x 4096.  Oracle: the reference's pcorrelator + argmax on the same window."""
     nsamp = int(fs * 1e-3)

@@ -52,8 +52,16 @@ def test_plan_shapes_of_the_baseline_configs(sdr, monkeypatch):
         (16368, 20, False): (655360, 4096, 160, False),  # C4: 2n = 654 720
         (16368, 10, False): (327680, 4096, 80, False),
         (16368, 40, False): (1310720, 8192, 160, False),
-        (2048, 40, False): (262144, 4096, 64, False),    # 5 * 2^15 has no radix: power of two
-        (26000, 1, False): (65536, 4096, 16, True),      # 2n = 52 000 > 40 960
+        (2048, 40, False): (196608, 4096, 48, False),    # 5 * 2^15 has no radix: 3 * 2^16
+        (26000, 1, False): (65536, 4096, 16, True),      # 2n = 52 000 > 49 152
+        (24000, 1, False): (49152, 4096, 12, True),      # 3 * 2^k: 0.75 of the next power of two
+        (12000, 1, False): (24576, 4096, 6, True),
+        (6000, 1, False): (12288, 4096, 3, True),
+        (3000, 1, False): (6144, 2048, 3, True),
+        (16368, 6, False): (196608, 4096, 48, False),    # 2n = 196 416
+        (16368, 12, False): (393216, 4096, 96, False),
+        (16368, 24, False): (786432, 4096, 192, False),
+        (16368, 48, False): (1572864, 8192, 192, False),
     }
     for (nsamp, ncoh, gpp), (M, L, R, fused) in want.items():
         got = sdr.plan_shape(nsamp, ncoh, gpp)
